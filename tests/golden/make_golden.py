@@ -1,0 +1,104 @@
+"""Generate the committed golden vectors from the UNMODIFIED reference.
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+Writes tests/golden/*.pt.  Every tensor is produced by the reference's own
+modules (cpc/model.py, cpc/transformers.py, cpc/criterion/criterion.py) built
+through the reference's factories (feature_loader.getEncoder/getAR,
+train.getCriterion), CPU fp32, eval mode (dropout off), seeds stated below.
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import ref_harness as rh  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+CRIT_SEED = 4321
+
+SMALL = dict(hiddenEncoder=32, hiddenGar=32, nPredicts=4, negativeSamplingExt=8, sizeWindow=2560)
+CASES = {
+    # name: (arg overrides, batch)
+    "tiny_lstm_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear"), 2),
+    "tiny_gru2_transformer": (dict(SMALL, arMode="GRU", nLevelsGRU=2, rnnMode="transformer", nPredicts=2), 2),
+    "tiny_transformer_ar_linear": (dict(SMALL, arMode="transformer", rnnMode="linear"), 3),
+    "tiny_lstm_reverse_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", cpc_mode="reverse"), 2),
+    "tiny_rnn_hneq_linear": (dict(SMALL, arMode="RNN", hiddenGar=24, rnnMode="linear", n_skipped=1), 2),
+}
+
+
+def synthetic_sequence(B, W, seed=1234):
+    g = torch.Generator().manual_seed(seed)
+    return 0.1 * torch.randn(B, 2, 1, W, generator=g)
+
+
+def fingerprint(state):
+    return {k: (float(v.double().sum()), float(v.double().abs().sum())) for k, v in state.items()
+            if v.dtype.is_floating_point}
+
+
+def run_case(name, over, B, full=True):
+    args = rh.reference_args(**over)
+    m, crit = rh.build_reference(args, seed=0)
+    seq = synthetic_sequence(B, args.sizeWindow)
+    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=False)
+    # the sampled indices, by replaying the reference's own sampleClean RNG calls
+    S = args.sizeWindow // 160
+    W = S - args.nPredicts
+    torch.manual_seed(CRIT_SEED)
+    n = args.negativeSamplingExt * W * B
+    batch_idx = torch.randint(0, B, (n,))
+    seq_idx = torch.randint(1, S, (n,))
+    # extIdx straight from the reference's sampleClean (re-run with the same seed)
+    torch.manual_seed(CRIT_SEED)
+    z_f = out["z"][B:]
+    if args.cpc_mode == "reverse":
+        z_f = torch.flip(z_f, [1])
+    sampled, _ = crit.sampleClean(z_f, W)
+    D = z_f.shape[-1]
+    # recover extIdx by matching? cheaper: recompute with the reference's exact expression
+    base = torch.arange(0, W).view(1, 1, W).expand(B, args.negativeSamplingExt, W).contiguous().view(-1)
+    ext = torch.remainder(seq_idx + base, S) + batch_idx * S
+    neg_ref = sampled[0][:, 1:]  # [B,NEG,W,D] gathered by the reference
+    assert torch.equal(neg_ref, z_f.contiguous().view(-1, D)[ext].view(B, -1, W, D)), \
+        "replayed indices do not reproduce the reference's gather"
+    state = rh.flat_state(m, crit)
+    state = {k: v for k, v in state.items() if v.dtype.is_floating_point
+             and not k.endswith(".mask") and not k.endswith(".z")}
+    fx = {
+        "args": {k: getattr(args, k) for k in ("hiddenEncoder", "hiddenGar", "nPredicts", "negativeSamplingExt",
+                                              "sizeWindow", "arMode", "nLevelsGRU", "rnnMode", "cpc_mode",
+                                              "abspos", "n_skipped")},
+        "B": B, "crit_seed": CRIT_SEED, "seq_seed": 1234, "init_seed": 0,
+        "loss": out["loss"], "acc": out["acc"],
+        "fingerprint": fingerprint(state),
+        "torch": torch.__version__,
+    }
+    if full:
+        fx.update({"batch_idx": batch_idx.int(), "seq_idx": seq_idx.int(), "ext_idx": ext.int(),
+                   "state": state, "sequence": seq, "c": out["c"], "z": out["z"], "grads": out["grads"]})
+    else:
+        g = out["grads"]
+        fx.update({
+            "c_slice": out["c"][:, ::16, ::32].clone(), "z_slice": out["z"][:, ::16, ::32].clone(),
+            "c_sum": float(out["c"].double().sum()), "z_sum": float(out["z"].double().sum()),
+            "grad_norm": {k: float(v.double().norm()) for k, v in g.items()},
+            "grad_slice": {k: v.flatten()[:: max(1, v.numel() // 64)][:64].clone() for k, v in g.items()},
+            "ext_sum": int(ext.sum()), "ext_head": ext[:2048].int().clone(),
+            "ext_weighted_sum": int((ext * (torch.arange(ext.numel()) % 1009)).sum()),
+        })
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "loss", [round(float(x), 5) for x in out["loss"].flatten()],
+          "acc", [round(float(x), 4) for x in out["acc"].flatten()])
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(os.cpu_count())
+    for name, (over, B) in CASES.items():
+        run_case(name, over, B)
+    # full-size default config (config 1 of BASELINE.json): summary only, weights by seed
+    run_case("default_b8_summary", dict(), 8, full=False)
+    run_case("default_linear_b8_summary", dict(rnnMode="linear"), 8, full=False)
