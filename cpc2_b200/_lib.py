@@ -110,3 +110,82 @@ def stream_ptr():
 
 def ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+class RowMap(ctypes.Structure):
+    _fields_ = [("seq_len", ctypes.c_int64), ("seq_stride", ctypes.c_int64), ("row_off", ctypes.c_int64)]
+
+
+class RowNormFwd(ctypes.Structure):
+    _fields_ = [
+        ("rows", ctypes.c_int64), ("C", ctypes.c_int), ("rows_per_group", ctypes.c_int64),
+        ("inp", ctypes.c_void_p), ("in_map", RowMap),
+        ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
+        ("out_bf16", ctypes.c_void_p), ("out_f32", ctypes.c_void_p), ("out_map", RowMap),
+        ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p),
+        ("eps", ctypes.c_float), ("unbiased", ctypes.c_int), ("relu", ctypes.c_int),
+    ]
+
+
+class RowNormBwd(ctypes.Structure):
+    _fields_ = [
+        ("rows", ctypes.c_int64), ("C", ctypes.c_int), ("rows_per_group", ctypes.c_int64),
+        ("dout", ctypes.c_void_p), ("dout_f32", ctypes.c_int), ("dout_map", RowMap),
+        ("dout2", ctypes.c_void_p), ("dout2_map", RowMap),
+        ("inp", ctypes.c_void_p), ("in_map", RowMap),
+        ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p), ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
+        ("dx_bf16", ctypes.c_void_p), ("dx_f32", ctypes.c_void_p), ("dx_map", RowMap), ("dx_accumulate", ctypes.c_int),
+        ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("dxsum", ctypes.c_void_p),
+        ("unbiased", ctypes.c_int), ("relu", ctypes.c_int),
+    ]
+
+
+class Conv0(ctypes.Structure):
+    _fields_ = [
+        ("N", ctypes.c_int), ("W", ctypes.c_int), ("C", ctypes.c_int), ("halo", ctypes.c_int), ("eps", ctypes.c_float),
+        ("x", ctypes.c_void_p), ("w", ctypes.c_void_p), ("b", ctypes.c_void_p), ("gamma", ctypes.c_void_p),
+        ("beta", ctypes.c_void_p),
+        ("out", ctypes.c_void_p), ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p),
+        ("dout", ctypes.c_void_p), ("dw", ctypes.c_void_p), ("db", ctypes.c_void_p), ("dgamma", ctypes.c_void_p),
+        ("dbeta", ctypes.c_void_p),
+    ]
+
+
+class Nce(ctypes.Structure):
+    _fields_ = [
+        ("K", ctypes.c_int), ("B", ctypes.c_int), ("W", ctypes.c_int), ("S", ctypes.c_int), ("NEG", ctypes.c_int),
+        ("ld", ctypes.c_int64),
+        ("logits", ctypes.c_void_p), ("ext", ctypes.c_void_p), ("weights", ctypes.c_void_p),
+        ("lse", ctypes.c_void_p), ("loss_sum", ctypes.c_void_p), ("hits", ctypes.c_void_p),
+        ("gscale", ctypes.c_void_p), ("dlogits", ctypes.c_void_p),
+    ]
+
+
+class Lstm(ctypes.Structure):
+    _fields_ = [
+        ("N", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int),
+        ("gx", ctypes.c_void_p), ("w_hh", ctypes.c_void_p), ("h0", ctypes.c_void_p), ("c0", ctypes.c_void_p),
+        ("h_pad", ctypes.c_void_p), ("out", ctypes.c_void_p), ("gates", ctypes.c_void_p), ("c_all", ctypes.c_void_p),
+        ("h_n", ctypes.c_void_p), ("c_n", ctypes.c_void_p),
+        ("dout", ctypes.c_void_p), ("dgates", ctypes.c_void_p),
+    ]
+
+
+class Attn(ctypes.Structure):
+    _fields_ = [
+        ("G", ctypes.c_int), ("Bt", ctypes.c_int), ("Hh", ctypes.c_int), ("S", ctypes.c_int), ("dk", ctypes.c_int),
+        ("scale", ctypes.c_float),
+        ("qkv", ctypes.c_void_p), ("gs_qkv", ctypes.c_int64), ("krel", ctypes.c_void_p),
+        ("out", ctypes.c_void_p), ("gs_out", ctypes.c_int64), ("probs", ctypes.c_void_p),
+        ("rng", ctypes.c_void_p), ("rng_site", ctypes.c_uint32), ("drop_p", ctypes.c_float),
+        ("dout", ctypes.c_void_p), ("dqkv", ctypes.c_void_p), ("dscore", ctypes.c_void_p), ("dkrel", ctypes.c_void_p),
+    ]
+
+
+# every symbol include/cpc_b200.h declares (checked by tests/test_abi.py)
+EXPORTED = [
+    "cpc_strerror", "cpc_version", "cpc_device_arch", "cpc_gemm_bf16", "cpc_rownorm_fwd", "cpc_rownorm_bwd",
+    "cpc_conv0_cn_relu_fwd", "cpc_conv0_cn_relu_bwd", "cpc_conv_weight_pack", "cpc_conv_wgrad_unpack",
+    "cpc_cast_f32_to_bf16", "cpc_cast_bf16_to_f32", "cpc_colsum", "cpc_groupsum", "cpc_neg_ext_index",
+    "cpc_nce_fwd", "cpc_nce_bwd", "cpc_lstm_fwd", "cpc_lstm_bwd", "cpc_attn_fwd", "cpc_attn_bwd",
+]

@@ -1,0 +1,285 @@
+// Causal, block-local multi-head attention with learned relative-position keys
+// (cpc/transformers.py:10-70 ScaledDotProductAttention, :73-104 MultiHeadAttention), forward and backward.
+//
+//   score[i,j] = (q_i.k_j + q_i.Krelpos[:, S-1-(i-j)]) / sqrt(dk)   for j <= i, -inf otherwise
+//   out_i      = sum_j dropout(softmax_j(score[i,:])) v_j
+//
+// The reference builds the relative term with a concatenate/view "skew" of a full [S,S] product; here the
+// shifted column is simply indexed.  One CTA per (group, sequence, head); the whole S x dk problem
+// (S <= 256, dk <= 64) sits in shared memory, one warp per query row.  Total work is ~2 GFLOP per step
+//  so CUDA cores suffice; the probabilities are kept (bf16, lower triangle) for the
+// backward instead of being recomputed.  Dropout masks come from a counter RNG keyed on
+// (seed, site, element index), so forward and backward regenerate the same mask with no mask tensor.
+#include "cpc_internal.h"
+#include "ptx.cuh"
+
+namespace cpc {
+
+struct AttnArgs {
+  const __nv_bfloat16* qkv;  // [G][T][3d]: q | k | v, head h at columns h*dk
+  long long gs_qkv;
+  const float* krel;  // [G][dk][S] or null
+  __nv_bfloat16* out;  // [G][T][d]
+  long long gs_out;
+  __nv_bfloat16* probs;  // [G][Bt][Hh][S][S] softmax probabilities before dropout
+  int S, dk, d, Bt, Hh;
+  float scale;
+  const unsigned long long* rng;
+  unsigned int site;
+  float drop_p;
+  // backward
+  const __nv_bfloat16* dout;  // [G][T][d]
+  __nv_bfloat16* dqkv;        // [G][T][3d]
+  __nv_bfloat16* dscore;      // scratch, same shape as probs
+  float* dkrel;               // [G][dk][S], atomically accumulated
+};
+
+__device__ __forceinline__ float ldf(const float* p) { return *p; }
+__device__ __forceinline__ float ldf(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ void stf(float* p, float v) { *p = v; }
+__device__ __forceinline__ void stf(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) attn_fwd_kernel(const AttnArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
+  const int S = a.S, dk = a.dk, SP = S | 1, DP = dk | 1;
+  T* Kt = reinterpret_cast<T*>(smem_dyn);  // [dk][SP]
+  T* Kr = Kt + dk * SP;                    // [dk][SP]
+  T* V = Kr + dk * SP;                     // [S][DP]
+  float* qrow = reinterpret_cast<float*>(V + S * DP + ((S * DP) & 1));  // [8][dk]
+  float* prow = qrow + 8 * dk;                                          // [8][S]
+  const int h = blockIdx.x, b = blockIdx.y, g = blockIdx.z;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const __nv_bfloat16* base = a.qkv + (long long)g * a.gs_qkv + (long long)b * S * 3 * a.d + h * dk;
+  for (int i = threadIdx.x; i < S * dk; i += blockDim.x) {
+    const int s = i / dk, c = i % dk;
+    stf(&Kt[c * SP + s], __bfloat162float(base[(long long)s * 3 * a.d + a.d + c]));
+    stf(&V[s * DP + c], __bfloat162float(base[(long long)s * 3 * a.d + 2 * a.d + c]));
+    if (a.krel != nullptr) {
+      const int cc = i / S, ss = i % S;
+      stf(&Kr[cc * SP + ss], a.krel[((long long)g * dk + cc) * S + ss]);
+    }
+  }
+  __syncthreads();
+  unsigned long long seed = 0;
+  uint32_t thresh = 0;
+  float dscale = 1.f;
+  if (a.rng != nullptr && a.drop_p > 0.f) {
+    seed = a.rng[0] + a.rng[1] * 0x632BE59BD9B4E019ull;
+    thresh = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    dscale = 1.f / (1.f - a.drop_p);
+  }
+  const long long pbase = (((long long)g * a.Bt + b) * a.Hh + h) * S * S;
+  float* q = qrow + warp * dk;
+  float* p = prow + warp * S;
+  for (int i = warp; i < S; i += 8) {
+    for (int c = lane; c < dk; c += 32) q[c] = __bfloat162float(base[(long long)i * 3 * a.d + c]);
+    __syncwarp();
+    float mx = -INFINITY;
+    for (int j = lane; j <= i; j += 32) {
+      float s = 0.f;
+      if (a.krel != nullptr) {
+        const int r = S - 1 - i + j;
+        for (int c = 0; c < dk; ++c) s = fmaf(q[c], ldf(&Kt[c * SP + j]) + ldf(&Kr[c * SP + r]), s);
+      } else {
+        for (int c = 0; c < dk; ++c) s = fmaf(q[c], ldf(&Kt[c * SP + j]), s);
+      }
+      s *= a.scale;
+      p[j] = s;
+      mx = fmaxf(mx, s);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int j = lane; j <= i; j += 32) {
+      const float e = __expf(p[j] - mx);
+      p[j] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    for (int j = lane; j <= i; j += 32) {
+      float pr = p[j] * inv;
+      if (a.probs != nullptr) a.probs[pbase + (long long)i * S + j] = __float2bfloat16(pr);
+      if (thresh != 0) pr = rng_u32(seed, a.site, pbase + (long long)i * S + j) >= thresh ? pr * dscale : 0.f;
+      p[j] = pr;
+    }
+    __syncwarp();
+    for (int c = lane; c < dk; c += 32) {
+      float acc = 0.f;
+      for (int j = 0; j <= i; ++j) acc = fmaf(p[j], ldf(&V[j * DP + c]), acc);
+      a.out[(long long)g * a.gs_out + ((long long)b * S + i) * a.d + h * dk + c] = __float2bfloat16(acc);
+    }
+    __syncwarp();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) attn_bwd_kernel(const AttnArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
+  const int S = a.S, dk = a.dk, SP = S | 1, DP = dk | 1;
+  T* Kt = reinterpret_cast<T*>(smem_dyn);  // [dk][SP]
+  T* Kr = Kt + dk * SP;                    // [dk][SP]
+  T* Vt = Kr + dk * SP;                    // [dk][SP]
+  T* Q = Vt + dk * SP;                     // [S][DP]
+  T* dO = Q + S * DP;                      // [S][DP]
+  float* dsrow = reinterpret_cast<float*>(dO + S * DP + ((3 * dk * SP + 2 * S * DP) & 1));  // [8][S]
+  const int h = blockIdx.x, b = blockIdx.y, g = blockIdx.z;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const __nv_bfloat16* base = a.qkv + (long long)g * a.gs_qkv + (long long)b * S * 3 * a.d + h * dk;
+  const long long obase = (long long)g * a.gs_out + (long long)b * S * a.d + h * dk;
+  for (int i = threadIdx.x; i < S * dk; i += blockDim.x) {
+    const int s = i / dk, c = i % dk;
+    stf(&Q[s * DP + c], __bfloat162float(base[(long long)s * 3 * a.d + c]));
+    stf(&Kt[c * SP + s], __bfloat162float(base[(long long)s * 3 * a.d + a.d + c]));
+    stf(&Vt[c * SP + s], __bfloat162float(base[(long long)s * 3 * a.d + 2 * a.d + c]));
+    stf(&dO[s * DP + c], __bfloat162float(a.dout[obase + (long long)s * a.d + c]));
+    if (a.krel != nullptr) {
+      const int cc = i / S, ss = i % S;
+      stf(&Kr[cc * SP + ss], a.krel[((long long)g * dk + cc) * S + ss]);
+    }
+  }
+  __syncthreads();
+  unsigned long long seed = 0;
+  uint32_t thresh = 0;
+  float dscale = 1.f;
+  if (a.rng != nullptr && a.drop_p > 0.f) {
+    seed = a.rng[0] + a.rng[1] * 0x632BE59BD9B4E019ull;
+    thresh = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    dscale = 1.f / (1.f - a.drop_p);
+  }
+  const long long pbase = (((long long)g * a.Bt + b) * a.Hh + h) * S * S;
+  float* ds = dsrow + warp * S;
+  __nv_bfloat16* dq_out = a.dqkv + (long long)g * a.gs_qkv + (long long)b * S * 3 * a.d + h * dk;
+
+  // ---- phase A: one warp per query row: dS row, dQ row
+  for (int i = warp; i < S; i += 8) {
+    float dsum = 0.f;
+    for (int c = lane; c < dk; c += 32)
+      dsum += ldf(&dO[i * DP + c]) * __bfloat162float(a.out[obase + (long long)i * a.d + c]);
+    dsum = warp_sum(dsum);  // D_i = dO_i . O_i = sum_j p~_ij dp~_ij
+    for (int j = lane; j <= i; j += 32) {
+      float dp = 0.f;
+      for (int c = 0; c < dk; ++c) dp = fmaf(ldf(&dO[i * DP + c]), ldf(&Vt[c * SP + j]), dp);
+      const long long e = pbase + (long long)i * S + j;
+      if (thresh != 0) dp = rng_u32(seed, a.site, e) >= thresh ? dp * dscale : 0.f;
+      const float pr = __bfloat162float(a.probs[e]);
+      const float v = pr * (dp - dsum) * a.scale;
+      ds[j] = v;
+      a.dscore[e] = __float2bfloat16(v);
+    }
+    __syncwarp();
+    for (int c = lane; c < dk; c += 32) {
+      float acc = 0.f;
+      if (a.krel != nullptr) {
+        for (int j = 0; j <= i; ++j) acc = fmaf(ds[j], ldf(&Kt[c * SP + j]) + ldf(&Kr[c * SP + S - 1 - i + j]), acc);
+      } else {
+        for (int j = 0; j <= i; ++j) acc = fmaf(ds[j], ldf(&Kt[c * SP + j]), acc);
+      }
+      dq_out[(long long)i * 3 * a.d + c] = __float2bfloat16(acc);
+    }
+    __syncwarp();
+  }
+  __syncthreads();  // dscore rows written by other warps of this CTA are now visible
+
+  // ---- phase B: one warp per key row j: dK_j, dV_j
+  for (int j = warp; j < S; j += 8) {
+    for (int c = lane; c < dk; c += 32) {
+      float dkacc = 0.f, dvacc = 0.f;
+      for (int i = j; i < S; ++i) {
+        const long long e = pbase + (long long)i * S + j;
+        const float dsv = __bfloat162float(a.dscore[e]);
+        float pr = __bfloat162float(a.probs[e]);
+        if (thresh != 0) pr = rng_u32(seed, a.site, e) >= thresh ? pr * dscale : 0.f;
+        dkacc = fmaf(dsv, ldf(&Q[i * DP + c]), dkacc);
+        dvacc = fmaf(pr, ldf(&dO[i * DP + c]), dvacc);
+      }
+      dq_out[(long long)j * 3 * a.d + a.d + c] = __float2bfloat16(dkacc);
+      dq_out[(long long)j * 3 * a.d + 2 * a.d + c] = __float2bfloat16(dvacc);
+    }
+  }
+  // ---- phase C: relative-position keys: dKrel[c][r] += sum_{i >= delta} dS[i][i-delta] * q_i[c], delta = S-1-r
+  if (a.krel != nullptr && a.dkrel != nullptr) {
+    for (int r = warp; r < S; r += 8) {
+      const int delta = S - 1 - r;
+      for (int c = lane; c < dk; c += 32) {
+        float acc = 0.f;
+        for (int i = delta; i < S; ++i)
+          acc = fmaf(__bfloat162float(a.dscore[pbase + (long long)i * S + (i - delta)]), ldf(&Q[i * DP + c]), acc);
+        red_add_f32(a.dkrel + ((long long)g * dk + c) * S + r, acc);
+      }
+    }
+  }
+}
+
+template <typename T>
+static size_t attn_smem(int S, int dk, bool bwd) {
+  const int SP = S | 1, DP = dk | 1;
+  if (!bwd) return (size_t)(2 * dk * SP + S * DP + 1) * sizeof(T) + (size_t)(8 * dk + 8 * S) * 4 + 16;
+  return (size_t)(3 * dk * SP + 2 * S * DP + 1) * sizeof(T) + (size_t)(8 * S) * 4 + 16;
+}
+
+}  // namespace cpc
+
+using namespace cpc;
+
+static int fill_attn(AttnArgs& a, const CpcAttn* d) {
+  if (d == nullptr || d->S <= 0 || d->S > 256 || d->dk <= 0 || d->dk > 64 || d->Hh <= 0 || d->Bt <= 0 || d->G <= 0)
+    return CPC_ERR_ARG;
+  if (d->qkv == nullptr || d->out == nullptr || d->probs == nullptr) return CPC_ERR_ARG;
+  a.qkv = static_cast<const __nv_bfloat16*>(d->qkv); a.gs_qkv = d->gs_qkv;
+  a.krel = static_cast<const float*>(d->krel);
+  a.out = static_cast<__nv_bfloat16*>(d->out); a.gs_out = d->gs_out;
+  a.probs = static_cast<__nv_bfloat16*>(d->probs);
+  a.S = d->S; a.dk = d->dk; a.d = d->dk * d->Hh; a.Bt = d->Bt; a.Hh = d->Hh;
+  a.scale = d->scale;
+  a.rng = static_cast<const unsigned long long*>(d->rng); a.site = d->rng_site; a.drop_p = d->drop_p;
+  a.dout = static_cast<const __nv_bfloat16*>(d->dout); a.dqkv = static_cast<__nv_bfloat16*>(d->dqkv);
+  a.dscore = static_cast<__nv_bfloat16*>(d->dscore); a.dkrel = static_cast<float*>(d->dkrel);
+  return CPC_OK;
+}
+
+template <typename KernT>
+static int set_smem(KernT kern, size_t bytes) {
+  if (bytes > 48 * 1024)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess)
+      return CPC_ERR_LAUNCH;
+  return CPC_OK;
+}
+
+extern "C" int cpc_attn_fwd(const CpcAttn* d, void* stream_) {
+  AttnArgs a;
+  int rc = fill_attn(a, d);
+  if (rc != CPC_OK) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  dim3 grid(a.Hh, a.Bt, d->G);
+  size_t sm = attn_smem<float>(a.S, a.dk, false);
+  if (sm <= 100 * 1024) {
+    if ((rc = set_smem(attn_fwd_kernel<float>, sm)) != CPC_OK) return rc;
+    attn_fwd_kernel<float><<<grid, 256, sm, stream>>>(a);
+  } else {
+    sm = attn_smem<__nv_bfloat16>(a.S, a.dk, false);
+    if ((rc = set_smem(attn_fwd_kernel<__nv_bfloat16>, sm)) != CPC_OK) return rc;
+    attn_fwd_kernel<__nv_bfloat16><<<grid, 256, sm, stream>>>(a);
+  }
+  return launch_status();
+}
+
+extern "C" int cpc_attn_bwd(const CpcAttn* d, void* stream_) {
+  AttnArgs a;
+  int rc = fill_attn(a, d);
+  if (rc != CPC_OK) return rc;
+  if (a.dout == nullptr || a.dqkv == nullptr || a.dscore == nullptr) return CPC_ERR_ARG;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  dim3 grid(a.Hh, a.Bt, d->G);
+  size_t sm = attn_smem<float>(a.S, a.dk, true);
+  if (sm <= 100 * 1024) {
+    if ((rc = set_smem(attn_bwd_kernel<float>, sm)) != CPC_OK) return rc;
+    attn_bwd_kernel<float><<<grid, 256, sm, stream>>>(a);
+  } else {
+    sm = attn_smem<__nv_bfloat16>(a.S, a.dk, true);
+    if (sm > 220 * 1024) return CPC_ERR_UNSUPPORTED;
+    if ((rc = set_smem(attn_bwd_kernel<__nv_bfloat16>, sm)) != CPC_OK) return rc;
+    attn_bwd_kernel<__nv_bfloat16><<<grid, 256, sm, stream>>>(a);
+  }
+  return launch_status();
+}

@@ -94,3 +94,153 @@ def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=N
         d.rng, d.rng_site, d.drop_p = rng.data_ptr(), rng_site, drop_p
     d.relu, d.accumulate = int(relu), int(accumulate)
     check(lib().cpc_gemm_bf16(ctypes.byref(d), stream_ptr()), "cpc_gemm_bf16")
+
+
+# --------------------------------------------------------------------------------------------------
+def _dp(t):
+    return t.data_ptr() if t is not None else None
+
+
+def rowmap(seq_len=0, seq_stride=0, row_off=0):
+    return _lib.RowMap(int(seq_len), int(seq_stride), int(row_off))
+
+
+def rownorm_fwd(inp, rows, C, gamma=None, beta=None, out_bf16=None, out_f32=None, mean=None, rstd=None,
+                in_map=None, out_map=None, rows_per_group=0, eps=1e-5, unbiased=False, relu=False):
+    d = _lib.RowNormFwd()
+    d.rows, d.C, d.rows_per_group = rows, C, rows_per_group
+    d.inp, d.in_map = _dp(inp), in_map or rowmap()
+    d.gamma, d.beta = _dp(gamma), _dp(beta)
+    d.out_bf16, d.out_f32, d.out_map = _dp(out_bf16), _dp(out_f32), out_map or rowmap()
+    d.mean, d.rstd = _dp(mean), _dp(rstd)
+    d.eps, d.unbiased, d.relu = eps, int(unbiased), int(relu)
+    check(lib().cpc_rownorm_fwd(ctypes.byref(d), stream_ptr()), "cpc_rownorm_fwd")
+
+
+def rownorm_bwd(dout, inp, mean, rstd, rows, C, gamma=None, beta=None, dx_bf16=None, dx_f32=None, dgamma=None,
+                dbeta=None, dxsum=None, dout2=None, dout_map=None, dout2_map=None, in_map=None, dx_map=None,
+                rows_per_group=0, unbiased=False, relu=False, dx_accumulate=False):
+    d = _lib.RowNormBwd()
+    d.rows, d.C, d.rows_per_group = rows, C, rows_per_group
+    d.dout, d.dout_f32, d.dout_map = _dp(dout), int(dout.dtype == torch.float32), dout_map or rowmap()
+    d.dout2, d.dout2_map = _dp(dout2), dout2_map or rowmap()
+    d.inp, d.in_map = _dp(inp), in_map or rowmap()
+    d.mean, d.rstd, d.gamma, d.beta = _dp(mean), _dp(rstd), _dp(gamma), _dp(beta)
+    d.dx_bf16, d.dx_f32, d.dx_map, d.dx_accumulate = _dp(dx_bf16), _dp(dx_f32), dx_map or rowmap(), int(dx_accumulate)
+    d.dgamma, d.dbeta, d.dxsum = _dp(dgamma), _dp(dbeta), _dp(dxsum)
+    d.unbiased, d.relu = int(unbiased), int(relu)
+    check(lib().cpc_rownorm_bwd(ctypes.byref(d), stream_ptr()), "cpc_rownorm_bwd")
+
+
+def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5):
+    d = _lib.Conv0()
+    d.N, d.W, d.C, d.halo, d.eps = N, W, C, halo, eps
+    d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
+    d.out, d.mean, d.rstd = _dp(out), _dp(mean), _dp(rstd)
+    check(lib().cpc_conv0_cn_relu_fwd(ctypes.byref(d), stream_ptr()), "cpc_conv0_cn_relu_fwd")
+
+
+def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, W, C, halo, eps=1e-5):
+    d = _lib.Conv0()
+    d.N, d.W, d.C, d.halo, d.eps = N, W, C, halo, eps
+    d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
+    d.mean, d.rstd = _dp(mean), _dp(rstd)
+    d.dout, d.dw, d.db, d.dgamma, d.dbeta = _dp(dout), _dp(dw), _dp(db), _dp(dgamma), _dp(dbeta)
+    check(lib().cpc_conv0_cn_relu_bwd(ctypes.byref(d), stream_ptr()), "cpc_conv0_cn_relu_bwd")
+
+
+def conv_weight_pack(w, wf, wd, Co, Ci, k, s):
+    check(lib().cpc_conv_weight_pack(ptr(w), ptr(wf), ptr(wd), Co, Ci, k, s, stream_ptr()), "cpc_conv_weight_pack")
+
+
+def conv_wgrad_unpack(dwf, dw, Co, Ci, k):
+    check(lib().cpc_conv_wgrad_unpack(ptr(dwf), ptr(dw), Co, Ci, k, stream_ptr()), "cpc_conv_wgrad_unpack")
+
+
+def cast_bf16(src, dst=None):
+    """fp32 -> bf16 copy of a contiguous tensor."""
+    assert src.dtype == torch.float32 and src.is_contiguous()
+    if dst is None:
+        dst = torch.empty(src.shape, dtype=BF16, device=src.device)
+    check(lib().cpc_cast_f32_to_bf16(ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr()), "cpc_cast_f32_to_bf16")
+    return dst
+
+
+def cast_f32(src, dst=None):
+    assert src.dtype == BF16 and src.is_contiguous()
+    if dst is None:
+        dst = torch.empty(src.shape, dtype=torch.float32, device=src.device)
+    check(lib().cpc_cast_bf16_to_f32(ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr()), "cpc_cast_bf16_to_f32")
+    return dst
+
+
+def colsum(inp, out, rows, C, ld, gs_in=0, groups=1):
+    check(lib().cpc_colsum(ptr(inp), int(inp.dtype == BF16), ptr(out), ctypes.c_int64(rows), C, ctypes.c_int64(ld),
+                           ctypes.c_int64(gs_in), groups, stream_ptr()), "cpc_colsum")
+
+
+def groupsum(inp, n, groups, out_f32=None, out_bf16=None, accumulate=False):
+    check(lib().cpc_groupsum(ptr(inp), int(inp.dtype == BF16), ptr(out_f32), ptr(out_bf16), ctypes.c_int64(n), groups,
+                             int(accumulate), stream_ptr()), "cpc_groupsum")
+
+
+def neg_ext_index(batch_idx, seq_idx, B, NEG, W, S):
+    ext = torch.empty_like(batch_idx)
+    check(lib().cpc_neg_ext_index(ptr(batch_idx), ptr(seq_idx), ptr(ext), B, NEG, W, S, stream_ptr()), "cpc_neg_ext_index")
+    return ext
+
+
+def _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld):
+    d = _lib.Nce()
+    d.K, d.B, d.W, d.S, d.NEG, d.ld = K, B, W, S, NEG, ld
+    d.logits, d.ext, d.weights, d.lse = _dp(logits), _dp(ext), _dp(weights), _dp(lse)
+    return d
+
+
+def nce_fwd(logits, ext, weights, lse, loss_sum, hits, K, B, W, S, NEG, ld):
+    d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
+    d.loss_sum, d.hits = _dp(loss_sum), _dp(hits)
+    check(lib().cpc_nce_fwd(ctypes.byref(d), stream_ptr()), "cpc_nce_fwd")
+
+
+def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld):
+    d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
+    d.gscale, d.dlogits = _dp(gscale), _dp(dlogits)
+    check(lib().cpc_nce_bwd(ctypes.byref(d), stream_ptr()), "cpc_nce_bwd")
+
+
+def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=None, c_all=None, h_n=None, c_n=None):
+    d = _lib.Lstm()
+    d.N, d.S, d.H = N, S, H
+    d.gx, d.w_hh, d.h0, d.c0 = _dp(gx), _dp(w_hh), _dp(h0), _dp(c0)
+    d.h_pad, d.out, d.gates, d.c_all, d.h_n, d.c_n = _dp(h_pad), _dp(out), _dp(gates), _dp(c_all), _dp(h_n), _dp(c_n)
+    check(lib().cpc_lstm_fwd(ctypes.byref(d), stream_ptr()), "cpc_lstm_fwd")
+
+
+def lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H, c0=None):
+    d = _lib.Lstm()
+    d.N, d.S, d.H = N, S, H
+    d.w_hh, d.c0, d.gates, d.c_all, d.dout, d.dgates = _dp(w_hh), _dp(c0), _dp(gates), _dp(c_all), _dp(dout), _dp(dgates)
+    check(lib().cpc_lstm_bwd(ctypes.byref(d), stream_ptr()), "cpc_lstm_bwd")
+
+
+def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p):
+    d = _lib.Attn()
+    d.G, d.Bt, d.Hh, d.S, d.dk = G, Bt, Hh, S, dk
+    d.scale = 1.0 / (dk ** 0.5)
+    d.qkv, d.gs_qkv, d.krel = _dp(qkv), Bt * S * 3 * Hh * dk, _dp(krel)
+    d.out, d.gs_out, d.probs = _dp(out), Bt * S * Hh * dk, _dp(probs)
+    if rng is not None and drop_p > 0:
+        d.rng, d.rng_site, d.drop_p = _dp(rng), site, drop_p
+    return d
+
+
+def attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
+    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
+    check(lib().cpc_attn_fwd(ctypes.byref(d), stream_ptr()), "cpc_attn_fwd")
+
+
+def attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
+    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
+    d.dout, d.dqkv, d.dscore, d.dkrel = _dp(dout), _dp(dqkv), _dp(dscore), _dp(dkrel)
+    check(lib().cpc_attn_bwd(ctypes.byref(d), stream_ptr()), "cpc_attn_bwd")

@@ -82,6 +82,126 @@ typedef struct {
 
 int cpc_gemm_bf16(const CpcGemmDesc* desc, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Row normalisation: ChannelNorm(+ReLU) of the encoder (cpc/model.py:52-60,103-107: mean / UNBIASED
+ * variance over channels, eps inside the sqrt, affine [1,C,1]) and nn.LayerNorm of the transformer
+ * blocks (cpc/transformers.py:124,130).  Rows are [C] bf16 vectors; a CpcRowMap places logical row r
+ * at buffer row (r / seq_len) * seq_stride + row_off + r % seq_len (seq_len == 0: identity), which is
+ * how the zero-halo channels-last conv buffers are addressed.  C must be 32 * {1,2,4,8,16}.
+ */
+typedef struct { int64_t seq_len, seq_stride, row_off; } CpcRowMap;
+
+typedef struct {
+  int64_t rows; int C;
+  int64_t rows_per_group;            /* gamma/beta are [groups][C]; 0 => one group */
+  const void* in; CpcRowMap in_map;  /* bf16 */
+  const void* gamma; const void* beta; /* fp32, may be null */
+  void* out_bf16; void* out_f32; CpcRowMap out_map; /* either may be null */
+  void* mean; void* rstd;            /* fp32 [rows], saved for backward (may be null) */
+  float eps; int unbiased; int relu;
+} CpcRowNormFwd;
+
+typedef struct {
+  int64_t rows; int C;
+  int64_t rows_per_group;
+  const void* dout; int dout_f32; CpcRowMap dout_map; /* gradient w.r.t. the output, bf16 or fp32 */
+  const void* dout2; CpcRowMap dout2_map;             /* optional second fp32 gradient, added */
+  const void* in; CpcRowMap in_map;                   /* forward input (bf16) */
+  const void* mean; const void* rstd; const void* gamma; const void* beta;
+  void* dx_bf16; void* dx_f32; CpcRowMap dx_map; int dx_accumulate;
+  void* dgamma; void* dbeta;  /* fp32 [groups][C], atomically accumulated (pre-zeroed by caller) */
+  void* dxsum;                /* fp32 [groups][C] column sums of dx = bias gradient of the producer */
+  int unbiased; int relu;
+} CpcRowNormBwd;
+
+int cpc_rownorm_fwd(const CpcRowNormFwd* desc, void* stream);
+int cpc_rownorm_bwd(const CpcRowNormBwd* desc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * conv0 (1 -> C channels, k 10, stride 5, pad 3) + ChannelNorm + ReLU fused (cpc/model.py:85,103).
+ * x fp32 [N, W]; out bf16 [N, L0 + 2*halo, C] channels-last with `halo` zero rows either side
+ * (L0 = (W - 4) / 5 + 1); mean/rstd fp32 [N*L0].  Backward recomputes the conv from x and accumulates
+ * dw [C,10], db, dgamma, dbeta (fp32, pre-zeroed) from dout (same layout as out).
+ */
+typedef struct {
+  int N, W, C, halo; float eps;
+  const void* x; const void* w; const void* b; const void* gamma; const void* beta;
+  void* out; void* mean; void* rstd;
+  const void* dout; void* dw; void* db; void* dgamma; void* dbeta;
+} CpcConv0;
+
+int cpc_conv0_cn_relu_fwd(const CpcConv0* desc, void* stream);
+int cpc_conv0_cn_relu_bwd(const CpcConv0* desc, void* stream);
+
+/* conv weight fp32 [Co,Ci,k] (k == 2*s) -> bf16 GEMM operands: wf [Co, k*Ci] (forward / wgrad) and
+ * wd [s*Ci, 2*Co] (dgrad; may be null).  cpc_conv_wgrad_unpack is the inverse for the fp32 gradient. */
+int cpc_conv_weight_pack(const void* w, void* wf, void* wd, int Co, int Ci, int k, int s, void* stream);
+int cpc_conv_wgrad_unpack(const void* dwf, void* dw, int Co, int Ci, int k, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Streaming helpers. */
+int cpc_cast_f32_to_bf16(const void* in, void* out, int64_t n, void* stream);
+int cpc_cast_bf16_to_f32(const void* in, void* out, int64_t n, void* stream);
+/* out[g][c] += sum_r in[g][r][c] (fp32 out, pre-initialised): bias gradients */
+int cpc_colsum(const void* in, int in_is_bf16, void* out, int64_t rows, int C, int64_t ld, int64_t gs_in,
+               int groups, void* stream);
+/* out[i] (+)= sum_g in[g][i] */
+int cpc_groupsum(const void* in, int in_is_bf16, void* out_f32, void* out_bf16, int64_t n, int groups,
+                 int accumulate, void* stream);
+/* extIdx = ((seqIdx + t) mod S) + batchIdx*S, int64, flat (b,n,t) order -- criterion.py:256-266 */
+int cpc_neg_ext_index(const void* batch_idx, const void* seq_idx, void* ext, int B, int NEG, int W, int S,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * InfoNCE gather + cross entropy + argmax (criterion.py:345-357) on the all-pairs logits
+ * logits fp32 [K][B*W][ld] (ld >= B*S), ext int64 [B][NEG][W], weights fp32 [B*W] or null.
+ * fwd: lse [K][B*W]; loss_sum[k] += sum_rows w*(lse - l_pos); hits[k] += #rows with argmax == positive.
+ * bwd: dlogits bf16 [K][B*W][ld] = gscale[k] * w/(B*W) * (softmax - onehot0), dense, zeros elsewhere.
+ */
+typedef struct {
+  int K, B, W, S, NEG; int64_t ld;
+  const void* logits; const void* ext; const void* weights;
+  void* lse; void* loss_sum; void* hits;
+  const void* gscale; void* dlogits;
+} CpcNce;
+
+int cpc_nce_fwd(const CpcNce* desc, void* stream);
+int cpc_nce_bwd(const CpcNce* desc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * LSTM recurrence (nn.LSTM as built at cpc/model.py:171-173, gate order i,f,g,o), H in {32,64,128,256,512}.
+ * gx fp32 [N,S,4H] = x.W_ih^T + b_ih + b_hh (a cpc_gemm_bf16 call); w_hh bf16 [4H,H].
+ * fwd writes out fp32 [N,S,H], h_pad bf16 [N,S+1,H] (row 0 = h0), gates bf16 [N,S,4H] (post-activation),
+ * c_all fp32 [N,S,H], h_n / c_n fp32 [N,H] (any may be null).  bwd consumes dout fp32 [N,S,H] and writes
+ * dgates bf16 [N,S,4H] (gradient w.r.t. the gate pre-activations); dW / dx follow as GEMMs.
+ */
+typedef struct {
+  int N, S, H;
+  const void* gx; const void* w_hh; const void* h0; const void* c0;
+  void* h_pad; void* out; void* gates; void* c_all; void* h_n; void* c_n;
+  const void* dout; void* dgates;
+} CpcLstm;
+
+int cpc_lstm_fwd(const CpcLstm* desc, void* stream);
+int cpc_lstm_bwd(const CpcLstm* desc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Causal relative-position multi-head attention (cpc/transformers.py:52-70, :97-104).
+ * qkv bf16 [G][Bt*S][3*d] (q|k|v, head h at columns h*dk), krel fp32 [G][dk][S] or null,
+ * out bf16 [G][Bt*S][d], probs bf16 [G][Bt][Hh][S][S] (saved), S <= 256, dk <= 64.
+ * bwd: dout bf16 like out -> dqkv bf16 like qkv, dkrel fp32 [G][dk][S] (accumulated), dscore scratch.
+ */
+typedef struct {
+  int G, Bt, Hh, S, dk; float scale;
+  const void* qkv; int64_t gs_qkv; const void* krel;
+  void* out; int64_t gs_out; void* probs;
+  const void* rng; uint32_t rng_site; float drop_p;
+  const void* dout; void* dqkv; void* dscore; void* dkrel;
+} CpcAttn;
+
+int cpc_attn_fwd(const CpcAttn* desc, void* stream);
+int cpc_attn_bwd(const CpcAttn* desc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

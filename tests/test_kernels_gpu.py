@@ -1,0 +1,375 @@
+"""Kernel-level parity tests (need a B200): every C-ABI op against a plain fp32 PyTorch statement of
+the same arithmetic on identical inputs (bf16-rounded where the kernel consumes bf16), and against the
+CPU oracle (oracle/cpc_oracle.py) for the criterion math.  Tolerances are stated per test; integer /
+index outputs are bit exact."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+BF = torch.bfloat16
+
+
+@pytest.fixture(scope="module")
+def K():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from cpc2_b200 import kernels
+    return kernels
+
+
+def bf(x):
+    return x.to(BF)
+
+
+def close(got, ref, rtol, atol, name=""):
+    got, ref = got.float(), ref.float()
+    err = (got - ref).abs()
+    bound = atol + rtol * ref.abs()
+    assert torch.isfinite(got).all(), f"{name}: non-finite"
+    bad = (err > bound)
+    assert not bad.any(), f"{name}: max err {err.max().item():.4g} (ref max {ref.abs().max().item():.4g}), " \
+                          f"{bad.sum().item()} / {bad.numel()} out of tolerance"
+
+
+def cos(a, b):
+    return F.cosine_similarity(a.float().flatten(), b.float().flatten(), dim=0).item()
+
+
+# ------------------------------------------------------------------------------------------ GEMM
+@pytest.mark.parametrize("M,N,Kd", [(128, 64, 64), (300, 256, 192), (928, 768, 256), (100, 32, 32)])
+def test_gemm_nt(K, M, N, Kd):
+    torch.manual_seed(0)
+    a, b = bf(torch.randn(M, Kd, device="cuda")), bf(torch.randn(N, Kd, device="cuda"))
+    out = torch.empty(M, N, device="cuda")
+    K.gemm(K.kmajor(a), K.kmajor(b), M, N, Kd, out_f32=out)
+    close(out, a.float() @ b.float().t(), 1e-4, 1e-3, "gemm nt")  # fp32 accumulate of exact bf16 products
+
+
+def test_gemm_transposed_operands_and_slabs(K):
+    torch.manual_seed(1)
+    S_, R, M, N = 4, 100, 256, 320
+    at, bt = bf(torch.randn(S_, R, M, device="cuda")), bf(torch.randn(S_, R, N, device="cuda"))
+    out = torch.ones(M, N, device="cuda")
+    A = K.View(at, M, R, S_, M, R * M, major=1)
+    B = K.View(bt, N, R, S_, N, R * N, major=1)
+    K.gemm(A, B, M, N, S_ * R, k_per_slab=R, k_splits=3, out_f32=out, accumulate=True)
+    close(out, 1 + torch.einsum("srm,srn->mn", at.float(), bt.float()), 1e-4, 1e-3, "gemm tn slabs splitk")
+
+
+# ------------------------------------------------------------------------------------------ row norms
+@pytest.mark.parametrize("C", [32, 256, 512])
+def test_channelnorm_relu_fwd_bwd(K, C):
+    torch.manual_seed(2)
+    N, L, halo = 3, 40, 2
+    y = bf(torch.randn(N * L, C, device="cuda") * 2 + 0.3)
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    out = torch.zeros(N, L + 2 * halo, C, device="cuda", dtype=BF)
+    out32 = torch.zeros(N * L, C, device="cuda")
+    mean, rstd = torch.empty(N * L, device="cuda"), torch.empty(N * L, device="cuda")
+    K.rownorm_fwd(y, N * L, C, gamma, beta, out_bf16=out, mean=mean, rstd=rstd,
+                  out_map=K.rowmap(L, L + 2 * halo, halo), unbiased=True, relu=True)
+    K.rownorm_fwd(y, N * L, C, gamma, beta, out_f32=out32, unbiased=True, relu=True)
+    yr = y.float().requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    m = yr.mean(1, keepdim=True)
+    v = yr.var(1, keepdim=True)  # unbiased, cpc/model.py:55
+    ref = torch.relu((yr - m) * torch.rsqrt(v + 1e-5) * g_ + b_)
+    close(out32, ref, 1e-4, 1e-4, "channelnorm fwd f32")
+    close(out[:, halo:halo + L].reshape(N * L, C), ref, 1e-2, 1e-2, "channelnorm fwd bf16")
+    assert out[:, :halo].abs().max() == 0 and out[:, halo + L:].abs().max() == 0  # halos untouched
+    dout = torch.randn(N, L + 2 * halo, C, device="cuda")
+    ref.backward(dout[:, halo:halo + L].reshape(N * L, C).to(BF).float())
+    dx = torch.zeros(N, L + 2, C, device="cuda", dtype=BF)
+    dg, db, dsum = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    K.rownorm_bwd(bf(dout), y, mean, rstd, N * L, C, gamma, beta, dx_bf16=dx, dgamma=dg, dbeta=db, dxsum=dsum,
+                  dout_map=K.rowmap(L, L + 2 * halo, halo), dx_map=K.rowmap(L, L + 2, 1), unbiased=True, relu=True)
+    close(dx[:, 1:1 + L].reshape(N * L, C), yr.grad, 2e-2, 2e-2, "channelnorm dx")
+    close(dg, g_.grad, 1e-3, 1e-2, "channelnorm dgamma")
+    close(db, b_.grad, 1e-3, 1e-2, "channelnorm dbeta")
+    close(dsum, yr.grad.sum(0), 1e-2, 3e-2, "channelnorm dxsum")
+
+
+def test_layernorm_groups_fwd_bwd(K):
+    torch.manual_seed(3)
+    G, T, C = 3, 50, 256
+    x = bf(torch.randn(G * T, C, device="cuda"))
+    gamma, beta = torch.rand(G, C, device="cuda") + 0.5, torch.randn(G, C, device="cuda") * 0.1
+    out = torch.empty(G * T, C, device="cuda")
+    mean, rstd = torch.empty(G * T, device="cuda"), torch.empty(G * T, device="cuda")
+    K.rownorm_fwd(x, G * T, C, gamma, beta, out_f32=out, mean=mean, rstd=rstd, rows_per_group=T)
+    xr = x.float().view(G, T, C).requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    ref = torch.stack([F.layer_norm(xr[g], (C,), g_[g], b_[g]) for g in range(G)])
+    close(out.view(G, T, C), ref, 1e-4, 1e-4, "layernorm fwd")
+    dout = torch.randn(G, T, C, device="cuda")
+    ref.backward(dout)
+    dx = torch.empty(G * T, C, device="cuda")
+    dg, db = torch.zeros(G, C, device="cuda"), torch.zeros(G, C, device="cuda")
+    K.rownorm_bwd(dout.view(G * T, C), x, mean, rstd, G * T, C, gamma, beta, dx_f32=dx, dgamma=dg, dbeta=db,
+                  rows_per_group=T)
+    close(dx.view(G, T, C), xr.grad, 1e-3, 1e-3, "layernorm dx")
+    close(dg, g_.grad, 1e-3, 1e-3, "layernorm dgamma")
+    close(db, b_.grad, 1e-3, 1e-3, "layernorm dbeta")
+
+
+# ------------------------------------------------------------------------------------------ conv0
+@pytest.mark.parametrize("C", [32, 256])
+def test_conv0_fused_fwd_bwd(K, C):
+    from oracle import cpc_oracle as oc
+    torch.manual_seed(4)
+    N, W, halo = 3, 1600, 2
+    L0 = (W - 4) // 5 + 1
+    x = 0.1 * torch.randn(N, W, device="cuda")
+    conv = torch.nn.Conv1d(1, C, 10, stride=5, padding=3).cuda()
+    gamma = (torch.rand(C, device="cuda") + 0.5).requires_grad_(True)
+    beta = (torch.randn(C, device="cuda") * 0.1).requires_grad_(True)
+    out = torch.zeros(N, L0 + 2 * halo, C, device="cuda", dtype=BF)
+    mean, rstd = torch.empty(N * L0, device="cuda"), torch.empty(N * L0, device="cuda")
+    K.conv0_fwd(x, conv.weight, conv.bias, gamma, beta, out, mean, rstd, N, W, C, halo)
+    ref = F.relu(oc.channel_norm(conv(x.unsqueeze(1)), gamma.view(1, C, 1), beta.view(1, C, 1)))  # [N,C,L0]
+    close(out[:, halo:halo + L0], ref.permute(0, 2, 1), 1e-2, 1e-2, "conv0 fwd")
+    dout = bf(torch.randn(N, L0 + 2 * halo, C, device="cuda"))
+    ref.backward(dout[:, halo:halo + L0].float().permute(0, 2, 1))
+    dw, db = torch.zeros(C, 10, device="cuda"), torch.zeros(C, device="cuda")
+    dg, dbe = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    K.conv0_bwd(x, conv.weight, conv.bias, gamma, beta, mean, rstd, dout, dw, db, dg, dbe, N, W, C, halo)
+    close(dw, conv.weight.grad.view(C, 10), 2e-3, 2e-3 * conv.weight.grad.abs().max().item(), "conv0 dw")
+    close(db, conv.bias.grad, 2e-3, 2e-3 * conv.bias.grad.abs().max().item(), "conv0 db")
+    close(dg, gamma.grad, 2e-3, 2e-3 * gamma.grad.abs().max().item(), "conv0 dgamma")
+    close(dbe, beta.grad, 2e-3, 2e-3 * beta.grad.abs().max().item(), "conv0 dbeta")
+
+
+# ------------------------------------------------------------------------------------------ conv1..4 as GEMMs
+@pytest.mark.parametrize("C,k,s,p,L", [(64, 8, 4, 2, 256), (256, 4, 2, 1, 128), (32, 4, 2, 1, 32)])
+def test_conv_implicit_gemm_fwd_dgrad_wgrad(K, C, k, s, p, L):
+    torch.manual_seed(5)
+    Nb = 3
+    Lout = L // s
+    Lp = L + 2 * p
+    assert Lp == s * (Lout + 1)
+    conv = torch.nn.Conv1d(C, C, k, stride=s, padding=p).cuda()
+    x = bf(torch.randn(Nb, L, C, device="cuda"))
+    xp = torch.zeros(Nb, Lp, C, device="cuda", dtype=BF)
+    xp[:, p:p + L] = x
+    wf = torch.empty(C, k * C, device="cuda", dtype=BF)
+    wd = torch.empty(s * C, 2 * C, device="cuda", dtype=BF)
+    K.conv_weight_pack(conv.weight, wf, wd, C, C, k, s)
+    assert torch.equal(wf, bf(conv.weight.permute(0, 2, 1).reshape(C, k * C)))
+    # forward
+    y = torch.empty(Nb, Lout, C, device="cuda")
+    A = K.View(xp, k * C, Lout, Nb, s * C, Lp * C, major=0, gmul=1)
+    K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=Nb, out_f32=y, bias=conv.bias.detach())
+    xr = x.float().permute(0, 2, 1).requires_grad_(True)
+    wq = conv.weight.detach().to(BF).float().requires_grad_(True)
+    ref = F.conv1d(xr, wq, conv.bias, stride=s, padding=p)
+    close(y, ref.permute(0, 2, 1), 1e-3, 1e-3, "conv fwd")
+    dy = bf(torch.randn(Nb, Lout, C, device="cuda"))
+    ref.backward(dy.float().permute(0, 2, 1))
+    # dgrad: rows [dy[t-1], dy[t]] . [W_hi; W_lo] -> padded dx
+    dyp = torch.zeros(Nb, Lout + 2, C, device="cuda", dtype=BF)
+    dyp[:, 1:1 + Lout] = dy
+    dxp = torch.empty(Nb, Lp, C, device="cuda", dtype=BF)
+    A = K.View(dyp, 2 * C, Lout + 1, Nb, C, (Lout + 2) * C, major=0, gmul=1)
+    K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=Nb, out_bf16=(dxp, s * C, Lp * C))
+    close(dxp[:, p:p + L], xr.grad.permute(0, 2, 1), 2e-2, 2e-2 * xr.grad.abs().max().item(), "conv dgrad")
+    # wgrad: dWf[co, j] = sum_{n,t} dy[n,t,co] * im2col[n,t,j]; both operands MN-major, slabs = sequences
+    dwf = torch.zeros(C, k * C, device="cuda")
+    A = K.View(dyp, C, Lout + 2, Nb, C, (Lout + 2) * C, major=1, row_off=1)
+    B = K.View(xp, k * C, Lout, Nb, s * C, Lp * C, major=1)
+    K.gemm(A, B, C, k * C, Nb * Lout, k_per_slab=Lout, k_splits=2, out_f32=dwf, accumulate=True)
+    dw = torch.empty_like(conv.weight)
+    K.conv_wgrad_unpack(dwf, dw, C, C, k)
+    close(dw, wq.grad, 1e-3, 1e-3 * wq.grad.abs().max().item(), "conv wgrad")
+
+
+# ------------------------------------------------------------------------------------------ helpers
+def test_streaming_helpers(K):
+    torch.manual_seed(6)
+    x = torch.randn(100003, device="cuda")
+    assert torch.equal(K.cast_bf16(x), x.to(BF))
+    assert torch.equal(K.cast_f32(x.to(BF)), x.to(BF).float())
+    G, R, C = 3, 500, 96
+    m = torch.randn(G, R, C, device="cuda")
+    out = torch.zeros(G, C, device="cuda")
+    K.colsum(m, out, R, C, C, R * C, G)
+    close(out, m.sum(1), 1e-4, 1e-3, "colsum f32")
+    out = torch.zeros(G, C, device="cuda")
+    K.colsum(bf(m), out, R, C, C, R * C, G)
+    close(out, bf(m).float().sum(1), 1e-4, 1e-3, "colsum bf16")
+    o32 = torch.ones(R * C, device="cuda")
+    K.groupsum(m, R * C, G, out_f32=o32, accumulate=True)
+    close(o32, 1 + m.sum(0).flatten(), 1e-5, 1e-5, "groupsum")
+
+
+@pytest.mark.parametrize("B,S,Kp,NEG", [(8, 128, 12, 128), (2, 16, 4, 8), (3, 256, 12, 64)])
+def test_neg_ext_index_bit_exact(K, B, S, Kp, NEG):
+    from oracle import cpc_oracle as oc
+    W = S - Kp
+    g = torch.Generator(device="cuda").manual_seed(11)
+    n = B * NEG * W
+    bi = torch.randint(0, B, (n,), device="cuda", generator=g)
+    si = torch.randint(1, S, (n,), device="cuda", generator=g)
+    ext = K.neg_ext_index(bi, si, B, NEG, W, S)
+    ref = oc.negative_ext_index(bi.cpu(), si.cpu(), B, S, W, NEG)
+    assert ext.dtype == torch.int64 and torch.equal(ext.cpu(), ref)
+
+
+# ------------------------------------------------------------------------------------------ InfoNCE tail
+@pytest.mark.parametrize("B,S,Kp,NEG,weighted", [(8, 128, 12, 128, False), (2, 16, 4, 8, True), (4, 64, 6, 200, False)])
+def test_nce_fwd_bwd(K, B, S, Kp, NEG, weighted):
+    from oracle import cpc_oracle as oc
+    torch.manual_seed(7)
+    W = S - Kp
+    T, BS = B * W, B * S
+    logits = torch.randn(Kp, T, BS, device="cuda") * 2
+    # force exact ties between the positive and a negative on some rows: torch.max keeps index 0
+    n = B * NEG * W
+    bi = torch.randint(0, B, (n,), device="cuda")
+    si = torch.randint(1, S, (n,), device="cuda")
+    ext = K.neg_ext_index(bi, si, B, NEG, W, S)
+    weights = (torch.rand(T, device="cuda") + 0.5) if weighted else None
+    lse = torch.empty(Kp, T, device="cuda")
+    loss, hits = torch.zeros(Kp, device="cuda"), torch.zeros(Kp, device="cuda")
+    K.nce_fwd(logits, ext, weights, lse, loss, hits, Kp, B, W, S, NEG, BS)
+    # reference: gather the NEG+1 scalars exactly as criterion.py:267-284 would see them
+    lg = logits.clone().requires_grad_(True)
+    e = ext.view(B, NEG, W)
+    ref_loss, ref_hits, total = [], [], 0
+    for k in range(Kp):
+        rows = lg[k].view(B, W, BS)
+        pos_col = (torch.arange(B, device="cuda").view(B, 1) * S + torch.arange(W, device="cuda").view(1, W) + k + 1)
+        pos = rows.gather(2, pos_col.unsqueeze(2))                       # [B,W,1]
+        neg = rows.gather(2, e.permute(0, 2, 1))                         # [B,W,NEG]
+        full = torch.cat([pos, neg], dim=2).reshape(T, NEG + 1)
+        ce = F.cross_entropy(full, torch.zeros(T, dtype=torch.long, device="cuda"), reduction="none")
+        if weights is not None:
+            ce = ce * weights
+        ref_loss.append(ce.mean())
+        ref_hits.append((full.max(1)[1] == 0).sum())
+        total = total + ce.mean() * (k + 1)  # distinct upstream gradient per k
+    close(loss / T, torch.stack(ref_loss), 1e-5, 1e-5, "nce loss")
+    assert torch.equal(hits.long(), torch.stack(ref_hits)), "argmax hits must be bit exact"
+    total.backward()
+    gscale = torch.arange(1, Kp + 1, device="cuda", dtype=torch.float32)
+    dl = torch.empty(Kp, T, BS, device="cuda", dtype=BF)
+    K.nce_bwd(logits, ext, weights, lse, gscale, dl, Kp, B, W, S, NEG, BS)
+    close(dl, lg.grad, 1e-2, 1e-2 * lg.grad.abs().max().item(), "nce dlogits")
+
+
+def test_nce_tie_goes_to_positive(K):
+    B, S, Kp, NEG = 1, 8, 2, 4
+    W = S - Kp
+    logits = torch.zeros(Kp, W, S, device="cuda")  # all equal -> argmax must be class 0 for every row
+    bi = torch.zeros(B * NEG * W, dtype=torch.long, device="cuda")
+    si = torch.randint(1, S, (B * NEG * W,), device="cuda")
+    ext = K.neg_ext_index(bi, si, B, NEG, W, S)
+    lse = torch.empty(Kp, W, device="cuda")
+    loss, hits = torch.zeros(Kp, device="cuda"), torch.zeros(Kp, device="cuda")
+    K.nce_fwd(logits, ext, None, lse, loss, hits, Kp, B, W, S, NEG, S)
+    assert hits.tolist() == [W] * Kp
+    close(loss / W, torch.full((Kp,), math.log(NEG + 1), device="cuda"), 1e-6, 1e-6, "uniform loss = ln(NEG+1)")
+
+
+# ------------------------------------------------------------------------------------------ LSTM
+@pytest.mark.parametrize("H,N,S", [(32, 5, 12), (64, 16, 9), (256, 16, 128), (256, 20, 16), (128, 3, 7), (512, 4, 6)])
+def test_lstm_recurrence_fwd_bwd(K, H, N, S):
+    torch.manual_seed(8)
+    lstm = torch.nn.LSTM(H, H, batch_first=True).cuda()
+    with torch.no_grad():
+        lstm.weight_hh_l0.copy_(lstm.weight_hh_l0.to(BF).float())  # kernel consumes bf16 W_hh
+    x = torch.randn(N, S, H, device="cuda")
+    gx = (x @ lstm.weight_ih_l0.t() + lstm.bias_ih_l0 + lstm.bias_hh_l0).detach().contiguous()
+    w_hh = lstm.weight_hh_l0.detach().to(BF).contiguous()
+    out = torch.empty(N, S, H, device="cuda")
+    h_pad = torch.empty(N, S + 1, H, device="cuda", dtype=BF)
+    gates = torch.empty(N, S, 4 * H, device="cuda", dtype=BF)
+    c_all = torch.empty(N, S, H, device="cuda")
+    h_n, c_n = torch.empty(N, H, device="cuda"), torch.empty(N, H, device="cuda")
+    K.lstm_fwd(gx, w_hh, N, S, H, h_pad=h_pad, out=out, gates=gates, c_all=c_all, h_n=h_n, c_n=c_n)
+    xr = x.clone().requires_grad_(True)
+    ref, (rh, rc) = lstm(xr)
+    # h is carried in bf16 between steps: tolerance is bf16 epsilon accumulated over the chain
+    close(out, ref, 2e-2, 2e-2, "lstm out")
+    close(h_n, rh[0], 2e-2, 2e-2, "lstm h_n")
+    close(c_n, rc[0], 2e-2, 3e-2, "lstm c_n")
+    close(h_pad[:, 1:], ref, 2e-2, 2e-2, "lstm h_pad")
+    assert h_pad[:, 0].abs().max() == 0
+    dout = torch.randn(N, S, H, device="cuda")
+    ref.backward(dout)
+    dgates = torch.empty(N, S, 4 * H, device="cuda", dtype=BF)
+    K.lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H)
+    # finish the backward with plain torch on the kernel's gate gradients
+    dg = dgates.float()
+    dx = dg @ lstm.weight_ih_l0
+    dw_ih = torch.einsum("nsg,nsh->gh", dg, x)
+    hprev = torch.cat([torch.zeros(N, 1, H, device="cuda"), ref.detach()[:, :-1]], dim=1)
+    dw_hh = torch.einsum("nsg,nsh->gh", dg, hprev)
+    assert cos(dx, xr.grad) > 0.999, cos(dx, xr.grad)
+    assert cos(dw_ih, lstm.weight_ih_l0.grad) > 0.999
+    assert cos(dw_hh, lstm.weight_hh_l0.grad) > 0.999
+    assert cos(dg.sum((0, 1)), lstm.bias_ih_l0.grad) > 0.999
+    close(dx, xr.grad, 5e-2, 5e-2 * xr.grad.abs().max().item(), "lstm dx")
+
+
+# ------------------------------------------------------------------------------------------ attention
+@pytest.mark.parametrize("G,Bt,Hh,S,dk,relpos", [(2, 3, 8, 116, 32, True), (1, 2, 8, 12, 4, True),
+                                                 (1, 2, 4, 128, 64, False), (1, 1, 8, 244, 64, True)])
+def test_attention_fwd_bwd(K, G, Bt, Hh, S, dk, relpos):
+    from oracle import cpc_oracle as oc
+    torch.manual_seed(9)
+    d = Hh * dk
+    qkv = bf(torch.randn(G, Bt * S, 3 * d, device="cuda"))
+    krel = (torch.rand(G, dk, S, device="cuda") - 0.5) * (2 / math.sqrt(dk)) if relpos else None
+    out = torch.empty(G, Bt * S, d, device="cuda", dtype=BF)
+    probs = torch.zeros(G, Bt, Hh, S, S, device="cuda", dtype=BF)
+    K.attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk)
+    qr = qkv.float().requires_grad_(True)
+    kr = krel.clone().requires_grad_(True) if relpos else None
+    refs = []
+    for g in range(G):
+        x = qr[g].view(Bt, S, 3, Hh, dk)
+        def heads(i):
+            return x[:, :, i].transpose(1, 2).reshape(Bt * Hh, S, dk)
+        o = oc.relpos_causal_attention(heads(0).cpu(), heads(1).cpu(), heads(2).cpu(),
+                                       None if kr is None else kr[g].cpu(), S)
+        refs.append(o.view(Bt, Hh, S, dk).transpose(1, 2).reshape(Bt * S, d))
+    ref = torch.stack(refs).cuda()
+    close(out, ref, 2e-2, 2e-2, "attention out")
+    dout = bf(torch.randn(G, Bt * S, d, device="cuda"))
+    ref.backward(dout.float())
+    dqkv = torch.empty_like(qkv)
+    dscore = torch.empty_like(probs)
+    dkrel = torch.zeros(G, dk, S, device="cuda") if relpos else None
+    K.attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk)
+    assert cos(dqkv, qr.grad) > 0.999, cos(dqkv, qr.grad)
+    close(dqkv, qr.grad, 5e-2, 3e-2 * qr.grad.abs().max().item(), "attention dqkv")
+    if relpos:
+        assert cos(dkrel, kr.grad) > 0.999
+        close(dkrel, kr.grad, 5e-2, 3e-2 * kr.grad.abs().max().item(), "attention dkrel")
+
+
+def test_attention_dropout_consistent(K):
+    torch.manual_seed(10)
+    G, Bt, Hh, S, dk = 1, 2, 8, 32, 8
+    d = Hh * dk
+    qkv = bf(torch.randn(G, Bt * S, 3 * d, device="cuda"))
+    rng = torch.tensor([99, 3], device="cuda", dtype=torch.int64)
+    out0 = torch.empty(G, Bt * S, d, device="cuda", dtype=BF)
+    out1 = torch.empty_like(out0)
+    probs = torch.zeros(G, Bt, Hh, S, S, device="cuda", dtype=BF)
+    K.attn_fwd(qkv, None, out0, probs, G, Bt, Hh, S, dk)
+    K.attn_fwd(qkv, None, out1, probs, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=0.5)
+    assert not torch.equal(out0, out1)
+    out2 = torch.empty_like(out0)
+    K.attn_fwd(qkv, None, out2, probs, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=0.5)
+    assert torch.equal(out1, out2)  # same (seed, step, site) -> same mask
+    # first row attends only to itself: either kept (scaled by 2) or dropped
+    v0 = qkv.view(Bt, S, 3, Hh, dk)[:, 0, 2].float()
+    o = out1.view(Bt, S, Hh, dk)[:, 0].float()
+    ok = ((o - 2 * v0).abs().amax(-1) < 0.1) | (o.abs().amax(-1) == 0)
+    assert ok.all()
