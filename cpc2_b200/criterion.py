@@ -1,0 +1,274 @@
+"""Drop-in for the reference's cpc/criterion/criterion.py on the training hot path:
+PredictionNetwork and CPCUnsupersivedCriterion (criterion.py:97-173, 193-363) with the same constructor
+signatures, attribute names, public methods and state_dict keys.
+
+What changes is the formulation, not the result.  The reference gathers [B, NEG+1, W, D] candidates per
+prediction step and reduces a broadcast product of that size (~15 GB of HBM traffic per step at the default
+config).  Here the K heads run as grouped tcgen05 GEMMs, the logits of ALL (token, frame) pairs are one
+batched GEMM pred_k . z^T (tensor cores, ~46 MB, L2 resident) and a gather kernel picks the NEG+1 scalars
+each row needs -- same sampled indices (the two torch.randint draws are issued in the reference's order on
+the same generator), same cross entropy, same first-max argmax.
+"""
+import torch
+import torch.nn as nn
+
+from . import kernels as K
+from . import ops
+from .ops import BF16
+from .transformers import TransformerStack, buildTransformerAR
+
+
+class PredictionNetwork(nn.Module):
+    """cpc/criterion/criterion.py:97-173.  rnnMode 'transformer' (default) or the bias-free Linear that any
+    other non-recurrent string selects in the reference ('linear', None, False)."""
+
+    def __init__(self, nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=None, dropout=False, sizeInputSeq=116,
+                 transformer_pruning=0):
+        super().__init__()
+        self.predictors = nn.ModuleList()
+        self.RESIDUAL_STD = 0.01
+        self.dimOutputAR = dimOutputAR
+        self.dimOutputEncoder = dimOutputEncoder
+        self.sizeInputSeq = sizeInputSeq
+        if dropout:
+            raise NotImplementedError("cpc2_b200: --dropout on the predictions is not on the accelerated path")
+        self.dropout = None
+        if rnnMode in ("RNN", "LSTM", "ffd", "conv4", "conv8", "conv12"):
+            raise NotImplementedError(f"cpc2_b200: prediction heads rnnMode='{rnnMode}' have no sm_100a kernels; "
+                                      "use 'transformer' (default) or 'linear'")
+        self.transformer = rnnMode == 'transformer'
+        for i in range(nPredicts):
+            if self.transformer:
+                self.predictors.append(buildTransformerAR(dimOutputEncoder, dimOutputAR, nLayers=1,
+                                                          sizeSeq=sizeInputSeq, abspos=False))
+            else:
+                self.predictors.append(nn.Linear(dimOutputAR, dimOutputEncoder, bias=False))
+                if dimOutputEncoder > dimOutputAR:
+                    residual = dimOutputEncoder - dimOutputAR
+                    self.predictors[-1].weight.data.copy_(torch.cat([
+                        torch.randn(dimOutputAR, dimOutputAR),
+                        self.RESIDUAL_STD * torch.randn(residual, dimOutputAR)], dim=0))
+        self._engine = None
+
+    def engine(self):
+        if self._engine is None:
+            if self.transformer:
+                eng = TransformerStack([p[0] for p in self.predictors])
+            else:
+                eng = LinearHeads([p for p in self.predictors])
+            object.__setattr__(self, "_engine", eng)
+        return self._engine
+
+    def forward(self, c, candidates):
+        """Reference signature (criterion.py:152-173): list of [B, n_cand, W, D] candidates -> list of
+        [B, n_cand, W] scores.  Used by getCosineDistances; the training path goes through the fused
+        criterion function instead."""
+        assert (len(candidates) == len(self.predictors))
+        eng = self.engine()
+        preds = _HeadsFn.apply(c, eng, self.training, *eng.arena.params)  # [K, B, W, D] fp32
+        return [(preds[k].unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(len(self.predictors))]
+
+
+class LinearHeads:
+    """K bias-free Linear heads on the same input: one grouped GEMM."""
+
+    def __init__(self, linears):
+        self.G = len(linears)
+        self.dout, self.d = linears[0].weight.shape
+        if self.d % 8 or self.dout % 8:
+            raise NotImplementedError("LinearHeads: dimensions must be multiples of 8")
+        self.arena = ops.Arena([l.weight for l in linears])
+
+    def forward(self, x, T, shared, training, want_f32=False):
+        G, d, do = self.G, self.d, self.dout
+        w16 = self.arena.span(self.arena.bf16(), 0, G, (G, do, d))
+        out = torch.empty(G, T, do, device=x.device, dtype=BF16)
+        out32 = torch.empty(G, T, do, device=x.device) if want_f32 else None
+        ops.linear_fwd(x, w16, T, do, d, groups=G, x_shared=True, out_bf16=out, out_f32=out32)
+        return out, out32, dict(x=x, w16=w16, T=T)
+
+    def backward(self, sv, dout):
+        G, d, do, T = self.G, self.d, self.dout, sv["T"]
+        dev = dout.device
+        if dout.dtype != BF16:
+            dout = K.cast_bf16(dout.contiguous().float())
+        dout = dout.view(G, T, do)
+        gflat = torch.zeros(self.arena.numel, device=dev)
+        dw = self.arena.span(gflat, 0, G, (G, do, d))
+        ops.linear_dw(dout, sv["x"], dw, T, do, d, groups=G, x_shared=True)
+        dx = torch.empty(T, d, device=dev)
+        A = K.View(dout, do, T, G, do, T * do, major=0, gmul=0)
+        B = K.View(sv["w16"], d, do, G, d, do * d, major=1, gmul=0)
+        K.gemm(A, B, T, d, G * do, k_per_slab=do, out_f32=dx)
+        return dx, gflat
+
+
+class _HeadsFn(torch.autograd.Function):
+    """All K heads on c [B, W, H] -> predictions [K, B, W, D] fp32 (public PredictionNetwork.forward path)."""
+
+    @staticmethod
+    def forward(ctx, c, eng, training, *params):
+        B, W, H = c.shape
+        xb = K.cast_bf16(c.detach().contiguous().float()).view(B * W, H)
+        out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True)
+        ctx.eng, ctx.saved, ctx.shape = eng, saved, (B, W, H)
+        return out32.view(eng.G, B, W, eng.dout)
+
+    @staticmethod
+    def backward(ctx, dout):
+        eng = ctx.eng
+        B, W, H = ctx.shape
+        dx, gflat = eng.backward(ctx.saved, dout.contiguous().float().view(eng.G, B * W, eng.dout))
+        return (dx.view(B, W, H), None, None, *eng.arena.grad_views(gflat))
+
+
+class BaseCriterion(nn.Module):
+    """cpc/criterion/criterion.py:176-182."""
+
+    def warmUp(self):
+        return False
+
+    def update(self):
+        return
+
+
+class CPCUnsupersivedCriterion(BaseCriterion):
+    """cpc/criterion/criterion.py:193-363."""
+
+    def __init__(self, nPredicts, dimOutputAR, dimOutputEncoder, negativeSamplingExt, mode=None, rnnMode=False,
+                 dropout=False, nSpeakers=0, sizeInputSeq=116, multihead_rnn=False, transformer_pruning=0,
+                 n_skipped=0, growth_rate=None, inflection_point_x=None):
+        super().__init__()
+        if multihead_rnn:
+            raise NotImplementedError("cpc2_b200: --multihead_rnn is a 'next' row (SURVEY 8f.3), not built yet")
+        self.wPrediction = PredictionNetwork(nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=rnnMode,
+                                             dropout=dropout, sizeInputSeq=sizeInputSeq - nPredicts)
+        self.nSkipped = n_skipped
+        self.nPredicts = nPredicts
+        self.negativeSamplingExt = negativeSamplingExt
+        self.lossCriterion = nn.CrossEntropyLoss(reduction='none')
+        self.growth_rate = growth_rate
+        self.inflection_point_x = inflection_point_x
+        self.weighting_function = lambda x: 0.00001 + 1 / (1 + torch.exp(-growth_rate * (x - inflection_point_x)))
+        if mode not in [None, "reverse"]:
+            raise ValueError("Invalid mode")
+        self.mode = mode
+
+    # -------------------------------------------------------------------------------------- sampling
+    def sampleIndices(self, batchSize, nNegativeExt, windowSize, device):
+        """The two RNG draws of sampleClean (criterion.py:247-255) in the reference's order, then the
+        integer index arithmetic (:256-266) on the GPU.  Returns extIdx int64 [B*NEG*W], flat (b, n, t)."""
+        n = self.negativeSamplingExt * windowSize * batchSize
+        batchIdx = torch.randint(low=0, high=batchSize, size=(n,), device=device)
+        seqIdx = torch.randint(low=1, high=nNegativeExt, size=(n,), device=device)
+        return K.neg_ext_index(batchIdx, seqIdx, batchSize, self.negativeSamplingExt, windowSize, nNegativeExt)
+
+    def sampleClean(self, encodedData, windowSize):
+        """Reference-compatible materialised sampling (criterion.py:237-286): list of K tensors
+        [B, NEG+1, W, D] and the zero labels.  Kept for API parity; the training path never calls it."""
+        batchSize, nNegativeExt, dimEncoded = encodedData.size()
+        extIdx = self.sampleIndices(batchSize, nNegativeExt, windowSize, encodedData.device)
+        negExt = encodedData.contiguous().view(-1, dimEncoded)[extIdx].view(
+            batchSize, self.negativeSamplingExt, windowSize, dimEncoded)
+        labelLoss = torch.zeros((batchSize * windowSize), dtype=torch.long, device=encodedData.device)
+        outputs = []
+        for k in range(1, self.nPredicts + 1):
+            posSeq = encodedData[:, k:k + windowSize].reshape(batchSize, 1, windowSize, dimEncoded)
+            outputs.append(torch.cat((posSeq, negExt), dim=1))
+        return outputs, labelLoss
+
+    def getPrediction(self, cFeature, encodedData, label):
+        """criterion.py:291-302 (materialised; API parity)."""
+        if self.mode == "reverse":
+            encodedData = torch.flip(encodedData, [1])
+            cFeature = torch.flip(cFeature, [1])
+        windowSize = cFeature.size(1) - self.nPredicts
+        cFeature = cFeature[:, :windowSize]
+        sampledData, labelLoss = self.sampleClean(encodedData, windowSize)
+        return self.wPrediction(cFeature, sampledData), labelLoss
+
+    def getCosineDistances(self, cFeature, encodedData):
+        """criterion.py:304-327: scores of the positives only."""
+        if self.mode == "reverse":
+            encodedData = torch.flip(encodedData, [1])
+            cFeature = torch.flip(cFeature, [1])
+        batchSize, seqSize, _ = cFeature.size()
+        dimEncoded = encodedData.size(2)
+        windowSize = seqSize - self.nPredicts
+        cFeature = cFeature[:, :windowSize]
+        out = [encodedData[:, k:k + windowSize].reshape(batchSize, 1, windowSize, dimEncoded)
+               for k in range(1, self.nPredicts + 1)]
+        return self.wPrediction(cFeature, out)
+
+    # -------------------------------------------------------------------------------------- forward
+    def forward(self, cFeature, encodedData, label, signal_quality=None):
+        """criterion.py:329-363 -> (losses [1, K - n_skipped], acc [1, K - n_skipped])."""
+        ops.require_cuda(cFeature, encodedData)
+        if self.mode == "reverse":
+            encodedData = torch.flip(encodedData, [1])
+            cFeature = torch.flip(cFeature, [1])
+        batchSize, seqSize, _ = cFeature.size()
+        windowSize = seqSize - self.nPredicts
+        extIdx = self.sampleIndices(batchSize, encodedData.size(1), windowSize, encodedData.device)
+        weights = None
+        if signal_quality is not None:
+            q = self.weighting_function(signal_quality.mean(dim=1))
+            weights = q.unsqueeze(1).repeat(1, windowSize).contiguous().view(-1).float()
+        eng = self.wPrediction.engine()
+        losses, acc = _CriterionFn.apply(cFeature, encodedData, extIdx, weights, eng, self.nPredicts,
+                                         self.negativeSamplingExt, self.training, *eng.arena.params)
+        return losses[:, self.nSkipped:], acc[:, self.nSkipped:]
+
+
+class _CriterionFn(torch.autograd.Function):
+    """heads -> all-pairs logits GEMM -> gather + CE + argmax, and the matching backward."""
+
+    @staticmethod
+    def forward(ctx, c, z, ext, weights, eng, Kp, NEG, training, *params):
+        B, S, H = c.shape
+        D = z.shape[2]
+        W = S - Kp
+        T, BS = B * W, B * S
+        dev = c.device
+        if BS % 8 != 0:
+            raise ValueError("B*S must be a multiple of 8")
+        cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
+        zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
+        preds, _, saved = eng.forward(cw, T, True, training)
+        logits = torch.empty(Kp, T, BS, device=dev)
+        ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D)
+        lse = torch.empty(Kp, T, device=dev)
+        loss_sum = torch.zeros(Kp, device=dev)
+        hits = torch.zeros(Kp, device=dev)
+        K.nce_fwd(logits, ext, weights, lse, loss_sum, hits, Kp, B, W, S, NEG, BS)
+        ctx.eng, ctx.saved = eng, saved
+        ctx.t = (preds, zb, logits, lse, ext, weights)
+        ctx.dims = (B, S, H, D, W, Kp, NEG)
+        losses = (loss_sum / T).view(1, Kp)
+        acc = (hits / (W * B)).view(1, Kp)
+        ctx.mark_non_differentiable(acc)
+        return losses, acc
+
+    @staticmethod
+    def backward(ctx, dloss, dacc):
+        B, S, H, D, W, Kp, NEG = ctx.dims
+        T, BS = B * W, B * S
+        preds, zb, logits, lse, ext, weights = ctx.t
+        eng = ctx.eng
+        dev = dloss.device
+        gscale = dloss.reshape(Kp).contiguous().float()
+        dlog = torch.empty(Kp, T, BS, device=dev, dtype=BF16)
+        K.nce_bwd(logits, ext, weights, lse, gscale, dlog, Kp, B, W, S, NEG, BS)
+        # dpred_k = dlog_k . z / D
+        dpred = torch.empty(Kp, T, D, device=dev, dtype=BF16)
+        K.gemm(K.kmajor(dlog), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_bf16=dpred, alpha=1.0 / D)
+        # dz = sum_k dlog_k^T . pred_k / D   (reduction over (k, token))
+        dz = torch.zeros(BS, D, device=dev)
+        A = K.View(dlog, BS, T, Kp, BS, T * BS, major=1, gmul=0)
+        Bv = K.View(preds, D, T, Kp, D, T * D, major=1, gmul=0)
+        K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
+               accumulate=True, alpha=1.0 / D)
+        dcw, gflat = eng.backward(ctx.saved, dpred)
+        dc = torch.zeros(B, S, H, device=dev)
+        dc[:, :W] = dcw.view(B, W, H)
+        return (dc, dz.view(B, S, D), None, None, None, None, None, None, *eng.arena.grad_views(gflat))

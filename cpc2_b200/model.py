@@ -1,0 +1,356 @@
+"""Drop-in for the reference's cpc/model.py on the training hot path: ChannelNorm, CPCEncoder, CPCAR,
+CPCModel -- same constructor signatures, attribute names and state_dict keys (cpc/model.py:27-108,
+158-207, 279-390), compute in libcpc_b200.so (sm_100a).  There is no eager / CPU fallback.
+
+Data layout in HBM: activations are bf16 CHANNELS-LAST [N, L + halo, C]; each layer's output buffer carries
+the zero halo rows the next strided conv needs, so the im2col matrix of a conv is an overlapping-row TMA
+view of its input and `encodedData = gEncoder(x).permute(0, 2, 1)` (model.py:382) is a free view.
+"""
+import torch
+import torch.nn as nn
+
+from . import kernels as K
+from . import ops
+from .ops import BF16
+
+# (kernel, stride, padding) of conv0..4, cpc/model.py:85-94
+GEOMETRY = ((10, 5, 3), (8, 4, 2), (4, 2, 1), (4, 2, 1), (4, 2, 1))
+
+
+class ChannelNorm(nn.Module):
+    """cpc/model.py:27-60.  Parameter container + standalone forward on [N, C, L] fp32."""
+
+    def __init__(self, numFeatures, epsilon=1e-05, affine=True):
+        super().__init__()
+        if affine:
+            self.weight = nn.parameter.Parameter(torch.Tensor(1, numFeatures, 1))
+            self.bias = nn.parameter.Parameter(torch.Tensor(1, numFeatures, 1))
+        else:
+            self.weight = None
+            self.bias = None
+        self.epsilon = epsilon
+        self.p = 0
+        self.affine = affine
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        if self.affine:
+            torch.nn.init.ones_(self.weight)
+            torch.nn.init.zeros_(self.bias)
+
+    def forward(self, x):
+        ops.require_cuda(x)
+        return _ChannelNormFn.apply(x, self.weight, self.bias, self.epsilon)
+
+
+class _ChannelNormFn(torch.autograd.Function):
+    """Standalone ChannelNorm (no ReLU) on NCL input; the encoder uses the fused kernels instead."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        N, C, L = x.shape
+        xcl = K.cast_bf16(x.permute(0, 2, 1).contiguous())
+        out = torch.empty(N, L, C, device=x.device, dtype=torch.float32)
+        mean = torch.empty(N * L, device=x.device)
+        rstd = torch.empty(N * L, device=x.device)
+        g = weight.detach().reshape(C).contiguous() if weight is not None else None
+        b = bias.detach().reshape(C).contiguous() if bias is not None else None
+        K.rownorm_fwd(xcl, N * L, C, g, b, out_f32=out, mean=mean, rstd=rstd, eps=eps, unbiased=True)
+        ctx.save_for_backward(xcl, mean, rstd, g, b)
+        ctx.shape = (N, C, L)
+        return out.permute(0, 2, 1)
+
+    @staticmethod
+    def backward(ctx, dout):
+        xcl, mean, rstd, g, b = ctx.saved_tensors
+        N, C, L = ctx.shape
+        d = dout.permute(0, 2, 1).contiguous().float()
+        dx = torch.empty(N, L, C, device=d.device)
+        dg = torch.zeros(C, device=d.device) if g is not None else None
+        db = torch.zeros(C, device=d.device) if g is not None else None
+        K.rownorm_bwd(d, xcl, mean, rstd, N * L, C, g, b, dx_f32=dx, dgamma=dg, dbeta=db, unbiased=True)
+        return (dx.permute(0, 2, 1), None if dg is None else dg.view(1, C, 1),
+                None if db is None else db.view(1, C, 1), None)
+
+
+class CPCEncoder(nn.Module):
+    """cpc/model.py:63-108: five strided Conv1d, each followed by ChannelNorm and ReLU."""
+
+    def __init__(self, sizeHidden=512, normMode="layerNorm"):
+        super().__init__()
+        validModes = ["batchNorm", "instanceNorm", "ID", "layerNorm"]
+        if normMode not in validModes:
+            raise ValueError(f"Norm mode must be in {validModes}")
+        if normMode != "layerNorm":
+            raise NotImplementedError("cpc2_b200 implements the default normMode='layerNorm' (ChannelNorm) path only")
+        self.dimEncoded = sizeHidden
+        self.conv0 = nn.Conv1d(1, sizeHidden, 10, stride=5, padding=3)
+        self.batchNorm0 = ChannelNorm(sizeHidden)
+        self.conv1 = nn.Conv1d(sizeHidden, sizeHidden, 8, stride=4, padding=2)
+        self.batchNorm1 = ChannelNorm(sizeHidden)
+        self.conv2 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
+        self.batchNorm2 = ChannelNorm(sizeHidden)
+        self.conv3 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
+        self.batchNorm3 = ChannelNorm(sizeHidden)
+        self.conv4 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
+        self.batchNorm4 = ChannelNorm(sizeHidden)
+        self.DOWNSAMPLING = 160
+
+    def getDimOutput(self):
+        return self.conv4.out_channels
+
+    def _params(self):
+        ps = []
+        for i in range(5):
+            conv, norm = getattr(self, f"conv{i}"), getattr(self, f"batchNorm{i}")
+            ps += [conv.weight, conv.bias, norm.weight, norm.bias]
+        return ps
+
+    def forward(self, x):
+        """x [N, 1, W] fp32 (W multiple of 160) -> [N, C, W/160] fp32 (a view of channels-last memory)."""
+        ops.require_cuda(x)
+        return _EncoderFn.apply(x, *self._params())
+
+
+class _EncoderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, *params):
+        N, one, W = x.shape
+        if one != 1 or W % 160 != 0:
+            raise ValueError("CPCEncoder expects [N, 1, W] with W a multiple of 160")
+        C = params[0].shape[0]
+        dev = x.device
+        x2 = x.detach().reshape(N, W).contiguous().float()
+        p = [t.detach() for t in params]
+        L = [W // 5, W // 20, W // 40, W // 80, W // 160]
+        pad_next = [GEOMETRY[i + 1][2] for i in range(4)] + [0]
+        acts, ys, means, rstds, packed = [], [None], [], [], [None]
+        # layer 0: fused conv + ChannelNorm + ReLU straight from the waveform
+        a = torch.empty(N, L[0] + 2 * pad_next[0], C, device=dev, dtype=BF16)
+        a[:, :pad_next[0]].zero_()
+        a[:, pad_next[0] + L[0]:].zero_()
+        mean = torch.empty(N * L[0], device=dev)
+        rstd = torch.empty(N * L[0], device=dev)
+        K.conv0_fwd(x2, p[0], p[1], p[2], p[3], a, mean, rstd, N, W, C, pad_next[0])
+        acts.append(a)
+        means.append(mean)
+        rstds.append(rstd)
+        z32 = None
+        for l in range(1, 5):
+            k, s, pd = GEOMETRY[l]
+            w, b, g, be = p[4 * l:4 * l + 4]
+            wf = torch.empty(C, k * C, device=dev, dtype=BF16)
+            wd = torch.empty(s * C, 2 * C, device=dev, dtype=BF16)
+            K.conv_weight_pack(w, wf, wd, C, C, k, s)
+            packed.append((wf, wd))
+            Lin, Lout = L[l - 1], L[l]
+            Lp = Lin + 2 * pd
+            y = torch.empty(N * Lout, C, device=dev, dtype=BF16)
+            A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
+            K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
+            hn = pad_next[l]
+            a = torch.empty(N, Lout + 2 * hn, C, device=dev, dtype=BF16)
+            if hn:
+                a[:, :hn].zero_()
+                a[:, hn + Lout:].zero_()
+            mean = torch.empty(N * Lout, device=dev)
+            rstd = torch.empty(N * Lout, device=dev)
+            if l == 4:
+                z32 = torch.empty(N, Lout, C, device=dev, dtype=torch.float32)
+            K.rownorm_fwd(y, N * Lout, C, g.reshape(C), be.reshape(C), out_bf16=a, out_f32=z32, mean=mean,
+                          rstd=rstd, out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True, relu=True)
+            ys.append(y)
+            acts.append(a)
+            means.append(mean)
+            rstds.append(rstd)
+        ctx.geom = (N, W, C, L, pad_next)
+        ctx.x2 = x2
+        ctx.acts, ctx.ys, ctx.means, ctx.rstds, ctx.packed = acts, ys, means, rstds, packed
+        ctx.p = p
+        return z32.permute(0, 2, 1)
+
+    @staticmethod
+    def backward(ctx, dz):
+        N, W, C, L, pad_next = ctx.geom
+        p = ctx.p
+        dev = dz.device
+        grads = [None] * 20
+        d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
+        dout, dout_map = d, None
+        for l in range(4, 0, -1):
+            k, s, pd = GEOMETRY[l]
+            w, b, g, be = p[4 * l:4 * l + 4]
+            wf, wd = ctx.packed[l]
+            Lin, Lout = L[l - 1], L[l]
+            Lp = Lin + 2 * pd
+            dy = torch.empty(N, Lout + 2, C, device=dev, dtype=BF16)
+            dy[:, 0].zero_()
+            dy[:, Lout + 1].zero_()
+            dg = torch.zeros(C, device=dev)
+            db = torch.zeros(C, device=dev)
+            dcb = torch.zeros(C, device=dev)
+            K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
+                          dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,
+                          dx_map=K.rowmap(Lout, Lout + 2, 1), unbiased=True, relu=True)
+            # wgrad: dWf[co, kk*C+ci] = sum_{n,t} dy[n,t,co] * a_pad[n, t*s+kk, ci]
+            dwf = torch.zeros(C, k * C, device=dev)
+            A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
+            B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
+            K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout, k_splits=ops.auto_splits(C, k * C, N * Lout, 1, Lout),
+                   out_f32=dwf, accumulate=True)
+            dw = torch.empty(C, C, k, device=dev)
+            K.conv_wgrad_unpack(dwf, dw, C, C, k)
+            grads[4 * l:4 * l + 4] = [dw, dcb, dg.view(1, C, 1), db.view(1, C, 1)]
+            # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
+            dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
+            A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
+            K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
+            dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
+        dw0 = torch.zeros(C, 10, device=dev)
+        db0 = torch.zeros(C, device=dev)
+        dg0 = torch.zeros(C, device=dev)
+        dbe0 = torch.zeros(C, device=dev)
+        K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
+                    pad_next[0])
+        grads[0:4] = [dw0.view(C, 1, 10), db0, dg0.view(1, C, 1), dbe0.view(1, C, 1)]
+        return (None, *grads)
+
+
+class CPCAR(nn.Module):
+    """cpc/model.py:158-207.  `baseNet` is an nn.LSTM/GRU/RNN used as the PARAMETER CONTAINER (cuDNN-layout
+    weight_ih_l*, weight_hh_l*, bias_ih_l*, bias_hh_l*, so reference checkpoints load unchanged); the
+    recurrence itself runs in the cluster-resident LSTM kernels."""
+
+    def __init__(self, dimEncoded, dimOutput, keepHidden, nLevelsGRU, mode="GRU", reverse=False):
+        super().__init__()
+        self.RESIDUAL_STD = 0.1
+        if mode == "LSTM":
+            self.baseNet = nn.LSTM(dimEncoded, dimOutput, num_layers=nLevelsGRU, batch_first=True)
+        elif mode == "RNN":
+            self.baseNet = nn.RNN(dimEncoded, dimOutput, num_layers=nLevelsGRU, batch_first=True)
+        else:
+            self.baseNet = nn.GRU(dimEncoded, dimOutput, num_layers=nLevelsGRU, batch_first=True)
+        self.hidden = None
+        self.keepHidden = keepHidden
+        self.reverse = reverse
+
+    def getDimOutput(self):
+        return self.baseNet.hidden_size
+
+    def forward(self, x):
+        ops.require_cuda(x)
+        if not isinstance(self.baseNet, nn.LSTM):
+            raise NotImplementedError("cpc2_b200: only arMode='LSTM' (and 'transformer') have sm_100a kernels so far")
+        if self.reverse:
+            x = torch.flip(x, [1])
+        nl = self.baseNet.num_layers
+        params = []
+        for l in range(nl):
+            params += [getattr(self.baseNet, f"{n}_l{l}") for n in ("weight_ih", "weight_hh", "bias_ih", "bias_hh")]
+        h0 = c0 = None
+        if self.hidden is not None:
+            h0, c0 = self.hidden
+        out, h_n, c_n = _LstmFn.apply(x, h0, c0, nl, *params)
+        if self.keepHidden:
+            self.hidden = (h_n.detach(), c_n.detach())
+        if self.reverse:
+            out = torch.flip(out, [1])
+        return out
+
+
+class _LstmFn(torch.autograd.Function):
+    """x [N,S,C] fp32 -> out [N,S,H] fp32 (+ final h, c [layers,N,H])."""
+
+    @staticmethod
+    def forward(ctx, x, h0, c0, nl, *params):
+        N, S, Cin = x.shape
+        dev = x.device
+        p = [t.detach() for t in params]
+        H = p[1].shape[1]
+        inp = K.cast_bf16(x.detach().contiguous().float()).view(N * S, Cin)
+        saved = []
+        h_ns, c_ns = [], []
+        out = None
+        prev_pad = None  # h_pad of the previous layer (input of layers > 0)
+        for l in range(nl):
+            w_ih, w_hh, b_ih, b_hh = p[4 * l:4 * l + 4]
+            Kin = w_ih.shape[1]
+            w_ih16, w_hh16 = K.cast_bf16(w_ih.contiguous()), K.cast_bf16(w_hh.contiguous())
+            bias = (b_ih + b_hh).contiguous()
+            gx = torch.empty(N * S, 4 * H, device=dev)
+            if l == 0:
+                K.gemm(K.kmajor(inp), K.kmajor(w_ih16), N * S, 4 * H, Kin, out_f32=gx, bias=bias)
+            else:  # rows 1..S of every sequence of the previous layer's padded bf16 output, one group per sequence
+                A = K.View(prev_pad, H, S + 1, N, H, (S + 1) * H, major=0, row_off=1, gmul=1)
+                K.gemm(A, K.kmajor(w_ih16), S, 4 * H, H, groups=N, out_f32=(gx, 4 * H, S * 4 * H), bias=bias)
+            out = torch.empty(N, S, H, device=dev)
+            h_pad = torch.empty(N, S + 1, H, device=dev, dtype=BF16)
+            gates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
+            c_all = torch.empty(N, S, H, device=dev)
+            h_n = torch.empty(N, H, device=dev)
+            c_n = torch.empty(N, H, device=dev)
+            h0l = h0[l].contiguous().float() if h0 is not None else None
+            c0l = c0[l].contiguous().float() if c0 is not None else None
+            K.lstm_fwd(gx, w_hh16, N, S, H, h0=h0l, c0=c0l, h_pad=h_pad, out=out, gates=gates, c_all=c_all,
+                       h_n=h_n, c_n=c_n)
+            saved.append((inp if l == 0 else prev_pad, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l))
+            h_ns.append(h_n)
+            c_ns.append(c_n)
+            prev_pad = h_pad
+        ctx.saved = saved
+        ctx.dims = (N, S, Cin, H, nl)
+        return out, torch.stack(h_ns), torch.stack(c_ns)
+
+    @staticmethod
+    def backward(ctx, dout, dh_n, dc_n):
+        N, S, Cin, H, nl = ctx.dims
+        dev = dout.device
+        d = dout.contiguous().float()
+        grads = [None] * (4 * nl)
+        for l in range(nl - 1, -1, -1):
+            x_in, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l = ctx.saved[l]
+            dgates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
+            K.lstm_bwd(w_hh16, gates, c_all, d, dgates, N, S, H, c0=c0l)
+            dg2 = dgates.view(N * S, 4 * H)
+            dbias = torch.zeros(4 * H, device=dev)
+            K.colsum(dg2, dbias, N * S, 4 * H, 4 * H)
+            # dW_hh = sum_{n,t} dgates[n,t]^T h_{t-1}[n]  (slabs = sequences, h_pad row t is h_{t-1})
+            dw_hh = torch.zeros(4 * H, H, device=dev)
+            Ag = K.View(dgates, 4 * H, S, N, 4 * H, S * 4 * H, major=1)
+            Bh = K.View(h_pad, H, S + 1, N, H, (S + 1) * H, major=1)
+            K.gemm(Ag, Bh, 4 * H, H, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, H, N * S, 1, S),
+                   out_f32=dw_hh, accumulate=True)
+            # dW_ih = dgates^T . input
+            dw_ih = torch.zeros(4 * H, Kin, device=dev)
+            if l == 0:
+                K.gemm(K.mnmajor(dg2), K.mnmajor(x_in), 4 * H, Kin, N * S,
+                       k_splits=ops.auto_splits(4 * H, Kin, N * S), out_f32=dw_ih, accumulate=True)
+            else:
+                Bx = K.View(x_in, H, S + 1, N, H, (S + 1) * H, major=1, row_off=1)
+                K.gemm(Ag, Bx, 4 * H, Kin, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, Kin, N * S, 1, S),
+                       out_f32=dw_ih, accumulate=True)
+            grads[4 * l:4 * l + 4] = [dw_ih, dw_hh, dbias, dbias.clone()]
+            # dx = dgates . W_ih
+            dx = torch.empty(N * S, Kin, device=dev)
+            K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
+            d = dx.view(N, S, Kin)
+        return (d, None, None, None, *grads)
+
+
+class CPCModel(nn.Module):
+    """cpc/model.py:279-390 (mask_prob must stay 0: the reference's masking path is broken on current torch
+    and off by default)."""
+
+    def __init__(self, encoder, AR, mask_prob=0.0, mask_length=10):
+        super().__init__()
+        self.gEncoder = encoder
+        self.gAR = AR
+        self.mask_prob = mask_prob
+        self.mask_length = mask_length
+        if mask_prob > 0.0:
+            raise NotImplementedError("cpc2_b200: span masking (mask_prob > 0) is outside the hot path")
+
+    def forward(self, batchData, label):
+        encodedData = self.gEncoder(batchData).permute(0, 2, 1)
+        cFeature = self.gAR(encodedData)
+        return cFeature, encodedData, label

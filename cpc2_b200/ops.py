@@ -1,0 +1,128 @@
+"""Host-side glue shared by the drop-in modules: parameter arenas, dropout RNG state, GEMM call shapes.
+
+Nothing here computes on tensors' values: it allocates buffers, describes views and launches the C-ABI
+kernels of libcpc_b200.so through `cpc2_b200.kernels`.
+"""
+import torch
+
+from . import kernels as K
+
+BF16 = torch.bfloat16
+NUM_SMS = 148
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("cpc2_b200 runs on CUDA tensors only (sm_100a kernels, no CPU fallback)")
+
+
+def auto_splits(M, N, K_total, groups=1, k_per_slab=0):
+    """Split-K factor for skinny weight-gradient GEMMs so that ~2 CTAs per SM are in flight."""
+    kps = k_per_slab or K_total
+    kblocks = ((kps + 63) // 64) * (K_total // kps)
+    bn = 256 if N >= 256 else (128 if N > 64 else 64)
+    tiles = ((M + 127) // 128) * ((N + bn - 1) // bn) * groups
+    if tiles >= NUM_SMS or kblocks <= 4:
+        return 1
+    return max(1, min(kblocks // 4, (2 * NUM_SMS + tiles - 1) // tiles))
+
+
+class Arena:
+    """A flat fp32 buffer that OWNS the storage of a list of parameters, in a layout chosen so that
+    groups of parameters form the stacked GEMM operands directly ([group][rows][cols]); one cast kernel
+    produces the bf16 shadow of all of them per step.  Parameter names/shapes (state_dict) are untouched:
+    each nn.Parameter's .data becomes a view into the arena."""
+
+    def __init__(self, params):
+        self.params = list(params)
+        self.offsets = []
+        off = 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += (p.numel() + 7) // 8 * 8  # keep every fp32 and bf16-shadow view 16-byte aligned
+        self.numel = off
+        self.flat = None
+
+    def valid(self):
+        if self.flat is None or not self.params:
+            return False
+        base = self.flat.data_ptr()
+        for i in (0, len(self.params) - 1):
+            p = self.params[i]
+            if p.device != self.flat.device or p.data_ptr() != base + 4 * self.offsets[i]:
+                return False
+        return True
+
+    def ensure(self):
+        """(Re)build the arena if the module was moved (.cuda()/.to()) since the last call."""
+        if self.valid():
+            return self.flat
+        dev = self.params[0].device
+        flat = torch.zeros(self.numel, dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            for p, off in zip(self.params, self.offsets):
+                view = flat[off:off + p.numel()].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+        self.flat = flat
+        return flat
+
+    def bf16(self):
+        return K.cast_bf16(self.ensure())
+
+    def view(self, flat, index, shape=None):
+        """View of parameter `index` inside another flat tensor with the same layout (bf16 shadow, grads)."""
+        p = self.params[index]
+        off = self.offsets[index]
+        return flat[off:off + p.numel()].view(p.shape if shape is None else shape)
+
+    def span(self, flat, first, count, shape):
+        """Contiguous view over `count` consecutive equally sized parameters starting at `first`."""
+        off = self.offsets[first]
+        n = 1
+        for s in shape:
+            n *= s
+        assert self.offsets[first + count - 1] + self.params[first + count - 1].numel() - off == n, \
+            "parameters are not densely packed"
+        return flat[off:off + n].view(shape)
+
+    def grad_views(self, gflat):
+        return [self.view(gflat, i) for i in range(len(self.params))]
+
+
+class DropoutState:
+    """Device-side (seed, step) pair feeding the counter RNG of the kernels; CUDA-graph safe."""
+    _states = {}
+
+    @classmethod
+    def next(cls, device):
+        key = (device.type, device.index)
+        st = cls._states.get(key)
+        if st is None:
+            st = torch.tensor([torch.initial_seed() & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=device)
+            cls._states[key] = st
+        snap = st.clone()
+        st[1:2].add_(1)
+        return snap
+
+
+def linear_fwd(x, w, M, N, Kd, groups=1, x_shared=False, **epi):
+    """y[g] = x[g] . w[g]^T ; x bf16 [M,K] (shared) or [G,M,K]; w bf16 [G,N,K] or [N,K]."""
+    A = K.kmajor(x, gmul=0 if (x_shared or x.dim() == 2) else 1)
+    B = K.kmajor(w)
+    K.gemm(A, B, M, N, Kd, groups=groups, **epi)
+
+
+def linear_dx(dy, w, M, N, Kd, groups=1, **epi):
+    """dx[g] = dy[g] . w[g] ; dy bf16 [G,M,N]; w bf16 [G,N,K] consumed MN-major (reduction over its rows)."""
+    A = K.kmajor(dy)
+    B = K.mnmajor(w)
+    K.gemm(A, B, M, Kd, N, groups=groups, **epi)
+
+
+def linear_dw(dy, x, dw, M, N, Kd, groups=1, x_shared=False):
+    """dw[g] (fp32 [G,N,K], pre-zeroed) += dy[g]^T . x[g]; reduction over the M rows, split-K."""
+    A = K.mnmajor(dy)
+    B = K.mnmajor(x, gmul=0 if (x_shared or x.dim() == 2) else 1)
+    K.gemm(A, B, N, Kd, M, groups=groups, k_splits=auto_splits(N, Kd, M, groups), out_f32=dw, accumulate=True)

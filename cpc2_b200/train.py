@@ -1,0 +1,198 @@
+"""Drop-in for the hot-path entry points of the reference's cpc/train.py and cpc/feature_loader.py:
+getEncoder / getAR (feature_loader.py:202-235), getCriterion (train.py:27-59), trainStep (train.py:72-142),
+valStep (train.py:145-187) -- same signatures and batch handling, built on the sm_100a modules.
+
+`GraphedTrainStep` is the B200-native way to run the step: the whole forward + backward (every kernel launch,
+the RNG draws of the negative sampler, the gradient buffers) is captured once in a CUDA graph and replayed,
+which removes the per-launch host overhead that otherwise dominates a ~1 ms step.
+"""
+import argparse
+import time
+
+import numpy as np
+import torch
+
+from . import criterion as cr
+from . import model as model_
+from . import transformers as tr
+
+
+def defaultArgs(**over):
+    """The architecture defaults of cpc/cpc_default_config.py:13-162 that the hot path reads."""
+    a = argparse.Namespace(
+        hiddenEncoder=256, hiddenGar=256, nPredicts=12, negativeSamplingExt=128, sizeWindow=20480,
+        samplingType="samespeaker", cpc_mode=None, encoder_type="cpc", normMode="layerNorm", arMode="LSTM",
+        nLevelsGRU=1, rnnMode="transformer", dropout=False, abspos=False, multihead_rnn=False,
+        transformer_pruning=0, n_skipped=0, growth_rate=None, inflection_point_x=None, supervised=False,
+        onEncoder=False, pathPhone=None, mask_prob=0.0, mask_length=10, learningRate=2e-4, beta1=0.9, beta2=0.999,
+        epsilon=1e-08, batchSizeGPU=8)
+    for k, v in over.items():
+        setattr(a, k, v)
+    return a
+
+
+def getEncoder(args):
+    """cpc/feature_loader.py:202-212 (CPC waveform encoder only)."""
+    if getattr(args, "encoder_type", "cpc") != "cpc":
+        raise NotImplementedError("cpc2_b200: only encoder_type='cpc' is on the accelerated path")
+    return model_.CPCEncoder(args.hiddenEncoder, args.normMode)
+
+
+def getAR(args):
+    """cpc/feature_loader.py:215-235."""
+    if args.arMode == 'transformer':
+        arNet = tr.buildTransformerAR(args.hiddenEncoder, args.hiddenGar, args.nLevelsGRU, args.sizeWindow // 160,
+                                      args.abspos)
+        args.hiddenGar = args.hiddenEncoder
+    elif args.cpc_mode == "bert" or args.arMode == 'no_ar':
+        raise NotImplementedError("cpc2_b200: bert / no_ar variants are outside the hot path")
+    else:
+        arNet = model_.CPCAR(args.hiddenEncoder, args.hiddenGar, args.samplingType == "sequential",
+                             args.nLevelsGRU, mode=args.arMode, reverse=args.cpc_mode == "reverse")
+    return arNet
+
+
+def getCriterion(args, downsampling, nSpeakers, nPhones):
+    """cpc/train.py:27-59 (unsupervised CPC criterion only)."""
+    if args.supervised or args.cpc_mode == 'none':
+        raise NotImplementedError("cpc2_b200: supervised / 'none' criteria are outside the hot path")
+    sizeInputSeq = (args.sizeWindow // downsampling)
+    return cr.CPCUnsupersivedCriterion(args.nPredicts, args.hiddenGar, args.hiddenEncoder,
+                                       args.negativeSamplingExt, mode=args.cpc_mode, rnnMode=args.rnnMode,
+                                       dropout=args.dropout, nSpeakers=nSpeakers, sizeInputSeq=sizeInputSeq,
+                                       multihead_rnn=args.multihead_rnn,
+                                       transformer_pruning=args.transformer_pruning, n_skipped=args.n_skipped,
+                                       growth_rate=args.growth_rate, inflection_point_x=args.inflection_point_x)
+
+
+def buildModelAndCriterion(args):
+    """Construction order of cpc/train.py:442-461, so one seed gives the reference's initial weights."""
+    encoderNet = getEncoder(args)
+    arNet = getAR(args)
+    cpcModel = model_.CPCModel(encoderNet, arNet, getattr(args, "mask_prob", 0.0), getattr(args, "mask_length", 10))
+    cpcCriterion = getCriterion(args, encoderNet.DOWNSAMPLING, 0, 0)
+    return cpcModel, cpcCriterion
+
+
+def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None, backward=True):
+    """The body of the reference's batch loop, cpc/train.py:95-109."""
+    past, future = sequence[:, 0, ...], sequence[:, 1, ...]
+    b = past.size(0)
+    combined = torch.cat([past, future], dim=0)
+    label = torch.cat([label, label])
+    c_feature, encoded_data, label = cpcModel(combined, label)
+    c_feature = c_feature[:b, :, :]
+    encoded_data = encoded_data[b:, :, :]
+    label = label[:b]
+    allLosses, allAcc = cpcCriterion(c_feature, encoded_data, label, signal_quality)
+    if backward:
+        totLoss = allLosses.sum()
+        totLoss.backward()
+    return allLosses, allAcc
+
+
+def trainStep(dataLoader, cpcModel, cpcCriterion, optimizer, scheduler, loggingStep):
+    """cpc/train.py:72-142."""
+    cpcModel.train()
+    cpcCriterion.train()
+    start_time = time.perf_counter()
+    n_examples = 0
+    logs = {}
+    it = 0
+    for step, full_data in enumerate(dataLoader):
+        sequence, label, *signal_quality = full_data
+        sequence = sequence.cuda(non_blocking=True)
+        label = label.cuda(non_blocking=True)
+        signal_quality = signal_quality[0].cuda(non_blocking=True) if len(signal_quality) else None
+        n_examples += sequence.size(0)
+        allLosses, allAcc = forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality)
+        optimizer.step()
+        optimizer.zero_grad()
+        if allLosses.nelement() > 0:
+            if "locLoss_train" not in logs:
+                logs["locLoss_train"] = np.zeros(allLosses.size(1))
+                logs["locAcc_train"] = np.zeros(allLosses.size(1))
+            it += 1
+            logs["locLoss_train"] += (allLosses.mean(dim=0)).detach().cpu().numpy()
+            logs["locAcc_train"] += (allAcc.mean(dim=0)).cpu().numpy()
+            if (step + 1) % loggingStep == 0:
+                new_time = time.perf_counter()
+                elapsed = new_time - start_time
+                print(f"Update {step + 1}")
+                print(f"elapsed: {elapsed:.1f} s")
+                print(f"{1000.0 * elapsed / loggingStep:.1f} ms per batch, "
+                      f"{1000.0 * elapsed / n_examples:.1f} ms / example")
+                start_time, n_examples = new_time, 0
+    if scheduler is not None:
+        scheduler.step()
+    logs = {k: v / max(it, 1) for k, v in logs.items()}
+    logs["iter"] = it
+    return logs
+
+
+def valStep(dataLoader, cpcModel, cpcCriterion):
+    """cpc/train.py:145-187."""
+    cpcCriterion.eval()
+    cpcModel.eval()
+    logs = {}
+    it = 0
+    for step, full_data in enumerate(dataLoader):
+        sequence, label, *signal_quality = full_data
+        sequence = sequence.cuda(non_blocking=True)
+        label = label.cuda(non_blocking=True)
+        with torch.no_grad():
+            allLosses, allAcc = forwardBackward(cpcModel, cpcCriterion, sequence, label, None, backward=False)
+        if "locLoss_val" not in logs:
+            logs["locLoss_val"] = np.zeros(allLosses.size(1))
+            logs["locAcc_val"] = np.zeros(allLosses.size(1))
+        it += 1
+        logs["locLoss_val"] += allLosses.mean(dim=0).cpu().numpy()
+        logs["locAcc_val"] += allAcc.mean(dim=0).cpu().numpy()
+    logs = {k: v / max(it, 1) for k, v in logs.items()}
+    logs["iter"] = it
+    return logs
+
+
+class GraphedTrainStep:
+    """Forward + backward of one batch captured in a CUDA graph (static input / output buffers).
+
+    step(sequence_host_or_device) copies the batch into the static input, replays the graph and returns the
+    static (losses, acc) tensors; parameter .grad tensors are static too (rewritten by every replay), so an
+    optimizer step can follow as usual.  `grad_hook(stage)` (optional) is invoked during capture right after
+    the criterion / AR / encoder gradients exist -- the data-parallel wrapper uses it to enqueue its bucketed
+    all-reduces on a side stream inside the same graph."""
+
+    def __init__(self, cpcModel, cpcCriterion, batch, sizeWindow, device="cuda", warmup=3, train_mode=True,
+                 after_backward=None):
+        self.model, self.crit = cpcModel, cpcCriterion
+        self.static_seq = torch.zeros(batch, 2, 1, sizeWindow, device=device)
+        self.static_label = torch.zeros(batch, dtype=torch.long, device=device)
+        self.params = [p for p in list(cpcModel.parameters()) + list(cpcCriterion.parameters()) if p.requires_grad]
+        cpcModel.train(train_mode)
+        cpcCriterion.train(train_mode)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._zero()
+                forwardBackward(cpcModel, cpcCriterion, self.static_seq, self.static_label)
+                if after_backward is not None:
+                    after_backward()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        self._zero()
+        with torch.cuda.graph(self.graph):
+            self.losses, self.acc = forwardBackward(cpcModel, cpcCriterion, self.static_seq, self.static_label)
+            if after_backward is not None:
+                after_backward()
+
+    def _zero(self):
+        for p in self.params:
+            p.grad = None
+
+    def step(self, sequence=None, non_blocking=True):
+        if sequence is not None:
+            self.static_seq.copy_(sequence, non_blocking=non_blocking)
+        self.graph.replay()
+        return self.losses, self.acc

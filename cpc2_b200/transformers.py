@@ -1,0 +1,285 @@
+"""Drop-in for the reference's cpc/transformers.py (causal block-local attention with relative-position
+keys, post-LN transformer block, builders) -- same classes, constructor signatures, parameter AND buffer
+names, so reference checkpoints load with strict=True.  The modules are parameter containers; the math runs
+in `TransformerStack`, which executes G independent blocks (the K prediction heads of the criterion, or one
+AR layer with G = 1) as grouped tcgen05 GEMMs + fused attention / LayerNorm kernels.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import kernels as K
+from . import ops
+from .ops import BF16
+
+
+class ScaledDotProductAttention(nn.Module):
+    """cpc/transformers.py:10-36 (parameters / buffers only; compute is cpc_attn_fwd/bwd)."""
+
+    def __init__(self, sizeSeq, dk, dropout, relpos=False):
+        super().__init__()
+        self.drop = nn.Dropout(dropout)
+        self.softmax = nn.Softmax(dim=2)
+        self.relpos = relpos
+        self.sizeSeq = sizeSeq
+        if relpos:
+            self.Krelpos = nn.Parameter(torch.Tensor(dk, sizeSeq))
+            self.initmat_(self.Krelpos)
+            self.register_buffer('z', torch.zeros(1, sizeSeq, 1))
+        mask = torch.tril(torch.ones(sizeSeq, sizeSeq), diagonal=0)
+        mask = 1 - mask
+        mask[mask == 1] = -float('inf')
+        self.register_buffer('mask', mask.unsqueeze(0))
+
+    def initmat_(self, mat, dim=0):
+        stdv = 1. / math.sqrt(mat.size(dim))
+        mat.data.uniform_(-stdv, stdv)
+
+
+class MultiHeadAttention(nn.Module):
+    """cpc/transformers.py:73-87."""
+
+    def __init__(self, sizeSeq, dropout, dmodel, nheads, abspos):
+        super().__init__()
+        self.Wo = nn.Linear(dmodel, dmodel, bias=False)
+        self.Wk = nn.Linear(dmodel, dmodel, bias=False)
+        self.Wq = nn.Linear(dmodel, dmodel, bias=False)
+        self.Wv = nn.Linear(dmodel, dmodel, bias=False)
+        self.nheads = nheads
+        self.dk = dmodel // nheads
+        self.Att = ScaledDotProductAttention(sizeSeq, self.dk, dropout, not abspos)
+
+
+class FFNetwork(nn.Module):
+    """cpc/transformers.py:107-113."""
+
+    def __init__(self, din, dout, dff, dropout):
+        super().__init__()
+        self.lin1 = nn.Linear(din, dff, bias=True)
+        self.lin2 = nn.Linear(dff, dout, bias=True)
+        self.relu = nn.ReLU()
+        self.drop = nn.Dropout(dropout)
+
+
+class TransformerLayer(nn.Module):
+    """cpc/transformers.py:119-134: y = LN(x + MHA(x)); out = LN(last_linear(y + FFN(y)))."""
+
+    def __init__(self, sizeSeq=32, dmodel=512, dout=512, dff=2048, dropout=0.1, nheads=8, abspos=False):
+        super().__init__()
+        self.multihead = MultiHeadAttention(sizeSeq, dropout, dmodel, nheads, abspos)
+        self.ln_multihead = nn.LayerNorm(dmodel)
+        self.ffnetwork = FFNetwork(dmodel, dmodel, dff, dropout)
+        self.last_linear = nn.Linear(dmodel, dout)
+        self.ln_ffnetwork = nn.LayerNorm(dout)
+        self.sizeSeq, self.dmodel, self.dout, self.dff = sizeSeq, dmodel, dout, dff
+        self.dropout_p, self.nheads = dropout, nheads
+        self._stack = None
+
+    def stack(self):
+        if self._stack is None:
+            object.__setattr__(self, "_stack", TransformerStack([self]))
+        return self._stack
+
+    def forward(self, x):
+        """x [N, S, dmodel] fp32, S a multiple of sizeSeq -> [N, S, dout] fp32."""
+        ops.require_cuda(x)
+        st = self.stack()
+        return _TransformerFn.apply(x, st, self.training, *st.arena.params)
+
+
+class StaticPositionEmbedding(nn.Module):
+    """cpc/transformers.py:161-173."""
+
+    def __init__(self, seqlen, dmodel):
+        super().__init__()
+        pos = torch.arange(0., seqlen).unsqueeze(1).repeat(1, dmodel)
+        dim = torch.arange(0., dmodel).unsqueeze(0).repeat(seqlen, 1)
+        div = torch.exp(- math.log(10000) * (2 * (dim // 2) / dmodel))
+        pos *= div
+        pos[:, 0::2] = torch.sin(pos[:, 0::2])
+        pos[:, 1::2] = torch.cos(pos[:, 1::2])
+        self.register_buffer('pe', pos.unsqueeze(0))
+
+    def forward(self, x):
+        return x + self.pe[:, :x.size(1), :]
+
+
+def buildTransformerAR(dimEncoded, dimAR, nLayers, sizeSeq, abspos):
+    """cpc/transformers.py:176-187."""
+    layerSequence = []
+    if abspos:
+        layerSequence += [StaticPositionEmbedding(sizeSeq, dimAR)]
+    layerSequence += [TransformerLayer(sizeSeq=sizeSeq, dmodel=dimAR, dout=dimEncoded, abspos=abspos)
+                      for i in range(nLayers)]
+    return nn.Sequential(*layerSequence)
+
+
+class TransformerStack:
+    """G independent TransformerLayers (identical shapes) executed together.  Owns the parameter arena:
+    stacked operands [G][rows][cols] are contiguous spans of it, their bf16 shadow is one cast per step."""
+
+    KINDS = ("Wo", "W1", "b1", "W2", "b2", "Wl", "bl", "ln1w", "ln1b", "ln2w", "ln2b")
+
+    def __init__(self, layers):
+        self.layers = list(layers)
+        l0 = self.layers[0]
+        self.G = len(self.layers)
+        self.S, self.d, self.dout, self.dff = l0.sizeSeq, l0.dmodel, l0.dout, l0.dff
+        self.Hh, self.dk = l0.nheads, l0.dmodel // l0.nheads
+        self.p_drop = l0.dropout_p
+        self.relpos = l0.multihead.Att.relpos
+        if self.d % 32 or self.dout % 32 or self.dff % 8 or self.S > 256 or self.dk > 64:
+            raise NotImplementedError("TransformerStack: dmodel/dout must be multiples of 32, sizeSeq <= 256, dk <= 64")
+        params = []
+        for l in self.layers:
+            params += [l.multihead.Wq.weight, l.multihead.Wk.weight, l.multihead.Wv.weight]
+        getters = {
+            "Wo": lambda l: l.multihead.Wo.weight, "W1": lambda l: l.ffnetwork.lin1.weight,
+            "b1": lambda l: l.ffnetwork.lin1.bias, "W2": lambda l: l.ffnetwork.lin2.weight,
+            "b2": lambda l: l.ffnetwork.lin2.bias, "Wl": lambda l: l.last_linear.weight,
+            "bl": lambda l: l.last_linear.bias, "ln1w": lambda l: l.ln_multihead.weight,
+            "ln1b": lambda l: l.ln_multihead.bias, "ln2w": lambda l: l.ln_ffnetwork.weight,
+            "ln2b": lambda l: l.ln_ffnetwork.bias,
+        }
+        self.first = {"Wqkv": 0}
+        for kind in self.KINDS:
+            self.first[kind] = len(params)
+            params += [getters[kind](l) for l in self.layers]
+        if self.relpos:
+            self.first["krel"] = len(params)
+            params += [l.multihead.Att.Krelpos for l in self.layers]
+        self.arena = ops.Arena(params)
+
+    def shapes(self):
+        G, d, dout, dff = self.G, self.d, self.dout, self.dff
+        sh = {"Wqkv": (G, 3 * d, d), "Wo": (G, d, d), "W1": (G, dff, d), "b1": (G, dff), "W2": (G, d, dff),
+              "b2": (G, d), "Wl": (G, dout, d), "bl": (G, dout), "ln1w": (G, d), "ln1b": (G, d),
+              "ln2w": (G, dout), "ln2b": (G, dout)}
+        if self.relpos:
+            sh["krel"] = (G, self.dk, self.S)
+        return sh
+
+    def spans(self, flat):
+        out = {}
+        for name, shape in self.shapes().items():
+            count = 3 * self.G if name == "Wqkv" else self.G
+            out[name] = self.arena.span(flat, self.first[name], count, shape)
+        return out
+
+    # ------------------------------------------------------------------------------------------ forward
+    def forward(self, x, T, shared, training, want_f32=False):
+        """x bf16 [T, d] (shared by all groups) or [G, T, d].  Returns (out bf16 [G,T,dout], out_f32|None, saved)."""
+        G, d, dout, dff, S = self.G, self.d, self.dout, self.dff, self.S
+        if T % S != 0:
+            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+        Bt = T // S
+        dev = x.device
+        w32 = self.arena.ensure()
+        P32 = self.spans(w32)
+        P16 = self.spans(self.arena.bf16())
+        drop = self.p_drop if training else 0.0
+        rng = ops.DropoutState.next(dev) if drop > 0 else None
+        qkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
+        ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared, out_bf16=qkv)
+        att = torch.empty(G, T, d, device=dev, dtype=BF16)
+        probs = torch.empty(G, Bt, self.Hh, S, S, device=dev, dtype=BF16)
+        K.attn_fwd(qkv, P32.get("krel"), att, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        pre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
+        res = (x, d, 0) if shared else x
+        ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res)
+        y = torch.empty(G, T, d, device=dev, dtype=BF16)
+        mean1 = torch.empty(G * T, device=dev)
+        rstd1 = torch.empty(G * T, device=dev)
+        K.rownorm_fwd(pre1, G * T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
+        h1 = torch.empty(G, T, dff, device=dev, dtype=BF16)
+        ops.linear_fwd(y, P16["W1"], T, dff, d, groups=G, out_bf16=h1, bias=P32["b1"], bias_gs=dff, relu=True,
+                       rng=rng, rng_site=2, drop_p=drop)
+        u = torch.empty(G, T, d, device=dev, dtype=BF16)
+        ops.linear_fwd(h1, P16["W2"], T, d, dff, groups=G, out_bf16=u, bias=P32["b2"], bias_gs=d, res=y)
+        pre2 = torch.empty(G, T, dout, device=dev, dtype=BF16)
+        ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout)
+        out = torch.empty(G, T, dout, device=dev, dtype=BF16)
+        out32 = torch.empty(G, T, dout, device=dev) if want_f32 else None
+        mean2 = torch.empty(G * T, device=dev)
+        rstd2 = torch.empty(G * T, device=dev)
+        K.rownorm_fwd(pre2, G * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
+                      rstd=rstd2, rows_per_group=T)
+        saved = dict(x=x, shared=shared, T=T, Bt=Bt, P16=P16, P32=P32, rng=rng, drop=drop, qkv=qkv, att=att,
+                     probs=probs, pre1=pre1, y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2,
+                     rstd2=rstd2)
+        return out, out32, saved
+
+    # ------------------------------------------------------------------------------------------ backward
+    def backward(self, sv, dout):
+        """dout bf16 or fp32 [G, T, dout].  Returns (dx fp32 [T,d] if shared else [G,T,d], flat fp32 grad arena)."""
+        G, d, do, dff, S = self.G, self.d, self.dout, self.dff, self.S
+        T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
+        dev = dout.device
+        gflat = torch.zeros(self.arena.numel, device=dev)
+        Gd = self.spans(gflat)
+        x, shared = sv["x"], sv["shared"]
+        # out = LN2(pre2)
+        dpre2 = torch.empty(G, T, do, device=dev, dtype=BF16)
+        K.rownorm_bwd(dout.reshape(G * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], G * T, do, P32["ln2w"], P32["ln2b"],
+                      dx_bf16=dpre2, dgamma=Gd["ln2w"], dbeta=Gd["ln2b"], rows_per_group=T)
+        # pre2 = u . Wl^T + bl
+        K.colsum(dpre2, Gd["bl"], T, do, do, T * do, G)
+        ops.linear_dw(dpre2, sv["u"], Gd["Wl"], T, do, d, groups=G)
+        du = torch.empty(G, T, d, device=dev, dtype=BF16)
+        ops.linear_dx(dpre2, P16["Wl"], T, do, d, groups=G, out_bf16=du)
+        # u = y + h1 . W2^T + b2
+        K.colsum(du, Gd["b2"], T, d, d, T * d, G)
+        ops.linear_dw(du, sv["h1"], Gd["W2"], T, d, dff, groups=G)
+        dh1 = torch.empty(G, T, dff, device=dev, dtype=BF16)
+        ops.linear_dx(du, P16["W2"], T, d, dff, groups=G, out_bf16=dh1, gate=sv["h1"],
+                      gate_scale=1.0 / (1.0 - sv["drop"]))
+        # h1 = dropout(relu(y . W1^T + b1))
+        K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
+        ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
+        dy = torch.empty(G, T, d, device=dev, dtype=BF16)
+        ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
+        # y = LN1(pre1)
+        dpre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
+        K.rownorm_bwd(dy.view(G * T, d), sv["pre1"], sv["mean1"], sv["rstd1"], G * T, d, P32["ln1w"], P32["ln1b"],
+                      dx_bf16=dpre1, dgamma=Gd["ln1w"], dbeta=Gd["ln1b"], rows_per_group=T)
+        # pre1 = x + att . Wo^T
+        ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=G)
+        datt = torch.empty(G, T, d, device=dev, dtype=BF16)
+        ops.linear_dx(dpre1, P16["Wo"], T, d, d, groups=G, out_bf16=datt)
+        dqkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
+        dscore = torch.empty_like(sv["probs"])
+        K.attn_bwd(sv["qkv"], P32.get("krel"), sv["att"], sv["probs"], datt, dqkv, dscore, Gd.get("krel"), G, Bt,
+                   self.Hh, S, self.dk, rng=sv["rng"], site=1, drop_p=sv["drop"])
+        # qkv = x . Wqkv^T
+        ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared)
+        if shared:
+            # dx = sum_g (dqkv_g . Wqkv_g + dpre1_g): one GEMM whose reduction runs over (group, 3d), then a group sum
+            dx = torch.empty(T, d, device=dev)
+            A = K.View(dqkv, 3 * d, T, G, 3 * d, T * 3 * d, major=0, gmul=0)
+            B = K.View(P16["Wqkv"], d, 3 * d, G, d, 3 * d * d, major=1, gmul=0)
+            K.gemm(A, B, T, d, G * 3 * d, k_per_slab=3 * d, out_f32=dx)
+            K.groupsum(dpre1, T * d, G, out_f32=dx, accumulate=True)
+        else:
+            dx = torch.empty(G, T, d, device=dev)
+            ops.linear_dx(dqkv, P16["Wqkv"], T, 3 * d, d, groups=G, out_f32=dx, res=dpre1)
+        return dx, gflat
+
+
+class _TransformerFn(torch.autograd.Function):
+    """One TransformerLayer (G = 1) as used by buildTransformerAR."""
+
+    @staticmethod
+    def forward(ctx, x, stack, training, *params):
+        N, S_in, d = x.shape
+        xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
+        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True)
+        ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
+        return out32.view(N, S_in, stack.dout)
+
+    @staticmethod
+    def backward(ctx, dout):
+        st = ctx.stack
+        N, S_in, d = ctx.shape
+        dx, gflat = st.backward(ctx.saved, dout.contiguous().float().view(1, N * S_in, st.dout))
+        return (dx.view(N, S_in, d), None, None, *st.arena.grad_views(gflat))
