@@ -157,7 +157,7 @@ class Nce(ctypes.Structure):
         ("ld", ctypes.c_int64),
         ("logits", ctypes.c_void_p), ("ext", ctypes.c_void_p), ("weights", ctypes.c_void_p),
         ("lse", ctypes.c_void_p), ("loss_sum", ctypes.c_void_p), ("hits", ctypes.c_void_p),
-        ("gscale", ctypes.c_void_p), ("dlogits", ctypes.c_void_p),
+        ("gscale", ctypes.c_void_p), ("dlogits", ctypes.c_void_p), ("dlogits_lo", ctypes.c_void_p),
     ]
 
 

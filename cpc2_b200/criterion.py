@@ -257,17 +257,22 @@ class _CriterionFn(torch.autograd.Function):
         eng = ctx.eng
         dev = dloss.device
         gscale = dloss.reshape(Kp).contiguous().float()
-        dlog = torch.empty(Kp, T, BS, device=dev, dtype=BF16)
-        K.nce_bwd(logits, ext, weights, lse, gscale, dlog, Kp, B, W, S, NEG, BS)
+        # d loss / d logits as a hi + lo pair of bf16 matrices (see nce.cu: the rounding error of the hi part is
+        # coherent across rows); each backward GEMM runs once per part, the second pass accumulating.
+        dlog = torch.empty(2, Kp, T, BS, device=dev, dtype=BF16)
+        K.nce_bwd(logits, ext, weights, lse, gscale, dlog[0], Kp, B, W, S, NEG, BS, dlogits_lo=dlog[1])
         # dpred_k = dlog_k . z / D
-        dpred = torch.empty(Kp, T, D, device=dev, dtype=BF16)
-        K.gemm(K.kmajor(dlog), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_bf16=dpred, alpha=1.0 / D)
+        dpred = torch.empty(Kp, T, D, device=dev)
+        for part in range(2):
+            K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
+                   accumulate=part > 0)
         # dz = sum_k dlog_k^T . pred_k / D   (reduction over (k, token))
         dz = torch.zeros(BS, D, device=dev)
-        A = K.View(dlog, BS, T, Kp, BS, T * BS, major=1, gmul=0)
         Bv = K.View(preds, D, T, Kp, D, T * D, major=1, gmul=0)
-        K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
-               accumulate=True, alpha=1.0 / D)
+        for part in range(2):
+            A = K.View(dlog[part], BS, T, Kp, BS, T * BS, major=1, gmul=0)
+            K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
+                   accumulate=True, alpha=1.0 / D)
         dcw, gflat = eng.backward(ctx.saved, dpred)
         dc = torch.zeros(B, S, H, device=dev)
         dc[:, :W] = dcw.view(B, W, H)

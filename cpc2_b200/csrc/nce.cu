@@ -25,6 +25,7 @@ struct NceArgs {
   float* hits;           // [K]  number of rows whose argmax is the positive
   const float* gscale;   // [K]  upstream gradient of each loss_k (backward)
   __nv_bfloat16* dlogits;  // [K][T][ld]
+  __nv_bfloat16* dlogits_lo;  // optional residual: dlogits + dlogits_lo carries ~16 mantissa bits
   int K, B, W, S, NEG;
 };
 
@@ -90,8 +91,17 @@ __global__ void __launch_bounds__(256) nce_bwd_kernel(const NceArgs a) {
     }
     __syncwarp();
     __nv_bfloat16* o = a.dlogits + ((long long)k * T + row) * a.ld;
-    for (long long c = lane * 2; c < a.ld; c += 64)
-      *reinterpret_cast<__nv_bfloat162*>(o + c) = __floats2bfloat162_rn(buf[c], buf[c + 1]);
+    __nv_bfloat16* ol = a.dlogits_lo != nullptr ? a.dlogits_lo + ((long long)k * T + row) * a.ld : nullptr;
+    for (long long c = lane * 2; c < a.ld; c += 64) {
+      const __nv_bfloat162 hi = __floats2bfloat162_rn(buf[c], buf[c + 1]);
+      *reinterpret_cast<__nv_bfloat162*>(o + c) = hi;
+      // The softmax mass of the negatives clusters around 1/(NEG+1): rounding it to bf16 is a COHERENT
+      // error over all rows, which survives the cancellation-heavy reductions downstream.  The residual
+      // is kept as a second bf16 matrix and the two backward GEMMs run a second, accumulating pass on it.
+      if (ol != nullptr)
+        *reinterpret_cast<__nv_bfloat162*>(ol + c) =
+            __floats2bfloat162_rn(buf[c] - __low2float(hi), buf[c + 1] - __high2float(hi));
+    }
     __syncwarp();
   }
 }
@@ -111,6 +121,7 @@ static int fill_nce(NceArgs& a, const CpcNce* d) {
   a.loss_sum = static_cast<float*>(d->loss_sum); a.hits = static_cast<float*>(d->hits);
   a.gscale = static_cast<const float*>(d->gscale);
   a.dlogits = static_cast<__nv_bfloat16*>(d->dlogits);
+  a.dlogits_lo = static_cast<__nv_bfloat16*>(d->dlogits_lo);
   a.K = d->K; a.B = d->B; a.W = d->W; a.S = d->S; a.NEG = d->NEG;
   return CPC_OK;
 }

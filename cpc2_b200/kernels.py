@@ -203,9 +203,9 @@ def nce_fwd(logits, ext, weights, lse, loss_sum, hits, K, B, W, S, NEG, ld):
     check(lib().cpc_nce_fwd(ctypes.byref(d), stream_ptr()), "cpc_nce_fwd")
 
 
-def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld):
+def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld, dlogits_lo=None):
     d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
-    d.gscale, d.dlogits = _dp(gscale), _dp(dlogits)
+    d.gscale, d.dlogits, d.dlogits_lo = _dp(gscale), _dp(dlogits), _dp(dlogits_lo)
     check(lib().cpc_nce_bwd(ctypes.byref(d), stream_ptr()), "cpc_nce_bwd")
 
 

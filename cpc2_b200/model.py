@@ -202,9 +202,13 @@ class _EncoderFn(torch.autograd.Function):
             K.conv_wgrad_unpack(dwf, dw, C, C, k)
             grads[4 * l:4 * l + 4] = [dw, dcb, dg.view(1, C, 1), db.view(1, C, 1)]
             # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
-            dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
             A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
-            K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
+            if ops.GRAD_F32 and l >= 2:
+                dxp = torch.empty(N, Lp, C, device=dev)
+                K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_f32=(dxp, s * C, Lp * C))
+            else:  # layer 0 consumes its (largest) gradient in bf16
+                dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
+                K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
             dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
         dw0 = torch.zeros(C, 10, device=dev)
         db0 = torch.zeros(C, device=dev)

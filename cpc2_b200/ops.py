@@ -9,6 +9,9 @@ from . import kernels as K
 
 BF16 = torch.bfloat16
 NUM_SMS = 148
+# Debug switch: keep the gradients that feed a normalisation backward in fp32 between kernels.  Measured to
+# make no difference to gradient parity (profiles/r01_grad_noise.log), so the default is bf16 (half the bytes).
+GRAD_F32 = False
 
 
 def require_cuda(*tensors):

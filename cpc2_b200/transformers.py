@@ -237,8 +237,12 @@ class TransformerStack:
         # h1 = dropout(relu(y . W1^T + b1))
         K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
         ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
-        dy = torch.empty(G, T, d, device=dev, dtype=BF16)
-        ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
+        if ops.GRAD_F32:
+            dy = torch.empty(G, T, d, device=dev)
+            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_f32=dy, res=du)
+        else:
+            dy = torch.empty(G, T, d, device=dev, dtype=BF16)
+            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
         # y = LN1(pre1)
         dpre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         K.rownorm_bwd(dy.view(G * T, d), sv["pre1"], sv["mean1"], sv["rstd1"], G * T, d, P32["ln1w"], P32["ln1b"],

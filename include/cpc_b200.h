@@ -156,13 +156,15 @@ int cpc_neg_ext_index(const void* batch_idx, const void* seq_idx, void* ext, int
  * InfoNCE gather + cross entropy + argmax (criterion.py:345-357) on the all-pairs logits
  * logits fp32 [K][B*W][ld] (ld >= B*S), ext int64 [B][NEG][W], weights fp32 [B*W] or null.
  * fwd: lse [K][B*W]; loss_sum[k] += sum_rows w*(lse - l_pos); hits[k] += #rows with argmax == positive.
- * bwd: dlogits bf16 [K][B*W][ld] = gscale[k] * w/(B*W) * (softmax - onehot0), dense, zeros elsewhere.
+ * bwd: dlogits bf16 [K][B*W][ld] = gscale[k] * w/(B*W) * (softmax - onehot0), dense, zeros elsewhere;
+ *      dlogits_lo (optional) receives the bf16 rounding residual so hi + lo ~ fp32 accuracy.
  */
 typedef struct {
   int K, B, W, S, NEG; int64_t ld;
   const void* logits; const void* ext; const void* weights;
   void* lse; void* loss_sum; void* hits;
   const void* gscale; void* dlogits;
+  void* dlogits_lo; /* optional bf16 residual (dlogits_f32 - dlogits), same shape; null to skip */
 } CpcNce;
 
 int cpc_nce_fwd(const CpcNce* desc, void* stream);
