@@ -13,6 +13,32 @@ from ._lib import GemmDesc, check, lib, ptr, stream_ptr
 BF16 = torch.bfloat16
 
 
+# ---- launch accounting / optional per-call profiling (used by bench.py) -------------------------------
+LAUNCHES = 0        # C-ABI launches issued by this process (bench.py reports the per-step count)
+PROFILE = None      # when a list: [name, work dict, start event, end event] per call
+_WORK = {}          # work model of the call being issued (set by the launcher just before _run)
+
+
+def set_work(**kw):
+    """Algorithmic work of the next call: flops=..., bytes=... (only read when profiling)."""
+    global _WORK
+    _WORK = kw
+
+
+def _run(name, args):
+    global LAUNCHES, _WORK
+    LAUNCHES += 1
+    if PROFILE is None:
+        check(getattr(lib(), name)(*args), name)
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    check(getattr(lib(), name)(*args), name)
+    e1.record()
+    PROFILE.append([name, _WORK, e0, e1])
+    _WORK = {}
+
+
 class View:
     """3-D operand view (dim0 contiguous) over a bf16 CUDA tensor, in elements.
     major 0: K-major (dim0 = reduction index); major 1: MN-major (dim0 = m / n index)."""
@@ -93,7 +119,11 @@ def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=N
     if rng is not None and drop_p > 0:
         d.rng, d.rng_site, d.drop_p = rng.data_ptr(), rng_site, drop_p
     d.relu, d.accumulate = int(relu), int(accumulate)
-    check(lib().cpc_gemm_bf16(ctypes.byref(d), stream_ptr()), "cpc_gemm_bf16")
+    if PROFILE is not None:
+        ob = (4 if out_f32 is not None else 0) + (2 if out_bf16 is not None else 0)
+        set_work(kind="tensor", flops=2.0 * M * N * K * groups, bytes=2.0 * groups * (M * K + N * K) + ob * M * N * groups,
+                 shape=f"g{groups} {M}x{N}x{K} a{A.major}b{B.major} s{k_splits}")
+    _run("cpc_gemm_bf16", (ctypes.byref(d), stream_ptr(),))
 
 
 # --------------------------------------------------------------------------------------------------
@@ -114,7 +144,9 @@ def rownorm_fwd(inp, rows, C, gamma=None, beta=None, out_bf16=None, out_f32=None
     d.out_bf16, d.out_f32, d.out_map = _dp(out_bf16), _dp(out_f32), out_map or rowmap()
     d.mean, d.rstd = _dp(mean), _dp(rstd)
     d.eps, d.unbiased, d.relu = eps, int(unbiased), int(relu)
-    check(lib().cpc_rownorm_fwd(ctypes.byref(d), stream_ptr()), "cpc_rownorm_fwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(rows) * C * (2 + (2 if out_bf16 is not None else 0) + (4 if out_f32 is not None else 0)))
+    _run("cpc_rownorm_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def rownorm_bwd(dout, inp, mean, rstd, rows, C, gamma=None, beta=None, dx_bf16=None, dx_f32=None, dgamma=None,
@@ -129,7 +161,10 @@ def rownorm_bwd(dout, inp, mean, rstd, rows, C, gamma=None, beta=None, dx_bf16=N
     d.dx_bf16, d.dx_f32, d.dx_map, d.dx_accumulate = _dp(dx_bf16), _dp(dx_f32), dx_map or rowmap(), int(dx_accumulate)
     d.dgamma, d.dbeta, d.dxsum = _dp(dgamma), _dp(dbeta), _dp(dxsum)
     d.unbiased, d.relu = int(unbiased), int(relu)
-    check(lib().cpc_rownorm_bwd(ctypes.byref(d), stream_ptr()), "cpc_rownorm_bwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(rows) * C * (2 + (4 if dout.dtype == torch.float32 else 2)
+                                                      + (2 if dx_bf16 is not None else 0) + (4 if dx_f32 is not None else 0)))
+    _run("cpc_rownorm_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5):
@@ -137,7 +172,9 @@ def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5):
     d.N, d.W, d.C, d.halo, d.eps = N, W, C, halo, eps
     d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
     d.out, d.mean, d.rstd = _dp(out), _dp(mean), _dp(rstd)
-    check(lib().cpc_conv0_cn_relu_fwd(ctypes.byref(d), stream_ptr()), "cpc_conv0_cn_relu_fwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(N) * (W // 5) * C * 2 + 4.0 * N * W)
+    _run("cpc_conv0_cn_relu_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, W, C, halo, eps=1e-5):
@@ -146,15 +183,17 @@ def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, 
     d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
     d.mean, d.rstd = _dp(mean), _dp(rstd)
     d.dout, d.dw, d.db, d.dgamma, d.dbeta = _dp(dout), _dp(dw), _dp(db), _dp(dgamma), _dp(dbeta)
-    check(lib().cpc_conv0_cn_relu_bwd(ctypes.byref(d), stream_ptr()), "cpc_conv0_cn_relu_bwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(N) * (W // 5) * C * 2 + 4.0 * N * W)
+    _run("cpc_conv0_cn_relu_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def conv_weight_pack(w, wf, wd, Co, Ci, k, s):
-    check(lib().cpc_conv_weight_pack(ptr(w), ptr(wf), ptr(wd), Co, Ci, k, s, stream_ptr()), "cpc_conv_weight_pack")
+    _run("cpc_conv_weight_pack", (ptr(w), ptr(wf), ptr(wd), Co, Ci, k, s, stream_ptr(),))
 
 
 def conv_wgrad_unpack(dwf, dw, Co, Ci, k):
-    check(lib().cpc_conv_wgrad_unpack(ptr(dwf), ptr(dw), Co, Ci, k, stream_ptr()), "cpc_conv_wgrad_unpack")
+    _run("cpc_conv_wgrad_unpack", (ptr(dwf), ptr(dw), Co, Ci, k, stream_ptr(),))
 
 
 def cast_bf16(src, dst=None):
@@ -162,7 +201,9 @@ def cast_bf16(src, dst=None):
     assert src.dtype == torch.float32 and src.is_contiguous()
     if dst is None:
         dst = torch.empty(src.shape, dtype=BF16, device=src.device)
-    check(lib().cpc_cast_f32_to_bf16(ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr()), "cpc_cast_f32_to_bf16")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=6.0 * src.numel())
+    _run("cpc_cast_f32_to_bf16", (ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr(),))
     return dst
 
 
@@ -170,23 +211,23 @@ def cast_f32(src, dst=None):
     assert src.dtype == BF16 and src.is_contiguous()
     if dst is None:
         dst = torch.empty(src.shape, dtype=torch.float32, device=src.device)
-    check(lib().cpc_cast_bf16_to_f32(ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr()), "cpc_cast_bf16_to_f32")
+    _run("cpc_cast_bf16_to_f32", (ptr(src), ptr(dst), ctypes.c_int64(src.numel()), stream_ptr(),))
     return dst
 
 
 def colsum(inp, out, rows, C, ld, gs_in=0, groups=1):
-    check(lib().cpc_colsum(ptr(inp), int(inp.dtype == BF16), ptr(out), ctypes.c_int64(rows), C, ctypes.c_int64(ld),
-                           ctypes.c_int64(gs_in), groups, stream_ptr()), "cpc_colsum")
+    _run("cpc_colsum", (ptr(inp), int(inp.dtype == BF16), ptr(out), ctypes.c_int64(rows), C, ctypes.c_int64(ld),
+                           ctypes.c_int64(gs_in), groups, stream_ptr(),))
 
 
 def groupsum(inp, n, groups, out_f32=None, out_bf16=None, accumulate=False):
-    check(lib().cpc_groupsum(ptr(inp), int(inp.dtype == BF16), ptr(out_f32), ptr(out_bf16), ctypes.c_int64(n), groups,
-                             int(accumulate), stream_ptr()), "cpc_groupsum")
+    _run("cpc_groupsum", (ptr(inp), int(inp.dtype == BF16), ptr(out_f32), ptr(out_bf16), ctypes.c_int64(n), groups,
+                             int(accumulate), stream_ptr(),))
 
 
 def neg_ext_index(batch_idx, seq_idx, B, NEG, W, S):
     ext = torch.empty_like(batch_idx)
-    check(lib().cpc_neg_ext_index(ptr(batch_idx), ptr(seq_idx), ptr(ext), B, NEG, W, S, stream_ptr()), "cpc_neg_ext_index")
+    _run("cpc_neg_ext_index", (ptr(batch_idx), ptr(seq_idx), ptr(ext), B, NEG, W, S, stream_ptr(),))
     return ext
 
 
@@ -200,13 +241,17 @@ def _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld):
 def nce_fwd(logits, ext, weights, lse, loss_sum, hits, K, B, W, S, NEG, ld):
     d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
     d.loss_sum, d.hits = _dp(loss_sum), _dp(hits)
-    check(lib().cpc_nce_fwd(ctypes.byref(d), stream_ptr()), "cpc_nce_fwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=4.0 * K * B * W * (NEG + 1) + 8.0 * B * NEG * W)
+    _run("cpc_nce_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld, dlogits_lo=None):
     d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
     d.gscale, d.dlogits, d.dlogits_lo = _dp(gscale), _dp(dlogits), _dp(dlogits_lo)
-    check(lib().cpc_nce_bwd(ctypes.byref(d), stream_ptr()), "cpc_nce_bwd")
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=(4.0 if dlogits_lo is not None else 2.0) * K * B * W * ld + 4.0 * K * B * W * (NEG + 1))
+    _run("cpc_nce_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=None, c_all=None, h_n=None, c_n=None):
@@ -214,14 +259,18 @@ def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=No
     d.N, d.S, d.H = N, S, H
     d.gx, d.w_hh, d.h0, d.c0 = _dp(gx), _dp(w_hh), _dp(h0), _dp(c0)
     d.h_pad, d.out, d.gates, d.c_all, d.h_n, d.c_n = _dp(h_pad), _dp(out), _dp(gates), _dp(c_all), _dp(h_n), _dp(c_n)
-    check(lib().cpc_lstm_fwd(ctypes.byref(d), stream_ptr()), "cpc_lstm_fwd")
+    if PROFILE is not None:
+        set_work(kind="latency", flops=2.0 * N * S * H * 4 * H, steps=S)
+    _run("cpc_lstm_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H, c0=None):
     d = _lib.Lstm()
     d.N, d.S, d.H = N, S, H
     d.w_hh, d.c0, d.gates, d.c_all, d.dout, d.dgates = _dp(w_hh), _dp(c0), _dp(gates), _dp(c_all), _dp(dout), _dp(dgates)
-    check(lib().cpc_lstm_bwd(ctypes.byref(d), stream_ptr()), "cpc_lstm_bwd")
+    if PROFILE is not None:
+        set_work(kind="latency", flops=2.0 * N * S * H * 4 * H, steps=S)
+    _run("cpc_lstm_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p):
@@ -237,10 +286,14 @@ def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p):
 
 def attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
     d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
-    check(lib().cpc_attn_fwd(ctypes.byref(d), stream_ptr()), "cpc_attn_fwd")
+    if PROFILE is not None:
+        set_work(kind="cuda-core", flops=3.0 * G * Bt * Hh * S * S * dk)
+    _run("cpc_attn_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
     d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
     d.dout, d.dqkv, d.dscore, d.dkrel = _dp(dout), _dp(dqkv), _dp(dscore), _dp(dkrel)
-    check(lib().cpc_attn_bwd(ctypes.byref(d), stream_ptr()), "cpc_attn_bwd")
+    if PROFILE is not None:
+        set_work(kind="cuda-core", flops=7.0 * G * Bt * Hh * S * S * dk)
+    _run("cpc_attn_bwd", (ctypes.byref(d), stream_ptr(),))

@@ -175,6 +175,17 @@ class _EncoderFn(torch.autograd.Function):
         p = ctx.p
         dev = dz.device
         grads = [None] * 20
+        # one flat fp32 buffer for every parameter gradient of the encoder (a single memset, and a single
+        # all-reduce bucket for the data-parallel wrapper); per-parameter gradients are views of it
+        sizes = []
+        for l in range(5):
+            kl = GEOMETRY[l][0]
+            sizes += [C * (1 if l == 0 else C) * kl, C, C, C]
+        gflat = torch.zeros(sum(sizes), device=dev)
+        gv, off = [], 0
+        for n_ in sizes:
+            gv.append(gflat[off:off + n_])
+            off += n_
         d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
         dout, dout_map = d, None
         for l in range(4, 0, -1):
@@ -186,9 +197,7 @@ class _EncoderFn(torch.autograd.Function):
             dy = torch.empty(N, Lout + 2, C, device=dev, dtype=BF16)
             dy[:, 0].zero_()
             dy[:, Lout + 1].zero_()
-            dg = torch.zeros(C, device=dev)
-            db = torch.zeros(C, device=dev)
-            dcb = torch.zeros(C, device=dev)
+            dw, dcb, dg, db = gv[4 * l:4 * l + 4]
             K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
                           dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,
                           dx_map=K.rowmap(Lout, Lout + 2, 1), unbiased=True, relu=True)
@@ -198,9 +207,8 @@ class _EncoderFn(torch.autograd.Function):
             B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
             K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout, k_splits=ops.auto_splits(C, k * C, N * Lout, 1, Lout),
                    out_f32=dwf, accumulate=True)
-            dw = torch.empty(C, C, k, device=dev)
             K.conv_wgrad_unpack(dwf, dw, C, C, k)
-            grads[4 * l:4 * l + 4] = [dw, dcb, dg.view(1, C, 1), db.view(1, C, 1)]
+            grads[4 * l:4 * l + 4] = [dw.view(C, C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
             # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
             A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
             if ops.GRAD_F32 and l >= 2:
@@ -210,10 +218,7 @@ class _EncoderFn(torch.autograd.Function):
                 dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
             dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
-        dw0 = torch.zeros(C, 10, device=dev)
-        db0 = torch.zeros(C, device=dev)
-        dg0 = torch.zeros(C, device=dev)
-        dbe0 = torch.zeros(C, device=dev)
+        dw0, db0, dg0, dbe0 = gv[0:4]
         K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
                     pad_next[0])
         grads[0:4] = [dw0.view(C, 1, 10), db0, dg0.view(1, C, 1), dbe0.view(1, C, 1)]
@@ -311,21 +316,29 @@ class _LstmFn(torch.autograd.Function):
         dev = dout.device
         d = dout.contiguous().float()
         grads = [None] * (4 * nl)
+        sizes = []
+        for l in range(nl):
+            sizes += [4 * H * ctx.saved[l][1], 4 * H * H, 4 * H, 4 * H]
+        gflat = torch.zeros(sum(sizes), device=dev)
+        gv, off = [], 0
+        for n_ in sizes:
+            gv.append(gflat[off:off + n_])
+            off += n_
         for l in range(nl - 1, -1, -1):
             x_in, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l = ctx.saved[l]
             dgates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
             K.lstm_bwd(w_hh16, gates, c_all, d, dgates, N, S, H, c0=c0l)
             dg2 = dgates.view(N * S, 4 * H)
-            dbias = torch.zeros(4 * H, device=dev)
+            dw_ih, dw_hh = gv[4 * l].view(4 * H, Kin), gv[4 * l + 1].view(4 * H, H)
+            dbias, dbias2 = gv[4 * l + 2], gv[4 * l + 3]
             K.colsum(dg2, dbias, N * S, 4 * H, 4 * H)
+            dbias2.copy_(dbias)
             # dW_hh = sum_{n,t} dgates[n,t]^T h_{t-1}[n]  (slabs = sequences, h_pad row t is h_{t-1})
-            dw_hh = torch.zeros(4 * H, H, device=dev)
             Ag = K.View(dgates, 4 * H, S, N, 4 * H, S * 4 * H, major=1)
             Bh = K.View(h_pad, H, S + 1, N, H, (S + 1) * H, major=1)
             K.gemm(Ag, Bh, 4 * H, H, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, H, N * S, 1, S),
                    out_f32=dw_hh, accumulate=True)
             # dW_ih = dgates^T . input
-            dw_ih = torch.zeros(4 * H, Kin, device=dev)
             if l == 0:
                 K.gemm(K.mnmajor(dg2), K.mnmajor(x_in), 4 * H, Kin, N * S,
                        k_splits=ops.auto_splits(4 * H, Kin, N * S), out_f32=dw_ih, accumulate=True)
@@ -333,7 +346,7 @@ class _LstmFn(torch.autograd.Function):
                 Bx = K.View(x_in, H, S + 1, N, H, (S + 1) * H, major=1, row_off=1)
                 K.gemm(Ag, Bx, 4 * H, Kin, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, Kin, N * S, 1, S),
                        out_f32=dw_ih, accumulate=True)
-            grads[4 * l:4 * l + 4] = [dw_ih, dw_hh, dbias, dbias.clone()]
+            grads[4 * l:4 * l + 4] = [dw_ih, dw_hh, dbias, dbias2]
             # dx = dgates . W_ih
             dx = torch.empty(N * S, Kin, device=dev)
             K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
