@@ -15,10 +15,14 @@
 // (k = slab*k_per_slab + kk) mapped to the outer tensor-map coordinate, which is how a reduction that runs
 // over (batch, time) or over (head, feature) is expressed without copying.
 //
-// CTA = 128 x BN output tile, 6 warps: warp0 TMA producer, warp1 MMA issuer (one elected thread) + TMEM
-// allocator, warps 2-5 epilogue (TMEM -> registers -> global).  K pipeline of STAGES smem stages guarded by
-// full/empty mbarriers; split-K across blockIdx.z with fp32 red.global.add for the skinny weight-gradient
-// shapes.
+// PERSISTENT CTAs (grid = min(tiles, SMs)) walk 128 x BN output tiles; 10 warps: warp0 TMA producer, warp1 MMA
+// issuer (one elected thread) + TMEM allocator, warps 2-9 epilogue.  K pipeline of STAGES smem stages guarded by
+// full/empty mbarriers; the accumulator is DOUBLE-BUFFERED in TMEM (2*BN columns) so the epilogue of one tile
+// overlaps the main loop of the next.  The epilogue reads TMEM with tcgen05.ld.16x256b (mma C-fragment layout:
+// four lanes cover 32 contiguous bytes of an output row) so every global access (outputs, residual, gate,
+// split-K reductions) is sector-coalesced: the thread-per-row 32x32b layout costs 32 sectors per store and
+// was 5-10x slower than the MMAs of the K=256 shapes that dominate this workload.  Split-K uses fp32
+// red.global.add.v2.
 #include "cpc_internal.h"
 #include "ptx.cuh"
 
@@ -33,6 +37,7 @@ struct GemmKernelArgs {
   int k_per_slab;
   int total_kblocks;  // slabs * kblocks_per_slab
   int k_splits;
+  int tiles_m, tiles_n, total_tiles;
   int a_row_off, a_gmul;
   int b_row_off, b_gmul;
   float alpha;
@@ -54,17 +59,43 @@ struct GemmKernelArgs {
   int accumulate;
 };
 
+constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, each owns half of the tile's columns
+constexpr int GEMM_THREADS = (2 + EPI_WARPS) * 32;
+
 template <int BN, int STAGES>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 1) * 8 + 16 + 1024;  // + alignment slack
+  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
+  static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (128 / 256 / 512 columns)
 };
 
+struct TileCoord {
+  int m0, n0, grp, kb_begin, nkb;
+};
+__device__ __forceinline__ TileCoord decode_tile(const GemmKernelArgs& p, int tile, int bn) {
+  TileCoord t;
+  const int mi = tile % p.tiles_m;
+  const int r = tile / p.tiles_m;
+  const int ni = r % p.tiles_n;
+  const int z = r / p.tiles_n;
+  t.m0 = mi * BM;
+  t.n0 = ni * bn;
+  t.grp = z / p.k_splits;
+  const int split = z % p.k_splits;
+  const int kb_per = (p.total_kblocks + p.k_splits - 1) / p.k_splits;
+  t.kb_begin = split * kb_per;
+  t.nkb = min(p.total_kblocks, t.kb_begin + kb_per) - t.kb_begin;
+  return t;
+}
+
+// PERSISTENT kernel: grid = min(tiles, SMs); CTA walks tiles blockIdx.x, +gridDim.x, ...  The accumulator is
+// double-buffered in TMEM so the epilogue of tile i (TMEM -> registers -> smem transpose -> coalesced global)
+// overlaps the TMA/MMA main loop of tile i+1.
 template <int BN, int STAGES, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmKernelArgs p) {
   using L = GemmSmem<BN, STAGES>;
@@ -72,20 +103,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
   uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* accum_bar = empty_bar + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint64_t* acc_full = empty_bar + STAGES;  // [2]
+  uint64_t* acc_empty = acc_full + 2;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM;
-  const int n0 = blockIdx.y * BN;
-  const int grp = blockIdx.z / p.k_splits;
-  const int split = blockIdx.z % p.k_splits;
-  // contiguous range of k-blocks for this split
-  const int kb_per = (p.total_kblocks + p.k_splits - 1) / p.k_splits;
-  const int kb_begin = split * kb_per;
-  const int kb_end = min(p.total_kblocks, kb_begin + kb_per);
-  const int nkb = kb_end - kb_begin;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -94,11 +117,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(accum_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], EPI_WARPS);
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, BN);
+    tmem_alloc(tmem_slot, L::TMEM_COLS);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -106,15 +132,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (nkb > 0) {
-    if (warp == 0) {
-      if (lane == 0) {
-        for (int it = 0; it < nkb; ++it) {
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(p, tile, BN);
+        for (int i = 0; i < tc.nkb; ++i, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
           mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
-          const int kb = kb_begin + it;
+          const int kb = tc.kb_begin + i;
           const int slab = kb / p.kblocks_per_slab;
           const int kk = (kb % p.kblocks_per_slab) * BK;
           uint8_t* sa = smem + s * L::STAGE_BYTES;
@@ -122,25 +151,34 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[s], m0 + j * 64, kk + p.a_row_off,
-                          grp * p.a_gmul + slab);
+              tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[s], tc.m0 + j * 64, kk + p.a_row_off,
+                          tc.grp * p.a_gmul + slab);
           } else {
-            tma_load_3d(sa, &tmA, &full_bar[s], kk, m0 + p.a_row_off, grp * p.a_gmul + slab);
+            tma_load_3d(sa, &tmA, &full_bar[s], kk, tc.m0 + p.a_row_off, tc.grp * p.a_gmul + slab);
           }
           if (B_MN) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              tma_load_3d(sb + j * (BK * 128), &tmB, &full_bar[s], n0 + j * 64, kk + p.b_row_off,
-                          grp * p.b_gmul + slab);
+              tma_load_3d(sb + j * (BK * 128), &tmB, &full_bar[s], tc.n0 + j * 64, kk + p.b_row_off,
+                          tc.grp * p.b_gmul + slab);
           } else {
-            tma_load_3d(sb, &tmB, &full_bar[s], kk, n0 + p.b_row_off, grp * p.b_gmul + slab);
+            tma_load_3d(sb, &tmB, &full_bar[s], kk, tc.n0 + p.b_row_off, tc.grp * p.b_gmul + slab);
           }
         }
       }
-    } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-        for (int it = 0; it < nkb; ++it) {
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
+        const TileCoord tc = decode_tile(p, tile, BN);
+        const int buf = lt & 1;
+        mbar_wait(&acc_empty[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t dcol = tmem_base + buf * BN;
+        for (int i = 0; i < tc.nkb; ++i, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&full_bar[s], ph);
@@ -156,101 +194,147 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                      : umma_smem_desc(sa + k * 32, 16, 1024, 2);
             const uint64_t bd = B_MN ? umma_smem_desc(sb + k * 2048, BK * 128, 1024, 2)
                                      : umma_smem_desc(sb + k * 32, 16, 1024, 2);
-            umma_ss(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+            umma_ss(dcol, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);  // frees this smem stage when the MMAs above retire
         }
-        umma_commit(accum_bar);  // accumulator complete
+        umma_commit(&acc_full[buf]);  // accumulator of this tile complete
       }
-    } else {
-      // ------------------------------------------------------------------ epilogue (warps 2..5)
-      const int q = warp & 3;  // TMEM lane quarter this warp may access
-      const int row = m0 + q * 32 + lane;
-      mbar_wait(accum_bar, 0);
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..9)
+    // tcgen05.ld.16x256b hands every thread the accumulator in the mma C-fragment layout: per 8-column group,
+    // thread t holds columns 2*(t%4), +1 of rows t/4 and t/4 + 8.  Four lanes therefore cover 32 contiguous bytes
+    // of one fp32 output row (a full sector; 16 bytes for bf16), so global accesses are sector-coalesced with no
+    // shared-memory transpose and every load/store of a chunk is independent (high ILP).
+    const int e = warp - 2;
+    const int q = warp & 3;       // TMEM lane quarter this warp may access
+    const int half = e >> 2;      // which half of the tile's columns
+    const int rsub = lane >> 2;         // row inside an 8-row slice
+    const int csub = (lane & 3) * 2;    // first of this lane's two columns inside an 8-column group
+    uint32_t seed_lo = 0, seed_hi = 0, drop_thresh = 0;
+    float drop_scale = 1.f;
+    if (p.rng != nullptr && p.drop_p > 0.f) {
+      const unsigned long long seed = p.rng[0] + p.rng[1] * 0x632BE59BD9B4E019ull;
+      seed_lo = static_cast<uint32_t>(seed);
+      seed_hi = static_cast<uint32_t>(seed >> 32) + p.rng_site * 0x85EBCA77u;
+      drop_thresh = static_cast<uint32_t>(fminf(p.drop_p, 0.9999f) * 65536.0f);
+      drop_scale = 1.f / (1.f - p.drop_p);
+    }
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
+      const TileCoord tc = decode_tile(p, tile, BN);
+      const int buf = lt & 1;
+      const long long g = tc.grp;
+      mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-      const bool row_ok = row < p.M;
-      const long long g = grp;
-      unsigned long long seed = 0;
-      uint32_t drop_thresh = 0;
-      float drop_scale = 1.f;
-      if (p.rng != nullptr && p.drop_p > 0.f) {
-        seed = p.rng[0] + p.rng[1] * 0x632BE59BD9B4E019ull;
-        drop_thresh = static_cast<uint32_t>(fminf(p.drop_p, 0.999999f) * 4294967296.0f);
-        drop_scale = 1.f / (1.f - p.drop_p);
-      }
+      const int row0 = tc.m0 + q * 32 + rsub;  // this lane's rows: row0 + 8*i, i = 0..3
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + half * (BN / 2);
+      const float* bias_g = p.bias != nullptr ? p.bias + g * p.gs_bias : nullptr;
+      const float relu_floor = p.relu ? 0.f : -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+      for (int c = 0; c < BN / 64; ++c) {
+        const int n_base = tc.n0 + half * (BN / 2) + c * 32 + csub;  // column of v[..][0] for j = 0
+        uint32_t v[2][16];
+        tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+        tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
         tmem_ld_wait();
-        const int nb = n0 + c * 32;
-        if (row_ok && nb < p.N) {
+        // number of valid 8-column groups of this chunk (warp-uniform: N is a multiple of 8)
+        const int jmax = min(4, (p.N - (n_base - csub)) >> 3);
+        if (jmax <= 0) continue;
+        float2 b2[4];
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const int n = nb + j;
-            if (n < p.N) {
-              float x[4];
+        for (int j = 0; j < 4; ++j) {
+          b2[j] = make_float2(0.f, 0.f);
+          if (bias_g != nullptr && j < jmax) b2[j] = *reinterpret_cast<const float2*>(bias_g + n_base + 8 * j);
+        }
 #pragma unroll
-              for (int e = 0; e < 4; ++e) x[e] = __uint_as_float(v[j + e]) * p.alpha;
-              if (p.bias != nullptr) {
-                const float4 b = *reinterpret_cast<const float4*>(p.bias + g * p.gs_bias + n);
-                x[0] += b.x; x[1] += b.y; x[2] += b.z; x[3] += b.w;
-              }
-              if (p.res != nullptr) {
-                const uint2 r = *reinterpret_cast<const uint2*>(p.res + g * p.gs_res + (long long)row * p.ld_res + n);
-                const __nv_bfloat162 r0 = *reinterpret_cast<const __nv_bfloat162*>(&r.x);
-                const __nv_bfloat162 r1 = *reinterpret_cast<const __nv_bfloat162*>(&r.y);
-                x[0] += __low2float(r0); x[1] += __high2float(r0);
-                x[2] += __low2float(r1); x[3] += __high2float(r1);
-              }
-              if (p.relu) {
+        for (int i = 0; i < 4; ++i) {
+          const int row = row0 + 8 * i;
+          if (row >= p.M) continue;
+          const long long rl = row;
+          // v[i >> 1] holds rows +0 / +8 (regs 0,1 / 2,3 of each column group) of the 16-lane slice i >> 1
+          float x[8];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) x[e] = fmaxf(x[e], 0.f);
-              }
-              if (p.gate != nullptr) {
-                const uint2 r = *reinterpret_cast<const uint2*>(p.gate + g * p.gs_gate + (long long)row * p.ld_gate + n);
-                const __nv_bfloat162 r0 = *reinterpret_cast<const __nv_bfloat162*>(&r.x);
-                const __nv_bfloat162 r1 = *reinterpret_cast<const __nv_bfloat162*>(&r.y);
-                x[0] = __low2float(r0) > 0.f ? x[0] * p.gate_scale : 0.f;
-                x[1] = __high2float(r0) > 0.f ? x[1] * p.gate_scale : 0.f;
-                x[2] = __low2float(r1) > 0.f ? x[2] * p.gate_scale : 0.f;
-                x[3] = __high2float(r1) > 0.f ? x[3] * p.gate_scale : 0.f;
-              }
-              if (drop_thresh != 0) {
-                const unsigned long long base = ((unsigned long long)g * p.M + row) * (unsigned long long)p.N + n;
+          for (int j = 0; j < 4; ++j) {
+            x[2 * j] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), p.alpha, b2[j].x);
+            x[2 * j + 1] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), p.alpha, b2[j].y);
+          }
+          if (p.res != nullptr) {
+            const __nv_bfloat16* res_r = p.res + g * p.gs_res + rl * p.ld_res + n_base;
+            __nv_bfloat162 r[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e)
-                  x[e] = rng_u32(seed, p.rng_site, base + e) >= drop_thresh ? x[e] * drop_scale : 0.f;
-              }
-              if (p.out_f32 != nullptr) {
-                float* o = p.out_f32 + g * p.gs_f32 + (long long)row * p.ldd_f32 + n;
-                if (p.k_splits > 1) {
-                  red_add_v4_f32(o, x[0], x[1], x[2], x[3]);
-                } else if (p.accumulate) {
-                  float4 old = *reinterpret_cast<float4*>(o);
-                  old.x += x[0]; old.y += x[1]; old.z += x[2]; old.w += x[3];
-                  *reinterpret_cast<float4*>(o) = old;
-                } else {
-                  *reinterpret_cast<float4*>(o) = make_float4(x[0], x[1], x[2], x[3]);
+            for (int j = 0; j < 4; ++j)
+              r[j] = j < jmax ? *reinterpret_cast<const __nv_bfloat162*>(res_r + 8 * j) : __floats2bfloat162_rn(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              x[2 * j] += __low2float(r[j]);
+              x[2 * j + 1] += __high2float(r[j]);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], relu_floor);
+          if (p.gate != nullptr) {
+            const __nv_bfloat16* gate_r = p.gate + g * p.gs_gate + rl * p.ld_gate + n_base;
+            __nv_bfloat162 r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              r[j] = j < jmax ? *reinterpret_cast<const __nv_bfloat162*>(gate_r + 8 * j) : __floats2bfloat162_rn(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              x[2 * j] = __low2float(r[j]) > 0.f ? x[2 * j] * p.gate_scale : 0.f;
+              x[2 * j + 1] = __high2float(r[j]) > 0.f ? x[2 * j + 1] * p.gate_scale : 0.f;
+            }
+          }
+          if (drop_thresh != 0) {
+            const unsigned long long ebase = (((unsigned long long)g * p.M + row) * (unsigned long long)p.N + n_base) >> 1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {  // one 32-bit draw per 2 consecutive columns
+              const uint32_t bits = rng_pair_u16(seed_lo, seed_hi, ebase + 4 * j);
+              x[2 * j] = (bits & 0xFFFFu) >= drop_thresh ? x[2 * j] * drop_scale : 0.f;
+              x[2 * j + 1] = (bits >> 16) >= drop_thresh ? x[2 * j + 1] * drop_scale : 0.f;
+            }
+          }
+          if (p.out_bf16 != nullptr) {
+            __nv_bfloat16* o16 = p.out_bf16 + g * p.gs_bf16 + rl * p.ldd_bf16 + n_base;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (j < jmax) *reinterpret_cast<__nv_bfloat162*>(o16 + 8 * j) = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+          }
+          if (p.out_f32 != nullptr) {
+            float* o32 = p.out_f32 + g * p.gs_f32 + rl * p.ldd_f32 + n_base;
+            if (p.k_splits > 1) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (j < jmax) red_add_v2_f32(o32 + 8 * j, x[2 * j], x[2 * j + 1]);
+            } else {
+              if (p.accumulate) {
+                float2 old[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  old[j] = j < jmax ? *reinterpret_cast<const float2*>(o32 + 8 * j) : make_float2(0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  x[2 * j] += old[j].x;
+                  x[2 * j + 1] += old[j].y;
                 }
               }
-              if (p.out_bf16 != nullptr) {
-                __nv_bfloat162 o0 = __floats2bfloat162_rn(x[0], x[1]);
-                __nv_bfloat162 o1 = __floats2bfloat162_rn(x[2], x[3]);
-                uint2 pk;
-                pk.x = *reinterpret_cast<uint32_t*>(&o0);
-                pk.y = *reinterpret_cast<uint32_t*>(&o1);
-                *reinterpret_cast<uint2*>(p.out_bf16 + g * p.gs_bf16 + (long long)row * p.ldd_bf16 + n) = pk;
-              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (j < jmax) *reinterpret_cast<float2*>(o32 + 8 * j) = make_float2(x[2 * j], x[2 * j + 1]);
             }
           }
         }
       }
+      // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld above): hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, BN);
+  if (warp == 1) tmem_dealloc(tmem_base, L::TMEM_COLS);
 }
 
 // ----------------------------------------------------------------------------------------------- host
@@ -275,8 +359,21 @@ static int encode_operand_map(CUtensorMap* map, const void* ptr, long long d0, l
   return r == CUDA_SUCCESS ? CPC_OK : CPC_ERR_TENSORMAP;
 }
 
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      n = v;
+    else
+      n = 148;
+  }
+  return n;
+}
+
 template <int BN, int STAGES, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int groups,
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelArgs ka, int groups,
                        cudaStream_t stream) {
   using L = GemmSmem<BN, STAGES>;
   auto kern = gemm_bf16_tcgen05_kernel<BN, STAGES, A_MN, B_MN>;
@@ -286,8 +383,11 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmK
       return CPC_ERR_LAUNCH;
     attr_done = true;
   }
-  dim3 grid((ka.M + BM - 1) / BM, (ka.N + BN - 1) / BN, groups * ka.k_splits);
-  kern<<<grid, 192, L::TOTAL, stream>>>(ta, tb, ka);
+  ka.tiles_m = (ka.M + BM - 1) / BM;
+  ka.tiles_n = (ka.N + BN - 1) / BN;
+  ka.total_tiles = ka.tiles_m * ka.tiles_n * groups * ka.k_splits;
+  const int grid = ka.total_tiles < sm_count() ? ka.total_tiles : sm_count();
+  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, ka);
   return cudaGetLastError() == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
 }
 
@@ -340,13 +440,31 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   ka.rng = static_cast<const unsigned long long*>(d->rng); ka.rng_site = d->rng_site; ka.drop_p = d->drop_p;
   ka.relu = d->relu; ka.accumulate = d->accumulate;
 
-  // tile-N selection: widest tile unless that leaves most of the 148 SMs without a CTA
-  int bn = 256;
-  if (d->N <= 64) bn = 64;
-  else if (d->N <= 128) bn = 128;
-  else {
-    const long long tiles256 = (long long)((d->M + BM - 1) / BM) * ((d->N + 255) / 256) * d->groups * k_splits;
-    if (tiles256 < 120) bn = 128;
+  // tile-N selection: minimise (waves over the SMs) x (cost of one 128 x bn tile), in SM cycles.  Per 64-wide
+  // k-block the tensor pipe needs max(2*bn, shared-memory operand reads at 128 B/cycle) cycles, and TMA has to
+  // deliver 16 KB + bn*128 B at the SM's share of the ~6300 B/cycle the L2 sustains chip-wide (<= ~128 B/cycle
+  // per SM): narrow tiles re-read A more often, wide tiles leave SMs idle on small problems.  Draining the
+  // accumulator costs ~8*bn cycles (TMEM read 64 B/cycle) and overlaps the next tile's main loop.
+  int bn = 64;
+  {
+    const int sms = sm_count();
+    const int nkb = (ka.total_kblocks + k_splits - 1) / k_splits;
+    double best = 1e30;
+    for (int cand = 64; cand <= 256; cand *= 2) {
+      if (cand > 64 && cand / 2 >= d->N) break;  // a wider tile would only add padding
+      const long long tiles = (long long)((d->M + BM - 1) / BM) * ((d->N + cand - 1) / cand) * d->groups * k_splits;
+      const long long waves = (tiles + sms - 1) / sms;
+      const double active = tiles < sms ? (double)tiles : (double)sms;
+      double rate = 6300.0 / active;
+      if (rate > 128.0) rate = 128.0;
+      const double load = (16384.0 + 128.0 * cand) / rate;
+      double mma = 2.0 * cand;
+      const double smem_rd = (4096.0 + 32.0 * cand) * 4.0 / 128.0;
+      if (smem_rd > mma) mma = smem_rd;
+      const double kb = load > mma ? load : mma;
+      const double cost = waves * nkb * kb + 8.0 * cand + 3000.0;
+      if (cost < best) { best = cost; bn = cand; }
+    }
   }
   if (d->force_bn == 64 || d->force_bn == 128 || d->force_bn == 256) bn = d->force_bn;
 

@@ -159,6 +159,17 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)
       : "r"(taddr)
       : "memory");
 }
+// 16 lanes x 256 bits, repeated 4x along columns (32 columns): mma C-fragment layout.  For repetition j, thread t
+// holds columns 8j + 2*(t%4), +1 of lane (base + t/4) in r[4j], r[4j+1] and of lane (base + t/4 + 8) in r[4j+2], r[4j+3].
+__device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.16x256b.x4.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -227,6 +238,9 @@ __device__ __forceinline__ void red_add_v4_f32(float* p, float a, float b, float
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
                : "memory");
 }
+__device__ __forceinline__ void red_add_v2_f32(float* p, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -237,13 +251,24 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
-// counter-based RNG for dropout: one 32-bit draw per (seed, site, index). splitmix64 finaliser.
-__device__ __forceinline__ uint32_t rng_u32(uint64_t seed, uint32_t site, uint64_t idx) {
+// counter-based RNG for dropout: one 64-bit draw per (seed, site, index). splitmix64 finaliser.
+__device__ __forceinline__ uint64_t rng_u64(uint64_t seed, uint32_t site, uint64_t idx) {
   uint64_t x = seed + 0x9E3779B97F4A7C15ull * (idx + 1) + (static_cast<uint64_t>(site) << 48);
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
   x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-  x = x ^ (x >> 31);
-  return static_cast<uint32_t>(x >> 32);
+  return x ^ (x >> 31);
+}
+// two 16-bit draws for a pair of consecutive elements (GEMM epilogue dropout): lowbias32 finaliser
+__device__ __forceinline__ uint32_t rng_pair_u16(uint32_t seed_lo, uint32_t seed_hi, uint64_t idx2) {
+  uint32_t h = static_cast<uint32_t>(idx2) * 0x9E3779B1u + seed_lo;
+  h ^= seed_hi + static_cast<uint32_t>(idx2 >> 32) * 0xC2B2AE3Du;
+  h ^= h >> 16; h *= 0x7FEB352Du;
+  h ^= h >> 15; h *= 0x846CA68Bu;
+  h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t rng_u32(uint64_t seed, uint32_t site, uint64_t idx) {
+  return static_cast<uint32_t>(rng_u64(seed, site, idx) >> 32);
 }
 
 }  // namespace cpc
