@@ -12,27 +12,10 @@
 // (seed, site, element index), so forward and backward regenerate the same mask with no mask tensor.
 #include "cpc_internal.h"
 #include "ptx.cuh"
+#include "attn_args.h"
 
 namespace cpc {
 
-struct AttnArgs {
-  const __nv_bfloat16* qkv;  // [G][T][3d]: q | k | v, head h at columns h*dk
-  long long gs_qkv;
-  const float* krel;  // [G][dk][S] or null
-  __nv_bfloat16* out;  // [G][T][d]
-  long long gs_out;
-  __nv_bfloat16* probs;  // [G][Bt][Hh][S][S] softmax probabilities before dropout
-  int S, dk, d, Bt, Hh;
-  float scale;
-  const unsigned long long* rng;
-  unsigned int site;
-  float drop_p;
-  // backward
-  const __nv_bfloat16* dout;  // [G][T][d]
-  __nv_bfloat16* dqkv;        // [G][T][3d]
-  __nv_bfloat16* dscore;      // scratch, same shape as probs
-  float* dkrel;               // [G][dk][S], atomically accumulated
-};
 
 __device__ __forceinline__ float ldf(const float* p) { return *p; }
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p) { return __bfloat162float(*p); }
@@ -251,6 +234,7 @@ extern "C" int cpc_attn_fwd(const CpcAttn* d, void* stream_) {
   int rc = fill_attn(a, d);
   if (rc != CPC_OK) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (attn_tc_supported(a)) return attn_fwd_tc(a, d->G, stream);
   dim3 grid(a.Hh, a.Bt, d->G);
   size_t sm = attn_smem<float>(a.S, a.dk, false);
   if (sm <= 100 * 1024) {
@@ -268,8 +252,10 @@ extern "C" int cpc_attn_bwd(const CpcAttn* d, void* stream_) {
   AttnArgs a;
   int rc = fill_attn(a, d);
   if (rc != CPC_OK) return rc;
-  if (a.dout == nullptr || a.dqkv == nullptr || a.dscore == nullptr) return CPC_ERR_ARG;
+  if (a.dout == nullptr || a.dqkv == nullptr) return CPC_ERR_ARG;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (attn_tc_supported(a)) return attn_bwd_tc(a, d->G, stream);
+  if (a.dscore == nullptr) return CPC_ERR_ARG;
   dim3 grid(a.Hh, a.Bt, d->G);
   size_t sm = attn_smem<float>(a.S, a.dk, true);
   if (sm <= 100 * 1024) {

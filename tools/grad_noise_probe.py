@@ -23,7 +23,7 @@ def rounded_state(model, crit):
     """Oracle weights with every tensor the GPU path consumes in bf16 rounded to bf16 (same function, fp32 math)."""
     st = ts._state_for_oracle(model, crit)
     for k, v in st.items():
-        is_gemm_w = v.dim() >= 2 and not k.endswith("Krelpos") and "conv0" not in k and "batchNorm" not in k
+        is_gemm_w = v.dim() >= 2 and (os.environ.get("ROUND_KREL") or not k.endswith("Krelpos")) and "conv0" not in k and "batchNorm" not in k
         if is_gemm_w:
             st[k] = v.to(torch.bfloat16).float()
     return st
