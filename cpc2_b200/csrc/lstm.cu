@@ -50,13 +50,23 @@ struct LstmArgs {
   __nv_bfloat16* dgates;      // [N, S, 4H] bf16 gradient w.r.t. the gate pre-activations
 };
 
-constexpr int NB = 16;  // sequences per cluster
+constexpr int NB = 8;          // sequences per cluster: one mma n-tile.  Small on purpose -- the recurrence is
+                               // latency-bound and the rest of the chip is idle, so more clusters beat wider ones
+constexpr int LSTM_THREADS = 256;
+
+// Per-step input tile of one CTA: its 4 x 32 gate columns of gx for the cluster's 8 sequences, fp32, fetched two
+// steps ahead with cp.async (16-byte chunks: every (sequence, gate) is one contiguous 128-byte segment).
+constexpr int GX_PITCH = 132;  // floats per sequence row: bank = 4*b + unit -> conflict-free reads
 
 template <int H>
-__global__ void __launch_bounds__(256, 1) lstm_fwd_kernel(const LstmArgs a) {
+__global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArgs a) {
   constexpr int CL = H / 32, KT = H / 16, HP = H + 8;
-  __shared__ __align__(16) __nv_bfloat16 h_s[2][NB][HP];
-  __shared__ __align__(16) __nv_bfloat16 stage[NB][32];
+  __shared__ __align__(16) __nv_bfloat16 h_s[2][NB][HP];          // h_{t-1} of the whole cluster (double-buffered)
+  __shared__ __align__(16) float gx_s[3][NB][GX_PITCH];           // prefetched input projections
+  __shared__ __align__(16) __nv_bfloat16 st_h[2][NB][40];         // this CTA's new h slice (bf16): DSMEM push, h_pad
+  __shared__ __align__(16) float st_o[2][NB][36];                 // ... fp32 (module output)
+  __shared__ __align__(16) float st_c[2][NB][36];                 // new cell state
+  __shared__ __align__(16) __nv_bfloat16 st_g[2][NB][136];        // post-activation gates i|f|g|o
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t cta = cluster_ctarank();
@@ -66,6 +76,9 @@ __global__ void __launch_bounds__(256, 1) lstm_fwd_kernel(const LstmArgs a) {
   const int unit_l = warp * 4 + u;   // unit inside the CTA's 32
   const int unit = cta * 32 + unit_l;
   const int H4 = 4 * H;
+  const int bsel = (lane & 3) * 2 + g0;   // the sequence this thread finishes after the gate exchange
+  const int nidx = n_base + bsel;
+  const bool valid = nidx < a.N;
 
   // W_hh rows of this thread's two fragment rows, resident for the whole kernel
   uint32_t afr[KT][4];
@@ -81,7 +94,7 @@ __global__ void __launch_bounds__(256, 1) lstm_fwd_kernel(const LstmArgs a) {
       afr[kt][3] = *reinterpret_cast<const uint32_t*>(w1 + k + 8);
     }
   }
-  for (int i = tid; i < NB * H; i += 256) {
+  for (int i = tid; i < NB * H; i += LSTM_THREADS) {
     const int b = i / H, k = i % H, n = n_base + b;
     const float v = (a.h0 != nullptr && n < a.N) ? a.h0[(long long)n * H + k] : 0.f;
     h_s[0][b][k] = __float2bfloat16(v);
@@ -92,124 +105,140 @@ __global__ void __launch_bounds__(256, 1) lstm_fwd_kernel(const LstmArgs a) {
     mbar_init(&bar[1], CL);
     fence_barrier_init();
   }
-  cluster_sync_all();
+  // gx prefetch: thread -> (sequence, gate, 16-byte chunk)
+  const int pf_b = tid >> 5, pf_g = (tid >> 3) & 3, pf_ch = tid & 7;
+  const bool pf_ok = n_base + pf_b < a.N;
+  const float* pf_src = a.gx + ((long long)(n_base + pf_b) * a.S) * H4 + pf_g * H + cta * 32 + pf_ch * 4;
+  auto prefetch = [&](int t) {
+    if (pf_ok && t < a.S) cp_async_16(&gx_s[t % 3][pf_b][pf_g * 32 + pf_ch * 4], pf_src + (long long)t * H4);
+    cp_async_commit();
+  };
+  prefetch(0);
+  prefetch(1);
+  cp_async_wait<1>();
+  cluster_sync_all();  // barriers initialised cluster-wide, h_s[0] and gx_s[0] visible
 
-  int bsel[2], nidx[2];
-  bool valid[2];
-  float c_state[2], gxv[2][4];
-#pragma unroll
-  for (int nt = 0; nt < 2; ++nt) {
-    bsel[nt] = nt * 8 + (lane & 3) * 2 + g0;
-    nidx[nt] = n_base + bsel[nt];
-    valid[nt] = nidx[nt] < a.N;
-    c_state[nt] = (valid[nt] && a.c0 != nullptr) ? a.c0[(long long)nidx[nt] * H + unit] : 0.f;
-#pragma unroll
-    for (int g = 0; g < 4; ++g)
-      gxv[nt][g] = valid[nt] ? a.gx[((long long)nidx[nt] * a.S + 0) * H4 + g * H + unit] : 0.f;
-  }
+  float c_state = (valid && a.c0 != nullptr) ? a.c0[(long long)nidx * H + unit] : 0.f;
 
   for (int t = 0; t < a.S; ++t) {
     const int p = t & 1;
+    prefetch(t + 2);
     if (t > 0) mbar_wait_cluster(&bar[p], ((t - 1) >> 1) & 1);
-    // prefetch next step's input projection while the MMAs run
-    float gxn[2][4];
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-      for (int g = 0; g < 4; ++g)
-        gxn[nt][g] = (valid[nt] && t + 1 < a.S) ? a.gx[((long long)nidx[nt] * a.S + t + 1) * H4 + g * H + unit] : 0.f;
-
-    float acc[2][2][4];
+    float acc[2][4];
 #pragma unroll
     for (int i = 0; i < 2; ++i)
 #pragma unroll
-      for (int j = 0; j < 2; ++j)
+      for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+    // B fragments: h_s[p][seq][k], two k-tiles per ldmatrix.x4
+    const uint32_t hrow = smem_u32(&h_s[p][lane & 7][(lane >> 3) * 8]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
-#pragma unroll
-    for (int kt = 0; kt < KT; ++kt) {
-      const int k = kt * 16 + (lane & 3) * 2;
-#pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        const __nv_bfloat16* hb = &h_s[p][nt * 8 + (lane >> 2)][k];
-        const uint32_t b0 = *reinterpret_cast<const uint32_t*>(hb);
-        const uint32_t b1 = *reinterpret_cast<const uint32_t*>(hb + 8);
-        mma_bf16_16816(acc[kt & 1][nt], afr[kt], b0, b1);
-      }
+    for (int kt2 = 0; kt2 < KT / 2; ++kt2) {
+      uint32_t bb[4];
+      ldsm_x4(bb, hrow + kt2 * 64);
+      mma_bf16_16816(acc[0], afr[2 * kt2], bb[0], bb[1]);
+      mma_bf16_16816(acc[1], afr[2 * kt2 + 1], bb[2], bb[3]);
     }
+    float c4[4];
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-      float c4[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) c4[e] = acc[0][nt][e] + acc[1][nt][e];
-      // rows (lane/4) and (lane/4 + 8) are gates g0 and g0+2 of unit u; the partner lane (xor 16) holds the
-      // other two gates.  After the exchange thread g0 owns sequence column (lane%4)*2 + g0.
-      const float s0 = g0 ? c4[0] : c4[1];
-      const float s1 = g0 ? c4[2] : c4[3];
-      const float r0 = __shfl_xor_sync(0xffffffffu, s0, 16);
-      const float r1 = __shfl_xor_sync(0xffffffffu, s1, 16);
-      const float pi = (g0 ? r0 : c4[0]) + gxv[nt][0];
-      const float pf = (g0 ? c4[1] : r0) + gxv[nt][1];
-      const float pg = (g0 ? r1 : c4[2]) + gxv[nt][2];
-      const float po = (g0 ? c4[3] : r1) + gxv[nt][3];
-      const float ig = sigmoid_f(pi), fg = sigmoid_f(pf), gg = tanh_f(pg), og = sigmoid_f(po);
-      const float cn = fg * c_state[nt] + ig * gg;
-      const float hn = og * tanh_f(cn);
-      c_state[nt] = cn;
-      stage[bsel[nt]][unit_l] = __float2bfloat16(hn);
-      if (valid[nt]) {
-        const long long row = (long long)nidx[nt] * a.S + t;
-        if (a.out != nullptr) a.out[row * H + unit] = hn;
-        if (a.h_pad != nullptr) a.h_pad[((long long)nidx[nt] * (a.S + 1) + t + 1) * H + unit] = __float2bfloat16(hn);
-        if (a.c_all != nullptr) a.c_all[row * H + unit] = cn;
-        if (a.gates != nullptr) {
-          __nv_bfloat16* gp = a.gates + row * H4 + unit;
-          gp[0] = __float2bfloat16(ig);
-          gp[H] = __float2bfloat16(fg);
-          gp[2 * H] = __float2bfloat16(gg);
-          gp[3 * H] = __float2bfloat16(og);
-        }
-        if (t == a.S - 1) {
-          if (a.h_n != nullptr) a.h_n[(long long)nidx[nt] * H + unit] = hn;
-          if (a.c_n != nullptr) a.c_n[(long long)nidx[nt] * H + unit] = cn;
-        }
-      }
-#pragma unroll
-      for (int g = 0; g < 4; ++g) gxv[nt][g] = gxn[nt][g];
-    }
+    for (int e = 0; e < 4; ++e) c4[e] = acc[0][e] + acc[1][e];
+    // rows (lane/4) and (lane/4 + 8) are gates g0 and g0+2 of unit u for sequences 2*(lane%4), +1; the partner
+    // lane (xor 16) holds the other two gates.  After the exchange this thread owns sequence 2*(lane%4) + g0.
+    const float s0 = g0 ? c4[0] : c4[1];
+    const float s1 = g0 ? c4[2] : c4[3];
+    const float r0 = __shfl_xor_sync(0xffffffffu, s0, 16);
+    const float r1 = __shfl_xor_sync(0xffffffffu, s1, 16);
+    const float* gxr = &gx_s[t % 3][bsel][unit_l];
+    const float pi = (g0 ? r0 : c4[0]) + gxr[0];
+    const float pf = (g0 ? c4[1] : r0) + gxr[32];
+    const float pg = (g0 ? r1 : c4[2]) + gxr[64];
+    const float po = (g0 ? c4[3] : r1) + gxr[96];
+    const float ig = sigmoid_f(pi), fg = sigmoid_f(pf), gg = tanh_f(pg), og = sigmoid_f(po);
+    const float cn = valid ? fg * c_state + ig * gg : 0.f;
+    const float hn = valid ? og * tanh_f(cn) : 0.f;
+    c_state = cn;
+    st_h[p][bsel][unit_l] = __float2bfloat16(hn);
+    st_o[p][bsel][unit_l] = hn;
+    st_c[p][bsel][unit_l] = cn;
+    st_g[p][bsel][unit_l] = __float2bfloat16(ig);
+    st_g[p][bsel][32 + unit_l] = __float2bfloat16(fg);
+    st_g[p][bsel][64 + unit_l] = __float2bfloat16(gg);
+    st_g[p][bsel][96 + unit_l] = __float2bfloat16(og);
+    cp_async_wait<1>();  // gx of step t+1 has landed (only the newest group may be in flight)
     __syncthreads();
     if (t + 1 < a.S) {
-      // push this CTA's [16 x 32] slice of h_t into buffer p^1 of every CTA of the cluster
-      const int chunk = tid & 63, b = chunk >> 2, part = chunk & 3;
-      const uint4 v = *reinterpret_cast<const uint4*>(&stage[b][part * 8]);
+      // warp d pushes this CTA's [8 x 32] bf16 slice of h_t into buffer p^1 of CTA d, then signals it
+      const int b = lane >> 2, part = lane & 3;
+      const uint4 v = *reinterpret_cast<const uint4*>(&st_h[p][b][part * 8]);
       const uint32_t dst = smem_u32(&h_s[p ^ 1][b][cta * 32 + part * 8]);
-      for (int d = tid >> 6; d < CL; d += 4) st_cluster_v4(mapa(dst, d), v.x, v.y, v.z, v.w);
-      __syncthreads();
-      if (tid < CL) mbar_arrive_remote(mapa(smem_u32(&bar[p ^ 1]), tid));
+      for (int d = warp; d < CL; d += LSTM_THREADS / 32) {
+        st_cluster_v4(mapa(dst, d), v.x, v.y, v.z, v.w);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(mapa(smem_u32(&bar[p ^ 1]), d));
+      }
+    }
+    // coalesced global writes of everything the backward (and the caller) needs, off the critical path
+    {
+      const int b = (tid & 63) >> 3, ch = tid & 7, n = n_base + b;
+      const long long row = (long long)n * a.S + t;
+      if (tid < 64) {
+        if (a.out != nullptr && n < a.N)
+          *reinterpret_cast<float4*>(a.out + row * H + cta * 32 + ch * 4) = *reinterpret_cast<const float4*>(&st_o[p][b][ch * 4]);
+      } else if (tid < 128) {
+        if (a.c_all != nullptr && n < a.N)
+          *reinterpret_cast<float4*>(a.c_all + row * H + cta * 32 + ch * 4) = *reinterpret_cast<const float4*>(&st_c[p][b][ch * 4]);
+      } else if (a.gates != nullptr) {
+        // 128 threads: (sequence, gate, 16-byte chunk of the 64-byte segment)
+        const int q = tid - 128, gb = q >> 4, gg_ = (q >> 2) & 3, gc = q & 3;
+        if (n_base + gb < a.N)
+          *reinterpret_cast<uint4*>(a.gates + ((long long)(n_base + gb) * a.S + t) * H4 + gg_ * H + cta * 32 + gc * 8) =
+              *reinterpret_cast<const uint4*>(&st_g[p][gb][gg_ * 32 + gc * 8]);
+      }
+      if (tid < 32 && a.h_pad != nullptr) {
+        const int hb = tid >> 2, hc = tid & 3;
+        if (n_base + hb < a.N)
+          *reinterpret_cast<uint4*>(a.h_pad + ((long long)(n_base + hb) * (a.S + 1) + t + 1) * H + cta * 32 + hc * 8) =
+              *reinterpret_cast<const uint4*>(&st_h[p][hb][hc * 8]);
+      }
+      if (t == a.S - 1 && tid < 64 && n < a.N) {
+        if (a.h_n != nullptr)
+          *reinterpret_cast<float4*>(a.h_n + (long long)n * H + cta * 32 + ch * 4) = *reinterpret_cast<const float4*>(&st_o[p][b][ch * 4]);
+        if (a.c_n != nullptr)
+          *reinterpret_cast<float4*>(a.c_n + (long long)n * H + cta * 32 + ch * 4) = *reinterpret_cast<const float4*>(&st_c[p][b][ch * 4]);
+      }
     }
   }
   cluster_sync_all();  // nobody exits while peers may still target its shared memory
 }
 
+// Backward recurrence.  CTA c owns hidden units [32c, 32c+32): it turns dh into the gate gradients of those units,
+// multiplies them with its 128 rows of W_hh (register-resident A fragments of W_hh^T, K-split over gate rows) and
+// sends each 32-unit block of the partial dh_{t-1} to the CTA that owns it (fp32, st.shared::cluster.v2 straight
+// from the accumulator fragments; warp w's two m-tiles are exactly the block of CTA w when H = 256).
 template <int H>
-__global__ void __launch_bounds__(256, 1) lstm_bwd_kernel(const LstmArgs a) {
+__global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArgs a) {
   constexpr int CL = H / 32;
-  constexpr int MTW = (H / 16 + 7) / 8;        // output (h) m-tiles per warp
-  constexpr int ACTIVE = (H / 16) / MTW;       // warps that own m-tiles
-  constexpr int GP = 128 + 8;                  // padded row of the local gate-gradient tile
-  constexpr int SP = H + 4;                    // padded row of the fp32 partial-dh stage
+  constexpr int MT = H / 16;                      // output (h) m-tiles
+  constexpr int MTW = (MT + 7) / 8;               // m-tiles per warp
+  constexpr int ACTIVE = MT / MTW;                // warps that own m-tiles
+  constexpr int ARRIVALS = CL * (MTW == 1 && MT > 1 ? 2 : 1);  // (warp, destination) pairs per step and barrier
+  constexpr int GP = 136;                         // bf16 pitch of the [seq][gate*32+unit] tiles
+  constexpr int CP = 36;                          // fp32 pitch of the [seq][unit] tiles
   extern __shared__ __align__(16) uint8_t smem_dyn[];
-  float* P = reinterpret_cast<float*>(smem_dyn);                         // [2][CL][NB][32]
-  float* stage = P + 2 * CL * NB * 32;                                   // [NB][SP]
-  __nv_bfloat16* dg_s = reinterpret_cast<__nv_bfloat16*>(stage + NB * SP);  // [NB][GP]
+  float* P = reinterpret_cast<float*>(smem_dyn);                                     // [2][CL][32 units][NB] partial dh
+  __nv_bfloat16* in_g = reinterpret_cast<__nv_bfloat16*>(P + 2 * CL * 32 * NB);      // [3][NB][GP] saved gates
+  float* in_c = reinterpret_cast<float*>(in_g + 3 * NB * GP);                        // [3][NB][CP] c_{t-1}
+  float* in_d = in_c + 3 * NB * CP;                                                  // [3][NB][CP] dout_t
+  __nv_bfloat16* dg_s = reinterpret_cast<__nv_bfloat16*>(in_d + 3 * NB * CP);        // [2][NB][GP] gate gradients
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t cta = cluster_ctarank();
   const int n_base = (blockIdx.x / CL) * NB;
-  const int g0 = lane >> 4;
   const int u = (lane >> 2) & 3;
   const int unit_l = warp * 4 + u;
   const int unit = cta * 32 + unit_l;
+  const int bsel = (lane & 3) * 2 + (lane >> 4);
+  const int nidx = n_base + bsel;
+  const bool valid = nidx < a.N;
   const int H4 = 4 * H;
 
   // A fragments of W_hh^T restricted to this CTA's 128 gate rows: A[j][r] = W_hh[rg(r)][j],
@@ -234,119 +263,120 @@ __global__ void __launch_bounds__(256, 1) lstm_bwd_kernel(const LstmArgs a) {
     }
   }
   if (tid == 0) {
-    mbar_init(&bar[0], CL);
-    mbar_init(&bar[1], CL);
+    mbar_init(&bar[0], ARRIVALS);
+    mbar_init(&bar[1], ARRIVALS);
     fence_barrier_init();
   }
+  // per-step input prefetch (cp.async, two steps ahead): 128 threads fetch the gates tile, 64 c_{t-1}, 64 dout_t
+  auto prefetch = [&](int sidx) {
+    const int t = a.S - 1 - sidx;
+    if (sidx < a.S) {
+      const int buf = sidx % 3;
+      if (tid < 128) {
+        const int b = tid >> 4, g = (tid >> 2) & 3, ch = tid & 3;
+        if (n_base + b < a.N)
+          cp_async_16(in_g + (buf * NB + b) * GP + g * 32 + ch * 8,
+                      a.gates + ((long long)(n_base + b) * a.S + t) * H4 + g * H + cta * 32 + ch * 8);
+      } else if (tid < 192) {
+        const int b = (tid - 128) >> 3, ch = tid & 7;
+        if (n_base + b < a.N) {
+          const float* src = t > 0 ? a.c_all + ((long long)(n_base + b) * a.S + t - 1) * H
+                                   : (a.c0 != nullptr ? a.c0 + (long long)(n_base + b) * H : nullptr);
+          float* dst = in_c + (buf * NB + b) * CP + ch * 4;
+          if (src != nullptr) cp_async_16(dst, src + cta * 32 + ch * 4);
+          else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      } else {
+        const int b = (tid - 192) >> 3, ch = tid & 7;
+        if (n_base + b < a.N)
+          cp_async_16(in_d + (buf * NB + b) * CP + ch * 4, a.dout + ((long long)(n_base + b) * a.S + t) * H + cta * 32 + ch * 4);
+      }
+    }
+    cp_async_commit();
+  };
+  prefetch(0);
+  prefetch(1);
+  cp_async_wait<1>();
   cluster_sync_all();
 
-  int bsel[2], nidx[2];
-  bool valid[2];
-  float dc_state[2] = {0.f, 0.f};
-#pragma unroll
-  for (int nt = 0; nt < 2; ++nt) {
-    bsel[nt] = nt * 8 + (lane & 3) * 2 + g0;
-    nidx[nt] = n_base + bsel[nt];
-    valid[nt] = nidx[nt] < a.N;
-  }
+  float dc_state = 0.f;
+  float ct = valid ? a.c_all[((long long)nidx * a.S + a.S - 1) * H + unit] : 0.f;  // c_{S-1}; later steps reuse c_{t-1}
 
   for (int sidx = 0; sidx < a.S; ++sidx) {
     const int t = a.S - 1 - sidx;
-    const int pp = sidx & 1;
-    // loads that do not depend on the recurrence first
-    float gi[2], gf[2], gg[2], go[2], ct[2], cprev[2], dh[2];
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-      if (valid[nt]) {
-        const long long row = (long long)nidx[nt] * a.S + t;
-        const __nv_bfloat16* gp = a.gates + row * H4 + unit;
-        gi[nt] = __bfloat162float(gp[0]);
-        gf[nt] = __bfloat162float(gp[H]);
-        gg[nt] = __bfloat162float(gp[2 * H]);
-        go[nt] = __bfloat162float(gp[3 * H]);
-        ct[nt] = a.c_all[row * H + unit];
-        cprev[nt] = t > 0 ? a.c_all[(row - 1) * H + unit]
-                          : (a.c0 != nullptr ? a.c0[(long long)nidx[nt] * H + unit] : 0.f);
-        dh[nt] = a.dout[row * H + unit];
-      } else {
-        gi[nt] = gf[nt] = gg[nt] = go[nt] = ct[nt] = cprev[nt] = dh[nt] = 0.f;
-      }
-    }
+    const int pp = sidx & 1, buf = sidx % 3;
+    prefetch(sidx + 2);
+    // everything that does not depend on the recurrence first
+    const __nv_bfloat16* gp = in_g + (buf * NB + bsel) * GP + unit_l;
+    const float gi = __bfloat162float(gp[0]), gf = __bfloat162float(gp[32]), gg = __bfloat162float(gp[64]),
+                go = __bfloat162float(gp[96]);
+    const float cprev = in_c[(buf * NB + bsel) * CP + unit_l];
+    float dh = in_d[(buf * NB + bsel) * CP + unit_l];
+    const float tc = tanh_f(ct);
     if (sidx > 0) {
       mbar_wait_cluster(&bar[pp], ((sidx - 1) >> 1) & 1);
+      const float* pr = P + ((pp * CL) * 32 + unit_l) * NB + bsel;
+      float s = 0.f;
 #pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        float s = 0.f;
-#pragma unroll
-        for (int src = 0; src < CL; ++src) s += P[((pp * CL + src) * NB + bsel[nt]) * 32 + unit_l];
-        dh[nt] += s;
-      }
+      for (int src = 0; src < CL; ++src) s += pr[src * 32 * NB];
+      dh += s;
     }
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-      const float tc = tanh_f(ct[nt]);
-      const float d_o = dh[nt] * tc * go[nt] * (1.f - go[nt]);
-      const float dc = dh[nt] * go[nt] * (1.f - tc * tc) + dc_state[nt];
-      const float d_i = dc * gg[nt] * gi[nt] * (1.f - gi[nt]);
-      const float d_f = dc * cprev[nt] * gf[nt] * (1.f - gf[nt]);
-      const float d_g = dc * gi[nt] * (1.f - gg[nt] * gg[nt]);
-      dc_state[nt] = dc * gf[nt];
-      const __nv_bfloat16 bi = __float2bfloat16(d_i), bf = __float2bfloat16(d_f), bg = __float2bfloat16(d_g),
-                          bo = __float2bfloat16(d_o);
-      __nv_bfloat16* ds = dg_s + bsel[nt] * GP + unit_l;
-      ds[0] = bi; ds[32] = bf; ds[64] = bg; ds[96] = bo;
-      if (valid[nt]) {
-        __nv_bfloat16* gp = a.dgates + ((long long)nidx[nt] * a.S + t) * H4 + unit;
-        gp[0] = bi; gp[H] = bf; gp[2 * H] = bg; gp[3 * H] = bo;
-      }
+    float d_i = 0.f, d_f = 0.f, d_g = 0.f, d_o = 0.f;
+    if (valid) {
+      d_o = dh * tc * go * (1.f - go);
+      const float dc = dh * go * (1.f - tc * tc) + dc_state;
+      d_i = dc * gg * gi * (1.f - gi);
+      d_f = dc * cprev * gf * (1.f - gf);
+      d_g = dc * gi * (1.f - gg * gg);
+      dc_state = dc * gf;
     }
+    ct = cprev;
+    __nv_bfloat16* ds = dg_s + (pp * NB + bsel) * GP + unit_l;
+    ds[0] = __float2bfloat16(d_i);
+    ds[32] = __float2bfloat16(d_f);
+    ds[64] = __float2bfloat16(d_g);
+    ds[96] = __float2bfloat16(d_o);
+    cp_async_wait<1>();
     __syncthreads();
-    if (t > 0) {
-      // partial dh[b][j] = sum_{r in my 128 gate rows} dgate[b][r] * W_hh[rg(r)][j]
-      if (warp < ACTIVE) {
-        float acc[MTW][2][4];
+    if (t > 0 && warp < ACTIVE) {
+      // partial dh_{t-1}[j][b] = sum_{r in my 128 gate rows} W_hh[rg(r)][j] * dgate[b][r]
+      float acc[MTW][4];
 #pragma unroll
-        for (int mt = 0; mt < MTW; ++mt)
+      for (int mt = 0; mt < MTW; ++mt)
 #pragma unroll
-          for (int nt = 0; nt < 2; ++nt)
+        for (int e = 0; e < 4; ++e) acc[mt][e] = 0.f;
+      const uint32_t brow = smem_u32(dg_s + (pp * NB + (lane & 7)) * GP + (lane >> 3) * 8);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) acc[mt][nt][e] = 0.f;
-#pragma unroll
-        for (int kt = 0; kt < 8; ++kt) {
-          const int r = kt * 16 + (lane & 3) * 2;
-#pragma unroll
-          for (int nt = 0; nt < 2; ++nt) {
-            const __nv_bfloat16* bp = dg_s + (nt * 8 + (lane >> 2)) * GP + r;
-            const uint32_t b0 = *reinterpret_cast<const uint32_t*>(bp);
-            const uint32_t b1 = *reinterpret_cast<const uint32_t*>(bp + 8);
-#pragma unroll
-            for (int mt = 0; mt < MTW; ++mt) mma_bf16_16816(acc[mt][nt], afr[mt][kt], b0, b1);
-          }
-        }
+      for (int kt2 = 0; kt2 < 4; ++kt2) {
+        uint32_t bb[4];
+        ldsm_x4(bb, brow + kt2 * 64);
 #pragma unroll
         for (int mt = 0; mt < MTW; ++mt) {
-          const int j0 = (warp * MTW + mt) * 16 + (lane >> 2);
-#pragma unroll
-          for (int nt = 0; nt < 2; ++nt) {
-            const int bb = nt * 8 + (lane & 3) * 2;
-            stage[bb * SP + j0] = acc[mt][nt][0];
-            stage[(bb + 1) * SP + j0] = acc[mt][nt][1];
-            stage[bb * SP + j0 + 8] = acc[mt][nt][2];
-            stage[(bb + 1) * SP + j0 + 8] = acc[mt][nt][3];
-          }
+          mma_bf16_16816(acc[mt], afr[mt][2 * kt2], bb[0], bb[1]);
+          mma_bf16_16816(acc[mt], afr[mt][2 * kt2 + 1], bb[2], bb[3]);
         }
       }
-      __syncthreads();
-      // reduce-scatter: block [16 x 32] of units owned by CTA d goes to P[pp^1][src = me] of CTA d
-      for (int c = tid; c < CL * 128; c += 256) {
-        const int d = c >> 7, b = (c & 127) >> 3, part = c & 7;
-        const float4 v = *reinterpret_cast<const float4*>(stage + b * SP + d * 32 + part * 4);
-        const uint32_t dst = smem_u32(P + (((pp ^ 1) * CL + cta) * NB + b) * 32 + part * 4);
-        st_cluster_v4(mapa(dst, d), __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z),
-                      __float_as_uint(v.w));
+      // accumulator (row j = m-tile*16 + lane/4 (+8), columns = sequences 2*(lane%4), +1) -> owner CTA of unit j
+#pragma unroll
+      for (int mt = 0; mt < MTW; ++mt) {
+        const int m = warp * MTW + mt;          // m-tile index: units [16m, 16m+16)
+        const int d = m >> 1;                   // owner CTA
+        const int jl = (m & 1) * 16 + (lane >> 2);
+        const uint32_t dst = smem_u32(P + (((pp ^ 1) * CL + cta) * 32 + jl) * NB + (lane & 3) * 2);
+        st_cluster_v2_f32(mapa(dst, d), acc[mt][0], acc[mt][1]);
+        st_cluster_v2_f32(mapa(dst + 8 * NB * 4, d), acc[mt][2], acc[mt][3]);
+        if (MTW == 1 || (mt & 1) == 1) {  // last m-tile this warp sends to destination d
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(mapa(smem_u32(&bar[pp ^ 1]), d));
+        }
       }
-      __syncthreads();
-      if (tid < CL) mbar_arrive_remote(mapa(smem_u32(&bar[pp ^ 1]), tid));
+    }
+    // coalesced write of this step's gate gradients (operand of the dW / dx GEMMs)
+    if (tid < 128) {
+      const int b = tid >> 4, g = (tid >> 2) & 3, ch = tid & 3;
+      if (n_base + b < a.N)
+        *reinterpret_cast<uint4*>(a.dgates + ((long long)(n_base + b) * a.S + t) * H4 + g * H + cta * 32 + ch * 8) =
+            *reinterpret_cast<const uint4*>(dg_s + (pp * NB + b) * GP + g * 32 + ch * 8);
     }
   }
   cluster_sync_all();
@@ -358,7 +388,7 @@ static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
   const int clusters = (a.N + NB - 1) / NB;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(CL * clusters);
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(LSTM_THREADS);
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -375,7 +405,7 @@ static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
     e = cudaLaunchKernelEx(&cfg, kern, a);
   } else {
     auto kern = lstm_bwd_kernel<H>;
-    const size_t smem = (size_t)(2 * CL * NB * 32 + NB * (H + 4)) * sizeof(float) + (size_t)NB * (128 + 8) * 2;
+    const size_t smem = (size_t)2 * CL * 32 * NB * 4 + (size_t)3 * NB * 136 * 2 + (size_t)2 * 3 * NB * 36 * 4 + (size_t)2 * NB * 136 * 2;
     if (CL > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cfg.dynamicSmemBytes = smem;
