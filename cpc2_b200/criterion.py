@@ -119,6 +119,7 @@ class _HeadsFn(torch.autograd.Function):
         eng = ctx.eng
         B, W, H = ctx.shape
         dx, gflat = eng.backward(ctx.saved, dout.contiguous().float().view(eng.G, B * W, eng.dout))
+        ops.grad_ready("criterion", gflat)
         return (dx.view(B, W, H), None, None, *eng.arena.grad_views(gflat))
 
 
@@ -276,4 +277,5 @@ class _CriterionFn(torch.autograd.Function):
         dcw, gflat = eng.backward(ctx.saved, dpred)
         dc = torch.zeros(B, S, H, device=dev)
         dc[:, :W] = dcw.view(B, W, H)
+        ops.grad_ready("criterion", gflat)
         return (dc, dz.view(B, S, D), None, None, None, None, None, None, *eng.arena.grad_views(gflat))

@@ -222,6 +222,7 @@ class _EncoderFn(torch.autograd.Function):
         K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
                     pad_next[0])
         grads[0:4] = [dw0.view(C, 1, 10), db0, dg0.view(1, C, 1), dbe0.view(1, C, 1)]
+        ops.grad_ready("encoder", gflat)
         return (None, *grads)
 
 
@@ -351,6 +352,7 @@ class _LstmFn(torch.autograd.Function):
             dx = torch.empty(N * S, Kin, device=dev)
             K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
             d = dx.view(N, S, Kin)
+        ops.grad_ready("ar", gflat)
         return (d, None, None, None, *grads)
 
 

@@ -14,6 +14,18 @@ NUM_SMS = 148
 GRAD_F32 = False
 
 
+# Callbacks invoked by the modules' backward right after every kernel writing a module's flat fp32 gradient
+# arena has been enqueued: fn(stage, gflat) with stage in {"criterion", "ar", "encoder"}.  The data-parallel
+# wrapper (dp.BucketedAllReduce) hooks its in-place all-reduce here, BEFORE autograd hands the views to
+# AccumulateGrad, so .grad aliases the reduced arena (no copies, CUDA-graph capturable).
+GRAD_READY = []
+
+
+def grad_ready(stage, gflat):
+    for fn in GRAD_READY:
+        fn(stage, gflat)
+
+
 def require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
