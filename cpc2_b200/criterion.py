@@ -59,6 +59,10 @@ class PredictionNetwork(nn.Module):
             object.__setattr__(self, "_engine", eng)
         return self._engine
 
+    def prefetch(self):
+        """bf16 shadow of all heads' weights (16.6 M at the default config) on a side stream, early in the step."""
+        self.engine().arena.prefetch(5)
+
     def forward(self, c, candidates):
         """Reference signature (criterion.py:152-173): list of [B, n_cand, W, D] candidates -> list of
         [B, n_cand, W] scores.  Used by getCosineDistances; the training path goes through the fused
@@ -262,20 +266,23 @@ class _CriterionFn(torch.autograd.Function):
         # coherent across rows); each backward GEMM runs once per part, the second pass accumulating.
         dlog = torch.empty(2, Kp, T, BS, device=dev, dtype=BF16)
         K.nce_bwd(logits, ext, weights, lse, gscale, dlog[0], Kp, B, W, S, NEG, BS, dlogits_lo=dlog[1])
-        # dpred_k = dlog_k . z / D
+        # dpred_k = dlog_k . z / D  (main stream: the heads' backward waits for it)
         dpred = torch.empty(Kp, T, D, device=dev)
+        dz = torch.zeros(BS, D, device=dev)
+        dc = torch.zeros(B, S, H, device=dev)
+        # dz = sum_k dlog_k^T . pred_k / D   (reduction over (k, token)); nothing downstream of the criterion
+        # needs it before the encoder backward, so it runs on a side stream next to the heads' backward
+        with ops.side(2):
+            Bv = K.View(preds, D, T, Kp, D, T * D, major=1, gmul=0)
+            for part in range(2):
+                A = K.View(dlog[part], BS, T, Kp, BS, T * BS, major=1, gmul=0)
+                K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
+                       accumulate=True, alpha=1.0 / D)
         for part in range(2):
             K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
                    accumulate=part > 0)
-        # dz = sum_k dlog_k^T . pred_k / D   (reduction over (k, token))
-        dz = torch.zeros(BS, D, device=dev)
-        Bv = K.View(preds, D, T, Kp, D, T * D, major=1, gmul=0)
-        for part in range(2):
-            A = K.View(dlog[part], BS, T, Kp, BS, T * BS, major=1, gmul=0)
-            K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
-                   accumulate=True, alpha=1.0 / D)
         dcw, gflat = eng.backward(ctx.saved, dpred)
-        dc = torch.zeros(B, S, H, device=dev)
         dc[:, :W] = dcw.view(B, W, H)
+        ops.join()
         ops.grad_ready("criterion", gflat)
         return (dc, dz.view(B, S, D), None, None, None, None, None, None, *eng.arena.grad_views(gflat))

@@ -106,15 +106,43 @@ class CPCEncoder(nn.Module):
             ps += [conv.weight, conv.bias, norm.weight, norm.bias]
         return ps
 
+    def _conv_weights(self):
+        return [getattr(self, f"conv{i}").weight for i in range(1, 5)]
+
+    def prefetch(self):
+        """Pack conv1..4 weights into their GEMM operand layouts on a side stream (train.prefetchWeights calls
+        this at the top of the step, so the packing overlaps conv0 instead of preceding every conv)."""
+        ws = self._conv_weights()
+        bufs = _alloc_packed(ws[0].shape[0], ws[0].device)
+        with ops.side(3):
+            _pack_conv_weights([w.detach() for w in ws], bufs)
+        self._pref = ops.Prefetched(ws, bufs, 3)
+
     def forward(self, x):
         """x [N, 1, W] fp32 (W multiple of 160) -> [N, C, W/160] fp32 (a view of channels-last memory)."""
         ops.require_cuda(x)
-        return _EncoderFn.apply(x, *self._params())
+        pref, self._pref = getattr(self, "_pref", None), None
+        return _EncoderFn.apply(x, pref, *self._params())
+
+
+def _alloc_packed(C, dev):
+    out = [None]
+    for l in range(1, 5):
+        k, s, _ = GEOMETRY[l]
+        out.append((torch.empty(C, k * C, device=dev, dtype=BF16), torch.empty(s * C, 2 * C, device=dev, dtype=BF16)))
+    return out
+
+
+def _pack_conv_weights(ws, bufs):
+    C = ws[0].shape[0]
+    for l in range(1, 5):
+        k, s, _ = GEOMETRY[l]
+        K.conv_weight_pack(ws[l - 1], bufs[l][0], bufs[l][1], C, C, k, s)
 
 
 class _EncoderFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, *params):
+    def forward(ctx, x, pref, *params):
         N, one, W = x.shape
         if one != 1 or W % 160 != 0:
             raise ValueError("CPCEncoder expects [N, 1, W] with W a multiple of 160")
@@ -124,11 +152,14 @@ class _EncoderFn(torch.autograd.Function):
         p = [t.detach() for t in params]
         L = [W // 5, W // 20, W // 40, W // 80, W // 160]
         pad_next = [GEOMETRY[i + 1][2] for i in range(4)] + [0]
-        acts, ys, means, rstds, packed = [], [None], [], [], [None]
+        acts, ys, means, rstds = [], [None], [], []
+        packed = None  # conv1..4 weights in GEMM layout: prefetched on a side stream, or packed there now
+        if pref is None:
+            packed = _alloc_packed(C, dev)
+            with ops.side(3):
+                _pack_conv_weights([p[4 * l] for l in range(1, 5)], packed)
         # layer 0: fused conv + ChannelNorm + ReLU straight from the waveform
-        a = torch.empty(N, L[0] + 2 * pad_next[0], C, device=dev, dtype=BF16)
-        a[:, :pad_next[0]].zero_()
-        a[:, pad_next[0] + L[0]:].zero_()
+        a = torch.empty(N, L[0] + 2 * pad_next[0], C, device=dev, dtype=BF16)  # halo rows are zeroed by the kernel
         mean = torch.empty(N * L[0], device=dev)
         rstd = torch.empty(N * L[0], device=dev)
         K.conv0_fwd(x2, p[0], p[1], p[2], p[3], a, mean, rstd, N, W, C, pad_next[0])
@@ -136,13 +167,17 @@ class _EncoderFn(torch.autograd.Function):
         means.append(mean)
         rstds.append(rstd)
         z32 = None
+        if pref is not None:
+            packed = pref.take([params[4 * l] for l in range(1, 5)])
+            if packed is None:  # parameters changed since the prefetch: pack again, inline
+                packed = _alloc_packed(C, dev)
+                _pack_conv_weights([p[4 * l] for l in range(1, 5)], packed)
+        else:
+            ops.join(3)
         for l in range(1, 5):
             k, s, pd = GEOMETRY[l]
             w, b, g, be = p[4 * l:4 * l + 4]
-            wf = torch.empty(C, k * C, device=dev, dtype=BF16)
-            wd = torch.empty(s * C, 2 * C, device=dev, dtype=BF16)
-            K.conv_weight_pack(w, wf, wd, C, C, k, s)
-            packed.append((wf, wd))
+            wf, wd = packed[l]
             Lin, Lout = L[l - 1], L[l]
             Lp = Lin + 2 * pd
             y = torch.empty(N * Lout, C, device=dev, dtype=BF16)
@@ -188,6 +223,7 @@ class _EncoderFn(torch.autograd.Function):
             off += n_
         d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
         dout, dout_map = d, None
+        keep = []  # buffers a side stream still reads: alive until the join
         for l in range(4, 0, -1):
             k, s, pd = GEOMETRY[l]
             w, b, g, be = p[4 * l:4 * l + 4]
@@ -201,13 +237,16 @@ class _EncoderFn(torch.autograd.Function):
             K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
                           dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,
                           dx_map=K.rowmap(Lout, Lout + 2, 1), unbiased=True, relu=True)
-            # wgrad: dWf[co, kk*C+ci] = sum_{n,t} dy[n,t,co] * a_pad[n, t*s+kk, ci]
+            # wgrad: dWf[co, kk*C+ci] = sum_{n,t} dy[n,t,co] * a_pad[n, t*s+kk, ci]   (side stream: only the
+            # optimizer needs it; the input-gradient chain continues on the main stream)
             dwf = torch.zeros(C, k * C, device=dev)
-            A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
-            B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
-            K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout, k_splits=ops.auto_splits(C, k * C, N * Lout, 1, Lout),
-                   out_f32=dwf, accumulate=True)
-            K.conv_wgrad_unpack(dwf, dw, C, C, k)
+            with ops.side(0):
+                A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
+                B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
+                K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout,
+                       k_splits=ops.auto_splits(C, k * C, N * Lout, 1, Lout), out_f32=dwf, accumulate=True)
+                K.conv_wgrad_unpack(dwf, dw, C, C, k)
+            keep.append(dwf)
             grads[4 * l:4 * l + 4] = [dw.view(C, C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
             # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
             A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
@@ -217,13 +256,16 @@ class _EncoderFn(torch.autograd.Function):
             else:  # layer 0 consumes its (largest) gradient in bf16
                 dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
+            keep += [dy, dout]
             dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
         dw0, db0, dg0, dbe0 = gv[0:4]
         K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
                     pad_next[0])
         grads[0:4] = [dw0.view(C, 1, 10), db0, dg0.view(1, C, 1), dbe0.view(1, C, 1)]
+        ops.join()
+        del keep
         ops.grad_ready("encoder", gflat)
-        return (None, *grads)
+        return (None, None, *grads)
 
 
 class CPCAR(nn.Module):
@@ -247,6 +289,21 @@ class CPCAR(nn.Module):
     def getDimOutput(self):
         return self.baseNet.hidden_size
 
+    def _rnn_params(self):
+        params = []
+        for l in range(self.baseNet.num_layers):
+            params += [getattr(self.baseNet, f"{n}_l{l}") for n in ("weight_ih", "weight_hh", "bias_ih", "bias_hh")]
+        return params
+
+    def prefetch(self):
+        """bf16 shadows of the recurrent weights and the summed bias, issued on a side stream at the top of the
+        step (train.prefetchWeights) so they overlap the encoder."""
+        params = self._rnn_params()
+        bufs = _alloc_rnn_shadows(params)
+        with ops.side(4):
+            _cast_rnn_weights([q.detach() for q in params], bufs)
+        self._pref = ops.Prefetched(params, bufs, 4)
+
     def forward(self, x):
         ops.require_cuda(x)
         if not isinstance(self.baseNet, nn.LSTM):
@@ -254,13 +311,12 @@ class CPCAR(nn.Module):
         if self.reverse:
             x = torch.flip(x, [1])
         nl = self.baseNet.num_layers
-        params = []
-        for l in range(nl):
-            params += [getattr(self.baseNet, f"{n}_l{l}") for n in ("weight_ih", "weight_hh", "bias_ih", "bias_hh")]
+        params = self._rnn_params()
         h0 = c0 = None
         if self.hidden is not None:
             h0, c0 = self.hidden
-        out, h_n, c_n = _LstmFn.apply(x, h0, c0, nl, *params)
+        pref, self._pref = getattr(self, "_pref", None), None
+        out, h_n, c_n = _LstmFn.apply(x, h0, c0, nl, pref, *params)
         if self.keepHidden:
             self.hidden = (h_n.detach(), c_n.detach())
         if self.reverse:
@@ -268,15 +324,37 @@ class CPCAR(nn.Module):
         return out
 
 
+def _alloc_rnn_shadows(params):
+    """Per layer: (w_ih bf16, w_hh bf16, b_ih + b_hh fp32), allocated on the current stream."""
+    out = []
+    for l in range(len(params) // 4):
+        w_ih, w_hh, b_ih, _ = params[4 * l:4 * l + 4]
+        out.append((torch.empty(w_ih.shape, device=w_ih.device, dtype=BF16),
+                    torch.empty(w_hh.shape, device=w_hh.device, dtype=BF16), torch.empty_like(b_ih)))
+    return out
+
+
+def _cast_rnn_weights(p, bufs):
+    for l, (w_ih16, w_hh16, bias) in enumerate(bufs):
+        w_ih, w_hh, b_ih, b_hh = p[4 * l:4 * l + 4]
+        K.cast_bf16(w_ih.contiguous(), w_ih16)
+        K.cast_bf16(w_hh.contiguous(), w_hh16)
+        torch.add(b_ih, b_hh, out=bias)
+
+
 class _LstmFn(torch.autograd.Function):
     """x [N,S,C] fp32 -> out [N,S,H] fp32 (+ final h, c [layers,N,H])."""
 
     @staticmethod
-    def forward(ctx, x, h0, c0, nl, *params):
+    def forward(ctx, x, h0, c0, nl, pref, *params):
         N, S, Cin = x.shape
         dev = x.device
         p = [t.detach() for t in params]
         H = p[1].shape[1]
+        shadows = pref.take(list(params)) if pref is not None else None
+        if shadows is None:
+            shadows = _alloc_rnn_shadows(p)
+            _cast_rnn_weights(p, shadows)
         inp = K.cast_bf16(x.detach().contiguous().float()).view(N * S, Cin)
         saved = []
         h_ns, c_ns = [], []
@@ -285,8 +363,7 @@ class _LstmFn(torch.autograd.Function):
         for l in range(nl):
             w_ih, w_hh, b_ih, b_hh = p[4 * l:4 * l + 4]
             Kin = w_ih.shape[1]
-            w_ih16, w_hh16 = K.cast_bf16(w_ih.contiguous()), K.cast_bf16(w_hh.contiguous())
-            bias = (b_ih + b_hh).contiguous()
+            w_ih16, w_hh16, bias = shadows[l]
             gx = torch.empty(N * S, 4 * H, device=dev)
             if l == 0:
                 K.gemm(K.kmajor(inp), K.kmajor(w_ih16), N * S, 4 * H, Kin, out_f32=gx, bias=bias)
@@ -325,6 +402,7 @@ class _LstmFn(torch.autograd.Function):
         for n_ in sizes:
             gv.append(gflat[off:off + n_])
             off += n_
+        keep = []
         for l in range(nl - 1, -1, -1):
             x_in, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l = ctx.saved[l]
             dgates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
@@ -332,28 +410,33 @@ class _LstmFn(torch.autograd.Function):
             dg2 = dgates.view(N * S, 4 * H)
             dw_ih, dw_hh = gv[4 * l].view(4 * H, Kin), gv[4 * l + 1].view(4 * H, H)
             dbias, dbias2 = gv[4 * l + 2], gv[4 * l + 3]
-            K.colsum(dg2, dbias, N * S, 4 * H, 4 * H)
-            dbias2.copy_(dbias)
-            # dW_hh = sum_{n,t} dgates[n,t]^T h_{t-1}[n]  (slabs = sequences, h_pad row t is h_{t-1})
-            Ag = K.View(dgates, 4 * H, S, N, 4 * H, S * 4 * H, major=1)
-            Bh = K.View(h_pad, H, S + 1, N, H, (S + 1) * H, major=1)
-            K.gemm(Ag, Bh, 4 * H, H, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, H, N * S, 1, S),
-                   out_f32=dw_hh, accumulate=True)
-            # dW_ih = dgates^T . input
-            if l == 0:
-                K.gemm(K.mnmajor(dg2), K.mnmajor(x_in), 4 * H, Kin, N * S,
-                       k_splits=ops.auto_splits(4 * H, Kin, N * S), out_f32=dw_ih, accumulate=True)
-            else:
-                Bx = K.View(x_in, H, S + 1, N, H, (S + 1) * H, major=1, row_off=1)
-                K.gemm(Ag, Bx, 4 * H, Kin, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, Kin, N * S, 1, S),
-                       out_f32=dw_ih, accumulate=True)
+            dx = torch.empty(N * S, Kin, device=dev)
+            with ops.side(1):
+                K.colsum(dg2, dbias, N * S, 4 * H, 4 * H)
+                dbias2.copy_(dbias)
+            with ops.side(0):
+                # dW_hh = sum_{n,t} dgates[n,t]^T h_{t-1}[n]  (slabs = sequences, h_pad row t is h_{t-1})
+                Ag = K.View(dgates, 4 * H, S, N, 4 * H, S * 4 * H, major=1)
+                Bh = K.View(h_pad, H, S + 1, N, H, (S + 1) * H, major=1)
+                K.gemm(Ag, Bh, 4 * H, H, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, H, N * S, 1, S),
+                       out_f32=dw_hh, accumulate=True)
+                # dW_ih = dgates^T . input
+                if l == 0:
+                    K.gemm(K.mnmajor(dg2), K.mnmajor(x_in), 4 * H, Kin, N * S,
+                           k_splits=ops.auto_splits(4 * H, Kin, N * S), out_f32=dw_ih, accumulate=True)
+                else:
+                    Bx = K.View(x_in, H, S + 1, N, H, (S + 1) * H, major=1, row_off=1)
+                    K.gemm(Ag, Bx, 4 * H, Kin, N * S, k_per_slab=S,
+                           k_splits=ops.auto_splits(4 * H, Kin, N * S, 1, S), out_f32=dw_ih, accumulate=True)
+            keep.append(dgates)
             grads[4 * l:4 * l + 4] = [dw_ih, dw_hh, dbias, dbias2]
             # dx = dgates . W_ih
-            dx = torch.empty(N * S, Kin, device=dev)
             K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
             d = dx.view(N, S, Kin)
+        ops.join()
+        del keep
         ops.grad_ready("ar", gflat)
-        return (d, None, None, None, *grads)
+        return (d, None, None, None, None, *grads)
 
 
 class CPCModel(nn.Module):

@@ -26,6 +26,72 @@ def grad_ready(stage, gflat):
         fn(stage, gflat)
 
 
+# ---- independent kernels on forked streams -----------------------------------------------------------
+# Most launches of the step are 10-40 us and fill a fraction of the 148 SMs; weight-gradient GEMMs, bias
+# column sums and weight casts do not sit on the critical path, so they are issued on side streams that fork
+# from / join back into the current stream.  Inside a CUDA-graph capture this becomes parallel graph branches.
+# Rule: every tensor a side stream touches is allocated on the main stream BEFORE the fork and kept alive past
+# the join (the launchers only borrow pointers), so the caching allocator never sees cross-stream reuse.
+CONCURRENT = True
+_SIDE = {}
+_PENDING = []
+
+
+class side:
+    """`with ops.side(i):` launches the body on side stream i (ordered after everything already queued on the
+    current stream).  `ops.join()` makes the current stream wait for every side stream used since;
+    `ops.join(i)` for stream i only."""
+
+    def __init__(self, index):
+        self.index = index
+        self.ctx = None
+
+    def __enter__(self):
+        if not CONCURRENT or K.PROFILE is not None:
+            return self
+        cur = torch.cuda.current_stream()
+        key = (cur.device.index, self.index)
+        s = _SIDE.get(key)
+        if s is None:
+            s = _SIDE[key] = torch.cuda.Stream(device=cur.device)
+        if all(k != key for k, _, _ in _PENDING):
+            _PENDING.append((key, s, cur))
+        s.wait_stream(cur)
+        self.ctx = torch.cuda.stream(s)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+            self.ctx = None
+        return False
+
+
+def join(index=None):
+    for item in list(_PENDING):
+        key, s, cur = item
+        if index is None or key[1] == index:
+            torch.cuda.current_stream().wait_stream(s)
+            _PENDING.remove(item)
+
+
+class Prefetched:
+    """Result of work issued early on a side stream (bf16 weight shadows, packed conv weights), valid only while
+    the parameters it was computed from are unchanged (checked through their autograd version counters)."""
+
+    def __init__(self, params, value, stream_index):
+        self.versions = [p._version for p in params]
+        self.ptrs = [p.data_ptr() for p in params]
+        self.value, self.stream_index = value, stream_index
+
+    def take(self, params):
+        join(self.stream_index)
+        if [p._version for p in params] == self.versions and [p.data_ptr() for p in params] == self.ptrs:
+            return self.value
+        return None
+
+
 def require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
@@ -83,7 +149,20 @@ class Arena:
         self.flat = flat
         return flat
 
+    def prefetch(self, stream_index):
+        """Issue the bf16 shadow cast on a side stream now; the next bf16() call picks it up."""
+        flat = self.ensure()
+        out = torch.empty(flat.shape, dtype=BF16, device=flat.device)
+        with side(stream_index):
+            K.cast_bf16(flat, out)
+        self._pref = Prefetched(self.params, out, stream_index)
+
     def bf16(self):
+        pref, self._pref = getattr(self, "_pref", None), None
+        if pref is not None:
+            out = pref.take(self.params)
+            if out is not None:
+                return out
         return K.cast_bf16(self.ensure())
 
     def view(self, flat, index, shape=None):

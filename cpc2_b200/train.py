@@ -74,8 +74,23 @@ def buildModelAndCriterion(args):
     return cpcModel, cpcCriterion
 
 
+def prefetchWeights(cpcModel, cpcCriterion):
+    """Issue every weight-only preparation of the step (conv weight packing, bf16 shadows of the AR and head
+    weights) on side streams now, so it overlaps the encoder instead of sitting in front of each consumer.
+    Works through DataParallel / DistributedDataParallel wrappers (`.module`)."""
+    m = getattr(cpcModel, "module", cpcModel)
+    c = getattr(cpcCriterion, "module", cpcCriterion)
+    mods = [getattr(m, "gEncoder", None), getattr(c, "wPrediction", None)]
+    ar = getattr(m, "gAR", None)
+    mods += list(ar) if isinstance(ar, torch.nn.Sequential) else [ar]
+    for mod in mods:
+        if mod is not None and hasattr(mod, "prefetch") and next(mod.parameters()).is_cuda:
+            mod.prefetch()
+
+
 def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None, backward=True):
     """The body of the reference's batch loop, cpc/train.py:95-109."""
+    prefetchWeights(cpcModel, cpcCriterion)
     past, future = sequence[:, 0, ...], sequence[:, 1, ...]
     b = past.size(0)
     combined = torch.cat([past, future], dim=0)

@@ -81,6 +81,9 @@ class TransformerLayer(nn.Module):
             object.__setattr__(self, "_stack", TransformerStack([self]))
         return self._stack
 
+    def prefetch(self):
+        self.stack().arena.prefetch(4)
+
     def forward(self, x):
         """x [N, S, dmodel] fp32, S a multiple of sizeSeq -> [N, S, dout] fp32."""
         ops.require_cuda(x)
@@ -219,54 +222,63 @@ class TransformerStack:
         gflat = torch.zeros(self.arena.numel, device=dev)
         Gd = self.spans(gflat)
         x, shared = sv["x"], sv["shared"]
-        # out = LN2(pre2)
+        # Buffers first (main stream), then the chain of input gradients on the main stream while the weight
+        # gradients and bias column sums run on side streams (ops.side): they are off the critical path.
         dpre2 = torch.empty(G, T, do, device=dev, dtype=BF16)
+        du = torch.empty(G, T, d, device=dev, dtype=BF16)
+        dh1 = torch.empty(G, T, dff, device=dev, dtype=BF16)
+        dy = torch.empty(G, T, d, device=dev, dtype=torch.float32 if ops.GRAD_F32 else BF16)
+        dpre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
+        datt = torch.empty(G, T, d, device=dev, dtype=BF16)
+        dqkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
+        dscore = torch.empty_like(sv["probs"])
+        dx = torch.empty(T, d, device=dev) if shared else torch.empty(G, T, d, device=dev)
+        # out = LN2(pre2)
         K.rownorm_bwd(dout.reshape(G * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], G * T, do, P32["ln2w"], P32["ln2b"],
                       dx_bf16=dpre2, dgamma=Gd["ln2w"], dbeta=Gd["ln2b"], rows_per_group=T)
         # pre2 = u . Wl^T + bl
-        K.colsum(dpre2, Gd["bl"], T, do, do, T * do, G)
-        ops.linear_dw(dpre2, sv["u"], Gd["Wl"], T, do, d, groups=G)
-        du = torch.empty(G, T, d, device=dev, dtype=BF16)
+        with ops.side(0):
+            ops.linear_dw(dpre2, sv["u"], Gd["Wl"], T, do, d, groups=G)
+        with ops.side(1):
+            K.colsum(dpre2, Gd["bl"], T, do, do, T * do, G)
         ops.linear_dx(dpre2, P16["Wl"], T, do, d, groups=G, out_bf16=du)
         # u = y + h1 . W2^T + b2
-        K.colsum(du, Gd["b2"], T, d, d, T * d, G)
-        ops.linear_dw(du, sv["h1"], Gd["W2"], T, d, dff, groups=G)
-        dh1 = torch.empty(G, T, dff, device=dev, dtype=BF16)
+        with ops.side(0):
+            ops.linear_dw(du, sv["h1"], Gd["W2"], T, d, dff, groups=G)
+        with ops.side(1):
+            K.colsum(du, Gd["b2"], T, d, d, T * d, G)
         ops.linear_dx(du, P16["W2"], T, d, dff, groups=G, out_bf16=dh1, gate=sv["h1"],
                       gate_scale=1.0 / (1.0 - sv["drop"]))
         # h1 = dropout(relu(y . W1^T + b1))
-        K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
-        ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
+        with ops.side(0):
+            ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
+        with ops.side(1):
+            K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
         if ops.GRAD_F32:
-            dy = torch.empty(G, T, d, device=dev)
             ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_f32=dy, res=du)
         else:
-            dy = torch.empty(G, T, d, device=dev, dtype=BF16)
             ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
         # y = LN1(pre1)
-        dpre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         K.rownorm_bwd(dy.view(G * T, d), sv["pre1"], sv["mean1"], sv["rstd1"], G * T, d, P32["ln1w"], P32["ln1b"],
                       dx_bf16=dpre1, dgamma=Gd["ln1w"], dbeta=Gd["ln1b"], rows_per_group=T)
         # pre1 = x + att . Wo^T
-        ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=G)
-        datt = torch.empty(G, T, d, device=dev, dtype=BF16)
+        with ops.side(0):
+            ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=G)
         ops.linear_dx(dpre1, P16["Wo"], T, d, d, groups=G, out_bf16=datt)
-        dqkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
-        dscore = torch.empty_like(sv["probs"])
         K.attn_bwd(sv["qkv"], P32.get("krel"), sv["att"], sv["probs"], datt, dqkv, dscore, Gd.get("krel"), G, Bt,
                    self.Hh, S, self.dk, rng=sv["rng"], site=1, drop_p=sv["drop"])
         # qkv = x . Wqkv^T
-        ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared)
+        with ops.side(0):
+            ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared)
         if shared:
             # dx = sum_g (dqkv_g . Wqkv_g + dpre1_g): one GEMM whose reduction runs over (group, 3d), then a group sum
-            dx = torch.empty(T, d, device=dev)
             A = K.View(dqkv, 3 * d, T, G, 3 * d, T * 3 * d, major=0, gmul=0)
             B = K.View(P16["Wqkv"], d, 3 * d, G, d, 3 * d * d, major=1, gmul=0)
             K.gemm(A, B, T, d, G * 3 * d, k_per_slab=3 * d, out_f32=dx)
             K.groupsum(dpre1, T * d, G, out_f32=dx, accumulate=True)
         else:
-            dx = torch.empty(G, T, d, device=dev)
             ops.linear_dx(dqkv, P16["Wqkv"], T, 3 * d, d, groups=G, out_f32=dx, res=dpre1)
+        ops.join()
         return dx, gflat
 
 

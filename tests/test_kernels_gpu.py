@@ -118,19 +118,20 @@ def test_layernorm_groups_fwd_bwd(K):
 
 
 # ------------------------------------------------------------------------------------------ conv0
-@pytest.mark.parametrize("C", [32, 256])
-def test_conv0_fused_fwd_bwd(K, C):
+@pytest.mark.parametrize("C,W", [(32, 1600), (256, 1600), (64, 1760), (96, 480), (512, 1760), (256, 20480)])
+def test_conv0_fused_fwd_bwd(K, C, W):
     from oracle import cpc_oracle as oc
     torch.manual_seed(4)
-    N, W, halo = 3, 1600, 2
+    N, halo = 3, 2
     L0 = (W - 4) // 5 + 1
     x = 0.1 * torch.randn(N, W, device="cuda")
     conv = torch.nn.Conv1d(1, C, 10, stride=5, padding=3).cuda()
     gamma = (torch.rand(C, device="cuda") + 0.5).requires_grad_(True)
     beta = (torch.randn(C, device="cuda") * 0.1).requires_grad_(True)
-    out = torch.zeros(N, L0 + 2 * halo, C, device="cuda", dtype=BF)
+    out = torch.full((N, L0 + 2 * halo, C), 7.0, device="cuda", dtype=BF)  # the kernel must zero the halo rows itself
     mean, rstd = torch.empty(N * L0, device="cuda"), torch.empty(N * L0, device="cuda")
     K.conv0_fwd(x, conv.weight, conv.bias, gamma, beta, out, mean, rstd, N, W, C, halo)
+    assert float(out[:, :halo].abs().max()) == 0.0 and float(out[:, halo + L0:].abs().max()) == 0.0
     ref = F.relu(oc.channel_norm(conv(x.unsqueeze(1)), gamma.view(1, C, 1), beta.view(1, C, 1)))  # [N,C,L0]
     close(out[:, halo:halo + L0], ref.permute(0, 2, 1), 1e-2, 1e-2, "conv0 fwd")
     dout = bf(torch.randn(N, L0 + 2 * halo, C, device="cuda"))
