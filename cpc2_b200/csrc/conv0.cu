@@ -170,24 +170,24 @@ __device__ __forceinline__ void zero_rows(__nv_bfloat16* base, int rows, int C) 
   for (int i = threadIdx.x; i < rows * C / 8; i += blockDim.x) p[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
-template <int NT>
-__global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_fwd_kernel(const Conv0Args a) {
-  constexpr int CW = 8 * NT;
+template <int NT, int NW>
+__global__ void __launch_bounds__(32 * NW) conv0_cn_relu_fwd_kernel(const Conv0Args a) {
+  constexpr int CW = 8 * NT, C = CW * NW;
   extern __shared__ __align__(128) unsigned char smem[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, q = lane & 3;
   unsigned char* sA = smem;
-  unsigned char* sB = smem + STRIP * 64;                                      // [C][64 B]
-  float2* sStat = reinterpret_cast<float2*>(sB + a.C * 64);                   // [2][NW][16]
-  unsigned char* sStage = sB + a.C * 64 + 2 * NW * 16 * 8 + warp * 16 * CW * 2;
+  unsigned char* sB = smem + STRIP * 64;                                    // [C][64 B]
+  float2* sStat = reinterpret_cast<float2*>(sB + C * 64);                   // [2][NW][16]
+  unsigned char* sStage = sB + C * 64 + 2 * NW * 16 * 8 + warp * 16 * CW * 2;
   const int spw = (a.L0 + STRIP - 1) / STRIP;
   const int n = blockIdx.x / spw, t0 = (blockIdx.x % spw) * STRIP;
   const int Lp = a.L0 + 2 * a.halo;
   build_a_rows(sA, nullptr, STRIP, a.x + (long long)n * a.W, a.W, a.L0, t0);
-  build_b_rows(sB, a.w, a.b, a.C);
+  build_b_rows(sB, a.w, a.b, C);
   if (a.halo > 0) {
-    if (t0 == 0) zero_rows(a.out + (long long)n * Lp * a.C, a.halo, a.C);
-    if (t0 + STRIP >= a.L0) zero_rows(a.out + ((long long)n * Lp + a.halo + a.L0) * a.C, a.halo, a.C);
+    if (t0 == 0) zero_rows(a.out + (long long)n * Lp * C, a.halo, C);
+    if (t0 + STRIP >= a.L0) zero_rows(a.out + ((long long)n * Lp + a.halo + a.L0) * C, a.halo, C);
   }
   const int c0 = warp * CW;
   float2 ga[NT], be[NT];
@@ -198,14 +198,19 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_fwd_kernel(
   }
   __syncthreads();
   const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB), stage_addr = smem_u32(sStage);
-  const float invC = 1.f / (float)a.C, invCm1 = 1.f / (float)(a.C - 1);
+  const float invCm1 = 1.f / (float)(C - 1);
+  constexpr int LPR = CW / 8, RPP = 32 / LPR;  // staged store: lanes per row, rows per pass
+  __nv_bfloat16* out_lane = a.out + ((long long)n * Lp + a.halo + t0 + lane / LPR) * C + c0 + (lane % LPR) * 8;
+  const int m = lane >> 3;
+  const uint32_t stsm_lane = stage_addr + ((lane & 7) + ((m & 1) << 3)) * (CW * 2);
+  const int stsm_row = (lane & 7) + ((m & 1) << 3);
 #pragma unroll 1
   for (int tile = 0; tile < TILES; ++tile) {
     const int tt = t0 + tile * 16;
     if (tt >= a.L0) break;  // uniform over the CTA
     float acc[NT][4];
     conv_tile<NT>(acc, sB_addr, c0, sA_addr, tile, lane);
-    // warp-local (mean, M2) over this warp's CW channels for frames g and g+8
+    // warp-local mean over this warp's CW channels for frames g and g+8; centre on it; M2 of the centred values
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
@@ -216,8 +221,9 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_fwd_kernel(
     float q0 = 0.f, q1 = 0.f;
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
-      q0 += (acc[j][0] - m0) * (acc[j][0] - m0) + (acc[j][1] - m0) * (acc[j][1] - m0);
-      q1 += (acc[j][2] - m1) * (acc[j][2] - m1) + (acc[j][3] - m1) * (acc[j][3] - m1);
+      acc[j][0] -= m0; acc[j][1] -= m0; acc[j][2] -= m1; acc[j][3] -= m1;
+      q0 = fmaf(acc[j][0], acc[j][0], q0); q0 = fmaf(acc[j][1], acc[j][1], q0);
+      q1 = fmaf(acc[j][2], acc[j][2], q1); q1 = fmaf(acc[j][3], acc[j][3], q1);
     }
     q0 = quad_sum(q0);
     q1 = quad_sum(q1);
@@ -227,52 +233,55 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_fwd_kernel(
       st[warp * 16 + g + 8] = make_float2(m1, q1);
     }
     __syncthreads();
+    // Chan's combination of the NW (mean, M2) partials of equal weight CW
+    float2 u0[NW], u1[NW];
     float mean0 = 0.f, mean1 = 0.f;
+#pragma unroll
     for (int w = 0; w < NW; ++w) {
-      mean0 += st[w * 16 + g].x;
-      mean1 += st[w * 16 + g + 8].x;
+      u0[w] = st[w * 16 + g];
+      u1[w] = st[w * 16 + g + 8];
+      mean0 += u0[w].x;
+      mean1 += u1[w].x;
     }
-    mean0 /= (float)NW;
-    mean1 /= (float)NW;
+    mean0 *= 1.f / NW;
+    mean1 *= 1.f / NW;
     float M0 = 0.f, M1 = 0.f;
+#pragma unroll
     for (int w = 0; w < NW; ++w) {
-      const float2 u0 = st[w * 16 + g], u1 = st[w * 16 + g + 8];
-      M0 += u0.y + CW * (u0.x - mean0) * (u0.x - mean0);
-      M1 += u1.y + CW * (u1.x - mean1) * (u1.x - mean1);
+      M0 += fmaf(CW * (u0[w].x - mean0), u0[w].x - mean0, u0[w].y);
+      M1 += fmaf(CW * (u1[w].x - mean1), u1[w].x - mean1, u1[w].y);
     }
-    (void)invC;
     const float r0 = rsqrtf(M0 * invCm1 + a.eps), r1 = rsqrtf(M1 * invCm1 + a.eps);
     if (warp == 0 && q == 0) {
       const long long row = (long long)n * a.L0 + tt;
       if (tt + g < a.L0) { a.mean[row + g] = mean0; a.rstd[row + g] = r0; }
       if (tt + g + 8 < a.L0) { a.mean[row + g + 8] = mean1; a.rstd[row + g + 8] = r1; }
     }
-    // normalise + affine + ReLU, pack to bf16 and stage through shared memory for 16-byte row stores
+    // xhat = (centred + (m_w - mean)) * rstd; y = relu(xhat * gamma + beta); pack to bf16, stage for 16-byte row stores
+    const float k0 = (m0 - mean0) * r0, k1 = (m1 - mean1) * r1;
 #pragma unroll
     for (int j = 0; j < NT; j += 2) {
       uint32_t pk[4];
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj) {
         const float2 gg = ga[j + jj], bb = be[j + jj];
-        const float y00 = fmaxf((acc[j + jj][0] - mean0) * r0 * gg.x + bb.x, 0.f);
-        const float y01 = fmaxf((acc[j + jj][1] - mean0) * r0 * gg.y + bb.y, 0.f);
-        const float y10 = fmaxf((acc[j + jj][2] - mean1) * r1 * gg.x + bb.x, 0.f);
-        const float y11 = fmaxf((acc[j + jj][3] - mean1) * r1 * gg.y + bb.y, 0.f);
+        const float y00 = fmaxf(fmaf(fmaf(acc[j + jj][0], r0, k0), gg.x, bb.x), 0.f);
+        const float y01 = fmaxf(fmaf(fmaf(acc[j + jj][1], r0, k0), gg.y, bb.y), 0.f);
+        const float y10 = fmaxf(fmaf(fmaf(acc[j + jj][2], r1, k1), gg.x, bb.x), 0.f);
+        const float y11 = fmaxf(fmaf(fmaf(acc[j + jj][3], r1, k1), gg.y, bb.y), 0.f);
         pk[2 * jj] = pack_bf16x2(y00, y01);
         pk[2 * jj + 1] = pack_bf16x2(y10, y11);
       }
-      const int m = lane >> 3;
-      stsm_x4(stage_addr + stage_off<CW>((lane & 7) + ((m & 1) << 3), j + (m >> 1)), pk[0], pk[1], pk[2], pk[3]);
+      const int chunk = j + (m >> 1);
+      const uint32_t swz = CW == 64 ? (uint32_t)((chunk ^ (stsm_row & 7)) << 4) : (uint32_t)((chunk ^ ((stsm_row >> 1) & 3)) << 4);
+      stsm_x4(stsm_lane + swz, pk[0], pk[1], pk[2], pk[3]);
     }
     __syncwarp();
-    constexpr int LPR = CW / 8, RPP = 32 / LPR;  // lanes per row, rows per pass
 #pragma unroll
     for (int p = 0; p < 16 / RPP; ++p) {
-      const int row = p * RPP + lane / LPR, chunk = lane % LPR;
-      if (tt + row < a.L0) {
-        const uint4 v = *reinterpret_cast<const uint4*>(sStage + stage_off<CW>(row, chunk));
-        *reinterpret_cast<uint4*>(a.out + ((long long)n * Lp + a.halo + tt + row) * a.C + c0 + chunk * 8) = v;
-      }
+      const int row = p * RPP + lane / LPR;
+      const uint4 v = *reinterpret_cast<const uint4*>(sStage + stage_off<CW>(row, lane % LPR));
+      if (tt + row < a.L0) *reinterpret_cast<uint4*>(out_lane + (long long)(tile * 16 + p * RPP) * C) = v;
     }
     __syncwarp();
   }
@@ -281,22 +290,11 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_fwd_kernel(
 // ------------------------------------------------------------------------------------------------ backward
 constexpr int STRIPB = 32;  // frames per work item of the backward (2 tiles); CTAs loop over items
 
-// D += A . v with v (accumulator layout: frames g / g+8, two channels) rounded to bf16 as hi + lo, so the
-// parameter gradients keep ~16 mantissa bits of every summand
-__device__ __forceinline__ void mma_hilo(float (&D)[4], const uint32_t (&A)[4], const float (&v)[4]) {
-  float h[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) h[i] = bf16_hi(v[i]);
-  mma_bf16_16816(D, A, movmatrix_t(pack_bf16x2(h[0], h[1])), movmatrix_t(pack_bf16x2(h[2], h[3])));
-  mma_bf16_16816(D, A, movmatrix_t(pack_bf16x2(v[0] - h[0], v[1] - h[1])),
-                 movmatrix_t(pack_bf16x2(v[2] - h[2], v[3] - h[3])));
-}
-
-template <int NT>
-__global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(const Conv0Args a) {
+template <int NT, int NW>
+__global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0Args a) {
   constexpr int CW = 8 * NT;
   extern __shared__ __align__(128) unsigned char smem[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, q = lane & 3;
   unsigned char* sA = smem;                                           // [STRIPB][64 B]
   unsigned char* sA1 = smem + STRIPB * 64;                            // [STRIPB][32 B]
@@ -306,13 +304,13 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
   for (int c = threadIdx.x; c < a.C; c += blockDim.x) sGB[c] = make_float2(a.gamma[c], a.beta[c]);
   build_b_rows(sB, a.w, a.b, a.C);
   const int c0 = warp * CW;
-  float D[NT][4];
+  float D[NT][4];       // rows m = g (taps 0..7) and m = g + 8 (taps 8, 9, then db) of [16 x CW]
+  float dgs[NT][2], dbs[NT][2];  // dgamma / dbeta partials of channels 8j + 2q + {0,1} (fp32, CUDA cores)
 #pragma unroll
-  for (int j = 0; j < NT; ++j) D[j][0] = D[j][1] = D[j][2] = D[j][3] = 0.f;
-  // constant A operands that pick "sum over frames" into row 11 (dgamma) and row 12 (dbeta) of D
-  const uint32_t ones = 0x3F803F80u;
-  const uint32_t a2[4] = {0u, g == 3 ? ones : 0u, 0u, g == 3 ? ones : 0u};
-  const uint32_t a3[4] = {0u, g == 4 ? ones : 0u, 0u, g == 4 ? ones : 0u};
+  for (int j = 0; j < NT; ++j) {
+    D[j][0] = D[j][1] = D[j][2] = D[j][3] = 0.f;
+    dgs[j][0] = dgs[j][1] = dbs[j][0] = dbs[j][1] = 0.f;
+  }
   const int ipw = (a.L0 + STRIPB - 1) / STRIPB;
   const int items = a.N * ipw;
   const int Lp = a.L0 + 2 * a.halo;
@@ -331,8 +329,8 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
       if (tt >= a.L0) break;  // uniform over the CTA
       const bool v0 = tt + g < a.L0, v1 = tt + g + 8 < a.L0;
       const long long row = (long long)n * a.L0 + tt;
-      const float mean0 = v0 ? __ldg(a.mean + row + g) : 0.f, rstd0 = v0 ? __ldg(a.rstd + row + g) : 0.f;
-      const float mean1 = v1 ? __ldg(a.mean + row + g + 8) : 0.f, rstd1 = v1 ? __ldg(a.rstd + row + g + 8) : 0.f;
+      const float rstd0 = v0 ? __ldg(a.rstd + row + g) : 0.f, rstd1 = v1 ? __ldg(a.rstd + row + g + 8) : 0.f;
+      const float nm0 = v0 ? -__ldg(a.mean + row + g) * rstd0 : 0.f, nm1 = v1 ? -__ldg(a.mean + row + g + 8) * rstd1 : 0.f;
       const __nv_bfloat16* dr0 = a.dout + ((long long)n * Lp + a.halo + tt + g) * a.C + c0 + 2 * q;
       const __nv_bfloat16* dr1 = dr0 + 8LL * a.C;
       uint32_t dv[NT][2];
@@ -347,27 +345,21 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
 #pragma unroll
       for (int j = 0; j < NT; ++j) {
         const float2 gb0 = sGB[c0 + 8 * j + 2 * q], gb1 = sGB[c0 + 8 * j + 2 * q + 1];
-        const __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&dv[j][0]);
-        const __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&dv[j][1]);
-        float d[4] = {__low2float(h0), __high2float(h0), __low2float(h1), __high2float(h1)};
-        float e[4];
+        float d[4] = {__uint_as_float(dv[j][0] << 16), __uint_as_float(dv[j][0] & 0xffff0000u),
+                      __uint_as_float(dv[j][1] << 16), __uint_as_float(dv[j][1] & 0xffff0000u)};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float mean = i < 2 ? mean0 : mean1, rstd = i < 2 ? rstd0 : rstd1;
           const float2 gb = (i & 1) ? gb1 : gb0;
-          const float xh = (acc[j][i] - mean) * rstd;
-          if (xh * gb.x + gb.y <= 0.f) d[i] = 0.f;
+          const float xh = fmaf(acc[j][i], i < 2 ? rstd0 : rstd1, i < 2 ? nm0 : nm1);
+          if (fmaf(xh, gb.x, gb.y) <= 0.f) d[i] = 0.f;  // ReLU mask (same arithmetic as the forward)
           acc[j][i] = xh;
-          e[i] = d[i] * xh;
+          dgs[j][i & 1] = fmaf(d[i], xh, dgs[j][i & 1]);
+          dbs[j][i & 1] += d[i];
           const float dn = d[i] * gb.x;
-          if (i < 2) { s1a += dn; s2a += dn * xh; } else { s1b += dn; s2b += dn * xh; }
+          if (i < 2) { s1a += dn; s2a = fmaf(dn, xh, s2a); } else { s1b += dn; s2b = fmaf(dn, xh, s2b); }
         }
-        // dgamma += sum_frames d * xhat, dbeta += sum_frames d   (rows 11 / 12 of D)
-        mma_hilo(D[j], a2, e);
-        const uint32_t p0 = pack_bf16x2(d[0], d[1]), p1 = pack_bf16x2(d[2], d[3]);
-        mma_bf16_16816(D[j], a3, movmatrix_t(p0), movmatrix_t(p1));
-        dv[j][0] = p0;  // masked gradient, still exact in bf16
-        dv[j][1] = p1;
+        dv[j][0] = pack_bf16x2(d[0], d[1]);  // masked gradient, exact in bf16
+        dv[j][1] = pack_bf16x2(d[2], d[3]);
       }
       s1a = quad_sum(s1a); s2a = quad_sum(s2a); s1b = quad_sum(s1b); s2b = quad_sum(s2b);
       float2* st = sStat + phase * NW * 16;
@@ -377,11 +369,14 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
       }
       __syncthreads();
       float S1a = 0.f, S2a = 0.f, S1b = 0.f, S2b = 0.f;
+#pragma unroll
       for (int w = 0; w < NW; ++w) {
         const float2 u0 = st[w * 16 + g], u1 = st[w * 16 + g + 8];
         S1a += u0.x; S2a += u0.y; S1b += u1.x; S2b += u1.y;
       }
-      S1a *= invC; S1b *= invC; S2a *= invCm1; S2b *= invCm1;
+      // dy = rstd * (dn - mean_c(dn) - xhat * sum_c(dn * xhat) / (C - 1)) = dn * rstd + (xhat * kb + ka)
+      const float ka0 = -S1a * invC * rstd0, kb0 = -S2a * invCm1 * rstd0;
+      const float ka1 = -S1b * invC * rstd1, kb1 = -S2b * invCm1 * rstd1;
       uint32_t a1[4];
       {
         const int mi = lane >> 3, r = lane & 7;
@@ -389,20 +384,22 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
       }
 #pragma unroll
       for (int j = 0; j < NT; ++j) {
-        const float2 gb0 = sGB[c0 + 8 * j + 2 * q], gb1 = sGB[c0 + 8 * j + 2 * q + 1];
-        const __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&dv[j][0]);
-        const __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&dv[j][1]);
-        const float dy0 = rstd0 * (__low2float(h0) * gb0.x - S1a - acc[j][0] * S2a);
-        const float dy1 = rstd0 * (__high2float(h0) * gb1.x - S1a - acc[j][1] * S2a);
-        const float dy2 = rstd1 * (__low2float(h1) * gb0.x - S1b - acc[j][2] * S2b);
-        const float dy3 = rstd1 * (__high2float(h1) * gb1.x - S1b - acc[j][3] * S2b);
+        const float g0 = sGB[c0 + 8 * j + 2 * q].x, g1 = sGB[c0 + 8 * j + 2 * q + 1].x;
+        const float dy0 = fmaf(__uint_as_float(dv[j][0] << 16) * g0, rstd0, fmaf(acc[j][0], kb0, ka0));
+        const float dy1 = fmaf(__uint_as_float(dv[j][0] & 0xffff0000u) * g1, rstd0, fmaf(acc[j][1], kb0, ka0));
+        const float dy2 = fmaf(__uint_as_float(dv[j][1] << 16) * g0, rstd1, fmaf(acc[j][2], kb1, ka1));
+        const float dy3 = fmaf(__uint_as_float(dv[j][1] & 0xffff0000u) * g1, rstd1, fmaf(acc[j][3], kb1, ka1));
         // dW[tap] += sum_frames x[tap] * dy (rows 0..9), db += sum_frames dy (row 10)
-        const float dy[4] = {dy0, dy1, dy2, dy3};
-        mma_hilo(D[j], a1, dy);
+        // dy enters the tensor core as bf16 hi + lo (~16 mantissa bits): the sum runs over every frame of the batch
+        const uint32_t h01 = pack_bf16x2(dy0, dy1), h23 = pack_bf16x2(dy2, dy3);
+        mma_bf16_16816(D[j], a1, movmatrix_t(h01), movmatrix_t(h23));
+        const uint32_t l01 = pack_bf16x2(dy0 - __uint_as_float(h01 << 16), dy1 - __uint_as_float(h01 & 0xffff0000u));
+        const uint32_t l23 = pack_bf16x2(dy2 - __uint_as_float(h23 << 16), dy3 - __uint_as_float(h23 & 0xffff0000u));
+        mma_bf16_16816(D[j], a1, movmatrix_t(l01), movmatrix_t(l23));
       }
     }
   }
-  // D rows: thread holds m = g (taps 0..7) in D[j][0..1] and m = g + 8 (taps 8, 9, db, dgamma, dbeta) in D[j][2..3]
+  // D rows: thread holds m = g (taps 0..7) in D[j][0..1] and m = g + 8 (taps 8, 9, db) in D[j][2..3]
 #pragma unroll
   for (int j = 0; j < NT; ++j) {
     const int c = c0 + 8 * j + 2 * q;
@@ -411,9 +408,20 @@ __global__ void __launch_bounds__(NT == 8 ? 256 : 512) conv0_cn_relu_bwd_kernel(
     if (g < 2) {
       red_add_f32(a.dw + (long long)c * K0 + g + 8, D[j][2]);
       red_add_f32(a.dw + (long long)(c + 1) * K0 + g + 8, D[j][3]);
-    } else if (g <= 4) {
-      float* dst = g == 2 ? a.db : (g == 3 ? a.dgamma : a.dbeta);
-      red_add_v2_f32(dst + c, D[j][2], D[j][3]);
+    } else if (g == 2) {
+      red_add_v2_f32(a.db + c, D[j][2], D[j][3]);
+    }
+    // dgamma / dbeta: sum the 8 lanes that share q (different frames), lanes 0..3 publish
+    float v[4] = {dgs[j][0], dgs[j][1], dbs[j][0], dbs[j][1]};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[i] += __shfl_xor_sync(0xffffffffu, v[i], 4);
+      v[i] += __shfl_xor_sync(0xffffffffu, v[i], 8);
+      v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+    }
+    if (g == 0) {
+      red_add_v2_f32(a.dgamma + c, v[0], v[1]);
+      red_add_v2_f32(a.dbeta + c, v[2], v[3]);
     }
   }
 }
@@ -448,12 +456,27 @@ extern "C" int cpc_conv0_cn_relu_fwd(const CpcConv0* d, void* stream_) {
   const int spw = (a.L0 + STRIP - 1) / STRIP;
   const unsigned blocks = (unsigned)(a.N * spw);
   const size_t smem = STRIP * 64 + (size_t)a.C * 64 + 2 * NW * 16 * 8 + (size_t)NW * 16 * (8 * NT) * 2;
-  if (smem > 48 * 1024) {
-    if (NT == 8) cudaFuncSetAttribute(conv0_cn_relu_fwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    else cudaFuncSetAttribute(conv0_cn_relu_fwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+#define CPC_CONV0_FWD(NT_, NW_)                                                                                       \
+  case NW_: {                                                                                                          \
+    if (smem > 48 * 1024)                                                                                              \
+      cudaFuncSetAttribute(conv0_cn_relu_fwd_kernel<NT_, NW_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    conv0_cn_relu_fwd_kernel<NT_, NW_><<<blocks, 32 * NW_, smem, stream>>>(a);                                         \
+    break;                                                                                                             \
   }
-  if (NT == 8) conv0_cn_relu_fwd_kernel<8><<<blocks, 32 * NW, smem, stream>>>(a);
-  else conv0_cn_relu_fwd_kernel<4><<<blocks, 32 * NW, smem, stream>>>(a);
+  if (NT == 8) {
+    switch (NW) {
+      CPC_CONV0_FWD(8, 1) CPC_CONV0_FWD(8, 2) CPC_CONV0_FWD(8, 3) CPC_CONV0_FWD(8, 4) CPC_CONV0_FWD(8, 5)
+      CPC_CONV0_FWD(8, 6) CPC_CONV0_FWD(8, 7) CPC_CONV0_FWD(8, 8)
+      default: return CPC_ERR_UNSUPPORTED;
+    }
+  } else {
+    switch (NW) {
+      CPC_CONV0_FWD(4, 1) CPC_CONV0_FWD(4, 3) CPC_CONV0_FWD(4, 5) CPC_CONV0_FWD(4, 7) CPC_CONV0_FWD(4, 9)
+      CPC_CONV0_FWD(4, 11) CPC_CONV0_FWD(4, 13) CPC_CONV0_FWD(4, 15)
+      default: return CPC_ERR_UNSUPPORTED;
+    }
+  }
+#undef CPC_CONV0_FWD
   return launch_status();
 }
 
@@ -468,20 +491,32 @@ extern "C" int cpc_conv0_cn_relu_bwd(const CpcConv0* d, void* stream_) {
     return CPC_ERR_ARG;
   const int items = a.N * ((a.L0 + STRIPB - 1) / STRIPB);
   const size_t smem = STRIPB * 96 + (size_t)a.C * 64 + 2 * NW * 16 * 8 + (size_t)a.C * 8;
-  if (smem > 48 * 1024) {
-    if (NT == 8) cudaFuncSetAttribute(conv0_cn_relu_bwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    else cudaFuncSetAttribute(conv0_cn_relu_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  }
-  int occ = 1;
-  if (NT == 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv0_cn_relu_bwd_kernel<8>, 32 * NW, smem);
-  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv0_cn_relu_bwd_kernel<4>, 32 * NW, smem);
-  if (occ < 1) occ = 1;
-  int sms = 148;
-  int dev = 0;
+  int sms = 148, dev = 0;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  long long blocks = (long long)sms * occ;
-  if (blocks > items) blocks = items;
-  if (NT == 8) conv0_cn_relu_bwd_kernel<8><<<(unsigned)blocks, 32 * NW, smem, stream>>>(a);
-  else conv0_cn_relu_bwd_kernel<4><<<(unsigned)blocks, 32 * NW, smem, stream>>>(a);
+#define CPC_CONV0_BWD(NT_, NW_)                                                                                       \
+  case NW_: {                                                                                                          \
+    if (smem > 48 * 1024)                                                                                              \
+      cudaFuncSetAttribute(conv0_cn_relu_bwd_kernel<NT_, NW_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    int occ = 1;                                                                                                       \
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv0_cn_relu_bwd_kernel<NT_, NW_>, 32 * NW_, smem);           \
+    long long blocks = (long long)sms * (occ < 1 ? 1 : occ);                                                           \
+    if (blocks > items) blocks = items;                                                                                \
+    conv0_cn_relu_bwd_kernel<NT_, NW_><<<(unsigned)blocks, 32 * NW_, smem, stream>>>(a);                               \
+    break;                                                                                                             \
+  }
+  if (NT == 8) {
+    switch (NW) {
+      CPC_CONV0_BWD(8, 1) CPC_CONV0_BWD(8, 2) CPC_CONV0_BWD(8, 3) CPC_CONV0_BWD(8, 4) CPC_CONV0_BWD(8, 5)
+      CPC_CONV0_BWD(8, 6) CPC_CONV0_BWD(8, 7) CPC_CONV0_BWD(8, 8)
+      default: return CPC_ERR_UNSUPPORTED;
+    }
+  } else {
+    switch (NW) {
+      CPC_CONV0_BWD(4, 1) CPC_CONV0_BWD(4, 3) CPC_CONV0_BWD(4, 5) CPC_CONV0_BWD(4, 7) CPC_CONV0_BWD(4, 9)
+      CPC_CONV0_BWD(4, 11) CPC_CONV0_BWD(4, 13) CPC_CONV0_BWD(4, 15)
+      default: return CPC_ERR_UNSUPPORTED;
+    }
+  }
+#undef CPC_CONV0_BWD
   return launch_status();
 }
