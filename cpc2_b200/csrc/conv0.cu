@@ -12,9 +12,9 @@
 // Per 16-frame tile the warps exchange (mean, M2) partials through shared memory (Chan's combination: one barrier,
 // no cancellation), normalise in registers and write bf16 rows through an stmatrix-staged, 16-byte-per-lane store.
 // The backward recomputes the conv the same way (bit-identical ReLU mask), needs no input gradient (the input is
-// audio) and reduces dW / db / dgamma / dbeta with further MMAs whose reduction index is the frame:
-//     D[16 x C] += A1[16 x 16 frames] . dy  +  A2 . (d * xhat)  +  A3 . d
-// with A1 rows 0..9 = x_hi taps, row 10 = ones (-> db), A2 row 11 = ones (-> dgamma), A3 row 12 = ones (-> dbeta).
+// audio) and reduces dW / db with a further MMA whose reduction index is the frame:
+//     D[16 x C] += A1[16 x 16 frames] . (dy_hi + dy_lo),   A1 rows 0..9 = x_hi taps, row 10 = ones (-> db)
+// (dy reaches the B-fragment layout through movmatrix.trans); dgamma / dbeta accumulate in fp32 registers.
 #include "cpc_internal.h"
 #include "ptx.cuh"
 
