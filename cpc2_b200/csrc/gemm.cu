@@ -91,10 +91,14 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmKernelArgs& p, int ti
   return t;
 }
 
+}  // namespace cpc
+#include "gemm_epilogue.cuh"
+namespace cpc {
+
 // PERSISTENT kernel: grid = min(tiles, SMs); CTA walks tiles blockIdx.x, +gridDim.x, ...  The accumulator is
 // double-buffered in TMEM so the epilogue of tile i (TMEM -> registers -> smem transpose -> coalesced global)
 // overlaps the TMA/MMA main loop of tile i+1.
-template <int BN, int STAGES, bool A_MN, bool B_MN>
+template <int BN, int STAGES, bool A_MN, bool B_MN, int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmKernelArgs p) {
@@ -202,131 +206,27 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..9)
-    // tcgen05.ld.16x256b hands every thread the accumulator in the mma C-fragment layout: per 8-column group,
-    // thread t holds columns 2*(t%4), +1 of rows t/4 and t/4 + 8.  Four lanes therefore cover 32 contiguous bytes
-    // of one fp32 output row (a full sector; 16 bytes for bf16), so global accesses are sector-coalesced with no
-    // shared-memory transpose and every load/store of a chunk is independent (high ILP).
+    // ------------------------------------------------------------------ epilogue (warps 2..9), gemm_epilogue.cuh
     const int e = warp - 2;
-    const int q = warp & 3;       // TMEM lane quarter this warp may access
-    const int half = e >> 2;      // which half of the tile's columns
-    const int rsub = lane >> 2;         // row inside an 8-row slice
-    const int csub = (lane & 3) * 2;    // first of this lane's two columns inside an 8-column group
-    uint32_t seed_lo = 0, seed_hi = 0, drop_thresh = 0;
-    float drop_scale = 1.f;
-    if (p.rng != nullptr && p.drop_p > 0.f) {
+    const int q = warp & 3;   // TMEM lane quarter this warp may access
+    const int half = e >> 2;  // which half of the tile's columns
+    EpiRng rng = {0u, 0u, 0u, 1.f};
+    if (MODE == EPI_DROP) {
       const unsigned long long seed = p.rng[0] + p.rng[1] * 0x632BE59BD9B4E019ull;
-      seed_lo = static_cast<uint32_t>(seed);
-      seed_hi = static_cast<uint32_t>(seed >> 32) + p.rng_site * 0x85EBCA77u;
-      drop_thresh = static_cast<uint32_t>(fminf(p.drop_p, 0.9999f) * 65536.0f);
-      drop_scale = 1.f / (1.f - p.drop_p);
+      rng.seed_lo = static_cast<uint32_t>(seed);
+      rng.seed_hi = static_cast<uint32_t>(seed >> 32) + p.rng_site * 0x85EBCA77u;
+      rng.thresh = static_cast<uint32_t>(fminf(p.drop_p, 0.9999f) * 65536.0f);
+      rng.scale = 1.f / (1.f - p.drop_p);
     }
     int lt = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
       const TileCoord tc = decode_tile(p, tile, BN);
       const int buf = lt & 1;
-      const long long g = tc.grp;
       mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-      const int row0 = tc.m0 + q * 32 + rsub;  // this lane's rows: row0 + 8*i, i = 0..3
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + half * (BN / 2);
-      const float* bias_g = p.bias != nullptr ? p.bias + g * p.gs_bias : nullptr;
-      const float relu_floor = p.relu ? 0.f : -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < BN / 64; ++c) {
-        const int n_base = tc.n0 + half * (BN / 2) + c * 32 + csub;  // column of v[..][0] for j = 0
-        uint32_t v[2][16];
-        tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
-        tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
-        tmem_ld_wait();
-        // number of valid 8-column groups of this chunk (warp-uniform: N is a multiple of 8)
-        const int jmax = min(4, (p.N - (n_base - csub)) >> 3);
-        if (jmax <= 0) continue;
-        float2 b2[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          b2[j] = make_float2(0.f, 0.f);
-          if (bias_g != nullptr && j < jmax) b2[j] = *reinterpret_cast<const float2*>(bias_g + n_base + 8 * j);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int row = row0 + 8 * i;
-          if (row >= p.M) continue;
-          const long long rl = row;
-          // v[i >> 1] holds rows +0 / +8 (regs 0,1 / 2,3 of each column group) of the 16-lane slice i >> 1
-          float x[8];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            x[2 * j] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), p.alpha, b2[j].x);
-            x[2 * j + 1] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), p.alpha, b2[j].y);
-          }
-          if (p.res != nullptr) {
-            const __nv_bfloat16* res_r = p.res + g * p.gs_res + rl * p.ld_res + n_base;
-            __nv_bfloat162 r[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              r[j] = j < jmax ? *reinterpret_cast<const __nv_bfloat162*>(res_r + 8 * j) : __floats2bfloat162_rn(0.f, 0.f);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              x[2 * j] += __low2float(r[j]);
-              x[2 * j + 1] += __high2float(r[j]);
-            }
-          }
-#pragma unroll
-          for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], relu_floor);
-          if (p.gate != nullptr) {
-            const __nv_bfloat16* gate_r = p.gate + g * p.gs_gate + rl * p.ld_gate + n_base;
-            __nv_bfloat162 r[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              r[j] = j < jmax ? *reinterpret_cast<const __nv_bfloat162*>(gate_r + 8 * j) : __floats2bfloat162_rn(0.f, 0.f);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              x[2 * j] = __low2float(r[j]) > 0.f ? x[2 * j] * p.gate_scale : 0.f;
-              x[2 * j + 1] = __high2float(r[j]) > 0.f ? x[2 * j + 1] * p.gate_scale : 0.f;
-            }
-          }
-          if (drop_thresh != 0) {
-            const unsigned long long ebase = (((unsigned long long)g * p.M + row) * (unsigned long long)p.N + n_base) >> 1;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {  // one 32-bit draw per 2 consecutive columns
-              const uint32_t bits = rng_pair_u16(seed_lo, seed_hi, ebase + 4 * j);
-              x[2 * j] = (bits & 0xFFFFu) >= drop_thresh ? x[2 * j] * drop_scale : 0.f;
-              x[2 * j + 1] = (bits >> 16) >= drop_thresh ? x[2 * j + 1] * drop_scale : 0.f;
-            }
-          }
-          if (p.out_bf16 != nullptr) {
-            __nv_bfloat16* o16 = p.out_bf16 + g * p.gs_bf16 + rl * p.ldd_bf16 + n_base;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              if (j < jmax) *reinterpret_cast<__nv_bfloat162*>(o16 + 8 * j) = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
-          }
-          if (p.out_f32 != nullptr) {
-            float* o32 = p.out_f32 + g * p.gs_f32 + rl * p.ldd_f32 + n_base;
-            if (p.k_splits > 1) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (j < jmax) red_add_v2_f32(o32 + 8 * j, x[2 * j], x[2 * j + 1]);
-            } else {
-              if (p.accumulate) {
-                float2 old[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                  old[j] = j < jmax ? *reinterpret_cast<const float2*>(o32 + 8 * j) : make_float2(0.f, 0.f);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  x[2 * j] += old[j].x;
-                  x[2 * j + 1] += old[j].y;
-                }
-              }
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (j < jmax) *reinterpret_cast<float2*>(o32 + 8 * j) = make_float2(x[2 * j], x[2 * j + 1]);
-            }
-          }
-        }
-      }
-      // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld above): hand it back to the MMA warp
+      epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng);
+      // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld inside): hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -372,11 +272,11 @@ static int sm_count() {
   return n;
 }
 
-template <int BN, int STAGES, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelArgs ka, int groups,
-                       cudaStream_t stream) {
+template <int BN, int STAGES, bool A_MN, bool B_MN, int MODE>
+static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelArgs ka, int groups,
+                            cudaStream_t stream) {
   using L = GemmSmem<BN, STAGES>;
-  auto kern = gemm_bf16_tcgen05_kernel<BN, STAGES, A_MN, B_MN>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, STAGES, A_MN, B_MN, MODE>;
   static bool attr_done = false;  // per instantiation
   if (!attr_done) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess)
@@ -389,6 +289,18 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelA
   const int grid = ka.total_tiles < sm_count() ? ka.total_tiles : sm_count();
   kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, ka);
   return cudaGetLastError() == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int groups,
+                       cudaStream_t stream) {
+  // epilogue mode (exclusive; the entry point has rejected combinations no mode covers)
+  if (ka.k_splits > 1) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_SPLITK>(ta, tb, ka, groups, stream);
+  if (ka.accumulate) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_ACCUM>(ta, tb, ka, groups, stream);
+  if (ka.rng != nullptr && ka.drop_p > 0.f) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_DROP>(ta, tb, ka, groups, stream);
+  if (ka.gate != nullptr) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_GATE>(ta, tb, ka, groups, stream);
+  if (ka.res != nullptr) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_RES>(ta, tb, ka, groups, stream);
+  return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_PLAIN>(ta, tb, ka, groups, stream);
 }
 
 template <int BN, int STAGES>
@@ -419,6 +331,12 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
                        d->gate || d->drop_p > 0.f))
     return CPC_ERR_ARG;
 
+  {  // one epilogue feature that needs extra global loads per launch (see gemm_epilogue.cuh)
+    const bool drop = d->rng != nullptr && d->drop_p > 0.f;
+    const int extra = (d->accumulate ? 1 : 0) + (drop ? 1 : 0) + (d->gate ? 1 : 0) + (d->res ? 1 : 0);
+    if (extra > 1) return CPC_ERR_UNSUPPORTED;
+    if (d->accumulate && (d->out_bf16 != nullptr || d->relu)) return CPC_ERR_UNSUPPORTED;
+  }
   GemmKernelArgs ka;
   ka.M = d->M; ka.N = d->N;
   ka.k_per_slab = k_per_slab;

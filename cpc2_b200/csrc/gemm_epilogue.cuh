@@ -1,0 +1,156 @@
+// Epilogue of the tcgen05 GEMM (gemm.cu): TMEM -> registers -> global, specialised per MODE so that the inner
+// loops carry no runtime feature tests.  For the K = 256 shapes that dominate the CPC step the epilogue, not the
+// MMA main loop, bounds the kernel (a 128 x 256 tile needs ~0.5 us of tensor time), so the code here is written
+// for instruction count and memory-level parallelism:
+//   * every global load a chunk needs (residual / gate / previous fp32 value for 4 rows x 4 column groups) is
+//     issued before the first dependent instruction, so one memory round trip covers the whole chunk;
+//   * addresses are lane-constant bases plus compile-time-strided offsets;
+//   * dropout folds its 1/(1-p) scale into alpha and the bias, and draws one 32-bit hash per two columns.
+#pragma once
+#include "cpc_internal.h"
+#include "ptx.cuh"
+
+namespace cpc {
+
+enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5 };
+
+struct EpiRng {
+  uint32_t seed_lo, seed_hi, thresh;
+  float scale;
+};
+
+__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// 32-bit counter hash (lowbias32 finaliser): two 16-bit draws for a pair of consecutive columns
+__device__ __forceinline__ uint32_t epi_hash(uint32_t idx2, uint32_t seed_lo, uint32_t seed_hi) {
+  uint32_t h = idx2 * 0x9E3779B1u + seed_lo;
+  h ^= seed_hi;
+  h ^= h >> 16; h *= 0x7FEB352Du;
+  h ^= h >> 15; h *= 0x846CA68Bu;
+  h ^= h >> 16;
+  return h;
+}
+
+// One 128 x BN accumulator tile.  Warp (q = TMEM lane quarter, half = column half) drains rows q*32 .. +31 of
+// columns half*BN/2 .. +BN/2 in chunks of 32 columns; tcgen05.ld.16x256b hands lane (rsub = lane/4, csub =
+// 2*(lane%4)) columns csub, csub+1 of every 8-column group for rows rsub + 8*i, i = 0..3 (four lanes cover 32
+// contiguous bytes of an fp32 row, 16 of a bf16 row).
+template <int MODE, int BN>
+__device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const TileCoord& tc, uint32_t taddr, int q,
+                                              int half, int lane, const EpiRng& rng) {
+  const int rsub = lane >> 2, csub = (lane & 3) * 2;
+  const long long g = tc.grp;
+  const int row0 = tc.m0 + q * 32 + rsub;
+  const int col0 = tc.n0 + half * (BN / 2) + csub;
+  bool rok[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) rok[i] = row0 + 8 * i < p.M;
+  float alpha = p.alpha;
+  if (MODE == EPI_DROP) alpha *= rng.scale;
+  const float relu_floor = p.relu ? 0.f : -INFINITY;
+  const float* bias_g = p.bias != nullptr ? p.bias + g * p.gs_bias + col0 : nullptr;
+  __nv_bfloat16* o16 = p.out_bf16 != nullptr ? p.out_bf16 + g * p.gs_bf16 + (long long)row0 * p.ldd_bf16 + col0 : nullptr;
+  float* o32 = p.out_f32 != nullptr ? p.out_f32 + g * p.gs_f32 + (long long)row0 * p.ldd_f32 + col0 : nullptr;
+  const __nv_bfloat16* aux = nullptr;  // residual (EPI_RES) or gate (EPI_GATE)
+  long long ld_aux = 0;
+  if (MODE == EPI_RES) { aux = p.res + g * p.gs_res + (long long)row0 * p.ld_res + col0; ld_aux = p.ld_res; }
+  if (MODE == EPI_GATE) { aux = p.gate + g * p.gs_gate + (long long)row0 * p.ld_gate + col0; ld_aux = p.ld_gate; }
+  const uint32_t pair0 = (uint32_t)(((unsigned long long)g * p.M + row0) * (unsigned long long)p.N + col0) >> 1;
+#pragma unroll 1
+  for (int c = 0; c < BN / 64; ++c) {
+    const int nb = col0 - csub + c * 32;  // first column of this chunk
+    const int jmax = min(4, (p.N - nb) >> 3);  // valid 8-column groups (warp-uniform: N is a multiple of 8)
+    if (jmax <= 0) break;
+    uint32_t v[2][16];
+    tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+    tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
+    // ---- every global load of the chunk, before anything depends on one
+    float2 b2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      b2[j] = (bias_g != nullptr && j < jmax) ? *reinterpret_cast<const float2*>(bias_g + c * 32 + 8 * j) : make_float2(0.f, 0.f);
+    uint32_t ax[4][4];
+    float2 old[4][4];
+    if (MODE == EPI_RES || MODE == EPI_GATE) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          ax[i][j] = (rok[i] && j < jmax)
+                         ? __ldg(reinterpret_cast<const unsigned int*>(aux + (long long)(8 * i) * ld_aux + c * 32 + 8 * j))
+                         : 0u;
+    }
+    if (MODE == EPI_ACCUM) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          old[i][j] = (rok[i] && j < jmax)
+                          ? *reinterpret_cast<const float2*>(o32 + (long long)(8 * i) * p.ldd_f32 + c * 32 + 8 * j)
+                          : make_float2(0.f, 0.f);
+    }
+    tmem_ld_wait();
+    if (MODE == EPI_DROP) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { b2[j].x *= rng.scale; b2[j].y *= rng.scale; }
+    }
+    // ---- arithmetic and stores, row by row (v[i >> 1] holds rows +0 / +8 in regs 0,1 / 2,3 of each group)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float x[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        x[2 * j] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[j].x);
+        x[2 * j + 1] = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[j].y);
+      }
+      if (MODE == EPI_RES) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { x[2 * j] += bf16lo(ax[i][j]); x[2 * j + 1] += bf16hi(ax[i][j]); }
+      }
+      if (MODE != EPI_SPLITK && MODE != EPI_ACCUM) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], relu_floor);
+      }
+      if (MODE == EPI_GATE) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          x[2 * j] = bf16lo(ax[i][j]) > 0.f ? x[2 * j] * p.gate_scale : 0.f;
+          x[2 * j + 1] = bf16hi(ax[i][j]) > 0.f ? x[2 * j + 1] * p.gate_scale : 0.f;
+        }
+      }
+      if (MODE == EPI_DROP) {
+        const uint32_t pr = pair0 + (uint32_t)(((long long)(8 * i) * p.N + c * 32) >> 1);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t bits = epi_hash(pr + 4 * j, rng.seed_lo, rng.seed_hi);
+          x[2 * j] = (bits & 0xFFFFu) >= rng.thresh ? x[2 * j] : 0.f;
+          x[2 * j + 1] = (bits >> 16) >= rng.thresh ? x[2 * j + 1] : 0.f;
+        }
+      }
+      if (MODE == EPI_ACCUM) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { x[2 * j] += old[i][j].x; x[2 * j + 1] += old[i][j].y; }
+      }
+      if (!rok[i]) continue;
+      if (MODE != EPI_SPLITK && o16 != nullptr) {
+        __nv_bfloat16* dst = o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < jmax) *reinterpret_cast<__nv_bfloat162*>(dst + 8 * j) = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+      }
+      if (o32 != nullptr) {
+        float* dst = o32 + (long long)(8 * i) * p.ldd_f32 + c * 32;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (j < jmax) {
+            if (MODE == EPI_SPLITK) red_add_v2_f32(dst + 8 * j, x[2 * j], x[2 * j + 1]);
+            else *reinterpret_cast<float2*>(dst + 8 * j) = make_float2(x[2 * j], x[2 * j + 1]);
+          }
+        }
+      }
+    }
+  }
+}
+
+}  // namespace cpc
