@@ -100,10 +100,11 @@ class LinearHeads:
         gflat = torch.zeros(self.arena.numel, device=dev)
         dw = self.arena.span(gflat, 0, G, (G, do, d))
         ops.linear_dw(dout, sv["x"], dw, T, do, d, groups=G, x_shared=True)
-        dx = torch.empty(T, d, device=dev)
+        dx = torch.zeros(T, d, device=dev)
         A = K.View(dout, do, T, G, do, T * do, major=0, gmul=0)
         B = K.View(sv["w16"], d, do, G, d, do * d, major=1, gmul=0)
-        K.gemm(A, B, T, d, G * do, k_per_slab=do, out_f32=dx)
+        K.gemm(A, B, T, d, G * do, k_per_slab=do, k_splits=ops.auto_splits(T, d, G * do, 1, do), out_f32=dx,
+               accumulate=True)
         return dx, gflat
 
 

@@ -222,10 +222,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
       const TileCoord tc = decode_tile(p, tile, BN);
       const int buf = lt & 1;
-      mbar_wait(&acc_full[buf], (lt >> 1) & 1);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + half * (BN / 2);
-      epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng);
+      epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng, &acc_full[buf], (lt >> 1) & 1);
       // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld inside): hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();

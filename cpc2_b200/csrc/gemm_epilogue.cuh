@@ -32,65 +32,99 @@ __device__ __forceinline__ uint32_t epi_hash(uint32_t idx2, uint32_t seed_lo, ui
   return h;
 }
 
+template <int MODE>
+struct EpiLoads {  // everything one 32-column chunk reads from global memory
+  float2 b2[4];
+  uint32_t ax[(MODE == EPI_RES || MODE == EPI_GATE) ? 4 : 1][4];
+  float2 old[MODE == EPI_ACCUM ? 4 : 1][4];
+};
+
+struct EpiLane {  // lane-constant addressing of one tile
+  const float* bias;
+  __nv_bfloat16* o16;
+  float* o32;
+  const __nv_bfloat16* aux;  // residual (EPI_RES) or gate (EPI_GATE)
+  long long ld_aux;
+  int col_first;  // first column of this warp's half (multiple of 8)
+  bool rok[4];
+};
+
+template <int MODE>
+__device__ __forceinline__ void epi_load_chunk(EpiLoads<MODE>& L, const GemmKernelArgs& p, const EpiLane& e, int c) {
+  const int jmax = (p.N - (e.col_first + c * 32)) >> 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    L.b2[j] = (e.bias != nullptr && j < jmax) ? *reinterpret_cast<const float2*>(e.bias + c * 32 + 8 * j) : make_float2(0.f, 0.f);
+  if (MODE == EPI_RES || MODE == EPI_GATE) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        L.ax[i][j] = (e.rok[i] && j < jmax)
+                         ? __ldg(reinterpret_cast<const unsigned int*>(e.aux + (long long)(8 * i) * e.ld_aux + c * 32 + 8 * j))
+                         : 0u;
+  }
+  if (MODE == EPI_ACCUM) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        L.old[i][j] = (e.rok[i] && j < jmax)
+                          ? *reinterpret_cast<const float2*>(e.o32 + (long long)(8 * i) * p.ldd_f32 + c * 32 + 8 * j)
+                          : make_float2(0.f, 0.f);
+  }
+}
+
 // One 128 x BN accumulator tile.  Warp (q = TMEM lane quarter, half = column half) drains rows q*32 .. +31 of
 // columns half*BN/2 .. +BN/2 in chunks of 32 columns; tcgen05.ld.16x256b hands lane (rsub = lane/4, csub =
 // 2*(lane%4)) columns csub, csub+1 of every 8-column group for rows rsub + 8*i, i = 0..3 (four lanes cover 32
-// contiguous bytes of an fp32 row, 16 of a bf16 row).
+// contiguous bytes of an fp32 row, 16 of a bf16 row).  The global loads of chunk 0 are issued BEFORE the wait for
+// the accumulator (they overlap the MMA main loop), those of chunk c+1 before the arithmetic of chunk c.
 template <int MODE, int BN>
 __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const TileCoord& tc, uint32_t taddr, int q,
-                                              int half, int lane, const EpiRng& rng) {
+                                              int half, int lane, const EpiRng& rng, uint64_t* acc_full_bar,
+                                              uint32_t parity) {
+  constexpr int NC = BN / 64;
   const int rsub = lane >> 2, csub = (lane & 3) * 2;
   const long long g = tc.grp;
   const int row0 = tc.m0 + q * 32 + rsub;
   const int col0 = tc.n0 + half * (BN / 2) + csub;
-  bool rok[4];
+  EpiLane e;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) rok[i] = row0 + 8 * i < p.M;
+  for (int i = 0; i < 4; ++i) e.rok[i] = row0 + 8 * i < p.M;
+  e.col_first = col0 - csub;
+  e.bias = p.bias != nullptr ? p.bias + g * p.gs_bias + col0 : nullptr;
+  e.o16 = p.out_bf16 != nullptr ? p.out_bf16 + g * p.gs_bf16 + (long long)row0 * p.ldd_bf16 + col0 : nullptr;
+  e.o32 = p.out_f32 != nullptr ? p.out_f32 + g * p.gs_f32 + (long long)row0 * p.ldd_f32 + col0 : nullptr;
+  e.aux = nullptr;
+  e.ld_aux = 0;
+  if (MODE == EPI_RES) { e.aux = p.res + g * p.gs_res + (long long)row0 * p.ld_res + col0; e.ld_aux = p.ld_res; }
+  if (MODE == EPI_GATE) { e.aux = p.gate + g * p.gs_gate + (long long)row0 * p.ld_gate + col0; e.ld_aux = p.ld_gate; }
   float alpha = p.alpha;
   if (MODE == EPI_DROP) alpha *= rng.scale;
   const float relu_floor = p.relu ? 0.f : -INFINITY;
-  const float* bias_g = p.bias != nullptr ? p.bias + g * p.gs_bias + col0 : nullptr;
-  __nv_bfloat16* o16 = p.out_bf16 != nullptr ? p.out_bf16 + g * p.gs_bf16 + (long long)row0 * p.ldd_bf16 + col0 : nullptr;
-  float* o32 = p.out_f32 != nullptr ? p.out_f32 + g * p.gs_f32 + (long long)row0 * p.ldd_f32 + col0 : nullptr;
-  const __nv_bfloat16* aux = nullptr;  // residual (EPI_RES) or gate (EPI_GATE)
-  long long ld_aux = 0;
-  if (MODE == EPI_RES) { aux = p.res + g * p.gs_res + (long long)row0 * p.ld_res + col0; ld_aux = p.ld_res; }
-  if (MODE == EPI_GATE) { aux = p.gate + g * p.gs_gate + (long long)row0 * p.ld_gate + col0; ld_aux = p.ld_gate; }
   const uint32_t pair0 = (uint32_t)(((unsigned long long)g * p.M + row0) * (unsigned long long)p.N + col0) >> 1;
-#pragma unroll 1
-  for (int c = 0; c < BN / 64; ++c) {
-    const int nb = col0 - csub + c * 32;  // first column of this chunk
-    const int jmax = min(4, (p.N - nb) >> 3);  // valid 8-column groups (warp-uniform: N is a multiple of 8)
+  EpiLoads<MODE> L[2];
+  epi_load_chunk<MODE>(L[0], p, e, 0);
+  mbar_wait(acc_full_bar, parity);
+  tc_fence_after();
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const int jmax = min(4, (p.N - (e.col_first + c * 32)) >> 3);  // valid 8-column groups (warp-uniform)
     if (jmax <= 0) break;
     uint32_t v[2][16];
     tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
     tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
-    // ---- every global load of the chunk, before anything depends on one
+    if (c + 1 < NC) epi_load_chunk<MODE>(L[(c + 1) & 1], p, e, c + 1);
+    tmem_ld_wait();
     float2 b2[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-      b2[j] = (bias_g != nullptr && j < jmax) ? *reinterpret_cast<const float2*>(bias_g + c * 32 + 8 * j) : make_float2(0.f, 0.f);
-    uint32_t ax[4][4];
-    float2 old[4][4];
-    if (MODE == EPI_RES || MODE == EPI_GATE) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          ax[i][j] = (rok[i] && j < jmax)
-                         ? __ldg(reinterpret_cast<const unsigned int*>(aux + (long long)(8 * i) * ld_aux + c * 32 + 8 * j))
-                         : 0u;
-    }
-    if (MODE == EPI_ACCUM) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          old[i][j] = (rok[i] && j < jmax)
-                          ? *reinterpret_cast<const float2*>(o32 + (long long)(8 * i) * p.ldd_f32 + c * 32 + 8 * j)
-                          : make_float2(0.f, 0.f);
-    }
-    tmem_ld_wait();
+    for (int j = 0; j < 4; ++j) b2[j] = L[c & 1].b2[j];
+    const bool* rok = e.rok;
+    __nv_bfloat16* o16 = e.o16;
+    float* o32 = e.o32;
+    auto& ax = L[c & 1].ax;
+    auto& old = L[c & 1].old;
     if (MODE == EPI_DROP) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) { b2[j].x *= rng.scale; b2[j].y *= rng.scale; }

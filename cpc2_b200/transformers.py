@@ -232,7 +232,7 @@ class TransformerStack:
         datt = torch.empty(G, T, d, device=dev, dtype=BF16)
         dqkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
         dscore = torch.empty_like(sv["probs"])
-        dx = torch.empty(T, d, device=dev) if shared else torch.empty(G, T, d, device=dev)
+        dx = torch.zeros(T, d, device=dev) if shared else torch.empty(G, T, d, device=dev)  # shared: split-K target
         # out = LN2(pre2)
         K.rownorm_bwd(dout.reshape(G * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], G * T, do, P32["ln2w"], P32["ln2b"],
                       dx_bf16=dpre2, dgamma=Gd["ln2w"], dbeta=Gd["ln2b"], rows_per_group=T)
@@ -274,7 +274,8 @@ class TransformerStack:
             # dx = sum_g (dqkv_g . Wqkv_g + dpre1_g): one GEMM whose reduction runs over (group, 3d), then a group sum
             A = K.View(dqkv, 3 * d, T, G, 3 * d, T * 3 * d, major=0, gmul=0)
             B = K.View(P16["Wqkv"], d, 3 * d, G, d, 3 * d * d, major=1, gmul=0)
-            K.gemm(A, B, T, d, G * 3 * d, k_per_slab=3 * d, out_f32=dx)
+            K.gemm(A, B, T, d, G * 3 * d, k_per_slab=3 * d, k_splits=ops.auto_splits(T, d, G * 3 * d, 1, 3 * d),
+                   out_f32=dx, accumulate=True)
             K.groupsum(dpre1, T * d, G, out_f32=dx, accumulate=True)
         else:
             ops.linear_dx(dqkv, P16["Wqkv"], T, 3 * d, d, groups=G, out_f32=dx, res=dpre1)
