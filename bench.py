@@ -226,8 +226,8 @@ def run_ours(opt):
     t0.record()
     for _ in range(opt.steps):
         losses, acc = step.step(host_seq, non_blocking=True)
-        host_out[0].copy_(losses.view(-1), non_blocking=True)
-        host_out[1].copy_(acc.view(-1), non_blocking=True)
+        host_out[0].copy_(losses.detach().view(-1), non_blocking=True)
+        host_out[1].copy_(acc.detach().view(-1), non_blocking=True)
         torch.cuda.current_stream().synchronize()  # the caller reads the loss every step (train.py:121-122)
     t1.record()
     barrier()
@@ -283,7 +283,14 @@ def run_ours(opt):
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # The step's CUDA graph holds captured NCCL launches; tearing the communicator down while the graph is
+        # alive blocks inside ncclCommDestroy (observed at N=2: JSON printed, process never exited).  All ranks
+        # meet once more, the graph is dropped, and the process leaves without the communicator teardown.
+        barrier()
+        del step
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():

@@ -163,7 +163,7 @@ class Nce(ctypes.Structure):
 
 class Lstm(ctypes.Structure):
     _fields_ = [
-        ("N", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int),
+        ("N", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int), ("cell", ctypes.c_int),
         ("gx", ctypes.c_void_p), ("w_hh", ctypes.c_void_p), ("h0", ctypes.c_void_p), ("c0", ctypes.c_void_p),
         ("h_pad", ctypes.c_void_p), ("out", ctypes.c_void_p), ("gates", ctypes.c_void_p), ("c_all", ctypes.c_void_p),
         ("h_n", ctypes.c_void_p), ("c_n", ctypes.c_void_p),

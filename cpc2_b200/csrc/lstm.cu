@@ -50,6 +50,7 @@ struct LstmArgs {
   __nv_bfloat16* dgates;      // [N, S, 4H] bf16 gradient w.r.t. the gate pre-activations
 };
 
+constexpr int CELL_LSTM = 0, CELL_GRU = 1, CELL_RNN = 2;
 constexpr int NB = 8;          // sequences per cluster: one mma n-tile.  Small on purpose -- the recurrence is
                                // latency-bound and the rest of the chip is idle, so more clusters beat wider ones
 constexpr int LSTM_THREADS = 256;
@@ -58,7 +59,7 @@ constexpr int LSTM_THREADS = 256;
 // steps ahead with cp.async (16-byte chunks: every (sequence, gate) is one contiguous 128-byte segment).
 constexpr int GX_PITCH = 132;  // floats per sequence row: bank = 4*b + unit -> conflict-free reads
 
-template <int H>
+template <int H, int CELL>
 __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArgs a) {
   constexpr int CL = H / 32, KT = H / 16, HP = H + 8;
   __shared__ __align__(16) __nv_bfloat16 h_s[2][NB][HP];          // h_{t-1} of the whole cluster (double-buffered)
@@ -118,7 +119,8 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
   cp_async_wait<1>();
   cluster_sync_all();  // barriers initialised cluster-wide, h_s[0] and gx_s[0] visible
 
-  float c_state = (valid && a.c0 != nullptr) ? a.c0[(long long)nidx * H + unit] : 0.f;
+  const float* s0p = CELL == CELL_LSTM ? a.c0 : a.h0;  // the fp32 carried state: c (LSTM) or h (GRU, RNN)
+  float c_state = (valid && s0p != nullptr) ? s0p[(long long)nidx * H + unit] : 0.f;
 
   for (int t = 0; t < a.S; ++t) {
     const int p = t & 1;
@@ -152,9 +154,22 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     const float pf = (g0 ? c4[1] : r0) + gxr[32];
     const float pg = (g0 ? r1 : c4[2]) + gxr[64];
     const float po = (g0 ? c4[3] : r1) + gxr[96];
-    const float ig = sigmoid_f(pi), fg = sigmoid_f(pf), gg = tanh_f(pg), og = sigmoid_f(po);
-    const float cn = valid ? fg * c_state + ig * gg : 0.f;
-    const float hn = valid ? og * tanh_f(cn) : 0.f;
+    float ig, fg, gg, og, cn, hn;
+    if constexpr (CELL == CELL_LSTM) {
+      ig = sigmoid_f(pi); fg = sigmoid_f(pf); gg = tanh_f(pg); og = sigmoid_f(po);
+      cn = valid ? fg * c_state + ig * gg : 0.f;
+      hn = valid ? og * tanh_f(cn) : 0.f;
+    } else if constexpr (CELL == CELL_GRU) {
+      // slots (r, z, n_x, hn): pg = W_in x + b_in (its W_hh slot is zero), po = W_hn h + b_hn
+      ig = sigmoid_f(pi); fg = sigmoid_f(pf); og = po; gg = tanh_f(pg + ig * po);
+      hn = valid ? gg + fg * (c_state - gg) : 0.f;   // (1-z) n + z h_{t-1}; c_state carries h in fp32
+      cn = hn;
+    } else {
+      // tanh RNN: slot 0 only
+      ig = tanh_f(pi); fg = 0.f; gg = 0.f; og = 0.f;
+      hn = valid ? ig : 0.f;
+      cn = hn;
+    }
     c_state = cn;
     st_h[p][bsel][unit_l] = __float2bfloat16(hn);
     st_o[p][bsel][unit_l] = hn;
@@ -214,7 +229,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
 // multiplies them with its 128 rows of W_hh (register-resident A fragments of W_hh^T, K-split over gate rows) and
 // sends each 32-unit block of the partial dh_{t-1} to the CTA that owns it (fp32, st.shared::cluster.v2 straight
 // from the accumulator fragments; warp w's two m-tiles are exactly the block of CTA w when H = 256).
-template <int H>
+template <int H, int CELL>
 __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArgs a) {
   constexpr int CL = H / 32;
   constexpr int MT = H / 16;                      // output (h) m-tiles
@@ -267,6 +282,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     mbar_init(&bar[1], ARRIVALS);
     fence_barrier_init();
   }
+  const float* s0p = CELL == CELL_LSTM ? a.c0 : a.h0;  // state before step 0: c0 (LSTM) or h0 (GRU / RNN, whose c_all holds h)
   // per-step input prefetch (cp.async, two steps ahead): 128 threads fetch the gates tile, 64 c_{t-1}, 64 dout_t
   auto prefetch = [&](int sidx) {
     const int t = a.S - 1 - sidx;
@@ -281,7 +297,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
         const int b = (tid - 128) >> 3, ch = tid & 7;
         if (n_base + b < a.N) {
           const float* src = t > 0 ? a.c_all + ((long long)(n_base + b) * a.S + t - 1) * H
-                                   : (a.c0 != nullptr ? a.c0 + (long long)(n_base + b) * H : nullptr);
+                                   : (s0p != nullptr ? s0p + (long long)(n_base + b) * H : nullptr);
           float* dst = in_c + (buf * NB + b) * CP + ch * 4;
           if (src != nullptr) cp_async_16(dst, src + cta * 32 + ch * 4);
           else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -323,12 +339,24 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     }
     float d_i = 0.f, d_f = 0.f, d_g = 0.f, d_o = 0.f;
     if (valid) {
-      d_o = dh * tc * go * (1.f - go);
-      const float dc = dh * go * (1.f - tc * tc) + dc_state;
-      d_i = dc * gg * gi * (1.f - gi);
-      d_f = dc * cprev * gf * (1.f - gf);
-      d_g = dc * gi * (1.f - gg * gg);
-      dc_state = dc * gf;
+      if constexpr (CELL == CELL_LSTM) {
+        d_o = dh * tc * go * (1.f - go);
+        const float dc = dh * go * (1.f - tc * tc) + dc_state;
+        d_i = dc * gg * gi * (1.f - gi);
+        d_f = dc * cprev * gf * (1.f - gf);
+        d_g = dc * gi * (1.f - gg * gg);
+        dc_state = dc * gf;
+      } else if constexpr (CELL == CELL_GRU) {
+        // saved slots: r = gi, z = gf, n = gg, hn = W_hn h + b_hn = go; cprev = h_{t-1}
+        dh += dc_state;                                   // the z-gated path h_{t-1} -> h_t stays in this thread
+        d_g = dh * (1.f - gf) * (1.f - gg * gg);          // d n_pre (input side)
+        d_f = dh * (cprev - gg) * gf * (1.f - gf);        // d z_pre
+        d_i = d_g * go * gi * (1.f - gi);                 // d r_pre
+        d_o = d_g * gi;                                   // d (W_hn h + b_hn) (hidden side of the n gate)
+        dc_state = dh * gf;
+      } else {
+        d_i = dh * (1.f - gi * gi);                       // saved slot 0 = h_t
+      }
     }
     ct = cprev;
     __nv_bfloat16* ds = dg_s + (pp * NB + bsel) * GP + unit_l;
@@ -382,7 +410,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
   cluster_sync_all();
 }
 
-template <int H>
+template <int H, int CELL>
 static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
   constexpr int CL = H / 32;
   const int clusters = (a.N + NB - 1) / NB;
@@ -399,12 +427,12 @@ static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
   cfg.numAttrs = 1;
   cudaError_t e;
   if (!backward) {
-    auto kern = lstm_fwd_kernel<H>;
+    auto kern = lstm_fwd_kernel<H, CELL>;
     if (CL > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     cfg.dynamicSmemBytes = 0;
     e = cudaLaunchKernelEx(&cfg, kern, a);
   } else {
-    auto kern = lstm_bwd_kernel<H>;
+    auto kern = lstm_bwd_kernel<H, CELL>;
     const size_t smem = (size_t)2 * CL * 32 * NB * 4 + (size_t)3 * NB * 136 * 2 + (size_t)2 * 3 * NB * 36 * 4 + (size_t)2 * NB * 136 * 2;
     if (CL > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -431,13 +459,23 @@ static int fill_lstm(LstmArgs& a, const CpcLstm* d) {
   return CPC_OK;
 }
 
-static int dispatch_lstm(const LstmArgs& a, int H, bool backward, cudaStream_t stream) {
+template <int CELL>
+static int dispatch_h(const LstmArgs& a, int H, bool backward, cudaStream_t stream) {
   switch (H) {
-    case 32: return launch_lstm<32>(a, backward, stream);
-    case 64: return launch_lstm<64>(a, backward, stream);
-    case 128: return launch_lstm<128>(a, backward, stream);
-    case 256: return launch_lstm<256>(a, backward, stream);
-    case 512: return launch_lstm<512>(a, backward, stream);
+    case 32: return launch_lstm<32, CELL>(a, backward, stream);
+    case 64: return launch_lstm<64, CELL>(a, backward, stream);
+    case 128: return launch_lstm<128, CELL>(a, backward, stream);
+    case 256: return launch_lstm<256, CELL>(a, backward, stream);
+    case 512: return launch_lstm<512, CELL>(a, backward, stream);
+    default: return CPC_ERR_UNSUPPORTED;
+  }
+}
+
+static int dispatch_lstm(const LstmArgs& a, int H, int cell, bool backward, cudaStream_t stream) {
+  switch (cell) {
+    case CELL_LSTM: return dispatch_h<CELL_LSTM>(a, H, backward, stream);
+    case CELL_GRU: return dispatch_h<CELL_GRU>(a, H, backward, stream);
+    case CELL_RNN: return dispatch_h<CELL_RNN>(a, H, backward, stream);
     default: return CPC_ERR_UNSUPPORTED;
   }
 }
@@ -447,7 +485,7 @@ extern "C" int cpc_lstm_fwd(const CpcLstm* d, void* stream_) {
   int rc = fill_lstm(a, d);
   if (rc != CPC_OK) return rc;
   if (a.gx == nullptr) return CPC_ERR_ARG;
-  return dispatch_lstm(a, d->H, false, static_cast<cudaStream_t>(stream_));
+  return dispatch_lstm(a, d->H, d->cell, false, static_cast<cudaStream_t>(stream_));
 }
 
 extern "C" int cpc_lstm_bwd(const CpcLstm* d, void* stream_) {
@@ -455,5 +493,5 @@ extern "C" int cpc_lstm_bwd(const CpcLstm* d, void* stream_) {
   int rc = fill_lstm(a, d);
   if (rc != CPC_OK) return rc;
   if (a.gates == nullptr || a.c_all == nullptr || a.dout == nullptr || a.dgates == nullptr) return CPC_ERR_ARG;
-  return dispatch_lstm(a, d->H, true, static_cast<cudaStream_t>(stream_));
+  return dispatch_lstm(a, d->H, d->cell, true, static_cast<cudaStream_t>(stream_));
 }

@@ -254,9 +254,13 @@ def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld, dlo
     _run("cpc_nce_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=None, c_all=None, h_n=None, c_n=None):
+CELL = {"LSTM": 0, "GRU": 1, "RNN": 2}
+
+
+def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=None, c_all=None, h_n=None, c_n=None,
+             cell="LSTM"):
     d = _lib.Lstm()
-    d.N, d.S, d.H = N, S, H
+    d.N, d.S, d.H, d.cell = N, S, H, CELL[cell]
     d.gx, d.w_hh, d.h0, d.c0 = _dp(gx), _dp(w_hh), _dp(h0), _dp(c0)
     d.h_pad, d.out, d.gates, d.c_all, d.h_n, d.c_n = _dp(h_pad), _dp(out), _dp(gates), _dp(c_all), _dp(h_n), _dp(c_n)
     if PROFILE is not None:
@@ -264,9 +268,10 @@ def lstm_fwd(gx, w_hh, N, S, H, h0=None, c0=None, h_pad=None, out=None, gates=No
     _run("cpc_lstm_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H, c0=None):
+def lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H, c0=None, h0=None, cell="LSTM"):
     d = _lib.Lstm()
-    d.N, d.S, d.H = N, S, H
+    d.N, d.S, d.H, d.cell = N, S, H, CELL[cell]
+    d.h0 = _dp(h0)
     d.w_hh, d.c0, d.gates, d.c_all, d.dout, d.dgates = _dp(w_hh), _dp(c0), _dp(gates), _dp(c_all), _dp(dout), _dp(dgates)
     if PROFILE is not None:
         set_work(kind="latency", flops=2.0 * N * S * H * 4 * H, steps=S)

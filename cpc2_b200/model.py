@@ -295,74 +295,101 @@ class CPCAR(nn.Module):
             params += [getattr(self.baseNet, f"{n}_l{l}") for n in ("weight_ih", "weight_hh", "bias_ih", "bias_hh")]
         return params
 
+    def _cell(self):
+        return "LSTM" if isinstance(self.baseNet, nn.LSTM) else "GRU" if isinstance(self.baseNet, nn.GRU) else "RNN"
+
     def prefetch(self):
         """bf16 shadows of the recurrent weights and the summed bias, issued on a side stream at the top of the
         step (train.prefetchWeights) so they overlap the encoder."""
         params = self._rnn_params()
-        bufs = _alloc_rnn_shadows(params)
+        cell = self._cell()
+        bufs = _alloc_rnn_shadows(params, cell)
         with ops.side(4):
-            _cast_rnn_weights([q.detach() for q in params], bufs)
+            _cast_rnn_weights([q.detach() for q in params], bufs, cell)
         self._pref = ops.Prefetched(params, bufs, 4)
 
     def forward(self, x):
         ops.require_cuda(x)
-        if not isinstance(self.baseNet, nn.LSTM):
-            raise NotImplementedError("cpc2_b200: only arMode='LSTM' (and 'transformer') have sm_100a kernels so far")
+        cell = self._cell()
+        if cell == "RNN" and self.baseNet.nonlinearity != "tanh":
+            raise NotImplementedError("cpc2_b200: nn.RNN with relu nonlinearity is never built by the reference")
         if self.reverse:
             x = torch.flip(x, [1])
         nl = self.baseNet.num_layers
         params = self._rnn_params()
         h0 = c0 = None
         if self.hidden is not None:
-            h0, c0 = self.hidden
+            if cell == "LSTM":
+                h0, c0 = self.hidden
+            else:
+                h0 = self.hidden
         pref, self._pref = getattr(self, "_pref", None), None
-        out, h_n, c_n = _LstmFn.apply(x, h0, c0, nl, pref, *params)
+        out, h_n, c_n = _RecurrentFn.apply(x, h0, c0, nl, pref, cell, *params)
         if self.keepHidden:
-            self.hidden = (h_n.detach(), c_n.detach())
+            self.hidden = (h_n.detach(), c_n.detach()) if cell == "LSTM" else h_n.detach()
         if self.reverse:
             out = torch.flip(out, [1])
         return out
 
 
-def _alloc_rnn_shadows(params):
-    """Per layer: (w_ih bf16, w_hh bf16, b_ih + b_hh fp32), allocated on the current stream."""
+_GATES = {"LSTM": 4, "GRU": 3, "RNN": 1}
+
+
+def _alloc_rnn_shadows(params, cell="LSTM"):
+    """Per layer: (w_ih bf16 [4H,Kin], w_hh bf16 [4H,H], bias fp32 [4H]) in the kernel's four-slot layout
+    (include/cpc_b200.h, CpcLstm), allocated on the current stream.  GRU / RNN leave some slots zero."""
     out = []
     for l in range(len(params) // 4):
-        w_ih, w_hh, b_ih, _ = params[4 * l:4 * l + 4]
-        out.append((torch.empty(w_ih.shape, device=w_ih.device, dtype=BF16),
-                    torch.empty(w_hh.shape, device=w_hh.device, dtype=BF16), torch.empty_like(b_ih)))
+        w_ih, w_hh = params[4 * l:4 * l + 2]
+        H, dev = w_hh.shape[1], w_ih.device
+        mk = torch.empty if cell == "LSTM" else torch.zeros
+        out.append((mk(4 * H, w_ih.shape[1], device=dev, dtype=BF16), mk(4 * H, H, device=dev, dtype=BF16),
+                    mk(4 * H, device=dev, dtype=torch.float32)))
     return out
 
 
-def _cast_rnn_weights(p, bufs):
+def _cast_rnn_weights(p, bufs, cell="LSTM"):
     for l, (w_ih16, w_hh16, bias) in enumerate(bufs):
         w_ih, w_hh, b_ih, b_hh = p[4 * l:4 * l + 4]
-        K.cast_bf16(w_ih.contiguous(), w_ih16)
-        K.cast_bf16(w_hh.contiguous(), w_hh16)
-        torch.add(b_ih, b_hh, out=bias)
+        H = w_hh.shape[1]
+        w_ih, w_hh = w_ih.contiguous(), w_hh.contiguous()
+        if cell == "LSTM":
+            K.cast_bf16(w_ih, w_ih16)
+            K.cast_bf16(w_hh, w_hh16)
+            torch.add(b_ih, b_hh, out=bias)
+        elif cell == "GRU":  # slots (r, z, n_x, hn): cpc_b200.h
+            K.cast_bf16(w_ih, w_ih16[:3 * H])
+            K.cast_bf16(w_hh[:2 * H], w_hh16[:2 * H])
+            K.cast_bf16(w_hh[2 * H:], w_hh16[3 * H:])
+            torch.add(b_ih[:2 * H], b_hh[:2 * H], out=bias[:2 * H])
+            bias[2 * H:3 * H].copy_(b_ih[2 * H:])
+            bias[3 * H:].copy_(b_hh[2 * H:])
+        else:
+            K.cast_bf16(w_ih, w_ih16[:H])
+            K.cast_bf16(w_hh, w_hh16[:H])
+            torch.add(b_ih, b_hh, out=bias[:H])
 
 
-class _LstmFn(torch.autograd.Function):
-    """x [N,S,C] fp32 -> out [N,S,H] fp32 (+ final h, c [layers,N,H])."""
+class _RecurrentFn(torch.autograd.Function):
+    """x [N,S,C] fp32 -> out [N,S,H] fp32 (+ final h, c [layers,N,H]) for nn.LSTM / nn.GRU / nn.RNN(tanh)."""
 
     @staticmethod
-    def forward(ctx, x, h0, c0, nl, pref, *params):
+    def forward(ctx, x, h0, c0, nl, pref, cell, *params):
         N, S, Cin = x.shape
         dev = x.device
         p = [t.detach() for t in params]
         H = p[1].shape[1]
         shadows = pref.take(list(params)) if pref is not None else None
         if shadows is None:
-            shadows = _alloc_rnn_shadows(p)
-            _cast_rnn_weights(p, shadows)
+            shadows = _alloc_rnn_shadows(p, cell)
+            _cast_rnn_weights(p, shadows, cell)
         inp = K.cast_bf16(x.detach().contiguous().float()).view(N * S, Cin)
         saved = []
         h_ns, c_ns = [], []
         out = None
         prev_pad = None  # h_pad of the previous layer (input of layers > 0)
         for l in range(nl):
-            w_ih, w_hh, b_ih, b_hh = p[4 * l:4 * l + 4]
-            Kin = w_ih.shape[1]
+            Kin = p[4 * l].shape[1]
             w_ih16, w_hh16, bias = shadows[l]
             gx = torch.empty(N * S, 4 * H, device=dev)
             if l == 0:
@@ -379,23 +406,24 @@ class _LstmFn(torch.autograd.Function):
             h0l = h0[l].contiguous().float() if h0 is not None else None
             c0l = c0[l].contiguous().float() if c0 is not None else None
             K.lstm_fwd(gx, w_hh16, N, S, H, h0=h0l, c0=c0l, h_pad=h_pad, out=out, gates=gates, c_all=c_all,
-                       h_n=h_n, c_n=c_n)
-            saved.append((inp if l == 0 else prev_pad, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l))
+                       h_n=h_n, c_n=c_n, cell=cell)
+            saved.append((inp if l == 0 else prev_pad, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l, h0l))
             h_ns.append(h_n)
             c_ns.append(c_n)
             prev_pad = h_pad
         ctx.saved = saved
-        ctx.dims = (N, S, Cin, H, nl)
+        ctx.dims = (N, S, Cin, H, nl, cell)
         return out, torch.stack(h_ns), torch.stack(c_ns)
 
     @staticmethod
     def backward(ctx, dout, dh_n, dc_n):
-        N, S, Cin, H, nl = ctx.dims
+        N, S, Cin, H, nl, cell = ctx.dims
         dev = dout.device
+        G = _GATES[cell]
         d = dout.contiguous().float()
         grads = [None] * (4 * nl)
         sizes = []
-        for l in range(nl):
+        for l in range(nl):  # four-slot (padded) gradient spans; the returned gradients are their leading G*H rows
             sizes += [4 * H * ctx.saved[l][1], 4 * H * H, 4 * H, 4 * H]
         gflat = torch.zeros(sum(sizes), device=dev)
         gv, off = [], 0
@@ -404,22 +432,28 @@ class _LstmFn(torch.autograd.Function):
             off += n_
         keep = []
         for l in range(nl - 1, -1, -1):
-            x_in, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l = ctx.saved[l]
+            x_in, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l, h0l = ctx.saved[l]
             dgates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
-            K.lstm_bwd(w_hh16, gates, c_all, d, dgates, N, S, H, c0=c0l)
+            K.lstm_bwd(w_hh16, gates, c_all, d, dgates, N, S, H, c0=c0l, h0=h0l, cell=cell)
             dg2 = dgates.view(N * S, 4 * H)
             dw_ih, dw_hh = gv[4 * l].view(4 * H, Kin), gv[4 * l + 1].view(4 * H, H)
             dbias, dbias2 = gv[4 * l + 2], gv[4 * l + 3]
             dx = torch.empty(N * S, Kin, device=dev)
             with ops.side(1):
                 K.colsum(dg2, dbias, N * S, 4 * H, 4 * H)
-                dbias2.copy_(dbias)
+                if cell == "GRU":  # b_hh = (r, z, hn) slots 0, 1, 3
+                    dbias2[:2 * H].copy_(dbias[:2 * H])
+                    dbias2[2 * H:3 * H].copy_(dbias[3 * H:])
+                else:
+                    dbias2.copy_(dbias)
             with ops.side(0):
                 # dW_hh = sum_{n,t} dgates[n,t]^T h_{t-1}[n]  (slabs = sequences, h_pad row t is h_{t-1})
                 Ag = K.View(dgates, 4 * H, S, N, 4 * H, S * 4 * H, major=1)
                 Bh = K.View(h_pad, H, S + 1, N, H, (S + 1) * H, major=1)
                 K.gemm(Ag, Bh, 4 * H, H, N * S, k_per_slab=S, k_splits=ops.auto_splits(4 * H, H, N * S, 1, S),
                        out_f32=dw_hh, accumulate=True)
+                if cell == "GRU":  # W_hh rows (r, z, n) <- slots 0, 1, 3
+                    dw_hh[2 * H:3 * H].copy_(dw_hh[3 * H:])
                 # dW_ih = dgates^T . input
                 if l == 0:
                     K.gemm(K.mnmajor(dg2), K.mnmajor(x_in), 4 * H, Kin, N * S,
@@ -429,14 +463,14 @@ class _LstmFn(torch.autograd.Function):
                     K.gemm(Ag, Bx, 4 * H, Kin, N * S, k_per_slab=S,
                            k_splits=ops.auto_splits(4 * H, Kin, N * S, 1, S), out_f32=dw_ih, accumulate=True)
             keep.append(dgates)
-            grads[4 * l:4 * l + 4] = [dw_ih, dw_hh, dbias, dbias2]
-            # dx = dgates . W_ih
+            grads[4 * l:4 * l + 4] = [dw_ih[:G * H], dw_hh[:G * H], dbias[:G * H], dbias2[:G * H]]
+            # dx = dgates . W_ih (zero slots of the padded W_ih contribute nothing)
             K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
             d = dx.view(N, S, Kin)
         ops.join()
         del keep
         ops.grad_ready("ar", gflat)
-        return (d, None, None, None, None, *grads)
+        return (d, None, None, None, None, None, *grads)
 
 
 class CPCModel(nn.Module):

@@ -171,14 +171,19 @@ int cpc_nce_fwd(const CpcNce* desc, void* stream);
 int cpc_nce_bwd(const CpcNce* desc, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
- * LSTM recurrence (nn.LSTM as built at cpc/model.py:171-173, gate order i,f,g,o), H in {32,64,128,256,512}.
- * gx fp32 [N,S,4H] = x.W_ih^T + b_ih + b_hh (a cpc_gemm_bf16 call); w_hh bf16 [4H,H].
- * fwd writes out fp32 [N,S,H], h_pad bf16 [N,S+1,H] (row 0 = h0), gates bf16 [N,S,4H] (post-activation),
- * c_all fp32 [N,S,H], h_n / c_n fp32 [N,H] (any may be null).  bwd consumes dout fp32 [N,S,H] and writes
- * dgates bf16 [N,S,4H] (gradient w.r.t. the gate pre-activations); dW / dx follow as GEMMs.
+ * Recurrence of CPCAR's nn.LSTM / nn.GRU / nn.RNN (cpc/model.py:171-179,196), H in {32,64,128,256,512}.
+ * cell = 0 LSTM (gate slots i,f,g,o), 1 GRU, 2 tanh RNN.  Every cell uses FOUR gate slots of width H:
+ *   LSTM: gx fp32 [N,S,4H] = x.W_ih^T + b_ih + b_hh, w_hh bf16 [4H,H] as torch stores them;
+ *   GRU : slots (r, z, n_x, hn): gx = (W_ir x + b_ir + b_hr | W_iz x + b_iz + b_hz | W_in x + b_in | b_hn),
+ *         w_hh = (W_hr | W_hz | 0 | W_hn); n = tanh(n_x + r * hn), h = (1-z) n + z h_prev;
+ *   RNN : slot 0 only (the other three slots of gx / w_hh are zero).
+ * fwd writes out fp32 [N,S,H], h_pad bf16 [N,S+1,H] (row 0 = h0), gates bf16 [N,S,4H] (post-activation;
+ * GRU slot 3 = W_hn h + b_hn), c_all fp32 [N,S,H] (LSTM: cell states; GRU/RNN: h in fp32), h_n / c_n fp32 [N,H]
+ * (any may be null).  bwd consumes dout fp32 [N,S,H] and writes dgates bf16 [N,S,4H], the gradient w.r.t. the
+ * four slot pre-activations (GRU: d r, d z, d n_x, d hn = d n_x * r); dW / dx follow as GEMMs.
  */
 typedef struct {
-  int N, S, H;
+  int N, S, H, cell;
   const void* gx; const void* w_hh; const void* h0; const void* c0;
   void* h_pad; void* out; void* gates; void* c_all; void* h_n; void* c_n;
   const void* dout; void* dgates;

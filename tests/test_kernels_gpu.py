@@ -317,6 +317,37 @@ def test_lstm_recurrence_fwd_bwd(K, H, N, S):
     close(dx, xr.grad, 5e-2, 5e-2 * xr.grad.abs().max().item(), "lstm dx")
 
 
+@pytest.mark.parametrize("cell,H,Cin,N,S,nl", [("GRU", 64, 32, 5, 20, 2), ("GRU", 256, 256, 16, 128, 1), ("RNN", 32, 64, 3, 9, 2),
+                                               ("LSTM", 64, 32, 9, 11, 2), ("GRU", 512, 128, 4, 6, 1)])
+def test_cpcar_module_matches_torch_rnn(K, cell, H, Cin, N, S, nl):
+    """cpc2_b200.model.CPCAR (cluster kernels, four-slot GRU / RNN layout) against torch's own nn.GRU / nn.RNN /
+    nn.LSTM on identical parameters: outputs, carried hidden state (keepHidden, cpc/model.py:196-201) and all
+    parameter / input gradients."""
+    from cpc2_b200.model import CPCAR
+    torch.manual_seed(11)
+    ar = CPCAR(Cin, H, True, nl, mode=cell).cuda()
+    ref = {"GRU": torch.nn.GRU, "RNN": torch.nn.RNN, "LSTM": torch.nn.LSTM}[cell](Cin, H, num_layers=nl, batch_first=True).cuda()
+    ref.load_state_dict(ar.baseNet.state_dict())
+    x1 = torch.randn(N, S, Cin, device="cuda")
+    x2 = torch.randn(N, S, Cin, device="cuda", requires_grad=True)
+    x2r = x2.detach().clone().requires_grad_(True)
+    with torch.no_grad():
+        o1 = ar(x1)
+        r1, hid = ref(x1)
+    close(o1, r1, 2e-2, 2e-2, f"{cell} out (first chunk)")
+    o2 = ar(x2)          # starts from the kept hidden state
+    r2, _ = ref(x2r, hid)
+    close(o2, r2, 2e-2, 2e-2, f"{cell} out (second chunk, carried state)")
+    dout = torch.randn_like(r2)
+    o2.backward(dout)
+    r2.backward(dout)
+    assert cos(x2.grad, x2r.grad) > 0.998, cos(x2.grad, x2r.grad)
+    for (n, g), (_, gr) in zip(ar.baseNet.named_parameters(), ref.named_parameters()):
+        assert g.grad.shape == gr.grad.shape, n
+        assert cos(g.grad, gr.grad) > 0.998, (n, cos(g.grad, gr.grad))
+        close(g.grad, gr.grad, 5e-2, 5e-2 * gr.grad.abs().max().item(), f"{cell} d{n}")
+
+
 # ------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("G,Bt,Hh,S,dk,relpos", [(2, 3, 8, 116, 32, True), (1, 2, 8, 12, 4, True),
                                                  (1, 2, 4, 128, 64, False), (1, 1, 8, 244, 64, True)])
