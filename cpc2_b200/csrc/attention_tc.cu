@@ -1,17 +1,22 @@
-// Tensor-core path of the causal relative-position attention (cpc/transformers.py:52-70), S <= 128, dk in {32, 64}:
-// the shapes of the default CPC step (12 prediction heads x 8 windows x 8 attention heads, S = 116, dk = 32) and
-// of the transformer AR (S = 128).  One CTA per (head group, window, attention head), four warps; each warp owns
-// 16-row query blocks {w, 7-w} (causal work is balanced), all products run on mma.sync.m16n8k16 bf16 with
-// operands fetched by ldmatrix from padded (conflict-free) shared-memory tiles:
+// Tensor-core path of the causal relative-position attention (cpc/transformers.py:52-70), S <= 256, dk in {32, 64}:
+// the shapes of the default CPC step (12 prediction heads x 8 windows x 8 attention heads, S = 116, dk = 32), of
+// the transformer AR (S = 128) and of the long-window sizing (S = 244 / 256, dk = 64).  One CTA per (head group,
+// window, attention head), four warps; the sequence is padded to SP in {128, 256} and cut in 16-row blocks that
+// are dealt to the warps in causal-balanced pairs {4q + w, SP/16 - 1 - 4q - w}; all products run on
+// mma.sync.m16n8k16 bf16 with operands fetched by ldmatrix from padded (conflict-free) shared-memory tiles that
+// cp.async fills while the fp32 Krel slice is converted and the row statistics D are computed.
 //
 //   forward   R = Q.Krel (only the r >= S-16-i0 columns a block can address), staged per warp in shared memory;
 //             scores = (Q.K^T + skew(R)) * scale with skew(R)[i,j] = R[i, S-1-i+j]  -- the reference's
 //             cat/view "skew" is an index shift here; softmax in registers (quad shuffles); P (bf16) is kept
 //             for the backward; O = dropout(P).V with the score accumulators re-used as A fragments.
 //   backward  row pass (query blocks): dP = dO.V^T, dS = P o (dP - D) * scale, dQ = dS.K + unskew(dS).Krel^T,
-//             dKrel += Q^T.unskew(dS) (shared-memory fp32 accumulation, one red.global per element per CTA);
-//             column pass (key blocks, transposed tiles): dV = P~^T.dO, dK = dS^T.Q.
-//             Both passes recompute dP / dS from registers, so nothing but P ever round-trips through memory.
+//             dKrel += Q^T.unskew(dS);
+//             column pass (key blocks): the same [i][j] tiles are recomputed, P~ and dS are transposed in
+//             registers (movmatrix) into the A fragments of dV = P~^T.dO and dK = dS^T.Q.
+//             Every P element a pass needs is fetched into registers BEFORE its loop (one exposed global
+//             latency per pass instead of one per 16-key step: the kernel was latency-bound, ncu r01), and
+//             nothing but P ever round-trips through memory.
 // Dropout masks are regenerated from a counter hash of the element index in both directions.
 // Larger S / odd head sizes fall back to the CUDA-core kernels of attention.cu.
 #include <cstdlib>
@@ -24,9 +29,9 @@ namespace cpc {
 
 namespace {
 
-constexpr int SP = 128;      // padded sequence length of the shared-memory tiles
-constexpr int PS = SP + 8;   // pitch (elements) of [.][SP] tiles: 272 B rows, conflict-free for ldmatrix
-constexpr int ATT_THREADS = 128;
+// warps per CTA: 8 at SP = 128 (one row block + one column block each, 2 CTAs/SM -> 16 warps/SM: the kernels are
+// bound by dependent-issue latency, not by the tensor pipe), 4 at SP = 256 (shared memory for the per-warp stage)
+__host__ __device__ constexpr int att_warps(int SP) { return SP == 128 ? 8 : 4; }
 
 struct DropCfg {
   uint32_t seed_lo, seed_hi, thresh;
@@ -38,33 +43,64 @@ __device__ __forceinline__ DropCfg make_drop(const AttnArgs& a) {
     const unsigned long long seed = a.rng[0] + a.rng[1] * 0x632BE59BD9B4E019ull;
     d.seed_lo = static_cast<uint32_t>(seed);
     d.seed_hi = static_cast<uint32_t>(seed >> 32) + a.site * 0x85EBCA77u;
-    d.thresh = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    d.thresh = static_cast<uint32_t>(fminf(a.drop_p, 0.9999f) * 65536.0f);  // 16-bit draws, two per hash
     d.scale = 1.f / (1.f - a.drop_p);
   }
   return d;
 }
-__device__ __forceinline__ bool keep_elem(const DropCfg& d, long long e) {
-  return rng_pair_u16(d.seed_lo, d.seed_hi, static_cast<unsigned long long>(e)) >= d.thresh;
+// keep flags of the element pair (row, j), (row, j + 1), j even: one hash, two 16-bit draws.  `row` is the global
+// row index ((group, window, head), i); the pair index is unique per (row, j / 2) for any S <= 512.
+__device__ __forceinline__ void keep_pair(const DropCfg& d, long long row, int j, bool& k0, bool& k1) {
+  const uint32_t h = rng_pair_u16(d.seed_lo, d.seed_hi, static_cast<unsigned long long>(row) * 256ull + (j >> 1));
+  k0 = (h & 0xFFFFu) >= d.thresh;
+  k1 = (h >> 16) >= d.thresh;
 }
 
-// rows [0, S) of a [S][dk] slice (row stride `ld` elements) -> shared [SP][PD] bf16, rows >= S zero
-template <int DK>
-__device__ __forceinline__ void load_rows(__nv_bfloat16* dst, const __nv_bfloat16* src, long long ld, int S) {
+// rows [0, S) of a [S][dk] slice (row stride `ld` elements) -> shared [SP][PD] bf16 by cp.async, rows >= S zero.
+// The caller commits / waits.
+template <int DK, int SP, int ATT_THREADS>
+__device__ __forceinline__ void load_rows_async(__nv_bfloat16* dst, const __nv_bfloat16* src, long long ld, int S) {
   constexpr int PD = DK + 8, CH = DK / 8;
+#pragma unroll 4
   for (int i = threadIdx.x; i < SP * CH; i += ATT_THREADS) {
     const int s = i / CH, ch = i % CH;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (s < S) v = *reinterpret_cast<const uint4*>(src + (long long)s * ld + ch * 8);
-    *reinterpret_cast<uint4*>(dst + s * PD + ch * 8) = v;
+    if (s < S) cp_async_16(dst + s * PD + ch * 8, src + (long long)s * ld + ch * 8);
+    else *reinterpret_cast<uint4*>(dst + s * PD + ch * 8) = make_uint4(0u, 0u, 0u, 0u);
   }
+}
+
+// the 16-row block warp `w` owns in pass `p` (NB blocks, two per (warp, q): one short, one long causal row)
+template <int NB, int NW>
+__device__ __forceinline__ int block_of(int warp, int p) {
+  const int q = p >> 1;
+  return (p & 1) ? NB - 1 - NW * q - warp : NW * q + warp;
+}
+
+// P[e], P[e+1] (bf16, probabilities before dropout) as one packed register; `second` = element e+1 is inside
+// the causal triangle.  The paired load needs an even S (4-byte alignment of every row start).
+__device__ __forceinline__ uint32_t load_p_pair(const __nv_bfloat16* probs, long long e, bool pair_ok, bool second) {
+  if (pair_ok && second) return *reinterpret_cast<const uint32_t*>(probs + e);
+  uint32_t lo = *reinterpret_cast<const unsigned short*>(probs + e);
+  if (second) lo |= static_cast<uint32_t>(*reinterpret_cast<const unsigned short*>(probs + e + 1)) << 16;
+  return lo;
+}
+__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+
+// transpose of an 8x8 b16 matrix held one row per quad (the C / A fragment layout of mma.m16n8k16)
+__device__ __forceinline__ uint32_t movmatrix_t(uint32_t v) {
+  uint32_t r;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
 }
 
 }  // namespace
 
 // ================================================================================================ forward
-template <int DK>
-__global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs a) {
-  constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, RP = SP + 8;
+template <int DK, int SP, int NW>
+__global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) {
+  constexpr int ATT_THREADS = NW * 32, ATT_WARPS = NW;
+  constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, RP = SP + 8, NB = SP / 16, NJ = SP / 8;
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(smem_dyn);
   __nv_bfloat16* Ks = Qs + SP * PD;
@@ -77,25 +113,29 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
   const int g = lane >> 2, t = lane & 3;
   const bool rel = a.krel != nullptr;
   const __nv_bfloat16* base = a.qkv + (long long)grp * a.gs_qkv + (long long)b * S * 3 * d + h * DK;
-  load_rows<DK>(Qs, base, 3 * d, S);
-  load_rows<DK>(Ks, base + d, 3 * d, S);
-  load_rows<DK>(Vs, base + 2 * d, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(Qs, base, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(Ks, base + d, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(Vs, base + 2 * d, 3 * d, S);
+  cp_async_commit();
   if (rel) {
     const float* kr = a.krel + (long long)grp * DK * S;
+#pragma unroll 8
     for (int i = threadIdx.x; i < DK * SP; i += ATT_THREADS) {
       const int c = i / SP, r = i % SP;
       KrT[r * PD + c] = __float2bfloat16(r < S ? kr[c * S + r] : 0.f);
     }
   }
+  cp_async_wait<0>();
   __syncthreads();
   const DropCfg drop = make_drop(a);
-  const long long pbase = (((long long)grp * a.Bt + b) * a.Hh + h) * S * S;
+  const long long rbase = (((long long)grp * a.Bt + b) * a.Hh + h) * S;  // global row index of query 0
+  const long long pbase = rbase * S;
   float* Rs = Rs_all + warp * 16 * RP;
   const int ntile_s = (S + 7) >> 3;
   const bool pair_ok = (S & 1) == 0;
 
-  for (int pass = 0; pass < 2; ++pass) {
-    const int rb = pass ? 7 - warp : warp;
+  for (int pass = 0; pass < NB / ATT_WARPS; ++pass) {
+    const int rb = block_of<NB, ATT_WARPS>(warp, pass);
     const int i0 = rb * 16;
     if (i0 >= S) continue;
     uint32_t aq[KS][4];
@@ -117,9 +157,9 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
       __syncwarp();
     }
     const int njt = min(2 * rb + 2, ntile_s);
-    float sc[16][4];
+    float sc[NJ][4];
 #pragma unroll
-    for (int jt = 0; jt < 16; ++jt) {
+    for (int jt = 0; jt < NJ; ++jt) {
       if (jt < njt) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -144,7 +184,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
     // softmax over each row (a row lives in the 4 lanes of a quad)
     float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
-    for (int jt = 0; jt < 16; ++jt)
+    for (int jt = 0; jt < NJ; ++jt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) mx[e >> 1] = fmaxf(mx[e >> 1], sc[jt][e]);
     float sum[2] = {0.f, 0.f};
@@ -155,7 +195,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
       if (mx[r] == -INFINITY) mx[r] = 0.f;  // padding row
     }
 #pragma unroll
-    for (int jt = 0; jt < 16; ++jt)
+    for (int jt = 0; jt < NJ; ++jt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const float p = __expf(sc[jt][e] - mx[e >> 1]);
@@ -173,7 +213,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
     // below): the backward's D_i = dO_i.O_i must equal sum_j P_ij dP_ij for the UNROUNDED P, otherwise the
     // rounding error of P, weighted by the common component of dP, leaks into every dS of the row.
 #pragma unroll
-    for (int jt = 0; jt < 16; ++jt) {
+    for (int jt = 0; jt < NJ; ++jt) {
       if (jt < njt) {
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
@@ -190,8 +230,10 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
               }
             }
             if (drop.thresh != 0) {
-              p0 = keep_elem(drop, e) ? p0 * drop.scale : 0.f;
-              p1 = keep_elem(drop, e + 1) ? p1 * drop.scale : 0.f;
+              bool k0, k1;
+              keep_pair(drop, rbase + i, j, k0, k1);
+              p0 = k0 ? p0 * drop.scale : 0.f;
+              p1 = k1 ? p1 * drop.scale : 0.f;
             }
           }
           sc[jt][2 * r] = p0;
@@ -206,7 +248,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
 #pragma unroll
       for (int e = 0; e < 4; ++e) o[nt][e] = 0.f;
 #pragma unroll
-    for (int kk = 0; kk < 8; ++kk) {
+    for (int kk = 0; kk < NB; ++kk) {
       if (2 * kk < njt) {
         uint32_t ap[4], al[4];
 #pragma unroll
@@ -240,18 +282,22 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_tc_kernel(const AttnArgs
 }
 
 // ================================================================================================ backward
-template <int DK>
-__global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs a) {
-  constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8;
+// SMEM_DKR: dKrel partial sums of the CTA are accumulated in shared memory and flushed once (SP = 128); the
+// SP = 256 instantiation has no room for that tile and reduces straight into global memory.
+template <int DK, int SP>
+__global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const AttnArgs a) {
+  constexpr int ATT_WARPS = att_warps(SP), ATT_THREADS = ATT_WARPS * 32;
+  constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, PS = SP + 8, NB = SP / 16, NJ = SP / 8;
+  constexpr bool SMEM_DKR = SP == 128;
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(smem_dyn);
   __nv_bfloat16* Ks = Qs + SP * PD;
   __nv_bfloat16* Vs = Ks + SP * PD;
   __nv_bfloat16* dOs = Vs + SP * PD;
-  __nv_bfloat16* Krs = dOs + SP * PD;                              // Krel [c][r] bf16, pitch PS
-  __nv_bfloat16* stage_all = Krs + DK * PS;                        // per warp unskew(dS) [16][PS]
-  float* Dsm = reinterpret_cast<float*>(stage_all + 4 * 16 * PS);  // [SP]
-  float* dKr = Dsm + SP;                                           // [DK][SP] fp32 accumulator
+  __nv_bfloat16* Krs = dOs + SP * PD;                                      // Krel [c][r] bf16, pitch PS
+  __nv_bfloat16* stage_all = Krs + DK * PS;                                // per warp unskew(dS) [16][PS]
+  float* Dsm = reinterpret_cast<float*>(stage_all + ATT_WARPS * 16 * PS);  // [SP]
+  float* dKr = Dsm + SP;                                                   // [DK][SP] fp32 accumulator (SMEM_DKR)
   const int S = a.S, d = a.d;
   const int h = blockIdx.x, b = blockIdx.y, grp = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -259,49 +305,70 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
   const bool rel = a.krel != nullptr;
   const __nv_bfloat16* base = a.qkv + (long long)grp * a.gs_qkv + (long long)b * S * 3 * d + h * DK;
   const long long obase = (long long)grp * a.gs_out + (long long)b * S * d + h * DK;
-  load_rows<DK>(Qs, base, 3 * d, S);
-  load_rows<DK>(Ks, base + d, 3 * d, S);
-  load_rows<DK>(Vs, base + 2 * d, 3 * d, S);
-  load_rows<DK>(dOs, a.dout + obase, d, S);
-  if (rel) {
-    const float* kr = a.krel + (long long)grp * DK * S;
-    for (int i = threadIdx.x; i < DK * SP; i += ATT_THREADS) {
-      const int c = i / SP, r = i % SP;
-      Krs[c * PS + r] = __float2bfloat16(r < S ? kr[c * S + r] : 0.f);
-      dKr[i] = 0.f;
-    }
-  }
-  __syncthreads();
-  // D_i = dO_i . O_i  (= sum_j P~_ij dP~_ij)
+  load_rows_async<DK, SP, ATT_THREADS>(Qs, base, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(Ks, base + d, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(Vs, base + 2 * d, 3 * d, S);
+  load_rows_async<DK, SP, ATT_THREADS>(dOs, a.dout + obase, d, S);
+  cp_async_commit();
+  // D_i = dO_i . O_i  (= sum_j P~_ij dP~_ij), straight from global memory while the tiles are in flight
   for (int i = threadIdx.x; i < SP; i += ATT_THREADS) {
     float acc = 0.f;
     if (i < S) {
       const __nv_bfloat16* orow = a.out + obase + (long long)i * d;
+      const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
+      uint4 ov[DK / 8], dv[DK / 8];
 #pragma unroll
       for (int ch = 0; ch < DK / 8; ++ch) {
-        const uint4 ov = *reinterpret_cast<const uint4*>(orow + ch * 8);
-        const uint4 dv = *reinterpret_cast<const uint4*>(dOs + i * PD + ch * 8);
-        const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
-        const __nv_bfloat162* d2 = reinterpret_cast<const __nv_bfloat162*>(&dv);
+        ov[ch] = *reinterpret_cast<const uint4*>(orow + ch * 8);
+        dv[ch] = *reinterpret_cast<const uint4*>(drow + ch * 8);
+      }
 #pragma unroll
-        for (int k = 0; k < 4; ++k) acc += __low2float(o2[k]) * __low2float(d2[k]) + __high2float(o2[k]) * __high2float(d2[k]);
+      for (int ch = 0; ch < DK / 8; ++ch) {
+        const uint32_t* o2 = reinterpret_cast<const uint32_t*>(&ov[ch]);
+        const uint32_t* d2 = reinterpret_cast<const uint32_t*>(&dv[ch]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc += bf16lo(o2[k]) * bf16lo(d2[k]) + bf16hi(o2[k]) * bf16hi(d2[k]);
       }
     }
     Dsm[i] = acc;
   }
+  if (rel) {
+    const float* kr = a.krel + (long long)grp * DK * S;
+#pragma unroll 8
+    for (int i = threadIdx.x; i < DK * SP; i += ATT_THREADS) {
+      const int c = i / SP, r = i % SP;
+      Krs[c * PS + r] = __float2bfloat16(r < S ? kr[c * S + r] : 0.f);
+      if (SMEM_DKR) dKr[i] = 0.f;
+    }
+  }
+  cp_async_wait<0>();
   __syncthreads();
   const DropCfg drop = make_drop(a);
-  const long long pbase = (((long long)grp * a.Bt + b) * a.Hh + h) * S * S;
+  const long long rbase = (((long long)grp * a.Bt + b) * a.Hh + h) * S;  // global row index of query 0
+  const long long pbase = rbase * S;
   const int ntile_s = (S + 7) >> 3;
+  const int nblk_s = (S + 15) >> 4;
   const bool pair_ok = (S & 1) == 0;
   __nv_bfloat16* stage = stage_all + warp * 16 * PS;
   __nv_bfloat16* dq_out = a.dqkv + (long long)grp * a.gs_qkv + (long long)b * S * 3 * d + h * DK;
+  float* dkr_out = a.dkrel != nullptr ? a.dkrel + (long long)grp * DK * S : nullptr;
 
   // ------------------------------------------------------------------ row pass: dQ, dKrel
-  for (int pass = 0; pass < 2; ++pass) {
-    const int rb = pass ? 7 - warp : warp;
+  for (int pass = 0; pass < NB / ATT_WARPS; ++pass) {
+    const int rb = block_of<NB, ATT_WARPS>(warp, pass);
     const int i0 = rb * 16;
     if (i0 >= S) continue;
+    const int njt = min(2 * rb + 2, ntile_s);
+    // every P pair of this row block, in flight together
+    uint32_t pv[NJ][2];
+#pragma unroll
+    for (int jt = 0; jt < NJ; ++jt)
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int i = i0 + g + 8 * r, j = jt * 8 + 2 * t;
+        pv[jt][r] = 0u;
+        if (jt < njt && i < S && j <= i) pv[jt][r] = load_p_pair(a.probs, pbase + (long long)i * S + j, pair_ok, j + 1 <= i);
+      }
     uint32_t ado[KS][4];
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) ldsm_x4(ado[ks], smem_u32(dOs + (i0 + (lane & 15)) * PD + ks * 16 + (lane >> 4) * 8));
@@ -310,68 +377,64 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
       for (int i = lane; i < 16 * PS / 8; i += 32) reinterpret_cast<uint4*>(stage)[i] = make_uint4(0u, 0u, 0u, 0u);
       __syncwarp();
     }
-    const int njt = min(2 * rb + 2, ntile_s);
     float dq[NT][4];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) dq[nt][e] = 0.f;
     const float Di[2] = {Dsm[i0 + g], Dsm[i0 + g + 8]};
-    for (int kk = 0; 2 * kk < njt; ++kk) {
-      float ds[2][4];
 #pragma unroll
-      for (int hf = 0; hf < 2; ++hf) {
-        const int jt = 2 * kk + hf;
+    for (int kk = 0; kk < NB; ++kk) {
+      if (2 * kk < njt) {
+        float ds[2][4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) ds[hf][e] = 0.f;
-        if (jt < njt) {
-          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int hf = 0; hf < 2; ++hf) {
+          const int jt = 2 * kk + hf;
 #pragma unroll
-          for (int ks = 0; ks < KS; ++ks) {
-            uint32_t bb[2];
-            ldsm_x2(bb, smem_u32(Vs + (jt * 8 + (lane & 7)) * PD + ks * 16 + ((lane >> 3) & 1) * 8));
-            mma_bf16_16816(acc, ado[ks], bb[0], bb[1]);
-          }
+          for (int e = 0; e < 4; ++e) ds[hf][e] = 0.f;
+          if (jt < njt) {
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int r = 0; r < 2; ++r) {
-            const int ii = g + 8 * r, i = i0 + ii, j = jt * 8 + 2 * t;
-            if (i < S && j <= i) {
-              const long long e = pbase + (long long)i * S + j;
-              float p0, p1 = 0.f;
-              if (pair_ok && j + 1 <= i) {
-                const __nv_bfloat162 pb = *reinterpret_cast<const __nv_bfloat162*>(a.probs + e);
-                p0 = __low2float(pb);
-                p1 = __high2float(pb);
-              } else {
-                p0 = __bfloat162float(a.probs[e]);
-                if (j + 1 <= i) p1 = __bfloat162float(a.probs[e + 1]);
-              }
-              float dp0 = acc[2 * r], dp1 = acc[2 * r + 1];
-              if (drop.thresh != 0) {
-                dp0 = keep_elem(drop, e) ? dp0 * drop.scale : 0.f;
-                dp1 = keep_elem(drop, e + 1) ? dp1 * drop.scale : 0.f;
-              }
-              const float s0 = p0 * (dp0 - Di[r]) * a.scale;
-              const float s1 = j + 1 <= i ? p1 * (dp1 - Di[r]) * a.scale : 0.f;
-              ds[hf][2 * r] = s0;
-              ds[hf][2 * r + 1] = s1;
-              if (rel) {
-                const int rr = S - 1 - i + j;
-                stage[ii * PS + rr] = __float2bfloat16(s0);
-                if (j + 1 <= i) stage[ii * PS + rr + 1] = __float2bfloat16(s1);
+            for (int ks = 0; ks < KS; ++ks) {
+              uint32_t bb[2];
+              ldsm_x2(bb, smem_u32(Vs + (jt * 8 + (lane & 7)) * PD + ks * 16 + ((lane >> 3) & 1) * 8));
+              mma_bf16_16816(acc, ado[ks], bb[0], bb[1]);
+            }
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              const int ii = g + 8 * r, i = i0 + ii, j = jt * 8 + 2 * t;
+              if (i < S && j <= i) {
+                const long long e = pbase + (long long)i * S + j;
+                const float p0 = bf16lo(pv[jt][r]), p1 = bf16hi(pv[jt][r]);
+                float dp0 = acc[2 * r], dp1 = acc[2 * r + 1];
+                if (drop.thresh != 0) {
+                  bool k0, k1;
+                  keep_pair(drop, rbase + i, j, k0, k1);
+                  dp0 = k0 ? dp0 * drop.scale : 0.f;
+                  dp1 = k1 ? dp1 * drop.scale : 0.f;
+                }
+                const float s0 = p0 * (dp0 - Di[r]) * a.scale;
+                const float s1 = j + 1 <= i ? p1 * (dp1 - Di[r]) * a.scale : 0.f;
+                ds[hf][2 * r] = s0;
+                ds[hf][2 * r + 1] = s1;
+                if (rel) {
+                  const int rr = S - 1 - i + j;
+                  stage[ii * PS + rr] = __float2bfloat16(s0);
+                  if (j + 1 <= i) stage[ii * PS + rr + 1] = __float2bfloat16(s1);
+                }
               }
             }
           }
         }
-      }
-      uint32_t ap[4] = {pack_bf16x2(ds[0][0], ds[0][1]), pack_bf16x2(ds[0][2], ds[0][3]),
-                        pack_bf16x2(ds[1][0], ds[1][1]), pack_bf16x2(ds[1][2], ds[1][3])};
+        uint32_t ap[4] = {pack_bf16x2(ds[0][0], ds[0][1]), pack_bf16x2(ds[0][2], ds[0][3]),
+                          pack_bf16x2(ds[1][0], ds[1][1]), pack_bf16x2(ds[1][2], ds[1][3])};
 #pragma unroll
-      for (int n2 = 0; n2 < NT / 2; ++n2) {
-        uint32_t bb[4];
-        ldsm_x4_t(bb, smem_u32(Ks + (kk * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
-        mma_bf16_16816(dq[2 * n2], ap, bb[0], bb[1]);
-        mma_bf16_16816(dq[2 * n2 + 1], ap, bb[2], bb[3]);
+        for (int n2 = 0; n2 < NT / 2; ++n2) {
+          uint32_t bb[4];
+          ldsm_x4_t(bb, smem_u32(Ks + (kk * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
+          mma_bf16_16816(dq[2 * n2], ap, bb[0], bb[1]);
+          mma_bf16_16816(dq[2 * n2 + 1], ap, bb[2], bb[3]);
+        }
       }
     }
     if (rel) {
@@ -389,7 +452,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
         }
       }
       // dKrel[c][r] += sum_ii Q[i0+ii][c] * unskew(dS)[ii][r]
-      if (a.dkrel != nullptr) {
+      if (dkr_out != nullptr) {
         uint32_t aqt[KS][4];
 #pragma unroll
         for (int mt = 0; mt < KS; ++mt)
@@ -402,13 +465,24 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
             mma_bf16_16816(acc, aqt[mt], bb[0], bb[1]);
             const int c = mt * 16 + g, r = r0 + 2 * t;
-            if (r < S) {
-              atomicAdd(&dKr[c * SP + r], acc[0]);
-              atomicAdd(&dKr[(c + 8) * SP + r], acc[2]);
-            }
-            if (r + 1 < S) {
-              atomicAdd(&dKr[c * SP + r + 1], acc[1]);
-              atomicAdd(&dKr[(c + 8) * SP + r + 1], acc[3]);
+            if (SMEM_DKR) {
+              if (r < S) {
+                atomicAdd(&dKr[c * SP + r], acc[0]);
+                atomicAdd(&dKr[(c + 8) * SP + r], acc[2]);
+              }
+              if (r + 1 < S) {
+                atomicAdd(&dKr[c * SP + r + 1], acc[1]);
+                atomicAdd(&dKr[(c + 8) * SP + r + 1], acc[3]);
+              }
+            } else {
+              if (r < S) {
+                red_add_f32(dkr_out + c * S + r, acc[0]);
+                red_add_f32(dkr_out + (c + 8) * S + r, acc[2]);
+              }
+              if (r + 1 < S) {
+                red_add_f32(dkr_out + c * S + r + 1, acc[1]);
+                red_add_f32(dkr_out + (c + 8) * S + r + 1, acc[3]);
+              }
             }
           }
         }
@@ -424,65 +498,88 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
     }
   }
 
-  // ------------------------------------------------------------------ column pass: dK, dV (transposed tiles [j][i])
-  for (int pass = 0; pass < 2; ++pass) {
-    const int jb = pass ? warp : 7 - warp;
+  // ------------------------------------------------------------------ column pass: dK, dV
+  for (int pass = 0; pass < NB / ATT_WARPS; ++pass) {
+    // multi-pass: long columns first; single pass: column block w costs NB - w, row block w cost w + 1 (balanced)
+    const int jb = block_of<NB, ATT_WARPS>(warp, NB / ATT_WARPS == 1 ? pass : pass ^ 1);
     const int j0 = jb * 16;
     if (j0 >= S) continue;
-    uint32_t av[KS][4];
+    // P pairs of the strip [i >= j0][j0 .. j0+15]: (query block, 8-key half, row half)
+    uint32_t pc[NB][2][2];
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) ldsm_x4(av[ks], smem_u32(Vs + (j0 + (lane & 15)) * PD + ks * 16 + (lane >> 4) * 8));
+    for (int ib = 0; ib < NB; ++ib)
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf)
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int i = ib * 16 + g + 8 * r, j = j0 + 8 * hf + 2 * t;
+          pc[ib][hf][r] = 0u;
+          if (ib >= jb && i < S && j <= i)
+            pc[ib][hf][r] = load_p_pair(a.probs, pbase + (long long)i * S + j, pair_ok, j + 1 <= i);
+        }
+    uint32_t bv[2][KS][2];  // V rows of this key block as B fragments of dP = dO . V^T
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf)
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks)
+        ldsm_x2(bv[hf][ks], smem_u32(Vs + (j0 + hf * 8 + (lane & 7)) * PD + ks * 16 + ((lane >> 3) & 1) * 8));
     float dk[NT][4], dv[NT][4];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) dk[nt][e] = dv[nt][e] = 0.f;
-    for (int kk = jb; 2 * kk < ntile_s; ++kk) {
-      float pt[2][4], dst[2][4];
 #pragma unroll
-      for (int hf = 0; hf < 2; ++hf) {
-        const int it = 2 * kk + hf;
+    for (int ib = 0; ib < NB; ++ib) {
+      if (ib >= jb && ib < nblk_s) {
+        uint32_t ado[KS][4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) pt[hf][e] = dst[hf][e] = 0.f;
-        if (it < ntile_s) {
+        for (int ks = 0; ks < KS; ++ks)
+          ldsm_x4(ado[ks], smem_u32(dOs + (ib * 16 + (lane & 15)) * PD + ks * 16 + (lane >> 4) * 8));
+        const float Di[2] = {Dsm[ib * 16 + g], Dsm[ib * 16 + g + 8]};
+        uint32_t pk[2][2], sk[2][2];
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
           float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int ks = 0; ks < KS; ++ks) {
-            uint32_t bb[2];
-            ldsm_x2(bb, smem_u32(dOs + (it * 8 + (lane & 7)) * PD + ks * 16 + ((lane >> 3) & 1) * 8));
-            mma_bf16_16816(acc, av[ks], bb[0], bb[1]);
-          }
+          for (int ks = 0; ks < KS; ++ks) mma_bf16_16816(acc, ado[ks], bv[hf][ks][0], bv[hf][ks][1]);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int j = j0 + g + 8 * (e >> 1), i = it * 8 + 2 * t + (e & 1);
+          for (int r = 0; r < 2; ++r) {
+            const int i = ib * 16 + g + 8 * r, j = j0 + 8 * hf + 2 * t;
+            float pd0 = 0.f, pd1 = 0.f, s0 = 0.f, s1 = 0.f;
             if (i < S && j <= i) {
-              const long long el = pbase + (long long)i * S + j;
-              const float p = __bfloat162float(a.probs[el]);
-              float pd = p, dp = acc[e];
+              const long long e = pbase + (long long)i * S + j;
+              const float p0 = bf16lo(pc[ib][hf][r]), p1 = bf16hi(pc[ib][hf][r]);
+              float dp0 = acc[2 * r], dp1 = acc[2 * r + 1];
+              pd0 = p0;
+              pd1 = p1;
               if (drop.thresh != 0) {
-                const bool keep = keep_elem(drop, el);
-                pd = keep ? p * drop.scale : 0.f;
-                dp = keep ? dp * drop.scale : 0.f;
+                bool k0, k1;
+                keep_pair(drop, rbase + i, j, k0, k1);
+                pd0 = k0 ? p0 * drop.scale : 0.f;
+                pd1 = k1 ? p1 * drop.scale : 0.f;
+                dp0 = k0 ? dp0 * drop.scale : 0.f;
+                dp1 = k1 ? dp1 * drop.scale : 0.f;
               }
-              pt[hf][e] = pd;
-              dst[hf][e] = p * (dp - Dsm[i]) * a.scale;
+              s0 = p0 * (dp0 - Di[r]) * a.scale;
+              s1 = p1 * (dp1 - Di[r]) * a.scale;  // p1 = 0 outside the triangle
             }
+            pk[hf][r] = pack_bf16x2(pd0, pd1);
+            sk[hf][r] = pack_bf16x2(s0, s1);
           }
         }
-      }
-      uint32_t ap[4] = {pack_bf16x2(pt[0][0], pt[0][1]), pack_bf16x2(pt[0][2], pt[0][3]),
-                        pack_bf16x2(pt[1][0], pt[1][1]), pack_bf16x2(pt[1][2], pt[1][3])};
-      uint32_t as[4] = {pack_bf16x2(dst[0][0], dst[0][1]), pack_bf16x2(dst[0][2], dst[0][3]),
-                        pack_bf16x2(dst[1][0], dst[1][1]), pack_bf16x2(dst[1][2], dst[1][3])};
+        // [i][j] tiles -> A fragments of the transposed [j][i] tile
+        const uint32_t ap[4] = {movmatrix_t(pk[0][0]), movmatrix_t(pk[1][0]), movmatrix_t(pk[0][1]), movmatrix_t(pk[1][1])};
+        const uint32_t as[4] = {movmatrix_t(sk[0][0]), movmatrix_t(sk[1][0]), movmatrix_t(sk[0][1]), movmatrix_t(sk[1][1])};
 #pragma unroll
-      for (int n2 = 0; n2 < NT / 2; ++n2) {
-        uint32_t bb[4];
-        ldsm_x4_t(bb, smem_u32(dOs + (kk * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
-        mma_bf16_16816(dv[2 * n2], ap, bb[0], bb[1]);
-        mma_bf16_16816(dv[2 * n2 + 1], ap, bb[2], bb[3]);
-        ldsm_x4_t(bb, smem_u32(Qs + (kk * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
-        mma_bf16_16816(dk[2 * n2], as, bb[0], bb[1]);
-        mma_bf16_16816(dk[2 * n2 + 1], as, bb[2], bb[3]);
+        for (int n2 = 0; n2 < NT / 2; ++n2) {
+          uint32_t bb[4];
+          ldsm_x4_t(bb, smem_u32(dOs + (ib * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
+          mma_bf16_16816(dv[2 * n2], ap, bb[0], bb[1]);
+          mma_bf16_16816(dv[2 * n2 + 1], ap, bb[2], bb[3]);
+          ldsm_x4_t(bb, smem_u32(Qs + (ib * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
+          mma_bf16_16816(dk[2 * n2], as, bb[0], bb[1]);
+          mma_bf16_16816(dk[2 * n2 + 1], as, bb[2], bb[3]);
+        }
       }
     }
 #pragma unroll
@@ -500,22 +597,23 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_tc_kernel(const AttnArgs
       }
     }
   }
-  if (rel && a.dkrel != nullptr) {
+  if (SMEM_DKR && rel && dkr_out != nullptr) {
     __syncthreads();
-    float* out = a.dkrel + (long long)grp * DK * S;
     for (int i = threadIdx.x; i < DK * S; i += ATT_THREADS) {
       const int c = i / S, r = i % S;
-      red_add_f32(out + i, dKr[c * SP + r]);
+      red_add_f32(dkr_out + i, dKr[c * SP + r]);
     }
   }
 }
 
 // ================================================================================================ host
-template <int DK>
-static size_t fwd_smem() { return (size_t)4 * SP * (DK + 8) * 2 + (size_t)4 * 16 * (SP + 8) * 4; }
-template <int DK>
+constexpr int FWD_WARPS = 4;  // the forward holds a whole score row block in registers (~210): 4 warps, 2 CTAs/SM
+template <int DK, int SP, int NW>
+static size_t fwd_smem() { return (size_t)4 * SP * (DK + 8) * 2 + (size_t)NW * 16 * (SP + 8) * 4; }
+template <int DK, int SP>
 static size_t bwd_smem() {
-  return (size_t)4 * SP * (DK + 8) * 2 + (size_t)DK * PS * 2 + (size_t)4 * 16 * PS * 2 + (size_t)SP * 4 + (size_t)DK * SP * 4;
+  return (size_t)4 * SP * (DK + 8) * 2 + (size_t)DK * (SP + 8) * 2 + (size_t)att_warps(SP) * 16 * (SP + 8) * 2 + (size_t)SP * 4 +
+         (SP == 128 ? (size_t)DK * SP * 4 : 0);
 }
 
 int attn_tc_supported(const AttnArgs& a) {
@@ -523,39 +621,42 @@ int attn_tc_supported(const AttnArgs& a) {
     const char* e = getenv("CPC_ATTN_TC");
     return e == nullptr || e[0] != '0';
   }();
-  return enabled && a.S <= SP && a.S >= 1 && (a.dk == 32 || a.dk == 64) && a.d % 8 == 0;
+  return enabled && a.S <= 256 && a.S >= 1 && (a.dk == 32 || a.dk == 64) && a.d % 8 == 0;
 }
 
-template <int DK>
+template <int DK, int SP>
 static int launch_fwd(const AttnArgs& a, int G, cudaStream_t stream) {
-  auto kern = attn_fwd_tc_kernel<DK>;
+  constexpr int NW = FWD_WARPS;
+  auto kern = attn_fwd_tc_kernel<DK, SP, NW>;
   static bool done = false;
   if (!done) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<DK>()) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<DK, SP, NW>()) != cudaSuccess)
       return CPC_ERR_LAUNCH;
     done = true;
   }
-  kern<<<dim3(a.Hh, a.Bt, G), ATT_THREADS, fwd_smem<DK>(), stream>>>(a);
+  kern<<<dim3(a.Hh, a.Bt, G), NW * 32, fwd_smem<DK, SP, NW>(), stream>>>(a);
   return launch_status();
 }
-template <int DK>
+template <int DK, int SP>
 static int launch_bwd(const AttnArgs& a, int G, cudaStream_t stream) {
-  auto kern = attn_bwd_tc_kernel<DK>;
+  auto kern = attn_bwd_tc_kernel<DK, SP>;
   static bool done = false;
   if (!done) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<DK>()) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<DK, SP>()) != cudaSuccess)
       return CPC_ERR_LAUNCH;
     done = true;
   }
-  kern<<<dim3(a.Hh, a.Bt, G), ATT_THREADS, bwd_smem<DK>(), stream>>>(a);
+  kern<<<dim3(a.Hh, a.Bt, G), att_warps(SP) * 32, bwd_smem<DK, SP>(), stream>>>(a);
   return launch_status();
 }
 
 int attn_fwd_tc(const AttnArgs& a, int G, cudaStream_t stream) {
-  return a.dk == 32 ? launch_fwd<32>(a, G, stream) : launch_fwd<64>(a, G, stream);
+  if (a.S <= 128) return a.dk == 32 ? launch_fwd<32, 128>(a, G, stream) : launch_fwd<64, 128>(a, G, stream);
+  return a.dk == 32 ? launch_fwd<32, 256>(a, G, stream) : launch_fwd<64, 256>(a, G, stream);
 }
 int attn_bwd_tc(const AttnArgs& a, int G, cudaStream_t stream) {
-  return a.dk == 32 ? launch_bwd<32>(a, G, stream) : launch_bwd<64>(a, G, stream);
+  if (a.S <= 128) return a.dk == 32 ? launch_bwd<32, 128>(a, G, stream) : launch_bwd<64, 128>(a, G, stream);
+  return a.dk == 32 ? launch_bwd<32, 256>(a, G, stream) : launch_bwd<64, 256>(a, G, stream);
 }
 
 }  // namespace cpc

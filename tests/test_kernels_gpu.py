@@ -350,7 +350,9 @@ def test_cpcar_module_matches_torch_rnn(K, cell, H, Cin, N, S, nl):
 
 # ------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("G,Bt,Hh,S,dk,relpos", [(2, 3, 8, 116, 32, True), (1, 2, 8, 12, 4, True),
-                                                 (1, 2, 4, 128, 64, False), (1, 1, 8, 244, 64, True)])
+                                                 (1, 2, 4, 128, 64, False), (1, 1, 8, 244, 64, True),
+                                                 (1, 2, 8, 117, 32, True), (2, 1, 4, 256, 64, True),
+                                                 (1, 2, 8, 200, 32, True), (1, 1, 2, 131, 32, False)])
 def test_attention_fwd_bwd(K, G, Bt, Hh, S, dk, relpos):
     from oracle import cpc_oracle as oc
     torch.manual_seed(9)
@@ -383,6 +385,59 @@ def test_attention_fwd_bwd(K, G, Bt, Hh, S, dk, relpos):
     if relpos:
         assert cos(dkrel, kr.grad) > 0.999
         close(dkrel, kr.grad, 5e-2, 3e-2 * kr.grad.abs().max().item(), "attention dkrel")
+
+
+@pytest.mark.parametrize("S,dk", [(32, 32), (64, 64), (160, 64)])
+def test_attention_dropout_backward_matches_masked_reference(K, S, dk):
+    """Dropout on the probabilities (transformers.py:69): the kernel's mask depends only on (seed, element index),
+    so it is recovered exactly by a forward with V = identity (out = P~) and fed to an fp32 autograd reference."""
+    torch.manual_seed(11)
+    G, Bt, Hh, p = 1, 2, 2, 0.25
+    if S > dk:  # recover the mask block by block: V = shifted identities
+        nblk = (S + dk - 1) // dk
+    else:
+        nblk = 1
+    d = Hh * dk
+    rng = torch.tensor([1234, 7], device="cuda", dtype=torch.int64)
+    krel = (torch.rand(G, dk, S, device="cuda") - 0.5) * (2 / math.sqrt(dk))
+    qkv = bf(torch.randn(G, Bt * S, 3 * d, device="cuda") * 0.5)
+    probs = torch.zeros(G, Bt, Hh, S, S, device="cuda", dtype=BF)
+    keep = torch.zeros(Bt, Hh, S, S, device="cuda", dtype=torch.bool)
+    for blk in range(nblk):
+        probe = qkv.clone().view(G, Bt, S, 3, Hh, dk)
+        probe[:, :, :, 2] = 0
+        for j in range(blk * dk, min(S, (blk + 1) * dk)):
+            probe[:, :, j, 2, :, j - blk * dk] = 1
+        o = torch.empty(G, Bt * S, d, device="cuda", dtype=BF)
+        K.attn_fwd(probe.view(G, Bt * S, 3 * d), krel, o, probs, G, Bt, Hh, S, dk, rng=rng, site=3, drop_p=p)
+        o = o.view(Bt, S, Hh, dk).permute(0, 2, 1, 3).float()  # [Bt, Hh, i, j - blk*dk] = P~[i, j]
+        w = min(S, (blk + 1) * dk) - blk * dk
+        keep[:, :, :, blk * dk:blk * dk + w] = o[..., :w] != 0
+    tri = torch.tril(torch.ones(S, S, device="cuda", dtype=torch.bool))
+    frac = keep[:, :, tri].float().mean().item()
+    assert abs(frac - (1 - p)) < 0.03, frac
+    out = torch.empty(G, Bt * S, d, device="cuda", dtype=BF)
+    K.attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=rng, site=3, drop_p=p)
+    qr = qkv.float().requires_grad_(True)
+    kr = krel.clone().requires_grad_(True)
+    x = qr[0].view(Bt, S, 3, Hh, dk)
+    q, k, v = (x[:, :, i].transpose(1, 2) for i in range(3))  # [Bt, Hh, S, dk]
+    idx = (S - 1 - torch.arange(S, device="cuda").view(S, 1) + torch.arange(S, device="cuda").view(1, S)).clamp(0, S - 1)
+    rel = torch.gather(q @ kr[0], 3, idx.expand(Bt, Hh, S, S))
+    sc = ((q @ k.transpose(2, 3)) + rel) / math.sqrt(dk)
+    sc = sc.masked_fill(~tri, float("-inf"))
+    P = torch.softmax(sc, dim=-1)
+    ref = ((P * keep / (1 - p)) @ v).transpose(1, 2).reshape(1, Bt * S, d)
+    close(out, ref, 2e-2, 2e-2, "dropout attention out")
+    dout = bf(torch.randn(G, Bt * S, d, device="cuda"))
+    ref.backward(dout.float())
+    dqkv = torch.empty_like(qkv)
+    dkrel = torch.zeros(G, dk, S, device="cuda")
+    K.attn_bwd(qkv, krel, out, probs, dout, dqkv, torch.empty_like(probs), dkrel, G, Bt, Hh, S, dk, rng=rng, site=3,
+               drop_p=p)
+    assert cos(dqkv, qr.grad) > 0.999, cos(dqkv, qr.grad)
+    assert cos(dkrel, kr.grad) > 0.999, cos(dkrel, kr.grad)
+    close(dqkv, qr.grad, 5e-2, 3e-2 * qr.grad.abs().max().item(), "dropout attention dqkv")
 
 
 def test_attention_dropout_consistent(K):
