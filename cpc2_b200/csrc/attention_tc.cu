@@ -282,13 +282,11 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
 }
 
 // ================================================================================================ backward
-// SMEM_DKR: dKrel partial sums of the CTA are accumulated in shared memory and flushed once (SP = 128); the
-// SP = 256 instantiation has no room for that tile and reduces straight into global memory.
 template <int DK, int SP>
 __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const AttnArgs a) {
   constexpr int ATT_WARPS = att_warps(SP), ATT_THREADS = ATT_WARPS * 32;
   constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, PS = SP + 8, NB = SP / 16, NJ = SP / 8;
-  constexpr bool SMEM_DKR = SP == 128;
+  constexpr bool FULL_U = NB == att_warps(SP);  // one row block per warp: the stages hold all of unskew(dS)
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(smem_dyn);
   __nv_bfloat16* Ks = Qs + SP * PD;
@@ -297,7 +295,6 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
   __nv_bfloat16* Krs = dOs + SP * PD;                                      // Krel [c][r] bf16, pitch PS
   __nv_bfloat16* stage_all = Krs + DK * PS;                                // per warp unskew(dS) [16][PS]
   float* Dsm = reinterpret_cast<float*>(stage_all + ATT_WARPS * 16 * PS);  // [SP]
-  float* dKr = Dsm + SP;                                                   // [DK][SP] fp32 accumulator (SMEM_DKR)
   const int S = a.S, d = a.d;
   const int h = blockIdx.x, b = blockIdx.y, grp = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -338,7 +335,6 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
     for (int i = threadIdx.x; i < DK * SP; i += ATT_THREADS) {
       const int c = i / SP, r = i % SP;
       Krs[c * PS + r] = __float2bfloat16(r < S ? kr[c * S + r] : 0.f);
-      if (SMEM_DKR) dKr[i] = 0.f;
     }
   }
   cp_async_wait<0>();
@@ -451,8 +447,10 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
           mma_bf16_16816(dq[nt], as, bb[0], bb[1]);
         }
       }
-      // dKrel[c][r] += sum_ii Q[i0+ii][c] * unskew(dS)[ii][r]
-      if (dkr_out != nullptr) {
+      // dKrel[c][r] += sum_ii Q[i0+ii][c] * unskew(dS)[ii][r]: with one row block per warp (FULL_U) the stages of
+      // the CTA form the whole unskew(dS) matrix and the product is taken once after the passes; otherwise per
+      // row block, reduced straight into global memory
+      if (!FULL_U && dkr_out != nullptr) {
         uint32_t aqt[KS][4];
 #pragma unroll
         for (int mt = 0; mt < KS; ++mt)
@@ -465,24 +463,13 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
             mma_bf16_16816(acc, aqt[mt], bb[0], bb[1]);
             const int c = mt * 16 + g, r = r0 + 2 * t;
-            if (SMEM_DKR) {
-              if (r < S) {
-                atomicAdd(&dKr[c * SP + r], acc[0]);
-                atomicAdd(&dKr[(c + 8) * SP + r], acc[2]);
-              }
-              if (r + 1 < S) {
-                atomicAdd(&dKr[c * SP + r + 1], acc[1]);
-                atomicAdd(&dKr[(c + 8) * SP + r + 1], acc[3]);
-              }
-            } else {
-              if (r < S) {
-                red_add_f32(dkr_out + c * S + r, acc[0]);
-                red_add_f32(dkr_out + (c + 8) * S + r, acc[2]);
-              }
-              if (r + 1 < S) {
-                red_add_f32(dkr_out + c * S + r + 1, acc[1]);
-                red_add_f32(dkr_out + (c + 8) * S + r + 1, acc[3]);
-              }
+            if (r < S) {
+              red_add_f32(dkr_out + c * S + r, acc[0]);
+              red_add_f32(dkr_out + (c + 8) * S + r, acc[2]);
+            }
+            if (r + 1 < S) {
+              red_add_f32(dkr_out + c * S + r + 1, acc[1]);
+              red_add_f32(dkr_out + (c + 8) * S + r + 1, acc[3]);
             }
           }
         }
@@ -597,11 +584,46 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
       }
     }
   }
-  if (SMEM_DKR && rel && dkr_out != nullptr) {
+  if (FULL_U && rel && dkr_out != nullptr) {
+    // dKrel[c][r] = sum_i Q[i][c] * U[i][r], U = unskew(dS) = the eight per-warp stages; warp w owns columns
+    // [16w, 16w+16) and only the query blocks that can address them (U[i][r] = 0 for i < S-1-r)
     __syncthreads();
-    for (int i = threadIdx.x; i < DK * S; i += ATT_THREADS) {
-      const int c = i / S, r = i % S;
-      red_add_f32(dkr_out + i, dKr[c * SP + r]);
+    const int r0 = warp * 16;
+    if (r0 < S) {
+      float acc[KS][2][4];
+#pragma unroll
+      for (int mt = 0; mt < KS; ++mt)
+#pragma unroll
+        for (int nn = 0; nn < 2; ++nn)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[mt][nn][e] = 0.f;
+      for (int ib = max(0, S - 16 - r0) >> 4; ib < nblk_s; ++ib) {
+        uint32_t aqt[KS][4];
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt)
+          ldsm_x4_t(aqt[mt], smem_u32(Qs + (ib * 16 + (lane & 7) + 8 * (lane >> 4)) * PD + mt * 16 + 8 * ((lane >> 3) & 1)));
+#pragma unroll
+        for (int nn = 0; nn < 2; ++nn) {
+          uint32_t bb[2];
+          ldsm_x2_t(bb, smem_u32(stage_all + (ib * 16 + (lane & 15)) * PS + r0 + nn * 8));
+#pragma unroll
+          for (int mt = 0; mt < KS; ++mt) mma_bf16_16816(acc[mt][nn], aqt[mt], bb[0], bb[1]);
+        }
+      }
+#pragma unroll
+      for (int mt = 0; mt < KS; ++mt)
+#pragma unroll
+        for (int nn = 0; nn < 2; ++nn) {
+          const int c = mt * 16 + g, r = r0 + nn * 8 + 2 * t;
+          if (r < S) {
+            red_add_f32(dkr_out + c * S + r, acc[mt][nn][0]);
+            red_add_f32(dkr_out + (c + 8) * S + r, acc[mt][nn][2]);
+          }
+          if (r + 1 < S) {
+            red_add_f32(dkr_out + c * S + r + 1, acc[mt][nn][1]);
+            red_add_f32(dkr_out + (c + 8) * S + r + 1, acc[mt][nn][3]);
+          }
+        }
     }
   }
 }
@@ -612,8 +634,7 @@ template <int DK, int SP, int NW>
 static size_t fwd_smem() { return (size_t)4 * SP * (DK + 8) * 2 + (size_t)NW * 16 * (SP + 8) * 4; }
 template <int DK, int SP>
 static size_t bwd_smem() {
-  return (size_t)4 * SP * (DK + 8) * 2 + (size_t)DK * (SP + 8) * 2 + (size_t)att_warps(SP) * 16 * (SP + 8) * 2 + (size_t)SP * 4 +
-         (SP == 128 ? (size_t)DK * SP * 4 : 0);
+  return (size_t)4 * SP * (DK + 8) * 2 + (size_t)DK * (SP + 8) * 2 + (size_t)att_warps(SP) * 16 * (SP + 8) * 2 + (size_t)SP * 4;
 }
 
 int attn_tc_supported(const AttnArgs& a) {
