@@ -279,6 +279,10 @@ class _CriterionFn(torch.autograd.Function):
                 A = K.View(dlog[part], BS, T, Kp, BS, T * BS, major=1, gmul=0)
                 K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
                        accumulate=True, alpha=1.0 / D)
+            # dz is complete here, long before the heads' backward below: an encoder backward that runs on its
+            # own side stream (the future half of CPCModel.forwardPastFuture) may start from this event
+            ops._READY.clear()
+            ops.set_ready(dz, ops.mark())
         for part in range(2):
             K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
                    accumulate=part > 0)

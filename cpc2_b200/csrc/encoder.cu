@@ -31,7 +31,7 @@ __global__ void conv_wgrad_unpack_kernel(const float* __restrict__ dwf, float* _
     const int kk = (int)(i % k);
     const int ci = (int)((i / k) % Ci);
     const int co = (int)(i / ((long long)k * Ci));
-    dw[i] = dwf[(long long)co * k * Ci + (long long)kk * Ci + ci];
+    red_add_f32(dw + i, dwf[(long long)co * k * Ci + (long long)kk * Ci + ci]);
   }
 }
 

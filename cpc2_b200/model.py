@@ -122,7 +122,7 @@ class CPCEncoder(nn.Module):
         """x [N, 1, W] fp32 (W multiple of 160) -> [N, C, W/160] fp32 (a view of channels-last memory)."""
         ops.require_cuda(x)
         pref, self._pref = getattr(self, "_pref", None), None
-        return _EncoderFn.apply(x, pref, *self._params())
+        return _EncoderFn.apply(x, _EncPlan(pref=pref), *self._params())
 
 
 def _alloc_packed(C, dev):
@@ -140,130 +140,196 @@ def _pack_conv_weights(ws, bufs):
         K.conv_weight_pack(ws[l - 1], bufs[l][0], bufs[l][1], C, C, k, s)
 
 
+def _geometry(N, W):
+    L = [W // 5, W // 20, W // 40, W // 80, W // 160]
+    pad_next = [GEOMETRY[i + 1][2] for i in range(4)] + [0]
+    return L, pad_next
+
+
+def _grad_sizes(C):
+    sizes = []
+    for l in range(5):
+        kl = GEOMETRY[l][0]
+        sizes += [C * (1 if l == 0 else C) * kl, C, C, C]
+    return sizes
+
+
+def _alloc_fwd(N, W, C, dev):
+    """Every buffer the encoder forward writes (activations carry the next conv's zero halo rows)."""
+    L, pad_next = _geometry(N, W)
+    b = dict(acts=[], ys=[None], means=[], rstds=[])
+    for l in range(5):
+        b["acts"].append(torch.empty(N, L[l] + 2 * pad_next[l], C, device=dev, dtype=BF16))
+        b["means"].append(torch.empty(N * L[l], device=dev))
+        b["rstds"].append(torch.empty(N * L[l], device=dev))
+        if l:
+            b["ys"].append(torch.empty(N * L[l], C, device=dev, dtype=BF16))
+    b["z32"] = torch.empty(N, L[4], C, device=dev, dtype=torch.float32)
+    return b
+
+
+def _alloc_bwd(N, W, C, dev):
+    """Workspace of the encoder backward: per conv layer dy (one zero row either side), the fp32 weight gradient
+    in GEMM layout (zeroed: split-K accumulates into it) and the padded input gradient."""
+    L, _ = _geometry(N, W)
+    w = [None]
+    for l in range(1, 5):
+        k, s, pd = GEOMETRY[l]
+        w.append(dict(dy=torch.empty(N, L[l] + 2, C, device=dev, dtype=BF16),
+                      dwf=torch.zeros(C, k * C, device=dev),
+                      dxp=torch.empty(N, L[l - 1] + 2 * pd, C, device=dev, dtype=BF16)))
+    return w
+
+
+class _EncPlan:
+    """How one _EncoderFn node runs.  Default: everything on the current stream, buffers allocated on the fly.
+    As one half of a past/future pair (CPCModel.forwardPastFuture): `role` 'future' runs on side stream 6 from
+    `fwd_after` on, with buffers the driver allocated on the main stream BEFORE that event; both halves reduce
+    their parameter gradients into `pair.gflat` and the half whose backward is issued last returns them."""
+
+    def __init__(self, pref=None, packed=None, role=None, pair=None, fwd_after=None, fwd_bufs=None, bwd_bufs=None):
+        self.pref, self.packed, self.role, self.pair = pref, packed, role, pair
+        self.fwd_after, self.fwd_bufs, self.bwd_bufs = fwd_after, fwd_bufs, bwd_bufs
+
+
+class _PairCtx:
+    def __init__(self, gflat):
+        self.gflat = gflat
+        self.pending = 2
+        self.first_done = None  # event: the half whose backward was issued first has finished
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
 class _EncoderFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, pref, *params):
+    def forward(ctx, x, plan, *params):
         N, one, W = x.shape
         if one != 1 or W % 160 != 0:
             raise ValueError("CPCEncoder expects [N, 1, W] with W a multiple of 160")
         C = params[0].shape[0]
         dev = x.device
-        x2 = x.detach().reshape(N, W).contiguous().float()
         p = [t.detach() for t in params]
-        L = [W // 5, W // 20, W // 40, W // 80, W // 160]
-        pad_next = [GEOMETRY[i + 1][2] for i in range(4)] + [0]
-        acts, ys, means, rstds = [], [None], [], []
-        packed = None  # conv1..4 weights in GEMM layout: prefetched on a side stream, or packed there now
-        if pref is None:
+        L, pad_next = _geometry(N, W)
+        future = plan.role == "future"
+        x2 = x.detach().reshape(N, W).contiguous().float()
+        bufs = plan.fwd_bufs if plan.fwd_bufs is not None else _alloc_fwd(N, W, C, dev)
+        acts, ys, means, rstds, z32 = bufs["acts"], bufs["ys"], bufs["means"], bufs["rstds"], bufs["z32"]
+        # conv1..4 weights in GEMM layout: handed in by the pair driver, prefetched on side stream 3, or packed now
+        packed, sync = plan.packed, None
+        if packed is None and plan.pref is not None:
+            packed = plan.pref.peek([params[4 * l] for l in range(1, 5)])
+        if packed is None:
             packed = _alloc_packed(C, dev)
             with ops.side(3):
                 _pack_conv_weights([p[4 * l] for l in range(1, 5)], packed)
-        # layer 0: fused conv + ChannelNorm + ReLU straight from the waveform
-        a = torch.empty(N, L[0] + 2 * pad_next[0], C, device=dev, dtype=BF16)  # halo rows are zeroed by the kernel
-        mean = torch.empty(N * L[0], device=dev)
-        rstd = torch.empty(N * L[0], device=dev)
-        K.conv0_fwd(x2, p[0], p[1], p[2], p[3], a, mean, rstd, N, W, C, pad_next[0])
-        acts.append(a)
-        means.append(mean)
-        rstds.append(rstd)
-        z32 = None
-        if pref is not None:
-            packed = pref.take([params[4 * l] for l in range(1, 5)])
-            if packed is None:  # parameters changed since the prefetch: pack again, inline
-                packed = _alloc_packed(C, dev)
-                _pack_conv_weights([p[4 * l] for l in range(1, 5)], packed)
-        else:
-            ops.join(3)
-        for l in range(1, 5):
-            k, s, pd = GEOMETRY[l]
-            w, b, g, be = p[4 * l:4 * l + 4]
-            wf, wd = packed[l]
-            Lin, Lout = L[l - 1], L[l]
-            Lp = Lin + 2 * pd
-            y = torch.empty(N * Lout, C, device=dev, dtype=BF16)
-            A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
-            K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
-            hn = pad_next[l]
-            a = torch.empty(N, Lout + 2 * hn, C, device=dev, dtype=BF16)
-            if hn:
-                a[:, :hn].zero_()
-                a[:, hn + Lout:].zero_()
-            mean = torch.empty(N * Lout, device=dev)
-            rstd = torch.empty(N * Lout, device=dev)
-            if l == 4:
-                z32 = torch.empty(N, Lout, C, device=dev, dtype=torch.float32)
-            K.rownorm_fwd(y, N * Lout, C, g.reshape(C), be.reshape(C), out_bf16=a, out_f32=z32, mean=mean,
-                          rstd=rstd, out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True, relu=True)
-            ys.append(y)
-            acts.append(a)
-            means.append(mean)
-            rstds.append(rstd)
+        with (ops.side(6, after=plan.fwd_after) if future else _null()):
+            # layer 0: fused conv + ChannelNorm + ReLU straight from the waveform (halo rows zeroed by the kernel)
+            K.conv0_fwd(x2, p[0], p[1], p[2], p[3], acts[0], means[0], rstds[0], N, W, C, pad_next[0])
+            if future:
+                ops.wait_side(3)  # the past half (main stream) consumes the pending join
+            else:
+                ops.join(3)
+            for l in range(1, 5):
+                k, s, pd = GEOMETRY[l]
+                w, b, g, be = p[4 * l:4 * l + 4]
+                wf, wd = packed[l]
+                Lin, Lout = L[l - 1], L[l]
+                Lp = Lin + 2 * pd
+                y, a = ys[l], acts[l]
+                A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
+                K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
+                hn = pad_next[l]
+                if hn:
+                    a[:, :hn].zero_()
+                    a[:, hn + Lout:].zero_()
+                K.rownorm_fwd(y, N * Lout, C, g.reshape(C), be.reshape(C), out_bf16=a, out_f32=z32 if l == 4 else None,
+                              mean=means[l], rstd=rstds[l], out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True,
+                              relu=True)
         ctx.geom = (N, W, C, L, pad_next)
         ctx.x2 = x2
         ctx.acts, ctx.ys, ctx.means, ctx.rstds, ctx.packed = acts, ys, means, rstds, packed
         ctx.p = p
+        ctx.plan = plan
         return z32.permute(0, 2, 1)
 
     @staticmethod
     def backward(ctx, dz):
         N, W, C, L, pad_next = ctx.geom
-        p = ctx.p
+        p, plan = ctx.p, ctx.plan
         dev = dz.device
-        grads = [None] * 20
+        pair, future = plan.pair, plan.role == "future"
         # one flat fp32 buffer for every parameter gradient of the encoder (a single memset, and a single
-        # all-reduce bucket for the data-parallel wrapper); per-parameter gradients are views of it
-        sizes = []
-        for l in range(5):
-            kl = GEOMETRY[l][0]
-            sizes += [C * (1 if l == 0 else C) * kl, C, C, C]
-        gflat = torch.zeros(sum(sizes), device=dev)
+        # all-reduce bucket for the data-parallel wrapper); per-parameter gradients are views of it.  Every kernel
+        # below ADDS into it atomically, so the two halves of a pair share one arena.
+        sizes = _grad_sizes(C)
+        gflat = pair.gflat if pair is not None else torch.zeros(sum(sizes), device=dev)
         gv, off = [], 0
         for n_ in sizes:
             gv.append(gflat[off:off + n_])
             off += n_
-        d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
-        dout, dout_map = d, None
-        keep = []  # buffers a side stream still reads: alive until the join
-        for l in range(4, 0, -1):
-            k, s, pd = GEOMETRY[l]
-            w, b, g, be = p[4 * l:4 * l + 4]
-            wf, wd = ctx.packed[l]
-            Lin, Lout = L[l - 1], L[l]
-            Lp = Lin + 2 * pd
-            dy = torch.empty(N, Lout + 2, C, device=dev, dtype=BF16)
-            dy[:, 0].zero_()
-            dy[:, Lout + 1].zero_()
-            dw, dcb, dg, db = gv[4 * l:4 * l + 4]
-            K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
-                          dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,
-                          dx_map=K.rowmap(Lout, Lout + 2, 1), unbiased=True, relu=True)
-            # wgrad: dWf[co, kk*C+ci] = sum_{n,t} dy[n,t,co] * a_pad[n, t*s+kk, ci]   (side stream: only the
-            # optimizer needs it; the input-gradient chain continues on the main stream)
-            dwf = torch.zeros(C, k * C, device=dev)
-            with ops.side(0):
-                A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
-                B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
-                K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout,
-                       k_splits=ops.auto_splits(C, k * C, N * Lout, 1, Lout), out_f32=dwf, accumulate=True)
-                K.conv_wgrad_unpack(dwf, dw, C, C, k)
-            keep.append(dwf)
-            grads[4 * l:4 * l + 4] = [dw.view(C, C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
-            # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
-            A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
-            if ops.GRAD_F32 and l >= 2:
-                dxp = torch.empty(N, Lp, C, device=dev)
-                K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_f32=(dxp, s * C, Lp * C))
-            else:  # layer 0 consumes its (largest) gradient in bf16
-                dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
+        ws = plan.bwd_bufs if plan.bwd_bufs is not None else _alloc_bwd(N, W, C, dev)
+        wg = 7 if future else 0  # weight-gradient side stream (forked from the stream this half runs on)
+        after = ops.pop_ready(dz) if future else None
+        last = True
+        with (ops.side(6, after=after) if future else _null()):
+            d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
+            dout, dout_map = d, None
+            for l in range(4, 0, -1):
+                k, s, pd = GEOMETRY[l]
+                w, b, g, be = p[4 * l:4 * l + 4]
+                wf, wd = ctx.packed[l]
+                Lin, Lout = L[l - 1], L[l]
+                Lp = Lin + 2 * pd
+                dy, dwf, dxp = ws[l]["dy"], ws[l]["dwf"], ws[l]["dxp"]
+                dy[:, 0].zero_()
+                dy[:, Lout + 1].zero_()
+                dw, dcb, dg, db = gv[4 * l:4 * l + 4]
+                K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
+                              dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,
+                              dx_map=K.rowmap(Lout, Lout + 2, 1), unbiased=True, relu=True)
+                # wgrad: dWf[co, kk*C+ci] = sum_{n,t} dy[n,t,co] * a_pad[n, t*s+kk, ci]   (side stream: only the
+                # optimizer needs it; the input-gradient chain continues on this stream).  Split-K >= 2 keeps the
+                # accumulation atomic (red.global), which is what lets two halves share dw.
+                with ops.side(wg):
+                    A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
+                    B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
+                    K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout,
+                           k_splits=max(2, ops.auto_splits(C, k * C, N * Lout, 1, Lout)), out_f32=dwf, accumulate=True)
+                    K.conv_wgrad_unpack(dwf, dw, C, C, k)
+                # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
+                A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
-            keep += [dy, dout]
-            dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
-        dw0, db0, dg0, dbe0 = gv[0:4]
-        K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
-                    pad_next[0])
-        grads[0:4] = [dw0.view(C, 1, 10), db0, dg0.view(1, C, 1), dbe0.view(1, C, 1)]
-        ops.join()
-        del keep
+                dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
+            dw0, db0, dg0, dbe0 = gv[0:4]
+            K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
+                        pad_next[0])
+            ops.join()
+            if pair is not None:
+                pair.pending -= 1
+                last = pair.pending == 0
+                if last:
+                    if pair.first_done is not None:
+                        torch.cuda.current_stream().wait_event(pair.first_done)
+                else:
+                    pair.first_done = ops.mark()
+        if future:
+            if last:
+                ops.join(6)
+        del ws
+        if not last:
+            return (None, None) + (None,) * 20
+        grads = []
+        for l in range(5):
+            k = GEOMETRY[l][0]
+            dw, dcb, dg, db = gv[4 * l:4 * l + 4]
+            grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
         ops.grad_ready("encoder", gflat)
         return (None, None, *grads)
 
@@ -490,3 +556,42 @@ class CPCModel(nn.Module):
         encodedData = self.gEncoder(batchData).permute(0, 2, 1)
         cFeature = self.gAR(encodedData)
         return cFeature, encodedData, label
+
+    def splittable(self):
+        """True when the training step may run as two halves (forwardPastFuture): a CPCEncoder front end and an
+        AR that carries no state between calls (keepHidden feeds the hidden state of ALL 2B rows forward)."""
+        return isinstance(self.gEncoder, CPCEncoder) and not getattr(self.gAR, "keepHidden", False)
+
+    def forwardPastFuture(self, past, future):
+        """The two consumers of cpc/train.py:95-104 without the dead work: trainStep concatenates past and future
+        windows, runs the model on all 2B rows and keeps `cFeature[:B]` and `encodedData[B:]` only.  Here the
+        past half goes encoder -> AR on the current stream while the future half is encoded on a side stream
+        (its backward likewise overlaps the heads' and the AR's), and the AR never sees the future rows.
+        Returns (cFeature of the past windows [B,S,H], encodedData of the future windows [B,S,C]): the same
+        values and the same parameter gradients as the concatenated call."""
+        ops.require_cuda(past, future)
+        enc = self.gEncoder
+        params = enc._params()
+        N, _, W = future.shape
+        C, dev = enc.dimEncoded, future.device
+        pref, enc._pref = getattr(enc, "_pref", None), None
+        ws = enc._conv_weights()
+        packed = pref.peek(ws) if pref is not None else None
+        if packed is None:
+            packed = _alloc_packed(C, dev)
+            with ops.side(3):
+                _pack_conv_weights([w.detach() for w in ws], packed)
+        # everything the future half touches on its side stream exists BEFORE the fork event (ops.side(after=))
+        fut = future.detach().reshape(N, W).contiguous().float().view(N, 1, W)
+        pair = _PairCtx(torch.zeros(sum(_grad_sizes(C)), device=dev))
+        plan_f = _EncPlan(packed=packed, role="future", pair=pair, fwd_bufs=_alloc_fwd(N, W, C, dev),
+                          bwd_bufs=_alloc_bwd(N, W, C, dev) if torch.is_grad_enabled() else None)
+        plan_f.fwd_after = ops.mark()
+        plan_p = _EncPlan(packed=packed, role="past", pair=pair)
+        if not torch.is_grad_enabled():
+            plan_f.pair = plan_p.pair = None
+        zPast = _EncoderFn.apply(past, plan_p, *params).permute(0, 2, 1)
+        cPast = self.gAR(zPast)
+        zFuture = _EncoderFn.apply(fut, plan_f, *params).permute(0, 2, 1)
+        ops.join(6)
+        return cPast, zFuture

@@ -39,11 +39,14 @@ _PENDING = []
 
 class side:
     """`with ops.side(i):` launches the body on side stream i (ordered after everything already queued on the
-    current stream).  `ops.join()` makes the current stream wait for every side stream used since;
-    `ops.join(i)` for stream i only."""
+    current stream, or -- `after=event` -- only after that event: the body must then touch nothing that was
+    allocated or written on the current stream later than the event).  `ops.join()` makes the current stream wait
+    for every side stream forked FROM IT since; `ops.join(i)` for stream i only.  A side stream has one parent at
+    a time: code that itself runs on a side stream forks with indices nobody else uses concurrently."""
 
-    def __init__(self, index):
+    def __init__(self, index, after=None):
         self.index = index
+        self.after = after
         self.ctx = None
 
     def __enter__(self):
@@ -56,7 +59,10 @@ class side:
             s = _SIDE[key] = torch.cuda.Stream(device=cur.device)
         if all(k != key for k, _, _ in _PENDING):
             _PENDING.append((key, s, cur))
-        s.wait_stream(cur)
+        if self.after is not None:
+            s.wait_event(self.after)
+        else:
+            s.wait_stream(cur)
         self.ctx = torch.cuda.stream(s)
         self.ctx.__enter__()
         return self
@@ -69,11 +75,43 @@ class side:
 
 
 def join(index=None):
+    cur = torch.cuda.current_stream()
     for item in list(_PENDING):
-        key, s, cur = item
-        if index is None or key[1] == index:
-            torch.cuda.current_stream().wait_stream(s)
+        key, s, parent = item
+        if parent.cuda_stream == cur.cuda_stream and key[0] == cur.device.index and (index is None or key[1] == index):
+            cur.wait_stream(s)
             _PENDING.remove(item)
+
+
+def wait_side(index):
+    """The current stream waits for side stream `index` WITHOUT consuming the pending join of its parent."""
+    cur = torch.cuda.current_stream()
+    s = _SIDE.get((cur.device.index, index))
+    if s is not None and s.cuda_stream != cur.cuda_stream:
+        cur.wait_stream(s)
+
+
+def mark():
+    """Event at the current point of the current stream (None when side streams are disabled)."""
+    if not CONCURRENT or K.PROFILE is not None:
+        return None
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream())
+    return ev
+
+
+# events attached to tensors handed across autograd nodes: "this gradient is complete at <event>", so that a
+# consumer running on a side stream can start from the event instead of from the producer's whole stream
+_READY = {}
+
+
+def set_ready(t, ev):
+    if ev is not None:
+        _READY[(t.device.index, t.data_ptr())] = ev
+
+
+def pop_ready(t):
+    return _READY.pop((t.device.index, t.data_ptr()), None)
 
 
 class Prefetched:
@@ -84,6 +122,13 @@ class Prefetched:
         self.versions = [p._version for p in params]
         self.ptrs = [p.data_ptr() for p in params]
         self.value, self.stream_index = value, stream_index
+
+    def peek(self, params):
+        """The value if still valid, WITHOUT synchronising: the caller orders its stream after side stream
+        `stream_index` itself (ops.join / ops.wait_side)."""
+        if [p._version for p in params] == self.versions and [p.data_ptr() for p in params] == self.ptrs:
+            return self.value
+        return None
 
     def take(self, params):
         join(self.stream_index)

@@ -74,6 +74,11 @@ def buildModelAndCriterion(args):
     return cpcModel, cpcCriterion
 
 
+# forwardBackward runs an unwrapped cpc2_b200 CPCModel as two halves (CPCModel.forwardPastFuture); False restores
+# the literal concatenated call of cpc/train.py:95-104 (wrapped models -- DataParallel / DDP -- always use it)
+SPLIT_PAST_FUTURE = True
+
+
 def prefetchWeights(cpcModel, cpcCriterion):
     """Issue every weight-only preparation of the step (conv weight packing, bf16 shadows of the AR and head
     weights) on side streams now, so it overlaps the encoder instead of sitting in front of each consumer.
@@ -93,12 +98,17 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
     prefetchWeights(cpcModel, cpcCriterion)
     past, future = sequence[:, 0, ...], sequence[:, 1, ...]
     b = past.size(0)
-    combined = torch.cat([past, future], dim=0)
-    label = torch.cat([label, label])
-    c_feature, encoded_data, label = cpcModel(combined, label)
-    c_feature = c_feature[:b, :, :]
-    encoded_data = encoded_data[b:, :, :]
-    label = label[:b]
+    if SPLIT_PAST_FUTURE and isinstance(cpcModel, model_.CPCModel) and cpcModel.splittable():
+        # same outputs and gradients as the concatenated call below, without its dead half (the AR over the
+        # future windows, whose output train.py:102 drops) and with the two encoder halves overlapped
+        c_feature, encoded_data = cpcModel.forwardPastFuture(past, future)
+    else:
+        combined = torch.cat([past, future], dim=0)
+        label2 = torch.cat([label, label])
+        c_feature, encoded_data, label2 = cpcModel(combined, label2)
+        c_feature = c_feature[:b, :, :]
+        encoded_data = encoded_data[b:, :, :]
+        label = label2[:b]
     allLosses, allAcc = cpcCriterion(c_feature, encoded_data, label, signal_quality)
     if backward:
         totLoss = allLosses.sum()

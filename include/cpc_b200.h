@@ -134,7 +134,8 @@ int cpc_conv0_cn_relu_fwd(const CpcConv0* desc, void* stream);
 int cpc_conv0_cn_relu_bwd(const CpcConv0* desc, void* stream);
 
 /* conv weight fp32 [Co,Ci,k] (k == 2*s) -> bf16 GEMM operands: wf [Co, k*Ci] (forward / wgrad) and
- * wd [s*Ci, 2*Co] (dgrad; may be null).  cpc_conv_wgrad_unpack is the inverse for the fp32 gradient. */
+ * wd [s*Ci, 2*Co] (dgrad; may be null).  cpc_conv_wgrad_unpack is the inverse for the fp32 gradient and ADDS
+ * (red.global) into dw, so the two half-batches of a step can reduce into one zero-initialised gradient. */
 int cpc_conv_weight_pack(const void* w, void* wf, void* wd, int Co, int Ci, int k, int s, void* stream);
 int cpc_conv_wgrad_unpack(const void* dwf, void* dw, int Co, int Ci, int k, void* stream);
 

@@ -183,7 +183,7 @@ def test_conv_implicit_gemm_fwd_dgrad_wgrad(K, C, k, s, p, L):
     A = K.View(dyp, C, Lout + 2, Nb, C, (Lout + 2) * C, major=1, row_off=1)
     B = K.View(xp, k * C, Lout, Nb, s * C, Lp * C, major=1)
     K.gemm(A, B, C, k * C, Nb * Lout, k_per_slab=Lout, k_splits=2, out_f32=dwf, accumulate=True)
-    dw = torch.empty_like(conv.weight)
+    dw = torch.zeros_like(conv.weight)  # the unpack ADDS (two half-batches share one gradient)
     K.conv_wgrad_unpack(dwf, dw, C, C, k)
     close(dw, wq.grad, 1e-3, 1e-3 * wq.grad.abs().max().item(), "conv wgrad")
 

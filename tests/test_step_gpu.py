@@ -217,3 +217,46 @@ def test_train_mode_dropout_runs_and_learns():
         hist.append(out["loss"].mean().item())
     first, last = sum(hist[:5]) / 5, sum(hist[-5:]) / 5
     assert all(h == h for h in hist) and last < first - 0.05, (first, last)
+
+
+@pytest.mark.parametrize("over", [dict(), dict(arMode="transformer", rnnMode="linear"),
+                                  dict(arMode="GRU", nLevelsGRU=2, hiddenEncoder=64, hiddenGar=128, nPredicts=4,
+                                       negativeSamplingExt=16, sizeWindow=5120, rnnMode="linear")])
+def test_past_future_split_matches_concatenated_call(over):
+    """train.forwardBackward runs the model as two halves (CPCModel.forwardPastFuture: past -> encoder -> AR,
+    future -> encoder on a side stream, no AR over the future rows).  Same losses, accuracies and parameter
+    gradients as the literal concatenated call of cpc/train.py:95-104 (differences: fp32 summation order only)."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    args = T.defaultArgs(**over)
+    model, crit = build(args)
+    model.eval()
+    crit.eval()
+    g = torch.Generator().manual_seed(5)
+    B = 8
+    seq = (0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=g)).cuda()
+    label = torch.zeros(B, dtype=torch.long, device="cuda")
+    res = {}
+    for split in (False, True):
+        T.SPLIT_PAST_FUTURE = split
+        try:
+            for p in list(model.parameters()) + list(crit.parameters()):
+                p.grad = None
+            torch.manual_seed(99)
+            losses, acc = T.forwardBackward(model, crit, seq, label)
+            torch.cuda.synchronize()
+        finally:
+            T.SPLIT_PAST_FUTURE = True
+        grads = {k: v.grad.detach().float().clone() for k, v in list(model.named_parameters()) + list(crit.named_parameters())
+                 if v.grad is not None}
+        res[split] = (losses.detach().clone(), acc.detach().clone(), grads)
+    assert torch.allclose(res[True][0], res[False][0], atol=1e-5), (res[True][0], res[False][0])
+    assert torch.equal(res[True][1], res[False][1])
+    assert set(res[True][2]) == set(res[False][2])
+    for k, gr in res[False][2].items():
+        gs = res[True][2][k]
+        if gr.abs().max() == 0:
+            assert gs.abs().max() == 0, k
+            continue
+        assert cosine(gs, gr) > 0.99999, (k, cosine(gs, gr))
+        assert (gs - gr).abs().max() <= 5e-3 * gr.abs().max() + 1e-7, k  # atomics: fp32 summation order
