@@ -101,10 +101,14 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     h_s[0][b][k] = __float2bfloat16(v);
     if (a.h_pad != nullptr && n < a.N && (k >> 5) == (int)cta) a.h_pad[(long long)n * (a.S + 1) * H + k] = __float2bfloat16(v);
   }
+  // bar[q] completes when the CL slices of h (CL x 512 bytes, st.async complete_tx) for a step of parity q have
+  // landed in h_s[q]; its single arrival is this CTA arming it (expect_tx) once the previous phase is consumed
+  constexpr uint32_t STEP_BYTES = CL * NB * 32 * 2;
   if (tid == 0) {
-    mbar_init(&bar[0], CL);
-    mbar_init(&bar[1], CL);
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
     fence_barrier_init();
+    if (a.S > 1) mbar_expect_tx(&bar[1], STEP_BYTES);
   }
   // gx prefetch: thread -> (sequence, gate, 16-byte chunk)
   const int pf_b = tid >> 5, pf_g = (tid >> 3) & 3, pf_ch = tid & 7;
@@ -125,7 +129,8 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
   for (int t = 0; t < a.S; ++t) {
     const int p = t & 1;
     prefetch(t + 2);
-    if (t > 0) mbar_wait_cluster(&bar[p], ((t - 1) >> 1) & 1);
+    if (t > 0) mbar_wait(&bar[p], ((t - 1) >> 1) & 1);
+    if (tid == 0 && t + 2 < a.S) mbar_expect_tx(&bar[p], STEP_BYTES);  // arm for step t+2 (h_{t+1} lands here)
     float acc[2][4];
 #pragma unroll
     for (int i = 0; i < 2; ++i)
@@ -181,15 +186,12 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     cp_async_wait<1>();  // gx of step t+1 has landed (only the newest group may be in flight)
     __syncthreads();
     if (t + 1 < a.S) {
-      // warp d pushes this CTA's [8 x 32] bf16 slice of h_t into buffer p^1 of CTA d, then signals it
+      // warp d pushes this CTA's [8 x 32] bf16 slice of h_t into buffer p^1 of CTA d; the bytes count on d's barrier
       const int b = lane >> 2, part = lane & 3;
       const uint4 v = *reinterpret_cast<const uint4*>(&st_h[p][b][part * 8]);
       const uint32_t dst = smem_u32(&h_s[p ^ 1][b][cta * 32 + part * 8]);
-      for (int d = warp; d < CL; d += LSTM_THREADS / 32) {
-        st_cluster_v4(mapa(dst, d), v.x, v.y, v.z, v.w);
-        __syncwarp();
-        if (lane == 0) mbar_arrive_remote(mapa(smem_u32(&bar[p ^ 1]), d));
-      }
+      const uint32_t dbar = smem_u32(&bar[p ^ 1]);
+      for (int d = warp; d < CL; d += LSTM_THREADS / 32) st_async_v4(mapa(dst, d), v.x, v.y, v.z, v.w, mapa(dbar, d));
     }
     // coalesced global writes of everything the backward (and the caller) needs, off the critical path
     {
@@ -235,7 +237,6 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
   constexpr int MT = H / 16;                      // output (h) m-tiles
   constexpr int MTW = (MT + 7) / 8;               // m-tiles per warp
   constexpr int ACTIVE = MT / MTW;                // warps that own m-tiles
-  constexpr int ARRIVALS = CL * (MTW == 1 && MT > 1 ? 2 : 1);  // (warp, destination) pairs per step and barrier
   constexpr int GP = 136;                         // bf16 pitch of the [seq][gate*32+unit] tiles
   constexpr int CP = 36;                          // fp32 pitch of the [seq][unit] tiles
   extern __shared__ __align__(16) uint8_t smem_dyn[];
@@ -277,10 +278,13 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
       }
     }
   }
+  // bar[q]: the CL partial dh tiles (CL x 32 units x 8 sequences fp32, st.async complete_tx) of a step of parity q
+  constexpr uint32_t STEP_BYTES = CL * 32 * NB * 4;
   if (tid == 0) {
-    mbar_init(&bar[0], ARRIVALS);
-    mbar_init(&bar[1], ARRIVALS);
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
     fence_barrier_init();
+    if (a.S > 1) mbar_expect_tx(&bar[1], STEP_BYTES);
   }
   const float* s0p = CELL == CELL_LSTM ? a.c0 : a.h0;  // state before step 0: c0 (LSTM) or h0 (GRU / RNN, whose c_all holds h)
   // per-step input prefetch (cp.async, two steps ahead): 128 threads fetch the gates tile, 64 c_{t-1}, 64 dout_t
@@ -330,13 +334,14 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     float dh = in_d[(buf * NB + bsel) * CP + unit_l];
     const float tc = tanh_f(ct);
     if (sidx > 0) {
-      mbar_wait_cluster(&bar[pp], ((sidx - 1) >> 1) & 1);
+      mbar_wait(&bar[pp], ((sidx - 1) >> 1) & 1);
       const float* pr = P + ((pp * CL) * 32 + unit_l) * NB + bsel;
       float s = 0.f;
 #pragma unroll
       for (int src = 0; src < CL; ++src) s += pr[src * 32 * NB];
       dh += s;
     }
+    if (tid == 0 && sidx + 2 < a.S) mbar_expect_tx(&bar[pp], STEP_BYTES);  // arm for step sidx+2
     float d_i = 0.f, d_f = 0.f, d_g = 0.f, d_o = 0.f;
     if (valid) {
       if constexpr (CELL == CELL_LSTM) {
@@ -391,12 +396,9 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
         const int d = m >> 1;                   // owner CTA
         const int jl = (m & 1) * 16 + (lane >> 2);
         const uint32_t dst = smem_u32(P + (((pp ^ 1) * CL + cta) * 32 + jl) * NB + (lane & 3) * 2);
-        st_cluster_v2_f32(mapa(dst, d), acc[mt][0], acc[mt][1]);
-        st_cluster_v2_f32(mapa(dst + 8 * NB * 4, d), acc[mt][2], acc[mt][3]);
-        if (MTW == 1 || (mt & 1) == 1) {  // last m-tile this warp sends to destination d
-          __syncwarp();
-          if (lane == 0) mbar_arrive_remote(mapa(smem_u32(&bar[pp ^ 1]), d));
-        }
+        const uint32_t dbar = mapa(smem_u32(&bar[pp ^ 1]), d);
+        st_async_v2_f32(mapa(dst, d), acc[mt][0], acc[mt][1], dbar);
+        st_async_v2_f32(mapa(dst + 8 * NB * 4, d), acc[mt][2], acc[mt][3], dbar);
       }
     }
     // coalesced write of this step's gate gradients (operand of the dW / dx GEMMs)
