@@ -131,9 +131,12 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     prefetch(t + 2);
     if (t > 0) mbar_wait(&bar[p], ((t - 1) >> 1) & 1);
     if (tid == 0 && t + 2 < a.S) mbar_expect_tx(&bar[p], STEP_BYTES);  // arm for step t+2 (h_{t+1} lands here)
-    float acc[2][4];
+    // four independent accumulator chains: the step is latency-bound and a chain of KT dependent HMMAs is its
+    // longest serial piece
+    constexpr int CH = KT >= 8 ? 4 : 2;
+    float acc[CH][4];
 #pragma unroll
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < CH; ++i)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
     // B fragments: h_s[p][seq][k], two k-tiles per ldmatrix.x4
@@ -142,12 +145,15 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     for (int kt2 = 0; kt2 < KT / 2; ++kt2) {
       uint32_t bb[4];
       ldsm_x4(bb, hrow + kt2 * 64);
-      mma_bf16_16816(acc[0], afr[2 * kt2], bb[0], bb[1]);
-      mma_bf16_16816(acc[1], afr[2 * kt2 + 1], bb[2], bb[3]);
+      mma_bf16_16816(acc[(2 * kt2) % CH], afr[2 * kt2], bb[0], bb[1]);
+      mma_bf16_16816(acc[(2 * kt2 + 1) % CH], afr[2 * kt2 + 1], bb[2], bb[3]);
     }
     float c4[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) c4[e] = acc[0][e] + acc[1][e];
+    for (int e = 0; e < 4; ++e) {
+      c4[e] = acc[0][e] + acc[1][e];
+      if (CH == 4) c4[e] += acc[2][e] + acc[3][e];
+    }
     // rows (lane/4) and (lane/4 + 8) are gates g0 and g0+2 of unit u for sequences 2*(lane%4), +1; the partner
     // lane (xor 16) holds the other two gates.  After the exchange this thread owns sequence 2*(lane%4) + g0.
     const float s0 = g0 ? c4[0] : c4[1];
@@ -373,11 +379,11 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     __syncthreads();
     if (t > 0 && warp < ACTIVE) {
       // partial dh_{t-1}[j][b] = sum_{r in my 128 gate rows} W_hh[rg(r)][j] * dgate[b][r]
-      float acc[MTW][4];
+      float acc[MTW][4], acc2[MTW][4];  // two chains per m-tile: halves the dependent-HMMA latency of the step
 #pragma unroll
       for (int mt = 0; mt < MTW; ++mt)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) acc[mt][e] = 0.f;
+        for (int e = 0; e < 4; ++e) acc[mt][e] = acc2[mt][e] = 0.f;
       const uint32_t brow = smem_u32(dg_s + (pp * NB + (lane & 7)) * GP + (lane >> 3) * 8);
 #pragma unroll
       for (int kt2 = 0; kt2 < 4; ++kt2) {
@@ -386,9 +392,13 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
 #pragma unroll
         for (int mt = 0; mt < MTW; ++mt) {
           mma_bf16_16816(acc[mt], afr[mt][2 * kt2], bb[0], bb[1]);
-          mma_bf16_16816(acc[mt], afr[mt][2 * kt2 + 1], bb[2], bb[3]);
+          mma_bf16_16816(acc2[mt], afr[mt][2 * kt2 + 1], bb[2], bb[3]);
         }
       }
+#pragma unroll
+      for (int mt = 0; mt < MTW; ++mt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[mt][e] += acc2[mt][e];
       // accumulator (row j = m-tile*16 + lane/4 (+8), columns = sequences 2*(lane%4), +1) -> owner CTA of unit j
 #pragma unroll
       for (int mt = 0; mt < MTW; ++mt) {

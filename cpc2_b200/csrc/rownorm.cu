@@ -90,6 +90,29 @@ __device__ __forceinline__ void store_f32(float* p, const float (&x)[V]) {
   }
 }
 
+// Outputs addressed through a RowMap with halo rows (row_off > 0 or seq_stride > row_off + seq_len) are the
+// zero-halo buffers of the implicit-GEMM convolutions: the warp that writes the first / last row of a sequence
+// also clears the halo rows before / after it, so no separate memset launches exist.
+template <int V, typename T>
+__device__ __forceinline__ void zero_halo(T* base, const RowMap& m, long long r, int lane) {
+  constexpr int C = 32 * V;
+  const long long n = r / m.seq_len, t = r - n * m.seq_len;
+  if (t != 0 && t != m.seq_len - 1) return;
+  float z[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) z[i] = 0.f;
+  if (t == 0)
+    for (long long h = 0; h < m.row_off; ++h) {
+      if constexpr (sizeof(T) == 2) store_bf16<V>(base + (n * m.seq_stride + h) * C + lane * V, z);
+      else store_f32<V>(base + (n * m.seq_stride + h) * C + lane * V, z);
+    }
+  if (t == m.seq_len - 1)
+    for (long long h = m.row_off + m.seq_len; h < m.seq_stride; ++h) {
+      if constexpr (sizeof(T) == 2) store_bf16<V>(base + (n * m.seq_stride + h) * C + lane * V, z);
+      else store_f32<V>(base + (n * m.seq_stride + h) * C + lane * V, z);
+    }
+}
+
 struct RowNormFwdArgs {
   const __nv_bfloat16* in;
   RowMap in_map;
@@ -146,8 +169,14 @@ __global__ void __launch_bounds__(256) rownorm_fwd_kernel(const RowNormFwdArgs a
       for (int i = 0; i < V; ++i) x[i] = fmaxf(x[i], 0.f);
     }
     const long long o = a.out_map(r) * C + lane * V;
-    if (a.out_bf16 != nullptr) store_bf16<V>(a.out_bf16 + o, x);
-    if (a.out_f32 != nullptr) store_f32<V>(a.out_f32 + o, x);
+    if (a.out_bf16 != nullptr) {
+      store_bf16<V>(a.out_bf16 + o, x);
+      zero_halo<V>(a.out_bf16, a.out_map, r, lane);
+    }
+    if (a.out_f32 != nullptr) {
+      store_f32<V>(a.out_f32 + o, x);
+      zero_halo<V>(a.out_f32, a.out_map, r, lane);
+    }
   }
 }
 
@@ -225,8 +254,12 @@ __global__ void __launch_bounds__(256) rownorm_bwd_kernel(const RowNormBwdArgs a
       as[i] += d[i];
     }
     const long long o = a.dx_map(r) * C + lane * V;
-    if (a.dx_bf16 != nullptr) store_bf16<V>(a.dx_bf16 + o, d);
+    if (a.dx_bf16 != nullptr) {
+      store_bf16<V>(a.dx_bf16 + o, d);
+      zero_halo<V>(a.dx_bf16, a.dx_map, r, lane);
+    }
     if (a.dx_f32 != nullptr) {
+      if (!a.dx_accumulate) zero_halo<V>(a.dx_f32, a.dx_map, r, lane);
       if (a.dx_accumulate) {
         float old[V];
         load_f32<V>(a.dx_f32 + o, old);

@@ -245,10 +245,7 @@ class _EncoderFn(torch.autograd.Function):
                 y, a = ys[l], acts[l]
                 A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
                 K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
-                hn = pad_next[l]
-                if hn:
-                    a[:, :hn].zero_()
-                    a[:, hn + Lout:].zero_()
+                hn = pad_next[l]  # halo rows of `a` are zeroed by the kernel (out_map)
                 K.rownorm_fwd(y, N * Lout, C, g.reshape(C), be.reshape(C), out_bf16=a, out_f32=z32 if l == 4 else None,
                               mean=means[l], rstd=rstds[l], out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True,
                               relu=True)
@@ -288,8 +285,6 @@ class _EncoderFn(torch.autograd.Function):
                 Lin, Lout = L[l - 1], L[l]
                 Lp = Lin + 2 * pd
                 dy, dwf, dxp = ws[l]["dy"], ws[l]["dwf"], ws[l]["dxp"]
-                dy[:, 0].zero_()
-                dy[:, Lout + 1].zero_()
                 dw, dcb, dg, db = gv[4 * l:4 * l + 4]
                 K.rownorm_bwd(dout, ctx.ys[l], ctx.means[l], ctx.rstds[l], N * Lout, C, g.reshape(C), be.reshape(C),
                               dx_bf16=dy, dgamma=dg, dbeta=db, dxsum=dcb, dout_map=dout_map,

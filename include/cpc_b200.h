@@ -87,7 +87,8 @@ int cpc_gemm_bf16(const CpcGemmDesc* desc, void* stream);
  * variance over channels, eps inside the sqrt, affine [1,C,1]) and nn.LayerNorm of the transformer
  * blocks (cpc/transformers.py:124,130).  Rows are [C] bf16 vectors; a CpcRowMap places logical row r
  * at buffer row (r / seq_len) * seq_stride + row_off + r % seq_len (seq_len == 0: identity), which is
- * how the zero-halo channels-last conv buffers are addressed.  C must be 32 * {1,2,4,8,16}.
+ * how the zero-halo channels-last conv buffers are addressed; the halo rows of an OUTPUT map (rows [0, row_off)
+ * and [row_off + seq_len, seq_stride) of every sequence) are cleared by the kernel.  C must be 32 * {1,2,4,8,16}.
  */
 typedef struct { int64_t seq_len, seq_stride, row_off; } CpcRowMap;
 

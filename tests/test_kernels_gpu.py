@@ -68,7 +68,7 @@ def test_channelnorm_relu_fwd_bwd(K, C):
     y = bf(torch.randn(N * L, C, device="cuda") * 2 + 0.3)
     gamma = torch.rand(C, device="cuda") + 0.5
     beta = torch.randn(C, device="cuda") * 0.1
-    out = torch.zeros(N, L + 2 * halo, C, device="cuda", dtype=BF)
+    out = torch.full((N, L + 2 * halo, C), 7.0, device="cuda", dtype=BF)  # the kernel must clear the halo rows
     out32 = torch.zeros(N * L, C, device="cuda")
     mean, rstd = torch.empty(N * L, device="cuda"), torch.empty(N * L, device="cuda")
     K.rownorm_fwd(y, N * L, C, gamma, beta, out_bf16=out, mean=mean, rstd=rstd,
@@ -81,14 +81,15 @@ def test_channelnorm_relu_fwd_bwd(K, C):
     ref = torch.relu((yr - m) * torch.rsqrt(v + 1e-5) * g_ + b_)
     close(out32, ref, 1e-4, 1e-4, "channelnorm fwd f32")
     close(out[:, halo:halo + L].reshape(N * L, C), ref, 1e-2, 1e-2, "channelnorm fwd bf16")
-    assert out[:, :halo].abs().max() == 0 and out[:, halo + L:].abs().max() == 0  # halos untouched
+    assert out[:, :halo].abs().max() == 0 and out[:, halo + L:].abs().max() == 0  # halos cleared
     dout = torch.randn(N, L + 2 * halo, C, device="cuda")
     ref.backward(dout[:, halo:halo + L].reshape(N * L, C).to(BF).float())
-    dx = torch.zeros(N, L + 2, C, device="cuda", dtype=BF)
+    dx = torch.full((N, L + 2, C), 7.0, device="cuda", dtype=BF)
     dg, db, dsum = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
     K.rownorm_bwd(bf(dout), y, mean, rstd, N * L, C, gamma, beta, dx_bf16=dx, dgamma=dg, dbeta=db, dxsum=dsum,
                   dout_map=K.rowmap(L, L + 2 * halo, halo), dx_map=K.rowmap(L, L + 2, 1), unbiased=True, relu=True)
     close(dx[:, 1:1 + L].reshape(N * L, C), yr.grad, 2e-2, 2e-2, "channelnorm dx")
+    assert dx[:, 0].abs().max() == 0 and dx[:, L + 1].abs().max() == 0
     close(dg, g_.grad, 1e-3, 1e-2, "channelnorm dgamma")
     close(db, b_.grad, 1e-3, 1e-2, "channelnorm dbeta")
     close(dsum, yr.grad.sum(0), 1e-2, 3e-2, "channelnorm dxsum")
