@@ -124,8 +124,9 @@ class _HeadsFn(torch.autograd.Function):
         eng = ctx.eng
         B, W, H = ctx.shape
         dx, gflat = eng.backward(ctx.saved, dout.contiguous().float().view(eng.G, B * W, eng.dout))
-        ops.grad_ready("criterion", gflat)
-        return (dx.view(B, W, H), None, None, *eng.arena.grad_views(gflat))
+        views = eng.arena.grad_views(gflat)
+        ops.grad_ready("criterion", gflat, eng.arena.params, views)
+        return (dx.view(B, W, H), None, None, *views)
 
 
 class BaseCriterion(nn.Module):
@@ -289,5 +290,6 @@ class _CriterionFn(torch.autograd.Function):
         dcw, gflat = eng.backward(ctx.saved, dpred)
         dc[:, :W] = dcw.view(B, W, H)
         ops.join()
-        ops.grad_ready("criterion", gflat)
-        return (dc, dz.view(B, S, D), None, None, None, None, None, None, *eng.arena.grad_views(gflat))
+        views = eng.arena.grad_views(gflat)
+        ops.grad_ready("criterion", gflat, eng.arena.params, views)
+        return (dc, dz.view(B, S, D), None, None, None, None, None, None, *views)

@@ -52,7 +52,7 @@ class BucketedAllReduce:
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             t.div_(self.world)
 
-    def _on_grad_ready(self, stage, gflat):
+    def _on_grad_ready(self, stage, gflat, params=None, grads=None):
         self.reduced.append((stage, gflat.numel()))
         self._arenas.append(gflat.untyped_storage().data_ptr())
         if not self.on_gpu:

@@ -254,6 +254,14 @@ def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld, dlo
     _run("cpc_nce_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
+def adam_step(table, n_spans, blocks, state, advance=True):
+    """cpc_adam_step: `table` = device bytes of a CpcAdamSpan array, `state` = device double[8]."""
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=28.0 * blocks * lib().cpc_adam_chunk())
+    _run("cpc_adam_step", (ctypes.c_void_p(table.data_ptr()), n_spans, ctypes.c_int64(blocks),
+                           ctypes.c_void_p(state.data_ptr()), int(advance), stream_ptr(),))
+
+
 CELL = {"LSTM": 0, "GRU": 1, "RNN": 2}
 
 

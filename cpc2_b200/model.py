@@ -253,6 +253,7 @@ class _EncoderFn(torch.autograd.Function):
         ctx.x2 = x2
         ctx.acts, ctx.ys, ctx.means, ctx.rstds, ctx.packed = acts, ys, means, rstds, packed
         ctx.p = p
+        ctx.params = list(params)
         ctx.plan = plan
         return z32.permute(0, 2, 1)
 
@@ -325,7 +326,7 @@ class _EncoderFn(torch.autograd.Function):
             k = GEOMETRY[l][0]
             dw, dcb, dg, db = gv[4 * l:4 * l + 4]
             grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
-        ops.grad_ready("encoder", gflat)
+        ops.grad_ready("encoder", gflat, ctx.params, grads)
         return (None, None, *grads)
 
 
@@ -473,6 +474,7 @@ class _RecurrentFn(torch.autograd.Function):
             c_ns.append(c_n)
             prev_pad = h_pad
         ctx.saved = saved
+        ctx.params = list(params)
         ctx.dims = (N, S, Cin, H, nl, cell)
         return out, torch.stack(h_ns), torch.stack(c_ns)
 
@@ -530,7 +532,7 @@ class _RecurrentFn(torch.autograd.Function):
             d = dx.view(N, S, Kin)
         ops.join()
         del keep
-        ops.grad_ready("ar", gflat)
+        ops.grad_ready("ar", gflat, ctx.params, grads)
         return (d, None, None, None, None, None, *grads)
 
 

@@ -21,9 +21,11 @@ GRAD_F32 = False
 GRAD_READY = []
 
 
-def grad_ready(stage, gflat):
+def grad_ready(stage, gflat, params=None, grads=None):
+    """`params` / `grads`: the parameters whose gradients live in `gflat` and their views of it (what an optimizer
+    that steps a stage as soon as it is reduced needs: autograd has not assigned .grad yet at this point)."""
     for fn in GRAD_READY:
-        fn(stage, gflat)
+        fn(stage, gflat, params, grads)
 
 
 # ---- independent kernels on forked streams -----------------------------------------------------------
@@ -74,10 +76,17 @@ class side:
         return False
 
 
+# side streams that only an explicit join(i) waits for (9: the staged optimizer step, which must not be pulled onto
+# the critical path by the blanket join() at the end of a module's backward)
+DETACHED = {9}
+
+
 def join(index=None):
     cur = torch.cuda.current_stream()
     for item in list(_PENDING):
         key, s, parent = item
+        if index is None and key[1] in DETACHED:
+            continue
         if parent.cuda_stream == cur.cuda_stream and key[0] == cur.device.index and (index is None or key[1] == index):
             cur.wait_stream(s)
             _PENDING.remove(item)

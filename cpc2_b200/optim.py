@@ -1,0 +1,181 @@
+"""Drop-in for the optimizer of cpc/train.py:472-479 (`torch.optim.Adam(g_params, lr, betas, eps)`), SURVEY 8f.1:
+one multi-tensor sm_100a launch (cpc_adam_step) updates every parameter of the model and the criterion.
+
+`FusedAdam` is a `torch.optim.Optimizer`: `param_groups` (so the reference's LR schedulers, train.py:502-517, drive
+`lr` as usual), `step()`, `zero_grad()`, and a `state_dict()` in torch.optim.Adam's format (`step`, `exp_avg`,
+`exp_avg_sq` per parameter), so optimizer states of reference checkpoints load and ours load back into
+torch.optim.Adam (train.py:486-490).  The step counter, learning rate and bias corrections live in device memory:
+a `step()` captured in a CUDA graph replays correctly (`sync_hyper()` pushes a changed lr before the replay).
+"""
+import torch
+
+from . import _lib
+from . import kernels as K
+from . import ops
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False):
+        if weight_decay != 0 or amsgrad:
+            raise NotImplementedError("cpc2_b200.FusedAdam: weight_decay / amsgrad are not used by cpc/train.py")
+        if not 0.0 <= lr or not 0.0 <= eps or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0:
+            raise ValueError("Invalid Adam hyper-parameter")
+        super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=0, amsgrad=False))
+        self._groups = [None] * len(self.param_groups)  # per group: device state, span tables, flat moments
+        self._dp, self._done, self._advanced = None, set(), False
+
+    # ------------------------------------------------------------------------------------------ internals
+    def _init_group(self, gi):
+        group = self.param_groups[gi]
+        params = [p for p in group["params"] if p.requires_grad]
+        if not params:
+            return None
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("cpc2_b200.FusedAdam runs on CUDA parameters only (no CPU fallback)")
+        total = sum((p.numel() + 3) // 4 * 4 for p in params)
+        m_flat = torch.zeros(total, device=dev)
+        v_flat = torch.zeros(total, device=dev)
+        off, step0 = 0, 0.0
+        for p in params:
+            n = p.numel()
+            st = self.state[p]
+            m, v = m_flat[off:off + n].view(p.shape), v_flat[off:off + n].view(p.shape)
+            if "exp_avg" in st:  # loaded state (load_state_dict) or a previous table: keep the values
+                m.copy_(st["exp_avg"])
+                v.copy_(st["exp_avg_sq"])
+                step0 = max(step0, float(st.get("step", 0.0)))
+            st["exp_avg"], st["exp_avg_sq"] = m, v
+            off += (n + 3) // 4 * 4
+        b1, b2 = group["betas"]
+        hyper = (group["lr"], b1, b2, group["eps"])
+        state = torch.tensor([step0, hyper[0], b1, b2, hyper[3], 0.0, 0.0, 0.0], dtype=torch.float64, device=dev)
+        g = dict(params=params, ids={id(p) for p in params}, state=state, hyper=hyper, tables={}, staging=[], m=m_flat,
+                 v=v_flat, pinned=torch.empty(8, dtype=torch.float64).pin_memory())
+        self._groups[gi] = g
+        return g
+
+    def _table(self, g, name, pairs):
+        """Device span table `name` over (parameter, gradient) pairs; rebuilt only when a pointer changed."""
+        chunk = _lib.lib().cpc_adam_chunk()
+        keys = [(p.data_ptr(), gr.data_ptr(), p.numel()) for p, gr in pairs]
+        t = g["tables"].setdefault(name, dict(keys=None, table=None, n_spans=0, blocks=0))
+        if keys == t["keys"]:
+            return t
+        spans = (_lib.AdamSpan * max(len(pairs), 1))()
+        blocks = 0
+        for i, (p, gr) in enumerate(pairs):
+            if gr.dtype != torch.float32 or not gr.is_contiguous() or not p.is_contiguous() or p.dtype != torch.float32 \
+                    or gr.numel() != p.numel():
+                raise RuntimeError("cpc2_b200.FusedAdam: parameters and gradients must be contiguous fp32 of equal size")
+            st = self.state[p]
+            spans[i].p, spans[i].g = p.data_ptr(), gr.data_ptr()
+            spans[i].m, spans[i].v = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+            spans[i].p16 = None
+            spans[i].n, spans[i].first_block = p.numel(), blocks
+            blocks += (p.numel() + chunk - 1) // chunk
+        # pinned staging buffer + async copy: capturable (a captured step() replays the copy, so every staging
+        # buffer stays alive and untouched for the lifetime of the optimizer)
+        raw = torch.frombuffer(bytearray(bytes(spans)), dtype=torch.uint8)
+        host = torch.empty(raw.numel(), dtype=torch.uint8).pin_memory()
+        host.copy_(raw)
+        g["staging"].append(host)
+        if t["table"] is None or t["table"].numel() != host.numel() or torch.cuda.is_current_stream_capturing():
+            t["table"] = torch.empty(host.numel(), dtype=torch.uint8, device=g["state"].device)
+        t["table"].copy_(host, non_blocking=True)
+        t["keys"], t["n_spans"], t["blocks"] = keys, len(pairs), blocks
+        return t
+
+    # ------------------------------------------------------------------------------------------ staged stepping
+    def attach(self, dp=None):
+        """Step each gradient bucket as soon as its module announces it (ops.grad_ready: criterion heads first,
+        90 % of the parameters), on a side stream -- after the bucket's all-reduce when `dp` (BucketedAllReduce) is
+        given -- so the update overlaps the rest of the backward.  step() then only joins and handles leftovers."""
+        if len(self.param_groups) != 1:
+            raise NotImplementedError("FusedAdam.attach: staged stepping supports a single parameter group")
+        self._dp = dp
+        if self._groups[0] is None:
+            self._init_group(0)
+        if self._on_stage not in ops.GRAD_READY:
+            ops.GRAD_READY.append(self._on_stage)  # after dp's hook: the all-reduce is queued first
+        return self
+
+    def detach(self):
+        if self._on_stage in ops.GRAD_READY:
+            ops.GRAD_READY.remove(self._on_stage)
+
+    def _on_stage(self, stage, gflat, params=None, grads=None):
+        g = self._groups[0]
+        if params is None or g is None:
+            return
+        mine = g["ids"]
+        pairs = [(p, gr) for p, gr in zip(params, grads) if gr is not None and id(p) in mine and id(p) not in self._done]
+        if not pairs:
+            return
+        if not torch.cuda.is_current_stream_capturing():
+            self.sync_hyper()
+        dp = self._dp
+        if dp is not None and dp.world > 1 and dp.on_gpu:
+            dp.stream.wait_stream(torch.cuda.current_stream())
+            dp._pending = True
+            ctx = torch.cuda.stream(dp.stream)  # behind this bucket's all-reduce
+        else:
+            ctx = ops.side(9)
+        with ctx:
+            t = self._table(g, stage, pairs)
+            K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
+        self._advanced = True
+        self._done.update(id(p) for p, _ in pairs)
+
+    def sync_hyper(self):
+        """Pushes lr / betas / eps of param_groups to the device if a scheduler changed them (call before replaying
+        a CUDA graph that contains step(); step() itself calls it when it runs eagerly)."""
+        for gi, group in enumerate(self.param_groups):
+            g = self._groups[gi]
+            if g is None:
+                continue
+            b1, b2 = group["betas"]
+            hyper = (group["lr"], b1, b2, group["eps"])
+            if hyper != g["hyper"]:
+                g["pinned"][:4] = torch.tensor(hyper, dtype=torch.float64)
+                g["state"][1:5].copy_(g["pinned"][:4], non_blocking=True)
+                g["hyper"] = hyper
+
+    # ------------------------------------------------------------------------------------------ Optimizer API
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        capturing = torch.cuda.is_current_stream_capturing()
+        ops.join(9)  # staged launches of this iteration (FusedAdam.attach); dp.finish() has joined dp.stream
+        for gi in range(len(self.param_groups)):
+            g = self._groups[gi] or self._init_group(gi)
+            if g is None:
+                continue
+            if not capturing:
+                self.sync_hyper()
+            pairs = [(p, p.grad) for p in g["params"] if p.grad is not None and id(p) not in self._done]
+            if pairs:
+                t = self._table(g, "rest", pairs)
+                K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not (self._advanced and gi == 0))
+            # the kernel wrote through raw pointers: tell autograd (and ops.Prefetched, which validates bf16 weight
+            # shadows by version counter) that the parameters changed
+            torch.autograd.graph.increment_version(g["params"])
+        self._done.clear()
+        self._advanced = False
+        return loss
+
+    def state_dict(self):
+        for gi, g in enumerate(self._groups):
+            if g is None:
+                continue
+            step = g["state"][0:1].to(torch.float32).cpu()[0]
+            for p in g["params"]:
+                self.state[p]["step"] = step.clone()
+        return super().state_dict()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._groups = [None] * len(self.param_groups)  # rebuilt (moments re-homed, step taken over) at the next step

@@ -188,8 +188,10 @@ class GraphedTrainStep:
     all-reduces on a side stream inside the same graph."""
 
     def __init__(self, cpcModel, cpcCriterion, batch, sizeWindow, device="cuda", warmup=3, train_mode=True,
-                 after_backward=None):
-        self.model, self.crit = cpcModel, cpcCriterion
+                 after_backward=None, optimizer=None):
+        """`optimizer` (cpc2_b200.optim.FusedAdam, or any capturable optimizer): its step() becomes part of the
+        graph, after `after_backward` (the data-parallel all-reduce) -- the whole of train.py:95-113 in one replay."""
+        self.model, self.crit, self.optimizer = cpcModel, cpcCriterion, optimizer
         self.static_seq = torch.zeros(batch, 2, 1, sizeWindow, device=device)
         self.static_label = torch.zeros(batch, dtype=torch.long, device=device)
         self.params = [p for p in list(cpcModel.parameters()) + list(cpcCriterion.parameters()) if p.requires_grad]
@@ -203,6 +205,8 @@ class GraphedTrainStep:
                 forwardBackward(cpcModel, cpcCriterion, self.static_seq, self.static_label)
                 if after_backward is not None:
                     after_backward()
+                if optimizer is not None:
+                    optimizer.step()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
@@ -211,6 +215,8 @@ class GraphedTrainStep:
             self.losses, self.acc = forwardBackward(cpcModel, cpcCriterion, self.static_seq, self.static_label)
             if after_backward is not None:
                 after_backward()
+            if optimizer is not None:
+                optimizer.step()
 
     def _zero(self):
         for p in self.params:
@@ -219,5 +225,7 @@ class GraphedTrainStep:
     def step(self, sequence=None, non_blocking=True):
         if sequence is not None:
             self.static_seq.copy_(sequence, non_blocking=non_blocking)
+        if self.optimizer is not None and hasattr(self.optimizer, "sync_hyper"):
+            self.optimizer.sync_hyper()  # a scheduler may have changed lr since the last replay
         self.graph.replay()
         return self.losses, self.acc

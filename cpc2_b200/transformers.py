@@ -299,5 +299,6 @@ class _TransformerFn(torch.autograd.Function):
         st = ctx.stack
         N, S_in, d = ctx.shape
         dx, gflat = st.backward(ctx.saved, dout.contiguous().float().view(1, N * S_in, st.dout))
-        ops.grad_ready("ar", gflat)
-        return (dx.view(N, S_in, d), None, None, *st.arena.grad_views(gflat))
+        views = st.arena.grad_views(gflat)
+        ops.grad_ready("ar", gflat, st.arena.params, views)
+        return (dx.view(N, S_in, d), None, None, *views)

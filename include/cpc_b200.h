@@ -150,6 +150,22 @@ int cpc_colsum(const void* in, int in_is_bf16, void* out, int64_t rows, int C, i
 /* out[i] (+)= sum_g in[g][i] */
 int cpc_groupsum(const void* in, int in_is_bf16, void* out_f32, void* out_bf16, int64_t n, int groups,
                  int accumulate, void* stream);
+/* ------------------------------------------------------------------------------------------------
+ * Multi-tensor Adam: the optimizer.step() of cpc/train.py:112 with torch.optim.Adam(g_params, lr, betas, eps)
+ * (cpc/train.py:472-479; no weight decay, no amsgrad) as ONE launch over every parameter.
+ * spans: DEVICE array; span i covers ceil(n / cpc_adam_chunk()) CTAs starting at first_block (prefix sum,
+ * total_blocks = the sum).  state: DEVICE double[8] = {step, lr, beta1, beta2, eps, -, -, -}; with advance != 0
+ * the call first advances step by one and derives the bias corrections on the device (CUDA-graph safe) -- an
+ * optimizer step issued in several launches (one per gradient bucket, as each is reduced) advances once.
+ * p16 (optional): bf16 copy of the updated parameter, written in the same pass. */
+typedef struct {
+  void* p; const void* g; void* m; void* v; void* p16;
+  int64_t n; int64_t first_block;
+} CpcAdamSpan;
+int cpc_adam_step(const CpcAdamSpan* spans_dev, int n_spans, int64_t total_blocks, double* state_dev, int advance,
+                  void* stream);
+int cpc_adam_chunk(void);
+
 /* extIdx = ((seqIdx + t) mod S) + batchIdx*S, int64, flat (b,n,t) order -- criterion.py:256-266 */
 int cpc_neg_ext_index(const void* batch_idx, const void* seq_idx, void* ext, int B, int NEG, int W, int S,
                       void* stream);

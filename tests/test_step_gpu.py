@@ -260,3 +260,106 @@ def test_past_future_split_matches_concatenated_call(over):
             continue
         assert cosine(gs, gr) > 0.99999, (k, cosine(gs, gr))
         assert (gs - gr).abs().max() <= 5e-3 * gr.abs().max() + 1e-7, k  # atomics: fp32 summation order
+
+
+def test_fused_adam_matches_torch_adam():
+    """cpc2_b200.optim.FusedAdam against torch.optim.Adam (cpc/train.py:472-479) over 5 steps on the same gradients:
+    parameters and moments agree to fp32 rounding; the state_dict round-trips into torch.optim.Adam and back."""
+    _need_gpu()
+    from cpc2_b200.optim import FusedAdam
+    torch.manual_seed(3)
+    shapes = [(256, 256, 8), (256,), (1, 256, 1), (37,), (3, 5, 7), (4099,), (1024, 768)]
+    ours = [torch.nn.Parameter(torch.randn(*s, device="cuda")) for s in shapes]
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in ours]
+    oa = FusedAdam(ours, lr=2e-4, betas=(0.9, 0.999), eps=1e-8)
+    ob = torch.optim.Adam(ref, lr=2e-4, betas=(0.9, 0.999), eps=1e-8)
+    sched_a = torch.optim.lr_scheduler.StepLR(oa, 2, gamma=0.5)
+    sched_b = torch.optim.lr_scheduler.StepLR(ob, 2, gamma=0.5)
+    for it in range(5):
+        for p, q in zip(ours, ref):
+            g = torch.randn_like(p) * (10.0 ** (it - 2))
+            p.grad, q.grad = g.clone(), g.clone()
+        oa.step()
+        ob.step()
+        oa.zero_grad()
+        ob.zero_grad()
+        sched_a.step()
+        sched_b.step()
+        for p, q in zip(ours, ref):
+            assert torch.allclose(p, q, rtol=2e-6, atol=1e-7), (it, (p - q).abs().max())
+    sa, sb = oa.state_dict(), ob.state_dict()
+    for k in sb["state"]:
+        assert float(sa["state"][k]["step"]) == float(sb["state"][k]["step"]) == 5
+        assert torch.allclose(sa["state"][k]["exp_avg"], sb["state"][k]["exp_avg"], rtol=1e-5, atol=1e-9)
+        assert torch.allclose(sa["state"][k]["exp_avg_sq"], sb["state"][k]["exp_avg_sq"], rtol=1e-5, atol=1e-12)
+    # round trip: torch state -> FusedAdam, one more step on both
+    oc = FusedAdam(ours, lr=2e-4)
+    oc.load_state_dict(sb)
+    for p, q in zip(ours, ref):
+        p.data.copy_(q.data)
+        g = torch.randn_like(p)
+        p.grad, q.grad = g.clone(), g.clone()
+    oc.step()
+    ob.step()
+    for p, q in zip(ours, ref):
+        assert torch.allclose(p, q, rtol=2e-6, atol=1e-7)
+
+
+def test_staged_adam_equals_single_launch():
+    """FusedAdam.attach(): stepping each gradient bucket from the ops.grad_ready hook (side stream, one counter
+    advance per iteration) gives bit-identical parameters to one launch after backward."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    g = torch.Generator().manual_seed(3)
+    seq = (0.1 * torch.randn(4, 2, 1, args.sizeWindow, generator=g)).cuda()
+    label = torch.zeros(4, dtype=torch.long, device="cuda")
+    finals = []
+    for staged in (False, True):
+        model, crit = build(args)
+        model.eval()
+        crit.eval()
+        opt = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=1e-3)
+        if staged:
+            opt.attach()
+        try:
+            for it in range(3):
+                torch.manual_seed(50 + it)
+                T.forwardBackward(model, crit, seq, label)
+                opt.step()
+                opt.zero_grad()
+        finally:
+            opt.detach()
+        torch.cuda.synchronize()
+        assert float(opt._groups[0]["state"][0]) == 3
+        finals.append([p.detach().clone() for p in list(crit.parameters()) + list(model.parameters())])
+    for a, b in zip(*finals):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)  # gradients differ by fp32 atomics order only
+
+
+def test_graphed_step_with_fused_adam_learns():
+    """GraphedTrainStep(optimizer=FusedAdam): forward + backward + Adam in one CUDA-graph replay; the loss on a
+    predictable batch (past == future) falls, and the device-side step counter advances once per replay."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    model, crit = build(args)
+    opt = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=2e-3)
+    g = torch.Generator().manual_seed(7)
+    base = torch.randn(8, 1, 1, args.sizeWindow, generator=g) * 0.1
+    seq = torch.cat([base, base], dim=1).cuda()
+    opt.attach()  # staged: each module's parameters are stepped as soon as its gradients exist
+    try:
+        step = T.GraphedTrainStep(model, crit, 8, args.sizeWindow, warmup=2, optimizer=opt)
+    finally:
+        opt.detach()
+    n0 = float(opt._groups[0]["state"][0])
+    hist = []
+    for it in range(160):
+        losses, _ = step.step(seq)
+        hist.append(losses.mean().item())
+    assert float(opt._groups[0]["state"][0]) == n0 + 160
+    first, last = sum(hist[:5]) / 5, sum(hist[-5:]) / 5
+    assert all(h == h for h in hist) and last < first - 0.05, (first, last)
