@@ -110,7 +110,7 @@ def cpu_step_seconds(args, B, steps, warmup):
     return sum(times) / len(times), torch.get_num_threads()
 
 
-def run_reference(opt):
+def run_reference(opt, out):
     """--impl reference: the reference algorithm's CPU implementation (oracle port) with every host thread."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -134,7 +134,7 @@ def run_reference(opt):
         "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    out.emit(json.dumps(line))
 
 
 def kernel_profile(model, crit, seq, label):
@@ -166,7 +166,7 @@ def kernel_profile(model, crit, seq, label):
     return sorted(rows.values(), key=lambda r: -r["ms"]), t0.elapsed_time(t1), prof
 
 
-def run_ours(opt):
+def run_ours(opt, out):
     import torch.distributed as dist
     from cpc2_b200 import _lib
     from cpc2_b200 import kernels as K
@@ -287,7 +287,7 @@ def run_ours(opt):
                                 "sample": f"2 full fwd+bwd steps of the same batch (8 x 20480 samples) after 1 warm-up, "
                                           f"oracle/cpc_oracle.py fp32, {threads} threads, {sec:.2f} s/step"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        out.emit(json.dumps(line))
     if world > 1:
         # The step's CUDA graph holds captured NCCL launches; tearing the communicator down while the graph is
         # alive blocks inside ncclCommDestroy (observed at N=2: JSON printed, process never exited).  All ranks
@@ -299,6 +299,20 @@ def run_ours(opt):
         os._exit(0)
 
 
+class StdoutToStderr:
+    """Everything libraries print on fd 1 (NCCL's version banner, ...) goes to stderr; the JSON line alone reaches
+    the real stdout (emit())."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, text):
+        sys.stdout.flush()
+        os.write(self.real, (text + "\n").encode())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -306,10 +320,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     opt = ap.parse_args()
+    out = StdoutToStderr()
     if opt.impl == "reference":
-        run_reference(opt)
+        run_reference(opt, out)
     else:
-        run_ours(opt)
+        run_ours(opt, out)
 
 
 if __name__ == "__main__":
