@@ -43,6 +43,15 @@ def peaks():
     return dict(hbm=6650.0, tensor=1400.0, tensor_burst=1590.0, source="fallback (B200_PROFILING.md)")
 
 
+def traffic_of(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel, {}).get("bytes_per_launch")
+    except (OSError, ValueError):
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -274,7 +283,9 @@ def run_ours(opt, out):
             roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"],
                     "note": f"{top['kind']}-bound kernel; see DESIGN.md"}
         roof.update({"kernel": top["name"], "launches_per_step": top["launches"], "share_of_kernel_time": top["ms"] / total,
-                     "avg_launch_us": 1e3 * top["ms"] / top["launches"], "traffic": None, "peak_source": pk["source"]})
+                     "avg_launch_us": 1e3 * top["ms"] / top["launches"], "traffic": traffic_of(top["name"]),
+                     "traffic_unit": "bytes per launch (ncu dram read+write, profiles/traffic.json)",
+                     "peak_source": pk["source"]})
         line["roofline"] = roof
         line["kernels"] = [
             {"name": r["name"], "launches": r["launches"], "us": round(1e3 * r["ms"], 1), "share": round(r["ms"] / total, 4),
