@@ -15,7 +15,7 @@ import torch.nn as nn
 from . import kernels as K
 from . import ops
 from .ops import BF16
-from .transformers import TransformerStack, buildTransformerAR
+from .transformers import TransformerStack, buildMultHeadTransformerAR, buildTransformerAR
 
 
 class PredictionNetwork(nn.Module):
@@ -73,11 +73,45 @@ class PredictionNetwork(nn.Module):
         return [(preds[k].unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(len(self.predictors))]
 
 
+class MultiHeadPredictionNetwork(nn.Module):
+    """cpc/criterion/criterion.py:44-94 (--multihead_rnn): ONE transformer block whose feed-forward network emits all
+    nPredicts predictions (MultiClassifierTransformerHead); prediction[:, :, k] scores the candidates of step k."""
+
+    def __init__(self, nPredicts, dimOutputAR, dimOutputEncoder, rnnMode='transformer_multi', dropout=False,
+                 sizeInputSeq=116, transformer_pruning=0):
+        super().__init__()
+        self.dimOutputAR = dimOutputAR
+        if dropout:
+            raise NotImplementedError("cpc2_b200: --dropout on the predictions is not on the accelerated path")
+        self.dropout = None
+        self.nPredicts = nPredicts
+        if rnnMode == 'transformer':
+            self.predictor = buildMultHeadTransformerAR(dimOutputEncoder, dimOutputAR, nLayers=1, sizeSeq=sizeInputSeq,
+                                                        abspos=False, nHeads=nPredicts)
+        elif rnnMode == 'transformer_adaptive_span':
+            raise NotImplementedError("cpc2_b200: transformer_adaptive_span is broken in the reference itself "
+                                      "(missing import, criterion.py:70-76)")
+        else:
+            raise ValueError(f"unknown mode {rnnMode}")
+
+    def engine(self):
+        return self.predictor[0].stack()
+
+    def prefetch(self):
+        self.engine().arena.prefetch(5)
+
+    def forward(self, c, candidates):
+        assert (len(candidates) == self.nPredicts)
+        eng = self.engine()
+        preds = _HeadsFn.apply(c, eng, self.training, *eng.arena.params)  # [K, B, W, D] fp32
+        return [(preds[k].unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(self.nPredicts)]
+
+
 class LinearHeads:
     """K bias-free Linear heads on the same input: one grouped GEMM."""
 
     def __init__(self, linears):
-        self.G = len(linears)
+        self.G = self.n_out = len(linears)
         self.dout, self.d = linears[0].weight.shape
         if self.d % 8 or self.dout % 8:
             raise NotImplementedError("LinearHeads: dimensions must be multiples of 8")
@@ -117,13 +151,13 @@ class _HeadsFn(torch.autograd.Function):
         xb = K.cast_bf16(c.detach().contiguous().float()).view(B * W, H)
         out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True)
         ctx.eng, ctx.saved, ctx.shape = eng, saved, (B, W, H)
-        return out32.view(eng.G, B, W, eng.dout)
+        return out32.view(eng.n_out, B, W, eng.dout)
 
     @staticmethod
     def backward(ctx, dout):
         eng = ctx.eng
         B, W, H = ctx.shape
-        dx, gflat = eng.backward(ctx.saved, dout.contiguous().float().view(eng.G, B * W, eng.dout))
+        dx, gflat = eng.backward(ctx.saved, dout.contiguous().float().view(eng.n_out, B * W, eng.dout))
         views = eng.arena.grad_views(gflat)
         ops.grad_ready("criterion", gflat, eng.arena.params, views)
         return (dx.view(B, W, H), None, None, *views)
@@ -147,9 +181,12 @@ class CPCUnsupersivedCriterion(BaseCriterion):
                  n_skipped=0, growth_rate=None, inflection_point_x=None):
         super().__init__()
         if multihead_rnn:
-            raise NotImplementedError("cpc2_b200: --multihead_rnn is a 'next' row (SURVEY 8f.3), not built yet")
-        self.wPrediction = PredictionNetwork(nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=rnnMode,
-                                             dropout=dropout, sizeInputSeq=sizeInputSeq - nPredicts)
+            self.wPrediction = MultiHeadPredictionNetwork(nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=rnnMode,
+                                                          dropout=dropout, sizeInputSeq=sizeInputSeq - nPredicts,
+                                                          transformer_pruning=transformer_pruning)
+        else:
+            self.wPrediction = PredictionNetwork(nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=rnnMode,
+                                                 dropout=dropout, sizeInputSeq=sizeInputSeq - nPredicts)
         self.nSkipped = n_skipped
         self.nPredicts = nPredicts
         self.negativeSamplingExt = negativeSamplingExt

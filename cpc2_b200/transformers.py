@@ -118,6 +118,52 @@ def buildTransformerAR(dimEncoded, dimAR, nLayers, sizeSeq, abspos):
     return nn.Sequential(*layerSequence)
 
 
+class MultiClassifierTransformerHead(nn.Module):
+    """cpc/transformers.py:137-158 (--multihead_rnn): one attention block whose feed-forward network emits
+    nclassifiers x dmodel features; last_linear and the final LayerNorm are shared by the classifiers.
+    forward(x [N, S, dmodel]) -> [N, S, nclassifiers, dout]."""
+
+    def __init__(self, nclassifiers, sizeSeq=32, dmodel=512, dout=512, dff=2048, dropout=0.1, nheads=8, abspos=False):
+        super().__init__()
+        self.multihead = MultiHeadAttention(sizeSeq, dropout, dmodel, nheads, abspos)
+        self.ln_multihead = nn.LayerNorm(dmodel)
+        self.ffnetwork = FFNetwork(dmodel, dmodel * nclassifiers, dff, dropout)
+        self.last_linear = nn.Linear(dmodel, dout)
+        self.ln_ffnetwork = nn.LayerNorm(dout)
+        self.nclassifiers = nclassifiers
+        self.dout = dmodel  # as in the reference (:151): the width of one classifier slice
+        self.sizeSeq, self.dmodel, self.dff = sizeSeq, dmodel, dff
+        self.dropout_p, self.nheads = dropout, nheads
+        self._stack = None
+
+    def stack(self):
+        if self._stack is None:
+            object.__setattr__(self, "_stack", MultiHeadStack(self))
+        return self._stack
+
+    def prefetch(self):
+        self.stack().arena.prefetch(4)
+
+    def forward(self, x):
+        ops.require_cuda(x)
+        st = self.stack()
+        N, S_in, _ = x.shape
+        out = _MultiHeadFn.apply(x, st, self.training, *st.arena.params)  # [K, N*S, dout]
+        return out.view(st.n_out, N, S_in, st.dout).permute(1, 2, 0, 3)
+
+
+def buildMultHeadTransformerAR(dimEncoded, dimAR, nLayers, sizeSeq, abspos, nHeads):
+    """cpc/transformers.py:190-212."""
+    layerSequence = []
+    if abspos:
+        layerSequence += [StaticPositionEmbedding(sizeSeq, dimAR)]
+    layerSequence += [TransformerLayer(sizeSeq=sizeSeq, dmodel=dimAR, dout=dimEncoded, abspos=abspos)
+                      for i in range(nLayers - 1)]
+    layerSequence += [MultiClassifierTransformerHead(nHeads, dmodel=dimAR, dout=dimEncoded, sizeSeq=sizeSeq,
+                                                     abspos=abspos)]
+    return nn.Sequential(*layerSequence)
+
+
 class TransformerStack:
     """G independent TransformerLayers (identical shapes) executed together.  Owns the parameter arena:
     stacked operands [G][rows][cols] are contiguous spans of it, their bf16 shadow is one cast per step."""
@@ -128,7 +174,8 @@ class TransformerStack:
         self.layers = list(layers)
         l0 = self.layers[0]
         self.G = len(self.layers)
-        self.S, self.d, self.dout, self.dff = l0.sizeSeq, l0.dmodel, l0.dout, l0.dff
+        self.S, self.d, self.dout, self.dff = l0.sizeSeq, l0.dmodel, l0.last_linear.out_features, l0.dff
+        self.n_out = self.G  # prediction groups this engine emits
         self.Hh, self.dk = l0.nheads, l0.dmodel // l0.nheads
         self.p_drop = l0.dropout_p
         self.relpos = l0.multihead.Att.relpos
@@ -301,4 +348,144 @@ class _TransformerFn(torch.autograd.Function):
         dx, gflat = st.backward(ctx.saved, dout.contiguous().float().view(1, N * S_in, st.dout))
         views = st.arena.grad_views(gflat)
         ops.grad_ready("ar", gflat, st.arena.params, views)
+        return (dx.view(N, S_in, d), None, None, *views)
+
+
+class MultiHeadStack(TransformerStack):
+    """Engine of MultiClassifierTransformerHead: the attention half of one TransformerLayer (G = 1), then
+        h1 = dropout(relu(y . W1^T + b1))                                   [T, dff]
+        u_k = y + h1 . W2[k]^T + b2[k]      k = 0..K-1   (one grouped GEMM, h1 and y shared)   [K, T, d]
+        out = LN(u . Wl^T + bl)             (one GEMM / one LayerNorm over the K*T rows)       [K, T, dout]
+    which is exactly the [K, T, dout] layout the criterion's logits GEMM consumes."""
+
+    def __init__(self, layer):
+        super().__init__([layer])
+        self.K = layer.nclassifiers
+        self.n_out = self.K
+
+    def shapes(self):
+        sh = super().shapes()
+        sh["W2"] = (1, self.K * self.d, self.dff)
+        sh["b2"] = (1, self.K * self.d)
+        return sh
+
+    def forward(self, x, T, shared, training, want_f32=False):
+        d, dout, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
+        if T % S != 0:
+            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+        if x.dim() != 2:
+            raise ValueError("MultiHeadStack takes one [T, d] input")
+        Bt = T // S
+        dev = x.device
+        P32 = self.spans(self.arena.ensure())
+        P16 = self.spans(self.arena.bf16())
+        drop = self.p_drop if training else 0.0
+        rng = ops.DropoutState.next(dev) if drop > 0 else None
+        qkv = torch.empty(1, T, 3 * d, device=dev, dtype=BF16)
+        ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=1, x_shared=True, out_bf16=qkv)
+        att = torch.empty(1, T, d, device=dev, dtype=BF16)
+        probs = torch.empty(1, Bt, self.Hh, S, S, device=dev, dtype=BF16)
+        K.attn_fwd(qkv, P32.get("krel"), att, probs, 1, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        pre1 = torch.empty(1, T, d, device=dev, dtype=BF16)
+        ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0))
+        y = torch.empty(T, d, device=dev, dtype=BF16)
+        mean1 = torch.empty(T, device=dev)
+        rstd1 = torch.empty(T, device=dev)
+        K.rownorm_fwd(pre1, T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
+        h1 = torch.empty(T, dff, device=dev, dtype=BF16)
+        ops.linear_fwd(y, P16["W1"].view(dff, d), T, dff, d, out_bf16=h1, bias=P32["b1"], relu=True, rng=rng,
+                       rng_site=2, drop_p=drop)
+        u = torch.empty(Kc, T, d, device=dev, dtype=BF16)
+        ops.linear_fwd(h1, P16["W2"].view(Kc, d, dff), T, d, dff, groups=Kc, x_shared=True, out_bf16=u,
+                       bias=P32["b2"], bias_gs=d, res=(y, d, 0))
+        pre2 = torch.empty(Kc * T, dout, device=dev, dtype=BF16)
+        ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"])
+        out = torch.empty(Kc, T, dout, device=dev, dtype=BF16)
+        out32 = torch.empty(Kc, T, dout, device=dev) if want_f32 else None
+        mean2 = torch.empty(Kc * T, device=dev)
+        rstd2 = torch.empty(Kc * T, device=dev)
+        K.rownorm_fwd(pre2, Kc * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
+                      rstd=rstd2, rows_per_group=Kc * T)
+        saved = dict(x=x, T=T, Bt=Bt, P16=P16, P32=P32, rng=rng, drop=drop, qkv=qkv, att=att, probs=probs, pre1=pre1,
+                     y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2, rstd2=rstd2)
+        return out, out32, saved
+
+    def backward(self, sv, dout):
+        """dout bf16 or fp32 [K, T, dout] -> (dx fp32 [T, d], flat fp32 grad arena)."""
+        d, do, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
+        T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
+        dev = dout.device
+        gflat = torch.zeros(self.arena.numel, device=dev)
+        Gd = self.spans(gflat)
+        x = sv["x"]
+        dpre2 = torch.empty(Kc * T, do, device=dev, dtype=BF16)
+        du = torch.empty(Kc, T, d, device=dev, dtype=BF16)
+        dh1 = torch.empty(T, dff, device=dev, dtype=BF16)
+        dy = torch.zeros(T, d, device=dev)
+        dpre1 = torch.empty(1, T, d, device=dev, dtype=BF16)
+        datt = torch.empty(1, T, d, device=dev, dtype=BF16)
+        dqkv = torch.empty(1, T, 3 * d, device=dev, dtype=BF16)
+        dscore = torch.empty_like(sv["probs"])
+        dx = torch.empty(T, d, device=dev)
+        # out = LN2(pre2)
+        K.rownorm_bwd(dout.reshape(Kc * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], Kc * T, do, P32["ln2w"], P32["ln2b"],
+                      dx_bf16=dpre2, dgamma=Gd["ln2w"], dbeta=Gd["ln2b"], rows_per_group=Kc * T)
+        # pre2 = u . Wl^T + bl   (Wl shared by the K slices)
+        with ops.side(0):
+            ops.linear_dw(dpre2, sv["u"].view(Kc * T, d), Gd["Wl"].view(do, d), Kc * T, do, d)
+        with ops.side(1):
+            K.colsum(dpre2, Gd["bl"], Kc * T, do, do)
+        ops.linear_dx(dpre2, P16["Wl"].view(do, d), Kc * T, do, d, out_bf16=du.view(Kc * T, d))
+        # u_k = y + h1 . W2[k]^T + b2[k]
+        with ops.side(0):
+            ops.linear_dw(du, sv["h1"], Gd["W2"].view(Kc, d, dff), T, d, dff, groups=Kc, x_shared=True)
+        with ops.side(1):
+            K.colsum(du, Gd["b2"], T, d, d, T * d, Kc)
+        # dh1 = gate o sum_k du_k . W2[k]: one GEMM whose reduction runs over (slice, feature)
+        A = K.View(du, d, T, Kc, d, T * d, major=0, gmul=0)
+        B = K.View(P16["W2"], dff, d, Kc, dff, d * dff, major=1, gmul=0)
+        K.gemm(A, B, T, dff, Kc * d, k_per_slab=d, out_bf16=dh1, gate=sv["h1"], gate_scale=1.0 / (1.0 - sv["drop"]))
+        # h1 = dropout(relu(y . W1^T + b1))
+        with ops.side(0):
+            ops.linear_dw(dh1, sv["y"], Gd["W1"].view(dff, d), T, dff, d)
+        with ops.side(1):
+            K.colsum(dh1, Gd["b1"], T, dff, dff)
+        # dy = dh1 . W1 + sum_k du_k
+        K.groupsum(du, T * d, Kc, out_f32=dy, accumulate=True)
+        ops.linear_dx(dh1, P16["W1"].view(dff, d), T, dff, d, out_f32=dy, accumulate=True)
+        # y = LN1(pre1)
+        K.rownorm_bwd(dy, sv["pre1"], sv["mean1"], sv["rstd1"], T, d, P32["ln1w"], P32["ln1b"], dx_bf16=dpre1,
+                      dgamma=Gd["ln1w"], dbeta=Gd["ln1b"], rows_per_group=T)
+        # pre1 = x + att . Wo^T
+        with ops.side(0):
+            ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=1)
+        ops.linear_dx(dpre1, P16["Wo"], T, d, d, groups=1, out_bf16=datt)
+        K.attn_bwd(sv["qkv"], P32.get("krel"), sv["att"], sv["probs"], datt, dqkv, dscore, Gd.get("krel"), 1, Bt,
+                   self.Hh, S, self.dk, rng=sv["rng"], site=1, drop_p=sv["drop"])
+        # qkv = x . Wqkv^T
+        with ops.side(0):
+            ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=1, x_shared=True)
+        ops.linear_dx(dqkv, P16["Wqkv"], T, 3 * d, d, groups=1, out_f32=dx.view(1, T, d), res=dpre1)
+        ops.join()
+        return dx, gflat
+
+
+class _MultiHeadFn(torch.autograd.Function):
+    """MultiClassifierTransformerHead as a module (x [N, S, d] fp32 -> [K, N*S, dout] fp32)."""
+
+    @staticmethod
+    def forward(ctx, x, stack, training, *params):
+        N, S_in, d = x.shape
+        xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
+        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True)
+        ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
+        return out32
+
+    @staticmethod
+    def backward(ctx, dout):
+        st = ctx.stack
+        N, S_in, d = ctx.shape
+        dx, gflat = st.backward(ctx.saved, dout.contiguous().float())
+        views = st.arena.grad_views(gflat)
+        ops.grad_ready("criterion", gflat, st.arena.params, views)
         return (dx.view(N, S_in, d), None, None, *views)

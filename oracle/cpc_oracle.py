@@ -206,6 +206,33 @@ def transformer_layer(p, x, prefix, size_seq, nheads=8, relpos=True, masks=None,
     return F.layer_norm(u, (dout,), p[prefix + "ln_ffnetwork.weight"], p[prefix + "ln_ffnetwork.bias"])
 
 
+def multi_classifier_transformer_head(p, x, prefix, size_seq, nclassifiers, nheads=8, relpos=True):
+    """cpc/transformers.py:137-158 (MultiClassifierTransformerHead.forward), eval mode: one attention block, an FFN
+    that emits nclassifiers x dmodel features, the SAME last_linear + LayerNorm applied to every classifier slice:
+        y   = LN(x + Wo(MHA(x)))
+        out = LN(last_linear(lin2(relu(lin1(y))).view(N, S, K, d) + y[:, :, None]))     -> [N, S, K, dout]"""
+    N, S, d = x.shape
+    dk = d // nheads
+
+    def split(t):
+        return t.view(N, S, nheads, dk).transpose(1, 2).reshape(N * nheads, S, dk)
+
+    q = split(x @ p[prefix + "multihead.Wq.weight"].t())
+    k = split(x @ p[prefix + "multihead.Wk.weight"].t())
+    v = split(x @ p[prefix + "multihead.Wv.weight"].t())
+    kr = p[prefix + "multihead.Att.Krelpos"] if relpos else None
+    a = relpos_causal_attention(q, k, v, kr, size_seq)
+    a = a.view(N, nheads, S, dk).transpose(1, 2).reshape(N, S, d)
+    a = a @ p[prefix + "multihead.Wo.weight"].t()
+    y = F.layer_norm(x + a, (d,), p[prefix + "ln_multihead.weight"], p[prefix + "ln_multihead.bias"])
+    h = F.relu(y @ p[prefix + "ffnetwork.lin1.weight"].t() + p[prefix + "ffnetwork.lin1.bias"])
+    f = h @ p[prefix + "ffnetwork.lin2.weight"].t() + p[prefix + "ffnetwork.lin2.bias"]
+    u = f.view(N, S, nclassifiers, d) + y.view(N, S, 1, d)
+    u = u @ p[prefix + "last_linear.weight"].t() + p[prefix + "last_linear.bias"]
+    dout = u.shape[-1]
+    return F.layer_norm(u, (dout,), p[prefix + "ln_ffnetwork.weight"], p[prefix + "ln_ffnetwork.bias"])
+
+
 def static_position_embedding(seqlen, dmodel):
     """cpc/transformers.py:161-173."""
     pos = torch.arange(0., seqlen).unsqueeze(1).repeat(1, dmodel)
@@ -263,8 +290,12 @@ def draw_negative_indices(B, S, W, NEG, generator=None, device="cpu"):
 
 
 def prediction_heads(p, c, K, rnn_mode, size_seq, prefix="wPrediction.predictors.",
-                     masks=None, drop_p=0.0):
-    """cpc/criterion/criterion.py:111-150,161-163: K independent heads on the same c."""
+                     masks=None, drop_p=0.0, multihead=False):
+    """cpc/criterion/criterion.py:111-150,161-163: K independent heads on the same c; multihead
+    (--multihead_rnn, criterion.py:44-94): one MultiClassifierTransformerHead, prediction[:, :, k] per step."""
+    if multihead:
+        pred = multi_classifier_transformer_head(p, c, "wPrediction.predictor.0.", size_seq, K)
+        return [pred[:, :, k] for k in range(K)]
     out = []
     for k in range(K):
         if rnn_mode == "transformer":
@@ -276,7 +307,7 @@ def prediction_heads(p, c, K, rnn_mode, size_seq, prefix="wPrediction.predictors
 
 
 def criterion_forward(p, c, z, batch_idx, seq_idx, K, NEG, rnn_mode="transformer", mode=None,
-                      n_skipped=0, weights=None, masks=None, drop_p=0.0, return_logits=False):
+                      n_skipped=0, weights=None, masks=None, drop_p=0.0, return_logits=False, multihead=False):
     """cpc/criterion/criterion.py:329-363 (forward) with getPrediction :291-302,
     sampleClean :237-286 and PredictionNetwork.forward :152-173.
 
@@ -292,7 +323,7 @@ def criterion_forward(p, c, z, batch_idx, seq_idx, K, NEG, rnn_mode="transformer
     cw = c[:, :W]
     ext = negative_ext_index(batch_idx, seq_idx, B, S, W, NEG)
     neg = z.reshape(-1, D)[ext].view(B, NEG, W, D)
-    preds = prediction_heads(p, cw, K, rnn_mode, W, masks=masks, drop_p=drop_p)
+    preds = prediction_heads(p, cw, K, rnn_mode, W, masks=masks, drop_p=drop_p, multihead=multihead)
     losses, accs, logits_all, arg_all = [], [], [], []
     for k in range(1, K + 1):
         pos = z[:, k:k + W].unsqueeze(1)                       # criterion.py:276-282
@@ -326,7 +357,7 @@ def quality_weighting(signal_quality, W, growth_rate, inflection_point_x):
 # the training step (forward + backward), cpc/train.py:95-109
 # --------------------------------------------------------------------------- #
 def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n_layers=1,
-               rnn_mode="transformer", cpc_mode=None, abspos=False, n_skipped=0, with_grad=True):
+               rnn_mode="transformer", cpc_mode=None, abspos=False, n_skipped=0, with_grad=True, multihead=False):
     """sequence [B,2,1,W] fp32.  Returns dict(loss [1,K], acc [1,K], c, z, grads{name: tensor})."""
     B = sequence.shape[0]
     if with_grad:
@@ -336,7 +367,7 @@ def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n
     c, z = cpc_model_forward(p, combined, ar_mode, n_layers, cpc_mode == "reverse", S, abspos)
     c_past, z_future = c[:B], z[B:]                                      # train.py:102-103
     loss, acc = criterion_forward(p, c_past, z_future, batch_idx, seq_idx, K, NEG, rnn_mode,
-                                  mode=cpc_mode, n_skipped=n_skipped)
+                                  mode=cpc_mode, n_skipped=n_skipped, multihead=multihead)
     out = {"loss": loss.detach(), "acc": acc.detach(), "c": c.detach(), "z": z.detach()}
     if with_grad:
         loss.sum().backward()                                            # train.py:108-109

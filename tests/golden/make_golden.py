@@ -27,6 +27,8 @@ CASES = {
     "tiny_transformer_ar_linear": (dict(SMALL, arMode="transformer", rnnMode="linear"), 3),
     "tiny_lstm_reverse_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", cpc_mode="reverse"), 2),
     "tiny_rnn_hneq_linear": (dict(SMALL, arMode="RNN", hiddenGar=24, rnnMode="linear", n_skipped=1), 2),
+    # --multihead_rnn (criterion.py:44-94): one MultiClassifierTransformerHead instead of K heads
+    "tiny_lstm_multihead": (dict(SMALL, arMode="LSTM", rnnMode="transformer", multihead_rnn=True), 2),
 }
 
 
@@ -71,7 +73,7 @@ def run_case(name, over, B, full=True):
     fx = {
         "args": {k: getattr(args, k) for k in ("hiddenEncoder", "hiddenGar", "nPredicts", "negativeSamplingExt",
                                               "sizeWindow", "arMode", "nLevelsGRU", "rnnMode", "cpc_mode",
-                                              "abspos", "n_skipped")},
+                                              "abspos", "n_skipped", "multihead_rnn")},
         "B": B, "crit_seed": CRIT_SEED, "seq_seed": 1234, "init_seed": 0,
         "loss": out["loss"], "acc": out["acc"],
         "fingerprint": fingerprint(state),
@@ -97,8 +99,12 @@ def run_case(name, over, B, full=True):
 
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count())
+    only = sys.argv[1:]  # optional: case names to (re)generate
     for name, (over, B) in CASES.items():
-        run_case(name, over, B)
+        if not only or name in only:
+            run_case(name, over, B)
+    if only:
+        sys.exit(0)
     # full-size default config (config 1 of BASELINE.json): summary only, weights by seed
     run_case("default_b8_summary", dict(), 8, full=False)
     run_case("default_linear_b8_summary", dict(rnnMode="linear"), 8, full=False)

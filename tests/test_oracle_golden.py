@@ -9,7 +9,7 @@ import torch
 from oracle import cpc_oracle as oc
 
 FULL_CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear",
-              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear"]
+              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead"]
 
 
 def _load(golden_dir, name):
@@ -38,7 +38,7 @@ def test_step_matches_reference(golden_dir, name):
     out = oc.train_step(fx["state"], fx["sequence"], fx["batch_idx"].long(), fx["seq_idx"].long(),
                         K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"],
                         n_layers=a["nLevelsGRU"], rnn_mode=a["rnnMode"], cpc_mode=a["cpc_mode"],
-                        abspos=a["abspos"], n_skipped=a["n_skipped"])
+                        abspos=a["abspos"], n_skipped=a["n_skipped"], multihead=a.get("multihead_rnn", False))
     torch.testing.assert_close(out["z"], fx["z"], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(out["c"], fx["c"], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=1e-6)
