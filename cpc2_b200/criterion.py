@@ -9,6 +9,8 @@ batched GEMM pred_k . z^T (tensor cores, ~46 MB, L2 resident) and a gather kerne
 each row needs -- same sampled indices (the two torch.randint draws are issued in the reference's order on
 the same generator), same cross entropy, same first-max argmax.
 """
+import math
+
 import torch
 import torch.nn as nn
 
@@ -16,6 +18,35 @@ from . import kernels as K
 from . import ops
 from .ops import BF16
 from .transformers import TransformerStack, buildMultHeadTransformerAR, buildTransformerAR
+
+
+class EqualizedLinear(nn.Module):
+    """cpc/criterion/custom_layers.py:44-76,134-151: nn.Linear with N(0, 1) weights, zero bias and the He constant
+    sqrt(2 / fan_in) applied to the OUTPUT at run time (parameter container; `weight` is that python float)."""
+
+    def __init__(self, nChannelsPrevious, nChannels, bias=True, equalized=True, lrMul=1.0, initBiasToZero=True):
+        super().__init__()
+        self.module = nn.Linear(nChannelsPrevious, nChannels, bias=bias)
+        self.equalized = equalized
+        if initBiasToZero and self.module.bias is not None:
+            self.module.bias.data.fill_(0)
+        self.weight = 1.0
+        if equalized:
+            self.module.weight.data.normal_(0, 1)
+            self.weight = math.sqrt(2.0 / nChannelsPrevious) * lrMul
+
+
+class FFNetwork(nn.Module):
+    """cpc/criterion/criterion.py:10-19 (the criterion's own FFNetwork: two EqualizedLinear layers)."""
+
+    def __init__(self, din, dout, dff, dropout):
+        super().__init__()
+        if dropout:
+            raise NotImplementedError("cpc2_b200: criterion.FFNetwork is only built with dropout 0 by the reference")
+        self.lin1 = EqualizedLinear(din, dff, bias=True, equalized=True)
+        self.lin2 = EqualizedLinear(dff, dout, bias=True, equalized=True)
+        self.relu = nn.ReLU()
+        self.drop = nn.Dropout(dropout)
 
 
 class PredictionNetwork(nn.Module):
@@ -30,17 +61,18 @@ class PredictionNetwork(nn.Module):
         self.dimOutputAR = dimOutputAR
         self.dimOutputEncoder = dimOutputEncoder
         self.sizeInputSeq = sizeInputSeq
-        if dropout:
-            raise NotImplementedError("cpc2_b200: --dropout on the predictions is not on the accelerated path")
-        self.dropout = None
-        if rnnMode in ("RNN", "LSTM", "ffd", "conv4", "conv8", "conv12"):
+        self.dropout = nn.Dropout(p=0.5) if dropout else None  # criterion.py:113; fused path: cpc_dropout
+        if rnnMode in ("RNN", "LSTM", "conv4", "conv8", "conv12"):
             raise NotImplementedError(f"cpc2_b200: prediction heads rnnMode='{rnnMode}' have no sm_100a kernels; "
                                       "use 'transformer' (default) or 'linear'")
         self.transformer = rnnMode == 'transformer'
+        self.ffd = rnnMode == 'ffd'
         for i in range(nPredicts):
             if self.transformer:
                 self.predictors.append(buildTransformerAR(dimOutputEncoder, dimOutputAR, nLayers=1,
                                                           sizeSeq=sizeInputSeq, abspos=False))
+            elif self.ffd:
+                self.predictors.append(FFNetwork(dimOutputAR, dimOutputEncoder, dimOutputEncoder, 0))
             else:
                 self.predictors.append(nn.Linear(dimOutputAR, dimOutputEncoder, bias=False))
                 if dimOutputEncoder > dimOutputAR:
@@ -54,6 +86,8 @@ class PredictionNetwork(nn.Module):
         if self._engine is None:
             if self.transformer:
                 eng = TransformerStack([p[0] for p in self.predictors])
+            elif self.ffd:
+                eng = FfdHeads([p for p in self.predictors])
             else:
                 eng = LinearHeads([p for p in self.predictors])
             object.__setattr__(self, "_engine", eng)
@@ -70,7 +104,8 @@ class PredictionNetwork(nn.Module):
         assert (len(candidates) == len(self.predictors))
         eng = self.engine()
         preds = _HeadsFn.apply(c, eng, self.training, *eng.arena.params)  # [K, B, W, D] fp32
-        return [(preds[k].unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(len(self.predictors))]
+        drop = self.dropout if self.dropout is not None else (lambda t: t)
+        return [(drop(preds[k]).unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(len(self.predictors))]
 
 
 class MultiHeadPredictionNetwork(nn.Module):
@@ -81,9 +116,7 @@ class MultiHeadPredictionNetwork(nn.Module):
                  sizeInputSeq=116, transformer_pruning=0):
         super().__init__()
         self.dimOutputAR = dimOutputAR
-        if dropout:
-            raise NotImplementedError("cpc2_b200: --dropout on the predictions is not on the accelerated path")
-        self.dropout = None
+        self.dropout = nn.Dropout(p=0.5) if dropout else None  # criterion.py:59; fused path: cpc_dropout
         self.nPredicts = nPredicts
         if rnnMode == 'transformer':
             self.predictor = buildMultHeadTransformerAR(dimOutputEncoder, dimOutputAR, nLayers=1, sizeSeq=sizeInputSeq,
@@ -104,7 +137,8 @@ class MultiHeadPredictionNetwork(nn.Module):
         assert (len(candidates) == self.nPredicts)
         eng = self.engine()
         preds = _HeadsFn.apply(c, eng, self.training, *eng.arena.params)  # [K, B, W, D] fp32
-        return [(preds[k].unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(self.nPredicts)]
+        drop = self.dropout if self.dropout is not None else (lambda t: t)
+        return [(drop(preds[k]).unsqueeze(1) * candidates[k]).mean(dim=3) for k in range(self.nPredicts)]
 
 
 class LinearHeads:
@@ -139,6 +173,75 @@ class LinearHeads:
         B = K.View(sv["w16"], d, do, G, d, do * d, major=1, gmul=0)
         K.gemm(A, B, T, d, G * do, k_per_slab=do, k_splits=ops.auto_splits(T, d, G * do, 1, do), out_f32=dx,
                accumulate=True)
+        return dx, gflat
+
+
+class FfdHeads:
+    """K feed-forward heads (rnnMode 'ffd': lin2(relu(lin1(c))) with EqualizedLinear layers, criterion.py:10-19,
+    125-128) on the same input: two grouped GEMMs forward (the He constants ride on alpha and a pre-scaled bias),
+    the relu mask applied in the epilogue of the dh GEMM backward."""
+
+    def __init__(self, nets):
+        self.G = self.n_out = len(nets)
+        self.dff, self.d = nets[0].lin1.module.weight.shape
+        self.dout = nets[0].lin2.module.weight.shape[0]
+        self.c1, self.c2 = float(nets[0].lin1.weight), float(nets[0].lin2.weight)
+        if self.d % 8 or self.dout % 8 or self.dff % 8:
+            raise NotImplementedError("FfdHeads: dimensions must be multiples of 8")
+        G = self.G
+        self.arena = ops.Arena([n.lin1.module.weight for n in nets] + [n.lin1.module.bias for n in nets] +
+                               [n.lin2.module.weight for n in nets] + [n.lin2.module.bias for n in nets])
+        self.first = dict(W1=0, b1=G, W2=2 * G, b2=3 * G)
+
+    def spans(self, flat):
+        G, d, dff, do = self.G, self.d, self.dff, self.dout
+        sh = dict(W1=(G, dff, d), b1=(G, dff), W2=(G, do, dff), b2=(G, do))
+        return {k: self.arena.span(flat, self.first[k], G, v) for k, v in sh.items()}
+
+    def forward(self, x, T, shared, training, want_f32=False):
+        G, d, dff, do = self.G, self.d, self.dff, self.dout
+        P32 = self.spans(self.arena.ensure())
+        P16 = self.spans(self.arena.bf16())
+        b1s, b2s = P32["b1"] * self.c1, P32["b2"] * self.c2  # (x W^T + b) * c = c * x W^T + (c b)
+        h = torch.empty(G, T, dff, device=x.device, dtype=BF16)
+        ops.linear_fwd(x, P16["W1"], T, dff, d, groups=G, x_shared=True, out_bf16=h, bias=b1s, bias_gs=dff, relu=True,
+                       alpha=self.c1)
+        out = torch.empty(G, T, do, device=x.device, dtype=BF16)
+        out32 = torch.empty(G, T, do, device=x.device) if want_f32 else None
+        ops.linear_fwd(h, P16["W2"], T, do, dff, groups=G, out_bf16=out, out_f32=out32, bias=b2s, bias_gs=do,
+                       alpha=self.c2)
+        return out, out32, dict(x=x, h=h, P16=P16, T=T)
+
+    def backward(self, sv, dout):
+        G, d, dff, do, T = self.G, self.d, self.dff, self.dout, sv["T"]
+        dev = dout.device
+        if dout.dtype != BF16:
+            dout = K.cast_bf16(dout.contiguous().float())
+        dout = dout.view(G, T, do)
+        gflat = torch.zeros(self.arena.numel, device=dev)
+        Gd = self.spans(gflat)
+        dh = torch.empty(G, T, dff, device=dev, dtype=BF16)
+        dx = torch.zeros(T, d, device=dev)
+        with ops.side(0):  # dW2 = c2 * dout^T . h
+            K.gemm(K.mnmajor(dout), K.mnmajor(sv["h"]), do, dff, T, groups=G, k_splits=ops.auto_splits(do, dff, T, G),
+                   out_f32=Gd["W2"], accumulate=True, alpha=self.c2)
+        with ops.side(1):
+            K.colsum(dout, Gd["b2"], T, do, do, T * do, G)
+            Gd["b2"].mul_(self.c2)
+        # dh = relu' o (c2 * dout . W2)
+        ops.linear_dx(dout, sv["P16"]["W2"], T, do, dff, groups=G, out_bf16=dh, gate=sv["h"], gate_scale=1.0,
+                      alpha=self.c2)
+        with ops.side(0):  # dW1 = c1 * dh^T . x
+            K.gemm(K.mnmajor(dh), K.mnmajor(sv["x"], gmul=0), dff, d, T, groups=G,
+                   k_splits=ops.auto_splits(dff, d, T, G), out_f32=Gd["W1"], accumulate=True, alpha=self.c1)
+        with ops.side(1):
+            K.colsum(dh, Gd["b1"], T, dff, dff, T * dff, G)
+            Gd["b1"].mul_(self.c1)
+        A = K.View(dh, dff, T, G, dff, T * dff, major=0, gmul=0)
+        B = K.View(sv["P16"]["W1"], d, dff, G, d, dff * d, major=1, gmul=0)
+        K.gemm(A, B, T, d, G * dff, k_per_slab=dff, k_splits=ops.auto_splits(T, d, G * dff, 1, dff), out_f32=dx,
+               accumulate=True, alpha=self.c1)
+        ops.join()
         return dx, gflat
 
 
@@ -259,8 +362,10 @@ class CPCUnsupersivedCriterion(BaseCriterion):
             q = self.weighting_function(signal_quality.mean(dim=1))
             weights = q.unsqueeze(1).repeat(1, windowSize).contiguous().view(-1).float()
         eng = self.wPrediction.engine()
+        # --dropout: nn.Dropout(0.5) on every prediction in train mode (criterion.py:168-169)
+        drop_pred = self.wPrediction.dropout.p if (self.wPrediction.dropout is not None and self.training) else 0.0
         losses, acc = _CriterionFn.apply(cFeature, encodedData, extIdx, weights, eng, self.nPredicts,
-                                         self.negativeSamplingExt, self.training, *eng.arena.params)
+                                         self.negativeSamplingExt, (self.training, drop_pred), *eng.arena.params)
         return losses[:, self.nSkipped:], acc[:, self.nSkipped:]
 
 
@@ -268,7 +373,8 @@ class _CriterionFn(torch.autograd.Function):
     """heads -> all-pairs logits GEMM -> gather + CE + argmax, and the matching backward."""
 
     @staticmethod
-    def forward(ctx, c, z, ext, weights, eng, Kp, NEG, training, *params):
+    def forward(ctx, c, z, ext, weights, eng, Kp, NEG, mode, *params):
+        training, drop_pred = mode
         B, S, H = c.shape
         D = z.shape[2]
         W = S - Kp
@@ -279,6 +385,10 @@ class _CriterionFn(torch.autograd.Function):
         cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
         zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
         preds, _, saved = eng.forward(cw, T, True, training)
+        ctx.pred_drop = None
+        if drop_pred > 0:
+            ctx.pred_drop = (ops.DropoutState.next(dev), drop_pred)
+            K.dropout_(preds, ctx.pred_drop[0], 7, drop_pred)
         logits = torch.empty(Kp, T, BS, device=dev)
         ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D)
         lse = torch.empty(Kp, T, device=dev)
@@ -324,6 +434,8 @@ class _CriterionFn(torch.autograd.Function):
         for part in range(2):
             K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
                    accumulate=part > 0)
+        if ctx.pred_drop is not None:
+            K.dropout_(dpred, ctx.pred_drop[0], 7, ctx.pred_drop[1])
         dcw, gflat = eng.backward(ctx.saved, dpred)
         dc[:, :W] = dcw.view(B, W, H)
         ops.join()

@@ -27,6 +27,34 @@ __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float
     out[i] = __bfloat162float(in[i]);
 }
 
+// Inverted dropout of a contiguous tensor, in place: x[i] = keep(i) ? x[i] / (1 - p) : 0.  keep(i) is a counter hash of
+// (seed, step, site, i) -- rng = device uint64[2] {seed, step} as in the GEMM / attention kernels -- so the backward
+// regenerates the mask from the same (rng, site) instead of storing it.  One hash per element pair.
+template <bool BF16>
+__global__ void dropout_kernel(void* __restrict__ x_, long long n, const unsigned long long* __restrict__ rng,
+                               uint32_t site, float p) {
+  const unsigned long long seed = rng[0] + rng[1] * 0x632BE59BD9B4E019ull;
+  const uint32_t seed_lo = static_cast<uint32_t>(seed);
+  const uint32_t seed_hi = static_cast<uint32_t>(seed >> 32) + site * 0x85EBCA77u;
+  const uint32_t thresh = static_cast<uint32_t>(fminf(p, 0.9999f) * 65536.0f);
+  const float scale = 1.f / (1.f - p);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i2 = (long long)blockIdx.x * blockDim.x + threadIdx.x; 2 * i2 < n; i2 += stride) {
+    const uint32_t h = rng_pair_u16(seed_lo, seed_hi, static_cast<unsigned long long>(i2));
+    const bool k0 = (h & 0xFFFFu) >= thresh, k1 = (h >> 16) >= thresh;
+    const long long i = 2 * i2;
+    if (BF16) {
+      __nv_bfloat16* x = static_cast<__nv_bfloat16*>(x_);
+      x[i] = k0 ? __float2bfloat16(__bfloat162float(x[i]) * scale) : __float2bfloat16(0.f);
+      if (i + 1 < n) x[i + 1] = k1 ? __float2bfloat16(__bfloat162float(x[i + 1]) * scale) : __float2bfloat16(0.f);
+    } else {
+      float* x = static_cast<float*>(x_);
+      x[i] = k0 ? x[i] * scale : 0.f;
+      if (i + 1 < n) x[i + 1] = k1 ? x[i + 1] * scale : 0.f;
+    }
+  }
+}
+
 // out[g][c] (+)= sum_r in[g][r][c]   (in bf16 or fp32), one block column-slab of 32 channels x row chunk
 template <bool IN_BF16>
 __global__ void __launch_bounds__(256) colsum_kernel(const void* __restrict__ in_, float* __restrict__ out, long long rows,
@@ -108,6 +136,17 @@ extern "C" int cpc_cast_bf16_to_f32(const void* in, void* out, int64_t n, void* 
   if (n == 0) return CPC_OK;
   cast_bf16_f32_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
       static_cast<const __nv_bfloat16*>(in), static_cast<float*>(out), n);
+  return launch_status();
+}
+
+extern "C" int cpc_dropout(void* x, int is_bf16, int64_t n, const void* rng, uint32_t site, float p, void* stream_) {
+  if (x == nullptr || rng == nullptr || n < 0 || !(p >= 0.f) || !(p < 1.f)) return CPC_ERR_ARG;
+  if (n == 0 || p == 0.f) return CPC_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (is_bf16)
+    dropout_kernel<true><<<grid_for((n + 1) / 2, 256), 256, 0, stream>>>(x, n, static_cast<const unsigned long long*>(rng), site, p);
+  else
+    dropout_kernel<false><<<grid_for((n + 1) / 2, 256), 256, 0, stream>>>(x, n, static_cast<const unsigned long long*>(rng), site, p);
   return launch_status();
 }
 

@@ -215,6 +215,14 @@ def cast_f32(src, dst=None):
     return dst
 
 
+def dropout_(x, rng, site, p):
+    """In-place inverted dropout with the counter-hash mask of (rng, site); same call on the gradient = backward."""
+    assert x.is_contiguous() and x.dtype in (BF16, torch.float32)
+    _run("cpc_dropout", (ptr(x), int(x.dtype == BF16), ctypes.c_int64(x.numel()), ptr(rng), ctypes.c_uint32(site),
+                         ctypes.c_float(p), stream_ptr(),))
+    return x
+
+
 def colsum(inp, out, rows, C, ld, gs_in=0, groups=1):
     _run("cpc_colsum", (ptr(inp), int(inp.dtype == BF16), ptr(out), ctypes.c_int64(rows), C, ctypes.c_int64(ld),
                            ctypes.c_int64(gs_in), groups, stream_ptr(),))

@@ -144,6 +144,10 @@ int cpc_conv_wgrad_unpack(const void* dwf, void* dw, int Co, int Ci, int k, void
  * Streaming helpers. */
 int cpc_cast_f32_to_bf16(const void* in, void* out, int64_t n, void* stream);
 int cpc_cast_bf16_to_f32(const void* in, void* out, int64_t n, void* stream);
+/* nn.Dropout on the predictions (cpc/criterion/criterion.py:113,168-169, `--dropout`), in place on a contiguous
+ * bf16 / fp32 tensor: x = keep ? x / (1 - p) : 0 with a counter-hash mask of (rng = device uint64[2] {seed, step},
+ * site, element index); calling it again with the same (rng, site) on the gradient is the backward. */
+int cpc_dropout(void* x, int is_bf16, int64_t n, const void* rng, uint32_t site, float p, void* stream);
 /* out[g][c] += sum_r in[g][r][c] (fp32 out, pre-initialised): bias gradients */
 int cpc_colsum(const void* in, int in_is_bf16, void* out, int64_t rows, int C, int64_t ld, int64_t gs_in,
                int groups, void* stream);

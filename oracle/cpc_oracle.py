@@ -301,6 +301,13 @@ def prediction_heads(p, c, K, rnn_mode, size_seq, prefix="wPrediction.predictors
         if rnn_mode == "transformer":
             m = None if masks is None else masks[k]
             out.append(transformer_layer(p, c, f"{prefix}{k}.0.", size_seq, masks=m, drop_p=drop_p))
+        elif rnn_mode == "ffd":
+            # criterion.py:10-19,125-128: FFNetwork of two EqualizedLinear layers (custom_layers.py:44-76,134-151):
+            # y = (x W^T + b) * sqrt(2 / fan_in), weights N(0, 1), no dropout (p = 0)
+            w1, b1 = p[f"{prefix}{k}.lin1.module.weight"], p[f"{prefix}{k}.lin1.module.bias"]
+            w2, b2 = p[f"{prefix}{k}.lin2.module.weight"], p[f"{prefix}{k}.lin2.module.bias"]
+            h = F.relu((c @ w1.t() + b1) * math.sqrt(2.0 / w1.shape[1]))
+            out.append((h @ w2.t() + b2) * math.sqrt(2.0 / w2.shape[1]))
         else:  # any other string falls through to the bias-free Linear (criterion.py:145-146)
             out.append(c @ p[f"{prefix}{k}.weight"].t())
     return out

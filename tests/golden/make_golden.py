@@ -29,6 +29,8 @@ CASES = {
     "tiny_rnn_hneq_linear": (dict(SMALL, arMode="RNN", hiddenGar=24, rnnMode="linear", n_skipped=1), 2),
     # --multihead_rnn (criterion.py:44-94): one MultiClassifierTransformerHead instead of K heads
     "tiny_lstm_multihead": (dict(SMALL, arMode="LSTM", rnnMode="transformer", multihead_rnn=True), 2),
+    # feed-forward heads (criterion.py:125-128)
+    "tiny_lstm_ffd": (dict(SMALL, arMode="LSTM", rnnMode="ffd"), 2),
 }
 
 

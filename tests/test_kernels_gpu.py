@@ -349,6 +349,27 @@ def test_cpcar_module_matches_torch_rnn(K, cell, H, Cin, N, S, nl):
         close(g.grad, gr.grad, 5e-2, 5e-2 * gr.grad.abs().max().item(), f"{cell} d{n}")
 
 
+def test_dropout_kernel_mask_is_a_function_of_rng_site_index(K):
+    """cpc_dropout: in place, kept elements scaled by 1/(1-p), the same (rng, site) reproduces the mask on another
+    tensor (that is the backward), a different site or step does not."""
+    torch.manual_seed(4)
+    n = 12 * 928 * 256 + 1
+    x = torch.randn(n, device="cuda") + 3.0
+    rng = torch.tensor([77, 5], device="cuda", dtype=torch.int64)
+    y = K.dropout_(x.clone(), rng, 7, 0.5)
+    keep = y != 0
+    assert abs(keep.float().mean().item() - 0.5) < 2e-3
+    assert torch.equal(y[keep], x[keep] * 2.0)
+    g = K.dropout_(bf(torch.ones(n, device="cuda")), rng, 7, 0.5)  # bf16 tensor, same mask
+    assert torch.equal(g != 0, keep) and torch.equal(g[keep].float(), torch.full_like(g[keep].float(), 2.0))
+    other = K.dropout_(x.clone(), rng, 8, 0.5) != 0
+    assert (other != keep).float().mean().item() > 0.4
+    rng2 = torch.tensor([77, 6], device="cuda", dtype=torch.int64)
+    assert ((K.dropout_(x.clone(), rng2, 7, 0.5) != 0) != keep).float().mean().item() > 0.4
+    q = K.dropout_(x.clone(), rng, 7, 0.1) != 0
+    assert abs(q.float().mean().item() - 0.9) < 2e-3
+
+
 # ------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("G,Bt,Hh,S,dk,relpos", [(2, 3, 8, 116, 32, True), (1, 2, 8, 12, 4, True),
                                                  (1, 2, 4, 128, 64, False), (1, 1, 8, 244, 64, True),

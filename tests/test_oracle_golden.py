@@ -9,7 +9,7 @@ import torch
 from oracle import cpc_oracle as oc
 
 FULL_CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear",
-              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead"]
+              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd"]
 
 
 def _load(golden_dir, name):

@@ -90,7 +90,7 @@ def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, min_cos=0.99)
 
 
 GOLDEN_CASES = ["tiny_lstm_linear", "tiny_lstm_reverse_linear", "tiny_transformer_ar_linear", "tiny_gru2_transformer",
-                "tiny_lstm_multihead"]
+                "tiny_lstm_multihead", "tiny_lstm_ffd"]
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -140,6 +140,7 @@ ORACLE_CASES = {
     "small_transformer_heads": dict(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16,
                                     sizeWindow=5120),
     "multihead_rnn_default_size": dict(multihead_rnn=True),
+    "ffd_heads_default_size": dict(rnnMode="ffd"),
 }
 
 
@@ -368,3 +369,27 @@ def test_graphed_step_with_fused_adam_learns():
     assert float(opt._groups[0]["state"][0]) == n0 + 160
     first, last = sum(hist[:5]) / 5, sum(hist[-5:]) / 5
     assert all(h == h for h in hist) and last < first - 0.05, (first, last)
+
+
+def test_prediction_dropout_flag():
+    """--dropout (nn.Dropout(0.5) on every prediction, criterion.py:113,168-169): eval mode is unaffected; in train
+    mode the step runs, the loss moves away from the eval loss (half of each prediction is zeroed, the rest doubled)
+    and every gradient stays finite; the mask changes from step to step."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120,
+                         rnnMode="linear", dropout=True)
+    model, crit = build(args)
+    plain = T.defaultArgs(**{**vars(args), "dropout": False})
+    model0, crit0 = build(plain)
+    crit0.load_state_dict(crit.state_dict())
+    model0.load_state_dict(model.state_dict())
+    g = torch.Generator().manual_seed(11)
+    seq = (0.1 * torch.randn(8, 2, 1, args.sizeWindow, generator=g)).cuda()
+    ev = run_step(model, crit, seq, train_mode=False, seed=5)
+    ev0 = run_step(model0, crit0, seq, train_mode=False, seed=5)
+    assert torch.allclose(ev["loss"], ev0["loss"], atol=1e-5)  # (loss sums are atomics: fp32 order only)
+    a = run_step(model, crit, seq, train_mode=True, seed=5)
+    b = run_step(model, crit, seq, train_mode=True, seed=5)
+    assert torch.isfinite(a["loss"]).all() and all(torch.isfinite(v).all() for v in a["grads"].values())
+    assert (a["loss"] - ev["loss"]).abs().max() > 1e-4 and (a["loss"] - b["loss"]).abs().max() > 1e-5
