@@ -222,52 +222,81 @@ __global__ void __launch_bounds__(256) rownorm_bwd_kernel(const RowNormBwdArgs a
     for (int i = 0; i < V; ++i) { ga[i] = 1.f; be[i] = 0.f; }
   }
   const float inv_n = a.unbiased ? 1.f / (C - 1) : 1.f / C;
-  for (long long rr = (long long)blockIdx.x * wpb + wib; rr < a.rows_per_group; rr += (long long)gridDim.x * wpb) {
-    const long long r = r0 + rr;
-    float x[V], d[V];
-    load_bf16<V>(a.in + a.in_map(r) * C + lane * V, x);
-    if (a.dout_f32) load_f32<V>(static_cast<const float*>(a.dout) + a.dout_map(r) * C + lane * V, d);
-    else load_bf16<V>(static_cast<const __nv_bfloat16*>(a.dout) + a.dout_map(r) * C + lane * V, d);
+  // R rows per warp and iteration with every load issued before the first use: the kernel is bound by the
+  // load -> reduce -> store latency chain of a row, not by bandwidth (a 1024-row layer took as long as an 8192-row one)
+  constexpr int R = V <= 8 ? 4 : 2;
+  for (long long rr0 = ((long long)blockIdx.x * wpb + wib) * R; rr0 < a.rows_per_group; rr0 += (long long)gridDim.x * wpb * R) {
+    float x[R][V], d[R][V], mean[R], rstd[R];
+    bool ok[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      ok[q] = rr0 + q < a.rows_per_group;
+      const long long r = r0 + rr0 + (ok[q] ? q : 0);
+      load_bf16<V>(a.in + a.in_map(r) * C + lane * V, x[q]);
+      if (a.dout_f32) load_f32<V>(static_cast<const float*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
+      else load_bf16<V>(static_cast<const __nv_bfloat16*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
+      mean[q] = a.mean[r];
+      rstd[q] = a.rstd[r];
+    }
     if (a.dout2 != nullptr) {
-      float d2[V];
-      load_f32<V>(a.dout2 + a.dout2_map(r) * C + lane * V, d2);
 #pragma unroll
-      for (int i = 0; i < V; ++i) d[i] += d2[i];
-    }
-    const float mean = a.mean[r], rstd = a.rstd[r];
-    float s1 = 0.f, s2 = 0.f;
+      for (int q = 0; q < R; ++q) {
+        const long long r = r0 + rr0 + (ok[q] ? q : 0);
+        float d2[V];
+        load_f32<V>(a.dout2 + a.dout2_map(r) * C + lane * V, d2);
 #pragma unroll
-    for (int i = 0; i < V; ++i) {
-      x[i] = (x[i] - mean) * rstd;  // xhat
-      if (a.relu && (x[i] * ga[i] + be[i]) <= 0.f) d[i] = 0.f;
-      ag[i] += d[i] * x[i];
-      ab[i] += d[i];
-      d[i] *= ga[i];  // dxhat
-      s1 += d[i];
-      s2 += d[i] * x[i];
+        for (int i = 0; i < V; ++i) d[q][i] += d2[i];
+      }
     }
-    s1 = warp_sum(s1) * (1.f / C);
-    s2 = warp_sum(s2) * inv_n;
+    float s1[R], s2[R];
 #pragma unroll
-    for (int i = 0; i < V; ++i) {
-      d[i] = rstd * (d[i] - s1 - x[i] * s2);
-      as[i] += d[i];
-    }
-    const long long o = a.dx_map(r) * C + lane * V;
-    if (a.dx_bf16 != nullptr) {
-      store_bf16<V>(a.dx_bf16 + o, d);
-      zero_halo<V>(a.dx_bf16, a.dx_map, r, lane);
-    }
-    if (a.dx_f32 != nullptr) {
-      if (!a.dx_accumulate) zero_halo<V>(a.dx_f32, a.dx_map, r, lane);
-      if (a.dx_accumulate) {
-        float old[V];
-        load_f32<V>(a.dx_f32 + o, old);
+    for (int q = 0; q < R; ++q) {
+      s1[q] = s2[q] = 0.f;
 #pragma unroll
-        for (int i = 0; i < V; ++i) old[i] += d[i];
-        store_f32<V>(a.dx_f32 + o, old);
-      } else {
-        store_f32<V>(a.dx_f32 + o, d);
+      for (int i = 0; i < V; ++i) {
+        x[q][i] = (x[q][i] - mean[q]) * rstd[q];  // xhat
+        if (!ok[q] || (a.relu && (x[q][i] * ga[i] + be[i]) <= 0.f)) d[q][i] = 0.f;
+        ag[i] += d[q][i] * x[q][i];
+        ab[i] += d[q][i];
+        d[q][i] *= ga[i];  // dxhat
+        s1[q] += d[q][i];
+        s2[q] += d[q][i] * x[q][i];
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        s1[q] += __shfl_xor_sync(0xffffffffu, s1[q], o);
+        s2[q] += __shfl_xor_sync(0xffffffffu, s2[q], o);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (!ok[q]) continue;
+      const long long r = r0 + rr0 + q;
+      const float m1 = s1[q] * (1.f / C), m2 = s2[q] * inv_n;
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        d[q][i] = rstd[q] * (d[q][i] - m1 - x[q][i] * m2);
+        as[i] += d[q][i];
+      }
+      const long long o = a.dx_map(r) * C + lane * V;
+      if (a.dx_bf16 != nullptr) {
+        store_bf16<V>(a.dx_bf16 + o, d[q]);
+        zero_halo<V>(a.dx_bf16, a.dx_map, r, lane);
+      }
+      if (a.dx_f32 != nullptr) {
+        if (!a.dx_accumulate) zero_halo<V>(a.dx_f32, a.dx_map, r, lane);
+        if (a.dx_accumulate) {
+          float old[V];
+          load_f32<V>(a.dx_f32 + o, old);
+#pragma unroll
+          for (int i = 0; i < V; ++i) old[i] += d[q][i];
+          store_f32<V>(a.dx_f32 + o, old);
+        } else {
+          store_f32<V>(a.dx_f32 + o, d[q]);
+        }
       }
     }
   }
@@ -358,7 +387,7 @@ extern "C" int cpc_rownorm_bwd(const CpcRowNormBwd* d, void* stream_) {
   a.rows_per_group = rpg; a.unbiased = d->unbiased; a.relu = d->relu;
   const int groups = (int)(d->rows / rpg);
   const int wpb = 8;
-  long long bx = (rpg + wpb * 8 - 1) / (wpb * 8);  // >= 8 rows per warp so the final atomics amortise
+  long long bx = (rpg + wpb * 4 - 1) / (wpb * 4);  // one 4-row batch per warp where the row count allows
   const long long cap = (148 * 8 + groups - 1) / groups;
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
