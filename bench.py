@@ -9,7 +9,8 @@ default config (encoder 256, 1-layer LSTM-256 AR, 12 transformer prediction head
 
 Prints ONE JSON line (rank 0).  `value`: inputs resident in HBM, CUDA-event time per step summed over K steps,
 max over ranks, L2 flushed between steps.  `e2e`: the same step through the public API
-(cpc2_b200.train.GraphedTrainStep.step) with a pinned HOST batch copied in and the losses copied out every step.
+(cpc2_b200.train.GraphedTrainStep.pipelined) with a pinned HOST batch copied in and the losses / accuracies copied
+out and read by the host every step (batch i+1 in flight and result i-1 being read while replay i runs).
 `roofline`: the dominant kernel family of the step, timed per launch with CUDA events in a separate eager
 pass behind a GPU-side delay (so host launch latency is not measured).  `cpu_baseline`: the CPU oracle
 (oracle/cpc_oracle.py, the restatement of the reference pinned by tests/golden) on the host cores.
@@ -238,11 +239,12 @@ def run_ours(opt, out):
     barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
-    for _ in range(opt.steps):
-        losses, acc = step.step(host_seq, non_blocking=True)
-        host_out[0].copy_(losses.detach().view(-1), non_blocking=True)
-        host_out[1].copy_(acc.detach().view(-1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the caller reads the loss every step (train.py:121-122)
+    n_read = 0
+    for losses_h, acc_h in step.pipelined(host_seq for _ in range(opt.steps)):
+        host_out[0].copy_(losses_h)  # the caller consumes every step's losses / accuracies on the host
+        host_out[1].copy_(acc_h)     # (train.py:121-122), one step behind the GPU
+        n_read += 1
+    assert n_read == opt.steps
     t1.record()
     barrier()
     ms_e2e = t0.elapsed_time(t1)

@@ -192,6 +192,7 @@ class GraphedTrainStep:
         """`optimizer` (cpc2_b200.optim.FusedAdam, or any capturable optimizer): its step() becomes part of the
         graph, after `after_backward` (the data-parallel all-reduce) -- the whole of train.py:95-113 in one replay."""
         self.model, self.crit, self.optimizer = cpcModel, cpcCriterion, optimizer
+        self._copy_stream, self._staged, self._staged_ready, self._picked = None, None, False, None
         self.static_seq = torch.zeros(batch, 2, 1, sizeWindow, device=device)
         self.static_label = torch.zeros(batch, dtype=torch.long, device=device)
         self.params = [p for p in list(cpcModel.parameters()) + list(cpcCriterion.parameters()) if p.requires_grad]
@@ -222,9 +223,59 @@ class GraphedTrainStep:
         for p in self.params:
             p.grad = None
 
+    def prefetch(self, sequence):
+        """Input staging: start the host -> device copy of the NEXT batch (pinned host memory) on a
+        copy stream while the current replay runs; the following step() picks it up with a device-side copy."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.static_seq.device)
+            self._staged = torch.empty_like(self.static_seq)
+        cs = self._copy_stream
+        if self._picked is not None:
+            cs.wait_event(self._picked)  # the previous pick-up (not the replay that follows it) has read the buffer
+        with torch.cuda.stream(cs):
+            self._staged.copy_(sequence, non_blocking=True)
+        self._staged_ready = True
+
+    def pipelined(self, batches):
+        """The batch loop of trainStep (cpc/train.py:84-122) as a three-deep pipeline: while replay i runs, batch i+1
+        travels host -> device on the copy stream and the host reads the (losses, acc) of step i-1 from pinned memory
+        -- every step's result still reaches the host, but the GPU never waits for the host to look at it.
+        `batches`: iterable of pinned [B,2,1,W] host tensors.  Yields (losses [K], acc [K]) host tensors per step,
+        in order (valid until the next-but-one yield)."""
+        nK = self.losses.numel()
+        out = [torch.empty(2, nK).pin_memory() for _ in range(2)]
+        evs = [torch.cuda.Event(), torch.cuda.Event()]
+        it = iter(batches)
+        nxt = next(it, None)
+        if nxt is None:
+            return
+        self.prefetch(nxt)
+        i = 0
+        while nxt is not None:
+            losses, acc = self.step()
+            nxt = next(it, None)
+            if nxt is not None:
+                self.prefetch(nxt)
+            o = out[i & 1]
+            o[0].copy_(losses.detach().view(-1), non_blocking=True)
+            o[1].copy_(acc.detach().view(-1), non_blocking=True)
+            evs[i & 1].record()
+            if i > 0:
+                evs[(i - 1) & 1].synchronize()
+                yield out[(i - 1) & 1][0], out[(i - 1) & 1][1]
+            i += 1
+        evs[(i - 1) & 1].synchronize()
+        yield out[(i - 1) & 1][0], out[(i - 1) & 1][1]
+
     def step(self, sequence=None, non_blocking=True):
         if sequence is not None:
             self.static_seq.copy_(sequence, non_blocking=non_blocking)
+        elif self._staged_ready:
+            torch.cuda.current_stream().wait_stream(self._copy_stream)
+            self.static_seq.copy_(self._staged, non_blocking=True)
+            self._picked = torch.cuda.Event()
+            self._picked.record()
+            self._staged_ready = False
         if self.optimizer is not None and hasattr(self.optimizer, "sync_hyper"):
             self.optimizer.sync_hyper()  # a scheduler may have changed lr since the last replay
         self.graph.replay()
