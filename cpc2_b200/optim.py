@@ -148,10 +148,13 @@ class FusedAdam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        for gi in range(len(self.param_groups)):  # (raises on CPU parameters before anything touches CUDA)
+            if self._groups[gi] is None:
+                self._init_group(gi)
         capturing = torch.cuda.is_current_stream_capturing()
         ops.join(9)  # staged launches of this iteration (FusedAdam.attach); dp.finish() has joined dp.stream
         for gi in range(len(self.param_groups)):
-            g = self._groups[gi] or self._init_group(gi)
+            g = self._groups[gi]
             if g is None:
                 continue
             if not capturing:

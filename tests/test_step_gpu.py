@@ -445,3 +445,41 @@ def test_pipelined_loop_yields_every_step_in_order():
     for (l, a), (dl, da) in zip(got, direct):
         assert l.shape == dl.shape and torch.isfinite(l).all()
         assert (l - dl).abs().max() < 0.05  # same batch, different negative draws per replay
+
+
+def test_val_step_and_keep_hidden_streaming():
+    """Forward-only consumers: valStep (cpc/train.py:145-187) gives the eval losses of trainStep's
+    forward without touching .grad; with keepHidden (samplingType 'sequential', feature_loader.py:229) two
+    consecutive half-windows through CPCAR reproduce one full window (the hidden state streams across calls) and
+    the two-halves fast path is not taken."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120,
+                         rnnMode="linear")
+    model, crit = build(args)
+    g = torch.Generator().manual_seed(31)
+    seq = (0.1 * torch.randn(4, 2, 1, args.sizeWindow, generator=g)).cuda()
+    label = torch.zeros(4, dtype=torch.long, device="cuda")
+    torch.manual_seed(3)
+    logs = T.valStep([(seq.cpu(), label.cpu())], model, crit)
+    assert logs["iter"] == 1 and logs["locLoss_val"].shape == (4,)
+    assert all(p.grad is None for p in model.parameters())
+    model.eval()
+    crit.eval()
+    torch.manual_seed(3)
+    losses, _ = T.forwardBackward(model, crit, seq, label, backward=False)
+    assert abs(float(losses.mean()) - float(logs["locLoss_val"].mean())) < 1e-4
+    # keepHidden streaming
+    ar = model.gAR
+    x = torch.randn(3, 32, 64, device="cuda")
+    with torch.no_grad():
+        full = ar(x)
+        ar.keepHidden = True
+        ar.hidden = None
+        a = ar(x[:, :16])
+        b = ar(x[:, 16:])
+        assert ar.hidden is not None
+    assert (torch.cat([a, b], dim=1) - full).abs().max() < 2e-2
+    assert not model.splittable()
+    ar.keepHidden, ar.hidden = False, None
+    assert model.splittable()

@@ -1,0 +1,73 @@
+"""CPU-side checks of the reference's module surface -- no kernel is launched: the drop-in modules
+expose the state_dict keys / shapes of the UNMODIFIED reference (read from the reference-generated golden fixtures),
+the reference's constructor errors, and the same initial weights for the same seed."""
+import os
+
+import pytest
+import torch
+
+from cpc2_b200 import criterion as cr
+from cpc2_b200 import model as M
+from cpc2_b200 import train as T
+from cpc2_b200 import transformers as tr
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear", "tiny_lstm_reverse_linear",
+         "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_state_dict_keys_shapes_and_init_match_reference(name):
+    fx = torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
+    args = T.defaultArgs(**fx["args"])
+    torch.manual_seed(fx["init_seed"])
+    model, crit = T.buildModelAndCriterion(args)
+    ours = dict(model.state_dict())
+    ours.update(crit.state_dict())
+    ours = {k: v for k, v in ours.items() if v.dtype.is_floating_point and not k.endswith(".mask") and not k.endswith(".z")}
+    ref = fx["state"]
+    assert set(ours) == set(ref), (sorted(set(ours) - set(ref)), sorted(set(ref) - set(ours)))
+    for k, v in ref.items():
+        assert tuple(ours[k].shape) == tuple(v.shape), k
+        # same construction order and RNG draws as cpc/train.py:442-461 -> identical initial weights
+        assert torch.equal(ours[k].float(), v), k
+    # reference state loads strictly (buffers `mask` / `z` of the attention modules are not in the fixture)
+    missing = crit.load_state_dict({k: v for k, v in ref.items() if k.startswith("wPrediction")}, strict=False)
+    assert not missing.unexpected_keys
+    assert all(k.endswith(".mask") or k.endswith(".z") for k in missing.missing_keys), missing.missing_keys
+
+
+def test_constructor_errors_of_the_reference():
+    with pytest.raises(ValueError):
+        M.CPCEncoder(32, normMode="nope")                      # cpc/model.py:71-73
+    with pytest.raises(ValueError, match="Invalid mode"):
+        cr.CPCUnsupersivedCriterion(4, 32, 32, 8, mode="sideways")   # criterion.py:232-233
+    with pytest.raises(ValueError, match="unknown mode"):
+        cr.MultiHeadPredictionNetwork(4, 32, 32, rnnMode="linear")   # criterion.py:77-78
+    c = cr.CPCUnsupersivedCriterion(4, 32, 32, 8, rnnMode="linear", sizeInputSeq=16)
+    with pytest.raises(AssertionError):
+        c.wPrediction(torch.zeros(1, 12, 32), [torch.zeros(1, 9, 12, 32)] * 3)   # criterion.py:154
+
+
+def test_attribute_surface():
+    args = T.defaultArgs(hiddenEncoder=32, hiddenGar=32, nPredicts=4, negativeSamplingExt=8, sizeWindow=2560)
+    model, crit = T.buildModelAndCriterion(args)
+    enc, ar = model.gEncoder, model.gAR
+    assert enc.DOWNSAMPLING == 160 and enc.dimEncoded == 32 and enc.getDimOutput() == 32
+    assert ar.getDimOutput() == 32 and ar.hidden is None and ar.keepHidden is False and ar.reverse is False
+    assert all(hasattr(ar.baseNet, n) for n in ("weight_ih_l0", "weight_hh_l0", "bias_ih_l0", "bias_hh_l0"))
+    assert crit.nPredicts == 4 and crit.negativeSamplingExt == 8 and crit.nSkipped == 0 and crit.mode is None
+    assert len(crit.wPrediction.predictors) == 4 and crit.warmUp() is False and crit.update() is None
+    assert isinstance(tr.buildTransformerAR(32, 32, 2, 16, True)[0], tr.StaticPositionEmbedding)
+    seq_args = T.defaultArgs(samplingType="sequential")
+    assert T.getAR(seq_args).keepHidden is True               # feature_loader.py:229
+
+
+def test_fused_adam_has_no_cpu_path():
+    from cpc2_b200.optim import FusedAdam
+    p = torch.nn.Parameter(torch.zeros(4))
+    p.grad = torch.ones(4)
+    with pytest.raises(RuntimeError, match="CUDA parameters only"):
+        FusedAdam([p]).step()
+    with pytest.raises(NotImplementedError):
+        FusedAdam([p], weight_decay=0.1)
