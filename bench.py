@@ -199,8 +199,13 @@ def run_ours(opt, out):
     model, crit = T.buildModelAndCriterion(args)
     model, crit = model.to(dev), crit.to(dev)
     torch.manual_seed(4321 + rank)  # every rank draws its own negatives, as in the reference
-    dp = BucketedAllReduce(model, crit)
+    # gradient arenas in NVSwitch-multicast symmetric memory + cpc_allreduce_mc when the box supports it
+    # (CPC_SYMMETRIC=0: NCCL all-reduce; =1: fail instead of falling back to NCCL)
+    sym = {"0": False, "1": True}.get(os.environ.get("CPC_SYMMETRIC", "auto"), "auto")
+    dp = BucketedAllReduce(model, crit, symmetric=sym)
     dp.broadcast_parameters()
+    if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1":  # diagnosis only (the printed line says so): what the step
+        dp._all_reduce_mean = lambda t: None            # costs at N ranks without the collective
     host_seq = synthetic_batch(B, W, rank)
     host_out = torch.empty(2, args.nPredicts).pin_memory()
 
@@ -263,7 +268,11 @@ def run_ours(opt, out):
         "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2_flush_between_steps": True, "cuda_graph": True, "dropout": "train mode (p=0.1 in the heads)",
                    "optimizer": "fused multi-tensor Adam (cpc_adam_step) inside the timed step, per bucket after its all-reduce",
-                   "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0},
+                   "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0,
+                   "grad_allreduce": ("none" if world == 1 else "cpc_allreduce_mc (NVSwitch multimem, in place)"
+                                      if dp.symmetric is not None else "NCCL all-reduce (AVG)"),
+                   **({"DIAGNOSTIC": "all-reduce skipped, not a valid number"}
+                      if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1" else {})},
         "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": host_seq.numel() * 4,
                 "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": ms_e2e / opt.steps},
         "gpu_launches": launches_per_step * opt.steps, "gpu_launches_per_step": launches_per_step,

@@ -165,7 +165,7 @@ class LinearHeads:
         if dout.dtype != BF16:
             dout = K.cast_bf16(dout.contiguous().float())
         dout = dout.view(G, T, do)
-        gflat = torch.zeros(self.arena.numel, device=dev)
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
         dw = self.arena.span(gflat, 0, G, (G, do, d))
         ops.linear_dw(dout, sv["x"], dw, T, do, d, groups=G, x_shared=True)
         dx = torch.zeros(T, d, device=dev)
@@ -218,7 +218,7 @@ class FfdHeads:
         if dout.dtype != BF16:
             dout = K.cast_bf16(dout.contiguous().float())
         dout = dout.view(G, T, do)
-        gflat = torch.zeros(self.arena.numel, device=dev)
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
         Gd = self.spans(gflat)
         dh = torch.empty(G, T, dff, device=dev, dtype=BF16)
         dx = torch.zeros(T, d, device=dev)
@@ -436,9 +436,18 @@ class _CriterionFn(torch.autograd.Function):
                    accumulate=part > 0)
         if ctx.pred_drop is not None:
             K.dropout_(dpred, ctx.pred_drop[0], 7, ctx.pred_drop[1])
-        dcw, gflat = eng.backward(ctx.saved, dpred)
+        if type(eng) is TransformerStack and ops.early_ffn():
+            dcw, gflat = eng.backward(ctx.saved, dpred, early_stage="criterion")
+        else:
+            dcw, gflat = eng.backward(ctx.saved, dpred)
         dc[:, :W] = dcw.view(B, W, H)
         ops.join()
         views = eng.arena.grad_views(gflat)
-        ops.grad_ready("criterion", gflat, eng.arena.params, views)
+        ann = ctx.saved.pop("announced", None)
+        if ann is None:
+            ops.grad_ready("criterion", gflat, eng.arena.params, views)
+        else:  # the feed-forward weights went out early (criterion.ffn): what is left, as two contiguous spans
+            i0, i1, off0, off1 = ann
+            ops.grad_ready("criterion.front", gflat[:off0], eng.arena.params[:i0], views[:i0])
+            ops.grad_ready("criterion.tail", gflat[off1:], eng.arena.params[i1:], views[i1:])
         return (dc, dz.view(B, S, D), None, None, None, None, None, None, *views)

@@ -9,17 +9,25 @@ encoder -- on a side stream as soon as the bucket's gradients exist, so the NVLi
 parameter gradients as views of one arena per module and announce it through `ops.grad_ready` before autograd
 sees the views), all-reduced in place with NCCL AVG; `.grad` tensors alias the reduced arena, nothing is copied.
 Everything is CUDA-graph capturable (see train.GraphedTrainStep).
+
+`symmetric=True` (NVSwitch boxes): the gradient arenas live in ONE symmetric-memory buffer mapped through an NVLink
+multicast address (torch.distributed._symmetric_memory provides the mapping, nothing else), and each bucket is reduced
+by cpc_allreduce_mc -- one kernel, the switch does the sum (multimem.ld_reduce) and the broadcast (multimem.st) --
+instead of NCCL's ring: half the NVLink bytes, two barriers instead of 2(N-1) hops, and no shared memory, so its
+CTAs co-reside with the backward's persistent GEMM CTAs.  The arenas then persist across steps: use
+zero_grad(set_to_none=True) (torch's default) -- a gradient left in .grad would alias the next step's arena.
 """
 import torch
 import torch.distributed as dist
 
+from . import kernels as K
 from . import ops
 
 
 class BucketedAllReduce:
     STAGES = ("criterion", "ar", "encoder")
 
-    def __init__(self, cpcModel, cpcCriterion, process_group=None):
+    def __init__(self, cpcModel, cpcCriterion, process_group=None, symmetric=False, max_blocks=0):
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.on_gpu = any(p.is_cuda for p in cpcModel.parameters())
@@ -35,8 +43,49 @@ class BucketedAllReduce:
         self._arenas = []      # storages reduced in the current step
         self._pending = False  # side stream carries work of the current step
         self.bytes_per_step = 4 * sum(p.numel() for b in self.buckets for p in b)
+        self.symmetric, self.max_blocks, self.mc_launches = None, max_blocks, 0
         if self.world > 1:
             ops.GRAD_READY.append(self._on_grad_ready)
+            if symmetric and self.on_gpu:
+                self._map_symmetric(next(p for p in cpcModel.parameters() if p.is_cuda).device, symmetric)
+
+    def _map_symmetric(self, dev, mode):
+        """One symmetric fp32 buffer for every gradient arena of the step + its multicast mapping.  mode "auto":
+        stay on NCCL when the box has no multicast support; True: raise."""
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        group = self.group if self.group is not None else dist.group.WORLD
+        numel = sum((p.numel() + 7) // 8 * 8 for b in self.buckets for p in b)
+        numel += 4 * 1024 * 1024  # padded gate slots of the recurrent arenas, per-arena alignment
+        try:
+            if symm.get_signal_pad_size() < _lib.lib().cpc_allreduce_pad_bytes(self.world):
+                raise RuntimeError("symmetric-memory signal pad too small")
+            buf = symm.empty(numel, dtype=torch.float32, device=dev)
+            hdl = symm.rendezvous(buf, group)
+            mc = int(hdl.multicast_ptr)
+            if mc == 0:
+                raise RuntimeError("no NVLink multicast support on this box")
+        except Exception:
+            if mode == "auto":
+                return
+            raise
+        buf.zero_()
+        self.symmetric = dict(buf=buf, hdl=hdl, mc=mc, base=buf.data_ptr(), bytes=4 * numel, pads=int(hdl.signal_pad_ptrs_dev),
+                              rank=int(hdl.rank), used=0, slots={})
+        ops.GRAD_ARENA = self._arena
+
+    def _arena(self, owner, numel, device):
+        sy = self.symmetric
+        slot = sy["slots"].get(owner)
+        if slot is None:  # first backward: carve (same order on every rank, so the offsets are symmetric)
+            n = (numel + 31) // 32 * 32
+            if sy["used"] + n > sy["buf"].numel() or device != sy["buf"].device:
+                return None
+            slot = sy["slots"][owner] = (sy["used"], numel)
+            sy["used"] += n
+        if slot[1] != numel:
+            return None
+        return sy["buf"][slot[0]:slot[0] + numel].zero_()
 
     def broadcast_parameters(self, src=0):
         """DDP's initial parameter broadcast (train.py:524-527 wraps after construction)."""
@@ -60,9 +109,16 @@ class BucketedAllReduce:
             return
         self.stream.wait_stream(torch.cuda.current_stream())
         self._pending = True
+        sy = self.symmetric
+        off = gflat.data_ptr() - sy["base"] if sy is not None else -1
         with torch.cuda.stream(self.stream):
-            gflat.record_stream(self.stream)
-            self._all_reduce_mean(gflat)
+            if 0 <= off < sy["bytes"] if sy is not None else False:
+                n = (gflat.numel() + 3) // 4 * 4  # arenas are padded to 32 floats inside the symmetric buffer
+                K.allreduce_mc(sy["mc"] + off, n, sy["pads"], sy["rank"], self.world, 1.0 / self.world, self.max_blocks)
+                self.mc_launches += 1
+            else:
+                gflat.record_stream(self.stream)
+                self._all_reduce_mean(gflat)
 
     def finish(self):
         """Join the side stream: call after backward, before the optimizer reads .grad.  Any gradient that does
@@ -82,6 +138,8 @@ class BucketedAllReduce:
     def remove(self):
         if self._on_grad_ready in ops.GRAD_READY:
             ops.GRAD_READY.remove(self._on_grad_ready)
+        if self.symmetric is not None and ops.GRAD_ARENA == self._arena:
+            ops.GRAD_ARENA = None
 
 
 def filter_distributed(files, global_rank, world_size):

@@ -223,6 +223,12 @@ def dropout_(x, rng, site, p):
     return x
 
 
+def allreduce_mc(mc_addr, n, signal_pads_dev, rank, world, scale, max_blocks=0):
+    """In-switch all-reduce (multimem.ld_reduce / multimem.st) of n floats at multicast address mc_addr, in place."""
+    _run("cpc_allreduce_mc", (ctypes.c_void_p(mc_addr), ctypes.c_int64(n), ctypes.c_void_p(signal_pads_dev), rank, world,
+                               ctypes.c_float(scale), max_blocks, stream_ptr(),))
+
+
 def colsum(inp, out, rows, C, ld, gs_in=0, groups=1):
     _run("cpc_colsum", (ptr(inp), int(inp.dtype == BF16), ptr(out), ctypes.c_int64(rows), C, ctypes.c_int64(ld),
                            ctypes.c_int64(gs_in), groups, stream_ptr(),))

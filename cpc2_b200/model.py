@@ -267,7 +267,7 @@ class _EncoderFn(torch.autograd.Function):
         # all-reduce bucket for the data-parallel wrapper); per-parameter gradients are views of it.  Every kernel
         # below ADDS into it atomically, so the two halves of a pair share one arena.
         sizes = _grad_sizes(C)
-        gflat = pair.gflat if pair is not None else torch.zeros(sum(sizes), device=dev)
+        gflat = pair.gflat if pair is not None else ops.grad_arena("encoder", sum(sizes), dev)
         gv, off = [], 0
         for n_ in sizes:
             gv.append(gflat[off:off + n_])
@@ -488,7 +488,7 @@ class _RecurrentFn(torch.autograd.Function):
         sizes = []
         for l in range(nl):  # four-slot (padded) gradient spans; the returned gradients are their leading G*H rows
             sizes += [4 * H * ctx.saved[l][1], 4 * H * H, 4 * H, 4 * H]
-        gflat = torch.zeros(sum(sizes), device=dev)
+        gflat = ops.grad_arena("ar", sum(sizes), dev)
         gv, off = [], 0
         for n_ in sizes:
             gv.append(gflat[off:off + n_])
@@ -580,7 +580,7 @@ class CPCModel(nn.Module):
                 _pack_conv_weights([w.detach() for w in ws], packed)
         # everything the future half touches on its side stream exists BEFORE the fork event (ops.side(after=))
         fut = future.detach().reshape(N, W).contiguous().float().view(N, 1, W)
-        pair = _PairCtx(torch.zeros(sum(_grad_sizes(C)), device=dev))
+        pair = _PairCtx(ops.grad_arena("encoder", sum(_grad_sizes(C)), dev))
         plan_f = _EncPlan(packed=packed, role="future", pair=pair, fwd_bufs=_alloc_fwd(N, W, C, dev),
                           bwd_bufs=_alloc_bwd(N, W, C, dev) if torch.is_grad_enabled() else None)
         plan_f.fwd_after = ops.mark()

@@ -3,6 +3,8 @@
 Nothing here computes on tensors' values: it allocates buffers, describes views and launches the C-ABI
 kernels of libcpc_b200.so through `cpc2_b200.kernels`.
 """
+import os
+
 import torch
 
 from . import kernels as K
@@ -28,6 +30,21 @@ def grad_ready(stage, gflat, params=None, grads=None):
         fn(stage, gflat, params, grads)
 
 
+# Where a module's flat gradient arena lives: None = a fresh zeroed tensor per backward; the data-parallel wrapper
+# installs fn(owner, numel, device) -> zeroed fp32 [numel] (or None) to place the arenas in NVSwitch-multicast
+# symmetric memory, so that its all-reduce is one in-switch kernel (dp.BucketedAllReduce(symmetric=True)).
+# `owner` identifies the arena across steps: the module's ops.Arena, or "encoder" / "ar" for the model's own.
+GRAD_ARENA = None
+
+
+def grad_arena(owner, numel, device):
+    if GRAD_ARENA is not None:
+        t = GRAD_ARENA(owner, numel, device)
+        if t is not None:
+            return t
+    return torch.zeros(numel, dtype=torch.float32, device=device)
+
+
 # ---- independent kernels on forked streams -----------------------------------------------------------
 # Most launches of the step are 10-40 us and fill a fraction of the 148 SMs; weight-gradient GEMMs, bias
 # column sums and weight casts do not sit on the critical path, so they are issued on side streams that fork
@@ -36,6 +53,17 @@ def grad_ready(stage, gflat, params=None, grads=None):
 # the join (the launchers only borrow pointers), so the caching allocator never sees cross-stream reuse.
 CONCURRENT = True
 _SIDE = {}
+# announce the heads' feed-forward gradients (3/4 of all parameters) a third of the way into their backward:
+# "auto" = when gradients are all-reduced (world > 1; +1 % at N = 8, neutral at N = 1), "1" / "0" force it
+EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")
+
+
+def early_ffn():
+    if EARLY_FFN == "auto":
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    return EARLY_FFN not in ("0", False)
+
 _PENDING = []
 
 
@@ -87,7 +115,8 @@ def join(index=None):
         key, s, parent = item
         if index is None and key[1] in DETACHED:
             continue
-        if parent.cuda_stream == cur.cuda_stream and key[0] == cur.device.index and (index is None or key[1] == index):
+        # blanket join: only the streams forked from the current one; join(i): stream i whoever forked it last
+        if key[0] == cur.device.index and ((index is None and parent.cuda_stream == cur.cuda_stream) or key[1] == index):
             cur.wait_stream(s)
             _PENDING.remove(item)
 

@@ -261,12 +261,15 @@ class TransformerStack:
         return out, out32, saved
 
     # ------------------------------------------------------------------------------------------ backward
-    def backward(self, sv, dout):
-        """dout bf16 or fp32 [G, T, dout].  Returns (dx fp32 [T,d] if shared else [G,T,d], flat fp32 grad arena)."""
+    def backward(self, sv, dout, early_stage=None):
+        """dout bf16 or fp32 [G, T, dout].  Returns (dx fp32 [T,d] if shared else [G,T,d], flat fp32 grad arena).
+        early_stage: announce the feed-forward weights' gradients (W1, b1, W2, b2: 3/4 of the parameters) through
+        ops.grad_ready(early_stage + ".ffn") as soon as they exist, a third of the way into this backward, so their
+        all-reduce / optimizer step overlaps the rest of it; sv["announced"] tells the caller what is left."""
         G, d, do, dff, S = self.G, self.d, self.dout, self.dff, self.S
         T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
         dev = dout.device
-        gflat = torch.zeros(self.arena.numel, device=dev)
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
         Gd = self.spans(gflat)
         x, shared = sv["x"], sv["shared"]
         # Buffers first (main stream), then the chain of input gradients on the main stream while the weight
@@ -301,6 +304,15 @@ class TransformerStack:
             ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
         with ops.side(1):
             K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
+        if early_stage is not None and ops.GRAD_READY:
+            i0, i1 = self.first["W1"], self.first["b2"] + G
+            off0 = self.arena.offsets[i0]
+            off1 = self.arena.offsets[i1] if i1 < len(self.arena.params) else self.arena.numel
+            views = self.arena.grad_views(gflat)
+            with ops.side(0):  # behind dW2 / dW1 (this stream) and the bias column sums (stream 1)
+                ops.wait_side(1)
+                ops.grad_ready(early_stage + ".ffn", gflat[off0:off1], self.arena.params[i0:i1], views[i0:i1])
+            sv["announced"] = (i0, i1, off0, off1)
         if ops.GRAD_F32:
             ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_f32=dy, res=du)
         else:
@@ -415,7 +427,7 @@ class MultiHeadStack(TransformerStack):
         d, do, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
         T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
         dev = dout.device
-        gflat = torch.zeros(self.arena.numel, device=dev)
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
         Gd = self.spans(gflat)
         x = sv["x"]
         dpre2 = torch.empty(Kc * T, do, device=dev, dtype=BF16)

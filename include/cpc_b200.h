@@ -141,6 +141,18 @@ int cpc_conv_weight_pack(const void* w, void* wf, void* wd, int Co, int Ci, int 
 int cpc_conv_wgrad_unpack(const void* dwf, void* dw, int Co, int Ci, int k, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Gradient all-reduce of the data-parallel step (DistributedDataParallel, cpc/train.py:523-527;
+ * cpc/distributed_training/distributed_mode.py:139-142) as ONE kernel over NVSwitch multicast memory, in place:
+ * every rank calls it with the multicast address of the same n-float span of a symmetric buffer (n % 4 == 0,
+ * 16-byte aligned) and a device array of `world` pointers to the ranks' signal pads (each at least
+ * cpc_allreduce_pad_bytes(world) bytes, zero-initialised once).  Afterwards every rank's copy holds
+ * scale * sum over ranks.  The caller maps the buffers (CUDA multicast objects / torch symmetric memory); the
+ * kernel only needs the addresses.  max_blocks <= 0: default CTA count. */
+int cpc_allreduce_mc(void* mc_ptr, int64_t n, void* const* signal_pads_dev, int rank, int world, float scale,
+                     int max_blocks, void* stream);
+int cpc_allreduce_pad_bytes(int world);
+
+/* ------------------------------------------------------------------------------------------------
  * Streaming helpers. */
 int cpc_cast_f32_to_bf16(const void* in, void* out, int64_t n, void* stream);
 int cpc_cast_bf16_to_f32(const void* in, void* out, int64_t n, void* stream);

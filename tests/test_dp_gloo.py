@@ -49,7 +49,8 @@ def _worker(rank, world, port, q):
         args = T.defaultArgs(hiddenEncoder=32, hiddenGar=32, nPredicts=2, negativeSamplingExt=4, sizeWindow=2560)
         torch.manual_seed(100 + rank)  # ranks start from DIFFERENT weights; the broadcast must fix that
         model, crit = T.buildModelAndCriterion(args)
-        dp = BucketedAllReduce(model, crit)
+        dp = BucketedAllReduce(model, crit, symmetric="auto")  # CPU parameters: no multicast mapping, gloo path
+        assert dp.symmetric is None
         dp.broadcast_parameters()
         w = model.gEncoder.conv1.weight.detach().clone()
         ws = [torch.empty_like(w) for _ in range(world)]

@@ -3,6 +3,7 @@ the same arithmetic on identical inputs (bf16-rounded where the kernel consumes 
 CPU oracle (oracle/cpc_oracle.py) for the criterion math.  Tolerances are stated per test; integer /
 index outputs are bit exact."""
 import math
+import os
 
 import pytest
 import torch
@@ -482,3 +483,22 @@ def test_attention_dropout_consistent(K):
     o = out1.view(Bt, S, Hh, dk)[:, 0].float()
     ok = ((o - 2 * v0).abs().amax(-1) < 0.1) | (o.abs().amax(-1) == 0)
     assert ok.all()
+
+
+@pytest.mark.gpu
+def test_allreduce_mc_matches_nccl_on_two_gpus():
+    """cpc_allreduce_mc (NVSwitch multimem all-reduce, in place on a symmetric buffer) against NCCL AVG over bucket
+    sizes of the step (tools/allreduce_bench.py --check-only under torchrun).  Needs two GPUs of one NVSwitch box."""
+    import subprocess
+    import sys
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29641",
+                          os.path.join(root, "tools", "allreduce_bench.py"), "--check-only"],
+                         capture_output=True, text=True, timeout=300, cwd=root)
+    text = out.stdout + out.stderr
+    if "multicast unavailable" in text:
+        pytest.skip("no NVLink multicast on this box")
+    assert out.returncode == 0 and "ALLREDUCE_MC OK" in text, text[-2000:]

@@ -313,8 +313,10 @@ def test_fused_adam_matches_torch_adam():
 
 def test_staged_adam_equals_single_launch():
     """FusedAdam.attach(): stepping each gradient bucket from the ops.grad_ready hook (side stream, one counter
-    advance per iteration) gives bit-identical parameters to one launch after backward."""
+    advance per iteration) gives bit-identical parameters to one launch after backward -- also when the heads announce
+    their feed-forward gradients early (ops.EARLY_FFN: stages criterion.ffn / .front / .tail)."""
     _need_gpu()
+    from cpc2_b200 import ops
     from cpc2_b200 import train as T
     from cpc2_b200.optim import FusedAdam
     args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
@@ -322,26 +324,39 @@ def test_staged_adam_equals_single_launch():
     seq = (0.1 * torch.randn(4, 2, 1, args.sizeWindow, generator=g)).cuda()
     label = torch.zeros(4, dtype=torch.long, device="cuda")
     finals = []
-    for staged in (False, True):
+    seen = []
+    spy = lambda stage, gflat, params=None, grads=None: seen.append(stage)
+    for staged in (False, True, "early"):
         model, crit = build(args)
         model.eval()
         crit.eval()
         opt = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=1e-3)
         if staged:
             opt.attach()
+        early0 = ops.EARLY_FFN
+        ops.EARLY_FFN = "1" if staged == "early" else "0"
+        ops.GRAD_READY.append(spy)
         try:
             for it in range(3):
                 torch.manual_seed(50 + it)
+                del seen[:]
                 T.forwardBackward(model, crit, seq, label)
                 opt.step()
                 opt.zero_grad()
         finally:
             opt.detach()
+            ops.GRAD_READY.remove(spy)
+            ops.EARLY_FFN = early0
         torch.cuda.synchronize()
         assert float(opt._groups[0]["state"][0]) == 3
+        if staged == "early":
+            assert seen[:3] == ["criterion.ffn", "criterion.front", "criterion.tail"], seen
+        else:
+            assert seen[0] == "criterion", seen
         finals.append([p.detach().clone() for p in list(crit.parameters()) + list(model.parameters())])
-    for a, b in zip(*finals):
-        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)  # gradients differ by fp32 atomics order only
+    for other in finals[1:]:
+        for a, b in zip(finals[0], other):
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)  # gradients differ by fp32 atomics order only
 
 
 def test_graphed_step_with_fused_adam_learns():
@@ -483,3 +498,30 @@ def test_val_step_and_keep_hidden_streaming():
     assert not model.splittable()
     ar.keepHidden, ar.hidden = False, None
     assert model.splittable()
+
+
+@pytest.mark.gpu
+def test_symmetric_allreduce_step_equals_nccl_step_on_two_gpus():
+    """The data-parallel step with its gradient arenas in multicast symmetric memory + cpc_allreduce_mc gives the same
+    losses after 8 Adam steps as the same step over NCCL (bench.py at N = 2, CPC_SYMMETRIC=1 vs 0)."""
+    import json
+    import subprocess
+    import sys
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lines = {}
+    for mode, port in (("0", 29651), ("1", 29652)):
+        env = dict(os.environ, CPC_SYMMETRIC=mode)
+        out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                              "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(root, "bench.py"),
+                              "--gpus", "2", "--steps", "5", "--warmup", "3"],
+                             capture_output=True, text=True, timeout=400, cwd=root, env=env)
+        if mode == "1" and out.returncode != 0 and "multicast" in (out.stderr + out.stdout):
+            pytest.skip("no NVLink multicast on this box")
+        assert out.returncode == 0, out.stderr[-2000:]
+        lines[mode] = json.loads(out.stdout.strip().splitlines()[-1])
+    assert lines["1"]["config"]["grad_allreduce"].startswith("cpc_allreduce_mc")
+    assert lines["0"]["config"]["grad_allreduce"].startswith("NCCL")
+    # rank 0's loss after the same 16 optimizer steps on the same batches (bf16 step, fp32 atomics order differs)
+    assert abs(lines["0"]["loss_mean"] - lines["1"]["loss_mean"]) < 1e-2, (lines["0"]["loss_mean"], lines["1"]["loss_mean"])
