@@ -49,9 +49,36 @@ class FFNetwork(nn.Module):
         self.drop = nn.Dropout(dropout)
 
 
+class EqualizedConv1d(nn.Module):
+    """cpc/criterion/custom_layers.py:44-105: nn.Conv1d with N(0, 1) weights, zero bias, output scaled by
+    sqrt(2 / (Cin * kernelSize)) at run time (parameter container)."""
+
+    def __init__(self, nChannelsPrevious, nChannels, kernelSize, padding=0, bias=True, stride=1, equalized=True,
+                 lrMul=1.0, initBiasToZero=True):
+        super().__init__()
+        self.module = nn.Conv1d(nChannelsPrevious, nChannels, kernelSize, padding=padding, bias=bias, stride=stride)
+        self.equalized = equalized
+        if initBiasToZero and self.module.bias is not None:
+            self.module.bias.data.fill_(0)
+        self.weight = 1.0
+        if equalized:
+            self.module.weight.data.normal_(0, 1)
+            self.weight = math.sqrt(2.0 / (nChannelsPrevious * kernelSize)) * lrMul
+
+
+class ShiftedConv(nn.Module):
+    """cpc/criterion/criterion.py:23-41: causal convolution head (kernelSize - 1 zero frames in front of the
+    sequence, then EqualizedConv1d); parameter container, run by ConvHeads."""
+
+    def __init__(self, dimOutputAR, dimOutputEncoder, kernelSize):
+        super().__init__()
+        self.module = EqualizedConv1d(dimOutputAR, dimOutputEncoder, kernelSize, equalized=True, padding=0)
+        self.kernelSize = kernelSize
+
+
 class PredictionNetwork(nn.Module):
     """cpc/criterion/criterion.py:97-173.  rnnMode 'transformer' (default) or the bias-free Linear that any
-    other non-recurrent string selects in the reference ('linear', None, False)."""
+    other string selects in the reference ('linear', None, False); 'ffd', 'conv4/8/12', 'RNN', 'LSTM' heads."""
 
     def __init__(self, nPredicts, dimOutputAR, dimOutputEncoder, rnnMode=None, dropout=False, sizeInputSeq=116,
                  transformer_pruning=0):
@@ -62,13 +89,18 @@ class PredictionNetwork(nn.Module):
         self.dimOutputEncoder = dimOutputEncoder
         self.sizeInputSeq = sizeInputSeq
         self.dropout = nn.Dropout(p=0.5) if dropout else None  # criterion.py:113; fused path: cpc_dropout
-        if rnnMode in ("RNN", "LSTM", "conv4", "conv8", "conv12"):
-            raise NotImplementedError(f"cpc2_b200: prediction heads rnnMode='{rnnMode}' have no sm_100a kernels; "
-                                      "use 'transformer' (default) or 'linear'")
         self.transformer = rnnMode == 'transformer'
         self.ffd = rnnMode == 'ffd'
+        self.recurrent = rnnMode if rnnMode in ("RNN", "LSTM") else None
+        self.conv = {"conv4": 4, "conv8": 8, "conv12": 12}.get(rnnMode)
         for i in range(nPredicts):
-            if self.transformer:
+            if self.recurrent == "RNN":  # criterion.py:116-119 (NOT batch_first: see RecurrentHeads)
+                self.predictors.append(nn.RNN(dimOutputAR, dimOutputEncoder))
+            elif self.recurrent == "LSTM":  # criterion.py:120-124
+                self.predictors.append(nn.LSTM(dimOutputAR, dimOutputEncoder, batch_first=True))
+            elif self.conv:  # criterion.py:129-140
+                self.predictors.append(ShiftedConv(dimOutputAR, dimOutputEncoder, self.conv))
+            elif self.transformer:
                 self.predictors.append(buildTransformerAR(dimOutputEncoder, dimOutputAR, nLayers=1,
                                                           sizeSeq=sizeInputSeq, abspos=False))
             elif self.ffd:
@@ -88,6 +120,10 @@ class PredictionNetwork(nn.Module):
                 eng = TransformerStack([p[0] for p in self.predictors])
             elif self.ffd:
                 eng = FfdHeads([p for p in self.predictors])
+            elif self.recurrent:
+                eng = RecurrentHeads([p for p in self.predictors], self.recurrent, self.sizeInputSeq)
+            elif self.conv:
+                eng = ConvHeads([p for p in self.predictors], self.sizeInputSeq)
             else:
                 eng = LinearHeads([p for p in self.predictors])
             object.__setattr__(self, "_engine", eng)
@@ -243,6 +279,123 @@ class FfdHeads:
                accumulate=True, alpha=self.c1)
         ops.join()
         return dx, gflat
+
+
+class ConvHeads:
+    """K ShiftedConv heads (criterion.py:23-41, rnnMode conv4 / conv8 / conv12) on the same input.  The ks frames
+    ending at t are unfolded ONCE into X [T, ks*H] (zeros before the start of each window) and the K causal
+    convolutions become one grouped GEMM with reduction length ks*H; (conv + b) * c = c * conv + (c b)."""
+
+    def __init__(self, convs, sizeSeq):
+        self.G = self.n_out = len(convs)
+        self.S = sizeSeq
+        self.dout, self.d, self.ks = convs[0].module.module.weight.shape
+        self.c = float(convs[0].module.weight)
+        if self.d % 8 or self.dout % 8:
+            raise NotImplementedError("ConvHeads: dimensions must be multiples of 8")
+        self.arena = ops.Arena([c.module.module.weight for c in convs] + [c.module.module.bias for c in convs])
+
+    def spans(self, flat):
+        G = self.G
+        return dict(W=self.arena.span(flat, 0, G, (G, self.dout, self.d, self.ks)),
+                    b=self.arena.span(flat, G, G, (G, self.dout)))
+
+    def forward(self, x, T, shared, training, want_f32=False):
+        G, d, do, ks, S = self.G, self.d, self.dout, self.ks, self.S
+        if T % S != 0:
+            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+        P32 = self.spans(self.arena.ensure())
+        P16 = self.spans(self.arena.bf16())
+        # X[b, t, j, :] = c[b, t - (ks - 1) + j, :]
+        xu = torch.nn.functional.pad(x.view(T // S, S, d), (0, 0, ks - 1, 0)).unfold(1, ks, 1)  # [Bt, S, d, ks]
+        xu = xu.permute(0, 1, 3, 2).contiguous().view(T, ks * d)
+        w2 = P16["W"].permute(0, 1, 3, 2).contiguous().view(G, do, ks * d)  # W2[g, co, j*d + ci] = W[g, co, ci, j]
+        out = torch.empty(G, T, do, device=x.device, dtype=BF16)
+        out32 = torch.empty(G, T, do, device=x.device) if want_f32 else None
+        ops.linear_fwd(xu, w2, T, do, ks * d, groups=G, x_shared=True, out_bf16=out, out_f32=out32,
+                       bias=P32["b"] * self.c, bias_gs=do, alpha=self.c)
+        return out, out32, dict(xu=xu, w2=w2, T=T)
+
+    def backward(self, sv, dout):
+        G, d, do, ks, S, T = self.G, self.d, self.dout, self.ks, self.S, sv["T"]
+        dev = dout.device
+        if dout.dtype != BF16:
+            dout = K.cast_bf16(dout.contiguous().float())
+        dout = dout.view(G, T, do)
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
+        Gd = self.spans(gflat)
+        dw2 = torch.zeros(G, do, ks * d, device=dev)
+        dxu = torch.zeros(T, ks * d, device=dev)
+        with ops.side(0):  # dW = c * dout^T . X, back to the Conv1d layout [co, ci, j]
+            K.gemm(K.mnmajor(dout), K.mnmajor(sv["xu"], gmul=0), do, ks * d, T, groups=G,
+                   k_splits=ops.auto_splits(do, ks * d, T, G), out_f32=dw2, accumulate=True, alpha=self.c)
+            Gd["W"].copy_(dw2.view(G, do, ks, d).permute(0, 1, 3, 2))
+        with ops.side(1):
+            K.colsum(dout, Gd["b"], T, do, do, T * do, G)
+            Gd["b"].mul_(self.c)
+        # dX = c * sum_g dout_g . W2_g, then folded back onto the frames it was unfolded from
+        A = K.View(dout, do, T, G, do, T * do, major=0, gmul=0)
+        B = K.View(sv["w2"], ks * d, do, G, ks * d, do * ks * d, major=1, gmul=0)
+        K.gemm(A, B, T, ks * d, G * do, k_per_slab=do, k_splits=ops.auto_splits(T, ks * d, G * do, 1, do), out_f32=dxu,
+               accumulate=True, alpha=self.c)
+        Bt = T // S
+        dpad = torch.zeros(Bt, S + ks - 1, d, device=dev)
+        dxu = dxu.view(Bt, S, ks, d)
+        for j in range(ks):
+            dpad[:, j:j + S] += dxu[:, :, j]
+        dx = dpad[:, ks - 1:].reshape(T, d)
+        ops.join()
+        return dx, gflat
+
+
+class RecurrentHeads:
+    """K recurrent heads (criterion.py:116-124): nn.LSTM(dimAR, dimEncoder, batch_first=True), or nn.RNN(dimAR,
+    dimEncoder) -- which the reference builds WITHOUT batch_first and feeds c [B, W, H] as is, so its recurrence
+    runs over the B windows of the batch with the W frames as independent rows; reproduced as such.  Each head is
+    the cluster recurrence kernel of the AR network (cpc_lstm_fwd / bwd through model._RecurrentFn); the heads'
+    gradients are gathered into one arena so the criterion announces one bucket like every other head type."""
+
+    def __init__(self, rnns, cell, sizeSeq):
+        self.G = self.n_out = len(rnns)
+        self.cell, self.S = cell, sizeSeq
+        self.d, self.dout = rnns[0].input_size, rnns[0].hidden_size
+        self.per = [[r.weight_ih_l0, r.weight_hh_l0, r.bias_ih_l0, r.bias_hh_l0] for r in rnns]
+        self.arena = ops.Arena([p for ps in self.per for p in ps])
+
+    def forward(self, x, T, shared, training, want_f32=False):
+        from .model import _RecurrentFn
+        G, d, do, S = self.G, self.d, self.dout, self.S
+        if T % S != 0:
+            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+        self.arena.ensure()
+        xin = x.float().view(T // S, S, d)
+        if self.cell == "RNN":
+            xin = xin.transpose(0, 1).contiguous()  # rows = frames, time = the windows of the batch
+        with torch.enable_grad():
+            xin = xin.detach().requires_grad_(True)
+            outs = []
+            for ps in self.per:
+                o = _RecurrentFn.apply(xin, None, None, 1, None, self.cell, *ps)[0]
+                outs.append(o.transpose(0, 1) if self.cell == "RNN" else o)
+            out32 = torch.stack(outs).reshape(G, T, do)
+        out = K.cast_bf16(out32.detach())
+        return out.view(G, T, do), (out32.detach() if want_f32 else None), dict(xin=xin, out32=out32, T=T)
+
+    def backward(self, sv, dout):
+        G, d, do, T = self.G, self.d, self.dout, sv["T"]
+        gflat = ops.grad_arena(self.arena, self.arena.numel, dout.device)
+        views = self.arena.grad_views(gflat)
+        hooks = list(ops.GRAD_READY)
+        ops.GRAD_READY[:] = []  # the per-head arenas of _RecurrentFn are not buckets of their own
+        try:
+            grads = torch.autograd.grad([sv["out32"]], [sv["xin"]] + list(self.arena.params),
+                                        [dout.float().reshape(G, T, do)])
+        finally:
+            ops.GRAD_READY[:] = hooks
+        dx = grads[0].transpose(0, 1) if self.cell == "RNN" else grads[0]
+        for v, g in zip(views, grads[1:]):
+            v.copy_(g)
+        return dx.reshape(T, d).contiguous(), gflat
 
 
 class _HeadsFn(torch.autograd.Function):

@@ -488,7 +488,7 @@ class _RecurrentFn(torch.autograd.Function):
         sizes = []
         for l in range(nl):  # four-slot (padded) gradient spans; the returned gradients are their leading G*H rows
             sizes += [4 * H * ctx.saved[l][1], 4 * H * H, 4 * H, 4 * H]
-        gflat = ops.grad_arena("ar", sum(sizes), dev)
+        gflat = ops.grad_arena(("rnn", id(ctx.params[0])), sum(sizes), dev)
         gv, off = [], 0
         for n_ in sizes:
             gv.append(gflat[off:off + n_])

@@ -308,6 +308,21 @@ def prediction_heads(p, c, K, rnn_mode, size_seq, prefix="wPrediction.predictors
             w2, b2 = p[f"{prefix}{k}.lin2.module.weight"], p[f"{prefix}{k}.lin2.module.bias"]
             h = F.relu((c @ w1.t() + b1) * math.sqrt(2.0 / w1.shape[1]))
             out.append((h @ w2.t() + b2) * math.sqrt(2.0 / w2.shape[1]))
+        elif rnn_mode == "LSTM":
+            # criterion.py:120-123: nn.LSTM(dimAR, dimEncoder, batch_first=True), zero initial state, output sequence
+            out.append(lstm_forward(p, c, 1, prefix=f"{prefix}{k}.")[0])
+        elif rnn_mode == "RNN":
+            # criterion.py:116-119: nn.RNN(dimAR, dimEncoder) WITHOUT batch_first, fed c [B, W, H] as is: the
+            # recurrence runs over dim 0 (the B windows of the batch), the W frames are its "batch"
+            out.append(rnn_forward(p, c.transpose(0, 1), 1, prefix=f"{prefix}{k}.")[0].transpose(0, 1))
+        elif rnn_mode in ("conv4", "conv8", "conv12"):
+            # criterion.py:23-41,129-137: ShiftedConv = ks-1 zero frames in front, then EqualizedConv1d
+            # (custom_layers.py:44-105): (conv1d(x) + b) * sqrt(2 / (Cin * ks)), weights N(0, 1)
+            w, b = p[f"{prefix}{k}.module.module.weight"], p[f"{prefix}{k}.module.module.bias"]
+            ks = w.shape[2]
+            x = F.pad(c.permute(0, 2, 1), (ks - 1, 0))
+            y = F.conv1d(x, w, b) * math.sqrt(2.0 / (w.shape[1] * ks))
+            out.append(y.permute(0, 2, 1))
         else:  # any other string falls through to the bias-free Linear (criterion.py:145-146)
             out.append(c @ p[f"{prefix}{k}.weight"].t())
     return out

@@ -31,6 +31,10 @@ CASES = {
     "tiny_lstm_multihead": (dict(SMALL, arMode="LSTM", rnnMode="transformer", multihead_rnn=True), 2),
     # feed-forward heads (criterion.py:125-128)
     "tiny_lstm_ffd": (dict(SMALL, arMode="LSTM", rnnMode="ffd"), 2),
+    # causal-convolution heads (ShiftedConv, criterion.py:23-41,129-140) and recurrent heads (:116-124)
+    "tiny_lstm_conv4": (dict(SMALL, arMode="LSTM", rnnMode="conv4"), 2),
+    "tiny_lstm_headsLSTM": (dict(SMALL, arMode="LSTM", rnnMode="LSTM"), 2),
+    "tiny_lstm_headsRNN": (dict(SMALL, arMode="LSTM", rnnMode="RNN"), 2),
 }
 
 

@@ -9,7 +9,8 @@ import torch
 from oracle import cpc_oracle as oc
 
 FULL_CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear",
-              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd"]
+              "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd",
+              "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN"]
 
 
 def _load(golden_dir, name):

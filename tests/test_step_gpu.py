@@ -90,7 +90,7 @@ def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, min_cos=0.99)
 
 
 GOLDEN_CASES = ["tiny_lstm_linear", "tiny_lstm_reverse_linear", "tiny_transformer_ar_linear", "tiny_gru2_transformer",
-                "tiny_lstm_multihead", "tiny_lstm_ffd"]
+                "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN"]
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -108,8 +108,11 @@ def test_against_reference_golden(name):
     out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long())
     # tiny models (C = 32): gradients of 32-wide layers carry more bf16 noise -> cosine 0.98; the two-layer GRU +
     # transformer-head case (B = 2, 16 frames) measured 0.9755 on one ChannelNorm gain (a 32-term cancelling sum)
-    check_against(out, fx["loss"], fx["acc"], fx["c"], fx["z"], fx["grads"],
-                  min_cos=0.97 if name in ("tiny_gru2_transformer", "tiny_lstm_multihead") else 0.98)
+    # tiny_lstm_headsLSTM: zero-state LSTM heads at C = 32 emit |pred| ~ 0.05, the logits are ~1e-3 and the encoder's
+    # gradients are differences of nearly equal terms: heads / AR / conv3-4 tensors >= 0.98, the first encoder layers
+    # 0.935-0.979.  The same heads at C = 128 (test_against_oracle[lstm_heads]) hold 0.985 / 0.99 on every tensor.
+    min_cos = {"tiny_gru2_transformer": 0.97, "tiny_lstm_multihead": 0.97, "tiny_lstm_headsLSTM": 0.93}.get(name, 0.98)
+    check_against(out, fx["loss"], fx["acc"], fx["c"], fx["z"], fx["grads"], min_cos=min_cos)
     # (tiny_lstm_multihead: every tensor >= 0.98 except gEncoder.batchNorm0.weight at 0.965, the same 32-term
     # cancelling sum)
 
@@ -141,6 +144,13 @@ ORACLE_CASES = {
                                     sizeWindow=5120),
     "multihead_rnn_default_size": dict(multihead_rnn=True),
     "ffd_heads_default_size": dict(rnnMode="ffd"),
+    "conv8_heads": dict(rnnMode="conv8", hiddenEncoder=128, hiddenGar=128, nPredicts=6, negativeSamplingExt=32,
+                        sizeWindow=10240),
+    "conv4_heads_default_size": dict(rnnMode="conv4"),
+    "lstm_heads": dict(rnnMode="LSTM", hiddenEncoder=128, hiddenGar=128, nPredicts=4, negativeSamplingExt=32,
+                       sizeWindow=10240),
+    "rnn_heads": dict(rnnMode="RNN", hiddenEncoder=128, hiddenGar=128, nPredicts=4, negativeSamplingExt=32,
+                      sizeWindow=10240),
 }
 
 
