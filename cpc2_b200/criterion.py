@@ -545,8 +545,7 @@ class _CriterionFn(torch.autograd.Function):
         logits = torch.empty(Kp, T, BS, device=dev)
         ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D)
         lse = torch.empty(Kp, T, device=dev)
-        loss_sum = torch.zeros(Kp, device=dev)
-        hits = torch.zeros(Kp, device=dev)
+        loss_sum, hits = torch.zeros(2, Kp, device=dev).unbind(0)  # (one memset)
         K.nce_fwd(logits, ext, weights, lse, loss_sum, hits, Kp, B, W, S, NEG, BS)
         ctx.eng, ctx.saved = eng, saved
         ctx.t = (preds, zb, logits, lse, ext, weights)
@@ -570,8 +569,8 @@ class _CriterionFn(torch.autograd.Function):
         K.nce_bwd(logits, ext, weights, lse, gscale, dlog[0], Kp, B, W, S, NEG, BS, dlogits_lo=dlog[1])
         # dpred_k = dlog_k . z / D  (main stream: the heads' backward waits for it)
         dpred = torch.empty(Kp, T, D, device=dev)
-        dz = torch.zeros(BS, D, device=dev)
-        dc = torch.zeros(B, S, H, device=dev)
+        acc0 = torch.zeros(BS * D + B * S * H, device=dev)  # dz | dc, one memset
+        dz, dc = acc0[:BS * D].view(BS, D), acc0[BS * D:].view(B, S, H)
         # dz = sum_k dlog_k^T . pred_k / D   (reduction over (k, token)); nothing downstream of the criterion
         # needs it before the encoder backward, so it runs on a side stream next to the heads' backward
         with ops.side(2):

@@ -173,11 +173,14 @@ def _alloc_bwd(N, W, C, dev):
     in GEMM layout (zeroed: split-K accumulates into it) and the padded input gradient."""
     L, _ = _geometry(N, W)
     w = [None]
+    dwf = torch.zeros(sum(C * GEOMETRY[l][0] * C for l in range(1, 5)), device=dev)  # one memset for the four layers
+    off = 0
     for l in range(1, 5):
         k, s, pd = GEOMETRY[l]
         w.append(dict(dy=torch.empty(N, L[l] + 2, C, device=dev, dtype=BF16),
-                      dwf=torch.zeros(C, k * C, device=dev),
+                      dwf=dwf[off:off + C * k * C].view(C, k * C),
                       dxp=torch.empty(N, L[l - 1] + 2 * pd, C, device=dev, dtype=BF16)))
+        off += C * k * C
     return w
 
 
@@ -476,14 +479,17 @@ class _RecurrentFn(torch.autograd.Function):
         ctx.saved = saved
         ctx.params = list(params)
         ctx.dims = (N, S, Cin, H, nl, cell)
+        ctx.set_materialize_grads(False)  # h_n / c_n carry no gradient on this path: no zero tensors made for them
         return out, torch.stack(h_ns), torch.stack(c_ns)
 
     @staticmethod
     def backward(ctx, dout, dh_n, dc_n):
         N, S, Cin, H, nl, cell = ctx.dims
-        dev = dout.device
+        dev = ctx.saved[0][4].device
         G = _GATES[cell]
-        d = dout.contiguous().float()
+        if dh_n is not None or dc_n is not None:
+            raise NotImplementedError("cpc2_b200: gradients through the final hidden state of CPCAR are not on the path")
+        d = dout.contiguous().float() if dout is not None else torch.zeros(N, S, H, device=dev)
         grads = [None] * (4 * nl)
         sizes = []
         for l in range(nl):  # four-slot (padded) gradient spans; the returned gradients are their leading G*H rows
