@@ -119,8 +119,12 @@ class CPCEncoder(nn.Module):
         self._pref = ops.Prefetched(ws, bufs, 3)
 
     def forward(self, x):
-        """x [N, 1, W] fp32 (W multiple of 160) -> [N, C, W/160] fp32 (a view of channels-last memory)."""
+        """x [N, 1, W] fp32 -> [N, C, S] fp32 (a view of channels-last memory), S = W / 160 for the training windows;
+        other lengths (the last chunk of a file at inference) run forward-only."""
         ops.require_cuda(x)
+        if x.shape[-1] % 160 != 0 and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            raise NotImplementedError("cpc2_b200: training windows must be a multiple of 160 samples (the reference's "
+                                      "sizeWindow, default 20480); any length runs forward-only under torch.no_grad()")
         pref, self._pref = getattr(self, "_pref", None), None
         return _EncoderFn.apply(x, _EncPlan(pref=pref), *self._params())
 
@@ -141,7 +145,13 @@ def _pack_conv_weights(ws, bufs):
 
 
 def _geometry(N, W):
-    L = [W // 5, W // 20, W // 40, W // 80, W // 160]
+    """Frames after each of the five strided convolutions (floor arithmetic of nn.Conv1d, cpc/model.py:85-94): W / 5,
+    W / 20 ... W / 160 when W is a multiple of 160, and whatever the floor gives for the last chunk of a file
+    (feature_loader.py:323-367 feeds chunks of any length)."""
+    L, n = [], W
+    for k, s, pd in GEOMETRY:
+        n = (n + 2 * pd - k) // s + 1
+        L.append(n)
     pad_next = [GEOMETRY[i + 1][2] for i in range(4)] + [0]
     return L, pad_next
 
@@ -214,12 +224,14 @@ class _EncoderFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, plan, *params):
         N, one, W = x.shape
-        if one != 1 or W % 160 != 0:
-            raise ValueError("CPCEncoder expects [N, 1, W] with W a multiple of 160")
+        if one != 1:
+            raise ValueError("CPCEncoder expects [N, 1, W]")
         C = params[0].shape[0]
         dev = x.device
         p = [t.detach() for t in params]
         L, pad_next = _geometry(N, W)
+        if L[4] < 1:
+            raise ValueError(f"CPCEncoder: {W} samples are shorter than one output frame")
         future = plan.role == "future"
         x2 = x.detach().reshape(N, W).contiguous().float()
         bufs = plan.fwd_bufs if plan.fwd_bufs is not None else _alloc_fwd(N, W, C, dev)

@@ -511,6 +511,40 @@ def test_val_step_and_keep_hidden_streaming():
 
 
 @pytest.mark.gpu
+def test_build_feature_chunks_of_any_length():
+    """Feature extraction as cpc/feature_loader.py:323-367 (buildFeature) drives the model: one file, batch 1, no
+    grad, chunks of maxSizeSeq = 64000 samples plus a last chunk whose length is not a multiple of the 160-sample
+    hop -- with and without the AR state carried across chunks (keepHidden) -- against the oracle."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    from oracle import cpc_oracle as oc
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120,
+                         rnnMode="linear")
+    model, _ = build(args)
+    model.eval()
+    g = torch.Generator().manual_seed(77)
+    wav = 0.1 * torch.randn(1, 64000 * 2 + 23457, generator=g)
+    st = {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+    for keep in (False, True):
+        model.gAR.keepHidden, model.gAR.hidden = keep, None
+        outs, refs, state = [], [], None
+        for start in range(0, wav.shape[1], 64000):
+            chunk = wav[:, start:start + 64000].view(1, 1, -1)
+            with torch.no_grad():
+                c, z, _ = model(chunk.cuda(), None)
+            outs.append((c.float().cpu(), z.float().cpu()))
+            zr = oc.encoder_forward(st, chunk).permute(0, 2, 1)
+            cr, state = oc.lstm_forward(st, zr, 1, state=state if keep else None)
+            refs.append((cr, zr))
+        for (c, z), (cr, zr) in zip(outs, refs):
+            assert c.shape == cr.shape and z.shape == zr.shape, (c.shape, cr.shape)
+            assert (z - zr).abs().max() <= 3e-2 * zr.abs().max() + 1e-3
+            assert (c - cr).abs().max() <= 3e-2 * cr.abs().max() + 1e-3
+        assert sum(c.shape[1] for c, _ in outs) == 400 + 400 + 146  # floor arithmetic of the five strided convs
+    model.gAR.keepHidden, model.gAR.hidden = False, None
+
+
+@pytest.mark.gpu
 def test_symmetric_allreduce_step_equals_nccl_step_on_two_gpus():
     """The data-parallel step with its gradient arenas in multicast symmetric memory + cpc_allreduce_mc gives the same
     losses after 8 Adam steps as the same step over NCCL (bench.py at N = 2, CPC_SYMMETRIC=1 vs 0)."""
