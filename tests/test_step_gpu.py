@@ -511,6 +511,50 @@ def test_val_step_and_keep_hidden_streaming():
 
 
 @pytest.mark.gpu
+def test_reference_wrappers_dataparallel_and_ddp():
+    """cpc/train.py:523-532 wraps model and criterion in nn.DataParallel (single process) or DistributedDataParallel
+    (--distributed): both wrappers must drive the sm_100a modules to the same losses and gradients as the bare modules
+    (the wrappers take the literal concatenated call of train.py:95-104; DDP's own bucket all-reduce replaces ours)."""
+    _need_gpu()
+    import torch.distributed as dist
+    from cpc2_b200 import train as T
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    g = torch.Generator().manual_seed(5)
+    seq = (0.1 * torch.randn(4, 2, 1, args.sizeWindow, generator=g)).cuda()
+    label = torch.zeros(4, dtype=torch.long, device="cuda")
+
+    def one(wrap):
+        model, crit = build(args)
+        model.eval()
+        crit.eval()
+        wm, wc = wrap(model), wrap(crit)
+        torch.manual_seed(9)
+        losses, _ = T.forwardBackward(wm, wc, seq, label)
+        torch.cuda.synchronize()
+        return losses.detach().clone(), {k: p.grad.detach().clone() for k, p in
+                                         list(model.named_parameters()) + list(crit.named_parameters())}
+
+    base_l, base_g = one(lambda m: m)
+    dp_l, dp_g = one(lambda m: torch.nn.DataParallel(m, device_ids=[0]))
+    assert torch.allclose(base_l, dp_l, atol=1e-5)
+    for k, v in base_g.items():
+        assert cosine(v, dp_g[k]) > 0.9999, k
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29671")
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+    try:
+        ddp_l, ddp_g = one(lambda m: torch.nn.parallel.DistributedDataParallel(m, device_ids=[0]))
+    finally:
+        if created:
+            dist.destroy_process_group()
+    assert torch.allclose(base_l, ddp_l, atol=1e-5)
+    for k, v in base_g.items():
+        assert cosine(v, ddp_g[k]) > 0.9999, k
+
+
+@pytest.mark.gpu
 def test_build_feature_chunks_of_any_length():
     """Feature extraction as cpc/feature_loader.py:323-367 (buildFeature) drives the model: one file, batch 1, no
     grad, chunks of maxSizeSeq = 64000 samples plus a last chunk whose length is not a multiple of the 160-sample
