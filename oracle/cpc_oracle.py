@@ -379,8 +379,10 @@ def quality_weighting(signal_quality, W, growth_rate, inflection_point_x):
 # the training step (forward + backward), cpc/train.py:95-109
 # --------------------------------------------------------------------------- #
 def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n_layers=1,
-               rnn_mode="transformer", cpc_mode=None, abspos=False, n_skipped=0, with_grad=True, multihead=False):
-    """sequence [B,2,1,W] fp32.  Returns dict(loss [1,K], acc [1,K], c, z, grads{name: tensor})."""
+               rnn_mode="transformer", cpc_mode=None, abspos=False, n_skipped=0, with_grad=True, multihead=False,
+               signal_quality=None, growth_rate=None, inflection_point_x=None):
+    """sequence [B,2,1,W] fp32.  Returns dict(loss [1,K], acc [1,K], c, z, grads{name: tensor}).
+    signal_quality [B, n] (train.py:104-106): per-token loss weights through quality_weighting."""
     B = sequence.shape[0]
     if with_grad:
         p = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
@@ -388,8 +390,11 @@ def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n
     S = combined.shape[-1] // DOWNSAMPLING
     c, z = cpc_model_forward(p, combined, ar_mode, n_layers, cpc_mode == "reverse", S, abspos)
     c_past, z_future = c[:B], z[B:]                                      # train.py:102-103
+    weights = None
+    if signal_quality is not None:
+        weights = quality_weighting(signal_quality, S - K, growth_rate, inflection_point_x)
     loss, acc = criterion_forward(p, c_past, z_future, batch_idx, seq_idx, K, NEG, rnn_mode,
-                                  mode=cpc_mode, n_skipped=n_skipped, multihead=multihead)
+                                  mode=cpc_mode, n_skipped=n_skipped, multihead=multihead, weights=weights)
     out = {"loss": loss.detach(), "acc": acc.detach(), "c": c.detach(), "z": z.detach()}
     if with_grad:
         loss.sum().backward()                                            # train.py:108-109

@@ -73,8 +73,9 @@ def build_reference(args, seed=0):
     return m, crit
 
 
-def reference_step(m, crit, sequence, crit_seed=4321, train_mode=False):
-    """cpc/train.py:95-109 on whatever device the modules live on. Returns dict."""
+def reference_step(m, crit, sequence, crit_seed=4321, train_mode=False, signal_quality=None):
+    """cpc/train.py:95-109 on whatever device the modules live on. Returns dict.
+    signal_quality [B, n]: per-window quality scores (train.py:104-106 passes them to the criterion)."""
     m.train(train_mode)
     crit.train(train_mode)
     for q in list(m.parameters()) + list(crit.parameters()):
@@ -86,7 +87,7 @@ def reference_step(m, crit, sequence, crit_seed=4321, train_mode=False):
     c, z, label = m(combined, label)
     c_p, z_f = c[:B], z[B:]
     torch.manual_seed(crit_seed)
-    losses, acc = crit(c_p, z_f, label[:B], None)
+    losses, acc = crit(c_p, z_f, label[:B], signal_quality)
     losses.sum().backward()
     grads = {k: v.grad.detach().clone() for k, v in m.named_parameters() if v.grad is not None}
     grads.update({k: v.grad.detach().clone() for k, v in crit.named_parameters() if v.grad is not None})

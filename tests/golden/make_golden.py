@@ -35,6 +35,9 @@ CASES = {
     "tiny_lstm_conv4": (dict(SMALL, arMode="LSTM", rnnMode="conv4"), 2),
     "tiny_lstm_headsLSTM": (dict(SMALL, arMode="LSTM", rnnMode="LSTM"), 2),
     "tiny_lstm_headsRNN": (dict(SMALL, arMode="LSTM", rnnMode="RNN"), 2),
+    # signal-quality weighted loss (criterion.py:230,334-338,350) with the first prediction step dropped (--n_skipped)
+    "tiny_lstm_quality_skip1": (dict(SMALL, arMode="LSTM", rnnMode="linear", n_skipped=1, growth_rate=10.0,
+                                     inflection_point_x=0.5, signal_quality=True), 3),
 }
 
 
@@ -49,10 +52,14 @@ def fingerprint(state):
 
 
 def run_case(name, over, B, full=True):
+    over = dict(over)
+    quality = None
+    if over.pop("signal_quality", False):  # [B, 5] scores in (0, 1), as the dataset's per-window quality tracks
+        quality = torch.rand(B, 5, generator=torch.Generator().manual_seed(99))
     args = rh.reference_args(**over)
     m, crit = rh.build_reference(args, seed=0)
     seq = synthetic_sequence(B, args.sizeWindow)
-    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=False)
+    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=False, signal_quality=quality)
     # the sampled indices, by replaying the reference's own sampleClean RNG calls
     S = args.sizeWindow // 160
     W = S - args.nPredicts
@@ -85,6 +92,9 @@ def run_case(name, over, B, full=True):
         "fingerprint": fingerprint(state),
         "torch": torch.__version__,
     }
+    if quality is not None:
+        fx["signal_quality"] = quality
+        fx["args"].update(growth_rate=args.growth_rate, inflection_point_x=args.inflection_point_x)
     if full:
         fx.update({"batch_idx": batch_idx.int(), "seq_idx": seq_idx.int(), "ext_idx": ext.int(),
                    "state": state, "sequence": seq, "c": out["c"], "z": out["z"], "grads": out["grads"]})

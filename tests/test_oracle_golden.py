@@ -10,7 +10,7 @@ from oracle import cpc_oracle as oc
 
 FULL_CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear",
               "tiny_lstm_reverse_linear", "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd",
-              "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN"]
+              "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN", "tiny_lstm_quality_skip1"]
 
 
 def _load(golden_dir, name):
@@ -39,7 +39,9 @@ def test_step_matches_reference(golden_dir, name):
     out = oc.train_step(fx["state"], fx["sequence"], fx["batch_idx"].long(), fx["seq_idx"].long(),
                         K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"],
                         n_layers=a["nLevelsGRU"], rnn_mode=a["rnnMode"], cpc_mode=a["cpc_mode"],
-                        abspos=a["abspos"], n_skipped=a["n_skipped"], multihead=a.get("multihead_rnn", False))
+                        abspos=a["abspos"], n_skipped=a["n_skipped"], multihead=a.get("multihead_rnn", False),
+                        signal_quality=fx.get("signal_quality"), growth_rate=a.get("growth_rate"),
+                        inflection_point_x=a.get("inflection_point_x"))
     torch.testing.assert_close(out["z"], fx["z"], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(out["c"], fx["c"], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=1e-6)

@@ -39,7 +39,7 @@ def cosine(a, b):
     return F.cosine_similarity(a.double().flatten(), b.double().flatten(), dim=0).item()
 
 
-def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321):
+def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_quality=None):
     """cpc/train.py:95-109.  If ext is given the sampler is bypassed so both sides use identical indices."""
     model.train(train_mode)
     crit.train(train_mode)
@@ -60,7 +60,7 @@ def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321):
         label = torch.zeros(2 * B, dtype=torch.long, device=seq.device)
         c, z, label = model(combined, label)
         torch.manual_seed(seed)
-        losses, acc = crit(c[:B], z[B:], label[:B], None)
+        losses, acc = crit(c[:B], z[B:], label[:B], signal_quality)
         losses.sum().backward()
     finally:
         crit.sampleIndices = orig
@@ -90,7 +90,7 @@ def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, min_cos=0.99)
 
 
 GOLDEN_CASES = ["tiny_lstm_linear", "tiny_lstm_reverse_linear", "tiny_transformer_ar_linear", "tiny_gru2_transformer",
-                "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN"]
+                "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN", "tiny_lstm_quality_skip1"]
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -105,7 +105,8 @@ def test_against_reference_golden(name):
     model.load_state_dict(ms, strict=False)
     missing = crit.load_state_dict(cs, strict=False)
     assert not missing.unexpected_keys
-    out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long())
+    quality = fx["signal_quality"].cuda() if "signal_quality" in fx else None
+    out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long(), signal_quality=quality)
     # tiny models (C = 32): gradients of 32-wide layers carry more bf16 noise -> cosine 0.98; the two-layer GRU +
     # transformer-head case (B = 2, 16 frames) measured 0.9755 on one ChannelNorm gain (a 32-term cancelling sum)
     # tiny_lstm_headsLSTM: zero-state LSTM heads at C = 32 emit |pred| ~ 0.05, the logits are ~1e-3 and the encoder's
