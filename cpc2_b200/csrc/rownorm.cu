@@ -13,9 +13,12 @@ struct RowMap {
   long long seq_len;     // rows per sequence
   long long seq_stride;  // rows between consecutive sequences in the buffer
   long long row_off;     // first valid row inside a sequence (halo)
+  // Row counts are below 2^31 (checked by the launchers): 32-bit division.  The 64-bit one is a ~100-instruction
+  // routine, and a backward thread evaluates a dozen maps before it can issue its first load.
   __device__ __forceinline__ long long operator()(long long r) const {
-    const long long n = r / seq_len;
-    return n * seq_stride + row_off + (r - n * seq_len);
+    if (seq_stride == seq_len && row_off == 0) return r;  // dense buffer
+    const unsigned n = (unsigned)r / (unsigned)seq_len;
+    return (long long)n * seq_stride + row_off + ((unsigned)r - n * (unsigned)seq_len);
   }
 };
 
@@ -96,7 +99,8 @@ __device__ __forceinline__ void store_f32(float* p, const float (&x)[V]) {
 template <int V, typename T>
 __device__ __forceinline__ void zero_halo(T* base, const RowMap& m, long long r, int lane) {
   constexpr int C = 32 * V;
-  const long long n = r / m.seq_len, t = r - n * m.seq_len;
+  if (m.seq_stride == m.seq_len) return;  // no halo rows
+  const long long n = (unsigned)r / (unsigned)m.seq_len, t = r - n * m.seq_len;
   if (t != 0 && t != m.seq_len - 1) return;
   float z[V];
 #pragma unroll
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(256) rownorm_fwd_kernel(const RowNormFwdArgs a
       a.rstd[r] = rstd;
     }
     if (a.gamma != nullptr) {
-      const long long g = r / a.rows_per_group;
+      const long long g = (unsigned)r / (unsigned)a.rows_per_group;
       float ga[V], be[V];
       load_f32<V>(a.gamma + g * C + lane * V, ga);
       load_f32<V>(a.beta + g * C + lane * V, be);
@@ -201,8 +205,10 @@ struct RowNormBwdArgs {
   int unbiased, relu, dout_f32, dx_accumulate;
 };
 
+// Two CTAs per SM for C <= 256 (128 registers): at 161 registers one CTA per SM was resident and a 256- or 348-CTA
+// launch ran as two or three full latency chains (load -> reduce -> store -> block reduction -> atomics) back to back.
 template <int V>
-__global__ void __launch_bounds__(256) rownorm_bwd_kernel(const RowNormBwdArgs a) {
+__global__ void __launch_bounds__(256, (V <= 8 ? 2 : 1)) rownorm_bwd_kernel(const RowNormBwdArgs a) {
   constexpr int C = 32 * V;
   __shared__ float red[3][8][C > 512 ? 1 : C];
   const int lane = threadIdx.x & 31;
@@ -341,7 +347,7 @@ static RowMap to_map(const CpcRowMap& m, long long rows) { return make_map(m.seq
 
 extern "C" int cpc_rownorm_fwd(const CpcRowNormFwd* d, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (d == nullptr || d->rows <= 0 || d->C % 32 != 0 || d->in == nullptr) return CPC_ERR_ARG;
+  if (d == nullptr || d->rows <= 0 || d->rows > 0x7fffffffLL || d->C % 32 != 0 || d->in == nullptr) return CPC_ERR_ARG;
   RowNormFwdArgs a;
   a.in = static_cast<const __nv_bfloat16*>(d->in);
   a.in_map = to_map(d->in_map, d->rows);
@@ -371,7 +377,8 @@ extern "C" int cpc_rownorm_fwd(const CpcRowNormFwd* d, void* stream_) {
 
 extern "C" int cpc_rownorm_bwd(const CpcRowNormBwd* d, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (d == nullptr || d->rows <= 0 || d->C % 32 != 0 || d->in == nullptr || d->dout == nullptr) return CPC_ERR_ARG;
+  if (d == nullptr || d->rows <= 0 || d->rows > 0x7fffffffLL || d->C % 32 != 0 || d->in == nullptr || d->dout == nullptr)
+    return CPC_ERR_ARG;
   const long long rpg = d->rows_per_group > 0 ? d->rows_per_group : d->rows;
   if (d->rows % rpg != 0) return CPC_ERR_ARG;
   RowNormBwdArgs a;
@@ -388,7 +395,10 @@ extern "C" int cpc_rownorm_bwd(const CpcRowNormBwd* d, void* stream_) {
   const int groups = (int)(d->rows / rpg);
   const int wpb = 8;
   long long bx = (rpg + wpb * 4 - 1) / (wpb * 4);  // one 4-row batch per warp where the row count allows
-  const long long cap = (148 * 8 + groups - 1) / groups;
+  // at most one resident wave (2 CTAs per SM, 1 at C = 512): further rows are further loop iterations of the same
+  // CTAs, which cost a load -> store chain, not another block reduction and launch ramp
+  long long cap = (148 * (d->C <= 256 ? 2 : 1)) / groups;
+  if (cap < 1) cap = 1;
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   dim3 grid((unsigned)bx, groups);
