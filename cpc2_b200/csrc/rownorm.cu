@@ -46,6 +46,31 @@ __device__ __forceinline__ void load_bf16(const __nv_bfloat16* p, float (&x)[V])
     x[0] = __bfloat162float(p[0]);
   }
 }
+// Raw 32-bit words of a row chunk: lets a kernel issue every load of several rows before the first conversion
+// (load + convert in one helper made each row's loads wait for the previous row's data).
+template <int W>
+__device__ __forceinline__ void load_words(const void* p, uint32_t (&w)[W]) {
+  if constexpr (W >= 4) {
+#pragma unroll
+    for (int i = 0; i < W; i += 4) {
+      const uint4 u = *reinterpret_cast<const uint4*>(static_cast<const uint32_t*>(p) + i);
+      w[i] = u.x; w[i + 1] = u.y; w[i + 2] = u.z; w[i + 3] = u.w;
+    }
+  } else if constexpr (W == 2) {
+    const uint2 u = *static_cast<const uint2*>(p);
+    w[0] = u.x; w[1] = u.y;
+  } else {
+    w[0] = *static_cast<const uint32_t*>(p);
+  }
+}
+template <int V>
+__device__ __forceinline__ void bf16_words_to_f32(const uint32_t (&w)[V / 2], float (&x)[V]) {
+#pragma unroll
+  for (int j = 0; j < V / 2; ++j) {
+    x[2 * j] = __uint_as_float(w[j] << 16);
+    x[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+  }
+}
 template <int V>
 __device__ __forceinline__ void store_bf16(__nv_bfloat16* p, const float (&x)[V]) {
   if constexpr (V >= 8) {
@@ -234,15 +259,56 @@ __global__ void __launch_bounds__(256, (V <= 8 ? 2 : 1)) rownorm_bwd_kernel(cons
   for (long long rr0 = ((long long)blockIdx.x * wpb + wib) * R; rr0 < a.rows_per_group; rr0 += (long long)gridDim.x * wpb * R) {
     float x[R][V], d[R][V], mean[R], rstd[R];
     bool ok[R];
+    long long rq[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       ok[q] = rr0 + q < a.rows_per_group;
-      const long long r = r0 + rr0 + (ok[q] ? q : 0);
-      load_bf16<V>(a.in + a.in_map(r) * C + lane * V, x[q]);
-      if (a.dout_f32) load_f32<V>(static_cast<const float*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
-      else load_bf16<V>(static_cast<const __nv_bfloat16*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
-      mean[q] = a.mean[r];
-      rstd[q] = a.rstd[r];
+      rq[q] = r0 + rr0 + (ok[q] ? q : 0);
+    }
+    if constexpr (V >= 2) {
+      // phase 1: every load of the R rows in flight (raw words), phase 2: conversions
+      uint32_t xw[R][V / 2];
+#pragma unroll
+      for (int q = 0; q < R; ++q) load_words<V / 2>(a.in + a.in_map(rq[q]) * C + lane * V, xw[q]);
+      if (a.dout_f32) {
+        uint32_t dw[R][V];
+#pragma unroll
+        for (int q = 0; q < R; ++q)
+          load_words<V>(static_cast<const float*>(a.dout) + a.dout_map(rq[q]) * C + lane * V, dw[q]);
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+          mean[q] = a.mean[rq[q]];
+          rstd[q] = a.rstd[rq[q]];
+        }
+#pragma unroll
+        for (int q = 0; q < R; ++q)
+#pragma unroll
+          for (int i = 0; i < V; ++i) d[q][i] = __uint_as_float(dw[q][i]);
+      } else {
+        uint32_t dw[R][V / 2];
+#pragma unroll
+        for (int q = 0; q < R; ++q)
+          load_words<V / 2>(static_cast<const __nv_bfloat16*>(a.dout) + a.dout_map(rq[q]) * C + lane * V, dw[q]);
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+          mean[q] = a.mean[rq[q]];
+          rstd[q] = a.rstd[rq[q]];
+        }
+#pragma unroll
+        for (int q = 0; q < R; ++q) bf16_words_to_f32<V>(dw[q], d[q]);
+      }
+#pragma unroll
+      for (int q = 0; q < R; ++q) bf16_words_to_f32<V>(xw[q], x[q]);
+    } else {
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const long long r = rq[q];
+        load_bf16<V>(a.in + a.in_map(r) * C + lane * V, x[q]);
+        if (a.dout_f32) load_f32<V>(static_cast<const float*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
+        else load_bf16<V>(static_cast<const __nv_bfloat16*>(a.dout) + a.dout_map(r) * C + lane * V, d[q]);
+        mean[q] = a.mean[r];
+        rstd[q] = a.rstd[r];
+      }
     }
     if (a.dout2 != nullptr) {
 #pragma unroll
