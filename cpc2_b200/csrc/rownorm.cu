@@ -166,6 +166,12 @@ __global__ void __launch_bounds__(256) rownorm_fwd_kernel(const RowNormFwdArgs a
   for (long long r = warp; r < a.rows; r += nwarps) {
     float x[V];
     load_bf16<V>(a.in + a.in_map(r) * C + lane * V, x);
+    float ga[V], be[V];  // requested with the row, not behind the mean / rstd stores below
+    if (a.gamma != nullptr) {
+      const long long g = (unsigned)r / (unsigned)a.rows_per_group;
+      load_f32<V>(a.gamma + g * C + lane * V, ga);
+      load_f32<V>(a.beta + g * C + lane * V, be);
+    }
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < V; ++i) s += x[i];
@@ -183,10 +189,6 @@ __global__ void __launch_bounds__(256) rownorm_fwd_kernel(const RowNormFwdArgs a
       a.rstd[r] = rstd;
     }
     if (a.gamma != nullptr) {
-      const long long g = (unsigned)r / (unsigned)a.rows_per_group;
-      float ga[V], be[V];
-      load_f32<V>(a.gamma + g * C + lane * V, ga);
-      load_f32<V>(a.beta + g * C + lane * V, be);
 #pragma unroll
       for (int i = 0; i < V; ++i) x[i] = x[i] * rstd * ga[i] + be[i];
     } else {
