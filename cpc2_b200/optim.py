@@ -89,8 +89,9 @@ class FusedAdam(torch.optim.Optimizer):
     # ------------------------------------------------------------------------------------------ staged stepping
     def attach(self, dp=None):
         """Step each gradient bucket as soon as its module announces it (ops.grad_ready: criterion heads first,
-        90 % of the parameters), on a side stream -- after the bucket's all-reduce when `dp` (BucketedAllReduce) is
-        given -- so the update overlaps the rest of the backward.  step() then only joins and handles leftovers."""
+        90 % of the parameters), on a side stream -- behind the event that marks the bucket's all-reduce done when
+        `dp` (BucketedAllReduce) is given -- so the update overlaps the rest of the backward and the next bucket's
+        all-reduce.  step() then only joins and handles leftovers."""
         if len(self.param_groups) != 1:
             raise NotImplementedError("FusedAdam.attach: staged stepping supports a single parameter group")
         self._dp = dp
@@ -115,13 +116,16 @@ class FusedAdam(torch.optim.Optimizer):
         if not torch.cuda.is_current_stream_capturing():
             self.sync_hyper()
         dp = self._dp
+        after = None
         if dp is not None and dp.world > 1 and dp.on_gpu:
-            dp.stream.wait_stream(torch.cuda.current_stream())
-            dp._pending = True
-            ctx = torch.cuda.stream(dp.stream)  # behind this bucket's all-reduce
-        else:
-            ctx = ops.side(9)
-        with ctx:
+            # dp's hook ran first: this bucket's all-reduce is the last thing queued on dp.stream.  The update waits
+            # for exactly that, on its OWN stream -- on dp.stream the next bucket's all-reduce would queue behind the
+            # 16.6 M-parameter update of the heads and the last (encoder) reduction would trail the backward
+            after = torch.cuda.Event()
+            after.record(dp.stream)
+        with ops.side(9, after=after):
+            if after is not None:
+                torch.cuda.current_stream().wait_event(after)  # (also when side streams are disabled)
             t = self._table(g, stage, pairs)
             K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
         self._advanced = True
