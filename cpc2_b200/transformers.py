@@ -269,7 +269,11 @@ class TransformerStack:
         G, d, do, dff, S = self.G, self.d, self.dout, self.dff, self.S
         T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
         dev = dout.device
-        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
+        gflat = sv.pop("gflat", None)  # cleared ahead of time by the caller (criterion forward), or now
+        if gflat is None:
+            gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
+        else:
+            ops.join(10)
         Gd = self.spans(gflat)
         x, shared = sv["x"], sv["shared"]
         # Buffers first (main stream), then the chain of input gradients on the main stream while the weight
@@ -427,7 +431,11 @@ class MultiHeadStack(TransformerStack):
         d, do, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
         T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
         dev = dout.device
-        gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
+        gflat = sv.pop("gflat", None)  # cleared ahead of time by the caller (criterion forward), or now
+        if gflat is None:
+            gflat = ops.grad_arena(self.arena, self.arena.numel, dev)
+        else:
+            ops.join(10)
         Gd = self.spans(gflat)
         x = sv["x"]
         dpre2 = torch.empty(Kc * T, do, device=dev, dtype=BF16)
