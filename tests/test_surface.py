@@ -71,3 +71,27 @@ def test_fused_adam_has_no_cpu_path():
         FusedAdam([p]).step()
     with pytest.raises(NotImplementedError):
         FusedAdam([p], weight_decay=0.1)
+
+
+def test_checkpoint_layout_round_trip(tmp_path):
+    """Checkpoints in the reference's layout (feature_loader.save_checkpoint, feature_loader.py:296-304:
+    {"gEncoder": model_state, "cpcCriterion": criterion_state, "optimizer": ..., "best": ...}) written from these
+    modules load back into fresh ones, and the model half is what loadModel (feature_loader.py:238-283) reads."""
+    args = T.defaultArgs(hiddenEncoder=32, hiddenGar=32, nPredicts=4, negativeSamplingExt=8, sizeWindow=2560)
+    torch.manual_seed(1)
+    model, crit = T.buildModelAndCriterion(args)
+    path = os.path.join(tmp_path, "checkpoint_0.pt")
+    torch.save({"gEncoder": model.state_dict(), "cpcCriterion": crit.state_dict(), "optimizer": None, "best": None},
+               path)
+    torch.manual_seed(2)  # different initial weights
+    model2, crit2 = T.buildModelAndCriterion(args)
+    assert not torch.equal(model2.gEncoder.conv1.weight, model.gEncoder.conv1.weight)
+    state = torch.load(path, map_location="cpu", weights_only=False)
+    assert set(state) == {"gEncoder", "cpcCriterion", "optimizer", "best"}
+    model2.load_state_dict(state["gEncoder"], strict=False)      # loadModel: strict=False
+    crit2.load_state_dict(state["cpcCriterion"])                 # loadCriterion (train.py:62-69): strict
+    for (k, a), (_, b) in zip(model.state_dict().items(), model2.state_dict().items()):
+        assert torch.equal(a, b), k
+    for (k, a), (_, b) in zip(crit.state_dict().items(), crit2.state_dict().items()):
+        assert torch.equal(a, b), k
+    assert all(k.startswith(("gEncoder.", "gAR.")) for k in state["gEncoder"])
