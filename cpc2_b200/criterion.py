@@ -518,7 +518,8 @@ class CPCUnsupersivedCriterion(BaseCriterion):
         # --dropout: nn.Dropout(0.5) on every prediction in train mode (criterion.py:168-169)
         drop_pred = self.wPrediction.dropout.p if (self.wPrediction.dropout is not None and self.training) else 0.0
         losses, acc = _CriterionFn.apply(cFeature, encodedData, extIdx, weights, eng, self.nPredicts,
-                                         self.negativeSamplingExt, (self.training, drop_pred), *eng.arena.params)
+                                         self.negativeSamplingExt, (self.training, drop_pred, torch.is_grad_enabled()),
+                                         *eng.arena.params)
         return losses[:, self.nSkipped:], acc[:, self.nSkipped:]
 
 
@@ -527,7 +528,7 @@ class _CriterionFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, c, z, ext, weights, eng, Kp, NEG, mode, *params):
-        training, drop_pred = mode
+        training, drop_pred, will_backward = mode
         B, S, H = c.shape
         D = z.shape[2]
         W = S - Kp
@@ -538,7 +539,7 @@ class _CriterionFn(torch.autograd.Function):
         cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
         zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
         preds, _, saved = eng.forward(cw, T, True, training)
-        if isinstance(eng, TransformerStack) and any(ctx.needs_input_grad):
+        if isinstance(eng, TransformerStack) and will_backward and any(ctx.needs_input_grad):
             # the heads' gradient arena (66 MB at the default config) is cleared NOW on an idle side stream: the same
             # memset at the top of the backward sat on the critical path for ~13 us
             with ops.side(10):
