@@ -540,8 +540,11 @@ def test_reference_wrappers_dataparallel_and_ddp():
     assert torch.allclose(base_l, dp_l, atol=1e-5)
     for k, v in base_g.items():
         assert cosine(v, dp_g[k]) > 0.9999, k
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29671")
+    import socket
+    with socket.socket() as sock:  # a free rendezvous port for the single-rank group
+        sock.bind(("127.0.0.1", 0))
+        port = sock.getsockname()[1]
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     created = not dist.is_initialized()
     if created:
         dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
