@@ -187,7 +187,7 @@ class LinearHeads:
             raise NotImplementedError("LinearHeads: dimensions must be multiples of 8")
         self.arena = ops.Arena([l.weight for l in linears])
 
-    def forward(self, x, T, shared, training, want_f32=False):
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
         G, d, do = self.G, self.d, self.dout
         w16 = self.arena.span(self.arena.bf16(), 0, G, (G, do, d))
         out = torch.empty(G, T, do, device=x.device, dtype=BF16)
@@ -234,7 +234,7 @@ class FfdHeads:
         sh = dict(W1=(G, dff, d), b1=(G, dff), W2=(G, do, dff), b2=(G, do))
         return {k: self.arena.span(flat, self.first[k], G, v) for k, v in sh.items()}
 
-    def forward(self, x, T, shared, training, want_f32=False):
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
         G, d, dff, do = self.G, self.d, self.dff, self.dout
         P32 = self.spans(self.arena.ensure())
         P16 = self.spans(self.arena.bf16())
@@ -300,10 +300,10 @@ class ConvHeads:
         return dict(W=self.arena.span(flat, 0, G, (G, self.dout, self.d, self.ks)),
                     b=self.arena.span(flat, G, G, (G, self.dout)))
 
-    def forward(self, x, T, shared, training, want_f32=False):
-        G, d, do, ks, S = self.G, self.d, self.dout, self.ks, self.S
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
+        G, d, do, ks, S = self.G, self.d, self.dout, self.ks, int(seq_len or self.S)
         if T % S != 0:
-            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+            raise ValueError(f"token count {T} is not a multiple of the sequence length {S}")
         P32 = self.spans(self.arena.ensure())
         P16 = self.spans(self.arena.bf16())
         # X[b, t, j, :] = c[b, t - (ks - 1) + j, :]
@@ -314,10 +314,10 @@ class ConvHeads:
         out32 = torch.empty(G, T, do, device=x.device) if want_f32 else None
         ops.linear_fwd(xu, w2, T, do, ks * d, groups=G, x_shared=True, out_bf16=out, out_f32=out32,
                        bias=P32["b"] * self.c, bias_gs=do, alpha=self.c)
-        return out, out32, dict(xu=xu, w2=w2, T=T)
+        return out, out32, dict(xu=xu, w2=w2, T=T, S=S)
 
     def backward(self, sv, dout):
-        G, d, do, ks, S, T = self.G, self.d, self.dout, self.ks, self.S, sv["T"]
+        G, d, do, ks, S, T = self.G, self.d, self.dout, self.ks, sv["S"], sv["T"]
         dev = dout.device
         if dout.dtype != BF16:
             dout = K.cast_bf16(dout.contiguous().float())
@@ -362,11 +362,11 @@ class RecurrentHeads:
         self.per = [[r.weight_ih_l0, r.weight_hh_l0, r.bias_ih_l0, r.bias_hh_l0] for r in rnns]
         self.arena = ops.Arena([p for ps in self.per for p in ps])
 
-    def forward(self, x, T, shared, training, want_f32=False):
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
         from .model import _RecurrentFn
-        G, d, do, S = self.G, self.d, self.dout, self.S
+        G, d, do, S = self.G, self.d, self.dout, int(seq_len or self.S)
         if T % S != 0:
-            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
+            raise ValueError(f"token count {T} is not a multiple of the sequence length {S}")
         self.arena.ensure()
         xin = x.float().view(T // S, S, d)
         if self.cell == "RNN":
@@ -405,7 +405,7 @@ class _HeadsFn(torch.autograd.Function):
     def forward(ctx, c, eng, training, *params):
         B, W, H = c.shape
         xb = K.cast_bf16(c.detach().contiguous().float()).view(B * W, H)
-        out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True)
+        out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True, seq_len=W)
         ctx.eng, ctx.saved, ctx.shape = eng, saved, (B, W, H)
         return out32.view(eng.n_out, B, W, eng.dout)
 
@@ -504,11 +504,16 @@ class CPCUnsupersivedCriterion(BaseCriterion):
     def forward(self, cFeature, encodedData, label, signal_quality=None):
         """criterion.py:329-363 -> (losses [1, K - n_skipped], acc [1, K - n_skipped])."""
         ops.require_cuda(cFeature, encodedData)
+        ops.reject_replica(self)
         if self.mode == "reverse":
             encodedData = torch.flip(encodedData, [1])
             cFeature = torch.flip(cFeature, [1])
         batchSize, seqSize, _ = cFeature.size()
         windowSize = seqSize - self.nPredicts
+        if batchSize * encodedData.size(1) > ops.NCE_BWD_MAX_BS and torch.is_grad_enabled():
+            raise ValueError(f"cpc2_b200: batch x frames = {batchSize * encodedData.size(1)} exceeds {ops.NCE_BWD_MAX_BS} "
+                             "(cpc_nce_bwd keeps one row of d(logits) per warp in shared memory; e.g. batchSizeGPU <= 50 at "
+                             "sizeWindow 20480): lower batchSizeGPU, the all-pairs logits also grow as (batch x frames)^2")
         extIdx = self.sampleIndices(batchSize, encodedData.size(1), windowSize, encodedData.device)
         weights = None
         if signal_quality is not None:
@@ -538,12 +543,12 @@ class _CriterionFn(torch.autograd.Function):
             raise ValueError("B*S must be a multiple of 8")
         cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
         zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
-        preds, _, saved = eng.forward(cw, T, True, training)
+        preds, _, saved = eng.forward(cw, T, True, training, seq_len=W)
         if isinstance(eng, TransformerStack) and will_backward and any(ctx.needs_input_grad):
             # the heads' gradient arena (66 MB at the default config) is cleared NOW on an idle side stream: the same
             # memset at the top of the backward sat on the critical path for ~13 us
-            with ops.side(10):
-                saved["gflat"] = ops.grad_arena(eng.arena, eng.arena.numel, dev)
+            # (allocated on THIS stream, cleared on side stream 10; the backward joins 10 before the first write)
+            saved["gflat"] = ops.grad_arena(eng.arena, eng.arena.numel, dev, zero_on=10)
         ctx.pred_drop = None
         if drop_pred > 0:
             ctx.pred_drop = (ops.DropoutState.next(dev), drop_pred)

@@ -74,7 +74,7 @@ class BucketedAllReduce:
                               rank=int(hdl.rank), used=0, slots={})
         ops.GRAD_ARENA = self._arena
 
-    def _arena(self, owner, numel, device):
+    def _arena(self, owner, numel, device, zero_on=None):
         sy = self.symmetric
         slot = sy["slots"].get(owner)
         if slot is None:  # first backward: carve (same order on every rank, so the offsets are symmetric)
@@ -85,7 +85,12 @@ class BucketedAllReduce:
             sy["used"] += n
         if slot[1] != numel:
             return None
-        return sy["buf"][slot[0]:slot[0] + numel].zero_()
+        t = sy["buf"][slot[0]:slot[0] + numel]
+        if zero_on is None:
+            return t.zero_()
+        with ops.side(zero_on):
+            t.zero_()
+        return t
 
     def broadcast_parameters(self, src=0):
         """DDP's initial parameter broadcast (train.py:524-527 wraps after construction)."""

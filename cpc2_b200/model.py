@@ -122,6 +122,7 @@ class CPCEncoder(nn.Module):
         """x [N, 1, W] fp32 -> [N, C, S] fp32 (a view of channels-last memory), S = W / 160 for the training windows;
         other lengths (the last chunk of a file at inference) run forward-only."""
         ops.require_cuda(x)
+        ops.reject_replica(self)
         if x.shape[-1] % 160 != 0 and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
             raise NotImplementedError("cpc2_b200: training windows must be a multiple of 160 samples (the reference's "
                                       "sizeWindow, default 20480); any length runs forward-only under torch.no_grad()")
@@ -387,9 +388,13 @@ class CPCAR(nn.Module):
 
     def forward(self, x):
         ops.require_cuda(x)
+        ops.reject_replica(self)
         cell = self._cell()
         if cell == "RNN" and self.baseNet.nonlinearity != "tanh":
             raise NotImplementedError("cpc2_b200: nn.RNN with relu nonlinearity is never built by the reference")
+        if self.baseNet.hidden_size not in ops.RECURRENT_H:
+            raise NotImplementedError(f"cpc2_b200: the recurrence kernels are built for hidden sizes {ops.RECURRENT_H} "
+                                      f"(csrc/lstm.cu), got {self.baseNet.hidden_size}")
         if self.reverse:
             x = torch.flip(x, [1])
         nl = self.baseNet.num_layers

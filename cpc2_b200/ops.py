@@ -37,12 +37,20 @@ def grad_ready(stage, gflat, params=None, grads=None):
 GRAD_ARENA = None
 
 
-def grad_arena(owner, numel, device):
+def grad_arena(owner, numel, device, zero_on=None):
+    """Zeroed fp32 [numel] gradient arena.  `zero_on`: side-stream index on which the clearing memset is issued
+    (the ALLOCATION always happens on the current stream, so the block belongs to the pool of the stream whose
+    kernels write it -- the rule above -- and only the memset overlaps other work; the caller joins that stream)."""
     if GRAD_ARENA is not None:
-        t = GRAD_ARENA(owner, numel, device)
+        t = GRAD_ARENA(owner, numel, device, zero_on) if zero_on is not None else GRAD_ARENA(owner, numel, device)
         if t is not None:
             return t
-    return torch.zeros(numel, dtype=torch.float32, device=device)
+    if zero_on is None:
+        return torch.zeros(numel, dtype=torch.float32, device=device)
+    t = torch.empty(numel, dtype=torch.float32, device=device)
+    with side(zero_on):
+        t.zero_()
+    return t
 
 
 # ---- independent kernels on forked streams -----------------------------------------------------------
@@ -181,6 +189,22 @@ def require_cuda(*tensors):
             raise RuntimeError("cpc2_b200 runs on CUDA tensors only (sm_100a kernels, no CPU fallback)")
 
 
+def reject_replica(module):
+    """nn.DataParallel over SEVERAL devices (cpc/train.py:529-532 with nGPU > 1) replicates the module per device and
+    calls the replicas from one thread each; the engines / arenas / side-stream state of this package are per process
+    (one process per GPU).  device_ids of length 1 never replicates and works.  Fail loudly instead of launching on
+    another device's pointers."""
+    if getattr(module, "_is_replica", False):
+        raise RuntimeError("cpc2_b200: nn.DataParallel across several devices is not supported -- run one process per "
+                           "GPU (--distributed / DistributedDataParallel, or cpc2_b200.dp.BucketedAllReduce)")
+
+
+# shapes the recurrence kernels are instantiated for (csrc/lstm.cu dispatch_h)
+RECURRENT_H = (32, 64, 128, 256, 512)
+# cpc_nce_bwd stages one row of d(logits) per warp in shared memory: 8 warps x B*S floats <= 200 KB (csrc/nce.cu)
+NCE_BWD_MAX_BS = 6400
+
+
 def auto_splits(M, N, K_total, groups=1, k_per_slab=0):
     """Split-K factor for skinny weight-gradient GEMMs so that ~2 CTAs per SM are in flight."""
     kps = k_per_slab or K_total
@@ -212,9 +236,9 @@ class Arena:
         if self.flat is None or not self.params:
             return False
         base = self.flat.data_ptr()
-        for i in (0, len(self.params) - 1):
-            p = self.params[i]
-            if p.device != self.flat.device or p.data_ptr() != base + 4 * self.offsets[i]:
+        dev = self.flat.device
+        for p, off in zip(self.params, self.offsets):  # every pointer (~110): a re-pointed .data anywhere rebuilds
+            if p.device != dev or p.data_ptr() != base + 4 * off:
                 return False
         return True
 

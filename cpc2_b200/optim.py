@@ -74,15 +74,28 @@ class FusedAdam(torch.optim.Optimizer):
             spans[i].p16 = None
             spans[i].n, spans[i].first_block = p.numel(), blocks
             blocks += (p.numel() + chunk - 1) // chunk
-        # pinned staging buffer + async copy: capturable (a captured step() replays the copy, so every staging
-        # buffer stays alive and untouched for the lifetime of the optimizer)
+        # pinned staging buffer + async copy.  While a CUDA graph is being captured the copy becomes a graph node that
+        # is replayed, so that buffer (and the device table it fills) must stay alive and untouched for the lifetime
+        # of the optimizer: one per captured table, kept in g["staging"].  Eager rebuilds (gradient pointers that move
+        # from step to step) reuse ONE pinned buffer per table, guarded by the event of its previous copy -- the list
+        # no longer grows with the number of steps.
         raw = torch.frombuffer(bytearray(bytes(spans)), dtype=torch.uint8)
-        host = torch.empty(raw.numel(), dtype=torch.uint8).pin_memory()
+        capturing = torch.cuda.is_current_stream_capturing()
+        host = None if capturing else t.get("host")
+        if host is None or host.numel() != raw.numel():
+            host = torch.empty(raw.numel(), dtype=torch.uint8).pin_memory()
+            if capturing:
+                g["staging"].append(host)
+            else:
+                t["host"], t["host_ev"] = host, torch.cuda.Event()
+        elif t.get("host_ev") is not None:
+            t["host_ev"].synchronize()  # the previous async copy out of this buffer has completed
         host.copy_(raw)
-        g["staging"].append(host)
-        if t["table"] is None or t["table"].numel() != host.numel() or torch.cuda.is_current_stream_capturing():
+        if t["table"] is None or t["table"].numel() != host.numel() or capturing:
             t["table"] = torch.empty(host.numel(), dtype=torch.uint8, device=g["state"].device)
         t["table"].copy_(host, non_blocking=True)
+        if not capturing:
+            t["host_ev"].record()
         t["keys"], t["n_spans"], t["blocks"] = keys, len(pairs), blocks
         return t
 
@@ -130,6 +143,26 @@ class FusedAdam(torch.optim.Optimizer):
             K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
         self._advanced = True
         self._done.update(id(p) for p, _ in pairs)
+
+    # ------------------------------------------------------------------------------------------ snapshot / restore
+    def snapshot(self):
+        """Copies of everything step() mutates besides the parameters (moments, device step counter), so that a
+        caller can run throw-away steps (GraphedTrainStep's warm-up before capture) and put the optimizer back.
+        Buffers keep their addresses: tables captured in a CUDA graph stay valid after restore()."""
+        out = []
+        for gi in range(len(self.param_groups)):
+            if self._groups[gi] is None:
+                self._init_group(gi)
+            g = self._groups[gi]
+            out.append(None if g is None else (g["m"].clone(), g["v"].clone(), g["state"].clone()))
+        return out
+
+    def restore(self, snap):
+        for g, sn in zip(self._groups, snap):
+            if g is not None and sn is not None:
+                g["m"].copy_(sn[0])
+                g["v"].copy_(sn[1])
+                g["state"].copy_(sn[2])
 
     def sync_hyper(self):
         """Pushes lr / betas / eps of param_groups to the device if a scheduler changed them (call before replaying

@@ -8,6 +8,7 @@ which removes the per-launch host overhead that otherwise dominates a ~1 ms step
 """
 import argparse
 import time
+import weakref
 
 import numpy as np
 import torch
@@ -116,31 +117,76 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
     return allLosses, allAcc
 
 
+# trainStep replays the whole step (forward + backward + FusedAdam update) as one CUDA graph when it can: an unwrapped
+# cpc2_b200 CPCModel without keepHidden state, a cpc2_b200.optim.FusedAdam optimizer, no signal-quality weights, a
+# batch shape seen before.  Anything else -- DataParallel / DDP wrappers, torch.optim.Adam, the ragged last batch of
+# an epoch -- takes the eager body below (still the two-halves forward and the fused kernels).  False: always eager.
+GRAPH_TRAIN_STEP = True
+_MAX_GRAPHS = 2
+_GRAPHED = weakref.WeakKeyDictionary()
+
+
+def _graph_runner(cpcModel, cpcCriterion, optimizer, sequence, signal_quality):
+    from . import ops
+    from .optim import FusedAdam
+    if not (GRAPH_TRAIN_STEP and signal_quality is None and isinstance(optimizer, FusedAdam)
+            and isinstance(cpcModel, model_.CPCModel) and isinstance(cpcCriterion, cr.CPCUnsupersivedCriterion)
+            and cpcModel.splittable() and sequence.is_cuda and sequence.dim() == 4 and torch.is_grad_enabled()):
+        return None
+    if any(h for h in ops.GRAD_READY if getattr(h, "__self__", None) is not optimizer):
+        return None  # somebody else (a data-parallel wrapper) hooks the gradients: its owner drives the graph itself
+    cache = _GRAPHED.setdefault(cpcModel, {})  # (not an attribute: the module stays deep-copyable / picklable)
+    key = (tuple(sequence.shape), id(cpcCriterion), id(optimizer), cpcModel.training, cpcCriterion.training)
+    runner = cache.get(key)
+    if runner is None:
+        if len(cache) >= _MAX_GRAPHS:
+            return None
+        attached = optimizer._on_stage in ops.GRAD_READY
+        optimizer.attach()  # each module's parameters are stepped as soon as its gradients exist
+        try:
+            runner = GraphedTrainStep(cpcModel, cpcCriterion, sequence.shape[0], sequence.shape[-1],
+                                      device=sequence.device, warmup=3, train_mode=cpcModel.training, optimizer=optimizer)
+        finally:
+            if not attached:
+                optimizer.detach()
+        cache[key] = runner
+    return runner
+
+
 def trainStep(dataLoader, cpcModel, cpcCriterion, optimizer, scheduler, loggingStep):
-    """cpc/train.py:72-142."""
+    """cpc/train.py:72-142: same signature, same batch handling, same returned logs.  The per-step
+    `.cpu().numpy()` log reads of the reference (train.py:121-122, one host sync per step) become float64 sums kept
+    on the device and read once per call (and at every logging step, where the reference prints timings)."""
     cpcModel.train()
     cpcCriterion.train()
     start_time = time.perf_counter()
     n_examples = 0
     logs = {}
     it = 0
+    sums = None  # [2, K] float64 on the device: per-step losses / accuracies summed
     for step, full_data in enumerate(dataLoader):
         sequence, label, *signal_quality = full_data
         sequence = sequence.cuda(non_blocking=True)
         label = label.cuda(non_blocking=True)
         signal_quality = signal_quality[0].cuda(non_blocking=True) if len(signal_quality) else None
         n_examples += sequence.size(0)
-        allLosses, allAcc = forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality)
-        optimizer.step()
-        optimizer.zero_grad()
+        runner = _graph_runner(cpcModel, cpcCriterion, optimizer, sequence, signal_quality)
+        if runner is not None:
+            allLosses, allAcc = runner.step(sequence)  # forward + backward + optimizer.step() in one replay
+        else:
+            if cpcModel in _GRAPHED:
+                optimizer.zero_grad()  # .grad may still point at the static gradients of an earlier graph replay
+            allLosses, allAcc = forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality)
+            optimizer.step()
+            optimizer.zero_grad()
         if allLosses.nelement() > 0:
-            if "locLoss_train" not in logs:
-                logs["locLoss_train"] = np.zeros(allLosses.size(1))
-                logs["locAcc_train"] = np.zeros(allLosses.size(1))
+            if sums is None:
+                sums = torch.zeros(2, allLosses.size(1), dtype=torch.float64, device=allLosses.device)
             it += 1
-            logs["locLoss_train"] += (allLosses.mean(dim=0)).detach().cpu().numpy()
-            logs["locAcc_train"] += (allAcc.mean(dim=0)).cpu().numpy()
+            sums[0] += allLosses.detach().mean(dim=0)
+            sums[1] += allAcc.detach().mean(dim=0)
             if (step + 1) % loggingStep == 0:
+                torch.cuda.synchronize()
                 new_time = time.perf_counter()
                 elapsed = new_time - start_time
                 print(f"Update {step + 1}")
@@ -150,6 +196,9 @@ def trainStep(dataLoader, cpcModel, cpcCriterion, optimizer, scheduler, loggingS
                 start_time, n_examples = new_time, 0
     if scheduler is not None:
         scheduler.step()
+    if sums is not None:
+        host = sums.cpu().numpy()
+        logs["locLoss_train"], logs["locAcc_train"] = host[0], host[1]
     logs = {k: v / max(it, 1) for k, v in logs.items()}
     logs["iter"] = it
     return logs
@@ -190,7 +239,15 @@ class GraphedTrainStep:
     def __init__(self, cpcModel, cpcCriterion, batch, sizeWindow, device="cuda", warmup=3, train_mode=True,
                  after_backward=None, optimizer=None):
         """`optimizer` (cpc2_b200.optim.FusedAdam, or any capturable optimizer): its step() becomes part of the
-        graph, after `after_backward` (the data-parallel all-reduce) -- the whole of train.py:95-113 in one replay."""
+        graph, after `after_backward` (the data-parallel all-reduce) -- the whole of train.py:95-113 in one replay.
+
+        Construction has NO side effects on the training state: the `warmup` eager passes that precede the capture
+        (allocator warm-up, lazy kernel attributes, NCCL channel setup) run real optimizer steps on an all-zero batch,
+        so parameters, the optimizer's moments and step counter (FusedAdam.snapshot / restore), the dropout counter and
+        the CUDA RNG state are saved first and put back afterwards -- a freshly built or checkpoint-loaded model starts
+        its first replay from exactly its loaded state (an optimizer without snapshot()/restore() is warmed up with
+        its real step(): pass a FusedAdam, or accept `warmup` updates on silence)."""
+        from . import ops
         self.model, self.crit, self.optimizer = cpcModel, cpcCriterion, optimizer
         self._copy_stream, self._staged, self._staged_ready, self._picked = None, None, False, None
         self.static_seq = torch.zeros(batch, 2, 1, sizeWindow, device=device)
@@ -198,7 +255,16 @@ class GraphedTrainStep:
         self.params = [p for p in list(cpcModel.parameters()) + list(cpcCriterion.parameters()) if p.requires_grad]
         cpcModel.train(train_mode)
         cpcCriterion.train(train_mode)
-        side = torch.cuda.Stream()
+        dev = self.static_seq.device
+        torch.cuda.synchronize(dev)
+        # ---- snapshot of everything the warm-up passes mutate
+        keep = optimizer is not None and warmup > 0
+        snap_p = [p.detach().clone() for p in self.params] if keep else None
+        snap_o = optimizer.snapshot() if keep and hasattr(optimizer, "snapshot") else None
+        rng_state = torch.cuda.get_rng_state(dev)
+        drop_state = ops.DropoutState._states.get((dev.type, dev.index))
+        drop_snap = drop_state.clone() if drop_state is not None else None
+        side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(warmup):
@@ -208,8 +274,19 @@ class GraphedTrainStep:
                     after_backward()
                 if optimizer is not None:
                     optimizer.step()
+            if keep and snap_o is not None:
+                with torch.no_grad():
+                    for p, q in zip(self.params, snap_p):
+                        p.copy_(q)  # in place: addresses (and the arenas the parameters live in) are unchanged
+                    optimizer.restore(snap_o)
+            if drop_snap is not None:
+                drop_state.copy_(drop_snap)
+            elif (dev.type, dev.index) in ops.DropoutState._states:
+                ops.DropoutState._states[(dev.type, dev.index)][1:2].zero_()
         torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
+        torch.cuda.synchronize(dev)
+        torch.cuda.set_rng_state(rng_state, dev)
+        del snap_p, snap_o
         self.graph = torch.cuda.CUDAGraph()
         self._zero()
         with torch.cuda.graph(self.graph):
@@ -218,6 +295,17 @@ class GraphedTrainStep:
                 after_backward()
             if optimizer is not None:
                 optimizer.step()
+
+    def close(self):
+        """Drop the captured graph (and the static outputs that live in its memory pool).  A graph that holds captured
+        NCCL launches must be destroyed BEFORE the process group: ncclCommDestroy otherwise waits on it forever.
+        Call on every rank, then dist.destroy_process_group()."""
+        if self.graph is not None:
+            torch.cuda.synchronize(self.static_seq.device)
+            self.losses = self.acc = None
+            self._zero()
+            self.graph.reset()
+            self.graph = None
 
     def _zero(self):
         for p in self.params:
@@ -278,5 +366,7 @@ class GraphedTrainStep:
             self._staged_ready = False
         if self.optimizer is not None and hasattr(self.optimizer, "sync_hyper"):
             self.optimizer.sync_hyper()  # a scheduler may have changed lr since the last replay
+        if self.graph is None:
+            raise RuntimeError("GraphedTrainStep.step() after close()")
         self.graph.replay()
         return self.losses, self.acc

@@ -85,8 +85,9 @@ class TransformerLayer(nn.Module):
         self.stack().arena.prefetch(4)
 
     def forward(self, x):
-        """x [N, S, dmodel] fp32, S a multiple of sizeSeq -> [N, S, dout] fp32."""
+        """x [N, S, dmodel] fp32 -> [N, S, dout] fp32 (any S: block-local attention over zero-padded blocks of sizeSeq)."""
         ops.require_cuda(x)
+        ops.reject_replica(self)
         st = self.stack()
         return _TransformerFn.apply(x, st, self.training, *st.arena.params)
 
@@ -146,6 +147,7 @@ class MultiClassifierTransformerHead(nn.Module):
 
     def forward(self, x):
         ops.require_cuda(x)
+        ops.reject_replica(self)
         st = self.stack()
         N, S_in, _ = x.shape
         out = _MultiHeadFn.apply(x, st, self.training, *st.arena.params)  # [K, N*S, dout]
@@ -217,13 +219,57 @@ class TransformerStack:
             out[name] = self.arena.span(flat, self.first[name], count, shape)
         return out
 
+    # ------------------------------------------------------------------------------------------ attention
+    def _blocks(self, T, seq_len):
+        """(tokens per sequence L, sequences N, blocks per sequence nb).  cpc/transformers.py:38-50: a sequence longer
+        than sizeSeq is zero-padded to a multiple of it and folded into the batch as independent causal blocks."""
+        S = self.S
+        L = S if seq_len is None else int(seq_len)
+        if L <= 0 or T % L != 0:
+            raise ValueError(f"token count {T} is not a multiple of the sequence length {L}")
+        return L, T // L, (L + S - 1) // S
+
+    def _attn_fwd(self, qkv, krel, G, T, seq_len, rng, drop):
+        """qkv bf16 [G, T, 3d] -> att bf16 [G, T, d] + what the backward needs.  When the sequences are not a whole
+        number of blocks the padded copies (pure data movement: zero rows appended per sequence, transformers.py:41-48,
+        cropped again after the product, :69) are what the attention kernels see."""
+        S, d = self.S, self.d
+        dev = qkv.device
+        L, N, nb = self._blocks(T, seq_len)
+        Bt = N * nb
+        padded = nb * S != L
+        if padded:
+            qkv_k = torch.zeros(G, N, nb * S, 3 * d, device=dev, dtype=BF16)
+            qkv_k[:, :, :L].copy_(qkv.view(G, N, L, 3 * d))
+        else:
+            qkv_k = qkv
+        att_k = torch.empty(G, N * nb * S, d, device=dev, dtype=BF16)
+        probs = torch.empty(G, Bt, self.Hh, S, S, device=dev, dtype=BF16)
+        K.attn_fwd(qkv_k, krel, att_k, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        att = att_k.view(G, N, nb * S, d)[:, :, :L].reshape(G, T, d) if padded else att_k
+        return att, dict(qkv=qkv_k, att=att_k, probs=probs, Bt=Bt, geom=(L, N, nb, padded))
+
+    def _attn_bwd(self, sa, krel, dkrel, datt, G, T, rng, drop):
+        """datt bf16 [G, T, d] -> dqkv bf16 [G, T, 3d] (dKrelpos accumulated into `dkrel`)."""
+        S, d = self.S, self.d
+        dev = datt.device
+        L, N, nb, padded = sa["geom"]
+        if padded:
+            datt_k = torch.zeros(G, N, nb * S, d, device=dev, dtype=BF16)
+            datt_k[:, :, :L].copy_(datt.view(G, N, L, d))
+        else:
+            datt_k = datt
+        dqkv_k = torch.empty(G, N * nb * S, 3 * d, device=dev, dtype=BF16)
+        dscore = torch.empty_like(sa["probs"])
+        K.attn_bwd(sa["qkv"], krel, sa["att"], sa["probs"], datt_k, dqkv_k, dscore, dkrel, G, sa["Bt"], self.Hh, S,
+                   self.dk, rng=rng, site=1, drop_p=drop)
+        return dqkv_k.view(G, N, nb * S, 3 * d)[:, :, :L].reshape(G, T, 3 * d) if padded else dqkv_k
+
     # ------------------------------------------------------------------------------------------ forward
-    def forward(self, x, T, shared, training, want_f32=False):
-        """x bf16 [T, d] (shared by all groups) or [G, T, d].  Returns (out bf16 [G,T,dout], out_f32|None, saved)."""
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
+        """x bf16 [T, d] (shared by all groups) or [G, T, d]; `seq_len`: tokens per sequence (default sizeSeq).
+        Returns (out bf16 [G,T,dout], out_f32|None, saved)."""
         G, d, dout, dff, S = self.G, self.d, self.dout, self.dff, self.S
-        if T % S != 0:
-            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
-        Bt = T // S
         dev = x.device
         w32 = self.arena.ensure()
         P32 = self.spans(w32)
@@ -232,9 +278,7 @@ class TransformerStack:
         rng = ops.DropoutState.next(dev) if drop > 0 else None
         qkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
         ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared, out_bf16=qkv)
-        att = torch.empty(G, T, d, device=dev, dtype=BF16)
-        probs = torch.empty(G, Bt, self.Hh, S, S, device=dev, dtype=BF16)
-        K.attn_fwd(qkv, P32.get("krel"), att, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        att, sa = self._attn_fwd(qkv, P32.get("krel"), G, T, seq_len, rng, drop)
         pre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         res = (x, d, 0) if shared else x
         ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res)
@@ -255,8 +299,8 @@ class TransformerStack:
         rstd2 = torch.empty(G * T, device=dev)
         K.rownorm_fwd(pre2, G * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
                       rstd=rstd2, rows_per_group=T)
-        saved = dict(x=x, shared=shared, T=T, Bt=Bt, P16=P16, P32=P32, rng=rng, drop=drop, qkv=qkv, att=att,
-                     probs=probs, pre1=pre1, y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2,
+        saved = dict(x=x, shared=shared, T=T, P16=P16, P32=P32, rng=rng, drop=drop, sa=sa, att=att,
+                     pre1=pre1, y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2,
                      rstd2=rstd2)
         return out, out32, saved
 
@@ -267,7 +311,7 @@ class TransformerStack:
         ops.grad_ready(early_stage + ".ffn") as soon as they exist, a third of the way into this backward, so their
         all-reduce / optimizer step overlaps the rest of it; sv["announced"] tells the caller what is left."""
         G, d, do, dff, S = self.G, self.d, self.dout, self.dff, self.S
-        T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
+        T, P16, P32 = sv["T"], sv["P16"], sv["P32"]
         dev = dout.device
         gflat = sv.pop("gflat", None)  # cleared ahead of time by the caller (criterion forward), or now
         if gflat is None:
@@ -284,8 +328,6 @@ class TransformerStack:
         dy = torch.empty(G, T, d, device=dev, dtype=torch.float32 if ops.GRAD_F32 else BF16)
         dpre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         datt = torch.empty(G, T, d, device=dev, dtype=BF16)
-        dqkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
-        dscore = torch.empty_like(sv["probs"])
         dx = torch.zeros(T, d, device=dev) if shared else torch.empty(G, T, d, device=dev)  # shared: split-K target
         # out = LN2(pre2)
         K.rownorm_bwd(dout.reshape(G * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], G * T, do, P32["ln2w"], P32["ln2b"],
@@ -328,8 +370,7 @@ class TransformerStack:
         with ops.side(0):
             ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=G)
         ops.linear_dx(dpre1, P16["Wo"], T, d, d, groups=G, out_bf16=datt)
-        K.attn_bwd(sv["qkv"], P32.get("krel"), sv["att"], sv["probs"], datt, dqkv, dscore, Gd.get("krel"), G, Bt,
-                   self.Hh, S, self.dk, rng=sv["rng"], site=1, drop_p=sv["drop"])
+        dqkv = self._attn_bwd(sv["sa"], P32.get("krel"), Gd.get("krel"), datt, G, T, sv["rng"], sv["drop"])
         # qkv = x . Wqkv^T
         with ops.side(0):
             ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared)
@@ -353,7 +394,7 @@ class _TransformerFn(torch.autograd.Function):
     def forward(ctx, x, stack, training, *params):
         N, S_in, d = x.shape
         xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
-        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True)
+        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
         ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
         return out32.view(N, S_in, stack.dout)
 
@@ -385,13 +426,10 @@ class MultiHeadStack(TransformerStack):
         sh["b2"] = (1, self.K * self.d)
         return sh
 
-    def forward(self, x, T, shared, training, want_f32=False):
+    def forward(self, x, T, shared, training, want_f32=False, seq_len=None):
         d, dout, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
-        if T % S != 0:
-            raise ValueError(f"token count {T} is not a multiple of sizeSeq {S}")
         if x.dim() != 2:
             raise ValueError("MultiHeadStack takes one [T, d] input")
-        Bt = T // S
         dev = x.device
         P32 = self.spans(self.arena.ensure())
         P16 = self.spans(self.arena.bf16())
@@ -399,9 +437,7 @@ class MultiHeadStack(TransformerStack):
         rng = ops.DropoutState.next(dev) if drop > 0 else None
         qkv = torch.empty(1, T, 3 * d, device=dev, dtype=BF16)
         ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=1, x_shared=True, out_bf16=qkv)
-        att = torch.empty(1, T, d, device=dev, dtype=BF16)
-        probs = torch.empty(1, Bt, self.Hh, S, S, device=dev, dtype=BF16)
-        K.attn_fwd(qkv, P32.get("krel"), att, probs, 1, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        att, sa = self._attn_fwd(qkv, P32.get("krel"), 1, T, seq_len, rng, drop)
         pre1 = torch.empty(1, T, d, device=dev, dtype=BF16)
         ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0))
         y = torch.empty(T, d, device=dev, dtype=BF16)
@@ -422,14 +458,14 @@ class MultiHeadStack(TransformerStack):
         rstd2 = torch.empty(Kc * T, device=dev)
         K.rownorm_fwd(pre2, Kc * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
                       rstd=rstd2, rows_per_group=Kc * T)
-        saved = dict(x=x, T=T, Bt=Bt, P16=P16, P32=P32, rng=rng, drop=drop, qkv=qkv, att=att, probs=probs, pre1=pre1,
+        saved = dict(x=x, T=T, P16=P16, P32=P32, rng=rng, drop=drop, sa=sa, att=att, pre1=pre1,
                      y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2, rstd2=rstd2)
         return out, out32, saved
 
     def backward(self, sv, dout):
         """dout bf16 or fp32 [K, T, dout] -> (dx fp32 [T, d], flat fp32 grad arena)."""
         d, do, dff, S, Kc = self.d, self.dout, self.dff, self.S, self.K
-        T, Bt, P16, P32 = sv["T"], sv["Bt"], sv["P16"], sv["P32"]
+        T, P16, P32 = sv["T"], sv["P16"], sv["P32"]
         dev = dout.device
         gflat = sv.pop("gflat", None)  # cleared ahead of time by the caller (criterion forward), or now
         if gflat is None:
@@ -444,8 +480,6 @@ class MultiHeadStack(TransformerStack):
         dy = torch.zeros(T, d, device=dev)
         dpre1 = torch.empty(1, T, d, device=dev, dtype=BF16)
         datt = torch.empty(1, T, d, device=dev, dtype=BF16)
-        dqkv = torch.empty(1, T, 3 * d, device=dev, dtype=BF16)
-        dscore = torch.empty_like(sv["probs"])
         dx = torch.empty(T, d, device=dev)
         # out = LN2(pre2)
         K.rownorm_bwd(dout.reshape(Kc * T, do), sv["pre2"], sv["mean2"], sv["rstd2"], Kc * T, do, P32["ln2w"], P32["ln2b"],
@@ -480,8 +514,7 @@ class MultiHeadStack(TransformerStack):
         with ops.side(0):
             ops.linear_dw(dpre1, sv["att"], Gd["Wo"], T, d, d, groups=1)
         ops.linear_dx(dpre1, P16["Wo"], T, d, d, groups=1, out_bf16=datt)
-        K.attn_bwd(sv["qkv"], P32.get("krel"), sv["att"], sv["probs"], datt, dqkv, dscore, Gd.get("krel"), 1, Bt,
-                   self.Hh, S, self.dk, rng=sv["rng"], site=1, drop_p=sv["drop"])
+        dqkv = self._attn_bwd(sv["sa"], P32.get("krel"), Gd.get("krel"), datt, 1, T, sv["rng"], sv["drop"])
         # qkv = x . Wqkv^T
         with ops.side(0):
             ops.linear_dw(dqkv, x, Gd["Wqkv"], T, 3 * d, d, groups=1, x_shared=True)
@@ -497,7 +530,7 @@ class _MultiHeadFn(torch.autograd.Function):
     def forward(ctx, x, stack, training, *params):
         N, S_in, d = x.shape
         xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
-        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True)
+        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
         ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
         return out32
 

@@ -24,6 +24,47 @@ import math
 import torch
 import torch.nn.functional as F
 
+# --------------------------------------------------------------------------- #
+# bf16-storage emulation (tools/grad_floor_probe.py only)
+# --------------------------------------------------------------------------- #
+# With EMULATE_BF16 = True every tensor that ANY bf16-operand implementation of this path has to round -- GEMM
+# operands (weights and the activations between layers) and the gradients that travel between layers -- is rounded
+# to bf16 in the forward AND in the backward, everything else (accumulation, statistics, softmax, losses) stays fp32.
+# The cosine between the gradients of this emulation and the exact fp32 gradients is the noise floor of bf16
+# storage for a given fixture; the GPU parity tests derive their per-tensor limits from it instead of typing them in.
+EMULATE_BF16 = False
+
+
+class _RoundBoth(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).float()
+
+
+class _RoundFwd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def _q(x):
+    """Activation stored in bf16 (its gradient travels in bf16 too)."""
+    return _RoundBoth.apply(x) if EMULATE_BF16 else x
+
+
+def _w(x):
+    """Weight consumed as a bf16 GEMM operand (its gradient is accumulated in fp32)."""
+    return _RoundFwd.apply(x) if EMULATE_BF16 else x
+
+
 # (kernel, stride, padding) of conv0..conv4 -- cpc/model.py:85-94
 ENCODER_GEOMETRY = ((10, 5, 3), (8, 4, 2), (4, 2, 1), (4, 2, 1), (4, 2, 1))
 DOWNSAMPLING = 160  # cpc/model.py:96
@@ -45,10 +86,12 @@ def channel_norm(x, weight=None, bias=None, eps=1e-5):
 def encoder_forward(p, x, prefix="gEncoder."):
     """cpc/model.py:102-108.  x [N,1,W] -> [N,C,W/160] (normMode layerNorm)."""
     for i, (_, s, pad) in enumerate(ENCODER_GEOMETRY):
-        x = F.conv1d(x, p[f"{prefix}conv{i}.weight"], p[f"{prefix}conv{i}.bias"],
-                     stride=s, padding=pad)
-        x = F.relu(channel_norm(x, p[f"{prefix}batchNorm{i}.weight"],
-                                p[f"{prefix}batchNorm{i}.bias"]))
+        w = p[f"{prefix}conv{i}.weight"]
+        x = F.conv1d(x, _w(w) if i else w, p[f"{prefix}conv{i}.bias"], stride=s, padding=pad)
+        if i:
+            x = _q(x)
+        x = _q(F.relu(channel_norm(x, p[f"{prefix}batchNorm{i}.weight"],
+                                   p[f"{prefix}batchNorm{i}.bias"])))
     return x
 
 
@@ -69,10 +112,11 @@ def lstm_forward(p, x, n_layers, prefix="gAR.baseNet.", state=None):
             c = x.new_zeros(N, H)
         else:
             h, c = state[0][l], state[1][l]
-        gx = x @ w_ih.t() + b
+        w_ih, w_hh = _w(w_ih), _w(w_hh)
+        gx = _q(x) @ w_ih.t() + b
         out = []
         for t in range(S):
-            g = gx[:, t] + h @ w_hh.t()
+            g = gx[:, t] + _q(h) @ w_hh.t()
             i, f, gg, o = g.split(H, dim=1)
             c = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(gg)
             h = torch.sigmoid(o) * torch.tanh(c)
@@ -92,10 +136,11 @@ def gru_forward(p, x, n_layers, prefix="gAR.baseNet.", state=None):
         H = w_hh.shape[1]
         N, S, _ = x.shape
         h = x.new_zeros(N, H) if state is None else state[l]
-        gx = x @ w_ih.t() + b_ih
+        w_ih, w_hh = _w(w_ih), _w(w_hh)
+        gx = _q(x) @ w_ih.t() + b_ih
         out = []
         for t in range(S):
-            gh = h @ w_hh.t() + b_hh
+            gh = _q(h) @ w_hh.t() + b_hh
             xr, xz, xn = gx[:, t].split(H, dim=1)
             hr, hz, hn = gh.split(H, dim=1)
             r = torch.sigmoid(xr + hr)
@@ -116,10 +161,11 @@ def rnn_forward(p, x, n_layers, prefix="gAR.baseNet.", state=None):
         b = p[f"{prefix}bias_ih_l{l}"] + p[f"{prefix}bias_hh_l{l}"]
         N, S, _ = x.shape
         h = x.new_zeros(N, w_hh.shape[1]) if state is None else state[l]
-        gx = x @ w_ih.t() + b
+        w_ih, w_hh = _w(w_ih), _w(w_hh)
+        gx = _q(x) @ w_ih.t() + b
         out = []
         for t in range(S):
-            h = torch.tanh(gx[:, t] + h @ w_hh.t())
+            h = torch.tanh(gx[:, t] + _q(h) @ w_hh.t())
             out.append(h)
         x = torch.stack(out, dim=1)
         hs.append(h)
@@ -188,20 +234,22 @@ def transformer_layer(p, x, prefix, size_seq, nheads=8, relpos=True, masks=None,
     def split(t):  # transformers.py:88-90
         return t.view(N, S, nheads, dk).transpose(1, 2).reshape(N * nheads, S, dk)
 
-    q = split(x @ p[prefix + "multihead.Wq.weight"].t())
-    k = split(x @ p[prefix + "multihead.Wk.weight"].t())
-    v = split(x @ p[prefix + "multihead.Wv.weight"].t())
+    x = _q(x)
+    q = split(_q(x @ _w(p[prefix + "multihead.Wq.weight"]).t()))
+    k = split(_q(x @ _w(p[prefix + "multihead.Wk.weight"]).t()))
+    v = split(_q(x @ _w(p[prefix + "multihead.Wv.weight"]).t()))
     kr = p[prefix + "multihead.Att.Krelpos"] if relpos else None
     a = relpos_causal_attention(q, k, v, kr, size_seq,
                                 None if masks is None else masks["att"], drop_p)
-    a = a.view(N, nheads, S, dk).transpose(1, 2).reshape(N, S, d)  # transformers.py:92-95
-    a = a @ p[prefix + "multihead.Wo.weight"].t()
-    y = F.layer_norm(x + a, (d,), p[prefix + "ln_multihead.weight"], p[prefix + "ln_multihead.bias"])
-    h = F.relu(y @ p[prefix + "ffnetwork.lin1.weight"].t() + p[prefix + "ffnetwork.lin1.bias"])
+    a = _q(a.view(N, nheads, S, dk).transpose(1, 2).reshape(N, S, d))  # transformers.py:92-95
+    a = a @ _w(p[prefix + "multihead.Wo.weight"]).t()
+    y = _q(F.layer_norm(_q(x + a), (d,), p[prefix + "ln_multihead.weight"], p[prefix + "ln_multihead.bias"]))
+    h = F.relu(y @ _w(p[prefix + "ffnetwork.lin1.weight"]).t() + p[prefix + "ffnetwork.lin1.bias"])
     if masks is not None:
         h = h * masks["ffn"] / (1.0 - drop_p)
-    f = h @ p[prefix + "ffnetwork.lin2.weight"].t() + p[prefix + "ffnetwork.lin2.bias"]
-    u = (y + f) @ p[prefix + "last_linear.weight"].t() + p[prefix + "last_linear.bias"]
+    h = _q(h)
+    f = h @ _w(p[prefix + "ffnetwork.lin2.weight"]).t() + p[prefix + "ffnetwork.lin2.bias"]
+    u = _q(_q(y + f) @ _w(p[prefix + "last_linear.weight"]).t() + p[prefix + "last_linear.bias"])
     dout = u.shape[-1]
     return F.layer_norm(u, (dout,), p[prefix + "ln_ffnetwork.weight"], p[prefix + "ln_ffnetwork.bias"])
 
@@ -324,7 +372,7 @@ def prediction_heads(p, c, K, rnn_mode, size_seq, prefix="wPrediction.predictors
             y = F.conv1d(x, w, b) * math.sqrt(2.0 / (w.shape[1] * ks))
             out.append(y.permute(0, 2, 1))
         else:  # any other string falls through to the bias-free Linear (criterion.py:145-146)
-            out.append(c @ p[f"{prefix}{k}.weight"].t())
+            out.append(c @ _w(p[f"{prefix}{k}.weight"]).t())
     return out
 
 
@@ -342,10 +390,13 @@ def criterion_forward(p, c, z, batch_idx, seq_idx, K, NEG, rnn_mode="transformer
         c = torch.flip(c, [1])
     B, S, D = z.shape
     W = S - K
-    cw = c[:, :W]
+    cw = _q(c[:, :W])
+    z = _q(z)
     ext = negative_ext_index(batch_idx, seq_idx, B, S, W, NEG)
     neg = z.reshape(-1, D)[ext].view(B, NEG, W, D)
     preds = prediction_heads(p, cw, K, rnn_mode, W, masks=masks, drop_p=drop_p, multihead=multihead)
+    if EMULATE_BF16:
+        preds = [_q(t) for t in preds]
     losses, accs, logits_all, arg_all = [], [], [], []
     for k in range(1, K + 1):
         pos = z[:, k:k + W].unsqueeze(1)                       # criterion.py:276-282

@@ -1,9 +1,13 @@
 """Import the UNMODIFIED reference (MarvinLvn/CPC2) from /root/reference -- TEST INFRASTRUCTURE.
 
-Used only by `tests/golden/make_golden.py`, in the build container, to generate
-the committed golden vectors that pin `oracle/cpc_oracle.py`.  /root/reference
-does not exist on the GPU box, so nothing under `tests/ -m gpu`, `smoke()` or
-`bench.py` imports this file.
+Used by `tests/golden/make_golden.py`, in the build container, to generate the
+committed golden vectors that pin `oracle/cpc_oracle.py`, and by the reference
+arm of `bench.py` (`--impl reference`, and the `stock_gpu` comparator).
+/root/reference does not exist on the GPU box: there the same files are imported
+from `oracle/_ref/cpc_reference.zip`, the byte-for-byte archive that
+`oracle/make_ref.py` (run by `build()`) packs from /root/reference -- git-ignored,
+so the history holds no reference source.  Nothing under `cpc2_b200/` and no
+`-m gpu` test imports this file.
 
 No reference file is edited or copied.  Three things are shimmed in-process:
   * empty stub modules for `progressbar`, `augment`, `torch_audiomentations`
@@ -22,11 +26,24 @@ import types
 import torch
 
 REFERENCE_ROOT = os.environ.get("CPC2_REFERENCE_ROOT", "/root/reference")
+ARCHIVE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "cpc_reference.zip")
+
+
+def reference_location():
+    """The reference tree if it is on this machine, else the archive packed by oracle/make_ref.py, else None."""
+    if os.path.isdir(os.path.join(REFERENCE_ROOT, "cpc")):
+        return REFERENCE_ROOT
+    if os.path.exists(ARCHIVE):
+        return ARCHIVE
+    return None
 
 
 def import_reference():
-    if not os.path.isdir(os.path.join(REFERENCE_ROOT, "cpc")):
-        raise RuntimeError(f"reference tree not found at {REFERENCE_ROOT}")
+    global REFERENCE_ROOT
+    loc = reference_location()
+    if loc is None:
+        raise RuntimeError(f"reference not found: neither {REFERENCE_ROOT} nor {ARCHIVE} (python oracle/make_ref.py)")
+    REFERENCE_ROOT = loc
     for name in ("progressbar", "augment", "augment.effects", "torch_audiomentations"):
         if name not in sys.modules:
             sys.modules[name] = types.ModuleType(name)
@@ -102,3 +119,57 @@ def flat_state(m, crit):
     out = {k: v.detach().clone() for k, v in m.state_dict().items()}
     out.update({k: v.detach().clone() for k, v in crit.state_dict().items()})
     return out
+
+
+def timed_reference_steps(over, B, steps, warmup, device="cpu", autocast=None, tf32=True, seed=0):
+    """Time `steps` iterations of the reference's own batch-loop body (cpc/train.py:95-109: concatenate past and
+    future windows, CPCModel.forward, slice, criterion, `allLosses.sum().backward()`) in TRAIN mode (dropout on,
+    as trainStep runs it), after `warmup` untimed ones, on the unmodified reference modules.  Returns
+    (seconds per step, last mean loss).  device 'cuda': CUDA-event time; `autocast` = torch.bfloat16 wraps the
+    forward in torch.autocast like mixed-precision users of the reference would; `tf32` sets the cuBLAS / cuDNN
+    TF32 switches (the reference pins torch 1.3 where they did not exist; on Ampere+ TF32 convs are the default)."""
+    import time
+    args = reference_args(**over)
+    m, crit = build_reference(args, seed=seed)
+    dev = torch.device(device)
+    m, crit = m.to(dev).train(), crit.to(dev).train()
+    g = torch.Generator().manual_seed(1234)
+    seq = (0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=g)).to(dev)
+    label = torch.zeros(2 * B, dtype=torch.long, device=dev)
+    params = list(m.parameters()) + list(crit.parameters())
+    if dev.type == "cuda":
+        torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
+        torch.backends.cudnn.allow_tf32 = bool(tf32)
+
+    def one():
+        for q in params:
+            q.grad = None
+        combined = torch.cat([seq[:, 0, ...], seq[:, 1, ...]], dim=0)
+        if autocast is not None:
+            with torch.autocast(dev.type, dtype=autocast):
+                c, z, lab = m(combined, label)
+                losses, acc = crit(c[:B], z[B:], lab[:B], None)
+        else:
+            c, z, lab = m(combined, label)
+            losses, acc = crit(c[:B], z[B:], lab[:B], None)
+        losses.sum().backward()
+        return losses
+
+    for _ in range(warmup):
+        one()
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            losses = one()
+        e1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / steps
+        return e0.elapsed_time(e1) * 1e-3 / steps, float(losses.mean()), wall
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        losses = one()
+    sec = (time.perf_counter() - t0) / steps
+    return sec, float(losses.mean()), sec

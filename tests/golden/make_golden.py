@@ -113,12 +113,94 @@ def run_case(name, over, B, full=True):
           "acc", [round(float(x), 4) for x in out["acc"].flatten()])
 
 
+# --------------------------------------------------------------------------------------------------------------
+# Fixtures taken AWAY FROM INITIALISATION.  At random init every logit is ~0, the softmax is uniform and the
+# encoder's gradients are sums of almost exactly cancelling terms -- a regime in which a gradient comparison
+# measures rounding noise.  The `*_trained` fixtures first run the reference's own optimiser
+# (torch.optim.Adam, cpc/train.py:472-479) on a predictable batch (future window = past window + small noise) until
+# the mean InfoNCE loss has left the ln(NEG+1) plateau, then round every parameter to a bf16-representable fp32
+# value (so the bf16 GEMM operands of the CUDA path are the SAME numbers the reference multiplies), and only then
+# take the golden step -- unmodified reference, CPU fp32, eval mode, a FRESH batch and fresh negative indices.
+TRAIN_LR = 5e-3
+TRAINED = {
+    # name: (arg overrides, batch, max optimiser steps)
+    **{k + "_trained": (v[0], max(v[1], 4), 900) for k, v in CASES.items() if k != "tiny_lstm_quality_skip1"},
+    # the default WIDTH (256 channels, 8 attention heads of 32: the tensor-core attention kernels) with transformer
+    # prediction heads on a short window; big tensors are stored as strided samples to keep the fixture small
+    "mid256_lstm_transformer_trained": (dict(hiddenEncoder=256, hiddenGar=256, nPredicts=2, negativeSamplingExt=16,
+                                             sizeWindow=5120, arMode="LSTM", rnnMode="transformer"), 4, 420),
+}
+SUB_MAX = 1 << 15  # gradients with more elements are stored as g.flatten()[::stride], stride = ceil(numel / SUB_MAX)
+
+
+def predictable_sequence(B, W, seed):
+    g = torch.Generator().manual_seed(seed)
+    past = 0.1 * torch.randn(B, 1, 1, W, generator=g)
+    return torch.cat([past, past + 0.01 * torch.randn(B, 1, 1, W, generator=g)], dim=1)
+
+
+def run_trained_case(name, over, B, max_steps):
+    import math
+    args = rh.reference_args(**over)
+    m, crit = rh.build_reference(args, seed=0)
+    params = list(m.parameters()) + list(crit.parameters())
+    opt = torch.optim.Adam(params, lr=TRAIN_LR, betas=(0.9, 0.999), eps=1e-8)
+    train_seq = predictable_sequence(B, args.sizeWindow, 777)
+    target = 0.8 * math.log(args.negativeSamplingExt + 1)
+    steps = 0
+    for steps in range(1, max_steps + 1):
+        out = rh.reference_step(m, crit, train_seq, crit_seed=1000 + steps, train_mode=False)
+        opt.step()
+        if float(out["loss"].mean()) < target and steps >= 20:
+            break
+    with torch.no_grad():
+        for q in params:
+            q.copy_(q.to(torch.bfloat16).float())
+    seq = predictable_sequence(B, args.sizeWindow, 1234)
+    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=False)
+    S = args.sizeWindow // 160
+    W = S - args.nPredicts
+    torch.manual_seed(CRIT_SEED)
+    n = args.negativeSamplingExt * W * B
+    batch_idx = torch.randint(0, B, (n,))
+    seq_idx = torch.randint(1, S, (n,))
+    base = torch.arange(0, W).view(1, 1, W).expand(B, args.negativeSamplingExt, W).contiguous().view(-1)
+    ext = torch.remainder(seq_idx + base, S) + batch_idx * S
+    state = rh.flat_state(m, crit)
+    state = {k: v for k, v in state.items() if v.dtype.is_floating_point
+             and not k.endswith(".mask") and not k.endswith(".z")}
+    big = sum(v.numel() for v in state.values()) > 1_000_000
+    grads, strides = {}, {}
+    for k, g in out["grads"].items():
+        st = max(1, -(-g.numel() // SUB_MAX)) if big else 1
+        strides[k] = st
+        grads[k] = g.flatten()[::st].clone() if st > 1 else g.clone()
+    fx = {
+        "args": {k: getattr(args, k) for k in ("hiddenEncoder", "hiddenGar", "nPredicts", "negativeSamplingExt",
+                                              "sizeWindow", "arMode", "nLevelsGRU", "rnnMode", "cpc_mode",
+                                              "abspos", "n_skipped", "multihead_rnn")},
+        "B": B, "crit_seed": CRIT_SEED, "seq_seed": 1234, "init_seed": 0, "trained_steps": steps, "train_lr": TRAIN_LR,
+        "loss": out["loss"], "acc": out["acc"], "torch": torch.__version__,
+        "batch_idx": batch_idx.int(), "seq_idx": seq_idx.int(), "ext_idx": ext.int(),
+        # parameters are exactly representable in bf16: stored as bf16 when the model is big
+        "state": {k: (v.to(torch.bfloat16) if big else v) for k, v in state.items()},
+        "sequence": seq, "c": out["c"], "z": out["z"], "grads": grads, "grad_stride": strides,
+        "grad_norm": {k: float(v.double().norm()) for k, v in out["grads"].items()},
+    }
+    torch.save(fx, os.path.join(OUT, name + ".pt"))
+    print(name, "steps", steps, "loss", [round(float(x), 4) for x in out["loss"].flatten()],
+          "acc", [round(float(x), 3) for x in out["acc"].flatten()], "(plateau %.3f)" % math.log(args.negativeSamplingExt + 1))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count())
     only = sys.argv[1:]  # optional: case names to (re)generate
     for name, (over, B) in CASES.items():
         if not only or name in only:
             run_case(name, over, B)
+    for name, (over, B, max_steps) in TRAINED.items():
+        if (not only or name in only) and not (only == [] and os.environ.get("CPC_GOLDEN_SKIP_TRAINED")):
+            run_trained_case(name, dict(over), B, max_steps)
     if only:
         sys.exit(0)
     # full-size default config (config 1 of BASELINE.json): summary only, weights by seed

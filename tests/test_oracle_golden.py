@@ -51,6 +51,74 @@ def test_step_matches_reference(golden_dir, name):
         torch.testing.assert_close(out["grads"][k], g, rtol=2e-4, atol=2e-6, msg=lambda m: f"{k}: {m}")
 
 
+TRAINED_CASES = [c + "_trained" for c in FULL_CASES if c != "tiny_lstm_quality_skip1"] + ["mid256_lstm_transformer_trained"]
+
+
+@pytest.mark.parametrize("name", TRAINED_CASES)
+def test_step_matches_reference_away_from_init(golden_dir, name):
+    """The same pin on fixtures taken after the reference's own Adam has moved the model off the ln(NEG+1) plateau
+    (tests/golden/make_golden.py, `*_trained`): logits are no longer ~0, so the gradients are not cancelling sums.
+    Big gradients are stored as strided samples (fx["grad_stride"])."""
+    fx = _load(golden_dir, name)
+    a = fx["args"]
+    state = {k: v.float() for k, v in fx["state"].items()}
+    out = oc.train_step(state, fx["sequence"], fx["batch_idx"].long(), fx["seq_idx"].long(),
+                        K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"],
+                        n_layers=a["nLevelsGRU"], rnn_mode=a["rnnMode"], cpc_mode=a["cpc_mode"],
+                        abspos=a["abspos"], n_skipped=a["n_skipped"], multihead=a.get("multihead_rnn", False))
+    import math
+    assert float((fx["loss"] - math.log(a["negativeSamplingExt"] + 1)).abs().max()) > 0.01  # really off the plateau
+    torch.testing.assert_close(out["z"], fx["z"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out["c"], fx["c"], rtol=1e-4, atol=2e-5)
+    torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=2e-6)
+    assert torch.equal(out["acc"], fx["acc"])
+    assert set(out["grads"]) == set(fx["grads"])
+    for k, g in fx["grads"].items():
+        st = fx["grad_stride"][k]
+        got = out["grads"][k].flatten()[::st] if st > 1 else out["grads"][k]
+        torch.testing.assert_close(got, g, rtol=5e-4, atol=1e-6 + 1e-5 * float(g.abs().max()), msg=lambda m: f"{k}: {m}")
+        assert abs(float(out["grads"][k].double().norm()) - fx["grad_norm"][k]) <= 1e-4 * fx["grad_norm"][k] + 1e-12, k
+
+
+def test_full_size_default_step_matches_reference_summary(golden_dir):
+    """BASELINE.json configs[0] at its real size (encoder 256, LSTM 256, 12 transformer heads, 128 negatives, window
+    20480, batch 8): the oracle's losses, activations, sampled indices and EVERY gradient (norm + a 64-element strided
+    sample per tensor) against what the unmodified reference produced (default_b8_summary.pt).  Weights come from the
+    same seeded constructors (the fingerprint proves they are the reference's)."""
+    from cpc2_b200 import train as T
+    fx = _load(golden_dir, "default_b8_summary")
+    a = fx["args"]
+    torch.manual_seed(fx["init_seed"])
+    model, crit = T.buildModelAndCriterion(T.defaultArgs())
+    state = {k: v.detach().float() for k, v in list(model.state_dict().items()) + list(crit.state_dict().items())}
+    for k, (sm, ab) in fx["fingerprint"].items():
+        v = state[k].double()
+        assert abs(float(v.sum()) - sm) <= 1e-6 * max(1.0, ab) and abs(float(v.abs().sum()) - ab) <= 1e-6 * max(1.0, ab), k
+    B, S = fx["B"], a["sizeWindow"] // 160
+    W = S - a["nPredicts"]
+    seq = 0.1 * torch.randn(B, 2, 1, a["sizeWindow"], generator=torch.Generator().manual_seed(fx["seq_seed"]))
+    torch.manual_seed(fx["crit_seed"])
+    bi, si = oc.draw_negative_indices(B, S, W, a["negativeSamplingExt"])
+    ext = oc.negative_ext_index(bi, si, B, S, W, a["negativeSamplingExt"])
+    assert torch.equal(ext[:2048].int(), fx["ext_head"]) and int(ext.sum()) == fx["ext_sum"]
+    assert int((ext * (torch.arange(ext.numel()) % 1009)).sum()) == fx["ext_weighted_sum"]
+    import os as _os
+    torch.set_num_threads(_os.cpu_count())
+    out = oc.train_step(state, seq, bi, si, K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"],
+                        n_layers=a["nLevelsGRU"], rnn_mode=a["rnnMode"])
+    torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=1e-5)
+    assert (out["acc"] - fx["acc"]).abs().max() <= 1.5 / (B * W)  # near-ties at init may flip one argmax in fp32
+    torch.testing.assert_close(out["z"][:, ::16, ::32], fx["z_slice"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out["c"][:, ::16, ::32], fx["c_slice"], rtol=1e-4, atol=1e-5)
+    assert set(out["grads"]) == set(fx["grad_norm"])
+    for k, n in fx["grad_norm"].items():
+        g = out["grads"][k]
+        assert abs(float(g.double().norm()) - n) <= 2e-3 * n + 1e-12, (k, float(g.double().norm()), n)
+        sl = g.flatten()[:: max(1, g.numel() // 64)][:64]
+        ref = fx["grad_slice"][k]
+        assert (sl - ref).abs().max() <= 2e-3 * float(ref.abs().max()) + 1e-3 * n / max(1.0, g.numel() ** 0.5), k
+
+
 def test_channel_norm_unbiased_variance():
     x = torch.randn(2, 8, 5)
     y = oc.channel_norm(x)

@@ -3,15 +3,21 @@ cpc/train.py:95-109, against
   (a) the committed golden vectors produced by the UNMODIFIED reference (tests/golden/*.pt), and
   (b) the CPU oracle (oracle/cpc_oracle.py) on identical weights, inputs and sampled negative indices.
 
-Stated tolerances (bf16 operands, fp32 accumulation / statistics): per-step loss abs <= 2e-2,
-accuracy abs <= 1 % (argmax can flip on near-ties in bf16), activations rel 3e-2 of the tensor's max,
-gradient cosine per parameter tensor >= 0.99 against the oracle evaluated on the bf16-rounded GEMM weights
-(the function the bf16 path computes) and >= 0.985 against the oracle on the fp32 weights: at random
-initialisation the encoder's bias / norm gradients are sums over 65k frames with near-total cancellation,
-and merely rounding the weights to bf16 in an otherwise exact fp32 evaluation already moves them to cosine
-0.9946 (tools/grad_noise_probe.py, profiles/r01_grad_noise.log).  Sampled indices are bit exact
-(tests/test_kernels_gpu.py checks the index kernel).
+ONE stated tolerance (bf16 operands, fp32 accumulation / statistics): per-step loss abs <= 2e-2,
+accuracy abs <= 1 % (argmax can flip on near-ties in bf16), activations rel 3e-2 of the tensor's max, gradient
+cosine per parameter tensor >= MIN_COS = 0.99 against the fp32 reference / oracle gradients.  The only exception
+is DERIVED, not typed in: where rounding GEMM operands and inter-layer gradients to bf16 -- which any bf16
+implementation must do -- already pushes the exact algorithm below 0.99, the limit is that noise floor minus
+FLOOR_MARGIN.  The floor is the cosine between the oracle evaluated with bf16 storage emulation
+(oracle.cpc_oracle.EMULATE_BF16) and the fp32 gradients: read from tests/golden/grad_floor.json
+(tools/grad_floor_probe.py) for the committed fixtures, computed on the spot for the oracle cases.  It only bites
+on fixtures taken AT RANDOM INITIALISATION (every logit ~0, encoder gradients are cancelling sums); the `*_trained`
+fixtures and the warmed-up oracle cases sit on the 0.99 line.  Sampled indices are bit exact
+(tests/test_kernels_gpu.py checks the index kernel).  Every comparison is appended to
+gpurun_out/parity_report.jsonl (worst cosine, its limit, loss / accuracy errors) so the numbers behind a green run
+can be read afterwards.
 """
+import json
 import os
 
 import pytest
@@ -21,6 +27,18 @@ import torch.nn.functional as F
 pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MIN_COS = 0.99
+FLOOR_MARGIN = 0.015
+with open(os.path.join(GOLD, "grad_floor.json")) as _fh:
+    GRAD_FLOOR = json.load(_fh)
+
+
+def report(tag, **kw):
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "parity_report.jsonl"), "a") as fh:
+            fh.write(json.dumps(dict(case=tag, **kw)) + "\n")
 
 
 def _need_gpu():
@@ -39,8 +57,9 @@ def cosine(a, b):
     return F.cosine_similarity(a.double().flatten(), b.double().flatten(), dim=0).item()
 
 
-def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_quality=None):
-    """cpc/train.py:95-109.  If ext is given the sampler is bypassed so both sides use identical indices."""
+def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_quality=None, collect=True):
+    """cpc/train.py:95-109.  If ext is given the sampler is bypassed so both sides use identical indices.
+    collect=False: leave everything on the device (no host copies of c / z / gradients)."""
     model.train(train_mode)
     crit.train(train_mode)
     for p in list(model.parameters()) + list(crit.parameters()):
@@ -64,58 +83,67 @@ def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_qua
         losses.sum().backward()
     finally:
         crit.sampleIndices = orig
+    if not collect:
+        return dict(loss=losses.detach())
     grads = {k: v.grad.detach().float().cpu() for k, v in model.named_parameters() if v.grad is not None}
     grads.update({k: v.grad.detach().float().cpu() for k, v in crit.named_parameters() if v.grad is not None})
     return dict(loss=losses.detach().cpu(), acc=acc.detach().cpu(), c=c.detach().cpu(), z=z.detach().cpu(),
                 grads=grads, ext=captured["ext"].cpu())
 
 
-def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, min_cos=0.99):
-    assert (out["loss"] - ref_loss).abs().max() <= 2e-2, (out["loss"], ref_loss)
-    assert (out["acc"] - ref_acc).abs().max() <= 0.0101 + 1.0 / ref_c.shape[1], (out["acc"], ref_acc)
-    for name, got, ref in (("z", out["z"], ref_z), ("c", out["c"], ref_c)):
-        err = (got - ref).abs().max().item()
-        assert err <= 3e-2 * ref.abs().max().item() + 1e-3, f"{name}: max err {err}"
-    bad = []
+def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, strides=None, tag=""):
+    """`floors`: per-tensor bf16-storage noise floor (see the module docstring); None = the plain 0.99 line.
+    `strides`: fixtures that store big gradients as g.flatten()[::stride]."""
+    loss_err = (out["loss"] - ref_loss).abs().max().item()
+    acc_err = (out["acc"] - ref_acc).abs().max().item()
+    rows, bad = [], []
     for k, g in ref_grads.items():
         assert k in out["grads"], f"missing grad {k}"
         if g.abs().max() == 0:
             continue
-        cs = cosine(out["grads"][k], g)
-        # layer-0 norm / bias gradients: 65k-frame sums with near-total cancellation (see module docstring)
-        lim = min_cos - 0.01 if ("batchNorm0" in k or "conv0.bias" in k) else min_cos
+        st = (strides or {}).get(k, 1)
+        got = out["grads"][k].flatten()[::st] if st > 1 else out["grads"][k]
+        cs = cosine(got, g)
+        lim = MIN_COS if floors is None else min(MIN_COS, floors.get(k, 1.0) - FLOOR_MARGIN)
+        rows.append((k, round(cs, 5), round(lim, 4)))
         if cs < lim:
-            bad.append((k, round(cs, 4)))
-    assert not bad, f"gradient cosine below {min_cos}: {bad}"
+            bad.append((k, round(cs, 4), round(lim, 4)))
+    worst = min(rows, key=lambda r: r[1] - r[2]) if rows else None
+    report(tag, loss_err=loss_err, acc_err=acc_err, worst=worst, min_cos=min(r[1] for r in rows) if rows else None,
+           n_below_099=sum(r[1] < MIN_COS for r in rows), n_tensors=len(rows), failed=bad)
+    assert loss_err <= 2e-2, (out["loss"], ref_loss)
+    assert acc_err <= 0.0101 + 1.0 / ref_c.shape[1], (out["acc"], ref_acc)
+    for name, got, ref in (("z", out["z"], ref_z), ("c", out["c"], ref_c)):
+        err = (got - ref).abs().max().item()
+        assert err <= 3e-2 * ref.abs().max().item() + 1e-3, f"{name}: max err {err}"
+    assert not bad, f"gradient cosine below its limit (tensor, cosine, limit): {bad}"
 
 
 GOLDEN_CASES = ["tiny_lstm_linear", "tiny_lstm_reverse_linear", "tiny_transformer_ar_linear", "tiny_gru2_transformer",
-                "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN", "tiny_lstm_quality_skip1"]
+                "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN",
+                "tiny_lstm_quality_skip1"]
+# (tiny_rnn_hneq_linear pins the oracle only: its hidden size 24 is not one the recurrence kernels are built for)
+# the same configurations after the reference's Adam has left the ln(NEG+1) plateau, plus the default width
+TRAINED_CASES = [c + "_trained" for c in GOLDEN_CASES if c != "tiny_lstm_quality_skip1"] + ["mid256_lstm_transformer_trained"]
 
 
-@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("name", GOLDEN_CASES + TRAINED_CASES)
 def test_against_reference_golden(name):
+    """CUDA path vs vectors of the UNMODIFIED reference: identical weights, inputs and sampled indices."""
     _need_gpu()
     from cpc2_b200 import train as T
     fx = torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
     args = T.defaultArgs(**fx["args"])
     model, crit = build(args)
-    ms = {k: v for k, v in fx["state"].items() if k.startswith("g")}
-    cs = {k: v for k, v in fx["state"].items() if k.startswith("wPrediction")}
+    ms = {k: v.float() for k, v in fx["state"].items() if k.startswith("g")}
+    cs = {k: v.float() for k, v in fx["state"].items() if k.startswith("wPrediction")}
     model.load_state_dict(ms, strict=False)
     missing = crit.load_state_dict(cs, strict=False)
     assert not missing.unexpected_keys
     quality = fx["signal_quality"].cuda() if "signal_quality" in fx else None
     out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long(), signal_quality=quality)
-    # tiny models (C = 32): gradients of 32-wide layers carry more bf16 noise -> cosine 0.98; the two-layer GRU +
-    # transformer-head case (B = 2, 16 frames) measured 0.9755 on one ChannelNorm gain (a 32-term cancelling sum)
-    # tiny_lstm_headsLSTM: zero-state LSTM heads at C = 32 emit |pred| ~ 0.05, the logits are ~1e-3 and the encoder's
-    # gradients are differences of nearly equal terms: heads / AR / conv3-4 tensors >= 0.98, the first encoder layers
-    # 0.935-0.979.  The same heads at C = 128 (test_against_oracle[lstm_heads]) hold 0.985 / 0.99 on every tensor.
-    min_cos = {"tiny_gru2_transformer": 0.97, "tiny_lstm_multihead": 0.97, "tiny_lstm_headsLSTM": 0.93}.get(name, 0.98)
-    check_against(out, fx["loss"], fx["acc"], fx["c"], fx["z"], fx["grads"], min_cos=min_cos)
-    # (tiny_lstm_multihead: every tensor >= 0.98 except gEncoder.batchNorm0.weight at 0.965, the same 32-term
-    # cancelling sum)
+    check_against(out, fx["loss"], fx["acc"], fx["c"], fx["z"], fx["grads"], floors=GRAD_FLOOR[name],
+                  strides=fx.get("grad_stride"), tag="golden/" + name)
 
 
 def _oracle_kwargs(args):
@@ -131,11 +159,19 @@ def _state_for_oracle(model, crit):
 
 
 ORACLE_CASES = {
+    # BASELINE.json configs[1]: the CPC default
     "default_lstm_transformer_heads": dict(),
     "default_linear_heads": dict(rnnMode="linear"),
+    # configs[2] as BASELINE.json states it: transformer AR (feature_loader.py:216-220) AND the default transformer heads
+    "config3_transformer_ar_transformer_heads": dict(arMode="transformer"),
     "transformer_ar": dict(arMode="transformer", rnnMode="linear"),
+    "transformer_ar_abspos": dict(arMode="transformer", abspos=True, rnnMode="linear"),
+    # configs[3]: hidden 512, 2-layer LSTM, window 40960 with the default transformer heads (dk = 64, W' = 244)
+    "config4_hidden512_lstm2_window40960_transformer_heads": dict(hiddenEncoder=512, hiddenGar=512, nLevelsGRU=2,
+                                                                  sizeWindow=40960),
     "lstm2_hidden512_window40960": dict(hiddenEncoder=512, hiddenGar=512, nLevelsGRU=2, sizeWindow=40960,
                                         rnnMode="linear"),
+    "reverse_mode_default_size": dict(cpc_mode="reverse"),
     "gru_ar_default_size": dict(arMode="GRU", rnnMode="linear"),
     "gru2_hidden_neq_encoder": dict(arMode="GRU", nLevelsGRU=2, hiddenEncoder=64, hiddenGar=128, nPredicts=4,
                                     negativeSamplingExt=16, sizeWindow=5120, rnnMode="linear"),
@@ -153,19 +189,51 @@ ORACLE_CASES = {
     "rnn_heads": dict(rnnMode="RNN", hiddenEncoder=128, hiddenGar=128, nPredicts=4, negativeSamplingExt=32,
                       sizeWindow=10240),
 }
+# cases that are ALSO compared at random initialisation (the regime round 1 tested); every case is compared after the
+# warm-up below
+AT_INIT = ("default_lstm_transformer_heads", "default_linear_heads", "transformer_ar", "gru2_hidden_neq_encoder")
+WARM_STEPS, WARM_LR = 400, 5e-3
 
 
-@pytest.mark.parametrize("name", list(ORACLE_CASES))
+def predictable_sequence(B, W, seed):
+    g = torch.Generator().manual_seed(seed)
+    past = 0.1 * torch.randn(B, 1, 1, W, generator=g)
+    return torch.cat([past, past + 0.01 * torch.randn(B, 1, 1, W, generator=g)], dim=1)
+
+
+def warm_up(model, crit, args, B):
+    """Move the model off the ln(NEG+1) plateau with torch.optim.Adam on a predictable batch (the regime the
+    reference trains in: logits no longer ~0, gradients no longer cancelling sums).  Runs on the CUDA path itself --
+    the comparison that follows is against the oracle evaluated at whatever state this leaves."""
+    import math
+    opt = torch.optim.Adam(list(model.parameters()) + list(crit.parameters()), lr=WARM_LR)
+    seq = predictable_sequence(B, args.sizeWindow, 777).cuda()
+    target = 0.8 * math.log(args.negativeSamplingExt + 1)
+    loss = float("nan")
+    for it in range(WARM_STEPS):
+        out = run_step(model, crit, seq, seed=1000 + it, collect=False)
+        opt.step()
+        if it % 10 == 9:
+            loss = float(out["loss"].mean())
+            assert loss == loss, "NaN during warm-up"
+            if loss < target and it >= 20:
+                break
+    return it + 1, loss
+
+
+@pytest.mark.parametrize("name", [n + "@init" for n in AT_INIT] + list(ORACLE_CASES))
 def test_against_oracle(name):
     _need_gpu()
     from cpc2_b200 import train as T
     from oracle import cpc_oracle as oc
-    over = ORACLE_CASES[name]
+    at_init = name.endswith("@init")
+    over = ORACLE_CASES[name.split("@")[0]]
     args = T.defaultArgs(**over)
     B = 8 if args.sizeWindow <= 20480 else 4
     model, crit = build(args)
-    g = torch.Generator().manual_seed(1234)
-    seq = 0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=g)
+    warm = (0, None) if at_init else warm_up(model, crit, args, B)
+    seq = predictable_sequence(B, args.sizeWindow, 1234) if not at_init else \
+        0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=torch.Generator().manual_seed(1234))
     out = run_step(model, crit, seq.cuda())
     S = args.sizeWindow // 160
     W = S - args.nPredicts
@@ -177,17 +245,18 @@ def test_against_oracle(name):
     seq_idx = torch.where(seq_idx == 0, torch.full_like(seq_idx, S), seq_idx)  # any representative works
     assert torch.equal(oc.negative_ext_index(batch_idx, seq_idx, B, S, W, args.negativeSamplingExt), ext)
     torch.set_num_threads(os.cpu_count())
-    ref = oc.train_step(_state_for_oracle(model, crit), seq, batch_idx, seq_idx, **_oracle_kwargs(args))
-    # GRU at 64 channels: AR gradients match to 0.9999, the encoder's cancelling sums are noisier than with the
-    # LSTM (tools/grad_cos_probe.py: batchNorm1.weight 0.9756, every other tensor >= 0.987) -> 0.97 for those cases
-    loose = 0.015 if name.startswith("gru2") else 0.0
-    check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], ref["grads"], min_cos=0.985 - loose)
     st = _state_for_oracle(model, crit)
-    for k, v in st.items():  # tensors the GPU path consumes as bf16 GEMM operands
-        if v.dim() >= 2 and not k.endswith("Krelpos") and "conv0" not in k and "batchNorm" not in k:
-            st[k] = v.to(torch.bfloat16).float()
-    refq = oc.train_step(st, seq, batch_idx, seq_idx, **_oracle_kwargs(args))
-    check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], refq["grads"], min_cos=0.99 - loose)
+    ref = oc.train_step(st, seq, batch_idx, seq_idx, **_oracle_kwargs(args))
+    # bf16-storage noise floor of THIS state, per tensor (module docstring): the exact algorithm with bf16 operands
+    oc.EMULATE_BF16 = True
+    try:
+        emu = oc.train_step(st, seq, batch_idx, seq_idx, **_oracle_kwargs(args))
+    finally:
+        oc.EMULATE_BF16 = False
+    floors = {k: cosine(emu["grads"][k], g) for k, g in ref["grads"].items() if g.abs().max() > 0}
+    report("oracle/" + name + "/setup", warm_steps=warm[0], warm_loss=warm[1], loss=[round(float(x), 4) for x in ref["loss"].flatten()],
+           min_floor=min(floors.values()), floors_below_099=sorted((round(v, 4), k) for k, v in floors.items() if v < MIN_COS))
+    check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], ref["grads"], floors=floors, tag="oracle/" + name)
 
 
 def test_default_init_matches_reference_fingerprint():
@@ -559,22 +628,26 @@ def test_reference_wrappers_dataparallel_and_ddp():
 
 
 @pytest.mark.gpu
-def test_build_feature_chunks_of_any_length():
+@pytest.mark.parametrize("ar_mode", ["LSTM", "transformer"])
+def test_build_feature_chunks_of_any_length(ar_mode):
     """Feature extraction as cpc/feature_loader.py:323-367 (buildFeature) drives the model: one file, batch 1, no
     grad, chunks of maxSizeSeq = 64000 samples plus a last chunk whose length is not a multiple of the 160-sample
-    hop -- with and without the AR state carried across chunks (keepHidden) -- against the oracle."""
+    hop -- with and without the AR state carried across chunks (keepHidden) for the LSTM, and through the transformer
+    AR's block-local padding (400 frames = 12.5 blocks of sizeSeq 32, transformers.py:38-50) -- against the oracle
+    (SURVEY 8f.4)."""
     _need_gpu()
     from cpc2_b200 import train as T
     from oracle import cpc_oracle as oc
     args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120,
-                         rnnMode="linear")
+                         rnnMode="linear", arMode=ar_mode)
     model, _ = build(args)
     model.eval()
     g = torch.Generator().manual_seed(77)
     wav = 0.1 * torch.randn(1, 64000 * 2 + 23457, generator=g)
     st = {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
-    for keep in (False, True):
-        model.gAR.keepHidden, model.gAR.hidden = keep, None
+    for keep in ((False, True) if ar_mode == "LSTM" else (False,)):
+        if ar_mode == "LSTM":
+            model.gAR.keepHidden, model.gAR.hidden = keep, None
         outs, refs, state = [], [], None
         for start in range(0, wav.shape[1], 64000):
             chunk = wav[:, start:start + 64000].view(1, 1, -1)
@@ -582,14 +655,18 @@ def test_build_feature_chunks_of_any_length():
                 c, z, _ = model(chunk.cuda(), None)
             outs.append((c.float().cpu(), z.float().cpu()))
             zr = oc.encoder_forward(st, chunk).permute(0, 2, 1)
-            cr, state = oc.lstm_forward(st, zr, 1, state=state if keep else None)
+            if ar_mode == "LSTM":
+                cr, state = oc.lstm_forward(st, zr, 1, state=state if keep else None)
+            else:
+                cr = oc.transformer_ar_forward(st, zr, 1, args.sizeWindow // 160)
             refs.append((cr, zr))
         for (c, z), (cr, zr) in zip(outs, refs):
             assert c.shape == cr.shape and z.shape == zr.shape, (c.shape, cr.shape)
             assert (z - zr).abs().max() <= 3e-2 * zr.abs().max() + 1e-3
             assert (c - cr).abs().max() <= 3e-2 * cr.abs().max() + 1e-3
         assert sum(c.shape[1] for c, _ in outs) == 400 + 400 + 146  # floor arithmetic of the five strided convs
-    model.gAR.keepHidden, model.gAR.hidden = False, None
+    if ar_mode == "LSTM":
+        model.gAR.keepHidden, model.gAR.hidden = False, None
 
 
 @pytest.mark.gpu
@@ -617,3 +694,234 @@ def test_symmetric_allreduce_step_equals_nccl_step_on_two_gpus():
     assert lines["0"]["config"]["grad_allreduce"].startswith("NCCL")
     # rank 0's loss after the same 16 optimizer steps on the same batches (bf16 step, fp32 atomics order differs)
     assert abs(lines["0"]["loss_mean"] - lines["1"]["loss_mean"]) < 1e-2, (lines["0"]["loss_mean"], lines["1"]["loss_mean"])
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# public surface of the criterion (cpc/criterion/criterion.py:237-327) and of train.py that round 1 left untested
+# ------------------------------------------------------------------------------------------------------------------
+def _criterion_fixture(rnn="transformer", mode=None, B=4, S=32, D=64, Kp=4, NEG=16):
+    from cpc2_b200 import criterion as cr
+    torch.manual_seed(0)
+    crit = cr.CPCUnsupersivedCriterion(Kp, D, D, NEG, mode=mode, rnnMode=rnn, sizeInputSeq=S).cuda().eval()
+    g = torch.Generator().manual_seed(17)
+    c = torch.randn(B, S, D, generator=g)
+    z = torch.randn(B, S, D, generator=g)
+    return crit, c, z
+
+
+def test_sample_clean_matches_reference_semantics():
+    """sampleClean (criterion.py:237-286): K tensors [B, NEG+1, W, D] whose slot 0 is the positive z[:, k:k+W] and whose
+    other slots are z gathered at extIdx = ((seqIdx + t) mod S) + batchIdx*S, the two randint draws issued in the
+    reference's order -- redrawn here with the same seed on the same device and pushed through the ORACLE's integer
+    arithmetic (bit exact); labels are zeros."""
+    _need_gpu()
+    from oracle import cpc_oracle as oc
+    crit, c, z = _criterion_fixture("linear")
+    B, S, D = z.shape
+    Kp, NEG = crit.nPredicts, crit.negativeSamplingExt
+    W = S - Kp
+    zg = z.cuda()
+    torch.manual_seed(99)
+    outs, labels = crit.sampleClean(zg, W)
+    torch.manual_seed(99)
+    n = NEG * W * B
+    bi = torch.randint(low=0, high=B, size=(n,), device="cuda")
+    si = torch.randint(low=1, high=S, size=(n,), device="cuda")
+    ext = oc.negative_ext_index(bi.cpu(), si.cpu(), B, S, W, NEG)
+    assert len(outs) == Kp and labels.shape == (B * W,) and labels.dtype == torch.long and int(labels.abs().sum()) == 0
+    neg = z.view(-1, D)[ext].view(B, NEG, W, D)
+    for k in range(1, Kp + 1):
+        o = outs[k - 1].cpu()
+        assert o.shape == (B, NEG + 1, W, D)
+        assert torch.equal(o[:, 0], z[:, k:k + W])
+        assert torch.equal(o[:, 1:], neg)
+
+
+@pytest.mark.parametrize("rnn,mode", [("transformer", None), ("linear", "reverse"), ("ffd", None)])
+def test_get_prediction_and_cosine_distances_match_oracle(rnn, mode):
+    """getPrediction (criterion.py:291-302) -> K score tensors [B, NEG+1, W] + labels, and getCosineDistances
+    (:304-327) -> the positives' scores [B, 1, W], through PredictionNetwork.forward (:152-173, the materialised
+    `(locC[:, None] * candidates).mean(3)` path feature_loader.py:78-80 uses), against the oracle on the same sampled
+    indices; then the backward of PredictionNetwork.forward (_HeadsFn): gradients of a cross entropy over those scores
+    w.r.t. c and every head parameter against the oracle's autograd (cosine >= 0.99)."""
+    _need_gpu()
+    from oracle import cpc_oracle as oc
+    crit, c, z = _criterion_fixture(rnn, mode)
+    B, S, D = z.shape
+    Kp, NEG = crit.nPredicts, crit.negativeSamplingExt
+    W = S - Kp
+    torch.manual_seed(5)
+    bi, si = oc.draw_negative_indices(B, S, W, NEG)
+    ext = oc.negative_ext_index(bi, si, B, S, W, NEG)
+    crit.sampleIndices = lambda *a: ext.cuda()
+    cg = c.cuda().requires_grad_(True)
+    zg = z.cuda()
+    preds, labels = crit.getPrediction(cg, zg, None)
+    state = {k: v.detach().float().cpu() for k, v in crit.state_dict().items()}
+    params = {k: v.clone().requires_grad_(True) for k, v in state.items() if v.is_floating_point()}
+    full = dict(state)
+    full.update(params)
+    cr_ = c.clone().requires_grad_(True)
+    rl, ra, logits, _ = oc.criterion_forward(full, cr_, z, bi, si, Kp, NEG, rnn_mode=rnn, mode=mode, return_logits=True)
+    assert len(preds) == Kp and labels.shape == (B * W,)
+    scale = max(float(l.abs().max()) for l in logits)
+    for k in range(Kp):
+        got = preds[k].detach().cpu().permute(0, 2, 1).reshape(B * W, NEG + 1)  # criterion.py:346-348
+        assert preds[k].shape == (B, NEG + 1, W)
+        assert (got - logits[k].detach()).abs().max() <= 3e-2 * scale + 1e-3, k
+    # the reference's loss on top of the materialised scores, and its gradients through PredictionNetwork.forward
+    loss = sum(torch.nn.functional.cross_entropy(p_.permute(0, 2, 1).reshape(B * W, NEG + 1), labels) for p_ in preds)
+    loss.backward()
+    rl.sum().backward()
+    assert abs(float(loss) - float(rl.sum())) <= 2e-2
+    assert cosine(cg.grad.cpu(), cr_.grad) >= 0.99
+    for name, p_ in crit.named_parameters():
+        ref = params[name].grad
+        if ref is None or ref.abs().max() == 0:
+            continue
+        assert cosine(p_.grad.cpu(), ref) >= 0.99, (name, cosine(p_.grad.cpu(), ref))
+    with torch.no_grad():
+        cosd = crit.getCosineDistances(c.cuda(), zg)
+    assert len(cosd) == Kp
+    for k in range(Kp):
+        assert cosd[k].shape == (B, 1, W)
+        ref_pos = logits[k].detach()[:, 0].view(B, W)
+        assert (cosd[k][:, 0].cpu() - ref_pos).abs().max() <= 3e-2 * scale + 1e-3, k
+
+
+def test_train_step_entry_point():
+    """cpc2_b200.train.trainStep (cpc/train.py:72-142, unchanged signature): with a FusedAdam optimizer and an
+    unwrapped model the batch loop replays ONE CUDA graph per step (forward + backward + Adam); the ragged last batch of
+    the loader and the GRAPH_TRAIN_STEP = False switch take the eager body.  Both give the reference's `logs`
+    (per-prediction-step means over the batches, `iter`), advance the optimizer once per batch, step the scheduler
+    once per call, and agree with each other up to the different negative draws."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    g = torch.Generator().manual_seed(41)
+    loader = [(predictable_sequence(4, args.sizeWindow, 100 + i).pin_memory(), torch.zeros(4, dtype=torch.long))
+              for i in range(5)]
+    loader.append((predictable_sequence(3, args.sizeWindow, 200).pin_memory(), torch.zeros(3, dtype=torch.long)))
+    res = {}
+    for graphed in (True, False):
+        model, crit = build(args)
+        opt = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=1e-3)
+        sched = torch.optim.lr_scheduler.StepLR(opt, 1, gamma=0.5)
+        before = [p.detach().clone() for p in model.parameters()]
+        T.GRAPH_TRAIN_STEP = graphed
+        try:
+            torch.manual_seed(7)
+            logs = T.trainStep(loader, model, crit, opt, sched, loggingStep=2)
+            logs2 = T.trainStep(loader[:2], model, crit, opt, None, loggingStep=10)  # graph reused, lr halved
+        finally:
+            T.GRAPH_TRAIN_STEP = True
+        torch.cuda.synchronize()
+        assert logs["iter"] == 6 and logs2["iter"] == 2
+        assert logs["locLoss_train"].shape == (4,) and logs["locAcc_train"].shape == (4,)
+        assert all(v == v for v in logs["locLoss_train"]) and all(0 <= v <= 1 for v in logs["locAcc_train"])
+        assert float(opt._groups[0]["state"][0]) == 8
+        assert abs(opt.param_groups[0]["lr"] - 5e-4) < 1e-12 and abs(float(opt._groups[0]["state"][1]) - 5e-4) < 1e-12
+        assert model.training and crit.training
+        assert any((p.detach() - b).abs().max() > 0 for p, b in zip(model.parameters(), before))
+        assert len(T._GRAPHED.get(model, {})) == (2 if graphed else 0)  # one graph per batch shape (4 and the ragged 3)
+        res[graphed] = logs
+    assert abs(res[True]["locLoss_train"] - res[False]["locLoss_train"]).max() < 0.05
+
+
+def test_graphed_step_construction_has_no_side_effects():
+    """GraphedTrainStep(optimizer=FusedAdam) warms up with real optimizer steps on an all-zero batch before
+    the capture; parameters, Adam moments and the device step counter must come out of the constructor exactly as they
+    went in (a checkpoint-loaded model starts from its loaded state), and the first replay is update number 1."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    model, crit = build(args)
+    params = list(crit.parameters()) + list(model.parameters())
+    opt = FusedAdam(params, lr=1e-3)
+    before = [p.detach().clone() for p in params]
+    step = T.GraphedTrainStep(model, crit, 4, args.sizeWindow, warmup=3, optimizer=opt)
+    torch.cuda.synchronize()
+    for p, b in zip(params, before):
+        assert torch.equal(p.detach(), b)
+    g0 = opt._groups[0]
+    assert float(g0["state"][0]) == 0 and float(g0["m"].abs().max()) == 0 and float(g0["v"].abs().max()) == 0
+    step.step(predictable_sequence(4, args.sizeWindow, 3).cuda())
+    torch.cuda.synchronize()
+    assert float(g0["state"][0]) == 1
+    assert any((p.detach() - b).abs().max() > 0 for p, b in zip(params, before))
+    # Adam's first update moves every touched weight by ~lr: the warm-up steps really were rolled back
+    worst = max(float((p.detach() - b).abs().max()) for p, b in zip(params, before))
+    assert worst <= 1.01e-3, worst
+    step.close()
+    with pytest.raises(RuntimeError):
+        step.step()
+
+
+def test_multi_device_dataparallel_replicas_are_rejected():
+    """nn.DataParallel over several devices replicates the modules (replicas carry `_is_replica`); the engines
+    and arenas of this package are per process, so a replica's forward raises instead of launching on device-0 pointers
+    (device_ids=[0] never replicates and is covered by test_reference_wrappers_dataparallel_and_ddp)."""
+    _need_gpu()
+    from cpc2_b200 import train as T
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    model, crit = build(args)
+    x = torch.zeros(2, 1, 5120, device="cuda")
+    for mod, inp in ((model.gEncoder, (x,)), (model.gAR, (torch.zeros(2, 32, 64, device="cuda"),)),
+                     (crit, (torch.zeros(2, 32, 64, device="cuda"), torch.zeros(2, 32, 64, device="cuda"), None))):
+        mod._is_replica = True
+        try:
+            with pytest.raises(RuntimeError, match="DataParallel"):
+                mod(*inp)
+        finally:
+            del mod._is_replica
+
+
+def test_shape_limits_fail_with_a_message():
+    """B*S above the cpc_nce_bwd shared-memory row buffer and hidden sizes the recurrence kernels are not
+    built for are rejected in Python with the limit in the message (not by a CPC_ERR_UNSUPPORTED in the backward)."""
+    _need_gpu()
+    from cpc2_b200 import criterion as cr
+    from cpc2_b200 import model as M
+    crit = cr.CPCUnsupersivedCriterion(4, 64, 64, 16, rnnMode="linear", sizeInputSeq=128).cuda()
+    big = torch.zeros(51, 128, 64, device="cuda", requires_grad=True)
+    with pytest.raises(ValueError, match="6400"):
+        crit(big, big, None)
+    ar = M.CPCAR(64, 48, False, 1, mode="LSTM").cuda()
+    with pytest.raises(NotImplementedError, match="hidden sizes"):
+        ar(torch.zeros(2, 8, 64, device="cuda"))
+
+
+@pytest.mark.parametrize("S_in", [48, 70, 20])
+def test_transformer_layer_pads_ragged_sequences(S_in):
+    """cpc/transformers.py:38-50,69: sequences that are not a whole number of sizeSeq blocks are zero padded per
+    sequence, folded into the batch as independent causal blocks and cropped again.  TransformerLayer forward AND
+    backward on [N, S_in, d] with sizeSeq 32 against the oracle (which restates `prepare`)."""
+    _need_gpu()
+    from cpc2_b200 import transformers as tr
+    from oracle import cpc_oracle as oc
+    torch.manual_seed(0)
+    d = 256
+    layer = tr.TransformerLayer(sizeSeq=32, dmodel=d, dout=d, abspos=False).cuda().eval()
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(3, S_in, d, generator=g)
+    dy = torch.randn(3, S_in, d, generator=g)
+    xg = x.cuda().requires_grad_(True)
+    y = layer(xg)
+    y.backward(dy.cuda())
+    state = {"l." + k: v.detach().float().cpu() for k, v in layer.state_dict().items()}
+    params = {k: v.clone().requires_grad_(True) for k, v in state.items() if v.is_floating_point()}
+    full = dict(state)
+    full.update(params)
+    xr = x.clone().requires_grad_(True)
+    yr = oc.transformer_layer(full, xr, "l.", 32)
+    yr.backward(dy)
+    assert y.shape == yr.shape
+    assert (y.detach().cpu() - yr.detach()).abs().max() <= 3e-2 * float(yr.abs().max()) + 1e-3
+    assert cosine(xg.grad.cpu(), xr.grad) >= 0.99
+    for name, p_ in layer.named_parameters():
+        ref = params["l." + name].grad
+        if ref is None or ref.abs().max() == 0:
+            continue
+        assert cosine(p_.grad.cpu(), ref) >= 0.99, (name, cosine(p_.grad.cpu(), ref))
