@@ -1,20 +1,31 @@
-"""bench.py -- training throughput of the CPC2 hot path (forward + backward [+ gradient all-reduce]).
+"""bench.py -- training throughput of the CPC2 hot path (forward + backward [+ gradient all-reduce] + Adam).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--quick]
     (N > 1: launched by torchrun, one rank per GPU, NCCL)
 
 Metric (BASELINE.json): training audio-seconds per second = N * B * sizeWindow / 16000 / step_time on the CPC
 default config (encoder 256, 1-layer LSTM-256 AR, 12 transformer prediction heads, 128 negatives, window
 20480, dropout on), B = 8 windows per GPU (weak scaling), synthetic audio, bf16 operands / fp32 accumulation.
 
-Prints ONE JSON line (rank 0).  `value`: inputs resident in HBM, CUDA-event time per step summed over K steps,
-max over ranks, L2 flushed between steps.  `e2e`: the same step through the public API
-(cpc2_b200.train.GraphedTrainStep.pipelined) with a pinned HOST batch copied in and the losses / accuracies copied
-out and read by the host every step (batch i+1 in flight and result i-1 being read while replay i runs).
-`roofline`: the dominant kernel family of the step, timed per launch with CUDA events in a separate eager
-pass behind a GPU-side delay (so host launch latency is not measured).  `cpu_baseline`: the CPU oracle
-(oracle/cpc_oracle.py, the restatement of the reference pinned by tests/golden) on the host cores.
-`--impl reference` times that CPU implementation alone with the same metric.
+Prints ONE JSON line (rank 0).
+  value         inputs resident in HBM, CUDA-event time per step summed over K steps, max over ranks, L2 flushed
+                between steps.
+  e2e           the same step through the public API (cpc2_b200.train.GraphedTrainStep.pipelined) with a pinned HOST
+                batch copied in and the losses / accuracies copied out and read by the host every step.
+  roofline      the dominant kernel family of the step, timed per launch with CUDA events in a separate eager pass
+                behind a GPU-side delay; `achieved` on ALGORITHMIC FLOPs (the all-pairs logits products count
+                2*T*(NEG+1)*D*K, not the executed 2*T*(B*S)*D*K).
+  cpu_baseline  the reference's own training step on the host cores: the UNMODIFIED reference modules imported from
+                oracle/_ref/cpc_reference.zip (kind "reference"; packed by build() from /root/reference) or, when that
+                archive is absent, the CPU oracle port (kind "port").
+  configs       (timed AFTER the headline region, so `value` is untouched) BASELINE.json configs[2..4]:
+                transformer AR, hidden 512 / 2-layer LSTM / window 40960, and the criterion-only sweep corners.
+  dropin        cpc2_b200.train.trainStep (the reference's entry point, cpc/train.py:72-142) over a 20-batch loader,
+                host-timed: with FusedAdam (one CUDA-graph replay per batch) and with torch.optim.Adam (eager).
+  stock_gpu     the UNMODIFIED reference modules on the same B200 (eager PyTorch: cuDNN + cuBLAS), fp32/TF32 and under
+                torch.autocast(bfloat16), same batch -- the stock kernels this build replaces.
+  replica_param_max_abs_diff (N > 1)  max |parameter - rank 0's parameter| over all ranks after the timed loop.
+`--impl reference` times the reference CPU implementation alone with the same metric.
 """
 import argparse
 import json
@@ -97,7 +108,21 @@ def synthetic_batch(B, W, rank):
         0.1 * torch.randn(B, 2, 1, W, generator=g)
 
 
-def cpu_step_seconds(args, B, steps, warmup):
+# ------------------------------------------------------------------------------------------------------ CPU arms
+def reference_available():
+    from oracle import ref_harness as rh
+    return rh.reference_location() is not None
+
+
+def cpu_reference_seconds(over, B, steps, warmup):
+    """The UNMODIFIED reference's batch-loop body (cpc/train.py:95-109, train mode) on all host threads."""
+    from oracle import ref_harness as rh
+    torch.set_num_threads(os.cpu_count())
+    sec, loss, _ = rh.timed_reference_steps(over, B, steps, warmup, device="cpu")
+    return sec, torch.get_num_threads()
+
+
+def cpu_port_seconds(args, B, steps, warmup):
     """The CPU oracle's training step (fwd + bwd) on all host threads; returns (seconds per step, threads)."""
     from cpc2_b200 import train as T
     from oracle import cpc_oracle as oc
@@ -120,52 +145,72 @@ def cpu_step_seconds(args, B, steps, warmup):
     return sum(times) / len(times), torch.get_num_threads()
 
 
+def cpu_baseline(args, B, steps, warmup):
+    """-> dict for the `cpu_baseline` key: the reference itself when its archive travelled, else the oracle port."""
+    W = args.sizeWindow
+    if reference_available():
+        sec, threads = cpu_reference_seconds({}, B, steps, warmup)
+        kind, what = "reference", "unmodified reference modules (oracle/_ref/cpc_reference.zip), train mode, fp32"
+    else:
+        sec, threads = cpu_port_seconds(args, B, steps, warmup)
+        kind, what = "port", "oracle/cpc_oracle.py, fp32"
+    return {"value": B * W / SAMPLE_RATE / sec, "unit": "audio-s/s", "cores": threads, "kind": kind,
+            "sample": f"{steps} full fwd+bwd steps of the same batch ({B} x {W} samples) after {warmup} warm-up, {what}, "
+                      f"{threads} threads, {sec:.2f} s/step"}
+
+
 def run_reference(opt, out):
-    """--impl reference: the reference algorithm's CPU implementation (oracle port) with every host thread."""
+    """--impl reference: the reference's CPU implementation of the step with every host thread."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from cpc2_b200 import train as T
     args = T.defaultArgs()
     B = 8
+    ref = reference_available()
+    timer = (lambda b, k, w: cpu_reference_seconds({}, b, k, w)) if ref else (lambda b, k, w: cpu_port_seconds(args, b, k, w))
     # bound the run: probe one step, shrink the per-step sample if K+W full steps would take too long
-    probe, threads = cpu_step_seconds(args, B, 1, 0)
+    probe, threads = timer(B, 1, 0)
     if probe * (opt.steps + opt.warmup) > 240:
         B = 2
-    sec, threads = cpu_step_seconds(args, B, opt.steps, opt.warmup)
+    sec, threads = timer(B, opt.steps, opt.warmup)
     value = B * args.sizeWindow / SAMPLE_RATE / sec
-    sample = f"{opt.steps} full fwd+bwd steps of batch {B} x {args.sizeWindow} samples (oracle port, fp32, {threads} threads)"
+    what = "unmodified reference, train mode" if ref else "oracle port"
+    sample = f"{opt.steps} full fwd+bwd steps of batch {B} x {args.sizeWindow} samples ({what}, fp32, {threads} threads)"
     line = {
         "impl": "reference", "metric": "train_audio_sec_per_sec", "value": value, "unit": "audio-s/s",
         "n_gpus": opt.gpus, "steps": opt.steps, "warmup": opt.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD.replace("batch 8 per GPU", f"batch {B} on the host CPU"), "global_batch": B},
-        "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": threads, "kind": "reference" if ref else "port",
+                         "sample": sample},
         "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     out.emit(json.dumps(line))
 
 
-def kernel_profile(model, crit, seq, label):
+# ------------------------------------------------------------------------------------------------------ GPU arm
+def kernel_profile(fwd_bwd, params):
     """One eager forward+backward with a CUDA-event pair around every C-ABI launch.  A GPU-side delay is queued
     first so the launches pile up behind it and the events bracket kernel time, not host launch latency."""
     from cpc2_b200 import kernels as K
-    from cpc2_b200 import train as T
-    for p in list(model.parameters()) + list(crit.parameters()):
+    for p in params:
         p.grad = None
-    T.forwardBackward(model, crit, seq, label)  # allocator warm-up at these shapes
-    for p in list(model.parameters()) + list(crit.parameters()):
+    fwd_bwd()  # allocator warm-up at these shapes
+    for p in params:
         p.grad = None
     torch.cuda.synchronize()
     K.PROFILE = []
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda._sleep(int(60e6))  # ~30-40 ms of GPU-side delay
     t0.record()
-    T.forwardBackward(model, crit, seq, label)
+    fwd_bwd()
     t1.record()
     torch.cuda.synchronize()
     prof, K.PROFILE = K.PROFILE, None
+    for p in params:
+        p.grad = None
     rows = {}
     for name, work, e0, e1 in prof:
         r = rows.setdefault(name, dict(name=name, launches=0, ms=0.0, flops=0.0, bytes=0.0, kind=work.get("kind", "hbm")))
@@ -176,149 +221,395 @@ def kernel_profile(model, crit, seq, label):
     return sorted(rows.values(), key=lambda r: -r["ms"]), t0.elapsed_time(t1), prof
 
 
-def run_ours(opt, out):
-    import torch.distributed as dist
-    from cpc2_b200 import _lib
-    from cpc2_b200 import kernels as K
+def roofline_of(rows, pk):
+    total = sum(r["ms"] for r in rows)
+    top = rows[0]
+    if top["kind"] == "hbm":
+        ach = top["bytes"] / (top["ms"] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
+    else:  # tensor, or the latency-bound recurrence reported against the tensor peak as SURVEY 8d asks
+        ach = top["flops"] / (top["ms"] * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"]}
+        if top["kind"] != "tensor":
+            roof["note"] = f"{top['kind']}-bound kernel; see DESIGN.md"
+    roof.update({"kernel": top["name"], "launches_per_step": top["launches"], "share_of_kernel_time": top["ms"] / total,
+                 "avg_launch_us": 1e3 * top["ms"] / top["launches"], "flops_counted": "algorithmic",
+                 "peak_source": pk["source"]})
+    return roof, total
+
+
+def kernel_table(rows, total):
+    return [{"name": r["name"], "launches": r["launches"], "us": round(1e3 * r["ms"], 1), "share": round(r["ms"] / total, 4),
+             "tflops": round(r["flops"] / (r["ms"] * 1e-3) / 1e12, 1) if r["flops"] else None,
+             "gbs": round(r["bytes"] / (r["ms"] * 1e-3) / 1e9, 1) if r["bytes"] else None, "kind": r["kind"]}
+            for r in rows]
+
+
+class Ctx:
+    """Process-wide facts of this bench run."""
+
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        # gradient arenas in NVSwitch-multicast symmetric memory + cpc_allreduce_mc when the box supports it
+        # (CPC_SYMMETRIC=0: NCCL all-reduce; =1: fail instead of falling back to NCCL)
+        self.sym = {"0": False, "1": True}.get(os.environ.get("CPC_SYMMETRIC", "auto"), "auto")
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, *vals):
+        if self.world == 1:
+            return list(vals)
+        t = torch.tensor(vals, device=self.dev, dtype=torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+
+class TrainRig:
+    """Model + criterion + data-parallel buckets + fused Adam + the captured step, for one configuration."""
+
+    def __init__(self, ctx, args, B):
+        from cpc2_b200 import kernels as K
+        from cpc2_b200 import train as T
+        from cpc2_b200.dp import BucketedAllReduce
+        from cpc2_b200.optim import FusedAdam
+        self.ctx, self.args, self.B = ctx, args, B
+        torch.manual_seed(0)
+        model, crit = T.buildModelAndCriterion(args)
+        self.model, self.crit = model.to(ctx.dev), crit.to(ctx.dev)
+        torch.manual_seed(4321 + ctx.rank)  # every rank draws its own negatives, as in the reference
+        self.dp = BucketedAllReduce(self.model, self.crit, symmetric=ctx.sym)
+        self.dp.broadcast_parameters()
+        if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1":  # diagnosis only (the printed line says so)
+            self.dp._all_reduce_mean = lambda t: None
+        n0 = K.LAUNCHES
+        self.adam = FusedAdam(list(self.crit.parameters()) + list(self.model.parameters()), lr=args.learningRate,
+                              betas=(args.beta1, args.beta2), eps=args.epsilon)  # cpc/train.py:472-479
+        self.adam.attach(self.dp if ctx.world > 1 else None)  # each bucket is stepped as soon as it is (all-)reduced
+        self.step = T.GraphedTrainStep(self.model, self.crit, B, args.sizeWindow, device=ctx.dev, warmup=3,
+                                       train_mode=True, after_backward=self.dp.finish, optimizer=self.adam)
+        self.launches_per_step = (K.LAUNCHES - n0) // 4  # 3 eager warm-up passes + 1 capture pass
+        self.host_seq = synthetic_batch(B, args.sizeWindow, ctx.rank)
+        self.step.static_seq.copy_(self.host_seq)
+
+    def timed(self, steps, warmup, clocks=False):
+        ctx = self.ctx
+        for _ in range(max(warmup, 3)):
+            self.step.step()
+        ctx.barrier()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        sampler = ClockSampler(ctx.local) if clocks else None
+        if sampler is not None:
+            sampler.__enter__()
+        ctx.barrier()
+        for e0, e1 in evs:
+            ctx.flush.zero_()
+            e0.record()
+            self.step.step()
+            e1.record()
+        ctx.barrier()
+        if sampler is not None:
+            sampler.__exit__()
+        return sum(e0.elapsed_time(e1) for e0, e1 in evs), sampler
+
+    def profile(self):
+        from cpc2_b200 import train as T
+        params = list(self.model.parameters()) + list(self.crit.parameters())
+        return kernel_profile(lambda: T.forwardBackward(self.model, self.crit, self.step.static_seq, self.step.static_label),
+                              params)
+
+    def close(self):
+        self.step.close()
+        self.adam.detach()
+        self.dp.remove()
+
+
+def measure_extra_config(ctx, name, over, B, steps, pk):
+    """One of BASELINE.json configs[2..3] through the same rig as the headline: ms/step, audio-s/s, dominant kernel."""
     from cpc2_b200 import train as T
+    args = T.defaultArgs(**over)
+    rig = TrainRig(ctx, args, B)
+    try:
+        ms_total, _ = rig.timed(steps, 3)
+        (ms_total,) = ctx.max_over_ranks(ms_total)
+        audio_s = ctx.world * B * args.sizeWindow / SAMPLE_RATE
+        res = {"workload": name, "batch_per_gpu": B, "sizeWindow": args.sizeWindow, "steps": steps,
+               "ms_per_step": ms_total / steps, "value": audio_s * steps / (ms_total * 1e-3), "unit": "audio-s/s",
+               "gpu_launches_per_step": rig.launches_per_step,
+               "params": sum(p.numel() for p in list(rig.model.parameters()) + list(rig.crit.parameters()))}
+        if ctx.world == 1:
+            rows, _, _ = rig.profile()
+            roof, total = roofline_of(rows, pk)
+            res["roofline"] = roof
+            res["kernel_time_sum_ms"] = total
+            res["kernels"] = kernel_table(rows, total)[:8]
+        return res
+    finally:
+        rig.close()
+
+
+def criterion_sweep(ctx, steps, pk, quick):
+    """BASELINE.json configs[4]: CPCUnsupersivedCriterion forward + backward (+ the heads' gradient all-reduce and
+    their fused Adam update) alone, on random c, z ~ N(0,1) [8, 128, 256] per GPU, as one CUDA-graph replay per step."""
+    from cpc2_b200 import criterion as cr
+    from cpc2_b200 import kernels as K
     from cpc2_b200.dp import BucketedAllReduce
+    from cpc2_b200.optim import FusedAdam
+    B, S, D = 8, 128, 256
+    corners = [(32, 4), (128, 12), (1024, 24)] if quick else [(n, k) for n in (32, 128, 1024) for k in (4, 12, 24)]
+    out = []
+    for rnn in ("transformer", "linear"):
+        for NEG, Kp in corners:
+            torch.manual_seed(0)
+            crit = cr.CPCUnsupersivedCriterion(Kp, D, D, NEG, rnnMode=rnn, sizeInputSeq=S).to(ctx.dev).train()
+            g = torch.Generator().manual_seed(17 + ctx.rank)
+            c = torch.randn(B, S, D, generator=g).to(ctx.dev).requires_grad_(True)
+            z = torch.randn(B, S, D, generator=g).to(ctx.dev).requires_grad_(True)
+            label = torch.zeros(B, dtype=torch.long, device=ctx.dev)
+            dp = BucketedAllReduce(None, crit, symmetric=ctx.sym)
+            dp.broadcast_parameters()
+            adam = FusedAdam(list(crit.parameters()), lr=2e-4)
+            adam.attach(dp if ctx.world > 1 else None)
+            params = list(crit.parameters())
+
+            def body():
+                for p in params:
+                    p.grad = None
+                c.grad = z.grad = None
+                crit.wPrediction.prefetch()
+                losses, acc = crit(c, z, label, None)
+                losses.sum().backward()
+                dp.finish()
+                adam.step()
+                return losses
+
+            n0 = K.LAUNCHES
+            snap_p = [p.detach().clone() for p in params]
+            snap_o = adam.snapshot()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    body()
+                with torch.no_grad():
+                    for p, q in zip(params, snap_p):
+                        p.copy_(q)
+                    adam.restore(snap_o)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            for p in params:
+                p.grad = None
+            with torch.cuda.graph(graph):
+                losses = body()
+            launches = (K.LAUNCHES - n0) // 4
+            for _ in range(3):
+                graph.replay()
+            ctx.barrier()
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            for e0, e1 in evs:
+                ctx.flush.zero_()
+                e0.record()
+                graph.replay()
+                e1.record()
+            ctx.barrier()
+            (ms,) = ctx.max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in evs))
+            W = S - Kp
+            algo = 3 * 2.0 * B * W * (NEG + 1) * D * Kp  # logits fwd + its two backward products
+            out.append({"rnnMode": rnn, "negatives": NEG, "nPredicts": Kp, "us_per_step": round(1e3 * ms / steps, 1),
+                        "windows_per_s": round(ctx.world * B * steps / (ms * 1e-3), 1),
+                        "logit_algorithmic_gflop": round(algo / 1e9, 3), "gpu_launches_per_step": launches,
+                        "loss_mean": round(float(losses.detach().mean()), 4),
+                        "head_params": sum(p.numel() for p in params)})
+            torch.cuda.synchronize()
+            graph.reset()
+            del graph
+            adam.detach()
+            dp.remove()
+    return {"shape": "c, z ~ N(0,1) [8, 128, 256] per GPU; step = criterion fwd + bwd + heads' all-reduce + fused Adam, "
+                     "one CUDA-graph replay, L2 flushed between steps", "n_gpus": ctx.world, "cases": out}
+
+
+def dropin_numbers(ctx, args, B, n_batches):
+    """cpc2_b200.train.trainStep -- the reference's own entry point (cpc/train.py:72-142) -- over a synthetic loader,
+    timed on the HOST clock around the call (H2D of every batch and the log read-back included)."""
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    W = args.sizeWindow
+    distinct = [synthetic_batch(B, W, 100 + i) for i in range(4)]
+    label = torch.zeros(B, dtype=torch.long)
+    loader = [(distinct[i % 4], label) for i in range(n_batches)]
+    res = {}
+    for key, make in (("trainStep_fused_adam_graph", lambda ps: FusedAdam(ps, lr=args.learningRate)),
+                      ("trainStep_torch_adam_eager", lambda ps: torch.optim.Adam(ps, lr=args.learningRate))):
+        torch.manual_seed(0)
+        model, crit = T.buildModelAndCriterion(args)
+        model, crit = model.to(ctx.dev), crit.to(ctx.dev)
+        opt = make(list(crit.parameters()) + list(model.parameters()))
+        T.trainStep(loader[:3], model, crit, opt, None, 10 ** 9)  # warm-up (captures the graph on the fused path)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        logs = T.trainStep(loader, model, crit, opt, None, 10 ** 9)
+        torch.cuda.synchronize()
+        sec = time.perf_counter() - t0
+        res[key] = {"value": n_batches * B * W / SAMPLE_RATE / sec, "unit": "audio-s/s", "ms_per_batch": 1e3 * sec / n_batches,
+                    "batches": n_batches, "loss_mean": float(logs["locLoss_train"].mean()),
+                    "graph_replay": len(T._GRAPHED.get(model, {})) > 0}
+        for r in T._GRAPHED.pop(model, {}).values():
+            r.close()
+    return res
+
+
+def stock_gpu_numbers(ctx, B, steps):
+    """The UNMODIFIED reference modules (eager PyTorch on cuDNN / cuBLAS) on this GPU, same batch shape, train mode."""
+    from oracle import ref_harness as rh
+    if rh.reference_location() is None:
+        return {"unavailable": "oracle/_ref/cpc_reference.zip not packed (python oracle/make_ref.py in the build container)"}
+    res = {}
+    for key, ac, tf32 in (("fp32_tf32", None, True), ("autocast_bf16", torch.bfloat16, True), ("fp32_strict", None, False)):
+        try:
+            sec, loss, wall = rh.timed_reference_steps({}, B, steps, 3, device=str(ctx.dev), autocast=ac, tf32=tf32)
+            res[key] = {"value": B * 20480 / SAMPLE_RATE / wall, "unit": "audio-s/s", "ms_per_step_wall": 1e3 * wall,
+                        "ms_per_step_gpu": 1e3 * sec, "loss_mean": loss}
+        except Exception as e:  # a stock path that does not run under autocast is a fact worth recording
+            res[key] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = True
+    res["what"] = ("cpc/train.py:95-109 on the reference's own modules, eager, fwd + bwd only (no optimizer), host wall "
+                   "clock per step with a final synchronize; value = audio-s/s of that")
+    return res
+
+
+def replica_check(ctx, rigs_params):
+    """max over ranks and parameters of |p - p on rank 0| (must be 0.0: replicas stay bit-identical)."""
+    flat = torch.cat([p.detach().reshape(-1) for p in rigs_params])
+    ref = flat.clone()
+    ctx.dist.broadcast(ref, 0)
+    d = (flat - ref).abs().max().to(torch.float64)
+    ctx.dist.all_reduce(d, op=ctx.dist.ReduceOp.MAX)
+    return float(d)
+
+
+def run_ours(opt, out):
+    from cpc2_b200 import _lib
+    from cpc2_b200 import train as T
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a B200; there is no CPU fallback for the product path")
     if _lib.needs_build():
         _lib.build()
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    ctx = Ctx()
+    world, rank = ctx.world, ctx.rank
     args = T.defaultArgs()
     B, W = args.batchSizeGPU, args.sizeWindow
-    torch.manual_seed(0)
-    model, crit = T.buildModelAndCriterion(args)
-    model, crit = model.to(dev), crit.to(dev)
-    torch.manual_seed(4321 + rank)  # every rank draws its own negatives, as in the reference
-    # gradient arenas in NVSwitch-multicast symmetric memory + cpc_allreduce_mc when the box supports it
-    # (CPC_SYMMETRIC=0: NCCL all-reduce; =1: fail instead of falling back to NCCL)
-    sym = {"0": False, "1": True}.get(os.environ.get("CPC_SYMMETRIC", "auto"), "auto")
-    dp = BucketedAllReduce(model, crit, symmetric=sym)
-    dp.broadcast_parameters()
-    if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1":  # diagnosis only (the printed line says so): what the step
-        dp._all_reduce_mean = lambda t: None            # costs at N ranks without the collective
-    host_seq = synthetic_batch(B, W, rank)
+    rig = TrainRig(ctx, args, B)
     host_out = torch.empty(2, args.nPredicts).pin_memory()
-
-    # launches per step, counted while the step is captured into the graph
-    n0 = K.LAUNCHES
-    from cpc2_b200.optim import FusedAdam
-    adam = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=args.learningRate,
-                    betas=(args.beta1, args.beta2), eps=args.epsilon)  # cpc/train.py:472-479
-    adam.attach(dp if world > 1 else None)  # each bucket is stepped as soon as it is (all-)reduced
-    step = T.GraphedTrainStep(model, crit, B, W, device=dev, warmup=3, train_mode=True, after_backward=dp.finish,
-                              optimizer=adam)
-    launches_per_step = (K.LAUNCHES - n0) // 4  # 3 eager warm-up passes + 1 capture pass
-    step.static_seq.copy_(host_seq)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(opt.warmup, 3)):
-        step.step()
-    barrier()
     # ---- value: inputs resident in HBM, per-step CUDA events, L2 flushed between steps
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(opt.steps)]
-    with ClockSampler(local) as clocks:
-        barrier()
-        for e0, e1 in evs:
-            flush.zero_()
-            e0.record()
-            step.step()
-            e1.record()
-        barrier()
-    ms_total = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+    ms_total, clocks = rig.timed(opt.steps, opt.warmup, clocks=True)
     # ---- e2e: pinned host batch in, losses out, every step, through the public API
-    barrier()
+    ctx.barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     n_read = 0
-    for losses_h, acc_h in step.pipelined(host_seq for _ in range(opt.steps)):
+    for losses_h, acc_h in rig.step.pipelined(rig.host_seq for _ in range(opt.steps)):
         host_out[0].copy_(losses_h)  # the caller consumes every step's losses / accuracies on the host
         host_out[1].copy_(acc_h)     # (train.py:121-122), one step behind the GPU
         n_read += 1
     assert n_read == opt.steps
     t1.record()
-    barrier()
+    ctx.barrier()
     ms_e2e = t0.elapsed_time(t1)
-    if world > 1:
-        t = torch.tensor([ms_total, ms_e2e], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, ms_e2e = t.tolist()
+    ms_total, ms_e2e = ctx.max_over_ranks(ms_total, ms_e2e)
     loss_now = float(host_out[0].mean())
     audio_s = world * B * W / SAMPLE_RATE
-    value = audio_s * opt.steps / (ms_total * 1e-3)
-    e2e = audio_s * opt.steps / (ms_e2e * 1e-3)
+    dp = rig.dp
     line = {
-        "metric": "train_audio_sec_per_sec", "value": value, "unit": "audio-s/s", "n_gpus": world,
-        "steps": opt.steps, "warmup": max(opt.warmup, 3), "ms_per_step": ms_total / opt.steps,
+        "metric": "train_audio_sec_per_sec", "value": audio_s * opt.steps / (ms_total * 1e-3), "unit": "audio-s/s",
+        "n_gpus": world, "steps": opt.steps, "warmup": max(opt.warmup, 3), "ms_per_step": ms_total / opt.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2_flush_between_steps": True, "cuda_graph": True, "dropout": "train mode (p=0.1 in the heads)",
+                   "programmatic_dependent_launch": os.environ.get("CPC_PDL", "1") != "0",
                    "optimizer": "fused multi-tensor Adam (cpc_adam_step) inside the timed step, per bucket after its all-reduce",
                    "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0,
                    "grad_allreduce": ("none" if world == 1 else "cpc_allreduce_mc (NVSwitch multimem, in place)"
                                       if dp.symmetric is not None else "NCCL all-reduce (AVG)"),
                    **({"DIAGNOSTIC": "all-reduce skipped, not a valid number"}
                       if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1" else {})},
-        "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": host_seq.numel() * 4,
-                "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": ms_e2e / opt.steps},
-        "gpu_launches": launches_per_step * opt.steps, "gpu_launches_per_step": launches_per_step,
+        "e2e": {"value": audio_s * opt.steps / (ms_e2e * 1e-3), "unit": "audio-s/s",
+                "h2d_bytes_per_step": rig.host_seq.numel() * 4, "d2h_bytes_per_step": host_out.numel() * 4,
+                "ms_per_step": ms_e2e / opt.steps},
+        "gpu_launches": rig.launches_per_step * opt.steps, "gpu_launches_per_step": rig.launches_per_step,
         "clocks": clocks.summary(), "loss_mean": loss_now,
     }
-    if rank == 0 and world == 1:
-        pk = peaks()
-        rows, eager_ms, _ = kernel_profile(model, crit, step.static_seq, step.static_label)
-        total = sum(r["ms"] for r in rows)
-        top = rows[0]
-        if top["kind"] == "tensor":
-            ach = top["flops"] / (top["ms"] * 1e-3) / 1e12
-            roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"]}
-        elif top["kind"] == "hbm":
-            ach = top["bytes"] / (top["ms"] * 1e-3) / 1e9
-            roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
-        else:  # latency-bound recurrence / CUDA-core attention: reported against the tensor peak as SURVEY 8d asks
-            ach = top["flops"] / (top["ms"] * 1e-3) / 1e12
-            roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"],
-                    "note": f"{top['kind']}-bound kernel; see DESIGN.md"}
-        roof.update({"kernel": top["name"], "launches_per_step": top["launches"], "share_of_kernel_time": top["ms"] / total,
-                     "avg_launch_us": 1e3 * top["ms"] / top["launches"], "traffic": traffic_of(top["name"]),
-                     "traffic_unit": "bytes per launch (ncu dram read+write, profiles/traffic.json)",
-                     "peak_source": pk["source"]})
+    if world > 1:
+        line["replica_param_max_abs_diff"] = replica_check(
+            ctx, list(rig.crit.parameters()) + list(rig.model.parameters()))
+    pk = peaks()
+    if world == 1:
+        rows, eager_ms, _ = rig.profile()
+        roof, total = roofline_of(rows, pk)
+        roof.update({"traffic": traffic_of(roof["kernel"]),
+                     "traffic_unit": "bytes per launch (ncu dram read+write, profiles/traffic.json)"})
         line["roofline"] = roof
-        line["kernels"] = [
-            {"name": r["name"], "launches": r["launches"], "us": round(1e3 * r["ms"], 1), "share": round(r["ms"] / total, 4),
-             "tflops": round(r["flops"] / (r["ms"] * 1e-3) / 1e12, 1) if r["flops"] else None,
-             "gbs": round(r["bytes"] / (r["ms"] * 1e-3) / 1e9, 1) if r["bytes"] else None, "kind": r["kind"]}
-            for r in rows]
+        line["kernels"] = kernel_table(rows, total)
         line["kernel_time_sum_ms"] = total
-        sec, threads = cpu_step_seconds(args, B, 2, 1)
-        line["cpu_baseline"] = {"value": B * W / SAMPLE_RATE / sec, "unit": "audio-s/s", "cores": threads, "kind": "port",
-                                "sample": f"2 full fwd+bwd steps of the same batch (8 x 20480 samples) after 1 warm-up, "
-                                          f"oracle/cpc_oracle.py fp32, {threads} threads, {sec:.2f} s/step"}
+    rig.close()
+    del rig
+    torch.cuda.empty_cache()
+
+    # ---- everything below is timed AFTER the headline region and never touches `value`
+    extra_steps = 5 if opt.quick else 10
+
+    def guarded(fn, *a):
+        try:
+            return fn(*a)
+        except Exception as e:  # the headline line must survive a failing extra
+            if world > 1:
+                raise  # (ranks must stay in lock step: fail loudly instead of desynchronising the collectives)
+            return {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+
+    configs = {}
+    configs["config3_transformer_ar"] = guarded(
+        measure_extra_config, ctx, "CPC with transformer AR (1 layer, sizeSeq 128, rel-pos; feature_loader.py:216-220), "
+        "transformer heads, samespeaker batches (identical criterion), batch 8 per GPU",
+        dict(arMode="transformer"), 8, extra_steps, pk)
+    torch.cuda.empty_cache()
+    configs["config4_hidden512_lstm2_w40960"] = guarded(
+        measure_extra_config, ctx, "CPC hidden 512, 2-layer LSTM AR, sizeWindow 40960, transformer heads, batch 8 per GPU",
+        dict(hiddenEncoder=512, hiddenGar=512, nLevelsGRU=2, sizeWindow=40960), 8, extra_steps, pk)
+    torch.cuda.empty_cache()
+    configs["config5_criterion_sweep"] = guarded(criterion_sweep, ctx, extra_steps, pk, opt.quick)
+    torch.cuda.empty_cache()
+    line["configs"] = configs
+    if rank == 0 and world == 1:
+        line["dropin"] = guarded(dropin_numbers, ctx, args, B, 20)
+        torch.cuda.empty_cache()
+        line["stock_gpu"] = guarded(stock_gpu_numbers, ctx, B, 5 if opt.quick else 10)
+        torch.cuda.empty_cache()
+        line["cpu_baseline"] = guarded(cpu_baseline, args, B, 2, 1)
     if rank == 0:
         out.emit(json.dumps(line))
     if world > 1:
-        # The step's CUDA graph holds captured NCCL launches; tearing the communicator down while the graph is
-        # alive blocks inside ncclCommDestroy (observed at N=2: JSON printed, process never exited).  All ranks
-        # meet once more, the graph is dropped, and the process leaves without the communicator teardown.
-        barrier()
-        del step
+        # every captured graph (they hold NCCL launches) has been closed above, so the communicator can be torn down
+        # normally; a watchdog turns a teardown that still blocks into a clean exit instead of a hung job
+        ctx.barrier()
         sys.stdout.flush()
         sys.stderr.flush()
-        os._exit(0)
+        dog = threading.Timer(60.0, lambda: os._exit(0))
+        dog.daemon = True
+        dog.start()
+        ctx.dist.destroy_process_group()
 
 
 class StdoutToStderr:
@@ -341,6 +632,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="fewer steps / sweep corners in the extra sections")
     opt = ap.parse_args()
     out = StdoutToStderr()
     if opt.impl == "reference":

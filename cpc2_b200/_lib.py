@@ -192,7 +192,7 @@ class AdamSpan(ctypes.Structure):
 
 # every symbol include/cpc_b200.h declares (checked by tests/test_abi.py)
 EXPORTED = [
-    "cpc_strerror", "cpc_version", "cpc_device_arch", "cpc_gemm_bf16", "cpc_rownorm_fwd", "cpc_rownorm_bwd",
+    "cpc_strerror", "cpc_version", "cpc_device_arch", "cpc_set_pdl", "cpc_gemm_bf16", "cpc_rownorm_fwd", "cpc_rownorm_bwd",
     "cpc_conv0_cn_relu_fwd", "cpc_conv0_cn_relu_bwd", "cpc_conv_weight_pack", "cpc_conv_wgrad_unpack",
     "cpc_cast_f32_to_bf16", "cpc_cast_bf16_to_f32", "cpc_colsum", "cpc_groupsum", "cpc_neg_ext_index",
     "cpc_nce_fwd", "cpc_nce_bwd", "cpc_lstm_fwd", "cpc_lstm_bwd", "cpc_attn_fwd", "cpc_attn_bwd",

@@ -554,13 +554,17 @@ class _CriterionFn(torch.autograd.Function):
             ctx.pred_drop = (ops.DropoutState.next(dev), drop_pred)
             K.dropout_(preds, ctx.pred_drop[0], 7, drop_pred)
         logits = torch.empty(Kp, T, BS, device=dev)
-        ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D)
+        # (algorithmic work of the logits: 2 T (NEG+1) D per prediction step -- SURVEY 8d -- the all-pairs product
+        # executes 2 T (B S) D)
+        algo = 2.0 * T * (NEG + 1) * D * Kp
+        ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D, algo_flops=algo)
         lse = torch.empty(Kp, T, device=dev)
         loss_sum, hits = torch.zeros(2, Kp, device=dev).unbind(0)  # (one memset)
         K.nce_fwd(logits, ext, weights, lse, loss_sum, hits, Kp, B, W, S, NEG, BS)
         ctx.eng, ctx.saved = eng, saved
         ctx.t = (preds, zb, logits, lse, ext, weights)
         ctx.dims = (B, S, H, D, W, Kp, NEG)
+        ctx.algo = algo
         losses = (loss_sum / T).view(1, Kp)
         acc = (hits / (W * B)).view(1, Kp)
         ctx.mark_non_differentiable(acc)
@@ -589,14 +593,14 @@ class _CriterionFn(torch.autograd.Function):
             for part in range(2):
                 A = K.View(dlog[part], BS, T, Kp, BS, T * BS, major=1, gmul=0)
                 K.gemm(A, Bv, BS, D, Kp * T, k_per_slab=T, k_splits=ops.auto_splits(BS, D, Kp * T, 1, T), out_f32=dz,
-                       accumulate=True, alpha=1.0 / D)
+                       accumulate=True, alpha=1.0 / D, algo_flops=ctx.algo / 2)
             # dz is complete here, long before the heads' backward below: an encoder backward that runs on its
             # own side stream (the future half of CPCModel.forwardPastFuture) may start from this event
             ops._READY.clear()
             ops.set_ready(dz, ops.mark())
         for part in range(2):
             K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
-                   accumulate=part > 0)
+                   accumulate=part > 0, algo_flops=ctx.algo / 2)
         if ctx.pred_drop is not None:
             K.dropout_(dpred, ctx.pred_drop[0], 7, ctx.pred_drop[1])
         if type(eng) is TransformerStack and ops.early_ffn():

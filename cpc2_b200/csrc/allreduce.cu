@@ -50,6 +50,7 @@ __device__ __forceinline__ void block_barrier(uint32_t* const* pads, int rank, i
 __global__ void __launch_bounds__(AR_THREADS) allreduce_mc_kernel(float* __restrict__ mc, long long n4,
                                                                   uint32_t* const* __restrict__ pads, int rank, int world,
                                                                   float scale) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   block_barrier(pads, rank, world);
   const long long per = (n4 + world - 1) / world;  // 16-byte units per rank
   const long long begin = per * rank;
@@ -102,7 +103,7 @@ extern "C" int cpc_allreduce_mc(void* mc_ptr, int64_t n, void* const* signal_pad
   const int cap = max_blocks > 0 ? (max_blocks < AR_MAX_BLOCKS ? max_blocks : AR_MAX_BLOCKS) : AR_DEFAULT_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  allreduce_mc_kernel<<<(unsigned)blocks, AR_THREADS, 0, stream>>>(static_cast<float*>(mc_ptr), n4,
+  launch_k(allreduce_mc_kernel, dim3((unsigned)blocks), dim3(AR_THREADS), 0, stream, static_cast<float*>(mc_ptr), n4,
                                                                  reinterpret_cast<uint32_t* const*>(signal_pads_dev), rank,
                                                                  world, scale);
   return launch_status();

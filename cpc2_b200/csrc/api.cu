@@ -1,4 +1,6 @@
 // Library-level entry points: status strings, version, driver entry point cache.
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "cpc_internal.h"
@@ -18,7 +20,23 @@ PFN_encodeTiled get_encode_tiled() {
   return fn;
 }
 
+static int g_pdl = -1;  // -1: not decided yet (environment CPC_PDL, default on)
+
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("CPC_PDL");
+    g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl != 0;
+}
+
 }  // namespace cpc
+
+extern "C" int cpc_set_pdl(int on) {
+  const int prev = cpc::pdl_enabled() ? 1 : 0;
+  cpc::g_pdl = on ? 1 : 0;
+  return prev;
+}
 
 extern "C" const char* cpc_strerror(int s) {
   switch (s) {

@@ -24,6 +24,7 @@ __device__ __forceinline__ void stf(__nv_bfloat16* p, float v) { *p = __float2bf
 
 template <typename T>
 __global__ void __launch_bounds__(256) attn_fwd_kernel(const AttnArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   const int S = a.S, dk = a.dk, SP = S | 1, DP = dk | 1;
   T* Kt = reinterpret_cast<T*>(smem_dyn);  // [dk][SP]
@@ -98,6 +99,7 @@ __global__ void __launch_bounds__(256) attn_fwd_kernel(const AttnArgs a) {
 
 template <typename T>
 __global__ void __launch_bounds__(256) attn_bwd_kernel(const AttnArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   const int S = a.S, dk = a.dk, SP = S | 1, DP = dk | 1;
   T* Kt = reinterpret_cast<T*>(smem_dyn);  // [dk][SP]
@@ -239,11 +241,11 @@ extern "C" int cpc_attn_fwd(const CpcAttn* d, void* stream_) {
   size_t sm = attn_smem<float>(a.S, a.dk, false);
   if (sm <= 100 * 1024) {
     if ((rc = set_smem(attn_fwd_kernel<float>, sm)) != CPC_OK) return rc;
-    attn_fwd_kernel<float><<<grid, 256, sm, stream>>>(a);
+    launch_k(attn_fwd_kernel<float>, dim3(grid), dim3(256), sm, stream, a);
   } else {
     sm = attn_smem<__nv_bfloat16>(a.S, a.dk, false);
     if ((rc = set_smem(attn_fwd_kernel<__nv_bfloat16>, sm)) != CPC_OK) return rc;
-    attn_fwd_kernel<__nv_bfloat16><<<grid, 256, sm, stream>>>(a);
+    launch_k(attn_fwd_kernel<__nv_bfloat16>, dim3(grid), dim3(256), sm, stream, a);
   }
   return launch_status();
 }
@@ -260,12 +262,12 @@ extern "C" int cpc_attn_bwd(const CpcAttn* d, void* stream_) {
   size_t sm = attn_smem<float>(a.S, a.dk, true);
   if (sm <= 100 * 1024) {
     if ((rc = set_smem(attn_bwd_kernel<float>, sm)) != CPC_OK) return rc;
-    attn_bwd_kernel<float><<<grid, 256, sm, stream>>>(a);
+    launch_k(attn_bwd_kernel<float>, dim3(grid), dim3(256), sm, stream, a);
   } else {
     sm = attn_smem<__nv_bfloat16>(a.S, a.dk, true);
     if (sm > 220 * 1024) return CPC_ERR_UNSUPPORTED;
     if ((rc = set_smem(attn_bwd_kernel<__nv_bfloat16>, sm)) != CPC_OK) return rc;
-    attn_bwd_kernel<__nv_bfloat16><<<grid, 256, sm, stream>>>(a);
+    launch_k(attn_bwd_kernel<__nv_bfloat16>, dim3(grid), dim3(256), sm, stream, a);
   }
   return launch_status();
 }

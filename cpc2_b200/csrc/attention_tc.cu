@@ -99,6 +99,7 @@ __device__ __forceinline__ uint32_t movmatrix_t(uint32_t v) {
 // ================================================================================================ forward
 template <int DK, int SP, int NW>
 __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int ATT_THREADS = NW * 32, ATT_WARPS = NW;
   constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, RP = SP + 8, NB = SP / 16, NJ = SP / 8;
   extern __shared__ __align__(16) uint8_t smem_dyn[];
@@ -284,6 +285,7 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
 // ================================================================================================ backward
 template <int DK, int SP>
 __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const AttnArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int ATT_WARPS = att_warps(SP), ATT_THREADS = ATT_WARPS * 32;
   constexpr int PD = DK + 8, KS = DK / 16, NT = DK / 8, PS = SP + 8, NB = SP / 16, NJ = SP / 8;
   constexpr bool FULL_U = NB == att_warps(SP);  // one row block per warp: the stages hold all of unskew(dS)
@@ -655,7 +657,7 @@ static int launch_fwd(const AttnArgs& a, int G, cudaStream_t stream) {
       return CPC_ERR_LAUNCH;
     done = true;
   }
-  kern<<<dim3(a.Hh, a.Bt, G), NW * 32, fwd_smem<DK, SP, NW>(), stream>>>(a);
+  launch_k(kern, dim3(dim3(a.Hh, a.Bt, G)), dim3(NW * 32), fwd_smem<DK, SP, NW>(), stream, a);
   return launch_status();
 }
 template <int DK, int SP>
@@ -667,7 +669,7 @@ static int launch_bwd(const AttnArgs& a, int G, cudaStream_t stream) {
       return CPC_ERR_LAUNCH;
     done = true;
   }
-  kern<<<dim3(a.Hh, a.Bt, G), att_warps(SP) * 32, bwd_smem<DK, SP>(), stream>>>(a);
+  launch_k(kern, dim3(dim3(a.Hh, a.Bt, G)), dim3(att_warps(SP) * 32), bwd_smem<DK, SP>(), stream, a);
   return launch_status();
 }
 

@@ -172,6 +172,7 @@ __device__ __forceinline__ void zero_rows(__nv_bfloat16* base, int rows, int C) 
 
 template <int NT, int NW>
 __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_fwd_kernel(const Conv0Args a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int CW = 8 * NT, C = CW * NW;
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -292,6 +293,7 @@ constexpr int STRIPB = 32;  // frames per work item of the backward (2 tiles); C
 
 template <int NT, int NW>
 __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0Args a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int CW = 8 * NT;
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -460,7 +462,7 @@ extern "C" int cpc_conv0_cn_relu_fwd(const CpcConv0* d, void* stream_) {
   case NW_: {                                                                                                          \
     if (smem > 48 * 1024)                                                                                              \
       cudaFuncSetAttribute(conv0_cn_relu_fwd_kernel<NT_, NW_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    conv0_cn_relu_fwd_kernel<NT_, NW_><<<blocks, 32 * NW_, smem, stream>>>(a);                                         \
+    launch_k(conv0_cn_relu_fwd_kernel<NT_, NW_>, dim3(blocks), dim3(32 * NW_), smem, stream, a);                                         \
     break;                                                                                                             \
   }
   if (NT == 8) {
@@ -501,7 +503,7 @@ extern "C" int cpc_conv0_cn_relu_bwd(const CpcConv0* d, void* stream_) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv0_cn_relu_bwd_kernel<NT_, NW_>, 32 * NW_, smem);           \
     long long blocks = (long long)sms * (occ < 1 ? 1 : occ);                                                           \
     if (blocks > items) blocks = items;                                                                                \
-    conv0_cn_relu_bwd_kernel<NT_, NW_><<<(unsigned)blocks, 32 * NW_, smem, stream>>>(a);                               \
+    launch_k(conv0_cn_relu_bwd_kernel<NT_, NW_>, dim3((unsigned)blocks), dim3(32 * NW_), smem, stream, a);                               \
     break;                                                                                                             \
   }
   if (NT == 8) {

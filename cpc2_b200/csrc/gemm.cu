@@ -135,6 +135,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // PDL: everything above (tensor-map fetch, barrier init, TMEM allocation) overlapped the tail of the preceding grid;
+  // nothing below reads or writes global memory before that grid has completed (cpc_internal.h)
+  pdl_sync();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -285,7 +288,7 @@ static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, GemmKe
   ka.tiles_n = (ka.N + BN - 1) / BN;
   ka.total_tiles = ka.tiles_m * ka.tiles_n * groups * ka.k_splits;
   const int grid = ka.total_tiles < sm_count() ? ka.total_tiles : sm_count();
-  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, ka);
+  launch_k(kern, dim3(grid), dim3(GEMM_THREADS), L::TOTAL, stream, ta, tb, ka);
   return cudaGetLastError() == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
 }
 

@@ -61,6 +61,7 @@ constexpr int GX_PITCH = 132;  // floats per sequence row: bank = 4*b + unit -> 
 
 template <int H, int CELL>
 __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int CL = H / 32, KT = H / 16, HP = H + 8;
   __shared__ __align__(16) __nv_bfloat16 h_s[2][NB][HP];          // h_{t-1} of the whole cluster (double-buffered)
   __shared__ __align__(16) float gx_s[3][NB][GX_PITCH];           // prefetched input projections
@@ -239,6 +240,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
 // from the accumulator fragments; warp w's two m-tiles are exactly the block of CTA w when H = 256).
 template <int H, int CELL>
 __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int CL = H / 32;
   constexpr int MT = H / 16;                      // output (h) m-tiles
   constexpr int MTW = (MT + 7) / 8;               // m-tiles per warp
@@ -430,13 +432,15 @@ static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
   cfg.gridDim = dim3(CL * clusters);
   cfg.blockDim = dim3(LSTM_THREADS);
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // PDL (cpc_internal.h)
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t e;
   if (!backward) {
     auto kern = lstm_fwd_kernel<H, CELL>;

@@ -36,6 +36,7 @@ struct NceArgs {
 // loss / hit sums are reduced in shared memory first: one global atomic per (block, step).
 template <int J>
 __global__ void __launch_bounds__(256) nce_fwd_kernel(const NceArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int KU = 4;
   extern __shared__ float acc[];  // [2][K]
   const int lane = threadIdx.x & 31;
@@ -96,6 +97,7 @@ __global__ void __launch_bounds__(256) nce_fwd_kernel(const NceArgs a) {
 // registers across the steps of the chunk.
 template <int J>
 __global__ void __launch_bounds__(256) nce_bwd_kernel(const NceArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int KU = 4;
   extern __shared__ float rowbuf[];  // [warps][ld]
   const int lane = threadIdx.x & 31;
@@ -189,12 +191,12 @@ extern "C" int cpc_nce_fwd(const CpcNce* d, void* stream_) {
   const size_t smem = (size_t)2 * a.K * sizeof(float);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int J = (a.NEG + 31) / 32;
-  if (J <= 1) nce_fwd_kernel<1><<<(unsigned)blocks, 256, smem, stream>>>(a);
-  else if (J <= 2) nce_fwd_kernel<2><<<(unsigned)blocks, 256, smem, stream>>>(a);
-  else if (J <= 4) nce_fwd_kernel<4><<<(unsigned)blocks, 256, smem, stream>>>(a);
-  else if (J <= 8) nce_fwd_kernel<8><<<(unsigned)blocks, 256, smem, stream>>>(a);
-  else if (J <= 16) nce_fwd_kernel<16><<<(unsigned)blocks, 256, smem, stream>>>(a);
-  else if (J <= 32) nce_fwd_kernel<32><<<(unsigned)blocks, 256, smem, stream>>>(a);
+  if (J <= 1) launch_k(nce_fwd_kernel<1>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
+  else if (J <= 2) launch_k(nce_fwd_kernel<2>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
+  else if (J <= 4) launch_k(nce_fwd_kernel<4>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
+  else if (J <= 8) launch_k(nce_fwd_kernel<8>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
+  else if (J <= 16) launch_k(nce_fwd_kernel<16>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
+  else if (J <= 32) launch_k(nce_fwd_kernel<32>, dim3((unsigned)blocks), dim3(256), smem, stream, a);
   else return CPC_ERR_UNSUPPORTED;  // more than 1024 negatives per token
   return launch_status();
 }
@@ -217,7 +219,7 @@ extern "C" int cpc_nce_bwd(const CpcNce* d, void* stream_) {
     if (smem > 48 * 1024 &&                                                                                          \
         cudaFuncSetAttribute(nce_bwd_kernel<JJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) \
       return CPC_ERR_LAUNCH;                                                                                         \
-    nce_bwd_kernel<JJ><<<(unsigned)blocks, 256, smem, stream>>>(a);                                                  \
+    launch_k(nce_bwd_kernel<JJ>, dim3((unsigned)blocks), dim3(256), smem, stream, a);                                                  \
   } while (0)
   if (J <= 1) CPC_NCE_BWD(1);
   else if (J <= 2) CPC_NCE_BWD(2);

@@ -28,6 +28,7 @@ struct AdamSpan {  // mirrors CpcAdamSpan
 // state: [0] step (as double), [1] lr, [2] beta1, [3] beta2, [4] eps, [5] step_size = lr / (1 - beta1^step),
 // [6] sqrt(1 - beta2^step)
 __global__ void adam_prologue_kernel(double* state) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const double step = state[0] + 1.0;
   state[0] = step;
   const double bc1 = 1.0 - pow(state[2], step);
@@ -47,6 +48,7 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
 
 __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamSpan* __restrict__ spans, int n_spans,
                                                             const double* __restrict__ state) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   // span of this CTA: binary search over the block prefix
   int lo = 0, hi = n_spans - 1;
   const long long blk = blockIdx.x;
@@ -116,8 +118,8 @@ extern "C" int cpc_adam_step(const CpcAdamSpan* spans_dev, int n_spans, int64_t 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (spans_dev == nullptr || state_dev == nullptr || n_spans <= 0 || total_blocks <= 0 || total_blocks > 0x7fffffffLL)
     return CPC_ERR_ARG;
-  if (advance) adam_prologue_kernel<<<1, 1, 0, stream>>>(state_dev);
-  adam_kernel<<<(unsigned)total_blocks, ADAM_THREADS, 0, stream>>>(reinterpret_cast<const AdamSpan*>(spans_dev), n_spans,
+  if (advance) launch_k(adam_prologue_kernel, dim3(1), dim3(1), 0, stream, state_dev);
+  launch_k(adam_kernel, dim3((unsigned)total_blocks), dim3(ADAM_THREADS), 0, stream, reinterpret_cast<const AdamSpan*>(spans_dev), n_spans,
                                                                   state_dev);
   return launch_status();
 }

@@ -159,6 +159,7 @@ struct RowNormFwdArgs {
 
 template <int V>
 __global__ void __launch_bounds__(256) rownorm_fwd_kernel(const RowNormFwdArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int C = 32 * V;
   const int lane = threadIdx.x & 31;
   const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -236,6 +237,7 @@ struct RowNormBwdArgs {
 // launch ran as two or three full latency chains (load -> reduce -> store -> block reduction -> atomics) back to back.
 template <int V>
 __global__ void __launch_bounds__(256, (V <= 8 ? 2 : 1)) rownorm_bwd_kernel(const RowNormBwdArgs a) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   constexpr int C = 32 * V;
   __shared__ float red[3][8][C > 512 ? 1 : C];
   const int lane = threadIdx.x & 31;
@@ -433,11 +435,11 @@ extern "C" int cpc_rownorm_fwd(const CpcRowNormFwd* d, void* stream_) {
   long long blocks = (d->rows + wpb - 1) / wpb;
   if (blocks > 148 * 16) blocks = 148 * 16;
   switch (d->C / 32) {
-    case 1: rownorm_fwd_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
-    case 2: rownorm_fwd_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
-    case 4: rownorm_fwd_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
-    case 8: rownorm_fwd_kernel<8><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
-    case 16: rownorm_fwd_kernel<16><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 1: launch_k(rownorm_fwd_kernel<1>, dim3((unsigned)blocks), dim3(256), 0, stream, a); break;
+    case 2: launch_k(rownorm_fwd_kernel<2>, dim3((unsigned)blocks), dim3(256), 0, stream, a); break;
+    case 4: launch_k(rownorm_fwd_kernel<4>, dim3((unsigned)blocks), dim3(256), 0, stream, a); break;
+    case 8: launch_k(rownorm_fwd_kernel<8>, dim3((unsigned)blocks), dim3(256), 0, stream, a); break;
+    case 16: launch_k(rownorm_fwd_kernel<16>, dim3((unsigned)blocks), dim3(256), 0, stream, a); break;
     default: return CPC_ERR_UNSUPPORTED;
   }
   return launch_status();
@@ -471,11 +473,11 @@ extern "C" int cpc_rownorm_bwd(const CpcRowNormBwd* d, void* stream_) {
   if (bx < 1) bx = 1;
   dim3 grid((unsigned)bx, groups);
   switch (d->C / 32) {
-    case 1: rownorm_bwd_kernel<1><<<grid, 256, 0, stream>>>(a); break;
-    case 2: rownorm_bwd_kernel<2><<<grid, 256, 0, stream>>>(a); break;
-    case 4: rownorm_bwd_kernel<4><<<grid, 256, 0, stream>>>(a); break;
-    case 8: rownorm_bwd_kernel<8><<<grid, 256, 0, stream>>>(a); break;
-    case 16: rownorm_bwd_kernel<16><<<grid, 256, 0, stream>>>(a); break;
+    case 1: launch_k(rownorm_bwd_kernel<1>, dim3(grid), dim3(256), 0, stream, a); break;
+    case 2: launch_k(rownorm_bwd_kernel<2>, dim3(grid), dim3(256), 0, stream, a); break;
+    case 4: launch_k(rownorm_bwd_kernel<4>, dim3(grid), dim3(256), 0, stream, a); break;
+    case 8: launch_k(rownorm_bwd_kernel<8>, dim3(grid), dim3(256), 0, stream, a); break;
+    case 16: launch_k(rownorm_bwd_kernel<16>, dim3(grid), dim3(256), 0, stream, a); break;
     default: return CPC_ERR_UNSUPPORTED;
   }
   return launch_status();

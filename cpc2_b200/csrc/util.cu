@@ -6,6 +6,7 @@
 namespace cpc {
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long n4 = n / 4;
@@ -22,6 +23,7 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16
 }
 
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ out, long long n) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     out[i] = __bfloat162float(in[i]);
@@ -33,6 +35,7 @@ __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float
 template <bool BF16>
 __global__ void dropout_kernel(void* __restrict__ x_, long long n, const unsigned long long* __restrict__ rng,
                                uint32_t site, float p) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const unsigned long long seed = rng[0] + rng[1] * 0x632BE59BD9B4E019ull;
   const uint32_t seed_lo = static_cast<uint32_t>(seed);
   const uint32_t seed_hi = static_cast<uint32_t>(seed >> 32) + site * 0x85EBCA77u;
@@ -59,6 +62,7 @@ __global__ void dropout_kernel(void* __restrict__ x_, long long n, const unsigne
 template <bool IN_BF16>
 __global__ void __launch_bounds__(256) colsum_kernel(const void* __restrict__ in_, float* __restrict__ out, long long rows,
                                                      int C, long long ld, long long gs_in, int row_chunks) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   __shared__ float red[8][33];
   const int g = blockIdx.z;
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -87,6 +91,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const void* __restrict__ in
 template <bool IN_BF16>
 __global__ void groupsum_kernel(const void* __restrict__ in_, float* __restrict__ out_f32,
                                 __nv_bfloat16* __restrict__ out_bf16, long long n, int groups, int accumulate) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     float acc = 0.f;
@@ -102,6 +107,7 @@ __global__ void groupsum_kernel(const void* __restrict__ in_, float* __restrict_
 // extIdx = ((seqIdx + t) mod S) + batchIdx * S, flat order (b, n, t)   -- criterion.py:256-266, int64, exact
 __global__ void neg_ext_index_kernel(const long long* __restrict__ batch_idx, const long long* __restrict__ seq_idx,
                                      long long* __restrict__ ext, long long n, int W, int S) {
+  pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const long long t = i % W;
@@ -126,7 +132,7 @@ extern "C" int cpc_cast_f32_to_bf16(const void* in, void* out, int64_t n, void* 
   if (in == nullptr || out == nullptr || n < 0) return CPC_ERR_ARG;
   if (n == 0) return CPC_OK;
   if ((reinterpret_cast<uintptr_t>(in) & 15) || (reinterpret_cast<uintptr_t>(out) & 7)) return CPC_ERR_ALIGN;
-  cast_f32_bf16_kernel<<<grid_for(n, 1024), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+  launch_k(cast_f32_bf16_kernel, dim3(grid_for(n, 1024)), dim3(256), 0, static_cast<cudaStream_t>(stream_), 
       static_cast<const float*>(in), static_cast<__nv_bfloat16*>(out), n);
   return launch_status();
 }
@@ -134,7 +140,7 @@ extern "C" int cpc_cast_f32_to_bf16(const void* in, void* out, int64_t n, void* 
 extern "C" int cpc_cast_bf16_to_f32(const void* in, void* out, int64_t n, void* stream_) {
   if (in == nullptr || out == nullptr || n < 0) return CPC_ERR_ARG;
   if (n == 0) return CPC_OK;
-  cast_bf16_f32_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+  launch_k(cast_bf16_f32_kernel, dim3(grid_for(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream_), 
       static_cast<const __nv_bfloat16*>(in), static_cast<float*>(out), n);
   return launch_status();
 }
@@ -144,9 +150,9 @@ extern "C" int cpc_dropout(void* x, int is_bf16, int64_t n, const void* rng, uin
   if (n == 0 || p == 0.f) return CPC_OK;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (is_bf16)
-    dropout_kernel<true><<<grid_for((n + 1) / 2, 256), 256, 0, stream>>>(x, n, static_cast<const unsigned long long*>(rng), site, p);
+    launch_k(dropout_kernel<true>, dim3(grid_for((n + 1) / 2, 256)), dim3(256), 0, stream, x, n, static_cast<const unsigned long long*>(rng), site, p);
   else
-    dropout_kernel<false><<<grid_for((n + 1) / 2, 256), 256, 0, stream>>>(x, n, static_cast<const unsigned long long*>(rng), site, p);
+    launch_k(dropout_kernel<false>, dim3(grid_for((n + 1) / 2, 256)), dim3(256), 0, stream, x, n, static_cast<const unsigned long long*>(rng), site, p);
   return launch_status();
 }
 
@@ -158,8 +164,8 @@ extern "C" int cpc_colsum(const void* in, int in_is_bf16, void* out, int64_t row
   if (chunks > 64) chunks = 64;
   dim3 grid((C + 31) / 32, chunks, groups);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (in_is_bf16) colsum_kernel<true><<<grid, 256, 0, stream>>>(in, static_cast<float*>(out), rows, C, ld, gs_in, chunks);
-  else colsum_kernel<false><<<grid, 256, 0, stream>>>(in, static_cast<float*>(out), rows, C, ld, gs_in, chunks);
+  if (in_is_bf16) launch_k(colsum_kernel<true>, dim3(grid), dim3(256), 0, stream, in, static_cast<float*>(out), rows, C, ld, gs_in, chunks);
+  else launch_k(colsum_kernel<false>, dim3(grid), dim3(256), 0, stream, in, static_cast<float*>(out), rows, C, ld, gs_in, chunks);
   return launch_status();
 }
 
@@ -168,10 +174,10 @@ extern "C" int cpc_groupsum(const void* in, int in_is_bf16, void* out_f32, void*
   if (in == nullptr || n <= 0 || groups <= 0 || (out_f32 == nullptr && out_bf16 == nullptr)) return CPC_ERR_ARG;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (in_is_bf16)
-    groupsum_kernel<true><<<grid_for(n, 256), 256, 0, stream>>>(in, static_cast<float*>(out_f32),
+    launch_k(groupsum_kernel<true>, dim3(grid_for(n, 256)), dim3(256), 0, stream, in, static_cast<float*>(out_f32),
                                                                  static_cast<__nv_bfloat16*>(out_bf16), n, groups, accumulate);
   else
-    groupsum_kernel<false><<<grid_for(n, 256), 256, 0, stream>>>(in, static_cast<float*>(out_f32),
+    launch_k(groupsum_kernel<false>, dim3(grid_for(n, 256)), dim3(256), 0, stream, in, static_cast<float*>(out_f32),
                                                                   static_cast<__nv_bfloat16*>(out_bf16), n, groups, accumulate);
   return launch_status();
 }
@@ -181,7 +187,7 @@ extern "C" int cpc_neg_ext_index(const void* batch_idx, const void* seq_idx, voi
   if (batch_idx == nullptr || seq_idx == nullptr || ext == nullptr || B <= 0 || NEG <= 0 || W <= 0 || S <= 0)
     return CPC_ERR_ARG;
   const long long n = (long long)B * NEG * W;
-  neg_ext_index_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+  launch_k(neg_ext_index_kernel, dim3(grid_for(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream_), 
       static_cast<const long long*>(batch_idx), static_cast<const long long*>(seq_idx), static_cast<long long*>(ext), n, W, S);
   return launch_status();
 }

@@ -30,14 +30,12 @@ class BucketedAllReduce:
     def __init__(self, cpcModel, cpcCriterion, process_group=None, symmetric=False, max_blocks=0):
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
-        self.on_gpu = any(p.is_cuda for p in cpcModel.parameters())
+        # cpcModel None: the criterion alone (BASELINE.json's criterion-only sweep: the heads' gradients are the bucket)
+        mods = [cpcCriterion] + ([cpcModel.gAR, cpcModel.gEncoder] if cpcModel is not None else [])
+        self.on_gpu = any(p.is_cuda for m in mods for p in m.parameters())
         # the CPU (gloo) form exists for the world-size-2 host-logic tests only: same buckets, same order
         self.stream = torch.cuda.Stream() if self.on_gpu else None
-        self.buckets = [
-            [p for p in cpcCriterion.parameters() if p.requires_grad],
-            [p for p in cpcModel.gAR.parameters() if p.requires_grad],
-            [p for p in cpcModel.gEncoder.parameters() if p.requires_grad],
-        ]
+        self.buckets = [[p for p in m.parameters() if p.requires_grad] for m in mods]
         self.reduced = []      # (stage, numel) per arena all-reduce of the current step (test / bench evidence)
         self.stragglers = 0    # gradients that had to be reduced one by one in finish()
         self._arenas = []      # storages reduced in the current step
@@ -47,7 +45,7 @@ class BucketedAllReduce:
         if self.world > 1:
             ops.GRAD_READY.append(self._on_grad_ready)
             if symmetric and self.on_gpu:
-                self._map_symmetric(next(p for p in cpcModel.parameters() if p.is_cuda).device, symmetric)
+                self._map_symmetric(next(p for b in self.buckets for p in b if p.is_cuda).device, symmetric)
 
     def _map_symmetric(self, dev, mode):
         """One symmetric fp32 buffer for every gradient arena of the step + its multicast mapping.  mode "auto":

@@ -85,8 +85,10 @@ def _out(t):
 
 def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=None, out_bf16=None, bias=None,
          bias_gs=0, res=None, gate=None, gate_scale=1.0, relu=False, accumulate=False, rng=None, rng_site=0,
-         drop_p=0.0, force_bn=0):
-    """cpc_gemm_bf16: D[g] = alpha * A_g . B_g^T (+ epilogue).  See include/cpc_b200.h."""
+         drop_p=0.0, force_bn=0, algo_flops=None):
+    """cpc_gemm_bf16: D[g] = alpha * A_g . B_g^T (+ epilogue).  See include/cpc_b200.h.
+    algo_flops: ALGORITHMIC work of the call when it differs from the executed 2*M*N*K*groups (the all-pairs logits
+    products compute every (token, frame) pair where the algorithm needs NEG + 1 of them); profiling only."""
     d = GemmDesc()
     d.M, d.N, d.K, d.groups, d.k_per_slab, d.k_splits, d.force_bn = M, N, K, groups, k_per_slab, k_splits, force_bn
     d.a, d.a_major = A.addr(), A.major
@@ -121,7 +123,8 @@ def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=N
     d.relu, d.accumulate = int(relu), int(accumulate)
     if PROFILE is not None:
         ob = (4 if out_f32 is not None else 0) + (2 if out_bf16 is not None else 0)
-        set_work(kind="tensor", flops=2.0 * M * N * K * groups, bytes=2.0 * groups * (M * K + N * K) + ob * M * N * groups,
+        set_work(kind="tensor", flops=2.0 * M * N * K * groups if algo_flops is None else float(algo_flops),
+                 executed_flops=2.0 * M * N * K * groups, bytes=2.0 * groups * (M * K + N * K) + ob * M * N * groups,
                  shape=f"g{groups} {M}x{N}x{K} a{A.major}b{B.major} s{k_splits}")
     _run("cpc_gemm_bf16", (ctypes.byref(d), stream_ptr(),))
 
@@ -314,7 +317,7 @@ def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p):
 def attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
     d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
     if PROFILE is not None:
-        set_work(kind="cuda-core", flops=3.0 * G * Bt * Hh * S * S * dk)
+        set_work(kind="tensor", flops=3.0 * G * Bt * Hh * S * S * dk)  # (mma.sync tensor cores, causal: ~half executed)
     _run("cpc_attn_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
@@ -322,5 +325,5 @@ def attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk,
     d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
     d.dout, d.dqkv, d.dscore, d.dkrel = _dp(dout), _dp(dqkv), _dp(dscore), _dp(dkrel)
     if PROFILE is not None:
-        set_work(kind="cuda-core", flops=7.0 * G * Bt * Hh * S * S * dk)
+        set_work(kind="tensor", flops=7.0 * G * Bt * Hh * S * S * dk)
     _run("cpc_attn_bwd", (ctypes.byref(d), stream_ptr(),))

@@ -38,6 +38,9 @@ const char* cpc_strerror(int status);
 int cpc_version(void);
 /* compute capability major*10+minor of the current device, or a negative status */
 int cpc_device_arch(void);
+/* Programmatic dependent launch of every kernel of the library (default on; environment CPC_PDL=0 turns it off).
+ * Returns the previous setting.  No reference counterpart: launch plumbing of the sm_100a path. */
+int cpc_set_pdl(int on);
 
 /* ------------------------------------------------------------------------------------------------
  * Grouped bf16 GEMM on tcgen05 tensor cores:  D[g][m,n] = alpha * sum_k A_g(m,k) * B_g(n,k) (+epilogue)
