@@ -78,6 +78,11 @@ class GemmDesc(ctypes.Structure):
         ("gate_scale", ctypes.c_float),
         ("rng", ctypes.c_void_p), ("rng_site", ctypes.c_uint32), ("drop_p", ctypes.c_float),
         ("relu", ctypes.c_int), ("accumulate", ctypes.c_int),
+        ("norm_gamma", ctypes.c_void_p), ("norm_beta", ctypes.c_void_p), ("gs_norm_param", ctypes.c_int64),
+        ("norm_bf16", ctypes.c_void_p), ("ld_norm_bf16", ctypes.c_int64), ("gs_norm_bf16", ctypes.c_int64),
+        ("norm_f32", ctypes.c_void_p), ("ld_norm_f32", ctypes.c_int64), ("gs_norm_f32", ctypes.c_int64),
+        ("norm_mean", ctypes.c_void_p), ("norm_rstd", ctypes.c_void_p), ("gs_norm_stat", ctypes.c_int64),
+        ("norm_eps", ctypes.c_float), ("norm_unbiased", ctypes.c_int), ("norm_halo", ctypes.c_int),
     ]
 
 
@@ -158,6 +163,7 @@ class Nce(ctypes.Structure):
         ("logits", ctypes.c_void_p), ("ext", ctypes.c_void_p), ("weights", ctypes.c_void_p),
         ("lse", ctypes.c_void_p), ("loss_sum", ctypes.c_void_p), ("hits", ctypes.c_void_p),
         ("gscale", ctypes.c_void_p), ("dlogits", ctypes.c_void_p), ("dlogits_lo", ctypes.c_void_p),
+        ("out_scale", ctypes.c_float),
     ]
 
 

@@ -455,13 +455,34 @@ class CPCUnsupersivedCriterion(BaseCriterion):
         self.mode = mode
 
     # -------------------------------------------------------------------------------------- sampling
-    def sampleIndices(self, batchSize, nNegativeExt, windowSize, device):
+    def sampleIndices(self, batchSize, nNegativeExt, windowSize, device, out=None):
         """The two RNG draws of sampleClean (criterion.py:247-255) in the reference's order, then the
-        integer index arithmetic (:256-266) on the GPU.  Returns extIdx int64 [B*NEG*W], flat (b, n, t)."""
+        integer index arithmetic (:256-266) on the GPU.  Returns extIdx int64 [B*NEG*W], flat (b, n, t).
+        `out`: three preallocated int64 [n] buffers (batchIdx, seqIdx, extIdx)."""
         n = self.negativeSamplingExt * windowSize * batchSize
-        batchIdx = torch.randint(low=0, high=batchSize, size=(n,), device=device)
-        seqIdx = torch.randint(low=1, high=nNegativeExt, size=(n,), device=device)
-        return K.neg_ext_index(batchIdx, seqIdx, batchSize, self.negativeSamplingExt, windowSize, nNegativeExt)
+        if out is None:
+            batchIdx = torch.randint(low=0, high=batchSize, size=(n,), device=device)
+            seqIdx = torch.randint(low=1, high=nNegativeExt, size=(n,), device=device)
+            return K.neg_ext_index(batchIdx, seqIdx, batchSize, self.negativeSamplingExt, windowSize, nNegativeExt)
+        batchIdx = torch.randint(low=0, high=batchSize, size=(n,), out=out[0])
+        seqIdx = torch.randint(low=1, high=nNegativeExt, size=(n,), out=out[1])
+        return K.neg_ext_index(batchIdx, seqIdx, batchSize, self.negativeSamplingExt, windowSize, nNegativeExt, out=out[2])
+
+    def prefetchIndices(self, batchSize, seqSize, device):
+        """Draw this step's negatives NOW, on a side stream (train.forwardBackward calls it at the top of the step):
+        the sampler depends on nothing the model computes, and its three small kernels otherwise sit between the AR
+        network and the prediction heads on the critical path.  Same two randint draws in the same order on the same
+        generator as forward() would issue (no other consumer of the generator runs in between: dropout uses its own
+        counter RNG), so seeded runs sample the same negatives either way.  Buffers are allocated on the current
+        stream (ops.side rule); forward() joins the side stream before it reads them."""
+        windowSize = seqSize - self.nPredicts
+        if windowSize <= 0 or "sampleIndices" in self.__dict__:  # (an instance-level sampler override: leave it alone)
+            return
+        n = self.negativeSamplingExt * windowSize * batchSize
+        bufs = [torch.empty(n, dtype=torch.int64, device=device) for _ in range(3)]
+        with ops.side(8):
+            ext = self.sampleIndices(batchSize, seqSize, windowSize, device, out=bufs)
+        self.__dict__["_pref_ext"] = ((batchSize, seqSize, windowSize, torch.device(device)), ext, bufs)
 
     def sampleClean(self, encodedData, windowSize):
         """Reference-compatible materialised sampling (criterion.py:237-286): list of K tensors
@@ -514,7 +535,13 @@ class CPCUnsupersivedCriterion(BaseCriterion):
             raise ValueError(f"cpc2_b200: batch x frames = {batchSize * encodedData.size(1)} exceeds {ops.NCE_BWD_MAX_BS} "
                              "(cpc_nce_bwd keeps one row of d(logits) per warp in shared memory; e.g. batchSizeGPU <= 50 at "
                              "sizeWindow 20480): lower batchSizeGPU, the all-pairs logits also grow as (batch x frames)^2")
-        extIdx = self.sampleIndices(batchSize, encodedData.size(1), windowSize, encodedData.device)
+        pref = self.__dict__.pop("_pref_ext", None)
+        if pref is not None:
+            ops.join(8)
+        if pref is not None and pref[0] == (batchSize, encodedData.size(1), windowSize, encodedData.device):
+            extIdx = pref[1]
+        else:
+            extIdx = self.sampleIndices(batchSize, encodedData.size(1), windowSize, encodedData.device)
         weights = None
         if signal_quality is not None:
             q = self.weighting_function(signal_quality.mean(dim=1))
@@ -559,14 +586,13 @@ class _CriterionFn(torch.autograd.Function):
         algo = 2.0 * T * (NEG + 1) * D * Kp
         ops.linear_fwd(preds, zb, T, BS, D, groups=Kp, out_f32=logits, alpha=1.0 / D, algo_flops=algo)
         lse = torch.empty(Kp, T, device=dev)
-        loss_sum, hits = torch.zeros(2, Kp, device=dev).unbind(0)  # (one memset)
-        K.nce_fwd(logits, ext, weights, lse, loss_sum, hits, Kp, B, W, S, NEG, BS)
+        # mean loss / accuracy per prediction step (criterion.py:350-357) accumulate pre-scaled by 1/T: no divisions after
+        losses, acc = torch.zeros(2, 1, Kp, device=dev).unbind(0)  # (one memset)
+        K.nce_fwd(logits, ext, weights, lse, losses, acc, Kp, B, W, S, NEG, BS, out_scale=1.0 / T)
         ctx.eng, ctx.saved = eng, saved
         ctx.t = (preds, zb, logits, lse, ext, weights)
         ctx.dims = (B, S, H, D, W, Kp, NEG)
         ctx.algo = algo
-        losses = (loss_sum / T).view(1, Kp)
-        acc = (hits / (W * B)).view(1, Kp)
         ctx.mark_non_differentiable(acc)
         return losses, acc
 

@@ -57,6 +57,19 @@ struct GemmKernelArgs {
   float drop_p;
   int relu;
   int accumulate;
+  // fused row normalisation (EPI_NORM), see CpcGemmDesc
+  const float* norm_gamma;
+  const float* norm_beta;
+  long long gs_norm_param;
+  __nv_bfloat16* norm_bf16;
+  long long ld_norm_bf16, gs_norm_bf16;
+  float* norm_f32;
+  long long ld_norm_f32, gs_norm_f32;
+  float* norm_mean;
+  float* norm_rstd;
+  long long gs_norm_stat;
+  float norm_eps;
+  int norm_unbiased, norm_halo;
 };
 
 constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, each owns half of the tile's columns
@@ -68,7 +81,9 @@ struct GemmSmem {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
+  static constexpr int STAT_OFF = BAR_OFF + (2 * STAGES + 4) * 8 + 16;  // EPI_NORM: [tile parity][column half][BM] float2
+  static constexpr int STAT_BYTES = 2 * 2 * BM * 8;
+  static constexpr int TOTAL = STAT_OFF + STAT_BYTES + 1024;  // + alignment slack
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (128 / 256 / 512 columns)
 };
 
@@ -226,7 +241,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const TileCoord tc = decode_tile(p, tile, BN);
       const int buf = lt & 1;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + half * (BN / 2);
-      epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng, &acc_full[buf], (lt >> 1) & 1);
+      if constexpr (MODE == EPI_NORM)
+        epilogue_tile_norm<BN>(p, tc, taddr, q, half, lane, &acc_full[buf], (lt >> 1) & 1,
+                               reinterpret_cast<float2*>(smem + L::STAT_OFF) + (lt & 1) * 2 * BM);
+      else
+        epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng, &acc_full[buf], (lt >> 1) & 1);
       // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld inside): hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
@@ -296,6 +315,10 @@ template <int BN, int STAGES, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int groups,
                        cudaStream_t stream) {
   // epilogue mode (exclusive; the entry point has rejected combinations no mode covers)
+  if (ka.norm_gamma != nullptr) {
+    if constexpr (BN == 256 && !A_MN && !B_MN) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_NORM>(ta, tb, ka, groups, stream);
+    else return CPC_ERR_UNSUPPORTED;
+  }
   if (ka.k_splits > 1) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_SPLITK>(ta, tb, ka, groups, stream);
   if (ka.accumulate) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_ACCUM>(ta, tb, ka, groups, stream);
   if (ka.rng != nullptr && ka.drop_p > 0.f) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_DROP>(ta, tb, ka, groups, stream);
@@ -323,7 +346,7 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (d == nullptr || d->M <= 0 || d->N <= 0 || d->K <= 0 || d->groups <= 0) return CPC_ERR_ARG;
   if (d->N % 8 != 0) return CPC_ERR_ARG;
-  if (d->out_f32 == nullptr && d->out_bf16 == nullptr) return CPC_ERR_ARG;
+  if (d->out_f32 == nullptr && d->out_bf16 == nullptr && d->norm_gamma == nullptr) return CPC_ERR_ARG;
   const int k_per_slab = d->k_per_slab > 0 ? d->k_per_slab : d->K;
   if (d->K % k_per_slab != 0) return CPC_ERR_ARG;
   const int slabs = d->K / k_per_slab;
@@ -358,6 +381,20 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   ka.gate_scale = d->gate_scale;
   ka.rng = static_cast<const unsigned long long*>(d->rng); ka.rng_site = d->rng_site; ka.drop_p = d->drop_p;
   ka.relu = d->relu; ka.accumulate = d->accumulate;
+  ka.norm_gamma = static_cast<const float*>(d->norm_gamma); ka.norm_beta = static_cast<const float*>(d->norm_beta);
+  ka.gs_norm_param = d->gs_norm_param;
+  ka.norm_bf16 = static_cast<__nv_bfloat16*>(d->norm_bf16); ka.ld_norm_bf16 = d->ld_norm_bf16; ka.gs_norm_bf16 = d->gs_norm_bf16;
+  ka.norm_f32 = static_cast<float*>(d->norm_f32); ka.ld_norm_f32 = d->ld_norm_f32; ka.gs_norm_f32 = d->gs_norm_f32;
+  ka.norm_mean = static_cast<float*>(d->norm_mean); ka.norm_rstd = static_cast<float*>(d->norm_rstd);
+  ka.gs_norm_stat = d->gs_norm_stat;
+  ka.norm_eps = d->norm_eps; ka.norm_unbiased = d->norm_unbiased; ka.norm_halo = d->norm_halo;
+  const bool fused_norm = d->norm_gamma != nullptr;
+  if (fused_norm) {
+    if (d->N != 256 || d->a_major != 0 || d->b_major != 0 || k_splits > 1 || d->accumulate || d->gate != nullptr ||
+        (d->rng != nullptr && d->drop_p > 0.f) || d->norm_beta == nullptr || d->out_f32 != nullptr ||
+        (d->norm_bf16 == nullptr && d->norm_f32 == nullptr) || d->norm_halo < 0 || d->norm_halo > 4)
+      return CPC_ERR_UNSUPPORTED;
+  }
 
   // tile-N selection: minimise (waves over the SMs) x (cost of one 128 x bn tile), in SM cycles.  Per 64-wide
   // k-block the tensor pipe needs max(2*bn, shared-memory operand reads at 128 B/cycle) cycles, and TMA has to
@@ -386,6 +423,7 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
     }
   }
   if (d->force_bn == 64 || d->force_bn == 128 || d->force_bn == 256) bn = d->force_bn;
+  if (fused_norm) bn = 256;  // one accumulator tile = one whole row
 
   CUtensorMap ta, tb;
   int rc = encode_operand_map(&ta, d->a, d->a_dim0, d->a_dim1, d->a_dim2, d->a_stride1, d->a_stride2, d->a_major, BM);

@@ -12,7 +12,7 @@
 
 namespace cpc {
 
-enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5 };
+enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5, EPI_NORM = 6 };
 
 struct EpiRng {
   uint32_t seed_lo, seed_hi, thresh;
@@ -184,6 +184,158 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const Til
         }
       }
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// EPI_NORM: row normalisation fused into the epilogue (ChannelNorm of conv1-4, cpc/model.py:52-60; nn.LayerNorm of
+// the transformer blocks, cpc/transformers.py:124,130).  N == BN == 256, so the accumulator tile holds WHOLE rows:
+//   sweep 1   x = alpha*acc + bias (+ residual); pre-norm x -> out_bf16 (saved for the backward); per-row sum(x),
+//             sum(x^2) in registers, folded over the four lanes that share a row (two shuffles) and over the two warps
+//             that share it (column halves) through 2 KB of shared memory and one 64-thread named barrier;
+//   sweep 2   the accumulator is read from TMEM a second time (reads are ~free next to the global stores):
+//             y = (x - mean) * rstd * gamma + beta, ReLU, -> norm_bf16 / norm_f32; mean / rstd -> fp32 [M].
+// fp32 sum / sum-of-squares over 256 values: the relative error of the variance is ~1e-6 * (1 + mean^2/var), far below
+// the bf16 rounding of the outputs.  The zero halo rows the next strided conv reads around each sequence are written
+// by the CTA that owns the first / last row tile of the group.
+__device__ __forceinline__ void epi_pair_barrier(int q) {
+  asm volatile("bar.sync %0, 64;" ::"r"(q + 1) : "memory");
+}
+
+template <int BN>
+__device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, const TileCoord& tc, uint32_t taddr, int q,
+                                                   int half, int lane, uint64_t* acc_full_bar, uint32_t parity,
+                                                   float2* stat) {
+  static_assert(BN == 256, "fused row norm: one 256-column tile per row");
+  constexpr int NC = BN / 64;  // 32-column chunks per warp (this warp owns BN/2 columns)
+  const int rsub = lane >> 2, csub = (lane & 3) * 2;
+  const long long g = tc.grp;
+  const int row0 = tc.m0 + q * 32 + rsub;
+  const int col0 = half * (BN / 2) + csub;
+  bool rok[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) rok[i] = row0 + 8 * i < p.M;
+  const float* bias = p.bias != nullptr ? p.bias + g * p.gs_bias + col0 : nullptr;
+  const float* gam = p.norm_gamma + g * p.gs_norm_param + col0;
+  const float* bet = p.norm_beta + g * p.gs_norm_param + col0;
+  const __nv_bfloat16* res = p.res != nullptr ? p.res + g * p.gs_res + (long long)row0 * p.ld_res + col0 : nullptr;
+  __nv_bfloat16* o16 = p.out_bf16 != nullptr ? p.out_bf16 + g * p.gs_bf16 + (long long)row0 * p.ldd_bf16 + col0 : nullptr;
+  __nv_bfloat16* n16 = p.norm_bf16 != nullptr ? p.norm_bf16 + g * p.gs_norm_bf16 + (long long)row0 * p.ld_norm_bf16 + col0 : nullptr;
+  float* n32 = p.norm_f32 != nullptr ? p.norm_f32 + g * p.gs_norm_f32 + (long long)row0 * p.ld_norm_f32 + col0 : nullptr;
+  const float alpha = p.alpha;
+
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
+  // the first chunk's bias / residual are requested before the accumulator is awaited (they overlap the main loop)
+  float2 b2[2][4];
+  uint32_t rx[2][4][4];
+  auto load_chunk = [&](int c, int slot) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      b2[slot][j] = bias != nullptr ? *reinterpret_cast<const float2*>(bias + c * 32 + 8 * j) : make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        rx[slot][i][j] = (res != nullptr && rok[i])
+                             ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
+                             : 0u;
+  };
+  load_chunk(0, 0);
+  mbar_wait(acc_full_bar, parity);
+  tc_fence_after();
+  // ---------------------------------------------------------------- sweep 1: pre-norm values + row statistics
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    uint32_t v[2][16];
+    tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+    tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
+    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
+        float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
+        s[i] += x0 + x1;
+        ss[i] = fmaf(x0, x0, fmaf(x1, x1, ss[i]));
+        if (o16 != nullptr && rok[i])
+          *reinterpret_cast<__nv_bfloat162*>(o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32 + 8 * j) = __floats2bfloat162_rn(x0, x1);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 1);
+    ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 1);
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 2);
+    ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 2);
+  }
+  if ((lane & 3) == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) stat[half * BM + q * 32 + rsub + 8 * i] = make_float2(s[i], ss[i]);
+  }
+  epi_pair_barrier(q);  // the two warps that share these 32 rows (column halves 0 / 1)
+  float mean[4], rstd[4];
+  const float inv_n = 1.f / static_cast<float>(BN);
+  const float inv_d = 1.f / static_cast<float>(p.norm_unbiased ? BN - 1 : BN);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 o = stat[(half ^ 1) * BM + q * 32 + rsub + 8 * i];
+    const float tot = s[i] + o.x, tots = ss[i] + o.y;
+    mean[i] = tot * inv_n;
+    const float var = fmaxf((tots - tot * mean[i]) * inv_d, 0.f);
+    rstd[i] = rsqrtf(var + p.norm_eps);
+  }
+  if (half == 0 && (lane & 3) == 0 && p.norm_mean != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (rok[i]) {
+        p.norm_mean[g * p.gs_norm_stat + row0 + 8 * i] = mean[i];
+        p.norm_rstd[g * p.gs_norm_stat + row0 + 8 * i] = rstd[i];
+      }
+    }
+  }
+  // ---------------------------------------------------------------- sweep 2: normalise, affine, ReLU, store
+  const float relu_floor = p.relu ? 0.f : -INFINITY;
+  load_chunk(0, 0);
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    uint32_t v[2][16];
+    tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+    tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
+    float2 g2[4], e2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      g2[j] = *reinterpret_cast<const float2*>(gam + c * 32 + 8 * j);
+      e2[j] = *reinterpret_cast<const float2*>(bet + c * 32 + 8 * j);
+    }
+    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (!rok[i]) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
+        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
+        const float y0 = fmaxf(fmaf((x0 - mean[i]) * rstd[i], g2[j].x, e2[j].x), relu_floor);
+        const float y1 = fmaxf(fmaf((x1 - mean[i]) * rstd[i], g2[j].y, e2[j].y), relu_floor);
+        if (n16 != nullptr)
+          *reinterpret_cast<__nv_bfloat162*>(n16 + (long long)(8 * i) * p.ld_norm_bf16 + c * 32 + 8 * j) = __floats2bfloat162_rn(y0, y1);
+        if (n32 != nullptr)
+          *reinterpret_cast<float2*>(n32 + (long long)(8 * i) * p.ld_norm_f32 + c * 32 + 8 * j) = make_float2(y0, y1);
+      }
+    }
+  }
+  // ---------------------------------------------------------------- zero halo rows around the sequence (group)
+  if (p.norm_halo > 0 && q == 0 && p.norm_bf16 != nullptr) {
+    __nv_bfloat16* base = p.norm_bf16 + g * p.gs_norm_bf16 + half * (BN / 2) + lane * 4;
+    if (tc.m0 == 0)
+      for (int h = 1; h <= p.norm_halo; ++h) *reinterpret_cast<uint2*>(base - (long long)h * p.ld_norm_bf16) = make_uint2(0u, 0u);
+    if (tc.m0 + BM >= p.M)
+      for (int h = 0; h < p.norm_halo; ++h)
+        *reinterpret_cast<uint2*>(base + (long long)(p.M + h) * p.ld_norm_bf16) = make_uint2(0u, 0u);
   }
 }
 

@@ -23,6 +23,7 @@ struct NceArgs {
   float* lse;            // [K][T]
   float* loss_sum;       // [K]  sum_rows w*ce
   float* hits;           // [K]  number of rows whose argmax is the positive
+  float out_scale;       // factor applied to what is added to loss_sum / hits
   const float* gscale;   // [K]  upstream gradient of each loss_k (backward)
   __nv_bfloat16* dlogits;  // [K][T][ld]
   __nv_bfloat16* dlogits_lo;  // optional residual: dlogits + dlogits_lo carries ~16 mantissa bits
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(256) nce_fwd_kernel(const NceArgs a) {
   __syncthreads();
   for (int i = threadIdx.x; i < 2 * a.K; i += blockDim.x) {
     const float x = acc[i];
-    if (x != 0.f) red_add_f32((i < a.K ? a.loss_sum + i : a.hits + (i - a.K)), x);
+    if (x != 0.f) red_add_f32((i < a.K ? a.loss_sum + i : a.hits + (i - a.K)), x * a.out_scale);
   }
 }
 
@@ -173,6 +174,7 @@ static int fill_nce(NceArgs& a, const CpcNce* d) {
   a.weights = static_cast<const float*>(d->weights);
   a.lse = static_cast<float*>(d->lse);
   a.loss_sum = static_cast<float*>(d->loss_sum); a.hits = static_cast<float*>(d->hits);
+  a.out_scale = d->out_scale != 0.f ? d->out_scale : 1.f;
   a.gscale = static_cast<const float*>(d->gscale);
   a.dlogits = static_cast<__nv_bfloat16*>(d->dlogits);
   a.dlogits_lo = static_cast<__nv_bfloat16*>(d->dlogits_lo);

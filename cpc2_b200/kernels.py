@@ -85,7 +85,7 @@ def _out(t):
 
 def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=None, out_bf16=None, bias=None,
          bias_gs=0, res=None, gate=None, gate_scale=1.0, relu=False, accumulate=False, rng=None, rng_site=0,
-         drop_p=0.0, force_bn=0, algo_flops=None):
+         drop_p=0.0, force_bn=0, algo_flops=None, norm=None):
     """cpc_gemm_bf16: D[g] = alpha * A_g . B_g^T (+ epilogue).  See include/cpc_b200.h.
     algo_flops: ALGORITHMIC work of the call when it differs from the executed 2*M*N*K*groups (the all-pairs logits
     products compute every (token, frame) pair where the algorithm needs NEG + 1 of them); profiling only."""
@@ -121,8 +121,21 @@ def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=N
     if rng is not None and drop_p > 0:
         d.rng, d.rng_site, d.drop_p = rng.data_ptr(), rng_site, drop_p
     d.relu, d.accumulate = int(relu), int(accumulate)
+    if norm is not None:  # fused ChannelNorm / LayerNorm of the output rows (N == 256), see CpcGemmDesc
+        d.norm_gamma, d.norm_beta, d.gs_norm_param = norm["gamma"].data_ptr(), norm["beta"].data_ptr(), norm.get("gs_param", 0)
+        t, ld, gs = _out(norm.get("out_bf16"))
+        if t is not None:
+            assert t.dtype == BF16
+            d.norm_bf16, d.ld_norm_bf16, d.gs_norm_bf16 = t.data_ptr() + 2 * norm.get("offset_bf16", 0), ld, gs
+        t, ld, gs = _out(norm.get("out_f32"))
+        if t is not None:
+            assert t.dtype == torch.float32
+            d.norm_f32, d.ld_norm_f32, d.gs_norm_f32 = t.data_ptr(), ld, gs
+        if norm.get("mean") is not None:
+            d.norm_mean, d.norm_rstd, d.gs_norm_stat = norm["mean"].data_ptr(), norm["rstd"].data_ptr(), norm.get("gs_stat", 0)
+        d.norm_eps, d.norm_unbiased, d.norm_halo = norm.get("eps", 1e-5), int(norm.get("unbiased", False)), norm.get("halo", 0)
     if PROFILE is not None:
-        ob = (4 if out_f32 is not None else 0) + (2 if out_bf16 is not None else 0)
+        ob = (4 if out_f32 is not None else 0) + (2 if out_bf16 is not None else 0) + (2 if norm is not None else 0)
         set_work(kind="tensor", flops=2.0 * M * N * K * groups if algo_flops is None else float(algo_flops),
                  executed_flops=2.0 * M * N * K * groups, bytes=2.0 * groups * (M * K + N * K) + ob * M * N * groups,
                  shape=f"g{groups} {M}x{N}x{K} a{A.major}b{B.major} s{k_splits}")
@@ -242,8 +255,8 @@ def groupsum(inp, n, groups, out_f32=None, out_bf16=None, accumulate=False):
                              int(accumulate), stream_ptr(),))
 
 
-def neg_ext_index(batch_idx, seq_idx, B, NEG, W, S):
-    ext = torch.empty_like(batch_idx)
+def neg_ext_index(batch_idx, seq_idx, B, NEG, W, S, out=None):
+    ext = torch.empty_like(batch_idx) if out is None else out
     _run("cpc_neg_ext_index", (ptr(batch_idx), ptr(seq_idx), ptr(ext), B, NEG, W, S, stream_ptr(),))
     return ext
 
@@ -255,9 +268,11 @@ def _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld):
     return d
 
 
-def nce_fwd(logits, ext, weights, lse, loss_sum, hits, K, B, W, S, NEG, ld):
+def nce_fwd(logits, ext, weights, lse, loss_sum, hits, K, B, W, S, NEG, ld, out_scale=1.0):
+    """loss_sum / hits (pre-zeroed) receive out_scale * their sums: out_scale = 1 / (B*W) yields the per-step mean
+    loss and accuracy of criterion.py:350-357 directly."""
     d = _nce(logits, ext, weights, lse, K, B, W, S, NEG, ld)
-    d.loss_sum, d.hits = _dp(loss_sum), _dp(hits)
+    d.loss_sum, d.hits, d.out_scale = _dp(loss_sum), _dp(hits), out_scale
     if PROFILE is not None:
         set_work(kind="hbm", bytes=4.0 * K * B * W * (NEG + 1) + 8.0 * B * NEG * W)
     _run("cpc_nce_fwd", (ctypes.byref(d), stream_ptr(),))

@@ -260,8 +260,15 @@ class _EncoderFn(torch.autograd.Function):
                 Lp = Lin + 2 * pd
                 y, a = ys[l], acts[l]
                 A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
+                hn = pad_next[l]  # halo rows of `a` are zeroed by the kernel that writes it
+                if ops.can_fuse_norm(C):
+                    # conv + bias -> y (kept for the backward), ChannelNorm + ReLU -> a, all in the GEMM epilogue
+                    K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b,
+                           relu=True, norm=dict(gamma=g.reshape(C), beta=be.reshape(C), out_bf16=(a, C, (Lout + 2 * hn) * C),
+                                                offset_bf16=hn * C, out_f32=(z32, C, Lout * C) if l == 4 else None,
+                                                mean=means[l], rstd=rstds[l], gs_stat=Lout, unbiased=True, halo=hn))
+                    continue
                 K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
-                hn = pad_next[l]  # halo rows of `a` are zeroed by the kernel (out_map)
                 K.rownorm_fwd(y, N * Lout, C, g.reshape(C), be.reshape(C), out_bf16=a, out_f32=z32 if l == 4 else None,
                               mean=means[l], rstd=rstds[l], out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True,
                               relu=True)

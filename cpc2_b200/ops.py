@@ -14,6 +14,13 @@ NUM_SMS = 148
 # Debug switch: keep the gradients that feed a normalisation backward in fp32 between kernels.  Measured to
 # make no difference to gradient parity (profiles/r01_grad_noise.log), so the default is bf16 (half the bytes).
 GRAD_F32 = False
+# ChannelNorm / LayerNorm of 256-wide rows inside the epilogue of the GEMM that produces them (one accumulator tile is
+# one whole row): no separate cpc_rownorm_fwd launch.  False restores the two-kernel form (also used for other widths).
+FUSE_NORM = os.environ.get("CPC_FUSE_NORM", "1") != "0"
+
+
+def can_fuse_norm(C):
+    return FUSE_NORM and C == 256
 
 
 # Callbacks invoked by the modules' backward right after every kernel writing a module's flat fp32 gradient

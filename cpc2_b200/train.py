@@ -99,6 +99,9 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
     prefetchWeights(cpcModel, cpcCriterion)
     past, future = sequence[:, 0, ...], sequence[:, 1, ...]
     b = past.size(0)
+    crit = getattr(cpcCriterion, "module", cpcCriterion)
+    if hasattr(crit, "prefetchIndices") and sequence.is_cuda:
+        crit.prefetchIndices(b, model_._geometry(b, sequence.shape[-1])[0][4], sequence.device)
     if SPLIT_PAST_FUTURE and isinstance(cpcModel, model_.CPCModel) and cpcModel.splittable():
         # same outputs and gradients as the concatenated call below, without its dead half (the AR over the
         # future windows, whose output train.py:102 drops) and with the two encoder halves overlapped

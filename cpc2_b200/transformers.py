@@ -281,24 +281,34 @@ class TransformerStack:
         att, sa = self._attn_fwd(qkv, P32.get("krel"), G, T, seq_len, rng, drop)
         pre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         res = (x, d, 0) if shared else x
-        ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res)
         y = torch.empty(G, T, d, device=dev, dtype=BF16)
         mean1 = torch.empty(G * T, device=dev)
         rstd1 = torch.empty(G * T, device=dev)
-        K.rownorm_fwd(pre1, G * T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
+        if ops.can_fuse_norm(d):  # y = LN(x + att . Wo^T) in the epilogue of the Wo product
+            ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res,
+                           norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], gs_param=d, out_bf16=y, mean=mean1, rstd=rstd1,
+                                     gs_stat=T))
+        else:
+            ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res)
+            K.rownorm_fwd(pre1, G * T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
         h1 = torch.empty(G, T, dff, device=dev, dtype=BF16)
         ops.linear_fwd(y, P16["W1"], T, dff, d, groups=G, out_bf16=h1, bias=P32["b1"], bias_gs=dff, relu=True,
                        rng=rng, rng_site=2, drop_p=drop)
         u = torch.empty(G, T, d, device=dev, dtype=BF16)
         ops.linear_fwd(h1, P16["W2"], T, d, dff, groups=G, out_bf16=u, bias=P32["b2"], bias_gs=d, res=y)
         pre2 = torch.empty(G, T, dout, device=dev, dtype=BF16)
-        ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout)
         out = torch.empty(G, T, dout, device=dev, dtype=BF16)
         out32 = torch.empty(G, T, dout, device=dev) if want_f32 else None
         mean2 = torch.empty(G * T, device=dev)
         rstd2 = torch.empty(G * T, device=dev)
-        K.rownorm_fwd(pre2, G * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
-                      rstd=rstd2, rows_per_group=T)
+        if ops.can_fuse_norm(dout):  # out = LN(u . Wl^T + bl) in the epilogue of the last_linear product
+            ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout,
+                           norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], gs_param=dout, out_bf16=out, out_f32=out32,
+                                     mean=mean2, rstd=rstd2, gs_stat=T))
+        else:
+            ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout)
+            K.rownorm_fwd(pre2, G * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
+                          rstd=rstd2, rows_per_group=T)
         saved = dict(x=x, shared=shared, T=T, P16=P16, P32=P32, rng=rng, drop=drop, sa=sa, att=att,
                      pre1=pre1, y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2,
                      rstd2=rstd2)
@@ -439,11 +449,15 @@ class MultiHeadStack(TransformerStack):
         ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=1, x_shared=True, out_bf16=qkv)
         att, sa = self._attn_fwd(qkv, P32.get("krel"), 1, T, seq_len, rng, drop)
         pre1 = torch.empty(1, T, d, device=dev, dtype=BF16)
-        ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0))
         y = torch.empty(T, d, device=dev, dtype=BF16)
         mean1 = torch.empty(T, device=dev)
         rstd1 = torch.empty(T, device=dev)
-        K.rownorm_fwd(pre1, T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
+        if ops.can_fuse_norm(d):
+            ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0),
+                           norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1))
+        else:
+            ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0))
+            K.rownorm_fwd(pre1, T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
         h1 = torch.empty(T, dff, device=dev, dtype=BF16)
         ops.linear_fwd(y, P16["W1"].view(dff, d), T, dff, d, out_bf16=h1, bias=P32["b1"], relu=True, rng=rng,
                        rng_site=2, drop_p=drop)
@@ -451,13 +465,18 @@ class MultiHeadStack(TransformerStack):
         ops.linear_fwd(h1, P16["W2"].view(Kc, d, dff), T, d, dff, groups=Kc, x_shared=True, out_bf16=u,
                        bias=P32["b2"], bias_gs=d, res=(y, d, 0))
         pre2 = torch.empty(Kc * T, dout, device=dev, dtype=BF16)
-        ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"])
         out = torch.empty(Kc, T, dout, device=dev, dtype=BF16)
         out32 = torch.empty(Kc, T, dout, device=dev) if want_f32 else None
         mean2 = torch.empty(Kc * T, device=dev)
         rstd2 = torch.empty(Kc * T, device=dev)
-        K.rownorm_fwd(pre2, Kc * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
-                      rstd=rstd2, rows_per_group=Kc * T)
+        if ops.can_fuse_norm(dout):
+            ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"],
+                           norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], out_bf16=out.view(Kc * T, dout),
+                                     out_f32=None if out32 is None else out32.view(Kc * T, dout), mean=mean2, rstd=rstd2))
+        else:
+            ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"])
+            K.rownorm_fwd(pre2, Kc * T, dout, P32["ln2w"], P32["ln2b"], out_bf16=out, out_f32=out32, mean=mean2,
+                          rstd=rstd2, rows_per_group=Kc * T)
         saved = dict(x=x, T=T, P16=P16, P32=P32, rng=rng, drop=drop, sa=sa, att=att, pre1=pre1,
                      y=y, mean1=mean1, rstd1=rstd1, h1=h1, u=u, pre2=pre2, mean2=mean2, rstd2=rstd2)
         return out, out32, saved

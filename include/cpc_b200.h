@@ -81,6 +81,19 @@ typedef struct {
   const void* rng; uint32_t rng_site; float drop_p; /* rng: device uint64[2] {seed, step}; inverted dropout */
   int relu;
   int accumulate;  /* out_f32 += result instead of = */
+  /* Fused row normalisation (norm_gamma != NULL): ChannelNorm (cpc/model.py:52-60, unbiased variance) / nn.LayerNorm
+   * (cpc/transformers.py:124,130) of every output row, applied to x = alpha*acc + bias (+ res) inside the epilogue --
+   * a 256-wide row is exactly one 128 x 256 accumulator tile, so its statistics never leave the SM.  Requires
+   * N == 256, K-major operands, no split-K / accumulate / gate / dropout.  out_bf16 (optional) receives the
+   * PRE-norm x (what the backward needs); the normalised rows y = (x - mean) * rstd * gamma + beta (ReLU if relu) go
+   * to norm_bf16 / norm_f32; mean / rstd fp32 [groups][M] (gs_stat apart).  norm_halo > 0: the norm_bf16 buffer of
+   * every group carries that many extra rows in front of row 0 and behind row M-1 (the zero padding of the next
+   * strided conv); the kernel clears them. */
+  const void* norm_gamma; const void* norm_beta; int64_t gs_norm_param; /* fp32 [groups][N] */
+  void* norm_bf16; int64_t ld_norm_bf16, gs_norm_bf16;
+  void* norm_f32;  int64_t ld_norm_f32,  gs_norm_f32;
+  void* norm_mean; void* norm_rstd; int64_t gs_norm_stat;
+  float norm_eps; int norm_unbiased; int norm_halo;
 } CpcGemmDesc;
 
 int cpc_gemm_bf16(const CpcGemmDesc* desc, void* stream);
@@ -202,6 +215,7 @@ typedef struct {
   void* lse; void* loss_sum; void* hits;
   const void* gscale; void* dlogits;
   void* dlogits_lo; /* optional bf16 residual (dlogits_f32 - dlogits), same shape; null to skip */
+  float out_scale;  /* fwd: loss_sum / hits receive out_scale * (their sums); 0 => 1 (1/(B*W) yields the means directly) */
 } CpcNce;
 
 int cpc_nce_fwd(const CpcNce* desc, void* stream);

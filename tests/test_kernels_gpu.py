@@ -41,6 +41,45 @@ def cos(a, b):
 
 
 # ------------------------------------------------------------------------------------------ GEMM
+@pytest.mark.parametrize("G,M,Kd,unbiased,relu,with_res,halo", [(3, 300, 192, True, True, False, 2), (2, 928, 256, False, False, True, 0),
+                                                                (1, 128, 2048, True, True, False, 1), (5, 37, 64, False, False, True, 0)])
+def test_gemm_fused_row_norm(K, G, M, Kd, unbiased, relu, with_res, halo):
+    """EPI_NORM: ChannelNorm (unbiased variance, cpc/model.py:52-60) / LayerNorm (cpc/transformers.py:124,130) of the
+    256-wide output rows inside the GEMM epilogue, against fp32 torch on the same bf16 operands: pre-norm rows, the
+    normalised rows (bf16 and fp32), mean / rstd, and the zero halo rows around every group."""
+    torch.manual_seed(2)
+    N = 256
+    a = bf(torch.randn(G, M, Kd, device="cuda"))
+    w = bf(torch.randn(G, N, Kd, device="cuda") / Kd ** 0.5)
+    bias = torch.randn(G, N, device="cuda")
+    gamma = 1 + 0.1 * torch.randn(G, N, device="cuda")
+    beta = 0.1 * torch.randn(G, N, device="cuda")
+    res = bf(torch.randn(G, M, N, device="cuda")) if with_res else None
+    pre = torch.empty(G, M, N, device="cuda", dtype=BF)
+    yb = torch.full((G, M + 2 * halo, N), 7.0, device="cuda", dtype=BF)
+    y32 = torch.empty(G, M, N, device="cuda")
+    mean = torch.empty(G * M, device="cuda")
+    rstd = torch.empty(G * M, device="cuda")
+    K.gemm(K.kmajor(a), K.kmajor(w), M, N, Kd, groups=G, out_bf16=pre, bias=bias, bias_gs=N, res=res, relu=relu,
+           norm=dict(gamma=gamma, beta=beta, gs_param=N, out_bf16=(yb, N, (M + 2 * halo) * N), offset_bf16=halo * N,
+                     out_f32=y32, mean=mean, rstd=rstd, gs_stat=M, unbiased=unbiased, halo=halo))
+    x = torch.einsum("gmk,gnk->gmn", a.float(), w.float()) + bias[:, None, :]
+    if with_res:
+        x = x + res.float()
+    mu = x.mean(-1, keepdim=True)
+    var = x.var(-1, unbiased=unbiased, keepdim=True)
+    ref = (x - mu) * torch.rsqrt(var + 1e-5) * gamma[:, None, :] + beta[:, None, :]
+    if relu:
+        ref = ref.relu()
+    close(pre, x, 1e-2, 1e-2, "pre-norm")
+    close(mean.view(G, M), mu.squeeze(-1), 1e-4, 1e-4, "mean")
+    close(rstd.view(G, M), torch.rsqrt(var + 1e-5).squeeze(-1), 1e-3, 1e-5, "rstd")
+    close(y32, ref, 1e-3, 2e-3, "norm f32")
+    close(yb[:, halo:halo + M], ref, 1e-2, 1e-2, "norm bf16")
+    if halo:
+        assert float(yb[:, :halo].float().abs().max()) == 0 and float(yb[:, halo + M:].float().abs().max()) == 0
+
+
 @pytest.mark.parametrize("M,N,Kd", [(128, 64, 64), (300, 256, 192), (928, 768, 256), (100, 32, 32)])
 def test_gemm_nt(K, M, N, Kd):
     torch.manual_seed(0)
