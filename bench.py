@@ -539,7 +539,7 @@ def run_ours(opt, out):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2_flush_between_steps": True, "cuda_graph": True, "dropout": "train mode (p=0.1 in the heads)",
-                   "programmatic_dependent_launch": os.environ.get("CPC_PDL", "1") != "0",
+                   "programmatic_dependent_launch": os.environ.get("CPC_PDL", "0") == "1",
                    "optimizer": "fused multi-tensor Adam (cpc_adam_step) inside the timed step, per bucket after its all-reduce",
                    "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0,
                    "grad_allreduce": ("none" if world == 1 else "cpc_allreduce_mc (NVSwitch multimem, in place)"

@@ -185,6 +185,7 @@ class Attn(ctypes.Structure):
         ("out", ctypes.c_void_p), ("gs_out", ctypes.c_int64), ("probs", ctypes.c_void_p),
         ("rng", ctypes.c_void_p), ("rng_site", ctypes.c_uint32), ("drop_p", ctypes.c_float),
         ("dout", ctypes.c_void_p), ("dqkv", ctypes.c_void_p), ("dscore", ctypes.c_void_p), ("dkrel", ctypes.c_void_p),
+        ("out_f32", ctypes.c_void_p),
     ]
 
 

@@ -20,12 +20,12 @@ PFN_encodeTiled get_encode_tiled() {
   return fn;
 }
 
-static int g_pdl = -1;  // -1: not decided yet (environment CPC_PDL, default on)
+static int g_pdl = -1;  // -1: not decided yet (environment CPC_PDL; default off, see cpc_internal.h)
 
 bool pdl_enabled() {
   if (g_pdl < 0) {
     const char* e = getenv("CPC_PDL");
-    g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+    g_pdl = (e != nullptr && e[0] == '1') ? 1 : 0;
   }
   return g_pdl != 0;
 }

@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(256) attn_fwd_kernel(const AttnArgs a) {
       float acc = 0.f;
       for (int j = 0; j <= i; ++j) acc = fmaf(p[j], ldf(&V[j * DP + c]), acc);
       a.out[(long long)g * a.gs_out + ((long long)b * S + i) * a.d + h * dk + c] = __float2bfloat16(acc);
+      if (a.out_f32 != nullptr) a.out_f32[(long long)g * a.gs_out + ((long long)b * S + i) * a.d + h * dk + c] = acc;
     }
     __syncwarp();
   }
@@ -140,7 +141,8 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(const AttnArgs a) {
   for (int i = warp; i < S; i += 8) {
     float dsum = 0.f;
     for (int c = lane; c < dk; c += 32)
-      dsum += ldf(&dO[i * DP + c]) * __bfloat162float(a.out[obase + (long long)i * a.d + c]);
+      dsum += ldf(&dO[i * DP + c]) * (a.out_f32 != nullptr ? a.out_f32[obase + (long long)i * a.d + c]
+                                                           : __bfloat162float(a.out[obase + (long long)i * a.d + c]));
     dsum = warp_sum(dsum);  // D_i = dO_i . O_i = sum_j p~_ij dp~_ij
     for (int j = lane; j <= i; j += 32) {
       float dp = 0.f;
@@ -214,6 +216,7 @@ static int fill_attn(AttnArgs& a, const CpcAttn* d) {
   a.qkv = static_cast<const __nv_bfloat16*>(d->qkv); a.gs_qkv = d->gs_qkv;
   a.krel = static_cast<const float*>(d->krel);
   a.out = static_cast<__nv_bfloat16*>(d->out); a.gs_out = d->gs_out;
+  a.out_f32 = static_cast<float*>(d->out_f32);
   a.probs = static_cast<__nv_bfloat16*>(d->probs);
   a.S = d->S; a.dk = d->dk; a.d = d->dk * d->Hh; a.Bt = d->Bt; a.Hh = d->Hh;
   a.scale = d->scale;

@@ -271,13 +271,18 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
       }
     }
     __nv_bfloat16* ob = a.out + (long long)grp * a.gs_out + (long long)b * S * d + h * DK;
+    float* of = a.out_f32 != nullptr ? a.out_f32 + (long long)grp * a.gs_out + (long long)b * S * d + h * DK : nullptr;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int c = nt * 8 + 2 * t;
-      if (i0 + g < S)
+      if (i0 + g < S) {
         *reinterpret_cast<__nv_bfloat162*>(ob + (long long)(i0 + g) * d + c) = __floats2bfloat162_rn(o[nt][0], o[nt][1]);
-      if (i0 + g + 8 < S)
+        if (of != nullptr) *reinterpret_cast<float2*>(of + (long long)(i0 + g) * d + c) = make_float2(o[nt][0], o[nt][1]);
+      }
+      if (i0 + g + 8 < S) {
         *reinterpret_cast<__nv_bfloat162*>(ob + (long long)(i0 + g + 8) * d + c) = __floats2bfloat162_rn(o[nt][2], o[nt][3]);
+        if (of != nullptr) *reinterpret_cast<float2*>(of + (long long)(i0 + g + 8) * d + c) = make_float2(o[nt][2], o[nt][3]);
+      }
     }
   }
 }
@@ -312,7 +317,23 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
   // D_i = dO_i . O_i  (= sum_j P~_ij dP~_ij), straight from global memory while the tiles are in flight
   for (int i = threadIdx.x; i < SP; i += ATT_THREADS) {
     float acc = 0.f;
-    if (i < S) {
+    if (i < S && a.out_f32 != nullptr) {  // O in fp32 (see CpcAttn.out_f32): D keeps its precision for peaked rows
+      const float* orow = a.out_f32 + obase + (long long)i * d;
+      const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
+      float4 ov[DK / 4];
+      uint4 dv[DK / 8];
+#pragma unroll
+      for (int ch = 0; ch < DK / 4; ++ch) ov[ch] = *reinterpret_cast<const float4*>(orow + ch * 4);
+#pragma unroll
+      for (int ch = 0; ch < DK / 8; ++ch) dv[ch] = *reinterpret_cast<const uint4*>(drow + ch * 8);
+#pragma unroll
+      for (int ch = 0; ch < DK / 8; ++ch) {
+        const uint32_t* d2 = reinterpret_cast<const uint32_t*>(&dv[ch]);
+        acc += ov[2 * ch].x * bf16lo(d2[0]) + ov[2 * ch].y * bf16hi(d2[0]) + ov[2 * ch].z * bf16lo(d2[1]) + ov[2 * ch].w * bf16hi(d2[1]);
+        acc += ov[2 * ch + 1].x * bf16lo(d2[2]) + ov[2 * ch + 1].y * bf16hi(d2[2]) + ov[2 * ch + 1].z * bf16lo(d2[3]) +
+               ov[2 * ch + 1].w * bf16hi(d2[3]);
+      }
+    } else if (i < S) {
       const __nv_bfloat16* orow = a.out + obase + (long long)i * d;
       const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
       uint4 ov[DK / 8], dv[DK / 8];

@@ -29,7 +29,11 @@ inline int launch_status() { return cudaGetLastError() == cudaSuccess ? CPC_OK :
 // up next to this kernel's.  Triggering only after the own wait bounds the chain to one early-launched kernel at a
 // time (its idle CTAs do not crowd out side-stream work).  Both instructions are no-ops in a grid launched without the
 // attribute, and the attribute degrades to a normal dependency after a memset / copy / foreign kernel; inside a
-// stream capture the edges become programmatic graph edges.  cpc_set_pdl(0) / CPC_PDL=0 turns the attribute off.
+// stream capture the edges become programmatic graph edges.
+// MEASURED (profiles/r02_bench_pdl.txt): inside the step's CUDA graph consecutive kernel nodes already start back to
+// back (gaps of ~0.1 us in the replay timeline), so PDL has only the prologues left to hide and the early CTAs it
+// parks on the SMs take room from the side-stream kernels: 1.165 ms/step with PDL against 1.153 ms without.  The
+// attribute is therefore OFF by default; cpc_set_pdl(1) / CPC_PDL=1 turns it on (every GPU test passes either way).
 bool pdl_enabled();
 
 #ifdef __CUDACC__

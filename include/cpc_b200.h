@@ -38,7 +38,8 @@ const char* cpc_strerror(int status);
 int cpc_version(void);
 /* compute capability major*10+minor of the current device, or a negative status */
 int cpc_device_arch(void);
-/* Programmatic dependent launch of every kernel of the library (default on; environment CPC_PDL=0 turns it off).
+/* Programmatic dependent launch of every kernel of the library (default off -- measured neutral inside the step's
+ * CUDA graph; environment CPC_PDL=1 turns it on).
  * Returns the previous setting.  No reference counterpart: launch plumbing of the sm_100a path. */
 int cpc_set_pdl(int on);
 
@@ -255,6 +256,10 @@ typedef struct {
   void* out; int64_t gs_out; void* probs;
   const void* rng; uint32_t rng_site; float drop_p;
   const void* dout; void* dqkv; void* dscore; void* dkrel;
+  /* optional fp32 copy of `out` ([G][Bt*S][d], group stride gs_out): written by fwd, read by bwd for the row statistic
+   * D_i = dO_i . O_i.  With O rounded to bf16 the rounding error of D is coherent along a row and, once the softmax is
+   * peaked (trained models), no longer small next to dP_ij - D_i: the Wq / Wk gradients lose two digits. */
+  void* out_f32;
 } CpcAttn;
 
 int cpc_attn_fwd(const CpcAttn* desc, void* stream);

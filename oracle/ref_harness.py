@@ -27,6 +27,7 @@ import torch
 
 REFERENCE_ROOT = os.environ.get("CPC2_REFERENCE_ROOT", "/root/reference")
 ARCHIVE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "cpc_reference.zip")
+ONES_ON_CPU = False
 
 
 def reference_location():
@@ -53,11 +54,13 @@ def import_reference():
             setattr(ta, cls, type(cls, (), {}))
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
-    if not torch.cuda.is_available() and not getattr(torch.ones, "_cpc_shim", False):
+    if not getattr(torch.ones, "_cpc_shim", False):
         _ones = torch.ones
 
         def ones(*a, **kw):
-            if str(kw.get("device", "")) == "cuda":
+            # criterion.py:340 hard-codes device='cuda': on a host without CUDA, or while the reference is being run
+            # on the CPU of a GPU box (ONES_ON_CPU, set by timed_reference_steps(device="cpu")), that means 'cpu'
+            if str(kw.get("device", "")) == "cuda" and (ONES_ON_CPU or not torch.cuda.is_available()):
                 kw["device"] = "cpu"
             return _ones(*a, **kw)
 
@@ -129,9 +132,11 @@ def timed_reference_steps(over, B, steps, warmup, device="cpu", autocast=None, t
     forward in torch.autocast like mixed-precision users of the reference would; `tf32` sets the cuBLAS / cuDNN
     TF32 switches (the reference pins torch 1.3 where they did not exist; on Ampere+ TF32 convs are the default)."""
     import time
+    global ONES_ON_CPU
     args = reference_args(**over)
     m, crit = build_reference(args, seed=seed)
     dev = torch.device(device)
+    ONES_ON_CPU = dev.type == "cpu"
     m, crit = m.to(dev).train(), crit.to(dev).train()
     g = torch.Generator().manual_seed(1234)
     seq = (0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=g)).to(dev)
@@ -167,9 +172,12 @@ def timed_reference_steps(over, B, steps, warmup, device="cpu", autocast=None, t
         e1.record()
         torch.cuda.synchronize()
         wall = (time.perf_counter() - t0) / steps
-        return e0.elapsed_time(e1) * 1e-3 / steps, float(losses.mean()), wall
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        losses = one()
-    sec = (time.perf_counter() - t0) / steps
-    return sec, float(losses.mean()), sec
+        return e0.elapsed_time(e1) * 1e-3 / steps, float(losses.detach().mean()), wall
+    try:
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            losses = one()
+        sec = (time.perf_counter() - t0) / steps
+    finally:
+        ONES_ON_CPU = False
+    return sec, float(losses.detach().mean()), sec
