@@ -579,6 +579,11 @@ def run_ours(opt, out):
                 raise  # (ranks must stay in lock step: fail loudly instead of desynchronising the collectives)
             return {"error": f"{type(e).__name__}: {str(e)[:300]}"}
 
+    if opt.headline_only:
+        if rank == 0:
+            out.emit(json.dumps(line))
+        finish(ctx)
+        return
     configs = {}
     configs["config3_transformer_ar"] = guarded(
         measure_extra_config, ctx, "CPC with transformer AR (1 layer, sizeSeq 128, rel-pos; feature_loader.py:216-220), "
@@ -600,7 +605,11 @@ def run_ours(opt, out):
         line["cpu_baseline"] = guarded(cpu_baseline, args, B, 2, 1)
     if rank == 0:
         out.emit(json.dumps(line))
-    if world > 1:
+    finish(ctx)
+
+
+def finish(ctx):
+    if ctx.world > 1:
         # every captured graph (they hold NCCL launches) has been closed above, so the communicator can be torn down
         # normally; a watchdog turns a teardown that still blocks into a clean exit instead of a hung job
         ctx.barrier()
@@ -633,6 +642,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quick", action="store_true", help="fewer steps / sweep corners in the extra sections")
+    ap.add_argument("--headline-only", action="store_true", help="skip configs / dropin / stock_gpu / cpu_baseline (A/B runs)")
     opt = ap.parse_args()
     out = StdoutToStderr()
     if opt.impl == "reference":
