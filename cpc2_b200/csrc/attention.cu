@@ -139,18 +139,25 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(const AttnArgs a) {
 
   // ---- phase A: one warp per query row: dS row, dQ row
   for (int i = warp; i < S; i += 8) {
-    float dsum = 0.f;
-    for (int c = lane; c < dk; c += 32)
-      dsum += ldf(&dO[i * DP + c]) * (a.out_f32 != nullptr ? a.out_f32[obase + (long long)i * a.d + c]
-                                                           : __bfloat162float(a.out[obase + (long long)i * a.d + c]));
-    dsum = warp_sum(dsum);  // D_i = dO_i . O_i = sum_j p~_ij dp~_ij
+    // D_i = sum_j p_ij dp~_ij / sum_j p_ij from the same (bf16) p and the same dp the row's dS uses: the row of dS
+    // then sums to zero to fp32 rounding (see attention_tc.cu: dO_i . O_i is only as accurate as the stored O)
+    float dsum = 0.f, psum = 0.f;
     for (int j = lane; j <= i; j += 32) {
       float dp = 0.f;
       for (int c = 0; c < dk; ++c) dp = fmaf(ldf(&dO[i * DP + c]), ldf(&Vt[c * SP + j]), dp);
       const long long e = pbase + (long long)i * S + j;
       if (thresh != 0) dp = rng_u32(seed, a.site, e) >= thresh ? dp * dscale : 0.f;
       const float pr = __bfloat162float(a.probs[e]);
-      const float v = pr * (dp - dsum) * a.scale;
+      ds[j] = dp;
+      dsum = fmaf(pr, dp, dsum);
+      psum += pr;
+    }
+    dsum = warp_sum(dsum);
+    psum = warp_sum(psum);
+    dsum = psum > 0.f ? dsum / psum : 0.f;
+    for (int j = lane; j <= i; j += 32) {
+      const long long e = pbase + (long long)i * S + j;
+      const float v = __bfloat162float(a.probs[e]) * (ds[j] - dsum) * a.scale;
       ds[j] = v;
       a.dscore[e] = __float2bfloat16(v);
     }

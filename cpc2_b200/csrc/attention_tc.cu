@@ -314,44 +314,12 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
   load_rows_async<DK, SP, ATT_THREADS>(Vs, base + 2 * d, 3 * d, S);
   load_rows_async<DK, SP, ATT_THREADS>(dOs, a.dout + obase, d, S);
   cp_async_commit();
-  // D_i = dO_i . O_i  (= sum_j P~_ij dP~_ij), straight from global memory while the tiles are in flight
-  for (int i = threadIdx.x; i < SP; i += ATT_THREADS) {
-    float acc = 0.f;
-    if (i < S && a.out_f32 != nullptr) {  // O in fp32 (see CpcAttn.out_f32): D keeps its precision for peaked rows
-      const float* orow = a.out_f32 + obase + (long long)i * d;
-      const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
-      float4 ov[DK / 4];
-      uint4 dv[DK / 8];
-#pragma unroll
-      for (int ch = 0; ch < DK / 4; ++ch) ov[ch] = *reinterpret_cast<const float4*>(orow + ch * 4);
-#pragma unroll
-      for (int ch = 0; ch < DK / 8; ++ch) dv[ch] = *reinterpret_cast<const uint4*>(drow + ch * 8);
-#pragma unroll
-      for (int ch = 0; ch < DK / 8; ++ch) {
-        const uint32_t* d2 = reinterpret_cast<const uint32_t*>(&dv[ch]);
-        acc += ov[2 * ch].x * bf16lo(d2[0]) + ov[2 * ch].y * bf16hi(d2[0]) + ov[2 * ch].z * bf16lo(d2[1]) + ov[2 * ch].w * bf16hi(d2[1]);
-        acc += ov[2 * ch + 1].x * bf16lo(d2[2]) + ov[2 * ch + 1].y * bf16hi(d2[2]) + ov[2 * ch + 1].z * bf16lo(d2[3]) +
-               ov[2 * ch + 1].w * bf16hi(d2[3]);
-      }
-    } else if (i < S) {
-      const __nv_bfloat16* orow = a.out + obase + (long long)i * d;
-      const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
-      uint4 ov[DK / 8], dv[DK / 8];
-#pragma unroll
-      for (int ch = 0; ch < DK / 8; ++ch) {
-        ov[ch] = *reinterpret_cast<const uint4*>(orow + ch * 8);
-        dv[ch] = *reinterpret_cast<const uint4*>(drow + ch * 8);
-      }
-#pragma unroll
-      for (int ch = 0; ch < DK / 8; ++ch) {
-        const uint32_t* o2 = reinterpret_cast<const uint32_t*>(&ov[ch]);
-        const uint32_t* d2 = reinterpret_cast<const uint32_t*>(&dv[ch]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) acc += bf16lo(o2[k]) * bf16lo(d2[k]) + bf16hi(o2[k]) * bf16hi(d2[k]);
-      }
-    }
-    Dsm[i] = acc;
-  }
+  // D_i = sum_j P_ij dP~_ij / sum_j P_ij is formed in the row pass from the SAME bf16 P and the SAME dP (identical
+  // MMA sequence) that dS = P o (dP~ - D) uses, so every row of dS sums to zero to fp32 rounding.  The flash-attention
+  // shortcut D_i = dO_i . O_i is only as good as O: in trained models K and V carry a large component common to all
+  // keys, dP_ij is nearly constant along a row, and the 2^-17 mismatch between O and the recomputed dP leaked,
+  // multiplied by that common component, into dQ (cosine 0.4-0.95 on Wq gradients away from init).
+  for (int i = threadIdx.x; i < SP; i += ATT_THREADS) Dsm[i] = 0.f;
   if (rel) {
     const float* kr = a.krel + (long long)grp * DK * S;
 #pragma unroll 8
@@ -401,7 +369,47 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) dq[nt][e] = 0.f;
-    const float Di[2] = {Dsm[i0 + g], Dsm[i0 + g + 8]};
+    float Di[2];
+    {
+      float dsum[2] = {0.f, 0.f}, psum[2] = {0.f, 0.f};
+#pragma unroll
+      for (int jt = 0; jt < NJ; ++jt) {
+        if (jt < njt) {
+          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int ks = 0; ks < KS; ++ks) {
+            uint32_t bb[2];
+            ldsm_x2(bb, smem_u32(Vs + (jt * 8 + (lane & 7)) * PD + ks * 16 + ((lane >> 3) & 1) * 8));
+            mma_bf16_16816(acc, ado[ks], bb[0], bb[1]);
+          }
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            const int i = i0 + g + 8 * r, j = jt * 8 + 2 * t;
+            if (i < S && j <= i) {
+              const float p0 = bf16lo(pv[jt][r]), p1 = bf16hi(pv[jt][r]);  // p1 = 0 outside the triangle
+              float dp0 = acc[2 * r], dp1 = j + 1 <= i ? acc[2 * r + 1] : 0.f;
+              if (drop.thresh != 0) {
+                bool k0, k1;
+                keep_pair(drop, rbase + i, j, k0, k1);
+                dp0 = k0 ? dp0 * drop.scale : 0.f;
+                dp1 = k1 ? dp1 * drop.scale : 0.f;
+              }
+              dsum[r] += p0 * dp0 + p1 * dp1;
+              psum[r] += p0 + p1;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        dsum[r] += __shfl_xor_sync(0xffffffffu, dsum[r], 1);
+        dsum[r] += __shfl_xor_sync(0xffffffffu, dsum[r], 2);
+        psum[r] += __shfl_xor_sync(0xffffffffu, psum[r], 1);
+        psum[r] += __shfl_xor_sync(0xffffffffu, psum[r], 2);
+        Di[r] = psum[r] > 0.f ? dsum[r] / psum[r] : 0.f;
+        if (t == 0) Dsm[i0 + g + 8 * r] = Di[r];  // for the column pass
+      }
+    }
 #pragma unroll
     for (int kk = 0; kk < NB; ++kk) {
       if (2 * kk < njt) {
@@ -508,6 +516,7 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
     }
   }
 
+  __syncthreads();  // every row block's D is in Dsm
   // ------------------------------------------------------------------ column pass: dK, dV
   for (int pass = 0; pass < NB / ATT_WARPS; ++pass) {
     // multi-pass: long columns first; single pass: column block w costs NB - w, row block w cost w + 1 (balanced)

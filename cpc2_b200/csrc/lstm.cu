@@ -29,6 +29,22 @@ namespace cpc {
 
 __device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 __device__ __forceinline__ float tanh_f(float x) { return 2.f * __fdividef(1.f, 1.f + __expf(-2.f * x)) - 1.f; }
+// sigmoid(x) and its derivative s(1-s) = sigmoid(x) sigmoid(-x); tanh(x) and 1 - tanh^2 = 4 sigmoid(2x) sigmoid(-2x).
+// Formed from exp(-|x|) so that the SMALL factor keeps its relative precision in saturation: the backward reads the
+// gate PRE-activations (bf16) and recomputes the gates, because a post-activation gate rounded to bf16 has lost
+// 1 - s (and 1 - tanh^2) entirely once |x| > 6 -- gradients of saturated units came out as exact zeros.
+__device__ __forceinline__ void sigmoid_d(float x, float& s, float& sn) {
+  const float e = __expf(-fabsf(x));
+  const float a = __fdividef(1.f, 1.f + e), b = e * a;
+  s = x >= 0.f ? a : b;
+  sn = x >= 0.f ? b : a;  // 1 - s
+}
+__device__ __forceinline__ void tanh_d(float x, float& th, float& d) {
+  const float e = __expf(-2.f * fabsf(x));
+  const float a = __fdividef(1.f, 1.f + e);
+  th = copysignf((1.f - e) * a, x);
+  d = 4.f * e * a * a;  // 1 - th^2
+}
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 lo, __nv_bfloat16 hi) {
   return static_cast<uint32_t>(__bfloat16_as_ushort(lo)) | (static_cast<uint32_t>(__bfloat16_as_ushort(hi)) << 16);
 }
@@ -41,7 +57,7 @@ struct LstmArgs {
   const float* c0;            // [N, H] or null
   __nv_bfloat16* h_pad;       // [N, S+1, H] bf16, row 0 = h0, row t+1 = h_t (operand of the dW_hh GEMM)
   float* out;                 // [N, S, H] fp32 module output (optional)
-  __nv_bfloat16* gates;       // [N, S, 4H] bf16 post-activation i,f,g,o (saved for backward; optional)
+  __nv_bfloat16* gates;       // [N, S, 4H] bf16 gate PRE-activations i,f,g,o (GRU: r, z, n, W_hn h; saved for backward; optional)
   float* c_all;               // [N, S, H] fp32 cell states (saved for backward; optional)
   float* h_n;                 // [N, H] final hidden (optional)
   float* c_n;                 // [N, H]
@@ -68,7 +84,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
   __shared__ __align__(16) __nv_bfloat16 st_h[2][NB][40];         // this CTA's new h slice (bf16): DSMEM push, h_pad
   __shared__ __align__(16) float st_o[2][NB][36];                 // ... fp32 (module output)
   __shared__ __align__(16) float st_c[2][NB][36];                 // new cell state
-  __shared__ __align__(16) __nv_bfloat16 st_g[2][NB][136];        // post-activation gates i|f|g|o
+  __shared__ __align__(16) __nv_bfloat16 st_g[2][NB][136];        // gate pre-activations i|f|g|o
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t cta = cluster_ctarank();
@@ -186,10 +202,10 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_fwd_kernel(const LstmArg
     st_h[p][bsel][unit_l] = __float2bfloat16(hn);
     st_o[p][bsel][unit_l] = hn;
     st_c[p][bsel][unit_l] = cn;
-    st_g[p][bsel][unit_l] = __float2bfloat16(ig);
-    st_g[p][bsel][32 + unit_l] = __float2bfloat16(fg);
-    st_g[p][bsel][64 + unit_l] = __float2bfloat16(gg);
-    st_g[p][bsel][96 + unit_l] = __float2bfloat16(og);
+    st_g[p][bsel][unit_l] = __float2bfloat16(pi);
+    st_g[p][bsel][32 + unit_l] = __float2bfloat16(pf);
+    st_g[p][bsel][64 + unit_l] = __float2bfloat16(CELL == CELL_GRU ? pg + ig * po : pg);
+    st_g[p][bsel][96 + unit_l] = __float2bfloat16(po);
     cp_async_wait<1>();  // gx of step t+1 has landed (only the newest group may be in flight)
     __syncthreads();
     if (t + 1 < a.S) {
@@ -336,11 +352,21 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     prefetch(sidx + 2);
     // everything that does not depend on the recurrence first
     const __nv_bfloat16* gp = in_g + (buf * NB + bsel) * GP + unit_l;
-    const float gi = __bfloat162float(gp[0]), gf = __bfloat162float(gp[32]), gg = __bfloat162float(gp[64]),
-                go = __bfloat162float(gp[96]);
+    const float xi = __bfloat162float(gp[0]), xf = __bfloat162float(gp[32]), xg = __bfloat162float(gp[64]),
+                xo = __bfloat162float(gp[96]);  // pre-activations
     const float cprev = in_c[(buf * NB + bsel) * CP + unit_l];
     float dh = in_d[(buf * NB + bsel) * CP + unit_l];
-    const float tc = tanh_f(ct);
+    float gi, gin, gf, gfn, gg, ggd, go, gon, tc, tcd;  // gate, complement (sigmoid) / 1 - gate^2 (tanh)
+    if constexpr (CELL == CELL_LSTM) {
+      sigmoid_d(xi, gi, gin); sigmoid_d(xf, gf, gfn); tanh_d(xg, gg, ggd); sigmoid_d(xo, go, gon);
+      tanh_d(ct, tc, tcd);
+    } else if constexpr (CELL == CELL_GRU) {
+      sigmoid_d(xi, gi, gin); sigmoid_d(xf, gf, gfn); tanh_d(xg, gg, ggd);
+      go = xo; gon = 0.f; tc = 0.f; tcd = 0.f;
+    } else {
+      tanh_d(xi, gi, gin);  // gin = 1 - h_t^2
+      gf = gfn = gg = ggd = go = gon = tc = tcd = 0.f;
+    }
     if (sidx > 0) {
       mbar_wait(&bar[pp], ((sidx - 1) >> 1) & 1);
       const float* pr = P + ((pp * CL) * 32 + unit_l) * NB + bsel;
@@ -353,22 +379,22 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     float d_i = 0.f, d_f = 0.f, d_g = 0.f, d_o = 0.f;
     if (valid) {
       if constexpr (CELL == CELL_LSTM) {
-        d_o = dh * tc * go * (1.f - go);
-        const float dc = dh * go * (1.f - tc * tc) + dc_state;
-        d_i = dc * gg * gi * (1.f - gi);
-        d_f = dc * cprev * gf * (1.f - gf);
-        d_g = dc * gi * (1.f - gg * gg);
+        d_o = dh * tc * go * gon;
+        const float dc = dh * go * tcd + dc_state;
+        d_i = dc * gg * gi * gin;
+        d_f = dc * cprev * gf * gfn;
+        d_g = dc * gi * ggd;
         dc_state = dc * gf;
       } else if constexpr (CELL == CELL_GRU) {
-        // saved slots: r = gi, z = gf, n = gg, hn = W_hn h + b_hn = go; cprev = h_{t-1}
+        // saved slots: r, z, n pre-activations and hn = W_hn h + b_hn = go; cprev = h_{t-1}
         dh += dc_state;                                   // the z-gated path h_{t-1} -> h_t stays in this thread
-        d_g = dh * (1.f - gf) * (1.f - gg * gg);          // d n_pre (input side)
-        d_f = dh * (cprev - gg) * gf * (1.f - gf);        // d z_pre
-        d_i = d_g * go * gi * (1.f - gi);                 // d r_pre
+        d_g = dh * gfn * ggd;                             // d n_pre (input side)
+        d_f = dh * (cprev - gg) * gf * gfn;               // d z_pre
+        d_i = d_g * go * gi * gin;                        // d r_pre
         d_o = d_g * gi;                                   // d (W_hn h + b_hn) (hidden side of the n gate)
         dc_state = dh * gf;
       } else {
-        d_i = dh * (1.f - gi * gi);                       // saved slot 0 = h_t
+        d_i = dh * gin;                                   // saved slot 0 = pre-activation of h_t
       }
     }
     ct = cprev;

@@ -245,11 +245,9 @@ class TransformerStack:
             qkv_k = qkv
         att_k = torch.empty(G, N * nb * S, d, device=dev, dtype=BF16)
         probs = torch.empty(G, Bt, self.Hh, S, S, device=dev, dtype=BF16)
-        # fp32 copy of the attention output for the backward's row statistic D_i = dO_i . O_i (CpcAttn.out_f32)
-        att32 = torch.empty(G, N * nb * S, d, device=dev) if torch.is_grad_enabled() else None
-        K.attn_fwd(qkv_k, krel, att_k, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop, out_f32=att32)
+        K.attn_fwd(qkv_k, krel, att_k, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
         att = att_k.view(G, N, nb * S, d)[:, :, :L].reshape(G, T, d) if padded else att_k
-        return att, dict(qkv=qkv_k, att=att_k, att32=att32, probs=probs, Bt=Bt, geom=(L, N, nb, padded))
+        return att, dict(qkv=qkv_k, att=att_k, probs=probs, Bt=Bt, geom=(L, N, nb, padded))
 
     def _attn_bwd(self, sa, krel, dkrel, datt, G, T, rng, drop):
         """datt bf16 [G, T, d] -> dqkv bf16 [G, T, 3d] (dKrelpos accumulated into `dkrel`)."""
@@ -264,7 +262,7 @@ class TransformerStack:
         dqkv_k = torch.empty(G, N * nb * S, 3 * d, device=dev, dtype=BF16)
         dscore = torch.empty_like(sa["probs"])
         K.attn_bwd(sa["qkv"], krel, sa["att"], sa["probs"], datt_k, dqkv_k, dscore, dkrel, G, sa["Bt"], self.Hh, S,
-                   self.dk, rng=rng, site=1, drop_p=drop, out_f32=sa["att32"])
+                   self.dk, rng=rng, site=1, drop_p=drop)
         return dqkv_k.view(G, N, nb * S, 3 * d)[:, :, :L].reshape(G, T, 3 * d) if padded else dqkv_k
 
     # ------------------------------------------------------------------------------------------ forward

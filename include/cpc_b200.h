@@ -229,7 +229,7 @@ int cpc_nce_bwd(const CpcNce* desc, void* stream);
  *   GRU : slots (r, z, n_x, hn): gx = (W_ir x + b_ir + b_hr | W_iz x + b_iz + b_hz | W_in x + b_in | b_hn),
  *         w_hh = (W_hr | W_hz | 0 | W_hn); n = tanh(n_x + r * hn), h = (1-z) n + z h_prev;
  *   RNN : slot 0 only (the other three slots of gx / w_hh are zero).
- * fwd writes out fp32 [N,S,H], h_pad bf16 [N,S+1,H] (row 0 = h0), gates bf16 [N,S,4H] (post-activation;
+ * fwd writes out fp32 [N,S,H], h_pad bf16 [N,S+1,H] (row 0 = h0), gates bf16 [N,S,4H] (gate PRE-activations, recomputed by bwd;
  * GRU slot 3 = W_hn h + b_hn), c_all fp32 [N,S,H] (LSTM: cell states; GRU/RNN: h in fp32), h_n / c_n fp32 [N,H]
  * (any may be null).  bwd consumes dout fp32 [N,S,H] and writes dgates bf16 [N,S,4H], the gradient w.r.t. the
  * four slot pre-activations (GRU: d r, d z, d n_x, d hn = d n_x * r); dW / dx follow as GEMMs.
@@ -256,9 +256,10 @@ typedef struct {
   void* out; int64_t gs_out; void* probs;
   const void* rng; uint32_t rng_site; float drop_p;
   const void* dout; void* dqkv; void* dscore; void* dkrel;
-  /* optional fp32 copy of `out` ([G][Bt*S][d], group stride gs_out): written by fwd, read by bwd for the row statistic
-   * D_i = dO_i . O_i.  With O rounded to bf16 the rounding error of D is coherent along a row and, once the softmax is
-   * peaked (trained models), no longer small next to dP_ij - D_i: the Wq / Wk gradients lose two digits. */
+  /* optional fp32 copy of `out` ([G][Bt*S][d], group stride gs_out) written by fwd.  The backward does NOT read it
+   * (nor `out`): its row statistic D_i = sum_j P_ij dP_ij / sum_j P_ij is formed from the same bf16 P and the same
+   * recomputed dP that dS = P o (dP - D) uses, so rows of dS sum to zero to fp32 rounding whatever common component
+   * K and V carry (D_i = dO_i . O_i, the flash-attention shortcut, cost the Wq gradients two digits in trained models). */
   void* out_f32;
 } CpcAttn;
 

@@ -55,6 +55,22 @@ class _RoundFwd(torch.autograd.Function):
         return g
 
 
+class _RoundBwd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).float()
+
+
+# extra rounding sites of one particular kernel design, for tools/attn_grad_probe.py (which rounding costs what):
+#   "ds"  the gradient of the attention scores is rounded to bf16 before dS.K and dS^T.Q
+#   "p"   the attention probabilities are rounded to bf16
+EMULATE_EXTRA = set()
+
+
 def _q(x):
     """Activation stored in bf16 (its gradient travels in bf16 too)."""
     return _RoundBoth.apply(x) if EMULATE_BF16 else x
@@ -213,9 +229,13 @@ def relpos_causal_attention(q, k, v, krelpos, size_seq, drop_mask=None, drop_p=0
         rel = torch.gather(qp, 2, r.unsqueeze(0).expand(q.shape[0], S, S))
         rel = torch.where((j <= i).unsqueeze(0), rel, torch.zeros((), dtype=q.dtype))
         score = score + rel
+    if "ds" in EMULATE_EXTRA:
+        score = _RoundBwd.apply(score)
     score = score / math.sqrt(dk)
     causal = torch.full((S, S), float("-inf")).triu(1)
     att = torch.softmax(score + causal, dim=2)
+    if "p" in EMULATE_EXTRA:
+        att = _RoundFwd.apply(att)
     if drop_mask is not None:
         att = att * drop_mask / (1.0 - drop_p)
     out = att @ v

@@ -50,9 +50,20 @@ def report(tag, **kw):
 
 
 def _predictable(B, W, seed):
+    """Tonal synthetic audio: per window a few amplitude-modulated sinusoids (80-1600 Hz) + a little noise, the future
+    window continuing the past one.  Unlike white noise its encoder features ARE predictable from their own past, so
+    Adam at the reference's learning-rate scale (cpc_default_config: 2e-4) leaves the ln(NEG+1) plateau in tens of
+    steps instead of collapsing (measured with the unmodified reference: lr 1e-3 / 5e-3 sits on the plateau)."""
     g = torch.Generator().manual_seed(seed)
-    past = 0.1 * torch.randn(B, 1, 1, W, generator=g)
-    return torch.cat([past, past + 0.01 * torch.randn(B, 1, 1, W, generator=g)], dim=1)
+    t = torch.arange(2 * W).float() / 16000.0
+    M = 6
+    f = 80.0 + 1500.0 * torch.rand(B, M, 1, generator=g)
+    ph = 6.2832 * torch.rand(B, M, 1, generator=g)
+    a = 0.02 + 0.05 * torch.rand(B, M, 1, generator=g)
+    fm = 1.0 + 4.0 * torch.rand(B, M, 1, generator=g)  # slow amplitude modulation, Hz
+    x = (a * (1 + 0.5 * torch.sin(6.2832 * fm * t)) * torch.sin(6.2832 * f * t + ph)).sum(1)
+    x = x + 0.005 * torch.randn(B, 2 * W, generator=g)
+    return x.view(B, 2, 1, W).contiguous()
 
 
 def _ref_step(m, crit, seq, seed):
@@ -72,9 +83,9 @@ def _ref_step(m, crit, seq, seed):
 
 
 CASES = {
-    "default": (dict(), 8, 400),
-    "config3_transformer_ar": (dict(arMode="transformer"), 8, 300),
-    "config4_hidden512_lstm2_w40960": (dict(hiddenEncoder=512, hiddenGar=512, nLevelsGRU=2, sizeWindow=40960), 4, 200),
+    "default": (dict(), 8, 150),
+    "config3_transformer_ar": (dict(arMode="transformer"), 8, 150),
+    "config4_hidden512_lstm2_w40960": (dict(hiddenEncoder=512, hiddenGar=512, nLevelsGRU=2, sizeWindow=40960), 4, 150),
 }
 
 
@@ -91,9 +102,9 @@ def test_step_matches_live_reference_away_from_init(name):
     if rargs.arMode != "transformer":
         m.train()  # cuDNN refuses an RNN backward in eval mode; the encoder / LSTM have no dropout or running statistics
     import math
-    opt = torch.optim.Adam(list(m.parameters()) + list(crit.parameters()), lr=5e-3)
+    opt = torch.optim.Adam(list(m.parameters()) + list(crit.parameters()), lr=3e-4)
     train_seq = _predictable(B, rargs.sizeWindow, 777).cuda()
-    target = 0.8 * math.log(rargs.negativeSamplingExt + 1)
+    target = 0.85 * math.log(rargs.negativeSamplingExt + 1)
     steps, loss = 0, float("nan")
     for steps in range(1, max_steps + 1):
         out = _ref_step(m, crit, train_seq, 1000 + steps) if steps % 10 == 0 else None

