@@ -431,7 +431,6 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
             for (int r = 0; r < 2; ++r) {
               const int ii = g + 8 * r, i = i0 + ii, j = jt * 8 + 2 * t;
               if (i < S && j <= i) {
-                const long long e = pbase + (long long)i * S + j;
                 const float p0 = bf16lo(pv[jt][r]), p1 = bf16hi(pv[jt][r]);
                 float dp0 = acc[2 * r], dp1 = acc[2 * r + 1];
                 if (drop.thresh != 0) {
@@ -566,7 +565,6 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
             const int i = ib * 16 + g + 8 * r, j = j0 + 8 * hf + 2 * t;
             float pd0 = 0.f, pd1 = 0.f, s0 = 0.f, s1 = 0.f;
             if (i < S && j <= i) {
-              const long long e = pbase + (long long)i * S + j;
               const float p0 = bf16lo(pc[ib][hf][r]), p1 = bf16hi(pc[ib][hf][r]);
               float dp0 = acc[2 * r], dp1 = acc[2 * r + 1];
               pd0 = p0;

@@ -106,6 +106,15 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmKernelArgs& p, int ti
   return t;
 }
 
+// Phase timestamps of the first and last tile of every CTA (tools/gemm_phase_probe.py builds a second library with
+// -DCPC_GEMM_TIMING; the shipped library compiles none of this).
+#ifdef CPC_GEMM_TIMING
+__device__ long long* g_gemm_timing = nullptr;
+#define GEMM_TSTAMP(slot) do { if (g_gemm_timing != nullptr) g_gemm_timing[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
+#else
+#define GEMM_TSTAMP(slot) do { } while (0)
+#endif
+
 }  // namespace cpc
 #include "gemm_epilogue.cuh"
 namespace cpc {
@@ -128,6 +137,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) GEMM_TSTAMP(0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -153,6 +163,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   // PDL: everything above (tensor-map fetch, barrier init, TMEM allocation) overlapped the tail of the preceding grid;
   // nothing below reads or writes global memory before that grid has completed (cpc_internal.h)
   pdl_sync();
+  if (threadIdx.x == 0) GEMM_TSTAMP(1);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -186,8 +197,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           } else {
             tma_load_3d(sb, &tmB, &full_bar[s], kk, tc.n0 + p.b_row_off, tc.grp * p.b_gmul + slab);
           }
+          if (it == 0) GEMM_TSTAMP(2);
         }
       }
+      GEMM_TSTAMP(3);  // every load of this CTA issued
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -205,6 +218,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
+          if (it == 0) GEMM_TSTAMP(4);
           const uint32_t sa = smem_u32(smem + s * L::STAGE_BYTES);
           const uint32_t sb = sa + L::A_BYTES;
 #pragma unroll
@@ -221,7 +235,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           umma_commit(&empty_bar[s]);  // frees this smem stage when the MMAs above retire
         }
         umma_commit(&acc_full[buf]);  // accumulator of this tile complete
+        if (lt == 0) GEMM_TSTAMP(5);
       }
+      GEMM_TSTAMP(6);  // every MMA of this CTA issued
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 2..9), gemm_epilogue.cuh
@@ -250,10 +266,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if (warp == 2 && lane == 0 && lt == 0) GEMM_TSTAMP(8);
     }
+    if (warp == 2 && lane == 0) GEMM_TSTAMP(9);
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) GEMM_TSTAMP(10);
   if (warp == 1) tmem_dealloc(tmem_base, L::TMEM_COLS);
 }
 
@@ -341,6 +360,13 @@ static int dispatch_major(const CUtensorMap& ta, const CUtensorMap& tb, const Ge
 }  // namespace cpc
 
 using namespace cpc;
+
+#ifdef CPC_GEMM_TIMING
+extern "C" int cpc_gemm_set_timing(void* buf) {
+  long long* p = static_cast<long long*>(buf);
+  return cudaMemcpyToSymbol(g_gemm_timing, &p, sizeof(p)) == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
+}
+#endif
 
 extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);

@@ -12,6 +12,9 @@
 
 namespace cpc {
 
+// (timing probe only) true for the CTA's first tile: accumulator buffer 0, first use
+__device__ __forceinline__ bool acc_full_bar_is_first(const uint64_t* bar) { return (reinterpret_cast<uintptr_t>(bar) & 8) == 0; }
+
 enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5, EPI_NORM = 6 };
 
 struct EpiRng {
@@ -107,6 +110,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const Til
   EpiLoads<MODE> L[2];
   epi_load_chunk<MODE>(L[0], p, e, 0);
   mbar_wait(acc_full_bar, parity);
+#ifdef CPC_GEMM_TIMING
+  if (parity == 0 && threadIdx.x == 64 && acc_full_bar_is_first(acc_full_bar)) GEMM_TSTAMP(7);
+#endif
   tc_fence_after();
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
@@ -242,6 +248,9 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
   };
   load_chunk(0, 0);
   mbar_wait(acc_full_bar, parity);
+#ifdef CPC_GEMM_TIMING
+  if (parity == 0 && threadIdx.x == 64 && acc_full_bar_is_first(acc_full_bar)) GEMM_TSTAMP(7);
+#endif
   tc_fence_after();
   // ---------------------------------------------------------------- sweep 1: pre-norm values + row statistics
 #pragma unroll
