@@ -330,9 +330,15 @@ class TrainRig:
                               params)
 
     def close(self):
+        import gc
         self.step.close()
         self.adam.detach()
-        self.dp.remove()
+        for p in list(self.model.parameters()) + list(self.crit.parameters()):
+            p.grad = None
+        self.dp.remove()  # (releases the symmetric gradient buffer synchronously: never inside a later capture)
+        self.step = self.adam = self.dp = self.model = self.crit = None
+        gc.collect()
+        torch.cuda.synchronize()
 
 
 def measure_extra_config(ctx, name, over, B, steps, pk):
@@ -364,6 +370,7 @@ def criterion_sweep(ctx, steps, pk, quick):
     their fused Adam update) alone, on random c, z ~ N(0,1) [8, 128, 256] per GPU, as one CUDA-graph replay per step."""
     from cpc2_b200 import criterion as cr
     from cpc2_b200 import kernels as K
+    from cpc2_b200 import ops
     from cpc2_b200.dp import BucketedAllReduce
     from cpc2_b200.optim import FusedAdam
     B, S, D = 8, 128, 256
@@ -406,6 +413,7 @@ def criterion_sweep(ctx, steps, pk, quick):
                     for p, q in zip(params, snap_p):
                         p.copy_(q)
                     adam.restore(snap_o)
+                ops.refresh_shadows(params)  # (as GraphedTrainStep does: the capture then holds no weight cast)
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
@@ -434,7 +442,8 @@ def criterion_sweep(ctx, steps, pk, quick):
                         "head_params": sum(p.numel() for p in params)})
             torch.cuda.synchronize()
             graph.reset()
-            del graph
+            del graph, losses
+            c.grad = z.grad = None
             adam.detach()
             dp.remove()
     return {"shape": "c, z ~ N(0,1) [8, 128, 256] per GPU; step = criterion fwd + bwd + heads' all-reduce + fused Adam, "

@@ -23,6 +23,8 @@
 // split-K reductions) is sector-coalesced: the thread-per-row 32x32b layout costs 32 sectors per store and
 // was 5-10x slower than the MMAs of the K=256 shapes that dominate this workload.  Split-K uses fp32
 // red.global.add.v2.
+#include <cstdlib>
+
 #include "cpc_internal.h"
 #include "ptx.cuh"
 
@@ -70,6 +72,7 @@ struct GemmKernelArgs {
   long long gs_norm_stat;
   float norm_eps;
   int norm_unbiased, norm_halo;
+  int vec16, vec16n;  // out_bf16 / norm_bf16 rows take 16-byte stores (base, row stride and group stride 16-byte aligned)
 };
 
 constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, each owns half of the tile's columns
@@ -414,6 +417,14 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   ka.norm_mean = static_cast<float*>(d->norm_mean); ka.norm_rstd = static_cast<float*>(d->norm_rstd);
   ka.gs_norm_stat = d->gs_norm_stat;
   ka.norm_eps = d->norm_eps; ka.norm_unbiased = d->norm_unbiased; ka.norm_halo = d->norm_halo;
+  static const bool vec_ok = [] {  // CPC_EPI_VEC16=0: 4-byte bf16x2 stores (A/B switch of the quad-transposed epilogue)
+    const char* e = getenv("CPC_EPI_VEC16");
+    return e == nullptr || e[0] != '0';
+  }();
+  ka.vec16 = vec_ok && ka.out_bf16 != nullptr && (reinterpret_cast<uintptr_t>(ka.out_bf16) & 15) == 0 && ka.ldd_bf16 % 8 == 0 &&
+             ka.gs_bf16 % 8 == 0;
+  ka.vec16n = vec_ok && ka.norm_bf16 != nullptr && (reinterpret_cast<uintptr_t>(ka.norm_bf16) & 15) == 0 &&
+              ka.ld_norm_bf16 % 8 == 0 && ka.gs_norm_bf16 % 8 == 0;
   const bool fused_norm = d->norm_gamma != nullptr;
   if (fused_norm) {
     if (d->N != 256 || d->a_major != 0 || d->b_major != 0 || k_splits > 1 || d->accumulate || d->gate != nullptr ||

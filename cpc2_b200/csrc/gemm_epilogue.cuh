@@ -35,6 +35,28 @@ __device__ __forceinline__ uint32_t epi_hash(uint32_t idx2, uint32_t seed_lo, ui
   return h;
 }
 
+// 4 x 4 transpose of 32-bit words inside each quad of lanes: on entry lane t (= lane % 4) holds w[j] = element (t, j),
+// on exit w[k] = element (k, t).  tcgen05.ld.16x256b hands a lane two consecutive columns of every 8-column group, so
+// a packed bf16x2 store covers 4 bytes per lane and 16 contiguous bytes per row -- HALF a 32-byte sector per row and
+// instruction, which made the bf16 stores (not the TMEM reads) the cost of the epilogue (3.7 us per 128 x 256 tile
+// against 1.1 us of TMEM read time, tools/gemm_phase_probe.py).  After the transpose lane t owns the whole 8-column
+// group t of the chunk: one 16-byte store per lane, 64 contiguous bytes per row, a quarter of the store instructions.
+__device__ __forceinline__ void quad_transpose4(uint32_t (&w)[4], int t) {
+  const bool odd = (t & 1) != 0, hi = (t & 2) != 0;
+  uint32_t s0 = odd ? w[0] : w[1], s1 = odd ? w[2] : w[3];
+  uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+  if (odd) { w[0] = r0; w[2] = r1; } else { w[1] = r0; w[3] = r1; }
+  s0 = hi ? w[0] : w[2];
+  s1 = hi ? w[1] : w[3];
+  r0 = __shfl_xor_sync(0xffffffffu, s0, 2);
+  r1 = __shfl_xor_sync(0xffffffffu, s1, 2);
+  if (hi) { w[0] = r0; w[1] = r1; } else { w[2] = r0; w[3] = r1; }
+}
+__device__ __forceinline__ uint32_t epi_pack_bf16x2(float a, float b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
 template <int MODE>
 struct EpiLoads {  // everything one 32-column chunk reads from global memory
   float2 b2[4];
@@ -172,13 +194,22 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const Til
 #pragma unroll
         for (int j = 0; j < 4; ++j) { x[2 * j] += old[i][j].x; x[2 * j + 1] += old[i][j].y; }
       }
-      if (!rok[i]) continue;
-      if (MODE != EPI_SPLITK && o16 != nullptr) {
+      if (MODE != EPI_SPLITK && o16 != nullptr) {  // (warp-uniform)
         __nv_bfloat16* dst = o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32;
+        if (p.vec16) {
+          uint32_t w[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j < jmax) *reinterpret_cast<__nv_bfloat162*>(dst + 8 * j) = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+          for (int j = 0; j < 4; ++j) w[j] = epi_pack_bf16x2(x[2 * j], x[2 * j + 1]);
+          quad_transpose4(w, lane & 3);  // before any row test: every lane takes part in the shuffles
+          if (rok[i] && (lane & 3) < jmax)
+            *reinterpret_cast<uint4*>(dst - csub + 8 * (lane & 3)) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if (rok[i]) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j < jmax) *reinterpret_cast<__nv_bfloat162*>(dst + 8 * j) = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+        }
       }
+      if (!rok[i]) continue;
       if (o32 != nullptr) {
         float* dst = o32 + (long long)(8 * i) * p.ldd_f32 + c * 32;
 #pragma unroll
@@ -262,14 +293,24 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
+      uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
         float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
         s[i] += x0 + x1;
         ss[i] = fmaf(x0, x0, fmaf(x1, x1, ss[i]));
-        if (o16 != nullptr && rok[i])
-          *reinterpret_cast<__nv_bfloat162*>(o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32 + 8 * j) = __floats2bfloat162_rn(x0, x1);
+        w[j] = epi_pack_bf16x2(x0, x1);
+      }
+      if (o16 != nullptr) {  // (warp-uniform)
+        __nv_bfloat16* dst = o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32;
+        if (p.vec16) {
+          quad_transpose4(w, lane & 3);
+          if (rok[i]) *reinterpret_cast<uint4*>(dst - csub + 8 * (lane & 3)) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if (rok[i]) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint32_t*>(dst + 8 * j) = w[j];
+        }
       }
     }
   }
@@ -323,17 +364,26 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      if (!rok[i]) continue;
+      uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
         const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
         const float y0 = fmaxf(fmaf((x0 - mean[i]) * rstd[i], g2[j].x, e2[j].x), relu_floor);
         const float y1 = fmaxf(fmaf((x1 - mean[i]) * rstd[i], g2[j].y, e2[j].y), relu_floor);
-        if (n16 != nullptr)
-          *reinterpret_cast<__nv_bfloat162*>(n16 + (long long)(8 * i) * p.ld_norm_bf16 + c * 32 + 8 * j) = __floats2bfloat162_rn(y0, y1);
-        if (n32 != nullptr)
+        w[j] = epi_pack_bf16x2(y0, y1);
+        if (n32 != nullptr && rok[i])
           *reinterpret_cast<float2*>(n32 + (long long)(8 * i) * p.ld_norm_f32 + c * 32 + 8 * j) = make_float2(y0, y1);
+      }
+      if (n16 != nullptr) {  // (warp-uniform)
+        __nv_bfloat16* dst = n16 + (long long)(8 * i) * p.ld_norm_bf16 + c * 32;
+        if (p.vec16n) {
+          quad_transpose4(w, lane & 3);
+          if (rok[i]) *reinterpret_cast<uint4*>(dst - csub + 8 * (lane & 3)) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if (rok[i]) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint32_t*>(dst + 8 * j) = w[j];
+        }
       }
     }
   }

@@ -139,10 +139,29 @@ class BucketedAllReduce:
             self._pending = False
 
     def remove(self):
+        """Unhook, and give the symmetric buffer back NOW: gradients that alias it are dropped and the buffer, its
+        rendezvous handle and the carved slots are released here, synchronously, on every rank.  Left to the garbage
+        collector the last reference can die in the middle of a later CUDA-graph capture, and freeing
+        symmetric memory is not permitted while a stream is capturing (the process aborts)."""
         if self._on_grad_ready in ops.GRAD_READY:
             ops.GRAD_READY.remove(self._on_grad_ready)
-        if self.symmetric is not None and ops.GRAD_ARENA == self._arena:
-            ops.GRAD_ARENA = None
+        if self.symmetric is not None:
+            if ops.GRAD_ARENA == self._arena:
+                ops.GRAD_ARENA = None
+            base, nbytes = self.symmetric["base"], self.symmetric["bytes"]
+            for b in self.buckets:
+                for p in b:
+                    if p.grad is not None and base <= p.grad.data_ptr() < base + nbytes:
+                        p.grad = None
+            if self.on_gpu:
+                torch.cuda.synchronize()
+            self.symmetric.clear()
+            self.symmetric = None
+            self._arenas = []
+            import gc
+            gc.collect()
+            if self.on_gpu:
+                torch.cuda.synchronize()
 
 
 def filter_distributed(files, global_rank, world_size):

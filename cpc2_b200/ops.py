@@ -5,6 +5,8 @@ kernels of libcpc_b200.so through `cpc2_b200.kernels`.
 """
 import os
 
+import weakref
+
 import torch
 
 from . import kernels as K
@@ -223,6 +225,32 @@ def auto_splits(M, N, K_total, groups=1, k_per_slab=0):
     return max(1, min(kblocks // 4, (2 * NUM_SMS + tiles - 1) // tiles))
 
 
+# parameter id -> (arena, offset, parameter): where cpc_adam_step stores the bf16 copy of an arena-homed parameter
+_SHADOW_OWNER = {}
+
+
+def shadow_target(p):
+    """(arena, address of p's slot in the arena's persistent bf16 shadow) or (None, None)."""
+    ent = _SHADOW_OWNER.get(id(p))
+    if ent is None:
+        return None, None
+    arena, q = ent[0](), ent[2]()
+    if arena is None or q is not p or getattr(arena, "_shadow", None) is None or not arena.valid():
+        return None, None
+    return arena, arena._shadow.data_ptr() + 2 * ent[1]
+
+
+def refresh_shadows(params):
+    """Bring the bf16 shadow of every arena that homes one of `params` up to date (eager cast on the current stream)."""
+    seen = set()
+    for p in params:
+        ent = _SHADOW_OWNER.get(id(p))
+        arena = ent[0]() if ent is not None else None
+        if arena is not None and id(arena) not in seen:
+            seen.add(id(arena))
+            arena.refresh_shadow()
+
+
 class Arena:
     """A flat fp32 buffer that OWNS the storage of a list of parameters, in a layout chosen so that
     groups of parameters form the stacked GEMM operands directly ([group][rows][cols]); one cast kernel
@@ -263,21 +291,56 @@ class Arena:
         self.flat = flat
         return flat
 
-    def prefetch(self, stream_index):
-        """Issue the bf16 shadow cast on a side stream now; the next bf16() call picks it up."""
+    # ---- persistent bf16 shadow -------------------------------------------------------------------------------
+    # ONE bf16 copy of the arena, kept across steps and valid while the parameters' autograd versions are the ones it
+    # was written at.  Writers: the cast kernel (any time the parameters changed behind our back: torch.optim.Adam,
+    # load_state_dict, an in-place edit) and cpc_adam_step itself (CpcAdamSpan.p16: the fused optimizer stores the
+    # updated parameter in both precisions, so a training loop on FusedAdam never launches the 16.6 M-element cast
+    # that used to sit next to conv0 at the top of every step).
+    def shadow_buffer(self):
         flat = self.ensure()
-        out = torch.empty(flat.shape, dtype=BF16, device=flat.device)
+        sh = getattr(self, "_shadow", None)
+        if sh is None or sh.device != flat.device or sh.numel() != flat.numel():
+            sh = torch.empty(flat.shape, dtype=BF16, device=flat.device)
+            self._shadow, self._shadow_key = sh, None
+            for q, off in zip(self.params, self.offsets):
+                _SHADOW_OWNER[id(q)] = (weakref.ref(self), off, weakref.ref(q))
+        return sh
+
+    def _key(self):
+        return ([q._version for q in self.params], self.flat.data_ptr() if self.flat is not None else 0)
+
+    def shadow_valid(self):
+        return getattr(self, "_shadow", None) is not None and self.valid() and self._shadow_key == self._key()
+
+    def mark_shadow_written(self):
+        """The shadow now equals the parameters (called by whoever just wrote it)."""
+        self._shadow_key = self._key()
+
+    def refresh_shadow(self):
+        """Cast now, on the current stream, if the shadow is stale."""
+        if not self.shadow_valid():
+            sh = self.shadow_buffer()
+            K.cast_bf16(self.flat, sh)
+            self.mark_shadow_written()
+        return self._shadow
+
+    def prefetch(self, stream_index):
+        """Make the bf16 shadow current: nothing to do when the optimizer wrote it, else the cast is issued on a
+        side stream now and the next bf16() call joins it."""
+        if self.shadow_valid():
+            return
+        sh = self.shadow_buffer()
         with side(stream_index):
-            K.cast_bf16(flat, out)
-        self._pref = Prefetched(self.params, out, stream_index)
+            K.cast_bf16(self.flat, sh)
+        self.mark_shadow_written()
+        self._pref_stream = stream_index
 
     def bf16(self):
-        pref, self._pref = getattr(self, "_pref", None), None
-        if pref is not None:
-            out = pref.take(self.params)
-            if out is not None:
-                return out
-        return K.cast_bf16(self.ensure())
+        st, self._pref_stream = getattr(self, "_pref_stream", None), None
+        if st is not None:
+            join(st)
+        return self.refresh_shadow()
 
     def view(self, flat, index, shape=None):
         """View of parameter `index` inside another flat tensor with the same layout (bf16 shadow, grads)."""

@@ -23,6 +23,7 @@ class FusedAdam(torch.optim.Optimizer):
         super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=0, amsgrad=False))
         self._groups = [None] * len(self.param_groups)  # per group: device state, span tables, flat moments
         self._dp, self._done, self._advanced = None, set(), False
+        self._shadowed = []  # arenas whose bf16 shadow the launches of this iteration wrote
 
     # ------------------------------------------------------------------------------------------ internals
     def _init_group(self, gi):
@@ -58,10 +59,14 @@ class FusedAdam(torch.optim.Optimizer):
     def _table(self, g, name, pairs):
         """Device span table `name` over (parameter, gradient) pairs; rebuilt only when a pointer changed."""
         chunk = _lib.lib().cpc_adam_chunk()
-        keys = [(p.data_ptr(), gr.data_ptr(), p.numel()) for p, gr in pairs]
-        t = g["tables"].setdefault(name, dict(keys=None, table=None, n_spans=0, blocks=0))
+        # arena-homed parameters (the prediction heads, a transformer AR): the kernel also stores the updated value
+        # into the arena's persistent bf16 shadow, so the next step finds its GEMM operands ready (ops.Arena)
+        shadow = [ops.shadow_target(p) for p, _ in pairs]
+        keys = [(p.data_ptr(), gr.data_ptr(), p.numel(), sh[1]) for (p, gr), sh in zip(pairs, shadow)]
+        t = g["tables"].setdefault(name, dict(keys=None, table=None, n_spans=0, blocks=0, arenas=[]))
         if keys == t["keys"]:
             return t
+        t["arenas"] = list({id(a): a for a, _ in shadow if a is not None}.values())
         spans = (_lib.AdamSpan * max(len(pairs), 1))()
         blocks = 0
         for i, (p, gr) in enumerate(pairs):
@@ -71,7 +76,7 @@ class FusedAdam(torch.optim.Optimizer):
             st = self.state[p]
             spans[i].p, spans[i].g = p.data_ptr(), gr.data_ptr()
             spans[i].m, spans[i].v = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
-            spans[i].p16 = None
+            spans[i].p16 = shadow[i][1]
             spans[i].n, spans[i].first_block = p.numel(), blocks
             blocks += (p.numel() + chunk - 1) // chunk
         # pinned staging buffer + async copy.  While a CUDA graph is being captured the copy becomes a graph node that
@@ -141,6 +146,7 @@ class FusedAdam(torch.optim.Optimizer):
                 torch.cuda.current_stream().wait_event(after)  # (also when side streams are disabled)
             t = self._table(g, stage, pairs)
             K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
+            self._shadowed.extend(t["arenas"])
         self._advanced = True
         self._done.update(id(p) for p, _ in pairs)
 
@@ -200,9 +206,15 @@ class FusedAdam(torch.optim.Optimizer):
             if pairs:
                 t = self._table(g, "rest", pairs)
                 K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not (self._advanced and gi == 0))
-            # the kernel wrote through raw pointers: tell autograd (and ops.Prefetched, which validates bf16 weight
-            # shadows by version counter) that the parameters changed
+                self._shadowed.extend(t["arenas"])
+            # arenas whose bf16 shadow matched the parameters before this update still match: the kernel stored both
+            current = [a for a in {id(a): a for a in self._shadowed}.values() if a.shadow_valid()]
+            # the kernel wrote through raw pointers: tell autograd (and ops.Prefetched / ops.Arena, which validate
+            # bf16 weight shadows by version counter) that the parameters changed
             torch.autograd.graph.increment_version(g["params"])
+            for a in current:
+                a.mark_shadow_written()
+        self._shadowed = []
         self._done.clear()
         self._advanced = False
         return loss

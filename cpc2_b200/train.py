@@ -286,6 +286,10 @@ class GraphedTrainStep:
                 drop_state.copy_(drop_snap)
             elif (dev.type, dev.index) in ops.DropoutState._states:
                 ops.DropoutState._states[(dev.type, dev.index)][1:2].zero_()
+            # the restore (or any edit since the last forward) left the persistent bf16 weight shadows stale: bring them
+            # up to date NOW, so that the capture below records no cast -- inside the graph cpc_adam_step keeps them
+            # current (CpcAdamSpan.p16)
+            ops.refresh_shadows(self.params)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(dev)
         torch.cuda.set_rng_state(rng_state, dev)
@@ -298,6 +302,7 @@ class GraphedTrainStep:
                 after_backward()
             if optimizer is not None:
                 optimizer.step()
+        self._versions_seen = sum(p._version for p in self.params)
 
     def close(self):
         """Drop the captured graph (and the static outputs that live in its memory pool).  A graph that holds captured
@@ -371,5 +376,14 @@ class GraphedTrainStep:
             self.optimizer.sync_hyper()  # a scheduler may have changed lr since the last replay
         if self.graph is None:
             raise RuntimeError("GraphedTrainStep.step() after close()")
+        if self.optimizer is not None:
+            # parameters edited since the last replay (load_state_dict, a manual in-place change): the graph holds no
+            # cast of the arena-homed weights, so refresh their bf16 shadows first.  One sum over the autograd version
+            # counters per step (~10 us of host time, hidden behind the previous replay) when nothing changed.
+            ver = sum(p._version for p in self.params)
+            if ver != self._versions_seen:
+                from . import ops
+                ops.refresh_shadows(self.params)
+                self._versions_seen = ver
         self.graph.replay()
         return self.losses, self.acc

@@ -360,19 +360,23 @@ class TransformerStack:
             ops.linear_dw(dh1, sv["y"], Gd["W1"], T, dff, d, groups=G)
         with ops.side(1):
             K.colsum(dh1, Gd["b1"], T, dff, dff, T * dff, G)
+        if ops.GRAD_F32:
+            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_f32=dy, res=du)
+        else:
+            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
         if early_stage is not None and ops.GRAD_READY:
             i0, i1 = self.first["W1"], self.first["b2"] + G
             off0 = self.arena.offsets[i0]
             off1 = self.arena.offsets[i1] if i1 < len(self.arena.params) else self.arena.numel
             views = self.arena.grad_views(gflat)
-            with ops.side(0):  # behind dW2 / dW1 (this stream) and the bias column sums (stream 1)
+            # AFTER the W1 input-gradient product above: the optimizer step this announces rewrites W1 / W2 in BOTH
+            # precisions (fp32 and the persistent bf16 shadow, CpcAdamSpan.p16), so every reader of their bf16 copies
+            # has to be queued first; side(0) waits for the main stream up to here, for dW2 / dW1 (its own work) and
+            # for the bias column sums (stream 1)
+            with ops.side(0):
                 ops.wait_side(1)
                 ops.grad_ready(early_stage + ".ffn", gflat[off0:off1], self.arena.params[i0:i1], views[i0:i1])
             sv["announced"] = (i0, i1, off0, off1)
-        if ops.GRAD_F32:
-            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_f32=dy, res=du)
-        else:
-            ops.linear_dx(dh1, P16["W1"], T, dff, d, groups=G, out_bf16=dy, res=du)
         # y = LN1(pre1)
         K.rownorm_bwd(dy.view(G * T, d), sv["pre1"], sv["mean1"], sv["rstd1"], G * T, d, P32["ln1w"], P32["ln1b"],
                       dx_bf16=dpre1, dgamma=Gd["ln1w"], dbeta=Gd["ln1b"], rows_per_group=T)
