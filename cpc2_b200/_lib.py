@@ -186,6 +186,7 @@ class Attn(ctypes.Structure):
         ("rng", ctypes.c_void_p), ("rng_site", ctypes.c_uint32), ("drop_p", ctypes.c_float),
         ("dout", ctypes.c_void_p), ("dqkv", ctypes.c_void_p), ("dscore", ctypes.c_void_p), ("dkrel", ctypes.c_void_p),
         ("out_f32", ctypes.c_void_p),
+        ("rowsum", ctypes.c_void_p),
     ]
 
 

@@ -405,7 +405,8 @@ class _HeadsFn(torch.autograd.Function):
     def forward(ctx, c, eng, training, *params):
         B, W, H = c.shape
         xb = K.cast_bf16(c.detach().contiguous().float()).view(B * W, H)
-        out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True, seq_len=W)
+        with ops.saving(any(ctx.needs_input_grad)):
+            out, out32, saved = eng.forward(xb, B * W, True, training, want_f32=True, seq_len=W)
         ctx.eng, ctx.saved, ctx.shape = eng, saved, (B, W, H)
         return out32.view(eng.n_out, B, W, eng.dout)
 
@@ -570,7 +571,8 @@ class _CriterionFn(torch.autograd.Function):
             raise ValueError("B*S must be a multiple of 8")
         cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
         zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
-        preds, _, saved = eng.forward(cw, T, True, training, seq_len=W)
+        with ops.saving(will_backward and any(ctx.needs_input_grad)):
+            preds, _, saved = eng.forward(cw, T, True, training, seq_len=W)
         if isinstance(eng, TransformerStack) and will_backward and any(ctx.needs_input_grad):
             # the heads' gradient arena (66 MB at the default config) is cleared NOW on an idle side stream: the same
             # memset at the top of the backward sat on the critical path for ~13 us

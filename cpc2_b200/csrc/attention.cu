@@ -224,6 +224,7 @@ static int fill_attn(AttnArgs& a, const CpcAttn* d) {
   a.krel = static_cast<const float*>(d->krel);
   a.out = static_cast<__nv_bfloat16*>(d->out); a.gs_out = d->gs_out;
   a.out_f32 = static_cast<float*>(d->out_f32);
+  a.rowsum = static_cast<float*>(d->rowsum);
   a.probs = static_cast<__nv_bfloat16*>(d->probs);
   a.S = d->S; a.dk = d->dk; a.d = d->dk * d->Hh; a.Bt = d->Bt; a.Hh = d->Hh;
   a.scale = d->scale;

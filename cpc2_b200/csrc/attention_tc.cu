@@ -210,9 +210,11 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
       sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], 2);
       inv[r] = sum[r] > 0.f ? 1.f / sum[r] : 0.f;
     }
-    // probabilities out (bf16, lower triangle); the copy that feeds P.V keeps fp32 accuracy (hi + lo bf16 pair
-    // below): the backward's D_i = dO_i.O_i must equal sum_j P_ij dP_ij for the UNROUNDED P, otherwise the
-    // rounding error of P, weighted by the common component of dP, leaks into every dS of the row.
+    // probabilities out (bf16, lower triangle).  P.V is formed from the SAME bf16-rounded values (the dropout scale
+    // is applied to the accumulator afterwards, so the operand stays exactly the stored P^): the backward's row
+    // statistic D_i = dO_i . O_i / sum_j P^_ij is then algebraically sum_j P^_ij dP~_ij / sum_j P^_ij for the very P^
+    // and V it multiplies -- rows of dS sum to zero to fp32 rounding (CpcAttn.out_f32 / rowsum).
+    float rs[2] = {0.f, 0.f};
 #pragma unroll
     for (int jt = 0; jt < NJ; ++jt) {
       if (jt < njt) {
@@ -222,8 +224,11 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
           float p0 = sc[jt][2 * r] * inv[r], p1 = sc[jt][2 * r + 1] * inv[r];
           if (i < S && j <= i) {
             const long long e = pbase + (long long)i * S + j;
+            const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+            p0 = __low2float(pb);
+            p1 = j + 1 <= i ? __high2float(pb) : 0.f;
+            rs[r] += p0 + p1;
             if (a.probs != nullptr) {
-              const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
               if (pair_ok && j + 1 <= i) *reinterpret_cast<__nv_bfloat162*>(a.probs + e) = pb;
               else {
                 a.probs[e] = __low2bfloat16(pb);
@@ -233,16 +238,26 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
             if (drop.thresh != 0) {
               bool k0, k1;
               keep_pair(drop, rbase + i, j, k0, k1);
-              p0 = k0 ? p0 * drop.scale : 0.f;
-              p1 = k1 ? p1 * drop.scale : 0.f;
+              p0 = k0 ? p0 : 0.f;
+              p1 = k1 ? p1 : 0.f;
             }
+          } else {
+            p0 = p1 = 0.f;
           }
           sc[jt][2 * r] = p0;
           sc[jt][2 * r + 1] = p1;
         }
       }
     }
-    // O = P~ . V : two adjacent score tiles form the A fragment of one 16-key step
+    if (a.rowsum != nullptr) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        rs[r] += __shfl_xor_sync(0xffffffffu, rs[r], 1);
+        rs[r] += __shfl_xor_sync(0xffffffffu, rs[r], 2);
+        if (t == 0 && i0 + g + 8 * r < S) a.rowsum[rbase + i0 + g + 8 * r] = rs[r];
+      }
+    }
+    // O = dropout_scale * (keep o P^) . V : two adjacent score tiles form the A fragment of one 16-key step
     float o[NT][4];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
@@ -251,24 +266,24 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_tc_kernel(const AttnArgs a) 
 #pragma unroll
     for (int kk = 0; kk < NB; ++kk) {
       if (2 * kk < njt) {
-        uint32_t ap[4], al[4];
+        uint32_t ap[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float x0 = sc[2 * kk + (q >> 1)][2 * (q & 1)], x1 = sc[2 * kk + (q >> 1)][2 * (q & 1) + 1];
-          const __nv_bfloat162 hi = __floats2bfloat162_rn(x0, x1);
-          ap[q] = *reinterpret_cast<const uint32_t*>(&hi);
-          al[q] = pack_bf16x2(x0 - __low2float(hi), x1 - __high2float(hi));
-        }
+        for (int q = 0; q < 4; ++q)  // (exact: the values are bf16 already)
+          ap[q] = pack_bf16x2(sc[2 * kk + (q >> 1)][2 * (q & 1)], sc[2 * kk + (q >> 1)][2 * (q & 1) + 1]);
 #pragma unroll
         for (int n2 = 0; n2 < NT / 2; ++n2) {
           uint32_t bb[4];
           ldsm_x4_t(bb, smem_u32(Vs + (kk * 16 + (lane & 15)) * PD + n2 * 16 + (lane >> 4) * 8));
           mma_bf16_16816(o[2 * n2], ap, bb[0], bb[1]);
           mma_bf16_16816(o[2 * n2 + 1], ap, bb[2], bb[3]);
-          mma_bf16_16816(o[2 * n2], al, bb[0], bb[1]);
-          mma_bf16_16816(o[2 * n2 + 1], al, bb[2], bb[3]);
         }
       }
+    }
+    if (drop.thresh != 0) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[nt][e] *= drop.scale;
     }
     __nv_bfloat16* ob = a.out + (long long)grp * a.gs_out + (long long)b * S * d + h * DK;
     float* of = a.out_f32 != nullptr ? a.out_f32 + (long long)grp * a.gs_out + (long long)b * S * d + h * DK : nullptr;
@@ -319,7 +334,31 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
   // shortcut D_i = dO_i . O_i is only as good as O: in trained models K and V carry a large component common to all
   // keys, dP_ij is nearly constant along a row, and the 2^-17 mismatch between O and the recomputed dP leaked,
   // multiplied by that common component, into dQ (cosine 0.4-0.95 on Wq gradients away from init).
-  for (int i = threadIdx.x; i < SP; i += ATT_THREADS) Dsm[i] = 0.f;
+  const bool fast_d = a.out_f32 != nullptr && a.rowsum != nullptr;  // (a) of CpcAttn: D_i = dO_i . O_i / rowsum_i
+  const long long rbase0 = (((long long)grp * a.Bt + b) * a.Hh + h) * S;
+  for (int i = threadIdx.x; i < SP; i += ATT_THREADS) {
+    float acc = 0.f;
+    if (fast_d && i < S) {  // straight from global memory while the tiles are in flight
+      const float* orow = a.out_f32 + obase + (long long)i * d;
+      const __nv_bfloat16* drow = a.dout + obase + (long long)i * d;
+      float4 ov[DK / 4];
+      uint4 dv[DK / 8];
+#pragma unroll
+      for (int ch = 0; ch < DK / 4; ++ch) ov[ch] = *reinterpret_cast<const float4*>(orow + ch * 4);
+#pragma unroll
+      for (int ch = 0; ch < DK / 8; ++ch) dv[ch] = *reinterpret_cast<const uint4*>(drow + ch * 8);
+      const float rsum = a.rowsum[rbase0 + i];
+#pragma unroll
+      for (int ch = 0; ch < DK / 8; ++ch) {
+        const uint32_t* d2 = reinterpret_cast<const uint32_t*>(&dv[ch]);
+        acc += ov[2 * ch].x * bf16lo(d2[0]) + ov[2 * ch].y * bf16hi(d2[0]) + ov[2 * ch].z * bf16lo(d2[1]) + ov[2 * ch].w * bf16hi(d2[1]);
+        acc += ov[2 * ch + 1].x * bf16lo(d2[2]) + ov[2 * ch + 1].y * bf16hi(d2[2]) + ov[2 * ch + 1].z * bf16lo(d2[3]) +
+               ov[2 * ch + 1].w * bf16hi(d2[3]);
+      }
+      acc = rsum > 0.f ? acc / rsum : 0.f;
+    }
+    Dsm[i] = acc;
+  }
   if (rel) {
     const float* kr = a.krel + (long long)grp * DK * S;
 #pragma unroll 8
@@ -369,8 +408,8 @@ __global__ void __launch_bounds__(att_warps(SP) * 32) attn_bwd_tc_kernel(const A
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) dq[nt][e] = 0.f;
-    float Di[2];
-    {
+    float Di[2] = {Dsm[i0 + g], Dsm[i0 + g + 8]};
+    if (!fast_d) {  // (b) of CpcAttn: one more dP sweep, D from the same P^ and dP~ the row's dS uses
       float dsum[2] = {0.f, 0.f}, psum[2] = {0.f, 0.f};
 #pragma unroll
       for (int jt = 0; jt < NJ; ++jt) {

@@ -22,7 +22,8 @@ struct AttnArgs {
   __nv_bfloat16* dqkv;        // [G][T][3d]
   __nv_bfloat16* dscore;      // scratch, same shape as probs
   float* dkrel;               // [G][dk][S], atomically accumulated
-  float* out_f32;             // optional fp32 copy of out (fwd writes, bwd reads it for D_i = dO_i . O_i)
+  float* out_f32;             // optional fp32 copy of out (fwd writes; with rowsum: bwd reads it for D_i = dO_i . O_i / rowsum_i)
+  float* rowsum;              // optional [G][Bt][Hh][S]: sum_j of the bf16-rounded probabilities of row i (fwd writes)
 };
 
 // tensor-core path (attention_tc.cu); returns CPC_ERR_UNSUPPORTED when the shape is outside its range

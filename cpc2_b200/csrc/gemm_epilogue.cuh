@@ -129,8 +129,16 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const Til
   if (MODE == EPI_DROP) alpha *= rng.scale;
   const float relu_floor = p.relu ? 0.f : -INFINITY;
   const uint32_t pair0 = (uint32_t)(((unsigned long long)g * p.M + row0) * (unsigned long long)p.N + col0) >> 1;
-  EpiLoads<MODE> L[2];
-  epi_load_chunk<MODE>(L[0], p, e, 0);
+  // EPI_ACCUM keeps a two-deep buffer (its 32 registers per chunk do not fit four times); every other mode requests
+  // the loads of ALL chunks before the accumulator is awaited: one L2 round trip per tile instead of one per chunk
+  constexpr int LD = MODE == EPI_ACCUM ? 2 : NC;
+  EpiLoads<MODE> L[LD];
+  if (MODE == EPI_ACCUM) {
+    epi_load_chunk<MODE>(L[0], p, e, 0);
+  } else {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) epi_load_chunk<MODE>(L[c % LD], p, e, c);
+  }
   mbar_wait(acc_full_bar, parity);
 #ifdef CPC_GEMM_TIMING
   if (parity == 0 && threadIdx.x == 64 && acc_full_bar_is_first(acc_full_bar)) GEMM_TSTAMP(7);
@@ -143,16 +151,16 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelArgs& p, const Til
     uint32_t v[2][16];
     tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
     tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
-    if (c + 1 < NC) epi_load_chunk<MODE>(L[(c + 1) & 1], p, e, c + 1);
+    if (MODE == EPI_ACCUM && c + 1 < NC) epi_load_chunk<MODE>(L[(c + 1) % LD], p, e, c + 1);
     tmem_ld_wait();
     float2 b2[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) b2[j] = L[c & 1].b2[j];
+    for (int j = 0; j < 4; ++j) b2[j] = L[c % LD].b2[j];
     const bool* rok = e.rok;
     __nv_bfloat16* o16 = e.o16;
     float* o32 = e.o32;
-    auto& ax = L[c & 1].ax;
-    auto& old = L[c & 1].old;
+    auto& ax = L[c % LD].ax;
+    auto& old = L[c % LD].old;
     if (MODE == EPI_DROP) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) { b2[j].x *= rng.scale; b2[j].y *= rng.scale; }
@@ -263,21 +271,27 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
 
   float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
   // the first chunk's bias / residual are requested before the accumulator is awaited (they overlap the main loop)
+  // The residual of the WHOLE tile row set (4 chunks x 4 rows x 4 column groups, 64 registers) is requested before the
+  // accumulator is awaited and kept for both sweeps: a chunk-by-chunk double buffer exposed one L2 round trip per chunk
+  // and sweep (8 x ~0.4 us of the 7-9 us this epilogue took, tools/gemm_phase_probe.py).  The per-column vectors
+  // (bias, gamma, beta: the same 1 KB for every row) are read per chunk and hit L1 after the first touch.
   float2 b2[2][4];
-  uint32_t rx[2][4][4];
-  auto load_chunk = [&](int c, int slot) {
+  uint32_t rx[NC][4][4];
+  auto load_bias = [&](int c, int slot) {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
       b2[slot][j] = bias != nullptr ? *reinterpret_cast<const float2*>(bias + c * 32 + 8 * j) : make_float2(0.f, 0.f);
+  };
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        rx[slot][i][j] = (res != nullptr && rok[i])
-                             ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
-                             : 0u;
-  };
-  load_chunk(0, 0);
+        rx[c][i][j] = (res != nullptr && rok[i])
+                          ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
+                          : 0u;
+  load_bias(0, 0);
   mbar_wait(acc_full_bar, parity);
 #ifdef CPC_GEMM_TIMING
   if (parity == 0 && threadIdx.x == 64 && acc_full_bar_is_first(acc_full_bar)) GEMM_TSTAMP(7);
@@ -289,15 +303,15 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
     uint32_t v[2][16];
     tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
     tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
-    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
+    if (c + 1 < NC) load_bias(c + 1, (c + 1) & 1);
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
-        float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
+        float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c][i][j]);
+        float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c][i][j]);
         s[i] += x0 + x1;
         ss[i] = fmaf(x0, x0, fmaf(x1, x1, ss[i]));
         w[j] = epi_pack_bf16x2(x0, x1);
@@ -348,7 +362,7 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
   }
   // ---------------------------------------------------------------- sweep 2: normalise, affine, ReLU, store
   const float relu_floor = p.relu ? 0.f : -INFINITY;
-  load_chunk(0, 0);
+  load_bias(0, 0);
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     uint32_t v[2][16];
@@ -360,15 +374,15 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
       g2[j] = *reinterpret_cast<const float2*>(gam + c * 32 + 8 * j);
       e2[j] = *reinterpret_cast<const float2*>(bet + c * 32 + 8 * j);
     }
-    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
+    if (c + 1 < NC) load_bias(c + 1, (c + 1) & 1);
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
-        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
+        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c][i][j]);
+        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c][i][j]);
         const float y0 = fmaxf(fmaf((x0 - mean[i]) * rstd[i], g2[j].x, e2[j].x), relu_floor);
         const float y1 = fmaxf(fmaf((x1 - mean[i]) * rstd[i], g2[j].y, e2[j].y), relu_floor);
         w[j] = epi_pack_bf16x2(y0, y1);

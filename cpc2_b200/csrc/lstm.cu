@@ -70,6 +70,11 @@ constexpr int CELL_LSTM = 0, CELL_GRU = 1, CELL_RNN = 2;
 constexpr int NB = 8;          // sequences per cluster: one mma n-tile.  Small on purpose -- the recurrence is
                                // latency-bound and the rest of the chip is idle, so more clusters beat wider ones
 constexpr int LSTM_THREADS = 256;
+// Backward: the per-step inputs (saved gates, c_{t-1}, dout_t) are fetched PF steps ahead into a ring of PF + 1
+// buffers.  Two steps (1.5 us) covered an idle memory system only: next to the fused Adam pass of the heads (500 MB, HBM
+// saturated for ~90 us) or a gradient all-reduce, load latency grows past that and every step stalled on its inputs --
+// the recurrence took 129 us instead of 98 (profiles/r02_timeline_dp_n1.txt).
+constexpr int BWD_PF = 6, BWD_RING = BWD_PF + 1;
 
 // Per-step input tile of one CTA: its 4 x 32 gate columns of gx for the cluster's 8 sequences, fp32, fetched two
 // steps ahead with cp.async (16-byte chunks: every (sequence, gate) is one contiguous 128-byte segment).
@@ -265,10 +270,10 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
   constexpr int CP = 36;                          // fp32 pitch of the [seq][unit] tiles
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   float* P = reinterpret_cast<float*>(smem_dyn);                                     // [2][CL][32 units][NB] partial dh
-  __nv_bfloat16* in_g = reinterpret_cast<__nv_bfloat16*>(P + 2 * CL * 32 * NB);      // [3][NB][GP] saved gates
-  float* in_c = reinterpret_cast<float*>(in_g + 3 * NB * GP);                        // [3][NB][CP] c_{t-1}
-  float* in_d = in_c + 3 * NB * CP;                                                  // [3][NB][CP] dout_t
-  __nv_bfloat16* dg_s = reinterpret_cast<__nv_bfloat16*>(in_d + 3 * NB * CP);        // [2][NB][GP] gate gradients
+  __nv_bfloat16* in_g = reinterpret_cast<__nv_bfloat16*>(P + 2 * CL * 32 * NB);      // [RING][NB][GP] saved gates
+  float* in_c = reinterpret_cast<float*>(in_g + BWD_RING * NB * GP);                 // [RING][NB][CP] c_{t-1}
+  float* in_d = in_c + BWD_RING * NB * CP;                                           // [RING][NB][CP] dout_t
+  __nv_bfloat16* dg_s = reinterpret_cast<__nv_bfloat16*>(in_d + BWD_RING * NB * CP); // [2][NB][GP] gate gradients
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t cta = cluster_ctarank();
@@ -311,11 +316,11 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     if (a.S > 1) mbar_expect_tx(&bar[1], STEP_BYTES);
   }
   const float* s0p = CELL == CELL_LSTM ? a.c0 : a.h0;  // state before step 0: c0 (LSTM) or h0 (GRU / RNN, whose c_all holds h)
-  // per-step input prefetch (cp.async, two steps ahead): 128 threads fetch the gates tile, 64 c_{t-1}, 64 dout_t
+  // per-step input prefetch (cp.async, BWD_PF steps ahead): 128 threads fetch the gates tile, 64 c_{t-1}, 64 dout_t
   auto prefetch = [&](int sidx) {
     const int t = a.S - 1 - sidx;
     if (sidx < a.S) {
-      const int buf = sidx % 3;
+      const int buf = sidx % BWD_RING;
       if (tid < 128) {
         const int b = tid >> 4, g = (tid >> 2) & 3, ch = tid & 3;
         if (n_base + b < a.N)
@@ -338,9 +343,9 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     }
     cp_async_commit();
   };
-  prefetch(0);
-  prefetch(1);
-  cp_async_wait<1>();
+#pragma unroll
+  for (int i = 0; i < BWD_PF; ++i) prefetch(i);
+  cp_async_wait<BWD_PF - 1>();
   cluster_sync_all();
 
   float dc_state = 0.f;
@@ -348,8 +353,8 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
 
   for (int sidx = 0; sidx < a.S; ++sidx) {
     const int t = a.S - 1 - sidx;
-    const int pp = sidx & 1, buf = sidx % 3;
-    prefetch(sidx + 2);
+    const int pp = sidx & 1, buf = sidx % BWD_RING;
+    prefetch(sidx + BWD_PF);
     // everything that does not depend on the recurrence first
     const __nv_bfloat16* gp = in_g + (buf * NB + bsel) * GP + unit_l;
     const float xi = __bfloat162float(gp[0]), xf = __bfloat162float(gp[32]), xg = __bfloat162float(gp[64]),
@@ -367,6 +372,10 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
       tanh_d(xi, gi, gin);  // gin = 1 - h_t^2
       gf = gfn = gg = ggd = go = gon = tc = tcd = 0.f;
     }
+    // pin the gate recomputation (ten MUFU ops) BEFORE the wait for the other CTAs' partial dh: volatile asm is not
+    // reordered against the volatile try_wait loop, so these values exist when the barrier flips and the transcendental
+    // latency hides behind the DSMEM exchange instead of extending the dependent chain of the step
+    asm volatile("" ::"f"(gi), "f"(gin), "f"(gf), "f"(gfn), "f"(gg), "f"(ggd), "f"(go), "f"(gon), "f"(tc), "f"(tcd), "f"(dh));
     if (sidx > 0) {
       mbar_wait(&bar[pp], ((sidx - 1) >> 1) & 1);
       const float* pr = P + ((pp * CL) * 32 + unit_l) * NB + bsel;
@@ -403,7 +412,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1) lstm_bwd_kernel(const LstmArg
     ds[32] = __float2bfloat16(d_f);
     ds[64] = __float2bfloat16(d_g);
     ds[96] = __float2bfloat16(d_o);
-    cp_async_wait<1>();
+    cp_async_wait<BWD_PF - 1>();  // the inputs of step sidx + 1 have landed
     __syncthreads();
     if (t > 0 && warp < ACTIVE) {
       // partial dh_{t-1}[j][b] = sum_{r in my 128 gate rows} W_hh[rg(r)][j] * dgate[b][r]
@@ -475,7 +484,7 @@ static int launch_lstm(const LstmArgs& a, bool backward, cudaStream_t stream) {
     e = cudaLaunchKernelEx(&cfg, kern, a);
   } else {
     auto kern = lstm_bwd_kernel<H, CELL>;
-    const size_t smem = (size_t)2 * CL * 32 * NB * 4 + (size_t)3 * NB * 136 * 2 + (size_t)2 * 3 * NB * 36 * 4 + (size_t)2 * NB * 136 * 2;
+    const size_t smem = (size_t)2 * CL * 32 * NB * 4 + (size_t)BWD_RING * NB * 136 * 2 + (size_t)2 * BWD_RING * NB * 36 * 4 + (size_t)2 * NB * 136 * 2;
     if (CL > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cfg.dynamicSmemBytes = smem;

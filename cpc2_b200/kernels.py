@@ -318,11 +318,14 @@ def lstm_bwd(w_hh, gates, c_all, dout, dgates, N, S, H, c0=None, h0=None, cell="
     _run("cpc_lstm_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32=None):
+def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32=None, rowsum=None):
     d = _lib.Attn()
     if out_f32 is not None:
         assert out_f32.dtype == torch.float32 and out_f32.shape == out.shape
         d.out_f32 = out_f32.data_ptr()
+    if rowsum is not None:
+        assert rowsum.dtype == torch.float32 and rowsum.numel() == G * Bt * Hh * S
+        d.rowsum = rowsum.data_ptr()
     d.G, d.Bt, d.Hh, d.S, d.dk = G, Bt, Hh, S, dk
     d.scale = 1.0 / (dk ** 0.5)
     d.qkv, d.gs_qkv, d.krel = _dp(qkv), Bt * S * 3 * Hh * dk, _dp(krel)
@@ -332,16 +335,16 @@ def _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32=No
     return d
 
 
-def attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0, out_f32=None):
-    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32)
+def attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0, out_f32=None, rowsum=None):
+    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32, rowsum)
     if PROFILE is not None:
         set_work(kind="tensor", flops=3.0 * G * Bt * Hh * S * S * dk)  # (mma.sync tensor cores, causal: ~half executed)
     _run("cpc_attn_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
 def attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0,
-             out_f32=None):
-    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32)
+             out_f32=None, rowsum=None):
+    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p, out_f32, rowsum)
     d.dout, d.dqkv, d.dscore, d.dkrel = _dp(dout), _dp(dqkv), _dp(dscore), _dp(dkrel)
     if PROFILE is not None:
         set_work(kind="tensor", flops=7.0 * G * Bt * Hh * S * S * dk)

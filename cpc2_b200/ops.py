@@ -21,6 +21,29 @@ GRAD_F32 = False
 FUSE_NORM = os.environ.get("CPC_FUSE_NORM", "1") != "0"
 
 
+# Inside torch.autograd.Function.forward grad mode is always off, so "will a backward follow?" cannot be read from
+# torch.is_grad_enabled() there: the Function says it (`with ops.saving(any(ctx.needs_input_grad))`), everything
+# below it asks ops.will_backward() before allocating buffers only a backward reads.
+_SAVING = []
+
+
+class saving:
+    def __init__(self, flag):
+        self.flag = bool(flag)
+
+    def __enter__(self):
+        _SAVING.append(self.flag)
+        return self
+
+    def __exit__(self, *exc):
+        _SAVING.pop()
+        return False
+
+
+def will_backward():
+    return _SAVING[-1] if _SAVING else torch.is_grad_enabled()
+
+
 def can_fuse_norm(C):
     return FUSE_NORM and C == 256
 

@@ -245,9 +245,14 @@ class TransformerStack:
             qkv_k = qkv
         att_k = torch.empty(G, N * nb * S, d, device=dev, dtype=BF16)
         probs = torch.empty(G, Bt, self.Hh, S, S, device=dev, dtype=BF16)
-        K.attn_fwd(qkv_k, krel, att_k, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop)
+        # fp32 copy of the attention output + the row sums of the stored (bf16) probabilities: the backward's exact row
+        # statistic D_i = dO_i . O_i / rowsum_i without a second dP sweep (CpcAttn.out_f32 / rowsum)
+        att32 = torch.empty(G, N * nb * S, d, device=dev) if ops.will_backward() else None
+        rowsum = torch.empty(G, Bt, self.Hh, S, device=dev) if ops.will_backward() else None
+        K.attn_fwd(qkv_k, krel, att_k, probs, G, Bt, self.Hh, S, self.dk, rng=rng, site=1, drop_p=drop, out_f32=att32,
+                   rowsum=rowsum)
         att = att_k.view(G, N, nb * S, d)[:, :, :L].reshape(G, T, d) if padded else att_k
-        return att, dict(qkv=qkv_k, att=att_k, probs=probs, Bt=Bt, geom=(L, N, nb, padded))
+        return att, dict(qkv=qkv_k, att=att_k, att32=att32, rowsum=rowsum, probs=probs, Bt=Bt, geom=(L, N, nb, padded))
 
     def _attn_bwd(self, sa, krel, dkrel, datt, G, T, rng, drop):
         """datt bf16 [G, T, d] -> dqkv bf16 [G, T, 3d] (dKrelpos accumulated into `dkrel`)."""
@@ -262,7 +267,7 @@ class TransformerStack:
         dqkv_k = torch.empty(G, N * nb * S, 3 * d, device=dev, dtype=BF16)
         dscore = torch.empty_like(sa["probs"])
         K.attn_bwd(sa["qkv"], krel, sa["att"], sa["probs"], datt_k, dqkv_k, dscore, dkrel, G, sa["Bt"], self.Hh, S,
-                   self.dk, rng=rng, site=1, drop_p=drop)
+                   self.dk, rng=rng, site=1, drop_p=drop, out_f32=sa["att32"], rowsum=sa["rowsum"])
         return dqkv_k.view(G, N, nb * S, 3 * d)[:, :, :L].reshape(G, T, 3 * d) if padded else dqkv_k
 
     # ------------------------------------------------------------------------------------------ forward
@@ -408,7 +413,8 @@ class _TransformerFn(torch.autograd.Function):
     def forward(ctx, x, stack, training, *params):
         N, S_in, d = x.shape
         xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
-        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
+        with ops.saving(any(ctx.needs_input_grad)):
+            out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
         ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
         return out32.view(N, S_in, stack.dout)
 
@@ -553,7 +559,8 @@ class _MultiHeadFn(torch.autograd.Function):
     def forward(ctx, x, stack, training, *params):
         N, S_in, d = x.shape
         xb = K.cast_bf16(x.detach().contiguous().float()).view(N * S_in, d)
-        out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
+        with ops.saving(any(ctx.needs_input_grad)):
+            out, out32, saved = stack.forward(xb, N * S_in, True, training, want_f32=True, seq_len=S_in)
         ctx.stack, ctx.saved, ctx.shape = stack, saved, (N, S_in, d)
         return out32
 

@@ -256,11 +256,16 @@ typedef struct {
   void* out; int64_t gs_out; void* probs;
   const void* rng; uint32_t rng_site; float drop_p;
   const void* dout; void* dqkv; void* dscore; void* dkrel;
-  /* optional fp32 copy of `out` ([G][Bt*S][d], group stride gs_out) written by fwd.  The backward does NOT read it
-   * (nor `out`): its row statistic D_i = sum_j P_ij dP_ij / sum_j P_ij is formed from the same bf16 P and the same
-   * recomputed dP that dS = P o (dP - D) uses, so rows of dS sum to zero to fp32 rounding whatever common component
-   * K and V carry (D_i = dO_i . O_i, the flash-attention shortcut, cost the Wq gradients two digits in trained models). */
+  /* Row statistic of the backward, D_i = sum_j P_ij dP_ij (the softmax Jacobian's common term).  dS = P o (dP - D) must
+   * sum to zero along every row to fp32 rounding: K and V of a trained model carry a large component common to all
+   * keys and any row-coherent error of D is multiplied by it in dQ.  Two exact ways to get it:
+   *   (a) out_f32 + rowsum given (fwd writes both): fwd forms O from the SAME bf16-rounded probabilities it stores,
+   *       O = dropout_scale * sum_j keep_ij P^_ij V_j, and rowsum_i = sum_j P^_ij; bwd takes D_i = dO_i . O_i / rowsum_i
+   *       -- algebraically sum_j P^_ij dP~_ij / sum_j P^_ij with the very P^ and V the backward multiplies;
+   *   (b) either null: bwd recomputes dP once more in a pre-pass and reduces P^ o dP~ itself (~20 % more time).
+   * out_f32: [G][Bt*S][d] fp32, group stride gs_out.  rowsum: [G][Bt][Hh][S] fp32. */
   void* out_f32;
+  void* rowsum;
 } CpcAttn;
 
 int cpc_attn_fwd(const CpcAttn* desc, void* stream);

@@ -13,7 +13,7 @@ BF = torch.bfloat16
 dev = "cuda"
 
 
-def case(G, Bt, Hh, S, dk, drop):
+def case(G, Bt, Hh, S, dk, drop, fast_d=True):
     d = Hh * dk
     qkv = (torch.randn(G, Bt * S, 3 * d, device=dev) * 0.5).to(BF)
     krel = (torch.rand(G, dk, S, device=dev) - 0.5) * (2 / math.sqrt(dk))
@@ -24,12 +24,15 @@ def case(G, Bt, Hh, S, dk, drop):
     dscore = torch.empty_like(probs)
     dkrel = torch.zeros(G, dk, S, device=dev)
     rng = torch.tensor([5, 1], device=dev, dtype=torch.int64) if drop else None
+    out32 = torch.empty(G, Bt * S, d, device=dev)
+    rowsum = torch.empty(G, Bt, Hh, S, device=dev)
+    extra = dict(out_f32=out32, rowsum=rowsum) if fast_d else {}
 
     def fwd():
-        K.attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=drop)
+        K.attn_fwd(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=drop, **extra)
 
     def bwd():
-        K.attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=drop)
+        K.attn_bwd(qkv, krel, out, probs, dout, dqkv, dscore, dkrel, G, Bt, Hh, S, dk, rng=rng, site=1, drop_p=drop, **extra)
     return fwd, bwd
 
 
@@ -51,6 +54,9 @@ if __name__ == "__main__":
                       ("heads g12 b8 h8 S116 dk32 eval", (12, 8, 8, 116, 32, 0.0)),
                       ("AR g1 b16 h8 S128 dk32", (1, 16, 8, 128, 32, 0.1)),
                       ("big heads g12 b4 h8 S244 dk64", (12, 4, 8, 244, 64, 0.1))]:
+        if not once:  # D from the forward's fp32 O / rowsum (a) against the in-kernel dP sweep (b), CpcAttn
+            f2, b2 = case(*cfg, fast_d=False)
+            print(f"{name + ' [D in-kernel]':40s} fwd {timeit(f2):8.1f} us   bwd {timeit(b2):8.1f} us", flush=True)
         fwd, bwd = case(*cfg)
         if once:
             fwd()
