@@ -877,6 +877,56 @@ def test_graphed_step_construction_has_no_side_effects():
         step.step()
 
 
+@pytest.mark.parametrize("ar_mode", ["LSTM", "transformer"])
+def test_adam_written_bf16_shadow_tracks_the_parameters(ar_mode):
+    """The arena-homed weights (prediction heads, transformer AR) have ONE persistent bf16 shadow that cpc_adam_step writes
+    together with the fp32 parameter (CpcAdamSpan.p16), so the captured step holds no weight cast.  After every replay the
+    shadow must equal a fresh round-to-nearest cast of the parameters, bit for bit; a parameter edited behind the
+    optimizer's back (in-place op -> autograd version bump) must be picked up by the next replay; and the same steps with
+    torch.optim.Adam (which never writes the shadow: it is re-cast every step) must give the same losses."""
+    _need_gpu()
+    from cpc2_b200 import kernels as K
+    from cpc2_b200 import train as T
+    from cpc2_b200.optim import FusedAdam
+    over = dict(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120, arMode=ar_mode)
+    args = T.defaultArgs(**over)
+    model, crit = build(args)
+    params = list(crit.parameters()) + list(model.parameters())
+    opt = FusedAdam(params, lr=1e-3)
+    step = T.GraphedTrainStep(model, crit, 4, args.sizeWindow, warmup=3, optimizer=opt, train_mode=False)
+    arenas = [crit.wPrediction.engine().arena]
+    if ar_mode == "transformer":
+        arenas += [m.stack().arena for m in model.gAR if hasattr(m, "stack")]
+    seq = predictable_sequence(4, args.sizeWindow, 3).cuda()
+    n0 = K.LAUNCHES
+
+    def check():
+        torch.cuda.synchronize()
+        for a in arenas:
+            assert a.shadow_valid()
+            assert torch.equal(a._shadow, a.flat.to(torch.bfloat16)), "bf16 shadow differs from the parameters"
+
+    losses = []
+    for _ in range(3):
+        losses.append(step.step(seq)[0].clone())
+        check()
+    assert K.LAUNCHES == n0, "a replay must not launch anything eagerly when nothing was edited"
+    with torch.no_grad():
+        arenas[0].params[0].mul_(0.5)  # behind the optimizer's back
+    assert not arenas[0].shadow_valid()
+    step.step(seq)
+    check()
+    step.close()
+    # the same three updates with torch.optim.Adam on a fresh copy (other negatives are drawn, so only the loss level
+    # is comparable: a stale or half-written shadow would send it off by far more than 3e-2)
+    model2, crit2 = build(args)
+    opt2 = torch.optim.Adam(list(crit2.parameters()) + list(model2.parameters()), lr=1e-3)
+    for i in range(3):
+        out = run_step(model2, crit2, seq, collect=False, seed=0)
+        opt2.step()
+        assert (out["loss"].cuda() - losses[i]).abs().max() < 3e-2, (i, out["loss"], losses[i])
+
+
 def test_multi_device_dataparallel_replicas_are_rejected():
     """nn.DataParallel over several devices replicates the modules (replicas carry `_is_replica`); the engines
     and arenas of this package are per process, so a replica's forward raises instead of launching on device-0 pointers
