@@ -326,6 +326,22 @@ class _EncoderFn(torch.autograd.Function):
                 A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
                 dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
+            grads = []
+            for l in range(5):
+                k = GEOMETRY[l][0]
+                dw, dcb, dg, db = gv[4 * l:4 * l + 4]
+                grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
+            # The gradients of conv1-4 and their norms (all but 3.3 K of the encoder's 2.4 M parameters) are complete
+            # once THIS half's conv1 weight gradient is (the other half of a pair has finished or is waited for below):
+            # announce them now, from the weight-gradient side stream, so that their all-reduce and optimizer step run
+            # next to conv0's backward instead of trailing the step; only conv0's own slice is announced at the end.
+            n0 = sum(sizes[:4])
+            early = ops.EARLY_ENCODER and bool(ops.GRAD_READY) and (pair is None or pair.pending == 1)
+            if early:
+                with ops.side(wg):  # behind every weight gradient of this half (this stream) and the main chain so far
+                    if pair is not None and pair.first_done is not None:
+                        torch.cuda.current_stream().wait_event(pair.first_done)
+                    ops.grad_ready("encoder.main", gflat[n0:], ctx.params[4:], grads[4:])
             dw0, db0, dg0, dbe0 = gv[0:4]
             K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
                         pad_next[0])
@@ -344,12 +360,10 @@ class _EncoderFn(torch.autograd.Function):
         del ws
         if not last:
             return (None, None) + (None,) * 20
-        grads = []
-        for l in range(5):
-            k = GEOMETRY[l][0]
-            dw, dcb, dg, db = gv[4 * l:4 * l + 4]
-            grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
-        ops.grad_ready("encoder", gflat, ctx.params, grads)
+        if early:
+            ops.grad_ready("encoder.conv0", gflat[:n0], ctx.params[:4], grads[:4])
+        else:
+            ops.grad_ready("encoder", gflat, ctx.params, grads)
         return (None, None, *grads)
 
 

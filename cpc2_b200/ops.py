@@ -98,6 +98,12 @@ _SIDE = {}
 EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")
 
 
+# announce the gradients of conv1-4 before conv0's backward runs (model._EncoderFn.backward): the encoder's all-reduce
+# and optimizer step then overlap the last kernel of the step instead of trailing it.  CPC_EARLY_ENCODER=0 restores the
+# single "encoder" announcement.
+EARLY_ENCODER = os.environ.get("CPC_EARLY_ENCODER", "1") != "0"
+
+
 def early_ffn():
     if EARLY_FFN == "auto":
         import torch.distributed as dist
