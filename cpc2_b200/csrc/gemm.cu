@@ -73,6 +73,7 @@ struct GemmKernelArgs {
   float norm_eps;
   int norm_unbiased, norm_halo;
   int vec16, vec16n;  // out_bf16 / norm_bf16 rows take 16-byte stores (base, row stride and group stride 16-byte aligned)
+  int cl_n;           // EPI_NORM_CL: CTAs per cluster = column chunks per row (tile index: chunk fastest); 0 otherwise
 };
 
 constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, each owns half of the tile's columns
@@ -86,7 +87,11 @@ struct GemmSmem {
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
   static constexpr int STAT_OFF = BAR_OFF + (2 * STAGES + 4) * 8 + 16;  // EPI_NORM: [tile parity][column half][BM] float2
   static constexpr int STAT_BYTES = 2 * 2 * BM * 8;
-  static constexpr int TOTAL = STAT_OFF + STAT_BYTES + 1024;  // + alignment slack
+  static constexpr int XCL_MAX = 4;                                  // EPI_NORM_CL: cluster size
+  static constexpr int XSTAT_OFF = STAT_OFF + STAT_BYTES;            // [2 * XCL_MAX][BM] float2 partial row statistics
+  static constexpr int XSTAT_BYTES = BN <= 128 ? 2 * XCL_MAX * BM * 8 : 0;
+  static constexpr int XBAR_OFF = XSTAT_OFF + XSTAT_BYTES;           // the exchange mbarrier
+  static constexpr int TOTAL = XBAR_OFF + 16 + 1024;  // + alignment slack
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (128 / 256 / 512 columns)
 };
 
@@ -95,10 +100,18 @@ struct TileCoord {
 };
 __device__ __forceinline__ TileCoord decode_tile(const GemmKernelArgs& p, int tile, int bn) {
   TileCoord t;
-  const int mi = tile % p.tiles_m;
-  const int r = tile / p.tiles_m;
-  const int ni = r % p.tiles_n;
-  const int z = r / p.tiles_n;
+  int mi, ni, z;
+  if (p.cl_n > 0) {  // the column chunks of a row are consecutive tiles = the CTAs of one cluster
+    ni = tile % p.tiles_n;
+    const int r = tile / p.tiles_n;
+    mi = r % p.tiles_m;
+    z = r / p.tiles_m;
+  } else {
+    mi = tile % p.tiles_m;
+    const int r = tile / p.tiles_m;
+    ni = r % p.tiles_n;
+    z = r / p.tiles_n;
+  }
   t.m0 = mi * BM;
   t.n0 = ni * bn;
   t.grp = z / p.k_splits;
@@ -153,6 +166,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_init(&acc_full[b], 1);
       mbar_init(&acc_empty[b], EPI_WARPS);
     }
+    if constexpr (MODE == EPI_NORM_CL) {
+      uint64_t* xbar = reinterpret_cast<uint64_t*>(smem + L::XBAR_OFF);
+      mbar_init(xbar, 1);
+      fence_barrier_init();
+      mbar_expect_tx(xbar, static_cast<uint32_t>((p.cl_n - 1) * 2 * BM * 8));  // the peers' partial row statistics
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -162,6 +181,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if constexpr (MODE == EPI_NORM_CL) cluster_sync_all();  // every CTA's exchange barrier is armed before anyone sends
   const uint32_t tmem_base = *tmem_slot;
   // PDL: everything above (tensor-map fetch, barrier init, TMEM allocation) overlapped the tail of the preceding grid;
   // nothing below reads or writes global memory before that grid has completed (cpc_internal.h)
@@ -263,6 +283,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if constexpr (MODE == EPI_NORM)
         epilogue_tile_norm<BN>(p, tc, taddr, q, half, lane, &acc_full[buf], (lt >> 1) & 1,
                                reinterpret_cast<float2*>(smem + L::STAT_OFF) + (lt & 1) * 2 * BM);
+      else if constexpr (MODE == EPI_NORM_CL)
+        epilogue_tile_norm_cl<BN>(p, tc, taddr, q, half, lane, &acc_full[buf], (lt >> 1) & 1,
+                                  NormClSmem{reinterpret_cast<float2*>(smem + L::XSTAT_OFF),
+                                             reinterpret_cast<uint64_t*>(smem + L::XBAR_OFF), p.cl_n});
       else
         epilogue_tile<MODE, BN>(p, tc, taddr, q, half, lane, rng, &acc_full[buf], (lt >> 1) & 1);
       // this warp's TMEM reads of the buffer are complete (tcgen05.wait::ld inside): hand it back to the MMA warp
@@ -328,6 +352,25 @@ static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, GemmKe
   ka.tiles_m = (ka.M + BM - 1) / BM;
   ka.tiles_n = (ka.N + BN - 1) / BN;
   ka.total_tiles = ka.tiles_m * ka.tiles_n * groups * ka.k_splits;
+  if constexpr (MODE == EPI_NORM_CL) {
+    // one tile per CTA, the tiles_n column chunks of a row form one cluster (their exchange barrier is single-use)
+    if (ka.tiles_n != ka.cl_n || ka.cl_n < 2 || ka.cl_n > L::XCL_MAX || ka.k_splits != 1) return CPC_ERR_UNSUPPORTED;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ka.total_tiles);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = L::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ka.cl_n;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    return cudaLaunchKernelEx(&cfg, kern, ta, tb, ka) == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
+  }
   const int grid = ka.total_tiles < sm_count() ? ka.total_tiles : sm_count();
   launch_k(kern, dim3(grid), dim3(GEMM_THREADS), L::TOTAL, stream, ta, tb, ka);
   return cudaGetLastError() == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
@@ -339,6 +382,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmK
   // epilogue mode (exclusive; the entry point has rejected combinations no mode covers)
   if (ka.norm_gamma != nullptr) {
     if constexpr (BN == 256 && !A_MN && !B_MN) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_NORM>(ta, tb, ka, groups, stream);
+    else if constexpr (!A_MN && !B_MN) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_NORM_CL>(ta, tb, ka, groups, stream);
     else return CPC_ERR_UNSUPPORTED;
   }
   if (ka.k_splits > 1) return launch_gemm_mode<BN, STAGES, A_MN, B_MN, EPI_SPLITK>(ta, tb, ka, groups, stream);
@@ -427,7 +471,7 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
               ka.ld_norm_bf16 % 8 == 0 && ka.gs_norm_bf16 % 8 == 0;
   const bool fused_norm = d->norm_gamma != nullptr;
   if (fused_norm) {
-    if (d->N != 256 || d->a_major != 0 || d->b_major != 0 || k_splits > 1 || d->accumulate || d->gate != nullptr ||
+    if ((d->N != 256 && d->N != 512) || d->a_major != 0 || d->b_major != 0 || k_splits > 1 || d->accumulate || d->gate != nullptr ||
         (d->rng != nullptr && d->drop_p > 0.f) || d->norm_beta == nullptr || d->out_f32 != nullptr ||
         (d->norm_bf16 == nullptr && d->norm_f32 == nullptr) || d->norm_halo < 0 || d->norm_halo > 4)
       return CPC_ERR_UNSUPPORTED;
@@ -460,7 +504,22 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
     }
   }
   if (d->force_bn == 64 || d->force_bn == 128 || d->force_bn == 256) bn = d->force_bn;
-  if (fused_norm) bn = 256;  // one accumulator tile = one whole row
+  ka.cl_n = 0;
+  if (fused_norm) {
+    // one BN = 256 accumulator tile = one whole row -- unless that leaves most SMs idle (conv3 / conv4 of the encoder:
+    // 16 / 8 row tiles per half batch) or the row is 512 wide: then the row is split over a 4-CTA cluster (EPI_NORM_CL).
+    // The split multiplies the main-loop work by four (every chunk streams the whole A tile, and the loop is bound by
+    // TMA latency / pipeline depth, not by bytes), so it only pays while 4 x row tiles x 2 concurrent half batches still
+    // fit the 148 SMs in one wave: measured, conv1 / conv2 (64 / 32 row tiles) got slower in the step (1.24 vs 1.22 ms).
+    static const int cl_below = [] {  // CPC_NORM_CLUSTER_BELOW=<row tiles>: 0 disables the cluster form for 256-wide rows
+      const char* e = getenv("CPC_NORM_CLUSTER_BELOW");
+      return e != nullptr ? atoi(e) : 17;
+    }();
+    const long long row_tiles = (long long)((d->M + BM - 1) / BM) * d->groups;
+    if (d->N == 512) { bn = 128; ka.cl_n = 4; }
+    else if (row_tiles < cl_below) { bn = 64; ka.cl_n = 4; }
+    else bn = 256;
+  }
 
   CUtensorMap ta, tb;
   int rc = encode_operand_map(&ta, d->a, d->a_dim0, d->a_dim1, d->a_dim2, d->a_stride1, d->a_stride2, d->a_major, BM);
@@ -469,7 +528,7 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   if (rc != CPC_OK) return rc;
 
   switch (bn) {
-    case 64: return dispatch_major<64, 6>(ta, tb, ka, d->groups, d->a_major, d->b_major, stream);
+    case 64: return dispatch_major<64, 8>(ta, tb, ka, d->groups, d->a_major, d->b_major, stream);  // 8 x 24 KB in flight
     case 128: return dispatch_major<128, 6>(ta, tb, ka, d->groups, d->a_major, d->b_major, stream);
     default: return dispatch_major<256, 4>(ta, tb, ka, d->groups, d->a_major, d->b_major, stream);
   }

@@ -15,7 +15,7 @@ namespace cpc {
 // (timing probe only) true for the CTA's first tile: accumulator buffer 0, first use
 __device__ __forceinline__ bool acc_full_bar_is_first(const uint64_t* bar) { return (reinterpret_cast<uintptr_t>(bar) & 8) == 0; }
 
-enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5, EPI_NORM = 6 };
+enum EpiMode { EPI_PLAIN = 0, EPI_RES = 1, EPI_GATE = 2, EPI_DROP = 3, EPI_ACCUM = 4, EPI_SPLITK = 5, EPI_NORM = 6, EPI_NORM_CL = 7 };
 
 struct EpiRng {
   uint32_t seed_lo, seed_hi, thresh;
@@ -271,27 +271,23 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
 
   float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
   // the first chunk's bias / residual are requested before the accumulator is awaited (they overlap the main loop)
-  // The residual of the WHOLE tile row set (4 chunks x 4 rows x 4 column groups, 64 registers) is requested before the
-  // accumulator is awaited and kept for both sweeps: a chunk-by-chunk double buffer exposed one L2 round trip per chunk
-  // and sweep (8 x ~0.4 us of the 7-9 us this epilogue took, tools/gemm_phase_probe.py).  The per-column vectors
-  // (bias, gamma, beta: the same 1 KB for every row) are read per chunk and hit L1 after the first touch.
+  // bias and residual of chunk c + 1 are requested while chunk c is processed (two register slots: all four chunks at
+  // once put this kernel over the 168 registers a 10-warp CTA can have and it spilled)
   float2 b2[2][4];
-  uint32_t rx[NC][4][4];
-  auto load_bias = [&](int c, int slot) {
+  uint32_t rx[2][4][4];
+  auto load_chunk = [&](int c, int slot) {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
       b2[slot][j] = bias != nullptr ? *reinterpret_cast<const float2*>(bias + c * 32 + 8 * j) : make_float2(0.f, 0.f);
-  };
-#pragma unroll
-  for (int c = 0; c < NC; ++c)
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        rx[c][i][j] = (res != nullptr && rok[i])
-                          ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
-                          : 0u;
-  load_bias(0, 0);
+        rx[slot][i][j] = (res != nullptr && rok[i])
+                             ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
+                             : 0u;
+  };
+  load_chunk(0, 0);
   mbar_wait(acc_full_bar, parity);
 #ifdef CPC_GEMM_TIMING
   if (parity == 0 && threadIdx.x == 64 && acc_full_bar_is_first(acc_full_bar)) GEMM_TSTAMP(7);
@@ -303,15 +299,15 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
     uint32_t v[2][16];
     tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
     tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
-    if (c + 1 < NC) load_bias(c + 1, (c + 1) & 1);
+    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c][i][j]);
-        float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c][i][j]);
+        float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
+        float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
         s[i] += x0 + x1;
         ss[i] = fmaf(x0, x0, fmaf(x1, x1, ss[i]));
         w[j] = epi_pack_bf16x2(x0, x1);
@@ -362,7 +358,7 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
   }
   // ---------------------------------------------------------------- sweep 2: normalise, affine, ReLU, store
   const float relu_floor = p.relu ? 0.f : -INFINITY;
-  load_bias(0, 0);
+  load_chunk(0, 0);
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     uint32_t v[2][16];
@@ -374,15 +370,15 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
       g2[j] = *reinterpret_cast<const float2*>(gam + c * 32 + 8 * j);
       e2[j] = *reinterpret_cast<const float2*>(bet + c * 32 + 8 * j);
     }
-    if (c + 1 < NC) load_bias(c + 1, (c + 1) & 1);
+    if (c + 1 < NC) load_chunk(c + 1, (c + 1) & 1);
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c][i][j]);
-        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c][i][j]);
+        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c & 1][j].x) + bf16lo(rx[c & 1][i][j]);
+        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c & 1][j].y) + bf16hi(rx[c & 1][i][j]);
         const float y0 = fmaxf(fmaf((x0 - mean[i]) * rstd[i], g2[j].x, e2[j].x), relu_floor);
         const float y1 = fmaxf(fmaf((x1 - mean[i]) * rstd[i], g2[j].y, e2[j].y), relu_floor);
         w[j] = epi_pack_bf16x2(y0, y1);
@@ -404,6 +400,193 @@ __device__ __forceinline__ void epilogue_tile_norm(const GemmKernelArgs& p, cons
   // ---------------------------------------------------------------- zero halo rows around the sequence (group)
   if (p.norm_halo > 0 && q == 0 && p.norm_bf16 != nullptr) {
     __nv_bfloat16* base = p.norm_bf16 + g * p.gs_norm_bf16 + half * (BN / 2) + lane * 4;
+    if (tc.m0 == 0)
+      for (int h = 1; h <= p.norm_halo; ++h) *reinterpret_cast<uint2*>(base - (long long)h * p.ld_norm_bf16) = make_uint2(0u, 0u);
+    if (tc.m0 + BM >= p.M)
+      for (int h = 0; h < p.norm_halo; ++h)
+        *reinterpret_cast<uint2*>(base + (long long)(p.M + h) * p.ld_norm_bf16) = make_uint2(0u, 0u);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// EPI_NORM_CL: the same row normalisation with the row SPLIT OVER A THREAD-BLOCK CLUSTER.  A 256- or 512-wide row is
+// cut in CN = 4 column chunks of BN = 64 / 128; the CN CTAs of a cluster (cluster rank = chunk index) each run the
+// main loop of one 128 x BN tile, reduce (sum x, sum x^2) over their own columns, push those partials into every
+// peer's shared memory with st.async (data + mbarrier complete_tx in one DSMEM hop, as the recurrent kernels do),
+// add up the 2*CN partials of a row and normalise their own columns.  Why: with one BN = 256 tile per row conv2 / 3 / 4
+// of the encoder are 32 / 16 / 8 CTAs on 148 SMs, each running a 16-k-block main loop and a two-sweep epilogue alone
+// (17 us); four times as many CTAs with a quarter of the MMA, load and epilogue work each are not bound by one SM's
+// L2 link and TMEM read port (tools/gemm_phase_probe.py), and 512-wide rows (hidden 512) become fusable at all.
+// One tile per CTA (grid = tiles, not persistent): the exchange barrier is used once, phase 0.
+struct NormClSmem {
+  float2* xstat;    // [2 * CN][BM]: slot 2 * rank + column half
+  uint64_t* xbar;   // armed for (CN - 1) * 2 * BM * 8 bytes at kernel start
+  int cn;
+};
+
+template <int BN>
+__device__ __forceinline__ void epilogue_tile_norm_cl(const GemmKernelArgs& p, const TileCoord& tc, uint32_t taddr, int q,
+                                                      int half, int lane, uint64_t* acc_full_bar, uint32_t parity,
+                                                      const NormClSmem& x) {
+  static_assert(BN == 64 || BN == 128, "cluster row norm: 64 or 128 columns per CTA");
+  constexpr int NC = BN / 64;  // 32-column chunks per warp (this warp owns BN/2 columns)
+  const int rsub = lane >> 2, csub = (lane & 3) * 2;
+  const long long g = tc.grp;
+  const int row0 = tc.m0 + q * 32 + rsub;
+  const int col0 = tc.n0 + half * (BN / 2) + csub;  // global column of this lane's first pair
+  const uint32_t rank = cluster_ctarank();
+  bool rok[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) rok[i] = row0 + 8 * i < p.M;
+  const float* bias = p.bias != nullptr ? p.bias + g * p.gs_bias + col0 : nullptr;
+  const float* gam = p.norm_gamma + g * p.gs_norm_param + col0;
+  const float* bet = p.norm_beta + g * p.gs_norm_param + col0;
+  const __nv_bfloat16* res = p.res != nullptr ? p.res + g * p.gs_res + (long long)row0 * p.ld_res + col0 : nullptr;
+  __nv_bfloat16* o16 = p.out_bf16 != nullptr ? p.out_bf16 + g * p.gs_bf16 + (long long)row0 * p.ldd_bf16 + col0 : nullptr;
+  __nv_bfloat16* n16 = p.norm_bf16 != nullptr ? p.norm_bf16 + g * p.gs_norm_bf16 + (long long)row0 * p.ld_norm_bf16 + col0 : nullptr;
+  float* n32 = p.norm_f32 != nullptr ? p.norm_f32 + g * p.gs_norm_f32 + (long long)row0 * p.ld_norm_f32 + col0 : nullptr;
+  const float alpha = p.alpha;
+
+  // everything the tile reads from global memory, requested before the accumulator is awaited
+  float2 b2[NC][4];
+  uint32_t rx[NC][4][4];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      b2[c][j] = bias != nullptr ? *reinterpret_cast<const float2*>(bias + c * 32 + 8 * j) : make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        rx[c][i][j] = (res != nullptr && rok[i])
+                          ? __ldg(reinterpret_cast<const unsigned int*>(res + (long long)(8 * i) * p.ld_res + c * 32 + 8 * j))
+                          : 0u;
+  }
+  mbar_wait(acc_full_bar, parity);
+#ifdef CPC_GEMM_TIMING
+  if (threadIdx.x == 64) GEMM_TSTAMP(7);
+#endif
+  tc_fence_after();
+  // ---------------------------------------------------------------- sweep 1: pre-norm values + partial row statistics
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    uint32_t v[2][16];
+    tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+    tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c][j].x) + bf16lo(rx[c][i][j]);
+        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c][j].y) + bf16hi(rx[c][i][j]);
+        s[i] += x0 + x1;
+        ss[i] = fmaf(x0, x0, fmaf(x1, x1, ss[i]));
+        w[j] = epi_pack_bf16x2(x0, x1);
+      }
+      if (o16 != nullptr) {  // (warp-uniform)
+        __nv_bfloat16* dst = o16 + (long long)(8 * i) * p.ldd_bf16 + c * 32;
+        if (p.vec16) {
+          quad_transpose4(w, lane & 3);
+          if (rok[i]) *reinterpret_cast<uint4*>(dst - csub + 8 * (lane & 3)) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if (rok[i]) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint32_t*>(dst + 8 * j) = w[j];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 1);
+    ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 1);
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 2);
+    ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 2);
+  }
+  // ---------------------------------------------------------------- exchange: this warp's partials to every CTA of the cluster
+  const int slot = 2 * (int)rank + half;
+  if ((lane & 3) == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2* mine = x.xstat + slot * BM + q * 32 + rsub + 8 * i;
+      *mine = make_float2(s[i], ss[i]);
+      const uint32_t a = smem_u32(mine), b = smem_u32(x.xbar);
+      for (uint32_t r = 0; r < (uint32_t)x.cn; ++r)
+        if (r != rank) st_async_v2_f32(mapa(a, r), s[i], ss[i], mapa(b, r));
+    }
+  }
+  asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps: local partials written
+  mbar_wait(x.xbar, 0);                           // ... and the (CN - 1) * 2 KB of the peers have landed
+  float mean[4], rstd[4];
+  const int width = BN * x.cn;
+  const float inv_n = 1.f / static_cast<float>(width);
+  const float inv_d = 1.f / static_cast<float>(p.norm_unbiased ? width - 1 : width);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float tot = 0.f, tots = 0.f;
+    for (int sl = 0; sl < 2 * x.cn; ++sl) {
+      const float2 o = x.xstat[sl * BM + q * 32 + rsub + 8 * i];
+      tot += o.x;
+      tots += o.y;
+    }
+    mean[i] = tot * inv_n;
+    const float var = fmaxf((tots - tot * mean[i]) * inv_d, 0.f);
+    rstd[i] = rsqrtf(var + p.norm_eps);
+  }
+  if (rank == 0 && half == 0 && (lane & 3) == 0 && p.norm_mean != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (rok[i]) {
+        p.norm_mean[g * p.gs_norm_stat + row0 + 8 * i] = mean[i];
+        p.norm_rstd[g * p.gs_norm_stat + row0 + 8 * i] = rstd[i];
+      }
+    }
+  }
+  // ---------------------------------------------------------------- sweep 2: normalise, affine, ReLU, store
+  const float relu_floor = p.relu ? 0.f : -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    uint32_t v[2][16];
+    tmem_ld_16x256b_x4(taddr + c * 32, v[0]);
+    tmem_ld_16x256b_x4(taddr + (16u << 16) + c * 32, v[1]);
+    float2 g2[4], e2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      g2[j] = *reinterpret_cast<const float2*>(gam + c * 32 + 8 * j);
+      e2[j] = *reinterpret_cast<const float2*>(bet + c * 32 + 8 * j);
+    }
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float x0 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1)]), alpha, b2[c][j].x) + bf16lo(rx[c][i][j]);
+        const float x1 = fmaf(__uint_as_float(v[i >> 1][4 * j + 2 * (i & 1) + 1]), alpha, b2[c][j].y) + bf16hi(rx[c][i][j]);
+        const float y0 = fmaxf(fmaf((x0 - mean[i]) * rstd[i], g2[j].x, e2[j].x), relu_floor);
+        const float y1 = fmaxf(fmaf((x1 - mean[i]) * rstd[i], g2[j].y, e2[j].y), relu_floor);
+        w[j] = epi_pack_bf16x2(y0, y1);
+        if (n32 != nullptr && rok[i])
+          *reinterpret_cast<float2*>(n32 + (long long)(8 * i) * p.ld_norm_f32 + c * 32 + 8 * j) = make_float2(y0, y1);
+      }
+      if (n16 != nullptr) {  // (warp-uniform)
+        __nv_bfloat16* dst = n16 + (long long)(8 * i) * p.ld_norm_bf16 + c * 32;
+        if (p.vec16n) {
+          quad_transpose4(w, lane & 3);
+          if (rok[i]) *reinterpret_cast<uint4*>(dst - csub + 8 * (lane & 3)) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if (rok[i]) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint32_t*>(dst + 8 * j) = w[j];
+        }
+      }
+    }
+  }
+  // ---------------------------------------------------------------- zero halo rows around the sequence (own columns)
+  if (p.norm_halo > 0 && q == 0 && p.norm_bf16 != nullptr && lane * 4 < BN / 2) {
+    __nv_bfloat16* base = p.norm_bf16 + g * p.gs_norm_bf16 + tc.n0 + half * (BN / 2) + lane * 4;
     if (tc.m0 == 0)
       for (int h = 1; h <= p.norm_halo; ++h) *reinterpret_cast<uint2*>(base - (long long)h * p.ld_norm_bf16) = make_uint2(0u, 0u);
     if (tc.m0 + BM >= p.M)

@@ -261,7 +261,7 @@ class _EncoderFn(torch.autograd.Function):
                 y, a = ys[l], acts[l]
                 A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
                 hn = pad_next[l]  # halo rows of `a` are zeroed by the kernel that writes it
-                if ops.can_fuse_norm(C):
+                if ops.can_fuse_norm(C, Lout, N):
                     # conv + bias -> y (kept for the backward), ChannelNorm + ReLU -> a, all in the GEMM epilogue
                     K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b,
                            relu=True, norm=dict(gamma=g.reshape(C), beta=be.reshape(C), out_bf16=(a, C, (Lout + 2 * hn) * C),

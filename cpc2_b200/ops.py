@@ -16,8 +16,9 @@ NUM_SMS = 148
 # Debug switch: keep the gradients that feed a normalisation backward in fp32 between kernels.  Measured to
 # make no difference to gradient parity (profiles/r01_grad_noise.log), so the default is bf16 (half the bytes).
 GRAD_F32 = False
-# ChannelNorm / LayerNorm of 256-wide rows inside the epilogue of the GEMM that produces them (one accumulator tile is
-# one whole row): no separate cpc_rownorm_fwd launch.  False restores the two-kernel form (also used for other widths).
+# ChannelNorm / LayerNorm of 256- and 512-wide rows inside the epilogue of the GEMM that produces them (one accumulator
+# tile is one whole row, or the row is split over a 4-CTA cluster that exchanges partial statistics through DSMEM): no
+# separate cpc_rownorm_fwd launch.  False restores the two-kernel form (also used for other widths).
 FUSE_NORM = os.environ.get("CPC_FUSE_NORM", "1") != "0"
 
 
@@ -44,8 +45,16 @@ def will_backward():
     return _SAVING[-1] if _SAVING else torch.is_grad_enabled()
 
 
-def can_fuse_norm(C):
-    return FUSE_NORM and C == 256
+def can_fuse_norm(C, rows=None, groups=1):
+    """256-wide rows: always (the kernel picks one BN = 256 tile per row or the 4-CTA cluster split by the number of row
+    tiles).  512-wide rows only exist in the cluster form, which streams the A tile four times: worth it for small
+    launches only (rows x groups up to 16 row tiles of 128), otherwise GEMM + cpc_rownorm_fwd is faster (measured at
+    hidden 512 / window 40960: 2.29 ms of GEMM time fused everywhere against 1.95 + 0.18 ms in two kernels)."""
+    if not FUSE_NORM:
+        return False
+    if C == 256:
+        return True
+    return C == 512 and rows is not None and ((rows + 127) // 128) * groups <= 16
 
 
 # Callbacks invoked by the modules' backward right after every kernel writing a module's flat fp32 gradient

@@ -289,7 +289,7 @@ class TransformerStack:
         y = torch.empty(G, T, d, device=dev, dtype=BF16)
         mean1 = torch.empty(G * T, device=dev)
         rstd1 = torch.empty(G * T, device=dev)
-        if ops.can_fuse_norm(d):  # y = LN(x + att . Wo^T) in the epilogue of the Wo product
+        if ops.can_fuse_norm(d, T, G):  # y = LN(x + att . Wo^T) in the epilogue of the Wo product
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res,
                            norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], gs_param=d, out_bf16=y, mean=mean1, rstd=rstd1,
                                      gs_stat=T))
@@ -306,7 +306,7 @@ class TransformerStack:
         out32 = torch.empty(G, T, dout, device=dev) if want_f32 else None
         mean2 = torch.empty(G * T, device=dev)
         rstd2 = torch.empty(G * T, device=dev)
-        if ops.can_fuse_norm(dout):  # out = LN(u . Wl^T + bl) in the epilogue of the last_linear product
+        if ops.can_fuse_norm(dout, T, G):  # out = LN(u . Wl^T + bl) in the epilogue of the last_linear product
             ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout,
                            norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], gs_param=dout, out_bf16=out, out_f32=out32,
                                      mean=mean2, rstd=rstd2, gs_stat=T))
@@ -462,7 +462,7 @@ class MultiHeadStack(TransformerStack):
         y = torch.empty(T, d, device=dev, dtype=BF16)
         mean1 = torch.empty(T, device=dev)
         rstd1 = torch.empty(T, device=dev)
-        if ops.can_fuse_norm(d):
+        if ops.can_fuse_norm(d, T):
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0),
                            norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1))
         else:
@@ -479,7 +479,7 @@ class MultiHeadStack(TransformerStack):
         out32 = torch.empty(Kc, T, dout, device=dev) if want_f32 else None
         mean2 = torch.empty(Kc * T, device=dev)
         rstd2 = torch.empty(Kc * T, device=dev)
-        if ops.can_fuse_norm(dout):
+        if ops.can_fuse_norm(dout, Kc * T):
             ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"],
                            norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], out_bf16=out.view(Kc * T, dout),
                                      out_f32=None if out32 is None else out32.view(Kc * T, dout), mean=mean2, rstd=rstd2))

@@ -41,14 +41,19 @@ def cos(a, b):
 
 
 # ------------------------------------------------------------------------------------------ GEMM
-@pytest.mark.parametrize("G,M,Kd,unbiased,relu,with_res,halo", [(3, 300, 192, True, True, False, 2), (2, 928, 256, False, False, True, 0),
-                                                                (1, 128, 2048, True, True, False, 1), (5, 37, 64, False, False, True, 0)])
-def test_gemm_fused_row_norm(K, G, M, Kd, unbiased, relu, with_res, halo):
-    """EPI_NORM: ChannelNorm (unbiased variance, cpc/model.py:52-60) / LayerNorm (cpc/transformers.py:124,130) of the
-    256-wide output rows inside the GEMM epilogue, against fp32 torch on the same bf16 operands: pre-norm rows, the
-    normalised rows (bf16 and fp32), mean / rstd, and the zero halo rows around every group."""
+@pytest.mark.parametrize("N,G,M,Kd,unbiased,relu,with_res,halo", [
+    # fewer than 65 row tiles: the row is split over a 4-CTA cluster, partial statistics exchanged through DSMEM (EPI_NORM_CL)
+    (256, 3, 300, 192, True, True, False, 2), (256, 2, 928, 256, False, False, True, 0),
+    (256, 1, 128, 2048, True, True, False, 1), (256, 5, 37, 64, False, False, True, 0), (256, 8, 1024, 2048, True, True, False, 2),
+    # 65 or more row tiles: one BN = 256 accumulator tile per row (EPI_NORM)
+    (256, 12, 928, 256, False, False, True, 0), (256, 9, 1000, 128, True, True, False, 1),
+    # 512-wide rows (hidden 512): always the cluster form, 128 columns per CTA
+    (512, 2, 300, 192, True, True, False, 2), (512, 12, 488, 512, False, False, True, 0), (512, 1, 50, 64, True, False, True, 1)])
+def test_gemm_fused_row_norm(K, N, G, M, Kd, unbiased, relu, with_res, halo):
+    """EPI_NORM / EPI_NORM_CL: ChannelNorm (unbiased variance, cpc/model.py:52-60) / LayerNorm (cpc/transformers.py:124,130)
+    of the 256- or 512-wide output rows inside the GEMM epilogue, against fp32 torch on the same bf16 operands: pre-norm
+    rows, the normalised rows (bf16 and fp32), mean / rstd, and the zero halo rows around every group."""
     torch.manual_seed(2)
-    N = 256
     a = bf(torch.randn(G, M, Kd, device="cuda"))
     w = bf(torch.randn(G, N, Kd, device="cuda") / Kd ** 0.5)
     bias = torch.randn(G, N, device="cuda")
