@@ -83,6 +83,7 @@ class GemmDesc(ctypes.Structure):
         ("norm_f32", ctypes.c_void_p), ("ld_norm_f32", ctypes.c_int64), ("gs_norm_f32", ctypes.c_int64),
         ("norm_mean", ctypes.c_void_p), ("norm_rstd", ctypes.c_void_p), ("gs_norm_stat", ctypes.c_int64),
         ("norm_eps", ctypes.c_float), ("norm_unbiased", ctypes.c_int), ("norm_halo", ctypes.c_int),
+        ("a_slab_mul", ctypes.c_int), ("b_slab_mul", ctypes.c_int),
     ]
 
 

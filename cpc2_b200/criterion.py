@@ -626,9 +626,10 @@ class _CriterionFn(torch.autograd.Function):
             # own side stream (the future half of CPCModel.forwardPastFuture) may start from this event
             ops._READY.clear()
             ops.set_ready(dz, ops.mark())
-        for part in range(2):
-            K.gemm(K.kmajor(dlog[part]), K.mnmajor(zb, gmul=0), T, D, BS, groups=Kp, out_f32=dpred, alpha=1.0 / D,
-                   accumulate=part > 0, algo_flops=ctx.algo / 2)
+        # one launch over both parts: the reduction runs over [hi | lo] (two slabs of BS, Kp planes apart in dlog)
+        # against the same z (slab step 0) -- one prologue / epilogue on the dependent chain instead of two
+        K.gemm(K.View(dlog, BS, T, 2 * Kp, BS, T * BS, major=0, gmul=1, smul=Kp), K.View(zb, D, BS, 1, D, major=1, smul=0),
+               T, D, 2 * BS, groups=Kp, k_per_slab=BS, out_f32=dpred, alpha=1.0 / D, algo_flops=ctx.algo)
         if ctx.pred_drop is not None:
             K.dropout_(dpred, ctx.pred_drop[0], 7, ctx.pred_drop[1])
         if type(eng) is TransformerStack and ops.early_ffn():

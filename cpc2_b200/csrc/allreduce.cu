@@ -8,17 +8,21 @@
 //   barrier (every slice has landed everywhere)
 //
 // Per GPU the NVLink traffic is n*4*(world-1)/world bytes out and in (a ring all-reduce moves twice that, in
-// 2(world-1) latency-bound hops), and the kernel needs no shared memory and few registers, so its CTAs co-reside with
-// the persistent GEMM CTAs of the backward it overlaps instead of taking whole SMs away from them.
+// 2(world-1) latency-bound hops).  The kernel overlaps the backward, whose persistent tcgen05 GEMM CTAs hold one SM each
+// with 320 threads x up to 168 registers = 53.8 K of the SM's 64 K registers: a reduction CTA co-resides with them only
+// if it fits the remaining 11.7 K registers (and uses no shared memory).  The first form of this kernel ran 48 CTAs of
+// 512 threads x 64 registers = 32 K registers each, which EVICTED the GEMM from 48 of the 148 SMs for the 150 us of the
+// heads' bucket -- every full-grid GEMM of the backward then needed a second round (N = 2: +150 us per step).  Now:
+// 128 threads x 64 registers = 8 K registers per CTA, up to 144 CTAs (the same ~2.4 MB of switch round trips in flight).
 // CUDA-graph safe: the signal slots are consumed (1 -> 0) by the waiter, nothing counts epochs.
+#include <cstdlib>
+
 #include "cpc_internal.h"
 #include "ptx.cuh"
 
 namespace cpc {
 
-constexpr int AR_THREADS = 512;
 constexpr int AR_MAX_BLOCKS = 144;
-constexpr int AR_DEFAULT_BLOCKS = 48;
 constexpr int AR_UNROLL = 8;  // independent switch round trips in flight per thread
 constexpr int AR_PAD_FIRST = 512;   // first u32 slot of the signal pad we use (the slots below are left to the host library)
 
@@ -47,6 +51,7 @@ __device__ __forceinline__ void block_barrier(uint32_t* const* pads, int rank, i
   __syncthreads();
 }
 
+template <int AR_THREADS>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_mc_kernel(float* __restrict__ mc, long long n4,
                                                                   uint32_t* const* __restrict__ pads, int rank, int world,
                                                                   float scale) {
@@ -97,15 +102,21 @@ extern "C" int cpc_allreduce_mc(void* mc_ptr, int64_t n, void* const* signal_pad
     return CPC_ERR_ARG;
   const long long n4 = n / 4;
   const long long per = (n4 + world - 1) / world;
-  long long blocks = (per + AR_THREADS * AR_UNROLL - 1) / (AR_THREADS * AR_UNROLL);
-  // 48 CTAs x 512 threads x 8 x 16 B = 3 MB in flight saturate the switch (measured at 8 GPUs: 66 MB in 191 us with 48
-  // CTAs, 215 us with 144) and leave 100 SMs untouched for the backward kernels the reduction overlaps
-  const int cap = max_blocks > 0 ? (max_blocks < AR_MAX_BLOCKS ? max_blocks : AR_MAX_BLOCKS) : AR_DEFAULT_BLOCKS;
+  // CPC_AR_THREADS=512 restores the first form (48 CTAs x 512 threads: 3 MB in flight saturate the switch -- measured at
+  // 8 GPUs, kernel alone: 66 MB in 191 us with 48 such CTAs, 215 us with 144 -- but see the register note above)
+  static const int threads = [] {
+    const char* e = getenv("CPC_AR_THREADS");
+    return e != nullptr && atoi(e) == 512 ? 512 : 128;
+  }();
+  long long blocks = (per + threads * AR_UNROLL - 1) / (threads * AR_UNROLL);
+  const int dflt = threads == 512 ? 48 : AR_MAX_BLOCKS;
+  const int cap = max_blocks > 0 ? (max_blocks < AR_MAX_BLOCKS ? max_blocks : AR_MAX_BLOCKS) : dflt;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  launch_k(allreduce_mc_kernel, dim3((unsigned)blocks), dim3(AR_THREADS), 0, stream, static_cast<float*>(mc_ptr), n4,
-                                                                 reinterpret_cast<uint32_t* const*>(signal_pads_dev), rank,
-                                                                 world, scale);
+  float* mc = static_cast<float*>(mc_ptr);
+  uint32_t* const* pads = reinterpret_cast<uint32_t* const*>(signal_pads_dev);
+  if (threads == 512) launch_k(allreduce_mc_kernel<512>, dim3((unsigned)blocks), dim3(512), 0, stream, mc, n4, pads, rank, world, scale);
+  else launch_k(allreduce_mc_kernel<128>, dim3((unsigned)blocks), dim3(128), 0, stream, mc, n4, pads, rank, world, scale);
   return launch_status();
 }
 

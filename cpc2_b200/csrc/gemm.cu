@@ -40,8 +40,8 @@ struct GemmKernelArgs {
   int total_kblocks;  // slabs * kblocks_per_slab
   int k_splits;
   int tiles_m, tiles_n, total_tiles;
-  int a_row_off, a_gmul;
-  int b_row_off, b_gmul;
+  int a_row_off, a_gmul, a_smul;
+  int b_row_off, b_gmul, b_smul;  // outer coordinate = grp * gmul + slab * smul
   float alpha;
   float* out_f32;
   long long ldd_f32, gs_f32;
@@ -208,17 +208,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
               tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[s], tc.m0 + j * 64, kk + p.a_row_off,
-                          tc.grp * p.a_gmul + slab);
+                          tc.grp * p.a_gmul + slab * p.a_smul);
           } else {
-            tma_load_3d(sa, &tmA, &full_bar[s], kk, tc.m0 + p.a_row_off, tc.grp * p.a_gmul + slab);
+            tma_load_3d(sa, &tmA, &full_bar[s], kk, tc.m0 + p.a_row_off, tc.grp * p.a_gmul + slab * p.a_smul);
           }
           if (B_MN) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
               tma_load_3d(sb + j * (BK * 128), &tmB, &full_bar[s], tc.n0 + j * 64, kk + p.b_row_off,
-                          tc.grp * p.b_gmul + slab);
+                          tc.grp * p.b_gmul + slab * p.b_smul);
           } else {
-            tma_load_3d(sb, &tmB, &full_bar[s], kk, tc.n0 + p.b_row_off, tc.grp * p.b_gmul + slab);
+            tma_load_3d(sb, &tmB, &full_bar[s], kk, tc.n0 + p.b_row_off, tc.grp * p.b_gmul + slab * p.b_smul);
           }
           if (it == 0) GEMM_TSTAMP(2);
         }
@@ -445,6 +445,8 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
   ka.k_splits = k_splits;
   ka.a_row_off = d->a_row_off; ka.a_gmul = d->a_gmul;
   ka.b_row_off = d->b_row_off; ka.b_gmul = d->b_gmul;
+  ka.a_smul = d->a_slab_mul == 0 ? 1 : (d->a_slab_mul < 0 ? 0 : d->a_slab_mul);
+  ka.b_smul = d->b_slab_mul == 0 ? 1 : (d->b_slab_mul < 0 ? 0 : d->b_slab_mul);
   ka.alpha = d->alpha;
   ka.out_f32 = static_cast<float*>(d->out_f32); ka.ldd_f32 = d->ldd_f32; ka.gs_f32 = d->gs_f32;
   ka.out_bf16 = static_cast<__nv_bfloat16*>(d->out_bf16); ka.ldd_bf16 = d->ldd_bf16; ka.gs_bf16 = d->gs_bf16;

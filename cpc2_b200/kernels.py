@@ -42,9 +42,12 @@ def _run(name, args):
 class View:
     """3-D operand view (dim0 contiguous) over a bf16 CUDA tensor, in elements.
     major 0: K-major (dim0 = reduction index); major 1: MN-major (dim0 = m / n index)."""
-    __slots__ = ("t", "major", "dim0", "dim1", "dim2", "stride1", "stride2", "row_off", "gmul", "offset")
+    __slots__ = ("t", "major", "dim0", "dim1", "dim2", "stride1", "stride2", "row_off", "gmul", "offset", "smul")
 
-    def __init__(self, t, dim0, dim1, dim2=1, stride1=None, stride2=None, major=0, row_off=0, gmul=0, offset=0):
+    def __init__(self, t, dim0, dim1, dim2=1, stride1=None, stride2=None, major=0, row_off=0, gmul=0, offset=0, smul=1):
+        """smul: step of the dim2 coordinate per reduction slab (1 = consecutive planes, 0 = the same plane for every
+        slab)."""
+        self.smul = int(smul)
         assert t.dtype == BF16 and t.is_cuda
         self.t, self.major = t, major
         self.dim0, self.dim1, self.dim2 = int(dim0), int(dim1), int(dim2)
@@ -93,10 +96,10 @@ def gemm(A, B, M, N, K, groups=1, k_per_slab=0, k_splits=1, alpha=1.0, out_f32=N
     d.M, d.N, d.K, d.groups, d.k_per_slab, d.k_splits, d.force_bn = M, N, K, groups, k_per_slab, k_splits, force_bn
     d.a, d.a_major = A.addr(), A.major
     d.a_dim0, d.a_dim1, d.a_dim2, d.a_stride1, d.a_stride2 = A.dim0, A.dim1, A.dim2, A.stride1, A.stride2
-    d.a_row_off, d.a_gmul = A.row_off, A.gmul
+    d.a_row_off, d.a_gmul, d.a_slab_mul = A.row_off, A.gmul, (-1 if A.smul == 0 else A.smul)
     d.b, d.b_major = B.addr(), B.major
     d.b_dim0, d.b_dim1, d.b_dim2, d.b_stride1, d.b_stride2 = B.dim0, B.dim1, B.dim2, B.stride1, B.stride2
-    d.b_row_off, d.b_gmul = B.row_off, B.gmul
+    d.b_row_off, d.b_gmul, d.b_slab_mul = B.row_off, B.gmul, (-1 if B.smul == 0 else B.smul)
     d.alpha = alpha
     t, ld, gs = _out(out_f32)
     if t is not None:

@@ -102,6 +102,8 @@ def grad_arena(owner, numel, device, zero_on=None):
 # the join (the launchers only borrow pointers), so the caching allocator never sees cross-stream reuse.
 CONCURRENT = True
 _SIDE = {}
+# priority of the stream GraphedTrainStep captures on (-1 = above the side streams, 0 = same; CPC_MAIN_PRIORITY)
+MAIN_PRIORITY = int(os.environ.get("CPC_MAIN_PRIORITY", "-1"))
 # announce the heads' feed-forward gradients (3/4 of all parameters) a third of the way into their backward:
 # "auto" = when gradients are all-reduced (world > 1; +1 % at N = 8, neutral at N = 1), "1" / "0" force it
 EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")

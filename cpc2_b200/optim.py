@@ -7,11 +7,17 @@ one multi-tensor sm_100a launch (cpc_adam_step) updates every parameter of the m
 torch.optim.Adam (train.py:486-490).  The step counter, learning rate and bias corrections live in device memory:
 a `step()` captured in a CUDA graph replays correctly (`sync_hyper()` pushes a changed lr before the replay).
 """
+import os
+
 import torch
 
 from . import _lib
 from . import kernels as K
 from . import ops
+
+# update an early-announced bucket only when the next bucket is announced (see FusedAdam._on_stage); CPC_ADAM_DEFER=0
+# restores update-right-behind-the-reduction
+DEFER_EARLY_UPDATE = os.environ.get("CPC_ADAM_DEFER", "1") != "0"
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -24,6 +30,7 @@ class FusedAdam(torch.optim.Optimizer):
         self._groups = [None] * len(self.param_groups)  # per group: device state, span tables, flat moments
         self._dp, self._done, self._advanced = None, set(), False
         self._shadowed = []  # arenas whose bf16 shadow the launches of this iteration wrote
+        self._deferred = []  # (stage, pairs, event) of early buckets whose update waits for the next announcement
 
     # ------------------------------------------------------------------------------------------ internals
     def _init_group(self, gi):
@@ -141,14 +148,36 @@ class FusedAdam(torch.optim.Optimizer):
             # 16.6 M-parameter update of the heads and the last (encoder) reduction would trail the backward
             after = torch.cuda.Event()
             after.record(dp.stream)
+        self._done.update(id(p) for p, _ in pairs)
+        if after is not None and DEFER_EARLY_UPDATE and stage.endswith(".ffn"):
+            # The early bucket (the heads' feed-forward weights, 12.6 M parameters, announced a third of the way into
+            # the heads' backward so that its all-reduce starts early) is REDUCED now but UPDATED later: its 380 MB
+            # Adam pass next to the heads' remaining bandwidth-bound backward kernels slows the dependent chain, while
+            # the recurrent backward that follows leaves HBM idle.  Launched by the next announcement (the end of the
+            # heads' backward) or by step().
+            self._deferred.append((stage, pairs, after))
+            return
+        self._flush_deferred()
+        self._launch(g, stage, pairs, after)
+
+    def _flush_deferred(self):
+        if not self._deferred:
+            return
+        here = ops.mark()  # not before this point of the announcing stream
+        for stage, pairs, after in self._deferred:
+            self._launch(self._groups[0], stage, pairs, after, also=here)
+        self._deferred = []
+
+    def _launch(self, g, stage, pairs, after, also=None):
         with ops.side(9, after=after):
             if after is not None:
                 torch.cuda.current_stream().wait_event(after)  # (also when side streams are disabled)
+            if also is not None:
+                torch.cuda.current_stream().wait_event(also)
             t = self._table(g, stage, pairs)
             K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
             self._shadowed.extend(t["arenas"])
         self._advanced = True
-        self._done.update(id(p) for p, _ in pairs)
 
     # ------------------------------------------------------------------------------------------ snapshot / restore
     def snapshot(self):
@@ -195,6 +224,7 @@ class FusedAdam(torch.optim.Optimizer):
             if self._groups[gi] is None:
                 self._init_group(gi)
         capturing = torch.cuda.is_current_stream_capturing()
+        self._flush_deferred()
         ops.join(9)  # staged launches of this iteration (FusedAdam.attach); dp.finish() has joined dp.stream
         for gi in range(len(self.param_groups)):
             g = self._groups[gi]

@@ -296,7 +296,11 @@ class GraphedTrainStep:
         del snap_p, snap_o
         self.graph = torch.cuda.CUDAGraph()
         self._zero()
-        with torch.cuda.graph(self.graph):
+        # the capture stream carries the dependent chain of the step; with ops.MAIN_PRIORITY < 0 its kernels are
+        # scheduled ahead of the forked branches (weight gradients, bias sums, all-reduce, Adam: ops.side streams have
+        # priority 0), which otherwise take SMs from the next link of the chain whenever both are ready
+        cap = torch.cuda.Stream(device=dev, priority=ops.MAIN_PRIORITY) if ops.MAIN_PRIORITY < 0 else None
+        with torch.cuda.graph(self.graph, **({"stream": cap} if cap is not None else {})):
             self.losses, self.acc = forwardBackward(cpcModel, cpcCriterion, self.static_seq, self.static_label)
             if after_backward is not None:
                 after_backward()

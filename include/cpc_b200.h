@@ -53,8 +53,8 @@ int cpc_set_pdl(int on);
  *   major = 0 (K-major):  dim0 = reduction index k, dim1 = m (or n) row,   dim2 = group / slab
  *   major = 1 (MN-major): dim0 = m (or n),          dim1 = reduction row,  dim2 = group / slab
  * The reduction index is k = slab*k_per_slab + kk; coordinates used for tile (m0|n0, kk, slab, group g):
- *   K-major : (kk,      m0 + row_off, g*gmul + slab)
- *   MN-major: (m0,      kk + row_off, g*gmul + slab)
+ *   K-major : (kk,      m0 + row_off, g*gmul + slab*slab_mul)
+ *   MN-major: (m0,      kk + row_off, g*gmul + slab*slab_mul)        (slab_mul: see the end of the struct; default 1)
  * Out-of-range coordinates read as zero (TMA fill), so M, N, k_per_slab need not be tile multiples.
  * Rows may overlap (stride1 < dim0): that is how the im2col matrix of a strided conv is expressed.
  */
@@ -95,6 +95,10 @@ typedef struct {
   void* norm_f32;  int64_t ld_norm_f32,  gs_norm_f32;
   void* norm_mean; void* norm_rstd; int64_t gs_norm_stat;
   float norm_eps; int norm_unbiased; int norm_halo;
+  /* Outer-coordinate step per slab: coordinate = g*gmul + slab*slab_mul.  0 selects the default 1 (consecutive slabs),
+   * -1 a step of zero (the operand is read again for every slab: a reduction over [hi | lo] parts of A against ONE B),
+   * any other value is the step itself (slabs that are `groups` planes apart: A laid out [part][group][m][k]). */
+  int a_slab_mul, b_slab_mul;
 } CpcGemmDesc;
 
 int cpc_gemm_bf16(const CpcGemmDesc* desc, void* stream);
