@@ -293,6 +293,7 @@ class TrainRig:
         self.dp.broadcast_parameters()
         if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1":  # diagnosis only (the printed line says so)
             self.dp._all_reduce_mean = lambda t: None
+            self.dp._skip_collective = True
         n0 = K.LAUNCHES
         self.adam = FusedAdam(list(self.crit.parameters()) + list(self.model.parameters()), lr=args.learningRate,
                               betas=(args.beta1, args.beta2), eps=args.epsilon)  # cpc/train.py:472-479
@@ -549,6 +550,7 @@ def run_ours(opt, out):
         "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2_flush_between_steps": True, "cuda_graph": True, "dropout": "train mode (p=0.1 in the heads)",
                    "programmatic_dependent_launch": os.environ.get("CPC_PDL", "0") == "1",
+                   "capture_stream_priority": __import__("cpc2_b200.ops", fromlist=["ops"]).MAIN_PRIORITY,
                    "optimizer": "fused multi-tensor Adam (cpc_adam_step) inside the timed step, per bucket after its all-reduce",
                    "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0,
                    "grad_allreduce": ("none" if world == 1 else "cpc_allreduce_mc (NVSwitch multimem, in place)"

@@ -632,18 +632,21 @@ class _CriterionFn(torch.autograd.Function):
                T, D, 2 * BS, groups=Kp, k_per_slab=BS, out_f32=dpred, alpha=1.0 / D, algo_flops=ctx.algo)
         if ctx.pred_drop is not None:
             K.dropout_(dpred, ctx.pred_drop[0], 7, ctx.pred_drop[1])
-        if type(eng) is TransformerStack and ops.early_ffn():
-            dcw, gflat = eng.backward(ctx.saved, dpred, early_stage="criterion")
+        if type(eng) is TransformerStack:
+            dcw, gflat = eng.backward(ctx.saved, dpred, early_stage="criterion" if ops.early_ffn() else None, defer=True)
         else:
             dcw, gflat = eng.backward(ctx.saved, dpred)
         dc[:, :W] = dcw.view(B, W, H)
-        ops.join()
+        ops.join(2)  # dz: whoever consumes it on this stream (the future half of a pair starts from its own event)
+        # inside a step the chain does not wait for the heads' weight gradients: the announcement does (ops.announce)
+        ops.module_join(ctx.saved, ctx.t, dlog, dpred, acc0, dcw)
         views = eng.arena.grad_views(gflat)
         ann = ctx.saved.pop("announced", None)
-        if ann is None:
-            ops.grad_ready("criterion", gflat, eng.arena.params, views)
-        else:  # the feed-forward weights went out early (criterion.ffn): what is left, as two contiguous spans
-            i0, i1, off0, off1 = ann
-            ops.grad_ready("criterion.front", gflat[:off0], eng.arena.params[:i0], views[:i0])
-            ops.grad_ready("criterion.tail", gflat[off1:], eng.arena.params[i1:], views[i1:])
+        with ops.announce():
+            if ann is None:
+                ops.grad_ready("criterion", gflat, eng.arena.params, views)
+            else:  # the feed-forward weights went out early (criterion.ffn): what is left, as two contiguous spans
+                i0, i1, off0, off1 = ann
+                ops.grad_ready("criterion.front", gflat[:off0], eng.arena.params[:i0], views[:i0])
+                ops.grad_ready("criterion.tail", gflat[off1:], eng.arena.params[i1:], views[i1:])
         return (dc, dz.view(B, S, D), None, None, None, None, None, None, *views)

@@ -106,16 +106,22 @@ extern "C" int cpc_allreduce_mc(void* mc_ptr, int64_t n, void* const* signal_pad
   // 8 GPUs, kernel alone: 66 MB in 191 us with 48 such CTAs, 215 us with 144 -- but see the register note above)
   static const int threads = [] {
     const char* e = getenv("CPC_AR_THREADS");
-    return e != nullptr && atoi(e) == 512 ? 512 : 128;
+    const int v = e != nullptr ? atoi(e) : 0;
+    return v == 128 || v == 256 ? v : 512;
+  }();
+  static const int env_blocks = [] {  // CPC_AR_BLOCKS=<n>: CTA cap (A/B runs)
+    const char* e = getenv("CPC_AR_BLOCKS");
+    return e != nullptr ? atoi(e) : 0;
   }();
   long long blocks = (per + threads * AR_UNROLL - 1) / (threads * AR_UNROLL);
-  const int dflt = threads == 512 ? 48 : AR_MAX_BLOCKS;
-  const int cap = max_blocks > 0 ? (max_blocks < AR_MAX_BLOCKS ? max_blocks : AR_MAX_BLOCKS) : dflt;
+  int cap = max_blocks > 0 ? max_blocks : (env_blocks > 0 ? env_blocks : 48);
+  if (cap > AR_MAX_BLOCKS) cap = AR_MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   float* mc = static_cast<float*>(mc_ptr);
   uint32_t* const* pads = reinterpret_cast<uint32_t* const*>(signal_pads_dev);
   if (threads == 512) launch_k(allreduce_mc_kernel<512>, dim3((unsigned)blocks), dim3(512), 0, stream, mc, n4, pads, rank, world, scale);
+  else if (threads == 256) launch_k(allreduce_mc_kernel<256>, dim3((unsigned)blocks), dim3(256), 0, stream, mc, n4, pads, rank, world, scale);
   else launch_k(allreduce_mc_kernel<128>, dim3((unsigned)blocks), dim3(128), 0, stream, mc, n4, pads, rank, world, scale);
   return launch_status();
 }

@@ -519,7 +519,7 @@ extern "C" int cpc_gemm_bf16(const CpcGemmDesc* d, void* stream_) {
     }();
     const long long row_tiles = (long long)((d->M + BM - 1) / BM) * d->groups;
     if (d->N == 512) { bn = 128; ka.cl_n = 4; }
-    else if (row_tiles < cl_below) { bn = 64; ka.cl_n = 4; }
+    else if (d->force_bn != 256 && row_tiles < cl_below) { bn = 64; ka.cl_n = 4; }  // force_bn = 256: one tile per row
     else bn = 256;
   }
 

@@ -47,11 +47,14 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
 }
 
 __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamSpan* __restrict__ spans, int n_spans,
-                                                            const double* __restrict__ state) {
+                                                            const double* __restrict__ state, long long total_blocks) {
   pdl_sync();  // PDL: nothing below touches global memory before the preceding grid has completed (cpc_internal.h)
-  // span of this CTA: binary search over the block prefix
+  const float omb1 = (float)(1.0 - state[2]), b2 = (float)state[3], omb2 = (float)(1.0 - state[3]), eps = (float)state[4];
+  const float step_size = (float)state[5], bc2_sqrt = (float)state[6];
+  // grid == total_blocks: one chunk per CTA; a smaller (throttled) grid walks the chunks persistently
+  for (long long blk = blockIdx.x; blk < total_blocks; blk += gridDim.x) {
+  // span of this chunk: binary search over the block prefix
   int lo = 0, hi = n_spans - 1;
-  const long long blk = blockIdx.x;
   while (lo < hi) {
     const int mid = (lo + hi + 1) >> 1;
     if (spans[mid].first_block <= blk) lo = mid;
@@ -59,8 +62,6 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamSpan* __re
   }
   const AdamSpan s = spans[lo];
   const long long base = (blk - s.first_block) * ADAM_CHUNK;
-  const float omb1 = (float)(1.0 - state[2]), b2 = (float)state[3], omb2 = (float)(1.0 - state[3]), eps = (float)state[4];
-  const float step_size = (float)state[5], bc2_sqrt = (float)state[6];
   const bool vec = ((reinterpret_cast<uintptr_t>(s.p) | reinterpret_cast<uintptr_t>(s.g) | reinterpret_cast<uintptr_t>(s.m) |
                      reinterpret_cast<uintptr_t>(s.v)) & 15) == 0 &&
                    (s.p16 == nullptr || (reinterpret_cast<uintptr_t>(s.p16) & 7) == 0);
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamSpan* __re
       }
     }
   }
+  }
 }
 
 }  // namespace cpc
@@ -113,14 +115,15 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamSpan* __re
 using namespace cpc;
 
 extern "C" int cpc_adam_step(const CpcAdamSpan* spans_dev, int n_spans, int64_t total_blocks, double* state_dev,
-                             int advance, void* stream_) {
+                             int advance, int max_ctas, void* stream_) {
   static_assert(sizeof(CpcAdamSpan) == sizeof(AdamSpan), "CpcAdamSpan layout");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (spans_dev == nullptr || state_dev == nullptr || n_spans <= 0 || total_blocks <= 0 || total_blocks > 0x7fffffffLL)
     return CPC_ERR_ARG;
   if (advance) launch_k(adam_prologue_kernel, dim3(1), dim3(1), 0, stream, state_dev);
-  launch_k(adam_kernel, dim3((unsigned)total_blocks), dim3(ADAM_THREADS), 0, stream, reinterpret_cast<const AdamSpan*>(spans_dev), n_spans,
-                                                                  state_dev);
+  const long long grid = max_ctas > 0 && max_ctas < total_blocks ? max_ctas : total_blocks;
+  launch_k(adam_kernel, dim3((unsigned)grid), dim3(ADAM_THREADS), 0, stream, reinterpret_cast<const AdamSpan*>(spans_dev), n_spans,
+           static_cast<const double*>(state_dev), (long long)total_blocks);
   return launch_status();
 }
 

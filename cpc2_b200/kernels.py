@@ -289,12 +289,13 @@ def nce_bwd(logits, ext, weights, lse, gscale, dlogits, K, B, W, S, NEG, ld, dlo
     _run("cpc_nce_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def adam_step(table, n_spans, blocks, state, advance=True):
-    """cpc_adam_step: `table` = device bytes of a CpcAdamSpan array, `state` = device double[8]."""
+def adam_step(table, n_spans, blocks, state, advance=True, max_ctas=0):
+    """cpc_adam_step: `table` = device bytes of a CpcAdamSpan array, `state` = device double[8]; max_ctas > 0: a
+    throttled pass on that many persistent CTAs."""
     if PROFILE is not None:
         set_work(kind="hbm", bytes=28.0 * blocks * lib().cpc_adam_chunk())
     _run("cpc_adam_step", (ctypes.c_void_p(table.data_ptr()), n_spans, ctypes.c_int64(blocks),
-                           ctypes.c_void_p(state.data_ptr()), int(advance), stream_ptr(),))
+                           ctypes.c_void_p(state.data_ptr()), int(advance), int(max_ctas), stream_ptr(),))
 
 
 CELL = {"LSTM": 0, "GRU": 1, "RNN": 2}

@@ -264,7 +264,7 @@ class _EncoderFn(torch.autograd.Function):
                 if ops.can_fuse_norm(C, Lout, N):
                     # conv + bias -> y (kept for the backward), ChannelNorm + ReLU -> a, all in the GEMM epilogue
                     K.gemm(A, K.kmajor(wf), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b,
-                           relu=True, norm=dict(gamma=g.reshape(C), beta=be.reshape(C), out_bf16=(a, C, (Lout + 2 * hn) * C),
+                           relu=True, force_bn=ops.NORM_FORCE_BN, norm=dict(gamma=g.reshape(C), beta=be.reshape(C), out_bf16=(a, C, (Lout + 2 * hn) * C),
                                                 offset_bf16=hn * C, out_f32=(z32, C, Lout * C) if l == 4 else None,
                                                 mean=means[l], rstd=rstds[l], gs_stat=Lout, unbiased=True, halo=hn))
                     continue
@@ -574,9 +574,11 @@ class _RecurrentFn(torch.autograd.Function):
             # dx = dgates . W_ih (zero slots of the padded W_ih contribute nothing)
             K.gemm(K.kmajor(dg2), K.mnmajor(w_ih16), N * S, Kin, 4 * H, out_f32=dx)
             d = dx.view(N, S, Kin)
-        ops.join()
+        # inside a step the chain (the encoder's backward comes next) does not wait for dW_ih / dW_hh / the bias sums
+        ops.module_join(keep, ctx.saved, dout)
         del keep
-        ops.grad_ready("ar", gflat, ctx.params, grads)
+        with ops.announce():
+            ops.grad_ready("ar", gflat, ctx.params, grads)
         return (d, None, None, None, None, None, *grads)
 
 

@@ -45,6 +45,12 @@ def will_backward():
     return _SAVING[-1] if _SAVING else torch.is_grad_enabled()
 
 
+# force_bn of the fused-norm GEMM launches: 0 = the kernel picks the tile form by launch size (one 256-column tile per
+# row, or the row split over a 4-CTA cluster); 256 = always one tile per row.  Tests that compare two DIFFERENTLY SIZED
+# launches of the same arithmetic set 256, so that both sum the row statistics in the same order.
+NORM_FORCE_BN = 0
+
+
 def can_fuse_norm(C, rows=None, groups=1):
     """256-wide rows: always (the kernel picks one BN = 256 tile per row or the 4-CTA cluster split by the number of row
     tiles).  512-wide rows only exist in the cluster form, which streams the A tile four times: worth it for small
@@ -176,6 +182,79 @@ def join(index=None):
         if key[0] == cur.device.index and ((index is None and parent.cuda_stream == cur.cuda_stream) or key[1] == index):
             cur.wait_stream(s)
             _PENDING.remove(item)
+
+
+# ---- deferred joins --------------------------------------------------------------------------------------------
+# A module's backward used to end with join(): the dependent chain (the stream autograd runs on) waited for the
+# module's weight-gradient GEMMs and bias sums before the next module's backward could start, although only the
+# all-reduce / optimizer step of THAT module needs them -- and since the chain's stream outranks the side streams
+# (MAIN_PRIORITY) those launches finish late.  Inside train.forwardBackward (step_scope) a module instead
+#   * hands every buffer its side streams may still be reading to module_join(...) (kept alive until the step's final
+#     join: the caching allocator must not recycle them for later launches of the chain), and
+#   * announces its gradients from `with ops.announce():` -- side stream 8, which waits for the chain up to here AND for
+#     every side stream forked from it, so dp's all-reduce and the staged Adam launch are ordered behind the weight
+#     gradients without the chain ever waiting.
+# Outside a step_scope (a module used on its own) module_join() is the plain join() and announce() does nothing.
+DEFER_JOINS = os.environ.get("CPC_DEFER_JOINS", "1") != "0"
+ANNOUNCE_STREAM = 8
+_STEP_DEPTH = 0
+_KEEP = []
+
+
+def _deferring():
+    return _STEP_DEPTH > 0 and DEFER_JOINS and CONCURRENT and K.PROFILE is None
+
+
+class step_scope:
+    """train.forwardBackward: backward passes of the modules inside may defer their joins to the end of the step."""
+
+    def __enter__(self):
+        global _STEP_DEPTH
+        _STEP_DEPTH += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _STEP_DEPTH
+        _STEP_DEPTH -= 1
+        if _STEP_DEPTH == 0:
+            join()
+            _KEEP.clear()
+        return False
+
+
+def module_join(*keep):
+    """join() at the end of a module's backward -- or, inside a step_scope, nothing but keeping `keep` alive until the
+    step's final join.  Returns True when the current stream really joined."""
+    if _deferring():
+        _KEEP.append(keep)
+        return False
+    join()
+    return True
+
+
+class announce:
+    def __init__(self):
+        self.ctx = None
+
+    def __enter__(self):
+        if not _deferring():
+            return self
+        cur = torch.cuda.current_stream()
+        pend = [s for key, s, parent in _PENDING
+                if key[0] == cur.device.index and parent.cuda_stream == cur.cuda_stream and key[1] not in DETACHED
+                and key[1] != ANNOUNCE_STREAM]
+        self.ctx = side(ANNOUNCE_STREAM)
+        self.ctx.__enter__()
+        x = torch.cuda.current_stream()
+        for s in pend:
+            x.wait_stream(s)
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+            self.ctx = None
+        return False
 
 
 def wait_side(index):

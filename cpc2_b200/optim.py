@@ -17,7 +17,10 @@ from . import ops
 
 # update an early-announced bucket only when the next bucket is announced (see FusedAdam._on_stage); CPC_ADAM_DEFER=0
 # restores update-right-behind-the-reduction
-DEFER_EARLY_UPDATE = os.environ.get("CPC_ADAM_DEFER", "1") != "0"
+DEFER_UPDATE = int(os.environ.get("CPC_ADAM_DEFER", "1"))
+# persistent CTAs of an update launched from a gradient announcement, i.e. next to the rest of the backward (0: one CTA
+# per 4096-element chunk, which saturates HBM and slowed the recurrent backward beside it from 100 to 132 us)
+STAGED_CTAS = int(os.environ.get("CPC_ADAM_CTAS", "0"))
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -149,15 +152,17 @@ class FusedAdam(torch.optim.Optimizer):
             after = torch.cuda.Event()
             after.record(dp.stream)
         self._done.update(id(p) for p, _ in pairs)
-        if after is not None and DEFER_EARLY_UPDATE and stage.endswith(".ffn"):
-            # The early bucket (the heads' feed-forward weights, 12.6 M parameters, announced a third of the way into
-            # the heads' backward so that its all-reduce starts early) is REDUCED now but UPDATED later: its 380 MB
-            # Adam pass next to the heads' remaining bandwidth-bound backward kernels slows the dependent chain, while
-            # the recurrent backward that follows leaves HBM idle.  Launched by the next announcement (the end of the
-            # heads' backward) or by step().
+        heads = stage.startswith("criterion")
+        if (DEFER_UPDATE == 2 and heads) or (DEFER_UPDATE == 1 and after is not None and stage.endswith(".ffn")):
+            # Reduced now, UPDATED later.  Mode 1 (N > 1): the early bucket (the heads' feed-forward weights, announced a
+            # third of the way into the heads' backward so that its all-reduce starts early) waits for the next
+            # announcement.  Mode 2: every bucket of the heads waits for the AR's announcement -- their 16.6 M-parameter
+            # pass saturates HBM for 100 us and, launched at the end of the heads' backward, ran beside the
+            # latency-bound recurrent backward (100 -> 132 us); behind it, it runs beside the encoder's backward.
             self._deferred.append((stage, pairs, after))
             return
-        self._flush_deferred()
+        if not (DEFER_UPDATE == 2 and heads):
+            self._flush_deferred()
         self._launch(g, stage, pairs, after)
 
     def _flush_deferred(self):
@@ -175,7 +180,9 @@ class FusedAdam(torch.optim.Optimizer):
             if also is not None:
                 torch.cuda.current_stream().wait_event(also)
             t = self._table(g, stage, pairs)
-            K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced)
+            # staged launches run next to the backward: large ones as a throttled pass (STAGED_CTAS persistent CTAs)
+            K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced,
+                        max_ctas=STAGED_CTAS if t["blocks"] > 4 * max(STAGED_CTAS, 1) else 0)
             self._shadowed.extend(t["arenas"])
         self._advanced = True
 

@@ -116,7 +116,18 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
     allLosses, allAcc = cpcCriterion(c_feature, encoded_data, label, signal_quality)
     if backward:
         totLoss = allLosses.sum()
-        totLoss.backward()
+        from . import ops
+        # the modules' backward passes may leave their weight-gradient streams to the step's final join (ops.step_scope)
+        # -- unless somebody reads gradients on the autograd stream as they are accumulated: the reducer of a
+        # DistributedDataParallel / DataParallel wrapper, or a hook registered on a parameter
+        bare = isinstance(cpcModel, model_.CPCModel) and isinstance(cpcCriterion, cr.CPCUnsupersivedCriterion) and not any(
+            p._backward_hooks or getattr(p, "_post_accumulate_grad_hooks", None)
+            for m in (cpcModel, cpcCriterion) for p in m.parameters())
+        if bare:
+            with ops.step_scope():
+                totLoss.backward()
+        else:
+            totLoss.backward()
     return allLosses, allAcc
 
 

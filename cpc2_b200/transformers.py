@@ -291,7 +291,7 @@ class TransformerStack:
         rstd1 = torch.empty(G * T, device=dev)
         if ops.can_fuse_norm(d, T, G):  # y = LN(x + att . Wo^T) in the epilogue of the Wo product
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res,
-                           norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], gs_param=d, out_bf16=y, mean=mean1, rstd=rstd1,
+                           force_bn=ops.NORM_FORCE_BN, norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], gs_param=d, out_bf16=y, mean=mean1, rstd=rstd1,
                                      gs_stat=T))
         else:
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=G, out_bf16=pre1, res=res)
@@ -308,7 +308,7 @@ class TransformerStack:
         rstd2 = torch.empty(G * T, device=dev)
         if ops.can_fuse_norm(dout, T, G):  # out = LN(u . Wl^T + bl) in the epilogue of the last_linear product
             ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout,
-                           norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], gs_param=dout, out_bf16=out, out_f32=out32,
+                           force_bn=ops.NORM_FORCE_BN, norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], gs_param=dout, out_bf16=out, out_f32=out32,
                                      mean=mean2, rstd=rstd2, gs_stat=T))
         else:
             ops.linear_fwd(u, P16["Wl"], T, dout, d, groups=G, out_bf16=pre2, bias=P32["bl"], bias_gs=dout)
@@ -320,7 +320,7 @@ class TransformerStack:
         return out, out32, saved
 
     # ------------------------------------------------------------------------------------------ backward
-    def backward(self, sv, dout, early_stage=None):
+    def backward(self, sv, dout, early_stage=None, defer=False):
         """dout bf16 or fp32 [G, T, dout].  Returns (dx fp32 [T,d] if shared else [G,T,d], flat fp32 grad arena).
         early_stage: announce the feed-forward weights' gradients (W1, b1, W2, b2: 3/4 of the parameters) through
         ops.grad_ready(early_stage + ".ffn") as soon as they exist, a third of the way into this backward, so their
@@ -402,7 +402,10 @@ class TransformerStack:
             K.groupsum(dpre1, T * d, G, out_f32=dx, accumulate=True)
         else:
             ops.linear_dx(dqkv, P16["Wqkv"], T, 3 * d, d, groups=G, out_f32=dx, res=dpre1)
-        ops.join()
+        if defer:  # the caller announces from `with ops.announce()` (ops.module_join: no join inside a step)
+            ops.module_join(sv, dout, dpre2, du, dh1, dy, dpre1, datt, dqkv)
+        else:
+            ops.join()
         return dx, gflat
 
 
@@ -464,7 +467,7 @@ class MultiHeadStack(TransformerStack):
         rstd1 = torch.empty(T, device=dev)
         if ops.can_fuse_norm(d, T):
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0),
-                           norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1))
+                           force_bn=ops.NORM_FORCE_BN, norm=dict(gamma=P32["ln1w"], beta=P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1))
         else:
             ops.linear_fwd(att, P16["Wo"], T, d, d, groups=1, out_bf16=pre1, res=(x, d, 0))
             K.rownorm_fwd(pre1, T, d, P32["ln1w"], P32["ln1b"], out_bf16=y, mean=mean1, rstd=rstd1, rows_per_group=T)
@@ -481,7 +484,7 @@ class MultiHeadStack(TransformerStack):
         rstd2 = torch.empty(Kc * T, device=dev)
         if ops.can_fuse_norm(dout, Kc * T):
             ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"],
-                           norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], out_bf16=out.view(Kc * T, dout),
+                           force_bn=ops.NORM_FORCE_BN, norm=dict(gamma=P32["ln2w"], beta=P32["ln2b"], out_bf16=out.view(Kc * T, dout),
                                      out_f32=None if out32 is None else out32.view(Kc * T, dout), mean=mean2, rstd=rstd2))
         else:
             ops.linear_fwd(u.view(Kc * T, d), P16["Wl"].view(dout, d), Kc * T, dout, d, out_bf16=pre2, bias=P32["bl"])

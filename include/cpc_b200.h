@@ -194,13 +194,16 @@ int cpc_groupsum(const void* in, int in_is_bf16, void* out_f32, void* out_bf16, 
  * total_blocks = the sum).  state: DEVICE double[8] = {step, lr, beta1, beta2, eps, -, -, -}; with advance != 0
  * the call first advances step by one and derives the bias corrections on the device (CUDA-graph safe) -- an
  * optimizer step issued in several launches (one per gradient bucket, as each is reduced) advances once.
- * p16 (optional): bf16 copy of the updated parameter, written in the same pass. */
+ * p16 (optional): bf16 copy of the updated parameter, written in the same pass.
+ * max_ctas > 0: the update runs on at most that many persistent CTAs (a THROTTLED pass: issued next to the latency-bound
+ * recurrent backward it would otherwise starve of HBM bandwidth, it takes a fraction of the bandwidth for longer);
+ * 0: one CTA per chunk. */
 typedef struct {
   void* p; const void* g; void* m; void* v; void* p16;
   int64_t n; int64_t first_block;
 } CpcAdamSpan;
 int cpc_adam_step(const CpcAdamSpan* spans_dev, int n_spans, int64_t total_blocks, double* state_dev, int advance,
-                  void* stream);
+                  int max_ctas, void* stream);
 int cpc_adam_chunk(void);
 
 /* extIdx = ((seqIdx + t) mod S) + batchIdx*S, int64, flat (b,n,t) order -- criterion.py:256-266 */
