@@ -19,8 +19,10 @@ from . import ops
 # restores update-right-behind-the-reduction
 DEFER_UPDATE = int(os.environ.get("CPC_ADAM_DEFER", "1"))
 # persistent CTAs of an update launched from a gradient announcement, i.e. next to the rest of the backward (0: one CTA
-# per 4096-element chunk, which saturates HBM and slowed the recurrent backward beside it from 100 to 132 us)
-STAGED_CTAS = int(os.environ.get("CPC_ADAM_CTAS", "0"))
+# per 4096-element chunk, which saturates HBM and slowed the recurrent backward beside it from 100 to 132 us).
+# Same-box sweep at N = 1 (ms/step): 64: 1.287, 96: 1.17, 148: 1.097, 192: 1.084, 256: 1.084, 296: 1.083, 384: 1.10,
+# 592: 1.10, unthrottled: 1.106.
+STAGED_CTAS = int(os.environ.get("CPC_ADAM_CTAS", "256"))
 
 
 class FusedAdam(torch.optim.Optimizer):
