@@ -445,7 +445,7 @@ def test_staged_adam_equals_single_launch():
     g = torch.Generator().manual_seed(3)
     seq = (0.1 * torch.randn(4, 2, 1, args.sizeWindow, generator=g)).cuda()
     label = torch.zeros(4, dtype=torch.long, device="cuda")
-    finals = []
+    finals, after2 = [], []
     seen = []
     spy = lambda stage, gflat, params=None, grads=None: seen.append(stage)
     for staged in (False, True, "early"):
@@ -465,6 +465,9 @@ def test_staged_adam_equals_single_launch():
                 T.forwardBackward(model, crit, seq, label)
                 opt.step()
                 opt.zero_grad()
+                if it == 1:
+                    torch.cuda.synchronize()
+                    after2.append([p.detach().clone() for p in list(crit.parameters()) + list(model.parameters())])
         finally:
             opt.detach()
             ops.GRAD_READY.remove(spy)
@@ -476,9 +479,21 @@ def test_staged_adam_equals_single_launch():
         else:
             assert seen[0] == "criterion", seen
         finals.append([p.detach().clone() for p in list(crit.parameters()) + list(model.parameters())])
+    # Two iterations: the gradients of the three runs differ by the fp32 order of the atomics only (measured <= 1e-6 of a
+    # tensor's largest entry), and so do the parameters -- a second counter advance, a bucket stepped twice or not at all
+    # would show here as a different bias correction (1e-3 per element).
+    for other in after2[1:]:
+        for a, b in zip(after2[0], other):
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)
+    # Third iteration: that 1e-6 noise can move a parameter across a bf16 rounding boundary of its weight shadow; one
+    # flipped weight (2^-8 relative) changes the step's activations and gradients by up to 0.5 % in a few entries, in
+    # the single-launch run as well as in the staged ones (tools/dbg_staged.py: two repeatable outcomes, each run lands
+    # on either; 9 of 16 single-launch repeats left the 1e-4 band against another single-launch run).  An Adam step moves
+    # an entry by at most ~lr, so the runs stay within 2 lr of each other and equal in all but a few entries.
     for other in finals[1:]:
         for a, b in zip(finals[0], other):
-            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)  # gradients differ by fp32 atomics order only
+            assert (a - b).abs().max().item() <= 2e-3
+            assert ((a - b).abs() > 1e-6 + 1e-4 * b.abs()).float().mean().item() <= 0.2  # (measured: 2 of 64 entries)
 
 
 def test_graphed_step_with_fused_adam_learns():
