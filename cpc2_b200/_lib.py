@@ -205,5 +205,6 @@ EXPORTED = [
     "cpc_conv0_cn_relu_fwd", "cpc_conv0_cn_relu_bwd", "cpc_conv_weight_pack", "cpc_conv_wgrad_unpack",
     "cpc_cast_f32_to_bf16", "cpc_cast_bf16_to_f32", "cpc_colsum", "cpc_groupsum", "cpc_neg_ext_index",
     "cpc_nce_fwd", "cpc_nce_bwd", "cpc_lstm_fwd", "cpc_lstm_bwd", "cpc_attn_fwd", "cpc_attn_bwd",
+    "cpc_attn_bwd_noalloc",
     "cpc_adam_step", "cpc_adam_chunk", "cpc_dropout", "cpc_allreduce_mc", "cpc_allreduce_pad_bytes",
 ]

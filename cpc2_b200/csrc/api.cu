@@ -47,6 +47,7 @@ extern "C" const char* cpc_strerror(int s) {
     case CPC_ERR_TENSORMAP: return "tensor map encoding failed";
     case CPC_ERR_LAUNCH: return "kernel launch failed";
     case CPC_ERR_UNSUPPORTED: return "unsupported configuration";
+    case CPC_ERR_TOO_LARGE: return "problem exceeds the built-in scratch of the no-allocation entry point";
     default: return "unknown status";
   }
 }

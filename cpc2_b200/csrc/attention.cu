@@ -282,3 +282,56 @@ extern "C" int cpc_attn_bwd(const CpcAttn* d, void* stream_) {
   }
   return launch_status();
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// cpc_attn_bwd_noalloc: the scratch-using (general, CUDA-core) backward above with its `dscore` scratch in a file-scope
+// device array instead of a caller-allocated buffer -- for callers that cannot allocate (code under CUDA-graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Nothing here (or below it) calls cudaMalloc / cudaFree or an allocating library routine.
+//   * CPC_ATTN_NOALLOC_MAX_ELEMS bf16 elements (8 MiB) are held by every GPU that loads the library, until exit;
+//   * every call SHARES the array: calls that overlap on the GPU (two streams, two graph branches) race on it;
+//   * it keeps the previous call's contents.  Nothing has to start at zero: phase A of the kernel writes every
+//     lower-triangle element (i >= j) of every (group, window, head) block before phases B / C read exactly those.
+// In host code `g_attn_dscore_static` is a host-side stand-in for the symbol, not a device address: the address the
+// kernel gets comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) __nv_bfloat16 g_attn_dscore_static[CPC_ATTN_NOALLOC_MAX_ELEMS];
+
+static int attn_static_scratch(__nv_bfloat16** out) {
+  constexpr int MAX_DEV = 64;
+  static __nv_bfloat16* addr[MAX_DEV] = {};  // per device (benign race: every thread resolves the same address)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return CPC_ERR_LAUNCH;
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_attn_dscore_static) != cudaSuccess || p == nullptr) {
+      (void)cudaGetLastError();
+      return CPC_ERR_LAUNCH;
+    }
+    addr[dev] = static_cast<__nv_bfloat16*>(p);
+  }
+  *out = addr[dev];
+  return CPC_OK;
+}
+
+extern "C" int cpc_attn_bwd_noalloc(const CpcAttn* d, void* stream_) {
+  AttnArgs a;
+  int rc = fill_attn(a, d);
+  if (rc != CPC_OK) return rc;
+  if (a.dout == nullptr || a.dqkv == nullptr) return CPC_ERR_ARG;
+  const long long elems = (long long)d->G * d->Bt * d->Hh * d->S * d->S;
+  if (elems > (long long)CPC_ATTN_NOALLOC_MAX_ELEMS) return CPC_ERR_TOO_LARGE;
+  if ((rc = attn_static_scratch(&a.dscore)) != CPC_OK) return rc;  // whatever the caller put in d->dscore is ignored
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  dim3 grid(a.Hh, a.Bt, d->G);
+  size_t sm = attn_smem<float>(a.S, a.dk, true);
+  if (sm <= 100 * 1024) {
+    if ((rc = set_smem(attn_bwd_kernel<float>, sm)) != CPC_OK) return rc;
+    launch_k(attn_bwd_kernel<float>, dim3(grid), dim3(256), sm, stream, a);
+  } else {
+    sm = attn_smem<__nv_bfloat16>(a.S, a.dk, true);
+    if (sm > 220 * 1024) return CPC_ERR_UNSUPPORTED;
+    if ((rc = set_smem(attn_bwd_kernel<__nv_bfloat16>, sm)) != CPC_OK) return rc;
+    launch_k(attn_bwd_kernel<__nv_bfloat16>, dim3(grid), dim3(256), sm, stream, a);
+  }
+  return launch_status();
+}

@@ -298,6 +298,14 @@ def adam_step(table, n_spans, blocks, state, advance=True, max_ctas=0):
                            ctypes.c_void_p(state.data_ptr()), int(advance), int(max_ctas), stream_ptr(),))
 
 
+def attn_bwd_noalloc(qkv, krel, out, probs, dout, dqkv, dkrel, G, Bt, Hh, S, dk, rng=None, site=0, drop_p=0.0):
+    """cpc_attn_bwd_noalloc: attn_bwd on the general kernel with the library's static scratch (no `dscore` buffer, no
+    allocation; G*Bt*Hh*S*S <= 4 Mi elements; calls that overlap on the GPU race on the shared scratch)."""
+    d = _attn(qkv, krel, out, probs, G, Bt, Hh, S, dk, rng, site, drop_p)
+    d.dout, d.dqkv, d.dkrel = _dp(dout), _dp(dqkv), _dp(dkrel)
+    _run("cpc_attn_bwd_noalloc", (ctypes.byref(d), stream_ptr(),))
+
+
 CELL = {"LSTM": 0, "GRU": 1, "RNN": 2}
 
 

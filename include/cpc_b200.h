@@ -31,7 +31,8 @@ typedef enum {
   CPC_ERR_DRIVER = -3,    /* cuTensorMapEncodeTiled entry point not found */
   CPC_ERR_TENSORMAP = -4, /* cuTensorMapEncodeTiled rejected the operand view */
   CPC_ERR_LAUNCH = -5,    /* kernel launch failed (see cudaGetLastError) */
-  CPC_ERR_UNSUPPORTED = -6
+  CPC_ERR_UNSUPPORTED = -6,
+  CPC_ERR_TOO_LARGE = -7  /* problem exceeds the built-in scratch of a no-allocation entry point */
 } CpcStatus;
 
 const char* cpc_strerror(int status);
@@ -277,6 +278,18 @@ typedef struct {
 
 int cpc_attn_fwd(const CpcAttn* desc, void* stream);
 int cpc_attn_bwd(const CpcAttn* desc, void* stream);
+
+/* cpc_attn_bwd for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as cpc_attn_bwd on its general (CUDA-core, any S <= 256 / dk <= 64) kernel -- the one that
+ * needs the `dscore` scratch -- but desc->dscore is ignored: the scratch is a file-scope device array inside the
+ * library of CPC_ATTN_NOALLOC_MAX_ELEMS bf16 elements (8 MiB, held by every GPU that loads the library until exit).
+ * G*Bt*Hh*S*S above that limit returns CPC_ERR_TOO_LARGE.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  Every call shares the one array and it keeps the previous call's contents (the kernel
+ * writes every element before reading it, nothing needs clearing): calls that OVERLAP on the GPU -- two streams, two
+ * branches of a graph -- race; issue them on one stream or order them with events. */
+#define CPC_ATTN_NOALLOC_MAX_ELEMS (4 * 1024 * 1024)
+int cpc_attn_bwd_noalloc(const CpcAttn* desc, void* stream);
 
 #ifdef __cplusplus
 }
