@@ -291,9 +291,12 @@ class TrainRig:
         torch.manual_seed(4321 + ctx.rank)  # every rank draws its own negatives, as in the reference
         self.dp = BucketedAllReduce(self.model, self.crit, symmetric=ctx.sym)
         self.dp.broadcast_parameters()
-        if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1":  # diagnosis only (the printed line says so)
+        diag = os.environ.get("CPC_DIAG_NO_ALLREDUCE", "")
+        if diag == "1":  # diagnosis only (the printed line says so)
             self.dp._all_reduce_mean = lambda t: None
             self.dp._skip_collective = True
+        elif diag:  # comma-separated stage prefixes whose reduction is skipped (symmetric path only)
+            self.dp._skip_collective = tuple(diag.split(","))
         n0 = K.LAUNCHES
         self.adam = FusedAdam(list(self.crit.parameters()) + list(self.model.parameters()), lr=args.learningRate,
                               betas=(args.beta1, args.beta2), eps=args.epsilon)  # cpc/train.py:472-479
@@ -551,12 +554,13 @@ def run_ours(opt, out):
                    "l2_flush_between_steps": True, "cuda_graph": True, "dropout": "train mode (p=0.1 in the heads)",
                    "programmatic_dependent_launch": os.environ.get("CPC_PDL", "0") == "1",
                    "capture_stream_priority": __import__("cpc2_b200.ops", fromlist=["ops"]).MAIN_PRIORITY,
+                   "capture_stream_priority": __import__("cpc2_b200.ops", fromlist=["ops"]).MAIN_PRIORITY,
                    "optimizer": "fused multi-tensor Adam (cpc_adam_step) inside the timed step, per bucket after its all-reduce",
                    "grad_allreduce_bytes": dp.bytes_per_step if world > 1 else 0,
                    "grad_allreduce": ("none" if world == 1 else "cpc_allreduce_mc (NVSwitch multimem, in place)"
                                       if dp.symmetric is not None else "NCCL all-reduce (AVG)"),
                    **({"DIAGNOSTIC": "all-reduce skipped, not a valid number"}
-                      if os.environ.get("CPC_DIAG_NO_ALLREDUCE") == "1" else {})},
+                      if os.environ.get("CPC_DIAG_NO_ALLREDUCE") else {})},
         "e2e": {"value": audio_s * opt.steps / (ms_e2e * 1e-3), "unit": "audio-s/s",
                 "h2d_bytes_per_step": rig.host_seq.numel() * 4, "d2h_bytes_per_step": host_out.numel() * 4,
                 "ms_per_step": ms_e2e / opt.steps},

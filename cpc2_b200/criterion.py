@@ -570,9 +570,14 @@ class _CriterionFn(torch.autograd.Function):
         if BS % 8 != 0:
             raise ValueError("B*S must be a multiple of 8")
         cw = K.cast_bf16(c.detach()[:, :W].contiguous().float()).view(T, H)
-        zb = K.cast_bf16(z.detach().contiguous().float()).view(BS, D)
+        # z is first read by the logits product, behind the heads: its cast runs on a side stream beside them
+        zf = z.detach().contiguous().float()
+        zb = torch.empty(BS, D, device=dev, dtype=BF16)
+        with ops.side(11):
+            K.cast_bf16(zf, zb)
         with ops.saving(will_backward and any(ctx.needs_input_grad)):
             preds, _, saved = eng.forward(cw, T, True, training, seq_len=W)
+        ops.join(11)
         if isinstance(eng, TransformerStack) and will_backward and any(ctx.needs_input_grad):
             # the heads' gradient arena (66 MB at the default config) is cleared NOW on an idle side stream: the same
             # memset at the top of the backward sat on the critical path for ~13 us

@@ -115,8 +115,9 @@ class BucketedAllReduce:
         sy = self.symmetric
         off = gflat.data_ptr() - sy["base"] if sy is not None else -1
         with torch.cuda.stream(self.stream):
-            if getattr(self, "_skip_collective", False):  # bench.py diagnosis (CPC_DIAG_NO_ALLREDUCE=1): same plumbing, no exchange
-                pass
+            skip = getattr(self, "_skip_collective", False)  # bench.py diagnosis (CPC_DIAG_NO_ALLREDUCE=1 / =<stage prefixes>)
+            if skip is True or (isinstance(skip, tuple) and stage.startswith(skip)):
+                pass  # same plumbing, no exchange: NOT a valid training step
             elif 0 <= off < sy["bytes"] if sy is not None else False:
                 n = (gflat.numel() + 3) // 4 * 4  # arenas are padded to 32 floats inside the symmetric buffer
                 K.allreduce_mc(sy["mc"] + off, n, sy["pads"], sy["rank"], self.world, 1.0 / self.world, self.max_blocks)

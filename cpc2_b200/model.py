@@ -299,6 +299,18 @@ class _EncoderFn(torch.autograd.Function):
         wg = 7 if future else 0  # weight-gradient side stream (forked from the stream this half runs on)
         after = ops.pop_ready(dz) if future else None
         last = True
+        grads = []
+        for l in range(5):
+            k = GEOMETRY[l][0]
+            dw, dcb, dg, db = gv[4 * l:4 * l + 4]
+            grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
+        # Early announcements (ops.EARLY_ENCODER): the gradients of layer l are complete once THIS half's weight gradient
+        # of layer l is (the other half of a pair has finished or is waited for) -- they are announced from the
+        # weight-gradient side stream, so that their all-reduce and optimizer step run next to the rest of the
+        # encoder's backward instead of trailing the step.  Mode 1: conv1-4 as one bucket behind conv1's weight
+        # gradient; mode 2: one bucket per layer (conv4 first; only conv1's 2 MB and conv0's 13 KB are reduced late).
+        early = ops.EARLY_ENCODER if (bool(ops.GRAD_READY) and (pair is None or pair.pending == 1)) else 0
+        lay_off = [sum(sizes[:4 * l]) for l in range(6)]
         with (ops.side(6, after=after) if future else _null()):
             d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
             dout, dout_map = d, None
@@ -322,22 +334,17 @@ class _EncoderFn(torch.autograd.Function):
                     K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout,
                            k_splits=max(2, ops.auto_splits(C, k * C, N * Lout, 1, Lout)), out_f32=dwf, accumulate=True)
                     K.conv_wgrad_unpack(dwf, dw, C, C, k)
+                    if early == 2:
+                        if pair is not None and pair.first_done is not None:
+                            torch.cuda.current_stream().wait_event(pair.first_done)
+                        ops.grad_ready(f"encoder.conv{l}", gflat[lay_off[l]:lay_off[l + 1]], ctx.params[4 * l:4 * l + 4],
+                                       grads[4 * l:4 * l + 4])
                 # dgrad: padded dx rows [t*s, t*s+s) = [dy[t-1], dy[t]] . [W_hi; W_lo]
                 A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
                 dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
-            grads = []
-            for l in range(5):
-                k = GEOMETRY[l][0]
-                dw, dcb, dg, db = gv[4 * l:4 * l + 4]
-                grads += [dw.view(C, 1 if l == 0 else C, k), dcb, dg.view(1, C, 1), db.view(1, C, 1)]
-            # The gradients of conv1-4 and their norms (all but 3.3 K of the encoder's 2.4 M parameters) are complete
-            # once THIS half's conv1 weight gradient is (the other half of a pair has finished or is waited for below):
-            # announce them now, from the weight-gradient side stream, so that their all-reduce and optimizer step run
-            # next to conv0's backward instead of trailing the step; only conv0's own slice is announced at the end.
             n0 = sum(sizes[:4])
-            early = ops.EARLY_ENCODER and bool(ops.GRAD_READY) and (pair is None or pair.pending == 1)
-            if early:
+            if early == 1:
                 with ops.side(wg):  # behind every weight gradient of this half (this stream) and the main chain so far
                     if pair is not None and pair.first_done is not None:
                         torch.cuda.current_stream().wait_event(pair.first_done)
@@ -488,7 +495,8 @@ class _RecurrentFn(torch.autograd.Function):
             _cast_rnn_weights(p, shadows, cell)
         inp = K.cast_bf16(x.detach().contiguous().float()).view(N * S, Cin)
         saved = []
-        h_ns, c_ns = [], []
+        h_ns = torch.empty(nl, N, H, device=dev)  # final states written in place by the kernels (no torch.stack)
+        c_ns = torch.empty(nl, N, H, device=dev)
         out = None
         prev_pad = None  # h_pad of the previous layer (input of layers > 0)
         for l in range(nl):
@@ -504,21 +512,18 @@ class _RecurrentFn(torch.autograd.Function):
             h_pad = torch.empty(N, S + 1, H, device=dev, dtype=BF16)
             gates = torch.empty(N, S, 4 * H, device=dev, dtype=BF16)
             c_all = torch.empty(N, S, H, device=dev)
-            h_n = torch.empty(N, H, device=dev)
-            c_n = torch.empty(N, H, device=dev)
+            h_n, c_n = h_ns[l], c_ns[l]
             h0l = h0[l].contiguous().float() if h0 is not None else None
             c0l = c0[l].contiguous().float() if c0 is not None else None
             K.lstm_fwd(gx, w_hh16, N, S, H, h0=h0l, c0=c0l, h_pad=h_pad, out=out, gates=gates, c_all=c_all,
                        h_n=h_n, c_n=c_n, cell=cell)
             saved.append((inp if l == 0 else prev_pad, Kin, w_ih16, w_hh16, h_pad, gates, c_all, c0l, h0l))
-            h_ns.append(h_n)
-            c_ns.append(c_n)
             prev_pad = h_pad
         ctx.saved = saved
         ctx.params = list(params)
         ctx.dims = (N, S, Cin, H, nl, cell)
         ctx.set_materialize_grads(False)  # h_n / c_n carry no gradient on this path: no zero tensors made for them
-        return out, torch.stack(h_ns), torch.stack(c_ns)
+        return out, h_ns, c_ns
 
     @staticmethod
     def backward(ctx, dout, dh_n, dc_n):

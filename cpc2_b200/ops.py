@@ -115,10 +115,11 @@ MAIN_PRIORITY = int(os.environ.get("CPC_MAIN_PRIORITY", "-1"))
 EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")
 
 
-# announce the gradients of conv1-4 before conv0's backward runs (model._EncoderFn.backward): the encoder's all-reduce
-# and optimizer step then overlap the last kernel of the step instead of trailing it.  CPC_EARLY_ENCODER=0 restores the
+# announce the encoder's gradients before its backward has finished (model._EncoderFn.backward): 1 = conv1-4 as one
+# bucket before conv0's backward runs, 2 = one bucket per layer as each weight gradient completes; their all-reduce and
+# optimizer step then overlap the rest of the backward instead of trailing the step.  CPC_EARLY_ENCODER=0 restores the
 # single "encoder" announcement.
-EARLY_ENCODER = os.environ.get("CPC_EARLY_ENCODER", "1") != "0"
+EARLY_ENCODER = int(os.environ.get("CPC_EARLY_ENCODER", "1"))
 
 
 def early_ffn():
@@ -169,7 +170,7 @@ class side:
 
 # side streams that only an explicit join(i) waits for (9: the staged optimizer step, which must not be pulled onto
 # the critical path by the blanket join() at the end of a module's backward)
-DETACHED = {9}
+DETACHED = {9, 12}
 
 
 def join(index=None):
@@ -191,12 +192,12 @@ def join(index=None):
 # (MAIN_PRIORITY) those launches finish late.  Inside train.forwardBackward (step_scope) a module instead
 #   * hands every buffer its side streams may still be reading to module_join(...) (kept alive until the step's final
 #     join: the caching allocator must not recycle them for later launches of the chain), and
-#   * announces its gradients from `with ops.announce():` -- side stream 8, which waits for the chain up to here AND for
+#   * announces its gradients from `with ops.announce():` -- side stream 13, which waits for the chain up to here AND for
 #     every side stream forked from it, so dp's all-reduce and the staged Adam launch are ordered behind the weight
 #     gradients without the chain ever waiting.
 # Outside a step_scope (a module used on its own) module_join() is the plain join() and announce() does nothing.
 DEFER_JOINS = os.environ.get("CPC_DEFER_JOINS", "1") != "0"
-ANNOUNCE_STREAM = 8
+ANNOUNCE_STREAM = 13  # (8 is the sampler's: criterion.prefetchIndices)
 _STEP_DEPTH = 0
 _KEEP = []
 
@@ -486,14 +487,23 @@ class DropoutState:
     _states = {}
 
     @classmethod
-    def next(cls, device):
+    def next(cls, device, side_index=None):
+        """Snapshot of (seed, step), then step += 1.  side_index: the two tiny kernels are issued on that side stream
+        (the caller joins it -- ops.join(side_index) -- before the first kernel that reads the snapshot and before the
+        next call): they then run beside the launch that precedes the first dropout site instead of in front of it."""
         key = (device.type, device.index)
         st = cls._states.get(key)
         if st is None:
             st = torch.tensor([torch.initial_seed() & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=device)
             cls._states[key] = st
-        snap = st.clone()
-        st[1:2].add_(1)
+        if side_index is None:
+            snap = st.clone()
+            st[1:2].add_(1)
+            return snap
+        snap = torch.empty_like(st)  # allocated on the current stream (the rule above), written on the side stream
+        with side(side_index):
+            snap.copy_(st)
+            st[1:2].add_(1)
         return snap
 
 

@@ -23,6 +23,7 @@ DEFER_UPDATE = int(os.environ.get("CPC_ADAM_DEFER", "1"))
 # Same-box sweep at N = 1 (ms/step): 64: 1.287, 96: 1.17, 148: 1.097, 192: 1.084, 256: 1.084, 296: 1.083, 384: 1.10,
 # 592: 1.10, unthrottled: 1.106.
 STAGED_CTAS = int(os.environ.get("CPC_ADAM_CTAS", "256"))
+SMALL_BUCKET = int(os.environ.get("CPC_ADAM_SMALL", "65536"))  # parameters; -1: every staged update on one stream
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -35,6 +36,7 @@ class FusedAdam(torch.optim.Optimizer):
         self._groups = [None] * len(self.param_groups)  # per group: device state, span tables, flat moments
         self._dp, self._done, self._advanced = None, set(), False
         self._shadowed = []  # arenas whose bf16 shadow the launches of this iteration wrote
+        self._first_done = None  # event behind the launch that advanced the step counter of this iteration
         self._deferred = []  # (stage, pairs, event) of early buckets whose update waits for the next announcement
 
     # ------------------------------------------------------------------------------------------ internals
@@ -176,16 +178,24 @@ class FusedAdam(torch.optim.Optimizer):
         self._deferred = []
 
     def _launch(self, g, stage, pairs, after, also=None):
-        with ops.side(9, after=after):
+        # small buckets (conv0's 3.3 K parameters, announced last) go to a second stream: on the first they queued behind
+        # the update of the bucket announced just before and the step ended that much later
+        small = sum(p.numel() for p, _ in pairs) <= SMALL_BUCKET
+        with ops.side(12 if small else 9, after=after):
+            cur = torch.cuda.current_stream()
             if after is not None:
-                torch.cuda.current_stream().wait_event(after)  # (also when side streams are disabled)
+                cur.wait_event(after)  # (also when side streams are disabled)
             if also is not None:
-                torch.cuda.current_stream().wait_event(also)
+                cur.wait_event(also)
+            if self._advanced and self._first_done is not None:
+                cur.wait_event(self._first_done)  # the launch that advanced the step counter (maybe on the other stream)
             t = self._table(g, stage, pairs)
             # staged launches run next to the backward: large ones as a throttled pass (STAGED_CTAS persistent CTAs)
             K.adam_step(t["table"], t["n_spans"], t["blocks"], g["state"], advance=not self._advanced,
                         max_ctas=STAGED_CTAS if t["blocks"] > 4 * max(STAGED_CTAS, 1) else 0)
             self._shadowed.extend(t["arenas"])
+            if not self._advanced:
+                self._first_done = ops.mark()
         self._advanced = True
 
     # ------------------------------------------------------------------------------------------ snapshot / restore
@@ -234,6 +244,7 @@ class FusedAdam(torch.optim.Optimizer):
                 self._init_group(gi)
         capturing = torch.cuda.is_current_stream_capturing()
         self._flush_deferred()
+        ops.join(12)
         ops.join(9)  # staged launches of this iteration (FusedAdam.attach); dp.finish() has joined dp.stream
         for gi in range(len(self.param_groups)):
             g = self._groups[gi]
@@ -256,6 +267,7 @@ class FusedAdam(torch.optim.Optimizer):
         self._shadowed = []
         self._done.clear()
         self._advanced = False
+        self._first_done = None
         return loss
 
     def state_dict(self):

@@ -78,6 +78,7 @@ def buildModelAndCriterion(args):
 # forwardBackward runs an unwrapped cpc2_b200 CPCModel as two halves (CPCModel.forwardPastFuture); False restores
 # the literal concatenated call of cpc/train.py:95-104 (wrapped models -- DataParallel / DDP -- always use it)
 SPLIT_PAST_FUTURE = True
+_ONES = {}  # seeds of the backward, per loss shape
 
 
 def prefetchWeights(cpcModel, cpcCriterion):
@@ -115,8 +116,14 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
         label = label2[:b]
     allLosses, allAcc = cpcCriterion(c_feature, encoded_data, label, signal_quality)
     if backward:
-        totLoss = allLosses.sum()
+        # totLoss = allLosses.sum(); totLoss.backward()  (cpc/train.py:107-109): the gradient of a sum with respect to
+        # every summand is one, so the backward is seeded with a cached tensor of ones -- the same gradients without
+        # the sum, the fill and the expand kernels autograd would put in front of the criterion's backward
         from . import ops
+        key = (tuple(allLosses.shape), allLosses.device, allLosses.dtype)
+        seed = _ONES.get(key)
+        if seed is None:
+            seed = _ONES[key] = torch.ones(allLosses.shape, device=allLosses.device, dtype=allLosses.dtype)
         # the modules' backward passes may leave their weight-gradient streams to the step's final join (ops.step_scope)
         # -- unless somebody reads gradients on the autograd stream as they are accumulated: the reducer of a
         # DistributedDataParallel / DataParallel wrapper, or a hook registered on a parameter
@@ -125,9 +132,9 @@ def forwardBackward(cpcModel, cpcCriterion, sequence, label, signal_quality=None
             for m in (cpcModel, cpcCriterion) for p in m.parameters())
         if bare:
             with ops.step_scope():
-                totLoss.backward()
+                torch.autograd.backward(allLosses, grad_tensors=seed)
         else:
-            totLoss.backward()
+            torch.autograd.backward(allLosses, grad_tensors=seed)
     return allLosses, allAcc
 
 

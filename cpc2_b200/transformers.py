@@ -280,9 +280,11 @@ class TransformerStack:
         P32 = self.spans(w32)
         P16 = self.spans(self.arena.bf16())
         drop = self.p_drop if training else 0.0
-        rng = ops.DropoutState.next(dev) if drop > 0 else None
+        rng = ops.DropoutState.next(dev, side_index=5) if drop > 0 else None  # first read by the attention kernel
         qkv = torch.empty(G, T, 3 * d, device=dev, dtype=BF16)
         ops.linear_fwd(x, P16["Wqkv"], T, 3 * d, d, groups=G, x_shared=shared, out_bf16=qkv)
+        if rng is not None:
+            ops.join(5)
         att, sa = self._attn_fwd(qkv, P32.get("krel"), G, T, seq_len, rng, drop)
         pre1 = torch.empty(G, T, d, device=dev, dtype=BF16)
         res = (x, d, 0) if shared else x

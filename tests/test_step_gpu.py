@@ -93,9 +93,14 @@ def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_qua
                 grads=grads, ext=captured["ext"].cpu())
 
 
-def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, strides=None, tag=""):
+def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, strides=None, tag="", loss_floor=0.0):
     """`floors`: per-tensor bf16-storage noise floor (see the module docstring); None = the plain 0.99 line.
-    `strides`: fixtures that store big gradients as g.flatten()[::stride]."""
+    `strides`: fixtures that store big gradients as g.flatten()[::stride].
+    `loss_floor`: the same floor for the loss -- |loss of the exact oracle - loss of the oracle with bf16 operands| at
+    THIS state.  The warm-up that precedes the oracle cases is chaotic (fp32 atomics order -> a weight crossing a bf16
+    rounding boundary -> another trajectory) and now and then ends in a state whose loss itself moves by 0.03 under
+    bf16 storage (measured: conv8 heads, gradient floors down to 0.70 in the same state); the limit is 2e-2 unless
+    twice that state's own floor is larger, derived at run time like the gradient limits."""
     loss_err = (out["loss"] - ref_loss).abs().max().item()
     acc_err = (out["acc"] - ref_acc).abs().max().item()
     rows, bad = [], []
@@ -118,7 +123,7 @@ def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, 
                          max_err_over_max=float(d.abs().max() / (ref.abs().max() + 1e-30)))
     report(tag, loss_err=loss_err, acc_err=acc_err, worst=worst, min_cos=min(r[1] for r in rows) if rows else None,
            n_below_099=sum(r[1] < MIN_COS for r in rows), n_tensors=len(rows), failed=bad, act=act)
-    assert loss_err <= 2e-2, (out["loss"], ref_loss)
+    assert loss_err <= max(2e-2, 2.0 * loss_floor), (out["loss"], ref_loss, loss_floor)
     assert acc_err <= 0.0101 + 1.0 / ref_c.shape[1], (out["acc"], ref_acc)
     assert act["z"]["rel_l2"] <= 3e-2 and act["z"]["max_err_over_max"] <= 3e-2 + 1e-3, act
     assert act["c"]["rel_l2"] <= 3e-2, act
@@ -271,9 +276,11 @@ def test_against_oracle(name):
     finally:
         oc.EMULATE_BF16 = False
     floors = {k: cosine(emu["grads"][k], g) for k, g in ref["grads"].items() if g.abs().max() > 0}
+    loss_floor = float((emu["loss"] - ref["loss"]).abs().max())
     report("oracle/" + name + "/setup", warm_steps=warm[0], warm_loss=warm[1], loss=[round(float(x), 4) for x in ref["loss"].flatten()],
-           min_floor=min(floors.values()), floors_below_099=sorted((round(v, 4), k) for k, v in floors.items() if v < MIN_COS))
-    check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], ref["grads"], floors=floors, tag="oracle/" + name)
+           loss_floor=loss_floor, min_floor=min(floors.values()), floors_below_099=sorted((round(v, 4), k) for k, v in floors.items() if v < MIN_COS))
+    check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], ref["grads"], floors=floors, tag="oracle/" + name,
+                  loss_floor=loss_floor)
 
 
 def test_default_init_matches_reference_fingerprint():
