@@ -154,6 +154,7 @@ class Conv0(ctypes.Structure):
         ("out", ctypes.c_void_p), ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p),
         ("dout", ctypes.c_void_p), ("dw", ctypes.c_void_p), ("db", ctypes.c_void_p), ("dgamma", ctypes.c_void_p),
         ("dbeta", ctypes.c_void_p),
+        ("x_stride", ctypes.c_int64),
     ]
 
 

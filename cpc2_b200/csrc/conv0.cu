@@ -25,7 +25,8 @@ constexpr int STRIP = 64;  // frames per CTA
 constexpr int TILES = STRIP / 16;
 
 struct Conv0Args {
-  const float* x;  // [N, W] waveform
+  const float* x;  // [N, W] waveform, rows x_stride elements apart
+  long long x_stride;
   const float* w;  // [C, 1, 10]
   const float* b;  // [C]
   const float* gamma;
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_fwd_kernel(const Conv0A
   const int spw = (a.L0 + STRIP - 1) / STRIP;
   const int n = blockIdx.x / spw, t0 = (blockIdx.x % spw) * STRIP;
   const int Lp = a.L0 + 2 * a.halo;
-  build_a_rows(sA, nullptr, STRIP, a.x + (long long)n * a.W, a.W, a.L0, t0);
+  build_a_rows(sA, nullptr, STRIP, a.x + (long long)n * a.x_stride, a.W, a.L0, t0);
   build_b_rows(sB, a.w, a.b, C);
   if (a.halo > 0) {
     if (t0 == 0) zero_rows(a.out + (long long)n * Lp * C, a.halo, C);
@@ -323,7 +324,7 @@ __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0A
   for (int item = blockIdx.x; item < items; item += gridDim.x) {
     const int n = item / ipw, t0 = (item % ipw) * STRIPB;
     __syncthreads();  // every warp is done with the previous item's operands
-    build_a_rows(sA, sA1, STRIPB, a.x + (long long)n * a.W, a.W, a.L0, t0);
+    build_a_rows(sA, sA1, STRIPB, a.x + (long long)n * a.x_stride, a.W, a.L0, t0);
     __syncthreads();
 #pragma unroll 1
     for (int tile = 0; tile < STRIPB / 16; ++tile, phase ^= 1) {
@@ -440,6 +441,7 @@ static int fill_conv0(Conv0Args& a, const CpcConv0* d, int& NT, int& NW) {
   a.x = static_cast<const float*>(d->x); a.w = static_cast<const float*>(d->w); a.b = static_cast<const float*>(d->b);
   a.gamma = static_cast<const float*>(d->gamma); a.beta = static_cast<const float*>(d->beta);
   a.out = static_cast<__nv_bfloat16*>(d->out); a.mean = static_cast<float*>(d->mean); a.rstd = static_cast<float*>(d->rstd);
+  a.x_stride = d->x_stride > 0 ? d->x_stride : d->W;
   a.N = d->N; a.W = d->W; a.L0 = (d->W + 2 * P0 - K0) / S0 + 1; a.halo = d->halo; a.C = d->C; a.eps = d->eps;
   a.dout = static_cast<const __nv_bfloat16*>(d->dout);
   a.dw = static_cast<float*>(d->dw); a.db = static_cast<float*>(d->db);

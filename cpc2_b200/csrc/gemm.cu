@@ -371,7 +371,17 @@ static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, GemmKe
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kern, ta, tb, ka) == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
   }
-  const int grid = ka.total_tiles < sm_count() ? ka.total_tiles : sm_count();
+  int cap = sm_count();
+  if constexpr (MODE == EPI_SPLITK || MODE == EPI_ACCUM) {
+    // weight-gradient products run on side streams next to the dependent chain; their persistent CTAs hold an SM each
+    // (200 KB of shared memory: nothing of the chain co-resides), so they may be capped (CPC_WGRAD_CTAS) to leave SMs free
+    static const int wcap = [] {
+      const char* e = getenv("CPC_WGRAD_CTAS");
+      return e != nullptr && atoi(e) > 0 ? atoi(e) : 0;
+    }();
+    if (wcap > 0 && wcap < cap) cap = wcap;
+  }
+  const int grid = ka.total_tiles < cap ? ka.total_tiles : cap;
   launch_k(kern, dim3(grid), dim3(GEMM_THREADS), L::TOTAL, stream, ta, tb, ka);
   return cudaGetLastError() == cudaSuccess ? CPC_OK : CPC_ERR_LAUNCH;
 }

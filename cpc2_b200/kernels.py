@@ -186,9 +186,9 @@ def rownorm_bwd(dout, inp, mean, rstd, rows, C, gamma=None, beta=None, dx_bf16=N
     _run("cpc_rownorm_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5):
+def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5, x_stride=0):
     d = _lib.Conv0()
-    d.N, d.W, d.C, d.halo, d.eps = N, W, C, halo, eps
+    d.N, d.W, d.C, d.halo, d.eps, d.x_stride = N, W, C, halo, eps, x_stride
     d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
     d.out, d.mean, d.rstd = _dp(out), _dp(mean), _dp(rstd)
     if PROFILE is not None:
@@ -196,9 +196,9 @@ def conv0_fwd(x, w, b, gamma, beta, out, mean, rstd, N, W, C, halo, eps=1e-5):
     _run("cpc_conv0_cn_relu_fwd", (ctypes.byref(d), stream_ptr(),))
 
 
-def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, W, C, halo, eps=1e-5):
+def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, W, C, halo, eps=1e-5, x_stride=0):
     d = _lib.Conv0()
-    d.N, d.W, d.C, d.halo, d.eps = N, W, C, halo, eps
+    d.N, d.W, d.C, d.halo, d.eps, d.x_stride = N, W, C, halo, eps, x_stride
     d.x, d.w, d.b, d.gamma, d.beta = _dp(x), _dp(w), _dp(b), _dp(gamma), _dp(beta)
     d.mean, d.rstd = _dp(mean), _dp(rstd)
     d.dout, d.dw, d.db, d.dgamma, d.dbeta = _dp(dout), _dp(dw), _dp(db), _dp(dgamma), _dp(dbeta)

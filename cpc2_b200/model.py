@@ -179,12 +179,18 @@ def _alloc_fwd(N, W, C, dev):
     return b
 
 
-def _alloc_bwd(N, W, C, dev):
+def _alloc_bwd(N, W, C, dev, zero_on=None):
     """Workspace of the encoder backward: per conv layer dy (one zero row either side), the fp32 weight gradient
     in GEMM layout (zeroed: split-K accumulates into it) and the padded input gradient."""
     L, _ = _geometry(N, W)
     w = [None]
-    dwf = torch.zeros(sum(C * GEOMETRY[l][0] * C for l in range(1, 5)), device=dev)  # one memset for the four layers
+    n_dwf = sum(C * GEOMETRY[l][0] * C for l in range(1, 5))  # one memset for the four layers
+    if zero_on is None:
+        dwf = torch.zeros(n_dwf, device=dev)
+    else:  # allocated on the current stream, cleared on a side stream (the caller joins it before the first write)
+        dwf = torch.empty(n_dwf, device=dev)
+        with ops.side(zero_on):
+            dwf.zero_()
     off = 0
     for l in range(1, 5):
         k, s, pd = GEOMETRY[l]
@@ -234,7 +240,13 @@ class _EncoderFn(torch.autograd.Function):
         if L[4] < 1:
             raise ValueError(f"CPCEncoder: {W} samples are shorter than one output frame")
         future = plan.role == "future"
-        x2 = x.detach().reshape(N, W).contiguous().float()
+        # the waveform is read IN PLACE when it is an fp32 view with unit sample stride (the past / future windows of a
+        # [B,2,1,W] batch, cpc/train.py:95-96, are rows 2W apart): no copy in front of conv0, forward or backward
+        xd = x.detach()
+        if ops.INPLACE_X and xd.dtype == torch.float32 and xd.stride(2) == 1 and (N == 1 or xd.stride(0) >= W):
+            x2, xs = xd, (xd.stride(0) if N > 1 else W)
+        else:
+            x2, xs = xd.reshape(N, W).contiguous().float(), W
         bufs = plan.fwd_bufs if plan.fwd_bufs is not None else _alloc_fwd(N, W, C, dev)
         acts, ys, means, rstds, z32 = bufs["acts"], bufs["ys"], bufs["means"], bufs["rstds"], bufs["z32"]
         # conv1..4 weights in GEMM layout: handed in by the pair driver, prefetched on side stream 3, or packed now
@@ -247,7 +259,7 @@ class _EncoderFn(torch.autograd.Function):
                 _pack_conv_weights([p[4 * l] for l in range(1, 5)], packed)
         with (ops.side(6, after=plan.fwd_after) if future else _null()):
             # layer 0: fused conv + ChannelNorm + ReLU straight from the waveform (halo rows zeroed by the kernel)
-            K.conv0_fwd(x2, p[0], p[1], p[2], p[3], acts[0], means[0], rstds[0], N, W, C, pad_next[0])
+            K.conv0_fwd(x2, p[0], p[1], p[2], p[3], acts[0], means[0], rstds[0], N, W, C, pad_next[0], x_stride=xs)
             if future:
                 ops.wait_side(3)  # the past half (main stream) consumes the pending join
             else:
@@ -273,7 +285,7 @@ class _EncoderFn(torch.autograd.Function):
                               mean=means[l], rstd=rstds[l], out_map=K.rowmap(Lout, Lout + 2 * hn, hn), unbiased=True,
                               relu=True)
         ctx.geom = (N, W, C, L, pad_next)
-        ctx.x2 = x2
+        ctx.x2, ctx.xs, ctx.x_version = x2, xs, x._version
         ctx.acts, ctx.ys, ctx.means, ctx.rstds, ctx.packed = acts, ys, means, rstds, packed
         ctx.p = p
         ctx.params = list(params)
@@ -312,6 +324,7 @@ class _EncoderFn(torch.autograd.Function):
         early = ops.EARLY_ENCODER if (bool(ops.GRAD_READY) and (pair is None or pair.pending == 1)) else 0
         lay_off = [sum(sizes[:4 * l]) for l in range(6)]
         with (ops.side(6, after=after) if future else _null()):
+            ops.wait_side(14)  # the arena / staging memsets issued beside the forward (forwardPastFuture)
             d = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]; free when it came from our own layout
             dout, dout_map = d, None
             for l in range(4, 0, -1):
@@ -351,7 +364,7 @@ class _EncoderFn(torch.autograd.Function):
                     ops.grad_ready("encoder.main", gflat[n0:], ctx.params[4:], grads[4:])
             dw0, db0, dg0, dbe0 = gv[0:4]
             K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
-                        pad_next[0])
+                        pad_next[0], x_stride=ctx.xs)
             ops.join()
             if pair is not None:
                 pair.pending -= 1
@@ -630,10 +643,15 @@ class CPCModel(nn.Module):
             with ops.side(3):
                 _pack_conv_weights([w.detach() for w in ws], packed)
         # everything the future half touches on its side stream exists BEFORE the fork event (ops.side(after=))
-        fut = future.detach().reshape(N, W).contiguous().float().view(N, 1, W)
-        pair = _PairCtx(ops.grad_arena("encoder", sum(_grad_sizes(C)), dev))
+        fut = future.detach()
+        if not (ops.INPLACE_X and fut.dtype == torch.float32 and fut.dim() == 3 and fut.stride(2) == 1):  # (else in place)
+            fut = fut.reshape(N, W).contiguous().float().view(N, 1, W)
+        # the gradient arena and the weight-gradient staging are cleared on an idle side stream (first written in the
+        # backward; both halves' backward start behind the criterion, which joins everything)
+        grad = torch.is_grad_enabled()
+        pair = _PairCtx(ops.grad_arena("encoder", sum(_grad_sizes(C)), dev, zero_on=14) if grad else None)
         plan_f = _EncPlan(packed=packed, role="future", pair=pair, fwd_bufs=_alloc_fwd(N, W, C, dev),
-                          bwd_bufs=_alloc_bwd(N, W, C, dev) if torch.is_grad_enabled() else None)
+                          bwd_bufs=_alloc_bwd(N, W, C, dev, zero_on=14) if grad else None)
         plan_f.fwd_after = ops.mark()
         plan_p = _EncPlan(packed=packed, role="past", pair=pair)
         if not torch.is_grad_enabled():

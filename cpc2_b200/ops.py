@@ -45,6 +45,8 @@ def will_backward():
     return _SAVING[-1] if _SAVING else torch.is_grad_enabled()
 
 
+# conv0 reads fp32 waveform views in place (row stride) instead of a contiguous copy; CPC_INPLACE_X=0: copy first
+INPLACE_X = os.environ.get("CPC_INPLACE_X", "1") != "0"
 # force_bn of the fused-norm GEMM launches: 0 = the kernel picks the tile form by launch size (one 256-column tile per
 # row, or the row split over a 4-CTA cluster); 256 = always one tile per row.  Tests that compare two DIFFERENTLY SIZED
 # launches of the same arithmetic set 256, so that both sum the row statistics in the same order.

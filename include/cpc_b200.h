@@ -151,6 +151,8 @@ typedef struct {
   const void* x; const void* w; const void* b; const void* gamma; const void* beta;
   void* out; void* mean; void* rstd;
   const void* dout; void* dw; void* db; void* dgamma; void* dbeta;
+  int64_t x_stride; /* elements between the rows of x; 0 => W (lets the past / future windows of a [B,2,1,W] batch,
+                       cpc/train.py:95-96, be read in place) */
 } CpcConv0;
 
 int cpc_conv0_cn_relu_fwd(const CpcConv0* desc, void* stream);
