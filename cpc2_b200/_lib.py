@@ -158,6 +158,27 @@ class Conv0(ctypes.Structure):
     ]
 
 
+class ColNorm(ctypes.Structure):
+    _fields_ = [
+        ("rows", ctypes.c_int64), ("C", ctypes.c_int), ("rows_per_group", ctypes.c_int64),
+        ("mode", ctypes.c_int), ("relu", ctypes.c_int),
+        ("inp", ctypes.c_void_p), ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
+        ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p),
+        ("running_mean", ctypes.c_void_p), ("running_var", ctypes.c_void_p), ("momentum", ctypes.c_float),
+        ("eps", ctypes.c_float),
+        ("partial", ctypes.c_void_p),
+        ("out_bf16", ctypes.c_void_p), ("out_map", RowMap), ("out_f32", ctypes.c_void_p),
+        ("dout", ctypes.c_void_p), ("dout_f32", ctypes.c_int), ("dout_map", RowMap),
+        ("sums", ctypes.c_void_p),
+        ("dx_bf16", ctypes.c_void_p), ("dx_map", RowMap), ("dx_f32", ctypes.c_void_p),
+        ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("dxsum", ctypes.c_void_p),
+    ]
+
+
+COLNORM_ID, COLNORM_STATS, COLNORM_GIVEN = 0, 1, 2
+COLNORM_CHUNK_ROWS = 256
+
+
 class Nce(ctypes.Structure):
     _fields_ = [
         ("K", ctypes.c_int), ("B", ctypes.c_int), ("W", ctypes.c_int), ("S", ctypes.c_int), ("NEG", ctypes.c_int),
@@ -203,7 +224,8 @@ class AdamSpan(ctypes.Structure):
 # every symbol include/cpc_b200.h declares (checked by tests/test_abi.py)
 EXPORTED = [
     "cpc_strerror", "cpc_version", "cpc_device_arch", "cpc_set_pdl", "cpc_gemm_bf16", "cpc_rownorm_fwd", "cpc_rownorm_bwd",
-    "cpc_conv0_cn_relu_fwd", "cpc_conv0_cn_relu_bwd", "cpc_conv_weight_pack", "cpc_conv_wgrad_unpack",
+    "cpc_conv0_cn_relu_fwd", "cpc_conv0_cn_relu_bwd", "cpc_colnorm_fwd", "cpc_colnorm_bwd", "cpc_conv0_plain_fwd",
+    "cpc_conv0_plain_bwd", "cpc_conv_weight_pack", "cpc_conv_wgrad_unpack",
     "cpc_cast_f32_to_bf16", "cpc_cast_bf16_to_f32", "cpc_colsum", "cpc_groupsum", "cpc_neg_ext_index",
     "cpc_nce_fwd", "cpc_nce_bwd", "cpc_lstm_fwd", "cpc_lstm_bwd", "cpc_attn_fwd", "cpc_attn_bwd",
     "cpc_attn_bwd_noalloc",

@@ -207,6 +207,72 @@ def conv0_bwd(x, w, b, gamma, beta, mean, rstd, dout, dw, db, dgamma, dbeta, N, 
     _run("cpc_conv0_cn_relu_bwd", (ctypes.byref(d), stream_ptr(),))
 
 
+COLNORM_MODES = {"ID": _lib.COLNORM_ID, "stats": _lib.COLNORM_STATS, "given": _lib.COLNORM_GIVEN}
+
+
+def colnorm_scratch(rows, C, rows_per_group, device):
+    """(partial, sums) scratch of cpc_colnorm_fwd / _bwd (include/cpc_b200.h)."""
+    rpg = rows_per_group or rows
+    groups = rows // rpg
+    chunks = (rpg + _lib.COLNORM_CHUNK_ROWS - 1) // _lib.COLNORM_CHUNK_ROWS
+    return (torch.empty(2 * groups * chunks * C, device=device, dtype=torch.float32),
+            torch.empty(2 * groups * C, device=device, dtype=torch.float32))
+
+
+def _colnorm_desc(inp, rows, C, rows_per_group, mode, relu, gamma, beta, mean, rstd, partial, eps):
+    d = _lib.ColNorm()
+    d.rows, d.C, d.rows_per_group = rows, C, rows_per_group
+    d.mode, d.relu, d.eps = COLNORM_MODES[mode], int(relu), eps
+    d.inp, d.gamma, d.beta, d.mean, d.rstd, d.partial = _dp(inp), _dp(gamma), _dp(beta), _dp(mean), _dp(rstd), _dp(partial)
+    d.out_map, d.dout_map, d.dx_map = rowmap(), rowmap(), rowmap()
+    return d
+
+
+def colnorm_fwd(inp, rows, C, mode, rows_per_group=0, gamma=None, beta=None, mean=None, rstd=None, partial=None,
+                running_mean=None, running_var=None, momentum=0.1, eps=1e-5, out_bf16=None, out_map=None, out_f32=None,
+                relu=True):
+    d = _colnorm_desc(inp, rows, C, rows_per_group, mode, relu, gamma, beta, mean, rstd, partial, eps)
+    d.running_mean, d.running_var, d.momentum = _dp(running_mean), _dp(running_var), momentum
+    d.out_bf16, d.out_f32, d.out_map = _dp(out_bf16), _dp(out_f32), out_map or rowmap()
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(rows) * C * ((4 if mode == "stats" else 2) + (2 if out_bf16 is not None else 0)
+                                                      + (4 if out_f32 is not None else 0)))
+    _run("cpc_colnorm_fwd", (ctypes.byref(d), stream_ptr(),))
+
+
+def colnorm_bwd(dout, inp, rows, C, mode, partial, sums, rows_per_group=0, gamma=None, beta=None, mean=None, rstd=None,
+                eps=1e-5, dout_map=None, dx_bf16=None, dx_map=None, dx_f32=None, dgamma=None, dbeta=None, dxsum=None,
+                relu=True):
+    d = _colnorm_desc(inp, rows, C, rows_per_group, mode, relu, gamma, beta, mean, rstd, partial, eps)
+    d.dout, d.dout_f32, d.dout_map = _dp(dout), int(dout.dtype == torch.float32), dout_map or rowmap()
+    d.sums = _dp(sums)
+    d.dx_bf16, d.dx_f32, d.dx_map = _dp(dx_bf16), _dp(dx_f32), dx_map or rowmap()
+    d.dgamma, d.dbeta, d.dxsum = _dp(dgamma), _dp(dbeta), _dp(dxsum)
+    if PROFILE is not None:
+        nb = 4 if dout.dtype == torch.float32 else 2
+        set_work(kind="hbm", bytes=float(rows) * C * (2 * (2 + nb) + (2 if dx_bf16 is not None else 0)
+                                                      + (4 if dx_f32 is not None else 0)))
+    _run("cpc_colnorm_bwd", (ctypes.byref(d), stream_ptr(),))
+
+
+def conv0_plain_fwd(x, w, b, out, N, W, C, x_stride=0):
+    d = _lib.Conv0()
+    d.N, d.W, d.C, d.x_stride = N, W, C, x_stride
+    d.x, d.w, d.b, d.out = _dp(x), _dp(w), _dp(b), _dp(out)
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(N) * ((W - 4) // 5 + 1) * C * 2 + 4.0 * N * W)
+    _run("cpc_conv0_plain_fwd", (ctypes.byref(d), stream_ptr(),))
+
+
+def conv0_plain_bwd(x, dout, dw, N, W, C, x_stride=0):
+    d = _lib.Conv0()
+    d.N, d.W, d.C, d.x_stride = N, W, C, x_stride
+    d.x, d.dout, d.dw = _dp(x), _dp(dout), _dp(dw)
+    if PROFILE is not None:
+        set_work(kind="hbm", bytes=float(N) * ((W - 4) // 5 + 1) * C * 4 + 4.0 * N * W)
+    _run("cpc_conv0_plain_bwd", (ctypes.byref(d), stream_ptr(),))
+
+
 def conv_weight_pack(w, wf, wd, Co, Ci, k, s):
     _run("cpc_conv_weight_pack", (ptr(w), ptr(wf), ptr(wd), Co, Ci, k, s, stream_ptr(),))
 

@@ -73,27 +73,47 @@ class _ChannelNormFn(torch.autograd.Function):
                 None if db is None else db.view(1, C, 1), None)
 
 
+class IDModule(nn.Module):
+    """cpc/model.py:18-24 (normMode "ID")."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__()
+
+    def forward(self, x):
+        return x
+
+
 class CPCEncoder(nn.Module):
-    """cpc/model.py:63-108: five strided Conv1d, each followed by ChannelNorm and ReLU."""
+    """cpc/model.py:63-108: five strided Conv1d, each followed by a norm layer and ReLU.  normMode "layerNorm" (the
+    default, ChannelNorm) runs the fused kernels (_EncoderFn); "batchNorm" / "instanceNorm" / "ID" keep the reference's
+    nn.BatchNorm1d / nn.InstanceNorm1d(affine=True) / IDModule as PARAMETER CONTAINERS (same state_dict keys, running
+    estimates included) and run the column-statistics kernels (_EncoderColFn, csrc/colnorm.cu)."""
 
     def __init__(self, sizeHidden=512, normMode="layerNorm"):
         super().__init__()
         validModes = ["batchNorm", "instanceNorm", "ID", "layerNorm"]
         if normMode not in validModes:
             raise ValueError(f"Norm mode must be in {validModes}")
-        if normMode != "layerNorm":
-            raise NotImplementedError("cpc2_b200 implements the default normMode='layerNorm' (ChannelNorm) path only")
+        if normMode == "instanceNorm":
+            def normLayer(x): return nn.InstanceNorm1d(x, affine=True)
+        elif normMode == "ID":
+            normLayer = IDModule
+        elif normMode == "layerNorm":
+            normLayer = ChannelNorm
+        else:
+            normLayer = nn.BatchNorm1d
+        self.normMode = normMode
         self.dimEncoded = sizeHidden
         self.conv0 = nn.Conv1d(1, sizeHidden, 10, stride=5, padding=3)
-        self.batchNorm0 = ChannelNorm(sizeHidden)
+        self.batchNorm0 = normLayer(sizeHidden)
         self.conv1 = nn.Conv1d(sizeHidden, sizeHidden, 8, stride=4, padding=2)
-        self.batchNorm1 = ChannelNorm(sizeHidden)
+        self.batchNorm1 = normLayer(sizeHidden)
         self.conv2 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
-        self.batchNorm2 = ChannelNorm(sizeHidden)
+        self.batchNorm2 = normLayer(sizeHidden)
         self.conv3 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
-        self.batchNorm3 = ChannelNorm(sizeHidden)
+        self.batchNorm3 = normLayer(sizeHidden)
         self.conv4 = nn.Conv1d(sizeHidden, sizeHidden, 4, stride=2, padding=1)
-        self.batchNorm4 = ChannelNorm(sizeHidden)
+        self.batchNorm4 = normLayer(sizeHidden)
         self.DOWNSAMPLING = 160
 
     def getDimOutput(self):
@@ -103,7 +123,9 @@ class CPCEncoder(nn.Module):
         ps = []
         for i in range(5):
             conv, norm = getattr(self, f"conv{i}"), getattr(self, f"batchNorm{i}")
-            ps += [conv.weight, conv.bias, norm.weight, norm.bias]
+            ps += [conv.weight, conv.bias]
+            if self.normMode != "ID":
+                ps += [norm.weight, norm.bias]
         return ps
 
     def _conv_weights(self):
@@ -127,6 +149,8 @@ class CPCEncoder(nn.Module):
             raise NotImplementedError("cpc2_b200: training windows must be a multiple of 160 samples (the reference's "
                                       "sizeWindow, default 20480); any length runs forward-only under torch.no_grad()")
         pref, self._pref = getattr(self, "_pref", None), None
+        if self.normMode != "layerNorm":
+            return _EncoderColFn.apply(x, _ColPlan(self, pref), *self._params())
         return _EncoderFn.apply(x, _EncPlan(pref=pref), *self._params())
 
 
@@ -387,6 +411,154 @@ class _EncoderFn(torch.autograd.Function):
         return (None, None, *grads)
 
 
+class _ColPlan:
+    """What _EncoderColFn needs from the module besides its parameters: the norm mode and, for nn.BatchNorm1d, whether
+    batch statistics are used (training mode or track_running_stats off), the running estimates and the momentum."""
+
+    def __init__(self, enc, pref):
+        self.mode, self.pref = enc.normMode, pref
+        self.layers = []
+        for i in range(5):
+            n = getattr(enc, f"batchNorm{i}")
+            d = dict(kind="ID", eps=1e-5, momentum=0.0, rm=None, rv=None)
+            if enc.normMode == "instanceNorm":
+                if n.track_running_stats:
+                    raise NotImplementedError("cpc2_b200: InstanceNorm1d with running statistics is never built by the reference")
+                d.update(kind="stats", eps=n.eps)
+            elif enc.normMode == "batchNorm":
+                batch_stats = n.training or n.running_mean is None
+                d.update(kind="stats" if batch_stats else "given", eps=n.eps)
+                if n.training and n.track_running_stats:
+                    # nn.BatchNorm1d.forward: num_batches_tracked += 1; momentum None = cumulative average
+                    n.num_batches_tracked.add_(1)
+                    if n.momentum is None:
+                        raise NotImplementedError("cpc2_b200: BatchNorm1d(momentum=None) is never built by the reference")
+                    d.update(rm=n.running_mean, rv=n.running_var, momentum=n.momentum)
+                elif not batch_stats:
+                    d.update(rm=n.running_mean, rv=n.running_var)
+            self.layers.append(d)
+
+
+class _EncoderColFn(torch.autograd.Function):
+    """The encoder under normMode batchNorm / instanceNorm / ID (cpc/model.py:71-82,102-107): conv0 on CUDA cores, conv1-4
+    as the same implicit GEMMs as _EncoderFn, statistics down the columns (csrc/colnorm.cu).  Single stream, literal
+    concatenated batch (batch statistics couple every row)."""
+
+    @staticmethod
+    def forward(ctx, x, plan, *params):
+        N, one, W = x.shape
+        if one != 1:
+            raise ValueError("CPCEncoder expects [N, 1, W]")
+        ident = plan.mode == "ID"
+        npl = 2 if ident else 4
+        C = params[0].shape[0]
+        dev = x.device
+        p = [t.detach() for t in params]
+        L, pad_next = _geometry(N, W)
+        if L[4] < 1:
+            raise ValueError(f"CPCEncoder: {W} samples are shorter than one output frame")
+        x2 = x.detach().reshape(N, W).contiguous().float()
+        packed = plan.pref.peek([params[npl * l] for l in range(1, 5)]) if plan.pref is not None else None
+        if packed is None:
+            packed = _alloc_packed(C, dev)
+            with ops.side(3):
+                _pack_conv_weights([p[npl * l] for l in range(1, 5)], packed)
+        acts, ys, means, rstds, kinds = [], [], [], [], []
+        z32 = torch.empty(N, L[4], C, device=dev, dtype=torch.float32)
+        for l in range(5):
+            k, s, pd = GEOMETRY[l]
+            lay = plan.layers[l]
+            w, b = p[npl * l], p[npl * l + 1]
+            g, be = (None, None) if ident else (p[npl * l + 2].reshape(C), p[npl * l + 3].reshape(C))
+            Lout, hn = L[l], pad_next[l]
+            y = torch.empty(N * Lout, C, device=dev, dtype=BF16)
+            a = torch.empty(N, Lout + 2 * hn, C, device=dev, dtype=BF16) if l < 4 else None  # (conv4's output: fp32 only)
+            if l == 0:
+                K.conv0_plain_fwd(x2, w, b, y, N, W, C)
+                ops.join(3)
+            else:
+                Lp = L[l - 1] + 2 * pd
+                A = K.View(acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=0, gmul=1)
+                K.gemm(A, K.kmajor(packed[l][0]), Lout, C, k * C, groups=N, out_bf16=(y, C, Lout * C), bias=b)
+            rpg = Lout if plan.mode == "instanceNorm" else 0
+            mean = rstd = partial = None
+            if lay["kind"] == "stats":
+                groups = N if rpg else 1
+                mean, rstd = torch.empty(groups * C, device=dev), torch.empty(groups * C, device=dev)
+                partial, _ = K.colnorm_scratch(N * Lout, C, rpg, dev)
+            elif lay["kind"] == "given":
+                mean = lay["rm"].detach().float().contiguous()
+                rstd = torch.rsqrt(lay["rv"].detach().float() + lay["eps"]).contiguous()
+            K.colnorm_fwd(y, N * Lout, C, lay["kind"], rows_per_group=rpg, gamma=g, beta=be, mean=mean, rstd=rstd,
+                          partial=partial, running_mean=lay["rm"] if lay["kind"] == "stats" else None,
+                          running_var=lay["rv"] if lay["kind"] == "stats" else None, momentum=lay["momentum"],
+                          eps=lay["eps"], out_bf16=a, out_map=K.rowmap(Lout, Lout + 2 * hn, hn) if l < 4 else None,
+                          out_f32=z32 if l == 4 else None, relu=True)
+            acts.append(a); ys.append(y); means.append(mean); rstds.append(rstd); kinds.append((lay["kind"], rpg))
+        ctx.geom = (N, W, C, L, pad_next)
+        ctx.x2, ctx.acts, ctx.ys, ctx.means, ctx.rstds, ctx.kinds, ctx.packed = x2, acts, ys, means, rstds, kinds, packed
+        ctx.p, ctx.params, ctx.ident = p, list(params), ident
+        return z32.permute(0, 2, 1)
+
+    @staticmethod
+    def backward(ctx, dz):
+        N, W, C, L, pad_next = ctx.geom
+        p, ident = ctx.p, ctx.ident
+        npl = 2 if ident else 4
+        dev = dz.device
+        sizes = []
+        for l in range(5):
+            sizes += [C * (1 if l == 0 else C) * GEOMETRY[l][0], C] + ([] if ident else [C, C])
+        gflat = ops.grad_arena("encoder", sum(sizes), dev)
+        gv, off = [], 0
+        for n_ in sizes:
+            gv.append(gflat[off:off + n_])
+            off += n_
+        grads = []
+        for l in range(5):
+            k = GEOMETRY[l][0]
+            grads += [gv[npl * l].view(C, 1 if l == 0 else C, k), gv[npl * l + 1]]
+            if not ident:
+                shape = ctx.params[npl * l + 2].shape  # [C] (BatchNorm1d / InstanceNorm1d)
+                grads += [gv[npl * l + 2].view(shape), gv[npl * l + 3].view(shape)]
+        dout = dz.permute(0, 2, 1).contiguous().float()  # [N, S, C]
+        dout_map = None
+        for l in range(4, -1, -1):
+            k, s, pd = GEOMETRY[l]
+            kind, rpg = ctx.kinds[l]
+            g, be = (None, None) if ident else (p[npl * l + 2].reshape(C), p[npl * l + 3].reshape(C))
+            dw, dcb = gv[npl * l], gv[npl * l + 1]
+            dg, db = (None, None) if ident else (gv[npl * l + 2], gv[npl * l + 3])
+            Lout = L[l]
+            partial, sums = K.colnorm_scratch(N * Lout, C, rpg, dev)
+            if l == 0:
+                dy0 = torch.empty(N * Lout, C, device=dev, dtype=torch.float32)
+                K.colnorm_bwd(dout, ctx.ys[0], N * Lout, C, kind, partial, sums, rows_per_group=rpg, gamma=g, beta=be,
+                              mean=ctx.means[0], rstd=ctx.rstds[0], dout_map=dout_map, dx_f32=dy0, dgamma=dg, dbeta=db,
+                              dxsum=dcb, relu=True)
+                K.conv0_plain_bwd(ctx.x2, dy0, dw, N, W, C)
+                break
+            Lin = L[l - 1]
+            Lp = Lin + 2 * pd
+            dy = torch.empty(N, Lout + 2, C, device=dev, dtype=BF16)
+            K.colnorm_bwd(dout, ctx.ys[l], N * Lout, C, kind, partial, sums, rows_per_group=rpg, gamma=g, beta=be,
+                          mean=ctx.means[l], rstd=ctx.rstds[l], dout_map=dout_map, dx_bf16=dy,
+                          dx_map=K.rowmap(Lout, Lout + 2, 1), dgamma=dg, dbeta=db, dxsum=dcb, relu=True)
+            # weight and input gradients: the same two GEMMs as _EncoderFn.backward
+            dwf = torch.zeros(C, k * C, device=dev)
+            A = K.View(dy, C, Lout + 2, N, C, (Lout + 2) * C, major=1, row_off=1)
+            B = K.View(ctx.acts[l - 1], k * C, Lout, N, s * C, Lp * C, major=1)
+            K.gemm(A, B, C, k * C, N * Lout, k_per_slab=Lout,
+                   k_splits=max(2, ops.auto_splits(C, k * C, N * Lout, 1, Lout)), out_f32=dwf, accumulate=True)
+            K.conv_wgrad_unpack(dwf, dw, C, C, k)
+            dxp = torch.empty(N, Lp, C, device=dev, dtype=BF16)
+            A = K.View(dy, 2 * C, Lout + 1, N, C, (Lout + 2) * C, major=0, gmul=1)
+            K.gemm(A, K.kmajor(ctx.packed[l][1]), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
+            dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
+        ops.grad_ready("encoder", gflat, ctx.params, grads)
+        return (None, None, *grads)
+
+
 class CPCAR(nn.Module):
     """cpc/model.py:158-207.  `baseNet` is an nn.LSTM/GRU/RNN used as the PARAMETER CONTAINER (cuDNN-layout
     weight_ih_l*, weight_hh_l*, bias_ih_l*, bias_hh_l*, so reference checkpoints load unchanged); the
@@ -621,7 +793,8 @@ class CPCModel(nn.Module):
     def splittable(self):
         """True when the training step may run as two halves (forwardPastFuture): a CPCEncoder front end and an
         AR that carries no state between calls (keepHidden feeds the hidden state of ALL 2B rows forward)."""
-        return isinstance(self.gEncoder, CPCEncoder) and not getattr(self.gAR, "keepHidden", False)
+        return isinstance(self.gEncoder, CPCEncoder) and self.gEncoder.normMode == "layerNorm" and \
+            not getattr(self.gAR, "keepHidden", False)  # (batch statistics span all 2B rows: no halves)
 
     def forwardPastFuture(self, past, future):
         """The two consumers of cpc/train.py:95-104 without the dead work: trainStep concatenates past and future

@@ -282,6 +282,11 @@ class GraphedTrainStep:
         keep = optimizer is not None and warmup > 0
         snap_p = [p.detach().clone() for p in self.params] if keep else None
         snap_o = optimizer.snapshot() if keep and hasattr(optimizer, "snapshot") else None
+        # nn.BatchNorm1d (encoder normMode "batchNorm") moves its running estimates and step count in every training-mode
+        # forward, optimizer or not
+        bufs = [b for m in (cpcModel, cpcCriterion) for n, b in m.named_buffers()
+                if ".running_" in n or n.endswith("num_batches_tracked")] if warmup > 0 else []
+        snap_b = [b.detach().clone() for b in bufs]
         rng_state = torch.cuda.get_rng_state(dev)
         drop_state = ops.DropoutState._states.get((dev.type, dev.index))
         drop_snap = drop_state.clone() if drop_state is not None else None
@@ -300,6 +305,9 @@ class GraphedTrainStep:
                     for p, q in zip(self.params, snap_p):
                         p.copy_(q)  # in place: addresses (and the arenas the parameters live in) are unchanged
                     optimizer.restore(snap_o)
+            with torch.no_grad():
+                for b, q in zip(bufs, snap_b):
+                    b.copy_(q)
             if drop_snap is not None:
                 drop_state.copy_(drop_snap)
             elif (dev.type, dev.index) in ops.DropoutState._states:
@@ -311,7 +319,7 @@ class GraphedTrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(dev)
         torch.cuda.set_rng_state(rng_state, dev)
-        del snap_p, snap_o
+        del snap_p, snap_o, snap_b
         self.graph = torch.cuda.CUDAGraph()
         self._zero()
         # the capture stream carries the dependent chain of the step; with ops.MAIN_PRIORITY < 0 its kernels are

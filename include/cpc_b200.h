@@ -158,6 +158,53 @@ typedef struct {
 int cpc_conv0_cn_relu_fwd(const CpcConv0* desc, void* stream);
 int cpc_conv0_cn_relu_bwd(const CpcConv0* desc, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * The encoder's other normalisation modes (cpc/model.py:71-82: normMode "batchNorm" -> nn.BatchNorm1d,
+ * "instanceNorm" -> nn.InstanceNorm1d(affine=True), "ID" -> IDModule), each followed by ReLU (cpc/model.py:102-107).
+ * `in` is the convolution output, bf16 [rows, C] dense; statistics run down the columns over groups of
+ * `rows_per_group` consecutive rows (batchNorm: one group of N*L rows; instanceNorm: N groups of L rows), biased
+ * variance, fp32.  C in {32, 64, 128, 256, 512}.
+ *   mode CPC_COLNORM_ID    : out = relu(in)
+ *   mode CPC_COLNORM_STATS : mean / rstd [groups, C] are COMPUTED (and saved for the backward); running_mean / running_var
+ *                            [C] (may be null; one group only) are updated as nn.BatchNorm1d does in training mode
+ *                            (momentum, unbiased variance)
+ *   mode CPC_COLNORM_GIVEN : mean / rstd [groups, C] are READ (nn.BatchNorm1d in eval mode: running_mean and
+ *                            1 / sqrt(running_var + eps)); the backward treats them as constants
+ * `partial` is caller-provided scratch of 2 * groups * ceil(rows_per_group / CPC_COLNORM_CHUNK_ROWS) * C floats
+ * (chunk partials, combined in a fixed order: results do not depend on the launch shape).
+ * Forward: out_bf16 through out_map (halo rows cleared, see CpcRowMap) and / or out_f32 dense [rows, C].
+ * Backward: dout (bf16 or fp32, through dout_map) -> dx_bf16 through dx_map (halo rows cleared) and / or dx_f32 dense;
+ * dgamma / dbeta [C] and dxsum [C] (column sums of dx = bias gradient of the convolution in front; exactly zero under
+ * computed statistics) are ADDED atomically; `sums` is scratch of 2 * groups * C floats.
+ */
+#define CPC_COLNORM_CHUNK_ROWS 256
+enum { CPC_COLNORM_ID = 0, CPC_COLNORM_STATS = 1, CPC_COLNORM_GIVEN = 2 };
+
+typedef struct {
+  int64_t rows; int C;
+  int64_t rows_per_group;              /* 0 => one group */
+  int mode; int relu;
+  const void* in;                      /* bf16 [rows, C] */
+  const void* gamma; const void* beta; /* fp32 [C], both or neither */
+  void* mean; void* rstd;              /* fp32 [groups, C] */
+  void* running_mean; void* running_var; float momentum; float eps;
+  void* partial;
+  void* out_bf16; CpcRowMap out_map; void* out_f32;
+  const void* dout; int dout_f32; CpcRowMap dout_map;
+  void* sums;
+  void* dx_bf16; CpcRowMap dx_map; void* dx_f32;
+  void* dgamma; void* dbeta; void* dxsum;
+} CpcColNorm;
+
+int cpc_colnorm_fwd(const CpcColNorm* desc, void* stream);
+int cpc_colnorm_bwd(const CpcColNorm* desc, void* stream);
+
+/* conv0 (cpc/model.py:85) WITHOUT a fused norm, for the modes above: x fp32 [N, W] (x_stride as in CpcConv0) ->
+ * out bf16 [N * L0, C] dense = conv + bias (gamma, beta, mean, rstd, halo unused).  Backward: dout = fp32 [N * L0, C]
+ * dense gradient of that output -> dw [C, 10] ADDED atomically (the bias gradient is cpc_colnorm_bwd's dxsum). */
+int cpc_conv0_plain_fwd(const CpcConv0* desc, void* stream);
+int cpc_conv0_plain_bwd(const CpcConv0* desc, void* stream);
+
 /* conv weight fp32 [Co,Ci,k] (k == 2*s) -> bf16 GEMM operands: wf [Co, k*Ci] (forward / wgrad) and
  * wd [s*Ci, 2*Co] (dgrad; may be null).  cpc_conv_wgrad_unpack is the inverse for the fp32 gradient and ADDS
  * (red.global) into dw, so the two half-batches of a step can reduce into one zero-initialised gradient. */

@@ -99,15 +99,32 @@ def channel_norm(x, weight=None, bias=None, eps=1e-5):
     return y
 
 
-def encoder_forward(p, x, prefix="gEncoder."):
-    """cpc/model.py:102-108.  x [N,1,W] -> [N,C,W/160] (normMode layerNorm)."""
+def encoder_forward(p, x, prefix="gEncoder.", norm_mode="layerNorm", bn_training=False, stats_out=None):
+    """cpc/model.py:102-108.  x [N,1,W] -> [N,C,W/160].  norm_mode as cpc/model.py:71-82: "layerNorm" (ChannelNorm),
+    "batchNorm" (nn.BatchNorm1d: batch statistics when bn_training, else the running estimates of the state),
+    "instanceNorm" (nn.InstanceNorm1d(affine=True): always instance statistics), "ID" (no norm).  `stats_out`: list that
+    receives per layer the (batch mean, UNBIASED batch variance) BatchNorm1d folds into its running estimates."""
     for i, (_, s, pad) in enumerate(ENCODER_GEOMETRY):
         w = p[f"{prefix}conv{i}.weight"]
         x = F.conv1d(x, _w(w) if i else w, p[f"{prefix}conv{i}.bias"], stride=s, padding=pad)
-        if i:
+        if i or norm_mode != "layerNorm":  # (conv0 + ChannelNorm is one kernel; the other modes store conv0's output)
             x = _q(x)
-        x = _q(F.relu(channel_norm(x, p[f"{prefix}batchNorm{i}.weight"],
-                                   p[f"{prefix}batchNorm{i}.bias"])))
+        if norm_mode == "layerNorm":
+            x = channel_norm(x, p[f"{prefix}batchNorm{i}.weight"], p[f"{prefix}batchNorm{i}.bias"])
+        elif norm_mode == "batchNorm":
+            g, b = p[f"{prefix}batchNorm{i}.weight"], p[f"{prefix}batchNorm{i}.bias"]
+            if bn_training:
+                if stats_out is not None:
+                    stats_out.append((x.detach().mean(dim=(0, 2)), x.detach().var(dim=(0, 2), unbiased=True)))
+                x = F.batch_norm(x, None, None, g, b, training=True, eps=1e-5)
+            else:
+                x = F.batch_norm(x, p[f"{prefix}batchNorm{i}.running_mean"].detach(),
+                                 p[f"{prefix}batchNorm{i}.running_var"].detach(), g, b, training=False, eps=1e-5)
+        elif norm_mode == "instanceNorm":
+            x = F.instance_norm(x, weight=p[f"{prefix}batchNorm{i}.weight"], bias=p[f"{prefix}batchNorm{i}.bias"], eps=1e-5)
+        elif norm_mode != "ID":
+            raise ValueError(f"Norm mode must be in ['batchNorm', 'instanceNorm', 'ID', 'layerNorm']")
+        x = _q(F.relu(x))
     return x
 
 
@@ -327,9 +344,9 @@ def transformer_ar_forward(p, x, n_layers, size_seq, abspos=False, prefix="gAR."
 # model container
 # --------------------------------------------------------------------------- #
 def cpc_model_forward(p, batch, ar_mode="LSTM", n_layers=1, reverse=False, size_seq=None,
-                      abspos=False):
+                      abspos=False, norm_mode="layerNorm", bn_training=False, stats_out=None):
     """cpc/model.py:381-390 (mask_prob == 0).  batch [N,1,W] -> (c [N,S,H], z [N,S,C])."""
-    z = encoder_forward(p, batch).permute(0, 2, 1)
+    z = encoder_forward(p, batch, norm_mode=norm_mode, bn_training=bn_training, stats_out=stats_out).permute(0, 2, 1)
     if ar_mode == "transformer":
         c = transformer_ar_forward(p, z, n_layers, size_seq, abspos)
     else:
@@ -451,7 +468,7 @@ def quality_weighting(signal_quality, W, growth_rate, inflection_point_x):
 # --------------------------------------------------------------------------- #
 def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n_layers=1,
                rnn_mode="transformer", cpc_mode=None, abspos=False, n_skipped=0, with_grad=True, multihead=False,
-               signal_quality=None, growth_rate=None, inflection_point_x=None):
+               signal_quality=None, growth_rate=None, inflection_point_x=None, norm_mode="layerNorm", bn_training=False):
     """sequence [B,2,1,W] fp32.  Returns dict(loss [1,K], acc [1,K], c, z, grads{name: tensor}).
     signal_quality [B, n] (train.py:104-106): per-token loss weights through quality_weighting."""
     B = sequence.shape[0]
@@ -459,14 +476,16 @@ def train_step(p, sequence, batch_idx, seq_idx, K=12, NEG=128, ar_mode="LSTM", n
         p = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
     combined = torch.cat([sequence[:, 0], sequence[:, 1]], dim=0)       # train.py:95-99
     S = combined.shape[-1] // DOWNSAMPLING
-    c, z = cpc_model_forward(p, combined, ar_mode, n_layers, cpc_mode == "reverse", S, abspos)
+    bn_stats = []
+    c, z = cpc_model_forward(p, combined, ar_mode, n_layers, cpc_mode == "reverse", S, abspos, norm_mode, bn_training,
+                             bn_stats)
     c_past, z_future = c[:B], z[B:]                                      # train.py:102-103
     weights = None
     if signal_quality is not None:
         weights = quality_weighting(signal_quality, S - K, growth_rate, inflection_point_x)
     loss, acc = criterion_forward(p, c_past, z_future, batch_idx, seq_idx, K, NEG, rnn_mode,
                                   mode=cpc_mode, n_skipped=n_skipped, multihead=multihead, weights=weights)
-    out = {"loss": loss.detach(), "acc": acc.detach(), "c": c.detach(), "z": z.detach()}
+    out = {"loss": loss.detach(), "acc": acc.detach(), "c": c.detach(), "z": z.detach(), "bn_stats": bn_stats}
     if with_grad:
         loss.sum().backward()                                            # train.py:108-109
         out["grads"] = {k: v.grad for k, v in p.items() if v.grad is not None}

@@ -38,6 +38,13 @@ CASES = {
     # signal-quality weighted loss (criterion.py:230,334-338,350) with the first prediction step dropped (--n_skipped)
     "tiny_lstm_quality_skip1": (dict(SMALL, arMode="LSTM", rnnMode="linear", n_skipped=1, growth_rate=10.0,
                                      inflection_point_x=0.5, signal_quality=True), 3),
+    # the encoder's other norm layers (cpc/model.py:71-82).  batchNorm in TRAIN mode (batch statistics + the update of
+    # the running estimates; linear heads and an LSTM have no dropout, so train mode changes nothing else) and in eval
+    # mode (running estimates, here after three training-mode forwards moved them off (0, 1))
+    "tiny_batchnorm_train_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="batchNorm", train_mode=True), 3),
+    "tiny_batchnorm_eval_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="batchNorm", bn_warm=3), 3),
+    "tiny_instancenorm_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="instanceNorm"), 3),
+    "tiny_idnorm_linear": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="ID"), 3),
 }
 
 
@@ -56,10 +63,18 @@ def run_case(name, over, B, full=True):
     quality = None
     if over.pop("signal_quality", False):  # [B, 5] scores in (0, 1), as the dataset's per-window quality tracks
         quality = torch.rand(B, 5, generator=torch.Generator().manual_seed(99))
+    train_mode = over.pop("train_mode", False)
+    bn_warm = over.pop("bn_warm", 0)
     args = rh.reference_args(**over)
     m, crit = rh.build_reference(args, seed=0)
     seq = synthetic_sequence(B, args.sizeWindow)
-    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=False, signal_quality=quality)
+    for i in range(bn_warm):  # training-mode forwards: only BatchNorm's running estimates change
+        m.train(True)
+        with torch.no_grad():
+            m(torch.cat([synthetic_sequence(B, args.sizeWindow, 50 + i)[:, 0], synthetic_sequence(B, args.sizeWindow, 50 + i)[:, 1]]),
+              torch.zeros(2 * B, dtype=torch.long))
+    state_before = {k: v.clone() for k, v in rh.flat_state(m, crit).items()}
+    out = rh.reference_step(m, crit, seq, CRIT_SEED, train_mode=train_mode, signal_quality=quality)
     # the sampled indices, by replaying the reference's own sampleClean RNG calls
     S = args.sizeWindow // 160
     W = S - args.nPredicts
@@ -80,13 +95,16 @@ def run_case(name, over, B, full=True):
     neg_ref = sampled[0][:, 1:]  # [B,NEG,W,D] gathered by the reference
     assert torch.equal(neg_ref, z_f.contiguous().view(-1, D)[ext].view(B, -1, W, D)), \
         "replayed indices do not reproduce the reference's gather"
-    state = rh.flat_state(m, crit)
-    state = {k: v for k, v in state.items() if v.dtype.is_floating_point
+    state_after = rh.flat_state(m, crit)
+    state = {k: v for k, v in state_before.items() if v.dtype.is_floating_point
              and not k.endswith(".mask") and not k.endswith(".z")}
     fx = {
         "args": {k: getattr(args, k) for k in ("hiddenEncoder", "hiddenGar", "nPredicts", "negativeSamplingExt",
                                               "sizeWindow", "arMode", "nLevelsGRU", "rnnMode", "cpc_mode",
-                                              "abspos", "n_skipped", "multihead_rnn")},
+                                              "abspos", "n_skipped", "multihead_rnn", "normMode")},
+        "train_mode": train_mode,
+        # BatchNorm1d's running estimates AFTER the step (train mode: updated by it)
+        "running_after": {k: v.clone() for k, v in state_after.items() if ".running_" in k or k.endswith("num_batches_tracked")},
         "B": B, "crit_seed": CRIT_SEED, "seq_seed": 1234, "init_seed": 0,
         "loss": out["loss"], "acc": out["acc"],
         "fingerprint": fingerprint(state),

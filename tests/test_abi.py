@@ -47,7 +47,7 @@ def test_version_and_strerror_do_not_need_a_gpu(lib):
 
 STRUCTS = {"CpcGemmDesc": _lib.GemmDesc, "CpcRowNormFwd": _lib.RowNormFwd, "CpcRowNormBwd": _lib.RowNormBwd,
            "CpcConv0": _lib.Conv0, "CpcNce": _lib.Nce, "CpcLstm": _lib.Lstm, "CpcAttn": _lib.Attn,
-           "CpcRowMap": _lib.RowMap, "CpcAdamSpan": _lib.AdamSpan}
+           "CpcRowMap": _lib.RowMap, "CpcAdamSpan": _lib.AdamSpan, "CpcColNorm": _lib.ColNorm}
 
 
 def c_struct_fields(name):

@@ -36,6 +36,17 @@ def close(got, ref, rtol, atol, name=""):
                           f"{bad.sum().item()} / {bad.numel()} out of tolerance"
 
 
+def close_but(got, ref, rtol, atol, name="", allow=3):
+    """`close` that tolerates a few elements: a ReLU mask recomputed in another summation order can flip where the
+    pre-activation is within rounding of zero (that element's gradient then differs by its full size)."""
+    got, ref = got.float(), ref.float()
+    assert torch.isfinite(got).all(), f"{name}: non-finite"
+    err = (got - ref).abs()
+    bad = err > atol + rtol * ref.abs()
+    assert bad.sum().item() <= allow, f"{name}: max err {err.max().item():.4g} (ref max {ref.abs().max().item():.4g}), " \
+                                      f"{bad.sum().item()} / {bad.numel()} out of tolerance"
+
+
 def cos(a, b):
     return F.cosine_similarity(a.float().flatten(), b.float().flatten(), dim=0).item()
 
@@ -138,6 +149,102 @@ def test_channelnorm_relu_fwd_bwd(K, C):
     close(dg, g_.grad, 1e-3, 1e-2, "channelnorm dgamma")
     close(db, b_.grad, 1e-3, 1e-2, "channelnorm dbeta")
     close(dsum, yr.grad.sum(0), 1e-2, 3e-2, "channelnorm dxsum")
+
+
+# ------------------------------------------------------------------------------------------ column norms
+@pytest.mark.parametrize("mode,C,N,L", [("batchNorm", 256, 3, 700), ("batchNorm", 32, 2, 16), ("instanceNorm", 256, 5, 300),
+                                        ("instanceNorm", 64, 3, 513), ("batchNormEval", 128, 2, 260), ("ID", 512, 2, 100)])
+def test_colnorm_relu_fwd_bwd(K, mode, C, N, L):
+    """cpc_colnorm_fwd / _bwd (encoder normMode batchNorm / instanceNorm / ID + ReLU, cpc/model.py:71-82,102-107) against
+    torch's F.batch_norm / F.instance_norm on the same bf16-rounded input, incl. halo maps, ragged chunk counts and the
+    running-estimate update."""
+    torch.manual_seed(5)
+    halo = 2
+    y = bf(torch.randn(N * L, C, device="cuda") * 1.5 + 0.4 + torch.randn(C, device="cuda"))
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.2
+    rm0, rv0 = torch.randn(C, device="cuda") * 0.1 + 0.4, torch.rand(C, device="cuda") + 1.5
+    rm, rv = rm0.clone(), rv0.clone()
+    kind = {"batchNorm": "stats", "instanceNorm": "stats", "batchNormEval": "given", "ID": "ID"}[mode]
+    rpg = L if mode == "instanceNorm" else 0
+    groups = N if rpg else 1
+    g, b = (None, None) if mode == "ID" else (gamma, beta)
+    mean = rstd = None
+    if kind == "stats":
+        mean, rstd = torch.empty(groups * C, device="cuda"), torch.empty(groups * C, device="cuda")
+    elif kind == "given":
+        mean, rstd = rm0.clone(), torch.rsqrt(rv0 + 1e-5)
+    partial, sums = K.colnorm_scratch(N * L, C, rpg, "cuda")
+    out = torch.full((N, L + 2 * halo, C), 7.0, device="cuda", dtype=BF)
+    out32 = torch.zeros(N * L, C, device="cuda")
+    K.colnorm_fwd(y, N * L, C, kind, rows_per_group=rpg, gamma=g, beta=b, mean=mean, rstd=rstd, partial=partial,
+                  running_mean=rm if mode == "batchNorm" else None, running_var=rv if mode == "batchNorm" else None,
+                  momentum=0.1, out_bf16=out, out_map=K.rowmap(L, L + 2 * halo, halo), out_f32=out32)
+    yr = y.float().view(N, L, C).permute(0, 2, 1).contiguous().requires_grad_(True)  # [N, C, L] as the reference sees it
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm_t, rv_t = rm0.clone(), rv0.clone()
+    if mode == "batchNorm":
+        pre = F.batch_norm(yr, rm_t, rv_t, g_, b_, training=True, momentum=0.1, eps=1e-5)
+    elif mode == "batchNormEval":
+        pre = F.batch_norm(yr, rm_t, rv_t, g_, b_, training=False, eps=1e-5)
+    elif mode == "instanceNorm":
+        pre = F.instance_norm(yr, weight=g_, bias=b_, eps=1e-5)
+    else:
+        pre = yr
+    ref = torch.relu(pre).permute(0, 2, 1).reshape(N * L, C)
+    close(out32, ref, 1e-4, 2e-4, f"colnorm {mode} fwd f32")
+    close(out[:, halo:halo + L].reshape(N * L, C), ref, 1e-2, 1e-2, f"colnorm {mode} fwd bf16")
+    assert out[:, :halo].abs().max() == 0 and out[:, halo + L:].abs().max() == 0
+    if mode == "batchNorm":
+        close(rm, rm_t, 1e-4, 1e-5, "running_mean")
+        close(rv, rv_t, 1e-4, 1e-5, "running_var")
+    dout = torch.randn(N, L + 2 * halo, C, device="cuda")
+    ref.backward(dout[:, halo:halo + L].reshape(N * L, C).to(BF).float())
+    dx = torch.full((N, L + 2, C), 7.0, device="cuda", dtype=BF)
+    dx32 = torch.zeros(N * L, C, device="cuda")
+    dg, db, dsum = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    K.colnorm_bwd(bf(dout), y, N * L, C, kind, partial, sums, rows_per_group=rpg, gamma=g, beta=b, mean=mean, rstd=rstd,
+                  dout_map=K.rowmap(L, L + 2 * halo, halo), dx_bf16=dx, dx_map=K.rowmap(L, L + 2, 1), dx_f32=dx32,
+                  dgamma=None if mode == "ID" else dg, dbeta=None if mode == "ID" else db, dxsum=dsum)
+    dref = yr.grad.permute(0, 2, 1).reshape(N * L, C)
+    close_but(dx32, dref, 1e-3, 1e-3 * float(dref.abs().max()) + 1e-5, f"colnorm {mode} dx f32")
+    close_but(dx[:, 1:1 + L].reshape(N * L, C), dref, 2e-2, 2e-2 * float(dref.abs().max()), f"colnorm {mode} dx bf16")
+    assert dx[:, 0].abs().max() == 0 and dx[:, L + 1].abs().max() == 0
+    if mode != "ID":
+        close(dg, g_.grad, 1e-3, 1e-2, f"colnorm {mode} dgamma")
+        close(db, b_.grad, 1e-3, 1e-2, f"colnorm {mode} dbeta")
+    # bias gradient of the convolution in front: zero under computed statistics (torch holds rounding noise there)
+    want = dref.sum(0)
+    if kind == "stats":
+        assert dsum.abs().max() == 0 and want.abs().max() <= 1e-3 * dref.abs().sum(0).max()
+    else:
+        close(dsum, want, 1e-3, 1e-2, f"colnorm {mode} dxsum")
+    # a second call with another launch shape gives the SAME bits (fixed-order chunk combination)
+    if kind == "stats":
+        mean2, rstd2 = torch.empty_like(mean), torch.empty_like(rstd)
+        K.colnorm_fwd(y, N * L, C, kind, rows_per_group=rpg, gamma=g, beta=b, mean=mean2, rstd=rstd2, partial=partial,
+                      out_f32=out32)
+        assert torch.equal(mean, mean2) and torch.equal(rstd, rstd2)
+
+
+@pytest.mark.parametrize("C,W,N", [(32, 1600, 2), (256, 2560, 3), (512, 1765, 2), (64, 20480, 2)])
+def test_conv0_plain_fwd_bwd(K, C, W, N):
+    """conv0 without a fused norm (cpc/model.py:85: Conv1d(1, C, 10, stride 5, padding 3)) against F.conv1d."""
+    torch.manual_seed(6)
+    x = torch.randn(N, W, device="cuda") * 0.3
+    w = (torch.randn(C, 1, 10, device="cuda") * 0.3).requires_grad_(True)
+    b = (torch.randn(C, device="cuda") * 0.1).requires_grad_(True)
+    L0 = (W - 4) // 5 + 1
+    y = torch.empty(N * L0, C, device="cuda", dtype=BF)
+    K.conv0_plain_fwd(x, w.detach(), b.detach(), y, N, W, C)
+    ref = F.conv1d(x.view(N, 1, W), w, b, stride=5, padding=3)  # [N, C, L0]
+    assert ref.shape[-1] == L0
+    close(y.view(N, L0, C), ref.permute(0, 2, 1), 1e-2, 1e-2, "conv0 plain fwd")
+    dy = torch.randn(N * L0, C, device="cuda")
+    ref.backward(dy.view(N, L0, C).permute(0, 2, 1))
+    dw = torch.zeros(C, 10, device="cuda")
+    K.conv0_plain_bwd(x, dy, dw, N, W, C)
+    close(dw, w.grad.view(C, 10), 1e-3, 1e-3 * float(w.grad.abs().max()), "conv0 plain dw")
 
 
 def test_layernorm_groups_fwd_bwd(K):

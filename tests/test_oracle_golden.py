@@ -51,6 +51,35 @@ def test_step_matches_reference(golden_dir, name):
         torch.testing.assert_close(out["grads"][k], g, rtol=2e-4, atol=2e-6, msg=lambda m: f"{k}: {m}")
 
 
+NORM_CASES = ["tiny_batchnorm_train_linear", "tiny_batchnorm_eval_linear", "tiny_instancenorm_linear", "tiny_idnorm_linear"]
+
+
+@pytest.mark.parametrize("name", NORM_CASES)
+def test_encoder_norm_modes_match_reference(golden_dir, name):
+    """normMode batchNorm (training mode: batch statistics and the running-estimate update; eval mode: running
+    estimates), instanceNorm and ID (cpc/model.py:71-82) against the unmodified reference."""
+    fx = _load(golden_dir, name)
+    a = fx["args"]
+    out = oc.train_step(fx["state"], fx["sequence"], fx["batch_idx"].long(), fx["seq_idx"].long(),
+                        K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"], n_layers=a["nLevelsGRU"],
+                        rnn_mode=a["rnnMode"], norm_mode=a["normMode"], bn_training=fx["train_mode"])
+    torch.testing.assert_close(out["z"], fx["z"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out["c"], fx["c"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=1e-6)
+    assert torch.equal(out["acc"], fx["acc"])
+    assert set(out["grads"]) == set(fx["grads"])
+    for k, g in fx["grads"].items():
+        # (conv biases in front of a batch / instance norm have a mathematically zero gradient: both sides hold noise)
+        torch.testing.assert_close(out["grads"][k], g, rtol=5e-4, atol=2e-6 + 2e-5 * float(g.abs().max()), msg=lambda m: f"{k}: {m}")
+    if fx["train_mode"]:  # running estimates as nn.BatchNorm1d updates them (momentum 0.1, unbiased variance)
+        for i, (mean, var) in enumerate(out["bn_stats"]):
+            k = f"gEncoder.batchNorm{i}."
+            torch.testing.assert_close(0.9 * fx["state"][k + "running_mean"] + 0.1 * mean, fx["running_after"][k + "running_mean"],
+                                       rtol=1e-5, atol=1e-7)
+            torch.testing.assert_close(0.9 * fx["state"][k + "running_var"] + 0.1 * var, fx["running_after"][k + "running_var"],
+                                       rtol=1e-5, atol=1e-7)
+
+
 TRAINED_CASES = [c + "_trained" for c in FULL_CASES if c != "tiny_lstm_quality_skip1"] + ["mid256_lstm_transformer_trained"]
 
 

@@ -93,7 +93,17 @@ def run_step(model, crit, seq, ext=None, train_mode=False, seed=4321, signal_qua
                 grads=grads, ext=captured["ext"].cpu())
 
 
-def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, strides=None, tag="", loss_floor=0.0):
+def zero_gradient_biases(norm_mode, bn_training=True):
+    """Conv biases in front of a norm layer that removes the column mean (batch statistics, instance statistics) have a
+    mathematically ZERO gradient: the reference's autograd leaves fp32 rounding noise there (|g| ~ 1e-9, cosine floor ~ 0,
+    tests/golden/grad_floor.json) and cpc_colnorm_bwd writes exact zeros.  Nothing to compare."""
+    if norm_mode == "instanceNorm" or (norm_mode == "batchNorm" and bn_training):
+        return {f"gEncoder.conv{i}.bias" for i in range(5)}
+    return set()
+
+
+def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, strides=None, tag="", loss_floor=0.0,
+                  skip=()):
     """`floors`: per-tensor bf16-storage noise floor (see the module docstring); None = the plain 0.99 line.
     `strides`: fixtures that store big gradients as g.flatten()[::stride].
     `loss_floor`: the same floor for the loss -- |loss of the exact oracle - loss of the oracle with bf16 operands| at
@@ -107,6 +117,10 @@ def check_against(out, ref_loss, ref_acc, ref_c, ref_z, ref_grads, floors=None, 
     for k, g in ref_grads.items():
         assert k in out["grads"], f"missing grad {k}"
         if g.abs().max() == 0:
+            continue
+        if k in skip:
+            wk = k.replace(".bias", ".weight")
+            assert out["grads"][k].abs().max() <= 1e-4 * out["grads"][wk].abs().max(), f"{k} should vanish"
             continue
         st = (strides or {}).get(k, 1)
         got = out["grads"][k].flatten()[::st] if st > 1 else out["grads"][k]
@@ -136,9 +150,11 @@ GOLDEN_CASES = ["tiny_lstm_linear", "tiny_lstm_reverse_linear", "tiny_transforme
 # (tiny_rnn_hneq_linear pins the oracle only: its hidden size 24 is not one the recurrence kernels are built for)
 # the same configurations after the reference's Adam has left the ln(NEG+1) plateau, plus the default width
 TRAINED_CASES = [c + "_trained" for c in GOLDEN_CASES if c != "tiny_lstm_quality_skip1"] + ["mid256_lstm_transformer_trained"]
+# the encoder's other norm layers (cpc/model.py:71-82): batchNorm in train and eval mode, instanceNorm, ID
+NORM_CASES = ["tiny_batchnorm_train_linear", "tiny_batchnorm_eval_linear", "tiny_instancenorm_linear", "tiny_idnorm_linear"]
 
 
-@pytest.mark.parametrize("name", GOLDEN_CASES + TRAINED_CASES)
+@pytest.mark.parametrize("name", GOLDEN_CASES + TRAINED_CASES + NORM_CASES)
 def test_against_reference_golden(name):
     """CUDA path vs vectors of the UNMODIFIED reference: identical weights, inputs and sampled indices."""
     _need_gpu()
@@ -152,15 +168,25 @@ def test_against_reference_golden(name):
     missing = crit.load_state_dict(cs, strict=False)
     assert not missing.unexpected_keys
     quality = fx["signal_quality"].cuda() if "signal_quality" in fx else None
-    out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long(), signal_quality=quality)
+    train = fx.get("train_mode", False)
+    out = run_step(model, crit, fx["sequence"].cuda(), ext=fx["ext_idx"].long(), signal_quality=quality, train_mode=train)
     check_against(out, fx["loss"], fx["acc"], fx["c"], fx["z"], fx["grads"], floors=GRAD_FLOOR[name],
-                  strides=fx.get("grad_stride"), tag="golden/" + name)
+                  strides=fx.get("grad_stride"), tag="golden/" + name,
+                  skip=zero_gradient_biases(fx["args"].get("normMode", "layerNorm"), train))
+    if train:  # nn.BatchNorm1d's running estimates after the step (momentum 0.1, unbiased variance) and its step count
+        st = model.state_dict()
+        for k, v in fx["running_after"].items():
+            if k.endswith("num_batches_tracked"):
+                assert int(st[k]) == int(v), k
+            else:
+                err = (st[k].float().cpu() - v).abs().max().item()
+                assert err <= 2e-2 * max(v.abs().max().item(), 1e-3), (k, err)
 
 
 def _oracle_kwargs(args):
     return dict(K=args.nPredicts, NEG=args.negativeSamplingExt, ar_mode=args.arMode, n_layers=args.nLevelsGRU,
                 rnn_mode=args.rnnMode, cpc_mode=args.cpc_mode, abspos=args.abspos, n_skipped=args.n_skipped,
-                multihead=args.multihead_rnn)
+                multihead=args.multihead_rnn, norm_mode=args.normMode)
 
 
 def _state_for_oracle(model, crit):
@@ -199,6 +225,15 @@ ORACLE_CASES = {
                        sizeWindow=10240),
     "rnn_heads": dict(rnnMode="RNN", hiddenEncoder=128, hiddenGar=128, nPredicts=4, negativeSamplingExt=32,
                       sizeWindow=10240),
+    # the encoder's other norm layers at the default width (cpc/model.py:71-82).  `_train`: the compared step runs in
+    # TRAIN mode (batch statistics; linear heads and an LSTM have no dropout, so nothing else changes); every batchNorm
+    # case is warmed up in train mode, so its running estimates have left (0, 1) before the eval-mode comparison
+    "batchnorm_encoder_train_mode": dict(normMode="batchNorm", rnnMode="linear", _train=True),
+    "batchnorm_encoder_eval_mode": dict(normMode="batchNorm", rnnMode="linear"),
+    "instancenorm_encoder": dict(normMode="instanceNorm", rnnMode="linear"),
+    "instancenorm_encoder_hidden512_window40960": dict(normMode="instanceNorm", rnnMode="linear", hiddenEncoder=512,
+                                                       hiddenGar=512, sizeWindow=40960),
+    "id_encoder": dict(normMode="ID", rnnMode="linear"),
 }
 # cases that are ALSO compared at random initialisation (the regime round 1 tested); every case is compared after the
 # warm-up below
@@ -223,7 +258,7 @@ def predictable_sequence(B, W, seed):
     return x.view(B, 2, 1, W).contiguous()
 
 
-def warm_up(model, crit, args, B):
+def warm_up(model, crit, args, B, train_mode=False):
     """Move the model off the ln(NEG+1) plateau with torch.optim.Adam on a predictable batch (the regime the
     reference trains in: logits no longer ~0, gradients no longer cancelling sums).  Runs on the CUDA path itself --
     the comparison that follows is against the oracle evaluated at whatever state this leaves."""
@@ -233,7 +268,7 @@ def warm_up(model, crit, args, B):
     target = 0.85 * math.log(args.negativeSamplingExt + 1)
     loss = float("nan")
     for it in range(WARM_STEPS):
-        out = run_step(model, crit, seq, seed=1000 + it, collect=False)
+        out = run_step(model, crit, seq, seed=1000 + it, collect=False, train_mode=train_mode)
         opt.step()
         if it % 10 == 9:
             loss = float(out["loss"].mean())
@@ -249,14 +284,16 @@ def test_against_oracle(name):
     from cpc2_b200 import train as T
     from oracle import cpc_oracle as oc
     at_init = name.endswith("@init")
-    over = ORACLE_CASES[name.split("@")[0]]
+    over = dict(ORACLE_CASES[name.split("@")[0]])
+    train = over.pop("_train", False)
     args = T.defaultArgs(**over)
     B = 8 if args.sizeWindow <= 20480 else 4
     model, crit = build(args)
-    warm = (0, None) if at_init else warm_up(model, crit, args, B)
+    warm = (0, None) if at_init else warm_up(model, crit, args, B, train_mode=args.normMode == "batchNorm")
     seq = predictable_sequence(B, args.sizeWindow, 1234) if not at_init else \
         0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=torch.Generator().manual_seed(1234))
-    out = run_step(model, crit, seq.cuda())
+    running = {k: v.detach().float().cpu().clone() for k, v in model.state_dict().items() if ".running_" in k}
+    out = run_step(model, crit, seq.cuda(), train_mode=train)
     S = args.sizeWindow // 160
     W = S - args.nPredicts
     # the oracle consumes the very indices the GPU criterion drew: feed ext through (batch_idx, seq_idx)
@@ -268,11 +305,11 @@ def test_against_oracle(name):
     assert torch.equal(oc.negative_ext_index(batch_idx, seq_idx, B, S, W, args.negativeSamplingExt), ext)
     torch.set_num_threads(os.cpu_count())
     st = _state_for_oracle(model, crit)
-    ref = oc.train_step(st, seq, batch_idx, seq_idx, **_oracle_kwargs(args))
+    ref = oc.train_step(st, seq, batch_idx, seq_idx, bn_training=train, **_oracle_kwargs(args))
     # bf16-storage noise floor of THIS state, per tensor (module docstring): the exact algorithm with bf16 operands
     oc.EMULATE_BF16 = True
     try:
-        emu = oc.train_step(st, seq, batch_idx, seq_idx, **_oracle_kwargs(args))
+        emu = oc.train_step(st, seq, batch_idx, seq_idx, bn_training=train, **_oracle_kwargs(args))
     finally:
         oc.EMULATE_BF16 = False
     floors = {k: cosine(emu["grads"][k], g) for k, g in ref["grads"].items() if g.abs().max() > 0}
@@ -280,7 +317,13 @@ def test_against_oracle(name):
     report("oracle/" + name + "/setup", warm_steps=warm[0], warm_loss=warm[1], loss=[round(float(x), 4) for x in ref["loss"].flatten()],
            loss_floor=loss_floor, min_floor=min(floors.values()), floors_below_099=sorted((round(v, 4), k) for k, v in floors.items() if v < MIN_COS))
     check_against(out, ref["loss"], ref["acc"], ref["c"], ref["z"], ref["grads"], floors=floors, tag="oracle/" + name,
-                  loss_floor=loss_floor)
+                  loss_floor=loss_floor, skip=zero_gradient_biases(args.normMode, train))
+    if train and args.normMode == "batchNorm":  # the running estimates moved as nn.BatchNorm1d moves them
+        for i, (mean, var) in enumerate(ref["bn_stats"]):
+            for key, stat in ((f"gEncoder.batchNorm{i}.running_mean", mean), (f"gEncoder.batchNorm{i}.running_var", var)):
+                want = 0.9 * running[key] + 0.1 * stat
+                err = (st[key] - want).abs().max().item()
+                assert err <= 2e-2 * max(want.abs().max().item(), 1e-3), (key, err)
 
 
 def test_default_init_matches_reference_fingerprint():
@@ -503,14 +546,18 @@ def test_staged_adam_equals_single_launch():
             assert ((a - b).abs() > 1e-6 + 1e-4 * b.abs()).float().mean().item() <= 0.2  # (measured: 2 of 64 entries)
 
 
-def test_graphed_step_with_fused_adam_learns():
+@pytest.mark.parametrize("norm", ["layerNorm", "batchNorm", "instanceNorm"])
+def test_graphed_step_with_fused_adam_learns(norm):
     """GraphedTrainStep(optimizer=FusedAdam): forward + backward + Adam in one CUDA-graph replay; the loss on a
-    predictable batch (past == future) falls, and the device-side step counter advances once per replay."""
+    predictable batch (past == future) falls, and the device-side step counter advances once per replay.  With a
+    batchNorm encoder (not splittable: the literal concatenated call is captured) the running estimates are untouched by
+    the construction and move once per replay."""
     _need_gpu()
     from cpc2_b200 import train as T
     from cpc2_b200.optim import FusedAdam
-    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120)
+    args = T.defaultArgs(hiddenEncoder=64, hiddenGar=64, nPredicts=4, negativeSamplingExt=16, sizeWindow=5120, normMode=norm)
     model, crit = build(args)
+    assert model.splittable() == (norm == "layerNorm")
     opt = FusedAdam(list(crit.parameters()) + list(model.parameters()), lr=2e-3)
     g = torch.Generator().manual_seed(7)
     base = torch.randn(8, 1, 1, args.sizeWindow, generator=g) * 0.1
@@ -521,11 +568,16 @@ def test_graphed_step_with_fused_adam_learns():
     finally:
         opt.detach()
     n0 = float(opt._groups[0]["state"][0])
+    if norm == "batchNorm":
+        bn = model.gEncoder.batchNorm2
+        assert int(bn.num_batches_tracked) == 0 and bn.running_mean.abs().max() == 0 and (bn.running_var == 1).all()
     hist = []
     for it in range(160):
         losses, _ = step.step(seq)
         hist.append(losses.mean().item())
     assert float(opt._groups[0]["state"][0]) == n0 + 160
+    if norm == "batchNorm":
+        assert int(bn.num_batches_tracked) == 160 and bn.running_mean.abs().max() > 0
     first, last = sum(hist[:5]) / 5, sum(hist[-5:]) / 5
     assert all(h == h for h in hist) and last < first - 0.05, (first, last)
 

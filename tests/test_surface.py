@@ -13,7 +13,9 @@ from cpc2_b200 import transformers as tr
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = ["tiny_lstm_linear", "tiny_gru2_transformer", "tiny_transformer_ar_linear", "tiny_lstm_reverse_linear",
-         "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN", "tiny_lstm_quality_skip1"]
+         "tiny_rnn_hneq_linear", "tiny_lstm_multihead", "tiny_lstm_ffd", "tiny_lstm_conv4", "tiny_lstm_headsLSTM", "tiny_lstm_headsRNN", "tiny_lstm_quality_skip1",
+         # encoder normMode batchNorm / instanceNorm / ID (cpc/model.py:71-82): BatchNorm1d's running estimates are keys too
+         "tiny_batchnorm_train_linear", "tiny_instancenorm_linear", "tiny_idnorm_linear"]
 
 
 @pytest.mark.parametrize("name", CASES)

@@ -34,7 +34,8 @@ def floors_of(fx):
                             n_layers=a["nLevelsGRU"], rnn_mode=a["rnnMode"], cpc_mode=a["cpc_mode"],
                             abspos=a["abspos"], n_skipped=a["n_skipped"], multihead=a.get("multihead_rnn", False),
                             signal_quality=fx.get("signal_quality"), growth_rate=a.get("growth_rate"),
-                            inflection_point_x=a.get("inflection_point_x"))
+                            inflection_point_x=a.get("inflection_point_x"), norm_mode=a.get("normMode", "layerNorm"),
+                            bn_training=fx.get("train_mode", False))
     finally:
         oc.EMULATE_BF16 = False
     res = {}
@@ -51,8 +52,12 @@ def floors_of(fx):
 def main():
     torch.set_num_threads(os.cpu_count())
     table = {}
+    only = sys.argv[1:]  # optional: fixture names to (re)compute, the rest of the table is kept
+    if only:
+        with open(os.path.join(GOLD, "grad_floor.json")) as fh:
+            table = json.load(fh)
     for f in sorted(os.listdir(GOLD)):
-        if not f.endswith(".pt"):
+        if not f.endswith(".pt") or (only and f[:-3] not in only):
             continue
         fx = torch.load(os.path.join(GOLD, f), weights_only=False)
         if "state" not in fx or "grads" not in fx:
