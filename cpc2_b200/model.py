@@ -344,7 +344,9 @@ class _EncoderFn(torch.autograd.Function):
         # of layer l is (the other half of a pair has finished or is waited for) -- they are announced from the
         # weight-gradient side stream, so that their all-reduce and optimizer step run next to the rest of the
         # encoder's backward instead of trailing the step.  Mode 1: conv1-4 as one bucket behind conv1's weight
-        # gradient; mode 2: one bucket per layer (conv4 first; only conv1's 2 MB and conv0's 13 KB are reduced late).
+        # gradient; mode 2: one bucket per layer (conv4 first; only conv1's 2 MB and conv0's 13 KB are reduced late);
+        # mode 3: mode 1 with conv0's bucket announced FIRST, straight behind conv0's backward (which ends before conv1's
+        # weight gradient does): its reduction and update then hide behind that GEMM instead of trailing conv1-4's.
         early = ops.EARLY_ENCODER if (bool(ops.GRAD_READY) and (pair is None or pair.pending == 1)) else 0
         lay_off = [sum(sizes[:4 * l]) for l in range(6)]
         with (ops.side(6, after=after) if future else _null()):
@@ -381,14 +383,23 @@ class _EncoderFn(torch.autograd.Function):
                 K.gemm(A, K.kmajor(wd), Lout + 1, s * C, 2 * C, groups=N, out_bf16=(dxp, s * C, Lp * C))
                 dout, dout_map = dxp, K.rowmap(Lin, Lp, pd)
             n0 = sum(sizes[:4])
-            if early == 1:
+
+            def announce_main():
                 with ops.side(wg):  # behind every weight gradient of this half (this stream) and the main chain so far
                     if pair is not None and pair.first_done is not None:
                         torch.cuda.current_stream().wait_event(pair.first_done)
                     ops.grad_ready("encoder.main", gflat[n0:], ctx.params[4:], grads[4:])
+
+            if early == 1:
+                announce_main()
             dw0, db0, dg0, dbe0 = gv[0:4]
             K.conv0_bwd(ctx.x2, p[0], p[1], p[2], p[3], ctx.means[0], ctx.rstds[0], dout, dw0, db0, dg0, dbe0, N, W, C,
                         pad_next[0], x_stride=ctx.xs)
+            if early == 3:
+                if pair is not None and pair.first_done is not None:
+                    torch.cuda.current_stream().wait_event(pair.first_done)  # the other half's conv0 gradients
+                ops.grad_ready("encoder.conv0", gflat[:n0], ctx.params[:4], grads[:4])
+                announce_main()
             ops.join()
             if pair is not None:
                 pair.pending -= 1
@@ -404,7 +415,9 @@ class _EncoderFn(torch.autograd.Function):
         del ws
         if not last:
             return (None, None) + (None,) * 20
-        if early:
+        if early == 3:
+            pass  # both buckets are announced
+        elif early:
             ops.grad_ready("encoder.conv0", gflat[:n0], ctx.params[:4], grads[:4])
         else:
             ops.grad_ready("encoder", gflat, ctx.params, grads)

@@ -119,9 +119,11 @@ EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")
 
 # announce the encoder's gradients before its backward has finished (model._EncoderFn.backward): 1 = conv1-4 as one
 # bucket before conv0's backward runs, 2 = one bucket per layer as each weight gradient completes; their all-reduce and
-# optimizer step then overlap the rest of the backward instead of trailing the step.  CPC_EARLY_ENCODER=0 restores the
-# single "encoder" announcement.
-EARLY_ENCODER = int(os.environ.get("CPC_EARLY_ENCODER", "1"))
+# optimizer step then overlap the rest of the backward instead of trailing the step; 3 = as 1, with conv0's small bucket
+# announced first, straight behind conv0's backward.  CPC_EARLY_ENCODER=0 restores the single "encoder" announcement.
+# Same-box A/B (tools/ab_early_encoder.sh, two repeats): N = 2: 1.246 / 1.242 / 1.315 ms per step for modes 1 / 3 / 2,
+# N = 1: 1.079 / 1.077 / 1.082.
+EARLY_ENCODER = int(os.environ.get("CPC_EARLY_ENCODER", "3"))
 
 
 def early_ffn():

@@ -233,7 +233,11 @@ ORACLE_CASES = {
     "instancenorm_encoder": dict(normMode="instanceNorm", rnnMode="linear"),
     "instancenorm_encoder_hidden512_window40960": dict(normMode="instanceNorm", rnnMode="linear", hiddenEncoder=512,
                                                        hiddenGar=512, sizeWindow=40960),
-    "id_encoder": dict(normMode="ID", rnnMode="linear"),
+    # no normalisation: with the reference's default init every conv + ReLU shrinks the activations 0.41x, z ends up at
+    # 1e-2 of the waveform and the loss never leaves ln(NEG+1) (unmodified reference on this batch, Adam 3e-4 ... 2e-3,
+    # 150 steps: 4.86 -> 4.82) -- every gradient stays a cancelling sum.  `_conv_gain` rescales the five conv weights to
+    # variance-preserving (He) size before the warm-up, after which the reference leaves the plateau within 70 steps.
+    "id_encoder": dict(normMode="ID", rnnMode="linear", _conv_gain=6 ** 0.5),
 }
 # cases that are ALSO compared at random initialisation (the regime round 1 tested); every case is compared after the
 # warm-up below
@@ -286,9 +290,14 @@ def test_against_oracle(name):
     at_init = name.endswith("@init")
     over = dict(ORACLE_CASES[name.split("@")[0]])
     train = over.pop("_train", False)
+    conv_gain = over.pop("_conv_gain", None)
     args = T.defaultArgs(**over)
     B = 8 if args.sizeWindow <= 20480 else 4
     model, crit = build(args)
+    if conv_gain is not None:
+        with torch.no_grad():
+            for i in range(5):
+                getattr(model.gEncoder, f"conv{i}").weight.mul_(conv_gain)
     warm = (0, None) if at_init else warm_up(model, crit, args, B, train_mode=args.normMode == "batchNorm")
     seq = predictable_sequence(B, args.sizeWindow, 1234) if not at_init else \
         0.1 * torch.randn(B, 2, 1, args.sizeWindow, generator=torch.Generator().manual_seed(1234))
