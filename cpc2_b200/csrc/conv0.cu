@@ -15,6 +15,8 @@
 // audio) and reduces dW / db with a further MMA whose reduction index is the frame:
 //     D[16 x C] += A1[16 x 16 frames] . (dy_hi + dy_lo),   A1 rows 0..9 = x_hi taps, row 10 = ones (-> db)
 // (dy reaches the B-fragment layout through movmatrix.trans); dgamma / dbeta accumulate in fp32 registers.
+#include <cstdlib>
+
 #include "cpc_internal.h"
 #include "ptx.cuh"
 
@@ -320,6 +322,29 @@ __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0A
   const uint32_t sA_addr = smem_u32(sA), sA1_addr = smem_u32(sA1), sB_addr = smem_u32(sB);
   const float invC = 1.f / (float)a.C, invCm1 = 1.f / (float)(a.C - 1);
   int phase = 0;
+  // Everything a tile reads from global memory (its 16 x CW slice of dout, mean and rstd of its rows) is requested ONE
+  // TILE AHEAD (8 warps per SM and a block barrier in every tile leave nothing else to cover the round trip).  Measured:
+  // 72.9 -> 72.3 us for the step's two launches -- the loads were not what the kernel waits for; a tile is ~3000
+  // dependent instructions per warp (conv MMAs, 32 elements of fp32 arithmetic per thread, barrier, weight-gradient
+  // MMAs) on two warps per scheduler.  Kept: it costs no registers (178 against 180).
+  uint32_t dv[NT][2], dvn[NT][2];
+  float rs0 = 0.f, rs1 = 0.f, mn0 = 0.f, mn1 = 0.f, rs0n = 0.f, rs1n = 0.f, mn0n = 0.f, mn1n = 0.f;
+  auto load_tile = [&](int n, int tt, uint32_t (&d)[NT][2], float& r0, float& r1, float& m0, float& m1) {
+    const bool v0 = tt + g < a.L0, v1 = tt + g + 8 < a.L0;
+    const long long row = (long long)n * a.L0 + tt;
+    r0 = v0 ? __ldg(a.rstd + row + g) : 0.f;
+    r1 = v1 ? __ldg(a.rstd + row + g + 8) : 0.f;
+    m0 = v0 ? __ldg(a.mean + row + g) : 0.f;
+    m1 = v1 ? __ldg(a.mean + row + g + 8) : 0.f;
+    const __nv_bfloat16* dr0 = a.dout + ((long long)n * Lp + a.halo + tt + g) * a.C + c0 + 2 * q;
+    const __nv_bfloat16* dr1 = dr0 + 8LL * a.C;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      d[j][0] = v0 ? __ldg(reinterpret_cast<const unsigned int*>(dr0 + 8 * j)) : 0u;
+      d[j][1] = v1 ? __ldg(reinterpret_cast<const unsigned int*>(dr1 + 8 * j)) : 0u;
+    }
+  };
+  if ((int)blockIdx.x < items) load_tile(blockIdx.x / ipw, (blockIdx.x % ipw) * STRIPB, dv, rs0, rs1, mn0, mn1);
 #pragma unroll 1
   for (int item = blockIdx.x; item < items; item += gridDim.x) {
     const int n = item / ipw, t0 = (item % ipw) * STRIPB;
@@ -330,18 +355,19 @@ __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0A
     for (int tile = 0; tile < STRIPB / 16; ++tile, phase ^= 1) {
       const int tt = t0 + tile * 16;
       if (tt >= a.L0) break;  // uniform over the CTA
-      const bool v0 = tt + g < a.L0, v1 = tt + g + 8 < a.L0;
-      const long long row = (long long)n * a.L0 + tt;
-      const float rstd0 = v0 ? __ldg(a.rstd + row + g) : 0.f, rstd1 = v1 ? __ldg(a.rstd + row + g + 8) : 0.f;
-      const float nm0 = v0 ? -__ldg(a.mean + row + g) * rstd0 : 0.f, nm1 = v1 ? -__ldg(a.mean + row + g + 8) * rstd1 : 0.f;
-      const __nv_bfloat16* dr0 = a.dout + ((long long)n * Lp + a.halo + tt + g) * a.C + c0 + 2 * q;
-      const __nv_bfloat16* dr1 = dr0 + 8LL * a.C;
-      uint32_t dv[NT][2];
-#pragma unroll
-      for (int j = 0; j < NT; ++j) {
-        dv[j][0] = v0 ? __ldg(reinterpret_cast<const unsigned int*>(dr0 + 8 * j)) : 0u;
-        dv[j][1] = v1 ? __ldg(reinterpret_cast<const unsigned int*>(dr1 + 8 * j)) : 0u;
+      {  // the tile this CTA processes next: the following one of this item, else the first one of its next item
+        int nn = n, ntt = tt + 16;
+        bool more = tile + 1 < STRIPB / 16 && ntt < a.L0;
+        if (!more) {
+          const int ni = item + gridDim.x;
+          more = ni < items;
+          nn = ni / ipw;
+          ntt = (ni % ipw) * STRIPB;
+        }
+        if (more) load_tile(nn, ntt, dvn, rs0n, rs1n, mn0n, mn1n);
       }
+      const float rstd0 = rs0, rstd1 = rs1;
+      const float nm0 = -mn0 * rstd0, nm1 = -mn1 * rstd1;
       float acc[NT][4];
       conv_tile<NT>(acc, sB_addr, c0, sA_addr, tile, lane);
       float s1a = 0.f, s2a = 0.f, s1b = 0.f, s2b = 0.f;
@@ -400,6 +426,9 @@ __global__ void __launch_bounds__(32 * NW) conv0_cn_relu_bwd_kernel(const Conv0A
         const uint32_t l23 = pack_bf16x2(dy2 - __uint_as_float(h23 << 16), dy3 - __uint_as_float(h23 & 0xffff0000u));
         mma_bf16_16816(D[j], a1, movmatrix_t(l01), movmatrix_t(l23));
       }
+#pragma unroll
+      for (int j = 0; j < NT; ++j) { dv[j][0] = dvn[j][0]; dv[j][1] = dvn[j][1]; }
+      rs0 = rs0n; rs1 = rs1n; mn0 = mn0n; mn1 = mn1n;
     }
   }
   // D rows: thread holds m = g (taps 0..7) in D[j][0..1] and m = g + 8 (taps 8, 9, db) in D[j][2..3]
@@ -493,6 +522,10 @@ extern "C" int cpc_conv0_cn_relu_bwd(const CpcConv0* d, void* stream_) {
   if (a.dout == nullptr || a.dw == nullptr || a.db == nullptr || a.dgamma == nullptr || a.dbeta == nullptr ||
       a.mean == nullptr || a.rstd == nullptr)
     return CPC_ERR_ARG;
+  // 64 channels per warp (NT = 8, ~180 registers, 8 warps per SM).  32 channels per warp (NT = 4, 128 registers, 16 warps
+  // per SM) was tried: per launch inside the step 36 -> 31 us, but the whole step got 0.4 % SLOWER (1.069 -> 1.074 ms,
+  // same box, two repeats: twice the resident warps next to the side-stream weight-gradient GEMMs this kernel overlaps)
+  // and alone with a cold L2 it is slower too (47 -> 53 us for 16 windows); profiles/r02_ab_conv0_bwd.txt.
   const int items = a.N * ((a.L0 + STRIPB - 1) / STRIPB);
   const size_t smem = STRIPB * 96 + (size_t)a.C * 64 + 2 * NW * 16 * 8 + (size_t)a.C * 8;
   int sms = 148, dev = 0;

@@ -113,7 +113,9 @@ _SIDE = {}
 # priority of the stream GraphedTrainStep captures on (-1 = above the side streams, 0 = same; CPC_MAIN_PRIORITY)
 MAIN_PRIORITY = int(os.environ.get("CPC_MAIN_PRIORITY", "-1"))
 # announce the heads' feed-forward gradients (3/4 of all parameters) a third of the way into their backward:
-# "auto" = when gradients are all-reduced (world > 1; +1 % at N = 8, neutral at N = 1), "1" / "0" force it
+# "auto" = when gradients are all-reduced across MORE THAN TWO ranks (+1 % at N = 8 in round 1, neutral at N = 1; at N = 2
+# the extra bucket costs more than its early start buys: 1.229 ms per step without against 1.243 / 1.246 with it, same
+# box, profiles/r02_ab_n2_adam.txt), "1" / "0" force it
 EARLY_FFN = os.environ.get("CPC_EARLY_FFN", "auto")
 
 
@@ -129,7 +131,7 @@ EARLY_ENCODER = int(os.environ.get("CPC_EARLY_ENCODER", "3"))
 def early_ffn():
     if EARLY_FFN == "auto":
         import torch.distributed as dist
-        return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 2
     return EARLY_FFN not in ("0", False)
 
 _PENDING = []
