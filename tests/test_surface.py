@@ -97,3 +97,31 @@ def test_checkpoint_layout_round_trip(tmp_path):
     for (k, a), (_, b) in zip(crit.state_dict().items(), crit2.state_dict().items()):
         assert torch.equal(a, b), k
     assert all(k.startswith(("gEncoder.", "gAR.")) for k in state["gEncoder"])
+
+
+def test_encoder_norm_modes_surface_and_plan():
+    """normMode batchNorm / instanceNorm / ID (cpc/model.py:71-82): the reference's norm modules are the parameter
+    containers, the step is not splittable into past / future halves, and the launch plan follows nn.BatchNorm1d's
+    semantics (training: batch statistics + one step of the running estimates; eval: the running estimates)."""
+    for mode, cls in (("batchNorm", torch.nn.BatchNorm1d), ("instanceNorm", torch.nn.InstanceNorm1d), ("ID", M.IDModule)):
+        enc = M.CPCEncoder(32, normMode=mode)
+        assert all(isinstance(getattr(enc, f"batchNorm{i}"), cls) for i in range(5))
+        assert len(enc._params()) == (10 if mode == "ID" else 20)
+        model = M.CPCModel(enc, M.CPCAR(32, 32, False, 1, mode="LSTM"))
+        assert not model.splittable()
+    assert M.CPCModel(M.CPCEncoder(32), M.CPCAR(32, 32, False, 1, mode="LSTM")).splittable()
+    enc = M.CPCEncoder(32, normMode="batchNorm")
+    enc.train()
+    plan = M._ColPlan(enc, None)
+    assert [d["kind"] for d in plan.layers] == ["stats"] * 5 and plan.layers[0]["rm"] is enc.batchNorm0.running_mean
+    assert plan.layers[0]["momentum"] == 0.1 and all(int(getattr(enc, f"batchNorm{i}").num_batches_tracked) == 1 for i in range(5))
+    enc.eval()
+    plan = M._ColPlan(enc, None)
+    assert [d["kind"] for d in plan.layers] == ["given"] * 5 and int(enc.batchNorm0.num_batches_tracked) == 1
+    enc.batchNorm2.momentum = None
+    enc.train()
+    with pytest.raises(NotImplementedError):
+        M._ColPlan(enc, None)
+    inst = M._ColPlan(M.CPCEncoder(32, normMode="instanceNorm").eval(), None)   # instance statistics in eval mode too
+    assert [d["kind"] for d in inst.layers] == ["stats"] * 5 and inst.layers[0]["rm"] is None
+    assert [d["kind"] for d in M._ColPlan(M.CPCEncoder(32, normMode="ID"), None).layers] == ["ID"] * 5
