@@ -599,6 +599,46 @@ def run_ours(opt, out):
             out.emit(json.dumps(line))
         finish(ctx)
         return
+    # At N > 1 an extra section that fails on one rank takes the job down (see `guarded`): the headline region above is
+    # complete and valid at that point, so rank 0 still prints its line -- with the failure named in `configs` -- from the
+    # exception path, or from SIGTERM when torchrun stops it because ANOTHER rank died.
+    emitted = []
+
+    def emit_headline(note):
+        if rank == 0 and not emitted:
+            emitted.append(True)
+            line.setdefault("configs", {})
+            line["configs"]["error"] = note
+            out.emit(json.dumps(line))
+
+    if world > 1 and rank == 0:
+        # a Python-level handler would only run once the main thread is back in the interpreter, and here it may sit in a
+        # collective that never completes: the C-level handler writes the signal number to a pipe a watcher thread reads
+        import signal
+        rfd, wfd = os.pipe()
+        os.set_blocking(wfd, False)
+        signal.signal(signal.SIGTERM, lambda signum, frame: None)
+        signal.set_wakeup_fd(wfd, warn_on_full_buffer=False)
+
+        def on_term():
+            os.read(rfd, 1)
+            emit_headline("terminated during the extra sections (another rank failed); the headline region is complete")
+            os._exit(1)
+
+        threading.Thread(target=on_term, daemon=True).start()
+    try:
+        run_extras(opt, out, ctx, line, args, B, pk, extra_steps, guarded)
+    except BaseException as e:
+        if world > 1:
+            emit_headline(f"{type(e).__name__}: {str(e)[:300]}")
+        raise
+    if rank == 0 and not emitted:
+        out.emit(json.dumps(line))
+    finish(ctx)
+
+
+def run_extras(opt, out, ctx, line, args, B, pk, extra_steps, guarded):
+    world, rank = ctx.world, ctx.rank
     configs = {}
     configs["config3_transformer_ar"] = guarded(
         measure_extra_config, ctx, "CPC with transformer AR (1 layer, sizeSeq 128, rel-pos; feature_loader.py:216-220), "
@@ -618,9 +658,6 @@ def run_ours(opt, out):
         line["stock_gpu"] = guarded(stock_gpu_numbers, ctx, B, 5 if opt.quick else 10)
         torch.cuda.empty_cache()
         line["cpu_baseline"] = guarded(cpu_baseline, args, B, 2, 1)
-    if rank == 0:
-        out.emit(json.dumps(line))
-    finish(ctx)
 
 
 def finish(ctx):
