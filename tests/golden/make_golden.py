@@ -145,6 +145,10 @@ TRAINED = {
     **{k + "_trained": (v[0], max(v[1], 4), 900) for k, v in CASES.items() if k != "tiny_lstm_quality_skip1"},
     # the default WIDTH (256 channels, 8 attention heads of 32: the tensor-core attention kernels) with transformer
     # prediction heads on a short window; big tensors are stored as strided samples to keep the fixture small
+    # encoder norm variants away from init (oracle pin only, tests/test_oracle_golden.py): instance statistics, and
+    # BatchNorm1d on its running estimates (the optimiser steps of this generator run in eval mode)
+    "tiny_instancenorm_linear_trained": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="instanceNorm"), 4, 900),
+    "tiny_batchnorm_eval_linear_trained": (dict(SMALL, arMode="LSTM", rnnMode="linear", normMode="batchNorm"), 4, 900),
     "mid256_lstm_transformer_trained": (dict(hiddenEncoder=256, hiddenGar=256, nPredicts=2, negativeSamplingExt=16,
                                              sizeWindow=5120, arMode="LSTM", rnnMode="transformer"), 4, 420),
 }
@@ -196,7 +200,7 @@ def run_trained_case(name, over, B, max_steps):
     fx = {
         "args": {k: getattr(args, k) for k in ("hiddenEncoder", "hiddenGar", "nPredicts", "negativeSamplingExt",
                                               "sizeWindow", "arMode", "nLevelsGRU", "rnnMode", "cpc_mode",
-                                              "abspos", "n_skipped", "multihead_rnn")},
+                                              "abspos", "n_skipped", "multihead_rnn", "normMode")},
         "B": B, "crit_seed": CRIT_SEED, "seq_seed": 1234, "init_seed": 0, "trained_steps": steps, "train_lr": TRAIN_LR,
         "loss": out["loss"], "acc": out["acc"], "torch": torch.__version__,
         "batch_idx": batch_idx.int(), "seq_idx": seq_idx.int(), "ext_idx": ext.int(),

@@ -109,6 +109,25 @@ def test_step_matches_reference_away_from_init(golden_dir, name):
         assert abs(float(out["grads"][k].double().norm()) - fx["grad_norm"][k]) <= 1e-4 * fx["grad_norm"][k] + 1e-12, k
 
 
+@pytest.mark.parametrize("name", ["tiny_instancenorm_linear_trained", "tiny_batchnorm_eval_linear_trained"])
+def test_encoder_norm_modes_match_reference_away_from_init(golden_dir, name):
+    """The norm-mode pin after the reference's own Adam has moved the weights (instance statistics; BatchNorm1d on its
+    running estimates, where nothing normalises and the activations have grown)."""
+    fx = _load(golden_dir, name)
+    a = fx["args"]
+    state = {k: v.float() for k, v in fx["state"].items()}
+    out = oc.train_step(state, fx["sequence"], fx["batch_idx"].long(), fx["seq_idx"].long(),
+                        K=a["nPredicts"], NEG=a["negativeSamplingExt"], ar_mode=a["arMode"], n_layers=a["nLevelsGRU"],
+                        rnn_mode=a["rnnMode"], norm_mode=a["normMode"], bn_training=False)
+    torch.testing.assert_close(out["z"], fx["z"], rtol=1e-4, atol=1e-5 * max(1.0, float(fx["z"].abs().max())))
+    torch.testing.assert_close(out["c"], fx["c"], rtol=1e-4, atol=2e-5)
+    torch.testing.assert_close(out["loss"], fx["loss"], rtol=1e-5, atol=2e-6)
+    assert torch.equal(out["acc"], fx["acc"])
+    assert set(out["grads"]) == set(fx["grads"])
+    for k, g in fx["grads"].items():
+        torch.testing.assert_close(out["grads"][k], g, rtol=5e-4, atol=2e-6 + 2e-5 * float(g.abs().max()), msg=lambda m: f"{k}: {m}")
+
+
 def test_full_size_default_step_matches_reference_summary(golden_dir):
     """BASELINE.json configs[0] at its real size (encoder 256, LSTM 256, 12 transformer heads, 128 negatives, window
     20480, batch 8): the oracle's losses, activations, sampled indices and EVERY gradient (norm + a 64-element strided
